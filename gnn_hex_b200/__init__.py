@@ -1,0 +1,9 @@
+"""gnn_hex_b200 -- B200-native fused forward/backward of GNN_Hex's `modern_two_headed` Q-network.
+
+The package is a thin host layer over libhexgnn.so (include/hexgnn.h).  Importing it never builds
+or falls back: a missing library raises on first use (python -m gnn_hex_b200.build).
+"""
+from ._lib import HexGnnError  # noqa: F401
+from .models import ModernTwoHeaded, get_pre_defined  # noqa: F401
+from .ops import CsrBlob, build_csr, fused_backward, fused_forward  # noqa: F401
+from . import data  # noqa: F401

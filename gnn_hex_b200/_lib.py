@@ -1,0 +1,117 @@
+"""ctypes binding of libhexgnn.so (include/hexgnn.h).  Fails loudly when the library is missing:
+there is no CPU or stock-PyTorch fallback for the product path."""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libhexgnn.so")
+
+HEXGNN_ADV_ONLY = 1
+HEXGNN_SEPARATE = 2
+HEXGNN_PATH_SIMT = 0x100
+HEXGNN_PATH_TC = 0x200
+
+ST_GRAPH_TOO_LARGE = 1
+ST_EDGE_CROSSES = 2
+ST_BATCH_UNSORTED = 4
+ST_FLAG_MIXED = 8
+STATUS_NAMES = {
+    ST_GRAPH_TOO_LARGE: "a graph has more nodes/edges than one tile holds (raise tile_rows)",
+    ST_EDGE_CROSSES: "an edge joins two different graphs or is out of range",
+    ST_BATCH_UNSORTED: "`batch` is not sorted / out of range",
+    ST_FLAG_MIXED: "x[:,2] is not constant over the batch (reference asserts this, GN0/models.py:538)",
+}
+
+ABI_VERSION = 2
+
+
+class HexModelDesc(C.Structure):
+    _fields_ = [("hidden", C.c_int32), ("num_layers", C.c_int32), ("num_head_layers", C.c_int32),
+                ("in_channels", C.c_int32)]
+
+
+class HexSizes(C.Structure):
+    _fields_ = [("csr_bytes", C.c_int64), ("fwd_ws_bytes", C.c_int64), ("stash_bytes", C.c_int64),
+                ("bwd_ws_bytes", C.c_int64), ("hidden_padded", C.c_int64)]
+
+
+class HexCsrLayout(C.Structure):
+    _fields_ = [("status", C.c_int64), ("ntiles", C.c_int64), ("gptr", C.c_int64), ("rowptr", C.c_int64),
+                ("col", C.c_int64), ("tile_g0", C.c_int64), ("scratch", C.c_int64), ("total_words", C.c_int64)]
+
+
+EXPORTS = ["hexgnn_abi_version", "hexgnn_last_error", "hexgnn_param_count", "hexgnn_param_offsets",
+           "hexgnn_sizes", "hexgnn_csr_layout", "hexgnn_build_csr", "hexgnn_forward", "hexgnn_backward"]
+
+_lib = None
+
+
+class HexGnnError(RuntimeError):
+    pass
+
+
+def lib():
+    """Load libhexgnn.so once.  Raises if it has not been built (python -m gnn_hex_b200.build)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise HexGnnError(f"{LIB_PATH} is missing: build it with `python -m gnn_hex_b200.build` "
+                          "(nvcc, sm_100a).  There is no fallback path.")
+    l = C.CDLL(LIB_PATH)
+    p, i32, i64, sz = C.c_void_p, C.c_int32, C.c_int64, C.c_size_t
+    D = C.POINTER(HexModelDesc)
+    l.hexgnn_abi_version.restype = C.c_int
+    l.hexgnn_abi_version.argtypes = []
+    l.hexgnn_last_error.restype = C.c_char_p
+    l.hexgnn_last_error.argtypes = []
+    l.hexgnn_param_count.restype = i64
+    l.hexgnn_param_count.argtypes = [D]
+    l.hexgnn_param_offsets.restype = i32
+    l.hexgnn_param_offsets.argtypes = [D, C.POINTER(i64), i32]
+    l.hexgnn_sizes.restype = C.c_int
+    l.hexgnn_sizes.argtypes = [D, i64, i64, i64, i32, C.POINTER(HexSizes)]
+    l.hexgnn_csr_layout.restype = C.c_int
+    l.hexgnn_csr_layout.argtypes = [i64, i64, i64, C.POINTER(HexCsrLayout)]
+    l.hexgnn_build_csr.restype = C.c_int
+    l.hexgnn_build_csr.argtypes = [p, i64, p, p, i64, i64, i32, p, sz, p]
+    l.hexgnn_forward.restype = C.c_int
+    l.hexgnn_forward.argtypes = [D, p, p, i64, i64, i64, p, i32, i32, p, p, p, p, sz, p]
+    l.hexgnn_backward.restype = C.c_int
+    l.hexgnn_backward.argtypes = [D, p, p, i64, i64, i64, p, i32, i32, p, p, p, p, p, p, sz, p]
+    v = l.hexgnn_abi_version()
+    if v != ABI_VERSION:
+        raise HexGnnError(f"libhexgnn.so ABI {v} != binding ABI {ABI_VERSION}: rebuild")
+    _lib = l
+    return l
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = lib().hexgnn_last_error().decode(errors="replace")
+        raise HexGnnError(f"{what} failed (code {rc}): {msg}")
+
+
+def make_desc(hidden, num_layers, num_head_layers):
+    return HexModelDesc(int(hidden), int(num_layers), int(num_head_layers), 2)
+
+
+def sizes(desc, N, E, B, tile_rows):
+    s = HexSizes()
+    check(lib().hexgnn_sizes(C.byref(desc), N, E, B, tile_rows, C.byref(s)), "hexgnn_sizes")
+    return s
+
+
+def csr_layout(N, E, B):
+    l = HexCsrLayout()
+    check(lib().hexgnn_csr_layout(N, E, B, C.byref(l)), "hexgnn_csr_layout")
+    return l
+
+
+def param_offsets(desc):
+    n = lib().hexgnn_param_offsets(C.byref(desc), None, 0)
+    if n < 0:
+        check(n, "hexgnn_param_offsets")
+    arr = (C.c_int64 * n)()
+    lib().hexgnn_param_offsets(C.byref(desc), arr, n)
+    return list(arr)

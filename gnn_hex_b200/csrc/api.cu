@@ -1,0 +1,149 @@
+// C-ABI of libhexgnn.so (declared in include/hexgnn.h).
+#include <stdarg.h>
+#include <string.h>
+#include "common.cuh"
+
+namespace hexgnn {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int bwd_grid_ctas() {
+  static int sms = 0;  // immutable after first use
+  if (sms == 0) {
+    int dev = 0, v = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess &&
+        cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0)
+      sms = v;
+    else
+      sms = 148;
+  }
+  return sms;
+}
+
+static bool tile_rows_ok(int tile_rows) { return tile_rows == 128; }
+
+}  // namespace hexgnn
+
+using namespace hexgnn;
+
+extern "C" {
+
+int hexgnn_abi_version(void) { return HEXGNN_ABI_VERSION; }
+const char* hexgnn_last_error(void) { return g_err; }
+
+int64_t hexgnn_param_count(const HexModelDesc* desc) {
+  Dims d;
+  if (!make_dims(desc, &d)) { set_error("bad model descriptor"); return HEXGNN_E_BADARG; }
+  ParamMap pm;
+  make_param_map(d, &pm);
+  return pm.total;
+}
+
+int32_t hexgnn_param_offsets(const HexModelDesc* desc, int64_t* offsets, int32_t max_entries) {
+  Dims d;
+  if (!make_dims(desc, &d)) { set_error("bad model descriptor"); return HEXGNN_E_BADARG; }
+  ParamMap pm;
+  make_param_map(d, &pm);
+  int32_t n = 0;
+  auto put = [&](int64_t o) { if (offsets && n < max_entries) offsets[n] = o; ++n; };
+  for (int s = 0; s < d.L; ++s) { put(sage_wl(pm, 0, s)); put(sage_bl(pm, 0, s, d.H)); put(sage_wr(pm, 0, s, d.H)); }
+  for (int h = 0; h < 2; ++h) {
+    for (int s = d.L; s < d.Lt; ++s) { put(sage_wl(pm, h, s)); put(sage_bl(pm, h, s, d.H)); put(sage_wr(pm, h, s, d.H)); }
+    put(pm.lin_w[h]); put(pm.lin_b[h]); put(pm.v0_w[h]); put(pm.v0_b[h]); put(pm.v1_w[h]); put(pm.v1_b[h]);
+  }
+  return n;
+}
+
+int hexgnn_csr_layout(int64_t N, int64_t E, int64_t B, HexCsrLayout* out) {
+  if (!out || N < 0 || E < 0 || B < 0) { set_error("csr_layout: bad argument"); return HEXGNN_E_BADARG; }
+  csr_layout(N, E, B, out);
+  return HEXGNN_OK;
+}
+
+int hexgnn_sizes(const HexModelDesc* desc, int64_t N, int64_t E, int64_t B, int32_t tile_rows, HexSizes* out) {
+  Dims d;
+  if (!make_dims(desc, &d) || !out || N < 0 || E < 0 || B < 0) { set_error("sizes: bad argument"); return HEXGNN_E_BADARG; }
+  if (!tile_rows_ok(tile_rows) || d.NJ > 8) {
+    set_error("sizes: unsupported tile_rows=%d or hidden=%d", tile_rows, d.H);
+    return HEXGNN_E_UNSUPPORTED;
+  }
+  HexCsrLayout l;
+  csr_layout(N, E, B, &l);
+  GradLayout gl;
+  grad_layout(d, &gl);
+  out->csr_bytes = l.total_words * 4;
+  out->fwd_ws_bytes = pack_floats(d) * 4;
+  out->stash_bytes = (int64_t)d.Lt * N * d.Hp * 4;
+  out->bwd_ws_bytes = (pack_floats(d) + (int64_t)(bwd_grid_ctas() + 1) * gl.total) * 4;
+  out->hidden_padded = d.Hp;
+  return HEXGNN_OK;
+}
+
+int hexgnn_build_csr(const int64_t* edge_index, int64_t E, const int64_t* batch, const int64_t* ptr, int64_t N,
+                     int64_t B, int32_t tile_rows, void* csr, size_t csr_bytes, void* stream) {
+  if (N < 0 || E < 0 || B < 1 || !csr || (E > 0 && !edge_index)) { set_error("build_csr: bad argument"); return HEXGNN_E_BADARG; }
+  if (N >= (1ll << 31) - 8 || E >= (1ll << 31) - 8) { set_error("build_csr: N/E exceed int32"); return HEXGNN_E_UNSUPPORTED; }
+  if (!batch && !ptr && B != 1) { set_error("build_csr: B must be 1 when neither batch nor ptr is given"); return HEXGNN_E_BADARG; }
+  if (!tile_rows_ok(tile_rows)) { set_error("build_csr: unsupported tile_rows=%d", tile_rows); return HEXGNN_E_UNSUPPORTED; }
+  HexCsrLayout l;
+  csr_layout(N, E, B, &l);
+  if ((int64_t)csr_bytes < l.total_words * 4) { set_error("build_csr: csr blob too small (%zu < %lld)", csr_bytes, (long long)l.total_words * 4); return HEXGNN_E_WORKSPACE; }
+  return launch_build_csr(edge_index, E, batch, ptr, N, B, tile_rows, csr, (cudaStream_t)stream);
+}
+
+int hexgnn_forward(const HexModelDesc* desc, const float* params, const float* x, int64_t N, int64_t E, int64_t B,
+                   const void* csr, int32_t tile_rows, int32_t flags, float* out_nodes, float* out_value,
+                   float* stash, void* ws, size_t ws_bytes, void* stream) {
+  Dims d;
+  if (!make_dims(desc, &d)) { set_error("forward: bad model descriptor"); return HEXGNN_E_BADARG; }
+  if (!params || !x || !csr || !out_nodes || !ws || N < 1 || B < 1 || E < 0) { set_error("forward: bad argument"); return HEXGNN_E_BADARG; }
+  if ((flags & HEXGNN_SEPARATE) && !out_value) { set_error("forward: SEPARATE needs out_value"); return HEXGNN_E_BADARG; }
+  if (!tile_rows_ok(tile_rows) || d.NJ > 8) { set_error("forward: unsupported tile_rows=%d or hidden=%d", tile_rows, d.H); return HEXGNN_E_UNSUPPORTED; }
+  if ((int64_t)ws_bytes < pack_floats(d) * 4) { set_error("forward: workspace too small"); return HEXGNN_E_WORKSPACE; }
+  ParamMap pm;
+  make_param_map(d, &pm);
+  PackView pv = pack_view(ws, d);
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc = launch_pack(d, pm, params, x, pv, false, st);
+  if (rc) return rc;
+  if (flags & HEXGNN_PATH_TC) { set_error("forward: tcgen05 path not built for this shape"); return HEXGNN_E_UNSUPPORTED; }
+  return launch_forward_simt(d, pm, params, x, N, E, B, csr, tile_rows, flags, out_nodes, out_value, stash, pv, st);
+}
+
+int hexgnn_backward(const HexModelDesc* desc, const float* params, const float* x, int64_t N, int64_t E, int64_t B,
+                    const void* csr, int32_t tile_rows, int32_t flags, const float* d_nodes, const float* d_value,
+                    const float* stash, float* grad_params, float* d_embeds, void* ws, size_t ws_bytes,
+                    void* stream) {
+  Dims d;
+  if (!make_dims(desc, &d)) { set_error("backward: bad model descriptor"); return HEXGNN_E_BADARG; }
+  if (!params || !x || !csr || !d_nodes || !stash || !grad_params || !ws || N < 1 || B < 1 || E < 0) { set_error("backward: bad argument"); return HEXGNN_E_BADARG; }
+  if (!tile_rows_ok(tile_rows) || d.NJ > 8) { set_error("backward: unsupported tile_rows=%d or hidden=%d", tile_rows, d.H); return HEXGNN_E_UNSUPPORTED; }
+  GradLayout gl;
+  grad_layout(d, &gl);
+  const int nparts = bwd_grid_ctas();
+  const int64_t need = (pack_floats(d) + (int64_t)(nparts + 1) * gl.total) * 4;
+  if ((int64_t)ws_bytes < need) { set_error("backward: workspace too small (%zu < %lld)", ws_bytes, (long long)need); return HEXGNN_E_WORKSPACE; }
+  ParamMap pm;
+  make_param_map(d, &pm);
+  PackView pv = pack_view(ws, d);
+  float* partials = (float*)ws + pack_floats(d);
+  float* packed_sum = partials + (int64_t)nparts * gl.total;
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc = launch_pack(d, pm, params, x, pv, true, st);
+  if (rc) return rc;
+  if (flags & HEXGNN_PATH_TC) { set_error("backward: tcgen05 path not built for this shape"); return HEXGNN_E_UNSUPPORTED; }
+  rc = launch_backward_simt(d, pm, params, x, N, E, B, csr, tile_rows, flags, d_nodes, d_value, stash, d_embeds, pv,
+                            partials, st);
+  if (rc) return rc;
+  CsrView cv = csr_view(const_cast<void*>(csr), N, E, B);
+  return launch_reduce_grads(d, pm, x, partials, nparts, cv.ntiles, packed_sum, grad_params, st);
+}
+
+}  // extern "C"

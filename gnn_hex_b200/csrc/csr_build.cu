@@ -1,0 +1,160 @@
+// Device-side CSR builder: edge_index [2,E] int64 (+ batch / ptr) -> destination-sorted CSR + tiles.
+//
+// Replaces, for the kernels' needs, the host chain graph -> edge_index -> Batch of the reference
+// (GN0/util/convert_graph.py:99-117, Batch.from_data_list at Rainbow/common/replay_buffer.py:215-216,
+// cpp_hex/hex_graph_game/util.cpp:22-41).  Contract (bit-exact, tests/test_csr.py):
+//   rowptr[i]  = #edges with destination < i
+//   col[...]   = sources of the edges stably sorted by destination (ties keep input order)
+// Integer work, HBM/L2-latency bound: 16 B per edge in, 4 B per edge + 4 B per node out.
+#include "common.cuh"
+
+namespace hexgnn {
+
+// ---- 1. init: status, gptr, zero the degree histogram ------------------------------------------
+__global__ void csr_init_kernel(CsrView v, const int64_t* __restrict__ batch, const int64_t* __restrict__ ptr,
+                                int N, int B) {
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int nth = gridDim.x * blockDim.x;
+  if (tid == 0) { *v.status = 0; *v.ntiles = 0; }
+  for (int i = tid; i <= N; i += nth) v.cursor[i] = 0;  // cursor doubles as the degree histogram
+  if (ptr) {
+    for (int g = tid; g <= B; g += nth) v.gptr[g] = (int)ptr[g];
+  } else if (batch) {
+    // batch is sorted: node i opens every graph in (batch[i-1], batch[i]]
+    for (int i = tid; i < N; i += nth) {
+      const long long b = batch[i];
+      const long long pb = i == 0 ? -1 : batch[i - 1];
+      if (b < pb || b < 0 || b >= B) { atomicOr(v.status, HEXGNN_ST_BATCH_UNSORTED); continue; }
+      for (long long g = pb + 1; g <= b; ++g) v.gptr[g] = i;
+      if (i == N - 1) for (long long g = b + 1; g <= B; ++g) v.gptr[g] = N;
+    }
+    if (N == 0) for (int g = tid; g <= B; g += nth) v.gptr[g] = 0;
+  } else {
+    for (int g = tid; g <= B; g += nth) v.gptr[g] = g == 0 ? 0 : N;
+  }
+}
+
+// ---- 2. in-degree histogram ---------------------------------------------------------------------
+__global__ void csr_hist_kernel(CsrView v, const int64_t* __restrict__ ei, int E, int N) {
+  const int nth = gridDim.x * blockDim.x;
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < E; e += nth) {
+    const long long s = ei[e], d = ei[(int64_t)E + e];
+    if (s < 0 || s >= N || d < 0 || d >= N) { atomicOr(v.status, HEXGNN_ST_EDGE_CROSSES); continue; }
+    atomicAdd(&v.cursor[d], 1);
+  }
+}
+
+// ---- 3. exclusive scan of the histogram (single CTA; N is a few 10^4..10^5) ----------------------
+__global__ void __launch_bounds__(1024) csr_scan_kernel(CsrView v, int N) {
+  __shared__ int warp_sums[32];
+  __shared__ int carry_s;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  if (tid == 0) carry_s = 0;
+  __syncthreads();
+  // each iteration scans 1024*4 entries
+  for (int base = 0; base <= N; base += 4096) {
+    const int i0 = base + tid * 4;
+    int a[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) a[k] = (i0 + k <= N) ? v.cursor[i0 + k] : 0;
+    const int tsum = a[0] + a[1] + a[2] + a[3];
+    int inc = tsum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      int t = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += t;
+    }
+    if (lane == 31) warp_sums[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+      int ws = warp_sums[lane];
+      int winc = ws;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, winc, o);
+        if (lane >= o) winc += t;
+      }
+      warp_sums[lane] = winc - ws;  // exclusive
+    }
+    __syncthreads();
+    const int carry = carry_s;
+    int ex = carry + warp_sums[wid] + inc - tsum;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      if (i0 + k <= N) { v.rowptr[i0 + k] = ex; v.cursor[i0 + k] = 0; }
+      ex += a[k];
+    }
+    __syncthreads();
+    if (tid == 1023) carry_s = ex;
+    __syncthreads();
+  }
+}
+
+// ---- 4. unstable fill with edge ids + greedy tile packing (last block) ----------------------------
+__global__ void csr_fill_kernel(CsrView v, const int64_t* __restrict__ ei, int E, int N, int B, int tile_rows,
+                                int tile_edges) {
+  if (blockIdx.x == gridDim.x - 1) {
+    // Greedy packing of whole graphs into tiles of <= tile_rows nodes, <= tile_edges edges,
+    // <= kMaxTileGraphs graphs.  Sequential by nature; B is a few thousand at most.
+    if (threadIdx.x == 0) {
+      int t = 0, rows = 0, edges = 0, cnt = 0, status = 0;
+      v.tile_g0[0] = 0;
+      for (int g = 0; g < B; ++g) {
+        const int r0 = v.gptr[g], r1 = v.gptr[g + 1];
+        const int n = r1 - r0;
+        const int ne = v.rowptr[r1] - v.rowptr[r0];
+        if (n > tile_rows || ne > tile_edges) status |= HEXGNN_ST_GRAPH_TOO_LARGE;
+        if (cnt > 0 && (rows + n > tile_rows || edges + ne > tile_edges || cnt >= kMaxTileGraphs)) {
+          v.tile_g0[++t] = g;
+          rows = edges = cnt = 0;
+        }
+        rows += n; edges += ne; ++cnt;
+      }
+      if (B > 0) v.tile_g0[++t] = B;
+      *v.ntiles = t;
+      if (status) atomicOr(v.status, status);
+    }
+    return;
+  }
+  const int nth = (gridDim.x - 1) * blockDim.x;
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < E; e += nth) {
+    const long long s = ei[e], d = ei[(int64_t)E + e];
+    if (s < 0 || s >= N || d < 0 || d >= N) continue;
+    const int pos = atomicAdd(&v.cursor[d], 1);
+    v.eid[v.rowptr[d] + pos] = e;
+  }
+}
+
+// ---- 5. per-row sort by edge id (=> stable), emit sources ----------------------------------------
+__global__ void csr_sort_kernel(CsrView v, const int64_t* __restrict__ ei, int N) {
+  const int nth = gridDim.x * blockDim.x;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += nth) {
+    const int b = v.rowptr[i], e = v.rowptr[i + 1];
+    // insertion sort: rows hold <= ~25 entries for Hex graphs
+    for (int p = b + 1; p < e; ++p) {
+      const int key = v.eid[p];
+      int q = p - 1;
+      while (q >= b && v.eid[q] > key) { v.eid[q + 1] = v.eid[q]; --q; }
+      v.eid[q + 1] = key;
+    }
+    for (int p = b; p < e; ++p) v.col[p] = (int)ei[v.eid[p]];
+  }
+}
+
+int launch_build_csr(const int64_t* edge_index, int64_t E, const int64_t* batch, const int64_t* ptr, int64_t N,
+                     int64_t B, int tile_rows, void* csr, cudaStream_t st) {
+  CsrView v = csr_view(csr, N, E, B);
+  const int threads = 256;
+  auto blocks = [&](int64_t n) { int64_t b = (n + threads - 1) / threads; return (int)(b < 1 ? 1 : (b > 1184 ? 1184 : b)); };
+  const int64_t init_n = (N + 1 > B + 1) ? N + 1 : B + 1;
+  csr_init_kernel<<<blocks(init_n), threads, 0, st>>>(v, batch, ptr, (int)N, (int)B);
+  if (E > 0) csr_hist_kernel<<<blocks(E), threads, 0, st>>>(v, edge_index, (int)E, (int)N);
+  csr_scan_kernel<<<1, 1024, 0, st>>>(v, (int)N);
+  csr_fill_kernel<<<blocks(E) + 1, threads, 0, st>>>(v, edge_index, (int)E, (int)N, (int)B, tile_rows,
+                                                    tile_rows * kEdgeCapPerRow);
+  if (N > 0) csr_sort_kernel<<<blocks(N), threads, 0, st>>>(v, edge_index, (int)N);
+  HEX_CUDA_CHECK(cudaGetLastError());
+  return HEXGNN_OK;
+}
+
+}  // namespace hexgnn

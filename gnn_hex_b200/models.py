@@ -1,0 +1,260 @@
+"""Host-side mirror of the reference model API for the `modern_two_headed` Q-network.
+
+`get_pre_defined("modern_two_headed", args)` (GN0/models.py:892,928-947) returns a module whose
+forward/simple_forward signatures, attributes and parameter NAMES match the reference's
+`DuellingTwoHeaded` (GN0/models.py:477-590) over PyG GraphSAGE, so checkpoints and callers
+(Rainbow/common/rainbow.py:221,263,268,302; GN0/RainbowDQN/evaluate_elo.py:251) carry over.
+All arithmetic runs in libhexgnn.so; this file only owns parameters and plumbing.
+"""
+from typing import Optional
+
+import torch
+from torch import nn
+
+from . import _lib, ops
+
+
+class _Conv(nn.Module):
+    """Parameter holder named like PyG 2.2.0 `SAGEConv`: lin_l (weight+bias), lin_r (weight)."""
+
+    def __init__(self, cin, cout):
+        super().__init__()
+        self.lin_l = nn.Linear(cin, cout, bias=True)
+        self.lin_r = nn.Linear(cin, cout, bias=False)
+
+
+class _SageParams(nn.Module):
+    """Holder named like `cachify_gnn(GraphSAGE)` (GN0/models.py:144-160): `.convs`, plus the
+    attributes callers read (`hidden_channels` train.py:301, `has_cache` rainbow.py:344)."""
+    supports_cache = True
+
+    def __init__(self, in_channels, hidden, num_layers):
+        super().__init__()
+        self.in_channels = in_channels
+        self.hidden_channels = hidden
+        self.num_layers = num_layers
+        self.has_cache = False
+        self.convs = nn.ModuleList([_Conv(in_channels if i == 0 else hidden, hidden) for i in range(num_layers)])
+
+
+class _MLPParams(nn.Module):
+    """Holder named like `MLP(hidden//2, 1, 4*hidden, 1)` (GN0/models.py:36-49): `.layers.{0,1}`."""
+
+    def __init__(self, hidden, num_input, num_output):
+        super().__init__()
+        self.layers = nn.ModuleList([nn.Linear(num_input, hidden), nn.Linear(hidden, num_output)])
+
+
+class _HeadParams(nn.Module):
+    """Holder named like `HeadNetwork` (GN0/models.py:318-334): gnn, linear, value_head."""
+    supports_cache = True
+
+    def __init__(self, hidden, num_layers):
+        super().__init__()
+        self.gnn = _SageParams(hidden, hidden, num_layers)
+        self.linear = nn.Linear(hidden, 1)
+        self.value_head = _MLPParams(hidden // 2, 4 * hidden, 1)
+        self.hidden_channels = hidden
+
+
+class _FusedQ(torch.autograd.Function):
+    """Autograd node around hexgnn_forward / hexgnn_backward.  The individual parameters are
+    inputs so that each `p.grad` is filled exactly as after the reference's loss.backward()."""
+
+    @staticmethod
+    def forward(ctx, model, x, csr, flags, *params):
+        need_grad = any(ctx.needs_input_grad[4:])
+        out_nodes, out_value, stash, hp = ops.fused_forward(model._desc, model._flat, x, csr, flags,
+                                                            want_stash=need_grad, ws=model._fwd_ws(csr))
+        ctx.model, ctx.csr, ctx.flags, ctx.stash = model, csr, flags, stash
+        ctx.save_for_backward(x)
+        ctx.flat_version = model._flat_version
+        if stash is not None:
+            L, H = model.num_layers, model.hidden_channels
+            model.final_conv_acts = stash[(L - 1) * csr.N * hp:L * csr.N * hp].view(csr.N, hp)[:, :H]
+        return out_nodes, out_value
+
+    @staticmethod
+    def backward(ctx, d_nodes, d_value):
+        model = ctx.model
+        (x,) = ctx.saved_tensors
+        if ctx.flat_version != model._flat_version:
+            raise _lib.HexGnnError("parameters were re-flattened between forward and backward")
+        if d_nodes is None:
+            d_nodes = torch.zeros(ctx.csr.N, dtype=torch.float32, device=x.device)
+        use_dv = bool(ctx.flags & ops.HEXGNN_SEPARATE) and d_value is not None
+        grad, d_emb = ops.fused_backward(model._desc, model._flat, x, ctx.csr, ctx.flags, d_nodes,
+                                         d_value if use_dv else None, ctx.stash,
+                                         want_d_embeds=model.capture_embed_grads, ws=model._bwd_ws(ctx.csr))
+        if d_emb is not None:
+            model.final_conv_grads = d_emb[:, :model.hidden_channels]
+        grads = tuple(grad[o:o + n].view(s) for (o, n, s) in model._slices)
+        return (None, None, None, None) + grads
+
+
+class ModernTwoHeaded(nn.Module):
+    """Drop-in for `get_pre_defined("modern_two_headed", args)` with norm=False, noisy_dqn=False.
+
+    forward(x, edge_index, graph_indices=None, ptr=None, set_cache=False, advantages_only=False,
+            seperate=False)            -- GN0/models.py:537
+    simple_forward(data)               -- GN0/models.py:586-590
+    Extra, non-reference keyword: `num_graphs` (avoids the host sync of `int(graph_indices.max())+1`,
+    models.py:576, when `ptr` is not passed) and `csr` (reuse a CSR built by `build_csr`).
+    """
+    supports_cache = True  # class attribute in the reference (models.py:148,486); read at train.py:98
+
+    def __init__(self, hidden_channels: int, num_layers: int, num_head_layers: int = 2, tile_rows: int = 128,
+                 strict: bool = False, path: str = "auto"):
+        super().__init__()
+        self.hidden_channels = int(hidden_channels)
+        self.num_layers = int(num_layers)
+        self.num_head_layers = int(num_head_layers)
+        self.tile_rows = int(tile_rows)
+        self.strict = strict                  # True: sync + raise on device-side status after each forward
+        self.path = path                      # "auto" | "simt" | "tc"
+        self.capture_embed_grads = False      # True: fill final_conv_grads (rl_loop/explain.py:41)
+        self.gnn = _SageParams(2, hidden_channels, num_layers)
+        self.maker_head = _HeadParams(hidden_channels, num_head_layers)
+        self.breaker_head = _HeadParams(hidden_channels, num_head_layers)
+        self.after_embed_norm = None
+        self.final_conv_acts = None
+        self.final_conv_grads = None
+        self._desc = _lib.make_desc(hidden_channels, num_layers, num_head_layers)
+        self._flat = None
+        self._flat_version = 0
+        self._slices = None
+        self._ws = {}
+
+    # ---- parameter order == include/hexgnn.h flat layout ---------------------------------------------
+    def _ordered_params(self):
+        ps = []
+        for c in self.gnn.convs:
+            ps += [c.lin_l.weight, c.lin_l.bias, c.lin_r.weight]
+        for head in (self.maker_head, self.breaker_head):
+            for c in head.gnn.convs:
+                ps += [c.lin_l.weight, c.lin_l.bias, c.lin_r.weight]
+            ps += [head.linear.weight, head.linear.bias,
+                   head.value_head.layers[0].weight, head.value_head.layers[0].bias,
+                   head.value_head.layers[1].weight, head.value_head.layers[1].bias]
+        return ps
+
+    def _flatten(self):
+        """Move every parameter into one flat fp32 buffer (the C-ABI's `params`) and re-point the
+        named parameters at views of it, so optimizers / state_dict keep working on the names."""
+        ps = self._ordered_params()
+        offs = _lib.param_offsets(self._desc)
+        total = int(_lib.lib().hexgnn_param_count(self._desc))
+        if len(offs) != len(ps):
+            raise _lib.HexGnnError("parameter table mismatch between models.py and libhexgnn.so")
+        dev = ps[0].device
+        flat = torch.empty(total, dtype=torch.float32, device=dev)
+        slices = []
+        with torch.no_grad():
+            for p, o in zip(ps, offs):
+                n = p.numel()
+                flat[o:o + n].copy_(p.detach().reshape(-1).to(torch.float32))
+                p.data = flat[o:o + n].view(p.shape)
+                slices.append((o, n, tuple(p.shape)))
+        if slices[-1][0] + slices[-1][1] != total:
+            raise _lib.HexGnnError("flat parameter size mismatch")
+        self._flat, self._slices = flat, slices
+        self._flat_version += 1
+        self._ws = {}
+
+    def _ensure_flat(self):
+        if self._flat is None or self._flat.device != self.gnn.convs[0].lin_l.weight.device:
+            self._flatten()
+
+    def _apply(self, fn, *args, **kwargs):
+        out = super()._apply(fn, *args, **kwargs)
+        self._flat = None  # .to()/.cuda()/.float() replace the parameter storages
+        return out
+
+    def reflatten(self):
+        """Call after replacing parameter tensors by hand (e.g. `p.data = ...`)."""
+        self._flat = None
+
+    @property
+    def flat_parameters(self):
+        self._ensure_flat()
+        return self._flat
+
+    def _fwd_ws(self, csr):
+        w = self._ws.get("fwd")
+        need = _lib.sizes(self._desc, csr.N, csr.E, csr.B, csr.tile_rows).fwd_ws_bytes // 4
+        if w is None or w.numel() < need or w.device != csr.blob.device:
+            w = torch.empty(need, dtype=torch.float32, device=csr.blob.device)
+            self._ws["fwd"] = w
+        return w
+
+    def _bwd_ws(self, csr):
+        w = self._ws.get("bwd")
+        need = _lib.sizes(self._desc, csr.N, csr.E, csr.B, csr.tile_rows).bwd_ws_bytes // 4
+        if w is None or w.numel() < need or w.device != csr.blob.device:
+            w = torch.empty(need, dtype=torch.float32, device=csr.blob.device)
+            self._ws["bwd"] = w
+        return w
+
+    # ---- reference API ---------------------------------------------------------------------------------
+    def build_csr(self, edge_index, graph_indices=None, ptr=None, num_nodes=None, num_graphs=None):
+        if num_graphs is None and ptr is None and graph_indices is not None:
+            # the reference does the same sync: batch_size = int(graph_indices.max()) + 1 (models.py:576)
+            num_graphs = int(graph_indices.max()) + 1
+        return ops.build_csr(edge_index, graph_indices, ptr, num_nodes=num_nodes, num_graphs=num_graphs,
+                             tile_rows=self.tile_rows)
+
+    def forward(self, x, edge_index, graph_indices: Optional[torch.Tensor] = None, ptr: Optional[torch.Tensor] = None,
+                set_cache: bool = False, advantages_only=False, seperate=False, num_graphs: Optional[int] = None,
+                csr: Optional[ops.CsrBlob] = None):
+        self._ensure_flat()
+        if csr is None:
+            csr = self.build_csr(edge_index, graph_indices, ptr, num_nodes=int(x.shape[0]), num_graphs=num_graphs)
+        flags = 0
+        if advantages_only:
+            flags |= ops.HEXGNN_ADV_ONLY
+        elif seperate:
+            flags |= ops.HEXGNN_SEPARATE
+        if self.path == "simt":
+            flags |= ops.HEXGNN_PATH_SIMT
+        elif self.path == "tc":
+            flags |= ops.HEXGNN_PATH_TC
+        self.final_conv_acts = None
+        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
+            out_nodes, out_value = _FusedQ.apply(self, x, csr, flags, *self._ordered_params())
+        else:
+            out_nodes, out_value, _, _ = ops.fused_forward(self._desc, self._flat, x, csr, flags, want_stash=False,
+                                                           ws=self._fwd_ws(csr))
+        if self.strict:
+            csr.raise_on_error()
+        if advantages_only:
+            return out_nodes.unsqueeze(1)           # [N,1] (models.py:567-569)
+        if seperate:
+            return out_value, out_nodes             # (value[B], adv - mean[N]) (models.py:580-581)
+        return out_nodes                            # [N] (models.py:584)
+
+    def simple_forward(self, data):
+        if getattr(data, "batch", None) is not None:
+            return self.forward(data.x, data.edge_index, data.batch, getattr(data, "ptr", None))
+        return self.forward(data.x, data.edge_index)
+
+    # no-op cache API: cached_norm=False in modern_two_headed (models.py:934,943)
+    def export_norm_cache(self, *args):
+        return []
+
+    def import_norm_cache(self, *args):
+        return None
+
+    def grow_width(self, *a, **k):
+        raise NotImplementedError("grow_width/grow_depth (GN0/models.py:494-508) are outside the fused path")
+
+    grow_depth = grow_width
+
+
+def get_pre_defined(name, args=None):
+    """`GN0/models.py:892` for the one name this package implements."""
+    if name != "modern_two_headed":
+        raise NotImplementedError(f"gnn_hex_b200 implements only 'modern_two_headed', not {name!r}")
+    if getattr(args, "norm", False) or getattr(args, "noisy_dqn", False):
+        raise NotImplementedError("norm=True / noisy_dqn=True are not on the fused path (SURVEY.md §8 f4)")
+    return ModernTwoHeaded(args.hidden_channels, args.num_layers,
+                           args.num_head_layers if hasattr(args, "num_head_layers") else 2)

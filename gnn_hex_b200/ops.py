@@ -1,0 +1,148 @@
+"""Tensor-level wrappers over the C-ABI (include/hexgnn.h).  PyTorch only provides device memory
+and the current stream here; all arithmetic happens in libhexgnn.so."""
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import HEXGNN_ADV_ONLY, HEXGNN_SEPARATE, HEXGNN_PATH_SIMT, HEXGNN_PATH_TC  # noqa: F401
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def _stream(device):
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def _require_cuda(t, name):
+    if not t.is_cuda:
+        raise _lib.HexGnnError(f"{name} must be a CUDA tensor: the fused path has no CPU fallback")
+
+
+class CsrBlob:
+    """Destination-sorted CSR + tile table of one batch, living in one int32 device blob."""
+
+    def __init__(self, blob, N, E, B, tile_rows):
+        self.blob, self.N, self.E, self.B, self.tile_rows = blob, N, E, B, tile_rows
+        self.layout = _lib.csr_layout(N, E, B)
+
+    def _view(self, off, n):
+        return self.blob[off:off + n]
+
+    @property
+    def status(self):
+        return self._view(self.layout.status, 1)
+
+    @property
+    def ntiles(self):
+        return self._view(self.layout.ntiles, 1)
+
+    @property
+    def gptr(self):
+        return self._view(self.layout.gptr, self.B + 1)
+
+    @property
+    def rowptr(self):
+        return self._view(self.layout.rowptr, self.N + 1)
+
+    @property
+    def col(self):
+        return self._view(self.layout.col, self.E)
+
+    @property
+    def tile_g0(self):
+        return self._view(self.layout.tile_g0, self.B + 1)
+
+    def raise_on_error(self):
+        """Host sync: read the device status word and raise if any kernel flagged the batch."""
+        st = int(self.status.item())
+        if st:
+            msgs = [m for bit, m in _lib.STATUS_NAMES.items() if st & bit]
+            raise _lib.HexGnnError("hexgnn device status %d: %s" % (st, "; ".join(msgs)))
+
+
+def build_csr(edge_index, batch=None, ptr=None, num_nodes=None, num_graphs=None, tile_rows=128):
+    """Device CSR builder (hexgnn_build_csr).  edge_index [2,E] int64 CUDA; batch [N] int64 and/or
+    ptr [B+1] int64; neither => single graph.  No host sync."""
+    _require_cuda(edge_index, "edge_index")
+    if edge_index.dtype != torch.int64 or edge_index.dim() != 2 or edge_index.shape[0] != 2:
+        raise _lib.HexGnnError("edge_index must be int64 [2,E]")
+    edge_index = edge_index.contiguous()
+    E = int(edge_index.shape[1])
+    if batch is not None:
+        _require_cuda(batch, "batch")
+        batch = batch.contiguous()
+        if batch.dtype != torch.int64:
+            raise _lib.HexGnnError("batch must be int64")
+    if ptr is not None:
+        if not ptr.is_cuda:
+            ptr = ptr.to(edge_index.device, non_blocking=True)
+        ptr = ptr.contiguous()
+        if ptr.dtype != torch.int64:
+            raise _lib.HexGnnError("ptr must be int64")
+    if num_nodes is None:
+        if batch is None:
+            raise _lib.HexGnnError("num_nodes is required when batch is not given")
+        num_nodes = int(batch.shape[0])
+    if num_graphs is None:
+        if ptr is not None:
+            num_graphs = int(ptr.shape[0]) - 1
+        elif batch is None:
+            num_graphs = 1
+        else:
+            raise _lib.HexGnnError("num_graphs is required when only `batch` is given (avoids a host sync)")
+    N, B = int(num_nodes), int(num_graphs)
+    lay = _lib.csr_layout(N, E, B)
+    blob = torch.empty(lay.total_words, dtype=torch.int32, device=edge_index.device)
+    rc = _lib.lib().hexgnn_build_csr(_ptr(edge_index), E, _ptr(batch), _ptr(ptr), N, B, tile_rows, _ptr(blob),
+                                     blob.numel() * 4, _stream(edge_index.device))
+    _lib.check(rc, "hexgnn_build_csr")
+    return CsrBlob(blob, N, E, B, tile_rows)
+
+
+def fused_forward(desc, flat_params, x, csr, flags=0, want_stash=False, ws=None):
+    """hexgnn_forward.  Returns (out_nodes [N], out_value [B], stash or None, hidden_padded)."""
+    _require_cuda(x, "x")
+    _require_cuda(flat_params, "parameters")
+    if x.dtype != torch.float32 or x.dim() != 2 or x.shape[1] != 3:
+        raise _lib.HexGnnError("x must be float32 [N,3]")
+    x = x.contiguous()
+    N, E, B = csr.N, csr.E, csr.B
+    if x.shape[0] != N:
+        raise _lib.HexGnnError("x rows != csr nodes")
+    sz = _lib.sizes(desc, N, E, B, csr.tile_rows)
+    dev = x.device
+    if ws is None or ws.numel() * 4 < sz.fwd_ws_bytes:
+        ws = torch.empty(sz.fwd_ws_bytes // 4, dtype=torch.float32, device=dev)
+    out_nodes = torch.empty(N, dtype=torch.float32, device=dev)
+    out_value = torch.empty(B, dtype=torch.float32, device=dev)
+    stash = torch.empty(sz.stash_bytes // 4, dtype=torch.float32, device=dev) if want_stash else None
+    rc = _lib.lib().hexgnn_forward(C.byref(desc), _ptr(flat_params), _ptr(x), N, E, B, _ptr(csr.blob), csr.tile_rows,
+                                   flags, _ptr(out_nodes), _ptr(out_value), _ptr(stash), _ptr(ws), ws.numel() * 4,
+                                   _stream(dev))
+    _lib.check(rc, "hexgnn_forward")
+    return out_nodes, out_value, stash, int(sz.hidden_padded)
+
+
+def fused_backward(desc, flat_params, x, csr, flags, d_nodes, d_value, stash, want_d_embeds=False, ws=None,
+                   grad_out=None):
+    """hexgnn_backward.  Returns (flat gradient [P], d_embeds [N,Hp] or None)."""
+    N, E, B = csr.N, csr.E, csr.B
+    sz = _lib.sizes(desc, N, E, B, csr.tile_rows)
+    dev = x.device
+    x = x.contiguous()
+    if ws is None or ws.numel() * 4 < sz.bwd_ws_bytes:
+        ws = torch.empty(sz.bwd_ws_bytes // 4, dtype=torch.float32, device=dev)
+    if grad_out is None:
+        grad_out = torch.empty(flat_params.numel(), dtype=torch.float32, device=dev)
+    d_nodes = d_nodes.contiguous().float()
+    if d_value is not None:
+        d_value = d_value.contiguous().float()
+    d_embeds = torch.empty((N, int(sz.hidden_padded)), dtype=torch.float32, device=dev) if want_d_embeds else None
+    rc = _lib.lib().hexgnn_backward(C.byref(desc), _ptr(flat_params), _ptr(x), N, E, B, _ptr(csr.blob), csr.tile_rows,
+                                    flags, _ptr(d_nodes), _ptr(d_value), _ptr(stash), _ptr(grad_out), _ptr(d_embeds),
+                                    _ptr(ws), ws.numel() * 4, _stream(dev))
+    _lib.check(rc, "hexgnn_backward")
+    return grad_out, d_embeds

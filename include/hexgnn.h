@@ -1,0 +1,147 @@
+/* hexgnn.h -- C-ABI of libhexgnn.so: B200 (sm_100a) fused forward/backward of GNN_Hex's
+ * `modern_two_headed` Q-network over batched Shannon node-switching Hex graphs.
+ *
+ * The reference has no FFI for this path: its boundary is the Python nn.Module protocol
+ *   get_pre_defined("modern_two_headed", args)            GN0/models.py:892,928-947
+ *   DuellingTwoHeaded.forward(x, edge_index, graph_indices, ptr, set_cache,
+ *                             advantages_only, seperate)  GN0/models.py:537-584
+ *   loss.backward() through it                            Rainbow/common/rainbow.py:316
+ * and, on the C++ side, collate_batch + NN_api::predict   cpp_hex/hex_graph_game/util.cpp:22-41,
+ *                                                         cpp_hex/CrazyAra/nn_api.cpp:14-19.
+ * These entry points are what a binding for that path calls (INTEGRATION.md shows the ctypes
+ * stub used by gnn_hex_b200/ and the libtorch stub a C++ maintainer would add).
+ *
+ * Conventions
+ *  - plain pointers and sizes; no torch types.  Every pointer except the descriptors and the
+ *    host out-parameters is a DEVICE pointer valid on `stream` (a cudaStream_t passed as void*).
+ *  - the caller owns every buffer (inputs, outputs, csr blob, stash, workspace); the library
+ *    allocates nothing, keeps no mutable global state and is re-entrant.  Work is enqueued on
+ *    `stream`; nothing synchronises the host.
+ *  - return 0 on success, a negative HEXGNN_E_* otherwise; hexgnn_last_error() gives a
+ *    thread-local message.
+ *  - data-dependent faults (a graph larger than the tile capacity, an edge crossing graphs)
+ *    cannot be seen by the host without a sync: kernels record them in the status word at the
+ *    start of the csr blob (see hexgnn_csr_layout) and poison the outputs with NaN.
+ */
+#ifndef HEXGNN_H_
+#define HEXGNN_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HEXGNN_ABI_VERSION 2
+
+enum {
+  HEXGNN_OK = 0,
+  HEXGNN_E_BADARG = -1,      /* null pointer, negative size, inconsistent descriptor            */
+  HEXGNN_E_UNSUPPORTED = -2, /* hidden size / tile capacity outside what the kernels were built for */
+  HEXGNN_E_WORKSPACE = -3,   /* a caller-provided buffer is smaller than hexgnn_sizes() says      */
+  HEXGNN_E_CUDA = -4         /* a CUDA runtime call failed (message has the cudaError string)     */
+};
+
+/* flags for hexgnn_forward / hexgnn_backward */
+enum {
+  HEXGNN_ADV_ONLY = 1,   /* advantages_only=True: out_nodes = 2*tanh(linear(g)), no value branch (models.py:567-569) */
+  HEXGNN_SEPARATE = 2,   /* seperate=True: out_value = tanh(value), out_nodes = adv - mean(adv)  (models.py:580-581) */
+  HEXGNN_PATH_SIMT = 0x100, /* force the fp32 CUDA-core kernels (default: tcgen05 3xTF32 kernels when the shape allows) */
+  HEXGNN_PATH_TC = 0x200    /* force the tcgen05 kernels; HEXGNN_E_UNSUPPORTED if the shape does not allow      */
+};
+
+/* device-side status bits (csr blob word 0) */
+enum {
+  HEXGNN_ST_GRAPH_TOO_LARGE = 1, /* a graph has more nodes/edges than one tile holds   */
+  HEXGNN_ST_EDGE_CROSSES = 2,    /* an edge joins two different graphs (or is out of range) */
+  HEXGNN_ST_BATCH_UNSORTED = 4,  /* `batch` is not non-decreasing                     */
+  HEXGNN_ST_FLAG_MIXED = 8       /* x[:,2] is not constant (the reference asserts this, models.py:538) */
+};
+
+/* Hyper-parameters of modern_two_headed (GN0/models.py:928-947): in_channels is 2. */
+typedef struct HexModelDesc {
+  int32_t hidden;          /* args.hidden_channels (35 / 110)   */
+  int32_t num_layers;      /* args.num_layers (10 / 15)         */
+  int32_t num_head_layers; /* args.num_head_layers (default 2)  */
+  int32_t in_channels;     /* must be 2                         */
+} HexModelDesc;
+
+/* Byte sizes of the caller-allocated buffers for one (N nodes, E directed edges, B graphs) batch. */
+typedef struct HexSizes {
+  int64_t csr_bytes;     /* csr blob for hexgnn_build_csr                                  */
+  int64_t fwd_ws_bytes;  /* workspace of hexgnn_forward                                    */
+  int64_t stash_bytes;   /* activation stash written by forward, read by backward           */
+  int64_t bwd_ws_bytes;  /* workspace of hexgnn_backward (per-CTA weight-gradient partials) */
+  int64_t hidden_padded; /* Hp: row pitch (floats) of stash rows and of d_embeds            */
+} HexSizes;
+
+/* Offsets (in int32 words from the blob start) of the arrays inside the csr blob. */
+typedef struct HexCsrLayout {
+  int64_t status;   /* [1]   status bits (HEXGNN_ST_*)                                   */
+  int64_t ntiles;   /* [1]   number of tiles                                             */
+  int64_t gptr;     /* [B+1] node prefix sums per graph (== PyG `ptr`, int32)            */
+  int64_t rowptr;   /* [N+1] CSR row pointers, rows = destination nodes                  */
+  int64_t col;      /* [E]   source node id of each edge, stably sorted by destination  */
+  int64_t tile_g0;  /* [B+1] first graph of each tile; tile t = graphs [tile_g0[t], tile_g0[t+1]) */
+  int64_t scratch;  /* internal                                                          */
+  int64_t total_words;
+} HexCsrLayout;
+
+int hexgnn_abi_version(void);
+const char* hexgnn_last_error(void);
+
+/* Number of fp32 parameters of the flat parameter buffer (486,974 for GNN-L, 37,382 for GNN-S). */
+int64_t hexgnn_param_count(const HexModelDesc* desc);
+
+/* Flat parameter layout.  Writes up to `max_entries` float offsets; returns the tensor count.
+ * Order (each tensor row-major as torch stores it, weight[out,in]):
+ *   body layer l = 0..L-1 :  convs.l.lin_l.weight, convs.l.lin_l.bias, convs.l.lin_r.weight
+ *   maker_head            :  gnn.convs.{0..Lh-1}.(lin_l.weight, lin_l.bias, lin_r.weight),
+ *                            linear.weight[1,H], linear.bias[1],
+ *                            value_head.layers.0.weight[H/2,4H], .bias[H/2],
+ *                            value_head.layers.1.weight[1,H/2],  .bias[1]
+ *   breaker_head          :  same as maker_head                                           */
+int32_t hexgnn_param_offsets(const HexModelDesc* desc, int64_t* offsets, int32_t max_entries);
+
+/* tile_rows: node capacity of one CTA tile (128 or 192); graphs are packed into tiles whole. */
+int hexgnn_sizes(const HexModelDesc* desc, int64_t N, int64_t E, int64_t B, int32_t tile_rows,
+                 HexSizes* out);
+int hexgnn_csr_layout(int64_t N, int64_t E, int64_t B, HexCsrLayout* out);
+
+/* Device CSR builder: replaces the host-side graph -> edge_index -> Batch chain of
+ * GN0/util/convert_graph.py:99-117 + Batch.from_data_list (replay_buffer.py:215-216) for the
+ * kernels' needs.  edge_index is [2,E] int64 row-major (messages flow row0 -> row1, as PyG);
+ * `batch` [N] int64 sorted (PyG Batch.batch) and/or `ptr` [B+1] int64; both NULL => one graph.
+ * Result (bit-exact contract): rowptr/col == stable sort of the edges by destination.        */
+int hexgnn_build_csr(const int64_t* edge_index, int64_t E, const int64_t* batch, const int64_t* ptr,
+                     int64_t N, int64_t B, int32_t tile_rows, void* csr, size_t csr_bytes, void* stream);
+
+/* Fused forward (replaces DuellingTwoHeaded.forward, GN0/models.py:537-584).
+ *   params     flat fp32 parameters (layout above)
+ *   x          [N,3] fp32: degree, is_terminal, maker flag (convert_graph.py:78-85)
+ *   out_nodes  [N]: Q (default) | 2*tanh(adv) (ADV_ONLY) | adv - mean(adv) (SEPARATE)
+ *   out_value  [B] tanh(value) (SEPARATE; optional otherwise, may be NULL)
+ *   stash      NULL for inference; else stash_bytes, kept for hexgnn_backward.  Layer l's output
+ *              h_{l+1} is rows [l*N, (l+1)*N) of pitch Hp floats; the body embedding
+ *              (`final_conv_acts`, models.py:553) is layer num_layers-1.                       */
+int hexgnn_forward(const HexModelDesc* desc, const float* params, const float* x, int64_t N, int64_t E,
+                   int64_t B, const void* csr, int32_t tile_rows, int32_t flags, float* out_nodes,
+                   float* out_value, float* stash, void* ws, size_t ws_bytes, void* stream);
+
+/* Fused backward (replaces loss.backward() through the model, rainbow.py:316).
+ *   d_nodes      [N] gradient w.r.t. out_nodes
+ *   d_value      [B] gradient w.r.t. out_value (SEPARATE) or NULL
+ *   grad_params  flat fp32, same layout as params; OVERWRITTEN (head not taken gets zeros).
+ *                Deterministic: per-CTA partial sums are reduced in a fixed order, no atomics.
+ *   d_embeds     optional [N,Hp] gradient w.r.t. the body embedding (`final_conv_grads`,
+ *                models.py:534-535), or NULL.                                                  */
+int hexgnn_backward(const HexModelDesc* desc, const float* params, const float* x, int64_t N, int64_t E,
+                    int64_t B, const void* csr, int32_t tile_rows, int32_t flags, const float* d_nodes,
+                    const float* d_value, const float* stash, float* grad_params, float* d_embeds,
+                    void* ws, size_t ws_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HEXGNN_H_ */

@@ -1,0 +1,340 @@
+"""TEST INFRASTRUCTURE ONLY -- CPU oracle for the ``modern_two_headed`` hot path of GNN_Hex.
+
+Pure torch (no torch_geometric / torch_scatter: neither is installable here), fp32 or fp64.
+Every function cites the reference lines it restates (paths relative to /root/reference).
+
+Parity status: the reference holds NO golden vector for the model numerics, and
+torch_geometric 2.2.0 / torch_scatter 2.1.0 (environment.yml:139,151) are absent, so the model
+half of this oracle is **parity unpinned** against the real PyG kernels.  It is pinned instead by
+(i) a hand-computed known answer on the reference's ``Debugging_manager`` graph
+(graph_game/multi_env_manager.py:170-175), (ii) fp64 gradcheck, (iii) batched == per-graph,
+permutation equivariance and edge-order invariance (tests/test_oracle.py).  The graph half
+(topology, edge_index, collate) IS pinned: fixtures under tests/golden/ come from the reference's
+own C++ game compiled unchanged (oracle/refgame/Makefile -> oracle/_ref/hexgen).
+"""
+from __future__ import annotations
+
+import math
+from types import SimpleNamespace
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import torch
+import torch.nn.functional as F
+
+# --------------------------------------------------------------------------------------
+# graph side
+# --------------------------------------------------------------------------------------
+
+
+def hex_board_undirected_edges(size: int) -> List[Tuple[int, int]]:
+    """Empty-board Shannon graph of a size x size Hex board, red graph, no worthless edges.
+
+    Restates graph_game/hex_board_game.py:214-232 (``graph_from_board(redgraph=True)``):
+    vertices 0,1 are the terminals, square i is vertex i+2.
+    """
+    sq = size
+    squares = size * size
+    edges: List[Tuple[int, int]] = []
+    for i in range(squares):
+        v = i + 2
+        if i < sq:
+            edges.append((v, 0))
+        if i // sq == sq - 1:
+            edges.append((v, 1))
+        if i % sq > 0 and (sq <= i <= squares - sq):
+            edges.append((v, v - 1))
+        if i >= sq:
+            edges.append((v, v - sq))
+            if i % sq != sq - 1:
+                edges.append((v, v - sq + 1))
+    return edges
+
+
+class SimpleShannonGame:
+    """Self-contained fallback position generator (no dead/captured removal).
+
+    Restates the rule core of graph_game/shannon_node_switching_game.py:80-116: a maker move
+    on v joins all of v's neighbours pairwise (unless both already touch the same terminal)
+    and removes v; a breaker move removes v.  Terminal bookkeeping (``_fix_teminal_connections``)
+    and dead/captured pruning are NOT restated -- fixtures for the benchmark come from the
+    compiled reference game instead; this class exists so the GPU box (no /root/reference)
+    can still synthesise arbitrary many valid symmetric graphs.
+    """
+
+    def __init__(self, size: int):
+        self.size = size
+        n = size * size + 2
+        self.adj: Dict[int, set] = {v: set() for v in range(n)}
+        for a, b in hex_board_undirected_edges(size):
+            self.adj[a].add(b)
+            self.adj[b].add(a)
+        self.maker_turn = True
+
+    def actions(self) -> List[int]:
+        return [v for v in self.adj if v > 1]
+
+    def make_move(self, v: int) -> None:
+        neigh = sorted(self.adj[v])
+        if self.maker_turn:
+            for i, a in enumerate(neigh):
+                for b in neigh[i + 1:]:
+                    both_t0 = 0 in self.adj[a] and 0 in self.adj[b]
+                    both_t1 = 1 in self.adj[a] and 1 in self.adj[b]
+                    if a in (0, 1) and b in (0, 1):
+                        continue
+                    if not (both_t0 or both_t1):
+                        self.adj[a].add(b)
+                        self.adj[b].add(a)
+        for a in neigh:
+            self.adj[a].discard(v)
+        del self.adj[v]
+        self.maker_turn = not self.maker_turn
+
+    def to_data(self) -> SimpleNamespace:
+        verts = sorted(self.adj)
+        vmap = {v: i for i, v in enumerate(verts)}
+        und = [(vmap[a], vmap[b]) for a in verts for b in sorted(self.adj[a]) if a < b]
+        return data_from_undirected(len(verts), und, int(self.maker_turn))
+
+
+def data_from_undirected(n: int, und_edges: Sequence[Tuple[int, int]], maker_flag: int) -> SimpleNamespace:
+    """``Data(x, edge_index)`` exactly as ``convert_node_switching_game(old_style=True)`` lays it out.
+
+    Restates GN0/util/convert_graph.py:77-85 (features: total degree, is_terminal on rows 0,1,
+    global maker flag) and :99-117 (``edge_index = cat(E, flip(E))``, int64).
+    """
+    if len(und_edges) == 0:
+        e = torch.zeros((2, 0), dtype=torch.long)
+    else:
+        e = torch.tensor(list(und_edges), dtype=torch.long).t().contiguous()
+    edge_index = torch.cat((e, torch.flip(e, dims=(0,))), dim=1)
+    x = torch.zeros((n, 3), dtype=torch.float32)
+    deg = torch.bincount(edge_index[1], minlength=n) if edge_index.numel() else torch.zeros(n, dtype=torch.long)
+    x[:, 0] = deg.float()
+    x[0, 1] = 1
+    x[1, 1] = 1
+    x[:, 2] = float(maker_flag)
+    return SimpleNamespace(x=x, edge_index=edge_index)
+
+
+def data_from_directed_csr(n: int, src: torch.Tensor, dst: torch.Tensor, maker_flag: int) -> SimpleNamespace:
+    """Build the Python-style ``Data`` from the C++ game's symmetric directed edge list
+    (cpp_hex/hex_graph_game/shannon_node_switching_game.cpp:718-720): keep s<t once, then flip."""
+    keep = src < dst
+    und = list(zip(src[keep].tolist(), dst[keep].tolist()))
+    return data_from_undirected(n, und, maker_flag)
+
+
+def collate(datas: Sequence[SimpleNamespace]) -> SimpleNamespace:
+    """PyG ``Batch.from_data_list`` for (x, edge_index) == C++ ``collate_batch``.
+
+    Restates cpp_hex/hex_graph_game/util.cpp:22-41: cat x; cat edge_index with per-graph node
+    offsets; ``batch`` = graph id per node; ``ptr`` = node prefix sums.  All int64.
+    """
+    xs, eis, batch = [], [], []
+    ptr = [0]
+    off = 0
+    for i, d in enumerate(datas):
+        n = d.x.shape[0]
+        xs.append(d.x)
+        eis.append(d.edge_index + off)
+        batch.append(torch.full((n,), i, dtype=torch.long))
+        off += n
+        ptr.append(off)
+    return SimpleNamespace(
+        x=torch.cat(xs, 0),
+        edge_index=torch.cat(eis, 1),
+        batch=torch.cat(batch, 0),
+        ptr=torch.tensor(ptr, dtype=torch.long),
+        num_graphs=len(datas),
+    )
+
+
+def csr_by_destination(edge_index: torch.Tensor, num_nodes: int) -> Tuple[torch.Tensor, torch.Tensor]:
+    """The CSR the device builder must reproduce bit-exactly: edges stably sorted by destination
+    (ties keep input order), ``rowptr[N+1]`` int32 and ``col[E]`` = source node id int32.
+    Message direction is edge_index[0] -> edge_index[1] (PyG ``flow='source_to_target'``)."""
+    src, dst = edge_index[0], edge_index[1]
+    order = torch.sort(dst, stable=True).indices
+    col = src[order].to(torch.int32)
+    deg = torch.bincount(dst, minlength=num_nodes)
+    rowptr = torch.zeros(num_nodes + 1, dtype=torch.int64)
+    rowptr[1:] = torch.cumsum(deg, 0)
+    return rowptr.to(torch.int32), col
+
+
+# --------------------------------------------------------------------------------------
+# model side
+# --------------------------------------------------------------------------------------
+
+
+def _scatter_sum(src: torch.Tensor, index: torch.Tensor, dim_size: int) -> torch.Tensor:
+    out = src.new_zeros((dim_size,) + tuple(src.shape[1:]))
+    return out.index_add_(0, index, src)
+
+
+class _ScatterExtremum(torch.autograd.Function):
+    """torch_scatter 2.1.0 `scatter_max` / `scatter_min` (csrc/cpu/scatter_cpu.cpp + reducer.h):
+    the CPU kernel scans rows in order and updates on strict `>` / `<`, so the FIRST row attaining
+    the extremum is the arg; backward routes the whole gradient to that row
+    (torch_scatter/scatter.py `scatter_max` -> `grad_in.scatter_(0, arg, grad_out)`).
+    Empty groups output 0 and receive no gradient."""
+
+    @staticmethod
+    def forward(ctx, src, index, dim_size, is_max):
+        idx = index.view(-1, *([1] * (src.dim() - 1))).expand_as(src)
+        out = src.new_zeros((dim_size,) + tuple(src.shape[1:]))
+        out = out.scatter_reduce(0, idx, src, reduce="amax" if is_max else "amin", include_self=False)
+        hit = src == out.index_select(0, index)
+        rows = torch.arange(src.shape[0], device=src.device).view(-1, *([1] * (src.dim() - 1))).expand_as(src)
+        cand = torch.where(hit, rows, torch.full_like(rows, src.shape[0]))
+        arg = torch.full(out.shape, src.shape[0], dtype=torch.long, device=src.device)
+        arg = arg.scatter_reduce(0, idx, cand, reduce="amin", include_self=True)
+        ctx.save_for_backward(arg)
+        ctx.n = src.shape[0]
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        (arg,) = ctx.saved_tensors
+        grad_in = grad_out.new_zeros((ctx.n + 1,) + tuple(grad_out.shape[1:]))
+        grad_in.scatter_(0, arg, grad_out)  # empty groups have arg == n -> dropped row
+        return grad_in[:ctx.n], None, None, None
+
+
+def scatter(src: torch.Tensor, index: torch.Tensor, dim_size: int, reduce: str) -> torch.Tensor:
+    """torch_scatter 2.1.0 ``scatter(src, index, dim=0, dim_size, reduce)`` semantics:
+    empty groups give 0 for every reduce; mean divides by max(count, 1)."""
+    if reduce == "sum":
+        return _scatter_sum(src, index, dim_size)
+    if reduce == "mean":
+        cnt = torch.bincount(index, minlength=dim_size).clamp(min=1).to(src.dtype)
+        return _scatter_sum(src, index, dim_size) / cnt.view(-1, *([1] * (src.dim() - 1)))
+    if reduce in ("max", "min"):
+        return _ScatterExtremum.apply(src, index, dim_size, reduce == "max")
+    raise ValueError(reduce)
+
+
+def sage_conv(x, edge_index, w_l, b_l, w_r):
+    """PyG 2.2.0 ``SAGEConv(aggr='mean', root_weight=True, bias=True)``:
+    ``lin_l(mean_{j->i} x_j) + lin_r(x_i)``; lin_l has the bias, lin_r none.
+    In-repo restatement of the same math: GN0/torch_script_models.py:52-73."""
+    src, dst = edge_index[0], edge_index[1]
+    n = x.shape[0]
+    agg = _scatter_sum(x.index_select(0, src), dst, n)
+    cnt = torch.bincount(dst, minlength=n).clamp(min=1).to(x.dtype)
+    mean = agg / cnt.unsqueeze(1)
+    return F.linear(mean, w_l, b_l) + F.linear(x, w_r)
+
+
+class _SageStack(torch.nn.Module):
+    """``cachify_gnn(GraphSAGE)`` with norm=None, dropout=0, act='relu', out_channels=None
+    (GN0/models.py:144-160,261-294): ReLU after EVERY layer incl. the last."""
+
+    def __init__(self, in_channels: int, hidden: int, num_layers: int):
+        super().__init__()
+        self.hidden_channels = hidden
+        self.num_layers = num_layers
+        self.has_cache = False
+        self.supports_cache = True
+        self.convs = torch.nn.ModuleList()
+        for i in range(num_layers):
+            c = torch.nn.Module()
+            cin = in_channels if i == 0 else hidden
+            c.lin_l = torch.nn.Linear(cin, hidden, bias=True)
+            c.lin_r = torch.nn.Linear(cin, hidden, bias=False)
+            self.convs.append(c)
+
+    def forward(self, x, edge_index):
+        for c in self.convs:
+            x = F.relu(sage_conv(x, edge_index, c.lin_l.weight, c.lin_l.bias, c.lin_r.weight))
+        return x
+
+
+class _MLP(torch.nn.Module):
+    """GN0/models.py:36-49,75-82 with num_hidden_layers=1, no output activation."""
+
+    def __init__(self, hidden, num_input, num_output):
+        super().__init__()
+        self.layers = torch.nn.ModuleList([torch.nn.Linear(num_input, hidden), torch.nn.Linear(hidden, num_output)])
+
+    def forward(self, x):
+        return self.layers[1](F.relu(self.layers[0](x)))
+
+
+class _Head(torch.nn.Module):
+    """``HeadNetwork`` (GN0/models.py:318-334,368-384) with value_head_type='mlp',
+    value_aggr_types=('sum','max','min','mean'), noisy_dqn=False."""
+
+    def __init__(self, hidden: int, num_layers: int):
+        super().__init__()
+        self.gnn = _SageStack(hidden, hidden, num_layers)
+        self.linear = torch.nn.Linear(hidden, 1)
+        self.value_head = _MLP(hidden // 2, 4 * hidden, 1)
+
+    def forward(self, x, edge_index, graph_indices, num_graphs, advantages_only=False):
+        x = self.gnn(x, edge_index)
+        adv = self.linear(x)
+        if advantages_only:
+            return adv
+        parts = [scatter(x, graph_indices, num_graphs, a) for a in ("sum", "max", "min", "mean")]
+        return adv, self.value_head(torch.cat(parts, dim=1))
+
+
+class ModernTwoHeadedOracle(torch.nn.Module):
+    """``get_pre_defined('modern_two_headed', args)`` with norm=False, noisy_dqn=False
+    (GN0/models.py:928-947 -> DuellingTwoHeaded :477-590).  Parameter names follow PyG 2.2.0 /
+    the reference attribute accesses so state_dicts interchange with the product module."""
+
+    def __init__(self, hidden_channels: int, num_layers: int, num_head_layers: int = 2):
+        super().__init__()
+        self.gnn = _SageStack(2, hidden_channels, num_layers)
+        self.maker_head = _Head(hidden_channels, num_head_layers)
+        self.breaker_head = _Head(hidden_channels, num_head_layers)
+        self.final_conv_acts = None
+
+    def forward(self, x, edge_index, graph_indices=None, ptr=None, set_cache=False,
+                advantages_only=False, seperate=False):
+        assert torch.all(x[:, 2] == x[0, 2])                                   # models.py:538
+        is_maker = x[0, 2]
+        x = x[:, :2]
+        if graph_indices is None:                                              # models.py:542-543
+            graph_indices = torch.zeros(x.size(0), dtype=torch.long, device=x.device)
+        num_graphs = int(graph_indices.max()) + 1 if graph_indices.numel() else 0
+        embeds = self.gnn(x, edge_index)
+        self.final_conv_acts = embeds
+        head = self.maker_head if is_maker == 1 else self.breaker_head        # models.py:556-565
+        res = head(embeds, edge_index, graph_indices, num_graphs, advantages_only=advantages_only)
+        if advantages_only:
+            return 2 * torch.tanh(res)                                         # models.py:567-569
+        adv = 2 * torch.tanh(res[0])
+        value = torch.tanh(res[1])
+        adv_means = scatter(adv, graph_indices, num_graphs, "mean")            # models.py:578
+        centred = adv - adv_means.index_select(0, graph_indices)
+        if seperate:
+            return value.squeeze(), centred.squeeze()
+        return (value.index_select(0, graph_indices) + centred).squeeze()     # models.py:584
+
+    def simple_forward(self, data):
+        if hasattr(data, "batch") and data.batch is not None:
+            return self.forward(data.x, data.edge_index, data.batch, getattr(data, "ptr", None))
+        return self.forward(data.x, data.edge_index)
+
+
+def rainbow_loss(q: torch.Tensor, ptr: torch.Tensor, action: torch.Tensor, target: torch.Tensor,
+                 weight: torch.Tensor) -> torch.Tensor:
+    """The scalar the learner differentiates: Rainbow/common/rainbow.py:301-312 with MSE --
+    ``td_est = Q[action + ptr[:-1]]``; ``loss = mean(w * (td_tgt - td_est)^2)``."""
+    td_est = q[action + ptr[:-1]]
+    return torch.mean(weight * (target - td_est) ** 2)
+
+
+def flops_forward(n_nodes: int, num_graphs: int, hidden: int, num_layers: int, num_head_layers: int = 2,
+                  advantages_only: bool = False) -> int:
+    """Algorithmic FLOPs: node-linear contractions of the un-padded model."""
+    H = hidden
+    per_node = 4 * 2 * H + (num_layers - 1 + num_head_layers) * 4 * H * H + 2 * H
+    f = n_nodes * per_node
+    if not advantages_only:
+        f += num_graphs * 2 * (4 * H * (H // 2) + (H // 2))
+    return f

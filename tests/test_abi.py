@@ -1,0 +1,55 @@
+"""CPU: the C-ABI library builds, loads and exports every symbol include/hexgnn.h declares."""
+import ctypes
+import os
+import re
+
+from gnn_hex_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_header_symbols_exported(lib_built):
+    hdr = open(os.path.join(ROOT, "include", "hexgnn.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(hexgnn_[a-z_0-9]+)\s*\(", hdr))
+    assert declared == set(_lib.EXPORTS), declared ^ set(_lib.EXPORTS)
+    so = ctypes.CDLL(lib_built)
+    for name in declared:
+        assert hasattr(so, name), name
+
+
+def test_abi_version_and_param_tables(lib_built):
+    l = _lib.lib()
+    assert l.hexgnn_abi_version() == _lib.ABI_VERSION
+    # parameter counts from SURVEY.md §7.0
+    assert l.hexgnn_param_count(_lib.make_desc(110, 15, 2)) == 486974
+    assert l.hexgnn_param_count(_lib.make_desc(35, 10, 2)) == 37382
+    offs = _lib.param_offsets(_lib.make_desc(35, 10, 2))
+    assert len(offs) == 3 * 10 + 2 * (3 * 2 + 6)
+    assert offs == sorted(offs) and offs[0] == 0
+
+
+def test_error_convention(lib_built):
+    l = _lib.lib()
+    bad = _lib.make_desc(35, 10, 2)
+    bad.in_channels = 3
+    assert l.hexgnn_param_count(bad) == -1
+    s = _lib.HexSizes()
+    rc = l.hexgnn_sizes(ctypes.byref(_lib.make_desc(35, 10, 2)), 10, 10, 1, 77, ctypes.byref(s))
+    assert rc == -2 and b"tile_rows" in l.hexgnn_last_error()
+    # null pointers are rejected before any CUDA call
+    rc = l.hexgnn_forward(ctypes.byref(_lib.make_desc(35, 10, 2)), None, None, 1, 0, 1, None, 128, 0, None, None, None,
+                          None, 0, None)
+    assert rc == -1
+
+
+def test_state_dict_names_match_reference_convention(lib_built):
+    from gnn_hex_b200 import ModernTwoHeaded
+    m = ModernTwoHeaded(35, 10)
+    keys = list(m.state_dict().keys())
+    assert "gnn.convs.0.lin_l.weight" in keys and "gnn.convs.0.lin_l.bias" in keys
+    assert "gnn.convs.9.lin_r.weight" in keys and "gnn.convs.0.lin_r.bias" not in keys
+    assert "maker_head.gnn.convs.1.lin_l.weight" in keys and "breaker_head.linear.bias" in keys
+    assert "maker_head.value_head.layers.0.weight" in keys and "maker_head.value_head.layers.1.bias" in keys
+    assert tuple(m.maker_head.value_head.layers[0].weight.shape) == (17, 140)
+    assert m.supports_cache and not m.gnn.has_cache and m.gnn.hidden_channels == 35

@@ -1,0 +1,205 @@
+"""GPU (B200): parity of the CUDA path, called through the C-ABI, against the CPU oracle.
+
+Bars (BASELINE.json north_star): CSR / batching bit-exact; Q-values and gradients within 1e-5
+relative (fp32).  Nothing here reads /root/reference."""
+import pytest
+import torch
+
+from gnn_hex_b200 import ModernTwoHeaded, data, ops, _lib
+from oracle import hexgnn_oracle as orc
+from helpers import REL_TOL, grad_errs, loss_inputs, make_pair, rel_err
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _csr_check(b, **kw):
+    d = b.to(DEV)
+    csr = ops.build_csr(d.edge_index, **{k: (getattr(d, v) if isinstance(v, str) else v) for k, v in kw.items()})
+    rowptr, col = orc.csr_by_destination(b.edge_index, b.x.shape[0])
+    assert int(csr.status.item()) == 0
+    assert torch.equal(csr.rowptr.cpu(), rowptr)
+    assert torch.equal(csr.col.cpu(), col)
+    assert torch.equal(csr.gptr.cpu().long(), b.ptr)
+    return csr
+
+
+@pytest.mark.parametrize("fixture", ["pos_11x11_seed1234.npz", "pos_7x7_seed1234.npz"])
+def test_csr_bit_exact(fixture):
+    gs = data.load_positions(fixture, maker=1)
+    b = data.collate(gs)
+    _csr_check(b, batch="batch", ptr="ptr", num_nodes=b.x.shape[0])
+    _csr_check(b, batch="batch", num_nodes=b.x.shape[0], num_graphs=b.num_graphs)
+    _csr_check(b, ptr="ptr", num_nodes=b.x.shape[0])
+    # shuffled edge order: still == stable sort by destination of THAT order
+    perm = torch.randperm(b.edge_index.shape[1], generator=torch.Generator().manual_seed(5))
+    b2 = data.HexBatch(x=b.x, edge_index=b.edge_index[:, perm].contiguous(), batch=b.batch, ptr=b.ptr,
+                       num_graphs=b.num_graphs)
+    csr = _csr_check(b2, batch="batch", ptr="ptr", num_nodes=b.x.shape[0])
+    # tiles: whole graphs, <= 128 rows, cover everything
+    t = csr.tile_g0.cpu()[: int(csr.ntiles.item()) + 1]
+    assert t[0] == 0 and t[-1] == b.num_graphs and torch.all(t[1:] > t[:-1])
+    rows = b.ptr[t[1:]] - b.ptr[t[:-1]]
+    assert rows.max() <= 128
+
+
+def test_csr_single_graph_and_empty_graphs():
+    g = data.empty_board(11)
+    d = g.to(DEV)
+    csr = ops.build_csr(d.edge_index, num_nodes=123)
+    rowptr, col = orc.csr_by_destination(g.edge_index, 123)
+    assert torch.equal(csr.rowptr.cpu(), rowptr) and torch.equal(csr.col.cpu(), col)
+    assert csr.gptr.cpu().tolist() == [0, 123] and int(csr.ntiles.item()) == 1
+    # batch vector that skips graph ids (empty graphs 1 and 3)
+    batch = torch.cat([torch.zeros(123, dtype=torch.long), torch.full((123,), 2, dtype=torch.long)])
+    ei = torch.cat([g.edge_index, g.edge_index + 123], 1)
+    csr = ops.build_csr(ei.to(DEV), batch.to(DEV), num_nodes=246, num_graphs=4)
+    assert csr.gptr.cpu().tolist() == [0, 123, 123, 246, 246]
+    assert int(csr.status.item()) == 0
+
+
+def test_csr_flags_bad_input():
+    g = data.empty_board(5)
+    ei = g.edge_index.clone()
+    ei[0, 0] = 10_000
+    csr = ops.build_csr(ei.to(DEV), num_nodes=27)
+    assert int(csr.status.item()) & _lib.ST_EDGE_CROSSES
+    batch = torch.tensor([0] * 20 + [1] * 3 + [0] * 4)
+    csr = ops.build_csr(g.edge_index.to(DEV), batch.to(DEV), num_nodes=27, num_graphs=2)
+    assert int(csr.status.item()) & _lib.ST_BATCH_UNSORTED
+    with pytest.raises(_lib.HexGnnError):
+        csr.raise_on_error()
+
+
+CONFIGS = {
+    "S": dict(hidden=35, layers=10, fixture="pos_7x7_seed1234.npz", board=7),
+    "L": dict(hidden=110, layers=15, fixture="pos_11x11_seed1234.npz", board=11),
+}
+
+
+def _batch(cfg, kind, maker, count):
+    if kind == "empty":
+        gs = [data.empty_board(cfg["board"], maker)] * count
+    else:
+        gs = data.load_positions(cfg["fixture"], maker=maker)[:count]
+    return data.collate(gs)
+
+
+@pytest.mark.parametrize("name,kind,maker,count", [
+    ("S", "play", 1, 256), ("S", "play", 0, 64), ("S", "empty", 1, 32),
+    ("L", "play", 1, 64), ("L", "play", 0, 32), ("L", "empty", 0, 16),
+])
+def test_forward_parity(name, kind, maker, count):
+    cfg = CONFIGS[name]
+    o, m = make_pair(cfg["hidden"], cfg["layers"])
+    m = m.to(DEV)
+    b = _batch(cfg, kind, maker, count)
+    d = b.to(DEV)
+    with torch.no_grad():
+        q_ref = o(b.x, b.edge_index, b.batch, b.ptr)
+        a_ref = o(b.x, b.edge_index, b.batch, advantages_only=True)
+        v_ref, c_ref = o(b.x, b.edge_index, b.batch, seperate=True)
+        q = m(d.x, d.edge_index, d.batch, d.ptr)
+        a = m(d.x, d.edge_index, d.batch, d.ptr, advantages_only=True)
+        v, c = m(d.x, d.edge_index, d.batch, d.ptr, seperate=True)
+    assert q.shape == q_ref.shape and a.shape == a_ref.shape and v.shape == v_ref.shape
+    assert rel_err(q, q_ref) <= REL_TOL
+    assert rel_err(a, a_ref) <= REL_TOL
+    assert rel_err(v, v_ref) <= REL_TOL and rel_err(c, c_ref) <= REL_TOL * max(1.0, float(a_ref.abs().max() / c_ref.abs().max()))
+    # simple_forward == forward (models.py:586-590) and single-graph call (graph_indices=None)
+    with torch.no_grad():
+        assert torch.equal(m.simple_forward(d), q)
+        g0 = data.HexGraph(x=b.x[: b.ptr[1]], edge_index=b.edge_index[:, b.edge_index[1] < b.ptr[1]])
+        q0 = m(g0.x.to(DEV), g0.edge_index.to(DEV))
+    assert rel_err(q0, q_ref[: b.ptr[1]]) <= REL_TOL
+
+
+@pytest.mark.parametrize("name,kind,maker,count", [
+    ("S", "play", 1, 256), ("S", "empty", 0, 16), ("L", "play", 1, 48), ("L", "empty", 1, 8),
+])
+def test_backward_parity(name, kind, maker, count):
+    cfg = CONFIGS[name]
+    o, m = make_pair(cfg["hidden"], cfg["layers"])
+    m = m.to(DEV)
+    b = _batch(cfg, kind, maker, count)
+    d = b.to(DEV)
+    action, target, weight = loss_inputs(b)
+    loss_ref = orc.rainbow_loss(o(b.x, b.edge_index, b.batch, b.ptr), b.ptr, action, target, weight)
+    loss_ref.backward()
+    q = m(d.x, d.edge_index, d.batch, d.ptr)
+    loss = orc.rainbow_loss(q, d.ptr, action.to(DEV), target.to(DEV), weight.to(DEV))
+    loss.backward()
+    assert rel_err(loss, loss_ref) <= REL_TOL
+    worst, wname = grad_errs(m, o)
+    assert worst <= REL_TOL, (worst, wname)
+    # the head not taken gets exactly zero gradient, like autograd leaves it untouched
+    other = m.breaker_head if maker == 1 else m.maker_head
+    assert all(float(p.grad.abs().max()) == 0.0 for p in other.parameters())
+    # embedding tap (models.py:553)
+    assert rel_err(m.final_conv_acts, o.final_conv_acts) <= REL_TOL
+
+
+def test_backward_other_modes_and_embed_grads():
+    o, m = make_pair(35, 10)
+    m = m.to(DEV)
+    m.capture_embed_grads = True
+    b = _batch(CONFIGS["S"], "play", 1, 40)
+    d = b.to(DEV)
+    gen = torch.Generator().manual_seed(3)
+    wn = torch.randn(b.x.shape[0], generator=gen)
+    wv = torch.randn(b.num_graphs, generator=gen)
+    # seperate=True
+    v_ref, c_ref = o(b.x, b.edge_index, b.batch, seperate=True)
+    o.final_conv_acts.retain_grad()
+    ((c_ref * wn).sum() + (v_ref * wv).sum()).backward()
+    v, c = m(d.x, d.edge_index, d.batch, d.ptr, seperate=True)
+    ((c * wn.to(DEV)).sum() + (v * wv.to(DEV)).sum()).backward()
+    worst, wname = grad_errs(m, o)
+    assert worst <= REL_TOL, (worst, wname)
+    assert rel_err(m.final_conv_grads, o.final_conv_acts.grad) <= REL_TOL
+    # advantages_only=True
+    o.zero_grad(); m.zero_grad()
+    (o(b.x, b.edge_index, b.batch, advantages_only=True).squeeze(1) * wn).sum().backward()
+    (m(d.x, d.edge_index, d.batch, d.ptr, advantages_only=True).squeeze(1) * wn.to(DEV)).sum().backward()
+    worst, wname = grad_errs(m, o)
+    assert worst <= REL_TOL, (worst, wname)
+
+
+def test_deterministic_bitwise():
+    _, m = make_pair(110, 15)
+    m = m.to(DEV)
+    b = _batch(CONFIGS["L"], "play", 1, 96).to(DEV)
+    action, target, weight = [t.to(DEV) for t in loss_inputs(data.collate(data.load_positions(CONFIGS["L"]["fixture"], maker=1)[:96]))]
+    outs = []
+    for _ in range(3):
+        m.zero_grad()
+        q = m(b.x, b.edge_index, b.batch, b.ptr)
+        orc.rainbow_loss(q, b.ptr, action, target, weight).backward()
+        outs.append((q.detach().clone(), torch.cat([p.grad.reshape(-1) for p in m.parameters()]).clone()))
+    for q, g in outs[1:]:
+        assert torch.equal(q, outs[0][0]) and torch.equal(g, outs[0][1])
+
+
+def test_ragged_mix_forward_and_oversize_flag():
+    o, m = make_pair(110, 15)
+    m = m.to(DEV)
+    gs = data.load_positions("pos_mix_5_13_seed1234.npz", maker=1)
+    small = [g for g in gs if g.x.shape[0] <= 128 and g.edge_index.shape[1] <= 1024][:96]
+    b = data.collate(small)
+    d = b.to(DEV)
+    with torch.no_grad():
+        q = m(d.x, d.edge_index, d.batch, d.ptr)
+        q_ref = o(b.x, b.edge_index, b.batch, b.ptr)
+    assert rel_err(q, q_ref) <= REL_TOL
+    big = [g for g in gs if g.x.shape[0] > 128][:2] + small[:2]
+    d = data.collate(big).to(DEV)
+    m.strict = True
+    with torch.no_grad(), pytest.raises(_lib.HexGnnError):
+        m(d.x, d.edge_index, d.batch, d.ptr)
+
+
+def test_cpu_tensors_are_rejected_loudly():
+    _, m = make_pair(35, 10)
+    b = _batch(CONFIGS["S"], "play", 1, 2)
+    with pytest.raises(_lib.HexGnnError):
+        m(b.x, b.edge_index, b.batch, b.ptr)

@@ -1,0 +1,155 @@
+"""CPU: pin the oracle (oracle/hexgnn_oracle.py) -- golden fixtures from the reference's C++ game,
+a hand-computed known answer, fp64 gradcheck and the structural invariants of the model."""
+import numpy as np
+import torch
+
+from gnn_hex_b200 import data
+from oracle import hexgnn_oracle as orc
+
+
+def test_empty_board_matches_reference_cpp_game():
+    """hex_board_undirected_edges (restating hex_board_game.py:214-232) == the compiled C++ game."""
+    z = np.load(data.GOLDEN_DIR + "/empty_boards_3_13.npz")
+    eo = 0
+    for g, size in enumerate(z["size"]):
+        n, ne = int(z["n"][g]), int(z["ne"][g])
+        ref = set(zip(z["src"][eo:eo + ne].tolist(), z["dst"][eo:eo + ne].tolist()))
+        eo += ne
+        mine = orc.hex_board_undirected_edges(int(size))
+        sym = set(mine) | {(b, a) for a, b in mine}
+        assert n == size * size + 2
+        assert sym == ref, f"size {size}"
+    # sizes pinned by construction: 11x11 -> 123/644, 7x7 -> 51/244
+    assert 2 * len(orc.hex_board_undirected_edges(11)) == 644
+    assert 2 * len(orc.hex_board_undirected_edges(7)) == 244
+
+
+def test_fixture_graphs_are_valid_and_symmetric():
+    for name in ("pos_11x11_seed1234.npz", "pos_7x7_seed1234.npz", "pos_mix_5_13_seed1234.npz"):
+        gs = data.load_positions(name)
+        assert len(gs) == 256
+        for g in gs[:40]:
+            ei = g.edge_index
+            n = g.x.shape[0]
+            assert ei.min() >= 0 and ei.max() < n
+            fwd = set(zip(ei[0].tolist(), ei[1].tolist()))
+            assert len(fwd) == ei.shape[1]                       # no duplicates
+            assert all((b, a) in fwd for a, b in fwd)            # symmetric
+            assert all(a != b for a, b in fwd)                   # no self loops
+            assert torch.equal(g.x[:, 0], torch.bincount(ei[1], minlength=n).float())
+            assert g.x[0, 1] == 1 and g.x[1, 1] == 1 and g.x[2:, 1].sum() == 0
+
+
+def test_collate_matches_cpp_collate_batch_semantics():
+    gs = data.load_positions("pos_7x7_seed1234.npz")[:5]
+    b = data.collate(gs)
+    o = orc.collate(gs)
+    for k in ("x", "edge_index", "batch", "ptr"):
+        assert torch.equal(getattr(b, k), getattr(o, k)), k
+    # util.cpp:22-41: graph i's edges are shifted by the node offset, batch[i-range] = i
+    off = 0
+    for i, g in enumerate(gs):
+        n = g.x.shape[0]
+        assert torch.all(b.batch[off:off + n] == i)
+        off += n
+    assert b.ptr[-1] == off
+
+
+def test_known_answer_debugging_manager_graph():
+    """Hand-computed forward on the reference's 4-node fixture (multi_env_manager.py:170-175):
+    x = [[0,0,1]]*3 + [[1,1,1]], one directed edge 2 -> 3, H=2, one body layer, one head layer."""
+    m = orc.ModernTwoHeadedOracle(2, 1, 1).double()
+    with torch.no_grad():
+        for p in m.parameters():
+            p.zero_()
+        c = m.gnn.convs[0]
+        c.lin_l.weight.copy_(torch.tensor([[1., 0.], [0., 1.]]))   # mean of neighbours
+        c.lin_r.weight.copy_(torch.tensor([[1., 0.], [0., 2.]]))   # root
+        c.lin_l.bias.copy_(torch.tensor([0.5, -0.5]))
+        h = m.maker_head
+        hc = h.gnn.convs[0]
+        hc.lin_l.weight.copy_(torch.eye(2)); hc.lin_r.weight.copy_(torch.eye(2))
+        h.linear.weight.copy_(torch.tensor([[1., -1.]])); h.linear.bias.fill_(0.25)
+        h.value_head.layers[0].weight.copy_(torch.tensor([[1., 0, 0, 0, 0, 0, 0, 0]]))  # sum of channel 0
+        h.value_head.layers[1].weight.fill_(0.5)
+    x = torch.tensor([[0, 0, 1], [0, 0, 1], [0, 0, 1], [1, 1, 1]], dtype=torch.float64)
+    ei = torch.tensor([[2], [3]])
+    q = m(x, ei)
+    # body: rows 0..2: x=(0,0), no in-edges -> relu(b) = (0.5, 0); row 3: mean = x_2 = (0,0), root (1,2)+b -> (1.5, 1.5)
+    # head layer: rows 0,1,2 -> (0.5,0) (+ nothing); row 3: mean = h_2 = (0.5,0) + own (1.5,1.5) -> (2.0,1.5)
+    g = torch.tensor([[0.5, 0.], [0.5, 0.], [0.5, 0.], [2.0, 1.5]], dtype=torch.float64)
+    a = 2 * torch.tanh(g[:, 0] - g[:, 1] + 0.25)
+    v = torch.tanh(0.5 * torch.relu(g[:, 0].sum()))
+    expect = v + a - a.mean()
+    assert torch.allclose(q, expect, atol=1e-12), (q, expect)
+    assert torch.allclose(m.final_conv_acts, torch.tensor([[0.5, 0], [0.5, 0], [0.5, 0], [1.5, 1.5]], dtype=torch.float64))
+    # breaker flag takes the (all-zero) breaker head: Q = 0
+    x2 = x.clone(); x2[:, 2] = 0
+    assert torch.allclose(m(x2, ei), torch.zeros(4, dtype=torch.float64))
+
+
+def _small_batch(k=3):
+    gs = data.load_positions("pos_7x7_seed1234.npz", maker=1)[:k]
+    return gs, data.collate(gs)
+
+
+def test_batched_equals_per_graph_and_output_modes():
+    torch.manual_seed(0)
+    m = orc.ModernTwoHeadedOracle(12, 3, 2).double()
+    gs, b = _small_batch(4)
+    x = b.x.double()
+    q = m(x, b.edge_index, b.batch, b.ptr)
+    single = torch.cat([m(g.x.double(), g.edge_index) for g in gs])
+    assert torch.allclose(q, single, atol=1e-12)
+    adv = m(x, b.edge_index, b.batch, advantages_only=True)
+    assert adv.shape == (x.shape[0], 1) and adv.abs().max() <= 2
+    v, c = m(x, b.edge_index, b.batch, seperate=True)
+    assert v.shape == (4,) and torch.allclose(v[b.batch] + c, q, atol=1e-12)
+
+
+def test_permutation_equivariance_and_edge_order_invariance():
+    torch.manual_seed(0)
+    m = orc.ModernTwoHeadedOracle(10, 3, 2).double()
+    g = data.load_positions("pos_7x7_seed1234.npz", maker=0)[7]
+    x, ei = g.x.double(), g.edge_index
+    q = m(x, ei)
+    gen = torch.Generator().manual_seed(3)
+    n = x.shape[0]
+    perm = torch.cat([torch.arange(2), 2 + torch.randperm(n - 2, generator=gen)])  # terminals stay rows 0,1
+    inv = torch.empty_like(perm); inv[perm] = torch.arange(n)
+    qp = m(x[perm], inv[ei])
+    assert torch.allclose(qp, q[perm], atol=1e-11)
+    eperm = torch.randperm(ei.shape[1], generator=gen)
+    assert torch.allclose(m(x, ei[:, eperm]), q, atol=1e-11)
+
+
+def test_gradcheck_fp64():
+    torch.manual_seed(0)
+    m = orc.ModernTwoHeadedOracle(6, 2, 2).double()
+    gs, b = _small_batch(2)
+    x = b.x.double()
+    params = list(m.maker_head.parameters()) + list(m.gnn.parameters())
+    names = [n for n, _ in list(m.maker_head.named_parameters()) + list(m.gnn.named_parameters())]
+
+    def f(*ps):
+        with torch.no_grad():
+            for p, v in zip(params, ps):
+                p.copy_(v)
+        sd = {("maker_head." + n if i < len(list(m.maker_head.parameters())) else "gnn." + n): v
+              for i, (n, v) in enumerate(zip(names, ps))}
+        return torch.func.functional_call(m, sd, (x, b.edge_index, b.batch, b.ptr))
+
+    ins = [p.detach().clone().requires_grad_(True) for p in params]
+    assert torch.autograd.gradcheck(f, ins, eps=1e-6, atol=1e-5, nondet_tol=0)
+
+
+def test_csr_by_destination_is_stable():
+    ei = torch.tensor([[3, 1, 2, 0, 2, 1], [0, 0, 1, 1, 0, 2]])
+    rowptr, col = orc.csr_by_destination(ei, 4)
+    assert rowptr.tolist() == [0, 3, 5, 6, 6]
+    assert col.tolist() == [3, 1, 2, 2, 0, 1]
+
+
+def test_flops_formula_matches_survey():
+    assert orc.flops_forward(1, 0, 110, 15, advantages_only=True) == 775500
+    assert orc.flops_forward(1, 0, 35, 10, advantages_only=True) == 54250
