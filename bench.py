@@ -1,0 +1,353 @@
+"""bench.py -- headline benchmark of the fused hot path (BASELINE.json configs[1]).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload play|empty]
+    torchrun --nnodes=1 --nproc-per-node N ... bench.py --gpus N --steps K --warmup W
+
+One "step" = one pass of the hot path over one replay batch of 256 11x11 Hex positions per GPU:
+device CSR build + fused forward (with stash) + fused backward + deterministic gradient reduction
+(+ NCCL all-reduce of the flat gradient when N > 1).  The optimizer is NOT part of the path
+ and is not timed.  Prints ONE JSON line on rank 0.
+
+  value  graphs/s with the batch already resident in HBM (CUDA events, L2 flushed between steps)
+  e2e    graphs/s through the public module API with HOST (pinned) inputs: H2D of x / edge_index /
+         batch / ptr + forward + loss + backward + D2H of the loss, every step
+  roofline / cpu_baseline: see DESIGN.md "Measurement".
+`--impl reference` times the CPU restatement of the reference PyG path (oracle/, kind "port":
+torch_geometric is not installable here) on the host cores for the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "Hex graphs/sec (fwd+bwd, GNN-L 11x11 b256)"
+UNIT = "graphs/s"
+HIDDEN, LAYERS, HEAD_LAYERS, BATCH = 110, 15, 2, 256
+FIXTURE = "pos_11x11_seed1234.npz"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="fused", choices=["fused", "reference"])
+    ap.add_argument("--workload", default="play", choices=["play", "empty"],
+                    help="play: 256 seeded random-playout positions (mean 77 nodes); empty: 256 empty boards (123 nodes)")
+    ap.add_argument("--path", default="auto", choices=["auto", "simt", "tc"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        d["source"] = "measured"
+        return d
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
+
+
+def make_batch(workload, rank=0):
+    """256 positions per rank.  Rank r rotates the fixture by 32*r so shards differ."""
+    from gnn_hex_b200 import data
+    if workload == "empty":
+        gs = [data.empty_board(11, 1)] * BATCH
+    else:
+        gs = data.load_positions(FIXTURE, maker=1)
+        k = (32 * rank) % len(gs)
+        gs = (gs[k:] + gs[:k])[:BATCH]
+    return data.collate(gs)
+
+
+def loss_inputs(batch, seed=1):
+    """Rainbow learner loss inputs (rainbow.py:301-312): action per graph, TD target, PER weight."""
+    import torch
+    g = torch.Generator().manual_seed(seed)
+    n = batch.ptr[1:] - batch.ptr[:-1]
+    u = torch.rand(batch.num_graphs, generator=g)
+    action = (2 + (u * (n - 2).clamp(min=1)).long()).clamp(max=n - 1).clamp(min=0)
+    target = torch.rand(batch.num_graphs, generator=g) * 2 - 1
+    weight = torch.rand(batch.num_graphs, generator=g) * 0.5 + 0.5
+    return action, target, weight
+
+
+def flops_train(batch):
+    """Algorithmic FLOPs of one fwd+bwd over `batch`: 3 x forward."""
+    H, L, Lh = HIDDEN, LAYERS, HEAD_LAYERS
+    per_node = 4 * 2 * H + (L - 1 + Lh) * 4 * H * H + 2 * H
+    fwd = int(batch.x.shape[0]) * per_node + batch.num_graphs * 2 * (4 * H * (H // 2) + (H // 2))
+    return fwd, 3 * fwd
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + self.Q,
+                                       "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            c = [t.strip() for t in line.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        self.f.close()
+        os.unlink(self.f.name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def time_cpu_port(batch, steps, warmup, max_seconds=None):
+    """fwd+bwd of the CPU restatement of the reference PyG path (oracle/, test infrastructure used
+    here only as the reported CPU baseline) on all host threads.  Returns (graphs/s, steps run, cores)."""
+    import torch
+    from oracle import hexgnn_oracle as orc
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    torch.manual_seed(0)
+    o = orc.ModernTwoHeadedOracle(HIDDEN, LAYERS, HEAD_LAYERS)
+    action, target, weight = loss_inputs(batch)
+
+    def step():
+        o.zero_grad(set_to_none=True)
+        q = o(batch.x, batch.edge_index, batch.batch, batch.ptr)
+        loss = orc.rainbow_loss(q, batch.ptr, action, target, weight)
+        loss.backward()
+        return float(loss.detach())
+
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter()
+    done = 0
+    for _ in range(steps):
+        step()
+        done += 1
+        if max_seconds is not None and time.perf_counter() - t0 > max_seconds:
+            break
+    dt = time.perf_counter() - t0
+    return batch.num_graphs * done / dt, done, cores, dt
+
+
+def run_reference(args, rank, world):
+    """Reference arm: the reference's own CPU implementation of the path.  torch_geometric /
+    torch_scatter are absent and not installable (no network), and the model is Python, so this is
+    the oracle port (kind "port") on all host cores; rank 0 only."""
+    if rank != 0:
+        return
+    batch = make_batch(args.workload)
+    value, done, cores, dt = time_cpu_port(batch, args.steps, args.warmup)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": done, "warmup": args.warmup, "ms_per_step": 1e3 * dt / done, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, batch, 1),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": f"{done} steps of the full {batch.num_graphs}-graph batch, torch fp32 oracle"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, batch, world):
+    return {"workload": f"GNN-L modern_two_headed fwd+bwd, hidden {HIDDEN}, {LAYERS}+{HEAD_LAYERS} SAGE layers, "
+                        f"{BATCH} 11x11 Hex positions per GPU ({args.workload})",
+            "graphs_per_gpu": batch.num_graphs, "global_batch": batch.num_graphs * world,
+            "nodes_per_gpu": int(batch.x.shape[0]), "edges_per_gpu": int(batch.edge_index.shape[1]),
+            "positions": ("tests/golden/" + FIXTURE + " (reference C++ game, seeded random playouts)")
+            if args.workload == "play" else "256 empty 11x11 boards (123 nodes / 644 edges each)",
+            "parallelism": f"dp{world}", "l2": "flushed between steps (256 MiB write)",
+            "optimizer": "excluded (not on the path)", "path": args.path}
+
+
+def run_fused(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    from gnn_hex_b200 import ModernTwoHeaded, _lib, ops
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the fused path has no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    torch.manual_seed(0)
+    model = ModernTwoHeaded(HIDDEN, LAYERS, HEAD_LAYERS, path=args.path).to(dev)
+    batch = make_batch(args.workload, rank)
+    hb = batch.pin_memory()                      # HOST copy of the step's inputs (e2e arm)
+    db = batch.to(dev)                           # resident copy (value arm)
+    action, target, weight = [t.to(dev) for t in loss_inputs(batch)]
+    scale = 1.0 / world                          # loss = mean over the GLOBAL batch (rainbow.py:312)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
+    loss_host = torch.empty(1, dtype=torch.float32).pin_memory()
+
+    def td_loss(q, ptr):
+        td_est = q[action + ptr[:-1]]
+        return torch.mean(weight * (target - td_est) ** 2) * scale
+
+    def step_resident():
+        model.zero_grad(set_to_none=True)
+        q = model(db.x, db.edge_index, db.batch, db.ptr)
+        loss = td_loss(q, db.ptr)
+        loss.backward()
+        if world > 1:
+            model.allreduce_gradients()
+        return loss
+
+    def step_e2e():
+        model.zero_grad(set_to_none=True)
+        b = hb.to(dev, non_blocking=True)
+        q = model(b.x, b.edge_index, b.batch, b.ptr)
+        loss = td_loss(q, b.ptr)
+        loss.backward()
+        if world > 1:
+            model.allreduce_gradients()
+        loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
+        return loss
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def timed(step_fn, steps, sync_each=False):
+        """Sum of per-step CUDA-event durations on the current stream; L2 flushed between steps."""
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        barrier()
+        for s, e in evs:
+            flush.fill_(1)
+            s.record()
+            step_fn()
+            e.record()
+            if sync_each:
+                e.synchronize()       # e2e: the caller reads the loss before the next step
+        barrier()
+        ms = sum(s.elapsed_time(e) for s, e in evs)
+        if world > 1:
+            t = torch.tensor([ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    for _ in range(args.warmup):
+        step_resident()
+    for _ in range(max(3, args.warmup // 2)):
+        step_e2e()
+    barrier()
+
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    _lib.profile_enable(True)
+    _lib.profile_read(0); _lib.profile_read(1)
+    l0 = ops.launch_counter
+    ms_total = timed(step_resident, args.steps)
+    launches = ops.launch_counter - l0
+    fwd_ms, fwd_n = _lib.profile_read(0)
+    bwd_ms, bwd_n = _lib.profile_read(1)
+    _lib.profile_enable(False)
+    ms_e2e = timed(step_e2e, args.steps, sync_each=True)
+    clocks = sampler.stop() if sampler else None
+
+    status = int(model.last_csr.status.item()) if getattr(model, "last_csr", None) is not None else 0
+    if status:
+        raise SystemExit(f"bench.py: device status {status} (a graph did not fit a tile?)")
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    graphs = batch.num_graphs * world
+    f_fwd, f_train = flops_train(batch)
+    pk = peaks()
+    # the node-linear contractions run in fp32 (SIMT) or 3xTF32 (tcgen05); the tensor-pipe roofline of
+    # an fp32-exact result is the TF32 dense peak = 1/2 of the measured bf16 peak (B200_PROFILING.md).
+    tf32_peak = 0.5 * pk["bf16_tflops"]
+    bwd_avg_ms = bwd_ms / max(bwd_n, 1)
+    achieved = (2 * f_fwd) / (bwd_avg_ms * 1e-3) / 1e12 if bwd_n else None
+    line = {
+        "metric": METRIC, "value": graphs * args.steps / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, batch, world),
+        "clocks": clocks,
+        "e2e": {"value": graphs * args.steps / (ms_e2e * 1e-3), "unit": UNIT,
+                "h2d_bytes_per_step": int(sum(t.numel() * t.element_size() for t in (hb.x, hb.edge_index, hb.batch, hb.ptr))),
+                "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "tensor", "kernel": "sage_bwd (fused backward, all layers)",
+                     "achieved": achieved, "peak": tf32_peak, "unit": "TFLOP/s",
+                     "frac": (achieved / tf32_peak) if achieved else None, "traffic": None,
+                     "peak_source": f"0.5 x bf16_tflops ({pk['source']}) = dense TF32",
+                     "flops_per_launch": 2 * f_fwd, "avg_launch_ms": bwd_avg_ms,
+                     "fwd_avg_launch_ms": fwd_ms / max(fwd_n, 1), "fwd_flops_per_launch": f_fwd,
+                     "kernel_share_of_step": (bwd_ms + fwd_ms) / ms_total},
+    }
+    if not args.no_cpu_baseline:
+        v, done, cores, dt = time_cpu_port(batch, 1000, 2, max_seconds=args.cpu_seconds)
+        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                                "sample": f"{done} fwd+bwd steps of the same {batch.num_graphs}-graph batch "
+                                          f"({dt:.1f} s), torch fp32 restatement of the PyG path"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world == 1 and args.gpus > 1:
+        # launched without torchrun: re-exec under torch.distributed.run
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29531"),
+               os.path.abspath(__file__)] + sys.argv[1:]
+        raise SystemExit(subprocess.call(cmd))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_fused(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

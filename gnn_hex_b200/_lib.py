@@ -22,7 +22,7 @@ STATUS_NAMES = {
     ST_FLAG_MIXED: "x[:,2] is not constant over the batch (reference asserts this, GN0/models.py:538)",
 }
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 
 class HexModelDesc(C.Structure):
@@ -41,7 +41,8 @@ class HexCsrLayout(C.Structure):
 
 
 EXPORTS = ["hexgnn_abi_version", "hexgnn_last_error", "hexgnn_param_count", "hexgnn_param_offsets",
-           "hexgnn_sizes", "hexgnn_csr_layout", "hexgnn_build_csr", "hexgnn_forward", "hexgnn_backward"]
+           "hexgnn_sizes", "hexgnn_csr_layout", "hexgnn_build_csr", "hexgnn_forward", "hexgnn_backward",
+           "hexgnn_profile_enable", "hexgnn_profile_read"]
 
 _lib = None
 
@@ -79,6 +80,10 @@ def lib():
     l.hexgnn_forward.argtypes = [D, p, p, i64, i64, i64, p, i32, i32, p, p, p, p, sz, p]
     l.hexgnn_backward.restype = C.c_int
     l.hexgnn_backward.argtypes = [D, p, p, i64, i64, i64, p, i32, i32, p, p, p, p, p, p, sz, p]
+    l.hexgnn_profile_enable.restype = C.c_int
+    l.hexgnn_profile_enable.argtypes = [C.c_int]
+    l.hexgnn_profile_read.restype = C.c_int
+    l.hexgnn_profile_read.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(i64)]
     v = l.hexgnn_abi_version()
     if v != ABI_VERSION:
         raise HexGnnError(f"libhexgnn.so ABI {v} != binding ABI {ABI_VERSION}: rebuild")
@@ -115,3 +120,14 @@ def param_offsets(desc):
     arr = (C.c_int64 * n)()
     lib().hexgnn_param_offsets(C.byref(desc), arr, n)
     return list(arr)
+
+
+def profile_enable(on=True):
+    check(lib().hexgnn_profile_enable(1 if on else 0), "hexgnn_profile_enable")
+
+
+def profile_read(which):
+    """(total ms, launches) of the dominant kernel (0 forward, 1 backward) since the last read."""
+    ms, n = C.c_double(0.0), C.c_int64(0)
+    check(lib().hexgnn_profile_read(which, C.byref(ms), C.byref(n)), "hexgnn_profile_read")
+    return ms.value, n.value

@@ -1,6 +1,7 @@
 // C-ABI of libhexgnn.so (declared in include/hexgnn.h).
 #include <stdarg.h>
 #include <string.h>
+#include <vector>
 #include "common.cuh"
 
 namespace hexgnn {
@@ -25,6 +26,34 @@ int bwd_grid_ctas() {
       sms = 148;
   }
   return sms;
+}
+
+// ---- profiling: thread-local event pairs --------------------------------------------------------
+struct ProfState {
+  bool on = false;
+  std::vector<cudaEvent_t> ev[2];  // start, stop, start, stop, ...
+  size_t used[2] = {0, 0};
+};
+static ProfState g_prof;  // process-wide: autograd runs hexgnn_backward on its own thread
+
+ProfScope::ProfScope(int which, cudaStream_t st) : slot_(-1), st_(st) {
+  if (!g_prof.on || which < 0 || which > 1) return;
+  auto& v = g_prof.ev[which];
+  size_t& u = g_prof.used[which];
+  if (u + 2 > v.size()) {
+    cudaEvent_t a, b;
+    if (cudaEventCreate(&a) != cudaSuccess || cudaEventCreate(&b) != cudaSuccess) return;
+    v.push_back(a);
+    v.push_back(b);
+  }
+  slot_ = which * (1 << 28) + (int)u;
+  cudaEventRecord(v[u], st);
+  u += 2;
+}
+ProfScope::~ProfScope() {
+  if (slot_ < 0) return;
+  const int which = slot_ >> 28, u = slot_ & ((1 << 28) - 1);
+  cudaEventRecord(g_prof.ev[which][u + 1], st_);
 }
 
 static bool tile_rows_ok(int tile_rows) { return tile_rows == 128; }
@@ -144,6 +173,28 @@ int hexgnn_backward(const HexModelDesc* desc, const float* params, const float* 
   if (rc) return rc;
   CsrView cv = csr_view(const_cast<void*>(csr), N, E, B);
   return launch_reduce_grads(d, pm, x, partials, nparts, cv.ntiles, packed_sum, grad_params, st);
+}
+
+int hexgnn_profile_enable(int on) {
+  g_prof.on = on != 0;
+  if (!on) g_prof.used[0] = g_prof.used[1] = 0;
+  return HEXGNN_OK;
+}
+
+int hexgnn_profile_read(int which, double* total_ms, int64_t* launches) {
+  if (which < 0 || which > 1 || !total_ms || !launches) { set_error("profile_read: bad argument"); return HEXGNN_E_BADARG; }
+  double tot = 0.0;
+  const size_t u = g_prof.used[which];
+  for (size_t i = 0; i + 1 < u; i += 2) {
+    HEX_CUDA_CHECK(cudaEventSynchronize(g_prof.ev[which][i + 1]));
+    float ms = 0.f;
+    HEX_CUDA_CHECK(cudaEventElapsedTime(&ms, g_prof.ev[which][i], g_prof.ev[which][i + 1]));
+    tot += ms;
+  }
+  *total_ms = tot;
+  *launches = (int64_t)(u / 2);
+  g_prof.used[which] = 0;
+  return HEXGNN_OK;
 }
 
 }  // extern "C"

@@ -181,6 +181,15 @@ void set_error(const char* fmt, ...);
     }                                                                                   \
   } while (0)
 
+// ---- per-kernel device timing for bench.py (api.cu) -------------------------------------------
+// ProfScope brackets one launch with CUDA events on `st` when profiling is enabled on this thread.
+struct ProfScope {
+  ProfScope(int which, cudaStream_t st);
+  ~ProfScope();
+  int slot_;
+  cudaStream_t st_;
+};
+
 // ---- launchers implemented in the .cu files ---------------------------------------------------
 int launch_build_csr(const int64_t* edge_index, int64_t E, const int64_t* batch, const int64_t* ptr, int64_t N,
                      int64_t B, int tile_rows, void* csr, cudaStream_t st);

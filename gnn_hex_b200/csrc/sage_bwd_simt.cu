@@ -347,7 +347,10 @@ static int launch_bwd_t(const BwdArgs& a, int grid, cudaStream_t st) {
   using S = BwdSmem<NJ, RPW>;
   auto kern = sage_bwd_simt_kernel<NJ, RPW>;
   HEX_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::bytes));
-  kern<<<grid, kThreads, S::bytes, st>>>(a);
+  {
+    ProfScope prof(1, st);
+    kern<<<grid, kThreads, S::bytes, st>>>(a);
+  }
   HEX_CUDA_CHECK(cudaGetLastError());
   return HEXGNN_OK;
 }

@@ -213,7 +213,10 @@ static int launch_fwd_t(const FwdArgs& a, cudaStream_t st) {
   auto kern = sage_fwd_simt_kernel<NJ, RPW>;
   HEX_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::bytes));
   int grid = (int)(a.B < 1 ? 1 : (a.B > bwd_grid_ctas() ? bwd_grid_ctas() : a.B));
-  kern<<<grid, kThreads, S::bytes, st>>>(a);
+  {
+    ProfScope prof(0, st);
+    kern<<<grid, kThreads, S::bytes, st>>>(a);
+  }
   HEX_CUDA_CHECK(cudaGetLastError());
   return HEXGNN_OK;
 }

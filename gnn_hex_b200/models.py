@@ -58,20 +58,22 @@ class _HeadParams(nn.Module):
 
 
 class _FusedQ(torch.autograd.Function):
-    """Autograd node around hexgnn_forward / hexgnn_backward.  The individual parameters are
-    inputs so that each `p.grad` is filled exactly as after the reference's loss.backward()."""
+    """Autograd node around hexgnn_forward / hexgnn_backward.
+
+    Only one parameter (`anchor`) is an autograd input: it makes the outputs require grad.  The
+    backward kernel writes the whole flat gradient in one pass and the module points every
+    `p.grad` at its slice of that buffer (accumulating when the slices are still in place, exactly
+    like autograd's `+=`), so a step costs no per-parameter kernels."""
 
     @staticmethod
-    def forward(ctx, model, x, csr, flags, *params):
-        need_grad = any(ctx.needs_input_grad[4:])
+    def forward(ctx, model, x, csr, flags, anchor):
         out_nodes, out_value, stash, hp = ops.fused_forward(model._desc, model._flat, x, csr, flags,
-                                                            want_stash=need_grad, ws=model._fwd_ws(csr))
+                                                            want_stash=True, ws=model._fwd_ws(csr))
         ctx.model, ctx.csr, ctx.flags, ctx.stash = model, csr, flags, stash
         ctx.save_for_backward(x)
         ctx.flat_version = model._flat_version
-        if stash is not None:
-            L, H = model.num_layers, model.hidden_channels
-            model.final_conv_acts = stash[(L - 1) * csr.N * hp:L * csr.N * hp].view(csr.N, hp)[:, :H]
+        L, H = model.num_layers, model.hidden_channels
+        model.final_conv_acts = stash[(L - 1) * csr.N * hp:L * csr.N * hp].view(csr.N, hp)[:, :H]
         return out_nodes, out_value
 
     @staticmethod
@@ -83,13 +85,19 @@ class _FusedQ(torch.autograd.Function):
         if d_nodes is None:
             d_nodes = torch.zeros(ctx.csr.N, dtype=torch.float32, device=x.device)
         use_dv = bool(ctx.flags & ops.HEXGNN_SEPARATE) and d_value is not None
+        accumulate = model._grads_in_place()
+        out = model._grad_scratch() if accumulate else model._flat_grad_buffer()
         grad, d_emb = ops.fused_backward(model._desc, model._flat, x, ctx.csr, ctx.flags, d_nodes,
                                          d_value if use_dv else None, ctx.stash,
-                                         want_d_embeds=model.capture_embed_grads, ws=model._bwd_ws(ctx.csr))
+                                         want_d_embeds=model.capture_embed_grads, ws=model._bwd_ws(ctx.csr),
+                                         grad_out=out)
+        if accumulate:
+            model._flat_grad.add_(grad)
+        else:
+            model._point_grads()
         if d_emb is not None:
             model.final_conv_grads = d_emb[:, :model.hidden_channels]
-        grads = tuple(grad[o:o + n].view(s) for (o, n, s) in model._slices)
-        return (None, None, None, None) + grads
+        return None, None, None, None, None
 
 
 class ModernTwoHeaded(nn.Module):
@@ -124,6 +132,8 @@ class ModernTwoHeaded(nn.Module):
         self._flat_version = 0
         self._slices = None
         self._ws = {}
+        self._flat_grad = None
+        self.last_csr = None
 
     # ---- parameter order == include/hexgnn.h flat layout ---------------------------------------------
     def _ordered_params(self):
@@ -160,6 +170,8 @@ class ModernTwoHeaded(nn.Module):
         self._flat, self._slices = flat, slices
         self._flat_version += 1
         self._ws = {}
+        self._flat_grad = None
+        self._params_cache = ps
 
     def _ensure_flat(self):
         if self._flat is None or self._flat.device != self.gnn.convs[0].lin_l.weight.device:
@@ -173,6 +185,61 @@ class ModernTwoHeaded(nn.Module):
     def reflatten(self):
         """Call after replacing parameter tensors by hand (e.g. `p.data = ...`)."""
         self._flat = None
+
+    # ---- flat gradient: every p.grad is a view of one buffer (the C-ABI's `grad_params`) ----------------
+    def _flat_grad_buffer(self):
+        if self._flat_grad is None or self._flat_grad.device != self._flat.device:
+            self._flat_grad = torch.zeros_like(self._flat)
+        return self._flat_grad
+
+    def _grad_scratch(self):
+        w = self._ws.get("gscratch")
+        if w is None or w.device != self._flat.device:
+            w = torch.empty_like(self._flat)
+            self._ws["gscratch"] = w
+        return w
+
+    def _grads_in_place(self):
+        """True when every p.grad still is our slice of the flat gradient (zero_grad(set_to_none=False)
+        or a second backward before the optimizer step): the new gradient must be ADDED."""
+        if self._flat_grad is None:
+            return False
+        base = self._flat_grad.data_ptr()
+        n_set = 0
+        for p, (o, n, _) in zip(self._params_cache, self._slices):
+            g = p.grad
+            if g is None:
+                continue
+            if g.data_ptr() != base + 4 * o:
+                # a foreign gradient tensor: fold it into the flat buffer semantics by copying it in
+                self._flat_grad[o:o + n].copy_(g.reshape(-1))
+            n_set += 1
+        if n_set == 0:
+            return False
+        if n_set != len(self._slices):
+            for p, (o, n, _) in zip(self._params_cache, self._slices):
+                if p.grad is None:
+                    self._flat_grad[o:o + n].zero_()
+        self._point_grads()
+        return True
+
+    def _point_grads(self):
+        fg = self._flat_grad
+        for p, (o, n, shp) in zip(self._params_cache, self._slices):
+            if p.requires_grad:
+                p.grad = fg[o:o + n].view(shp)
+
+    @property
+    def flat_gradient(self):
+        """The flat fp32 gradient all `p.grad` alias (None before the first backward)."""
+        return self._flat_grad
+
+    def allreduce_gradients(self, group=None):
+        """Data-parallel learner step (BASELINE config 5): ONE all-reduce (sum) of the flat gradient
+        over NCCL; the caller scales its loss by 1/world_size.  No reference counterpart."""
+        import torch.distributed as dist
+        if self._flat_grad is not None and dist.is_initialized() and dist.get_world_size(group) > 1:
+            dist.all_reduce(self._flat_grad, op=dist.ReduceOp.SUM, group=group)
 
     @property
     def flat_parameters(self):
@@ -219,8 +286,10 @@ class ModernTwoHeaded(nn.Module):
         elif self.path == "tc":
             flags |= ops.HEXGNN_PATH_TC
         self.final_conv_acts = None
-        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
-            out_nodes, out_value = _FusedQ.apply(self, x, csr, flags, *self._ordered_params())
+        self.last_csr = csr
+        anchor = self._params_cache[0]
+        if torch.is_grad_enabled() and anchor.requires_grad:
+            out_nodes, out_value = _FusedQ.apply(self, x, csr, flags, anchor)
         else:
             out_nodes, out_value, _, _ = ops.fused_forward(self._desc, self._flat, x, csr, flags, want_stash=False,
                                                            ws=self._fwd_ws(csr))

@@ -8,6 +8,17 @@ from . import _lib
 from ._lib import HEXGNN_ADV_ONLY, HEXGNN_SEPARATE, HEXGNN_PATH_SIMT, HEXGNN_PATH_TC  # noqa: F401
 
 
+# kernels launched by each C-ABI call (csr: init, hist, scan, fill, sort; forward: pack, fused;
+# backward: pack, fused, reduce, unpack) -- bench.py's `gpu_launches` is read off this counter.
+LAUNCHES = {"build_csr": 5, "forward": 2, "backward": 4}
+launch_counter = 0
+
+
+def _count(what):
+    global launch_counter
+    launch_counter += LAUNCHES[what]
+
+
 def _ptr(t):
     return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
 
@@ -99,6 +110,7 @@ def build_csr(edge_index, batch=None, ptr=None, num_nodes=None, num_graphs=None,
     rc = _lib.lib().hexgnn_build_csr(_ptr(edge_index), E, _ptr(batch), _ptr(ptr), N, B, tile_rows, _ptr(blob),
                                      blob.numel() * 4, _stream(edge_index.device))
     _lib.check(rc, "hexgnn_build_csr")
+    _count("build_csr")
     return CsrBlob(blob, N, E, B, tile_rows)
 
 
@@ -123,6 +135,7 @@ def fused_forward(desc, flat_params, x, csr, flags=0, want_stash=False, ws=None)
                                    flags, _ptr(out_nodes), _ptr(out_value), _ptr(stash), _ptr(ws), ws.numel() * 4,
                                    _stream(dev))
     _lib.check(rc, "hexgnn_forward")
+    _count("forward")
     return out_nodes, out_value, stash, int(sz.hidden_padded)
 
 
@@ -145,4 +158,5 @@ def fused_backward(desc, flat_params, x, csr, flags, d_nodes, d_value, stash, wa
                                     flags, _ptr(d_nodes), _ptr(d_value), _ptr(stash), _ptr(grad_out), _ptr(d_embeds),
                                     _ptr(ws), ws.numel() * 4, _stream(dev))
     _lib.check(rc, "hexgnn_backward")
+    _count("backward")
     return grad_out, d_embeds

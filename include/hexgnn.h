@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define HEXGNN_ABI_VERSION 2
+#define HEXGNN_ABI_VERSION 3
 
 enum {
   HEXGNN_OK = 0,
@@ -140,6 +140,15 @@ int hexgnn_backward(const HexModelDesc* desc, const float* params, const float* 
                     int64_t B, const void* csr, int32_t tile_rows, int32_t flags, const float* d_nodes,
                     const float* d_value, const float* stash, float* grad_params, float* d_embeds,
                     void* ws, size_t ws_bytes, void* stream);
+
+/* Measurement aid (bench.py `roofline`): while enabled (process-wide; NOT re-entrant, use from one
+ * stream at a time), hexgnn_forward and
+ * hexgnn_backward bracket their dominant kernel (which: 0 = fused forward, 1 = fused backward) with
+ * CUDA events recorded on `stream`.  hexgnn_profile_read synchronises on the recorded events, returns
+ * the summed device time (ms) and the number of bracketed launches since the last read, and resets.
+ * This is the only mutable state the library keeps besides the thread-local error string. */
+int hexgnn_profile_enable(int on);
+int hexgnn_profile_read(int which, double* total_ms, int64_t* launches);
 
 #ifdef __cplusplus
 }

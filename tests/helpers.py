@@ -37,17 +37,41 @@ def rel_err(a, b):
     return float((a - b).abs().max() / denom)
 
 
-def grad_errs(model, oracle):
-    """Per-tensor max|d| / max(|ref tensor|_max, 1e-3*|all ref grads|_max)."""
-    ref = dict(oracle.named_parameters())
+def oracle64(o):
+    """fp64 copy of an oracle module: the arbiter of fp32 round-off."""
+    h = o.gnn.hidden_channels
+    o64 = orc.ModernTwoHeadedOracle(h, o.gnn.num_layers, o.maker_head.gnn.num_layers).double()
+    o64.load_state_dict({k: v.double() for k, v in o.state_dict().items()})
+    return o64
+
+
+def grad_errs(model, oracle, oracle_fp64=None):
+    """Gradient parity of the product module against the oracle.
+
+    Returns (global_err, worst_excess, name):
+      global_err   max|g - ref| / max|ref| over the WHOLE flat gradient -- the 1e-5 bar of BASELINE.json.
+      worst_excess per tensor, with scale_t = max(|ref_t|_max, 1e-3 * |ref|_max):
+                   err_t / max(REL_TOL, 5 * err_t(fp32 oracle vs fp64 oracle)); <= 1 means the kernel is
+                   within fp32 round-off of the truth wherever the fp32 oracle itself is.  Deep-layer
+                   gradients are ~1e-3 of the largest one, so their per-tensor relative round-off (of
+                   ANY fp32 implementation, the oracle included) exceeds 1e-5; fp64 arbitrates.
+    ref = the fp64 oracle when given, else the fp32 oracle."""
+    r32 = dict(oracle.named_parameters())
+    ref = dict(oracle_fp64.named_parameters()) if oracle_fp64 is not None else r32
     gmax = max(float(p.grad.abs().max()) for p in ref.values() if p.grad is not None)
-    worst, name_worst = 0.0, None
+    glob, worst, name_worst = 0.0, 0.0, None
     for name, p in model.named_parameters():
         rg = ref[name].grad
         rg = torch.zeros_like(ref[name]) if rg is None else rg
-        g = torch.zeros_like(rg) if p.grad is None else p.grad.detach().cpu().to(rg.dtype)
+        rg = rg.double()
+        g = torch.zeros_like(rg) if p.grad is None else p.grad.detach().cpu().double()
         scale = max(float(rg.abs().max()), 1e-3 * gmax)
-        e = float((g.double() - rg.double()).abs().max()) / scale
+        d = float((g - rg).abs().max())
+        glob = max(glob, d / gmax)
+        allow = REL_TOL
+        if oracle_fp64 is not None and r32[name].grad is not None:
+            allow = max(REL_TOL, 5.0 * float((r32[name].grad.double() - rg).abs().max()) / scale)
+        e = d / scale / allow
         if e > worst:
             worst, name_worst = e, name
-    return worst, name_worst
+    return glob, worst, name_worst

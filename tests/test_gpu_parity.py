@@ -7,7 +7,7 @@ import torch
 
 from gnn_hex_b200 import ModernTwoHeaded, data, ops, _lib
 from oracle import hexgnn_oracle as orc
-from helpers import REL_TOL, grad_errs, loss_inputs, make_pair, rel_err
+from helpers import REL_TOL, grad_errs, loss_inputs, make_pair, oracle64, rel_err
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
@@ -126,12 +126,16 @@ def test_backward_parity(name, kind, maker, count):
     action, target, weight = loss_inputs(b)
     loss_ref = orc.rainbow_loss(o(b.x, b.edge_index, b.batch, b.ptr), b.ptr, action, target, weight)
     loss_ref.backward()
+    o64 = oracle64(o)
+    orc.rainbow_loss(o64(b.x.double(), b.edge_index, b.batch, b.ptr), b.ptr, action, target.double(),
+                     weight.double()).backward()
     q = m(d.x, d.edge_index, d.batch, d.ptr)
     loss = orc.rainbow_loss(q, d.ptr, action.to(DEV), target.to(DEV), weight.to(DEV))
     loss.backward()
     assert rel_err(loss, loss_ref) <= REL_TOL
-    worst, wname = grad_errs(m, o)
-    assert worst <= REL_TOL, (worst, wname)
+    glob, worst, wname = grad_errs(m, o, o64)
+    assert glob <= REL_TOL, glob                # 1e-5 relative on the gradient (BASELINE.json)
+    assert worst <= 1.0, (worst, wname)         # per tensor: within fp32 round-off of the fp64 truth
     # the head not taken gets exactly zero gradient, like autograd leaves it untouched
     other = m.breaker_head if maker == 1 else m.maker_head
     assert all(float(p.grad.abs().max()) == 0.0 for p in other.parameters())
@@ -143,7 +147,12 @@ def test_backward_other_modes_and_embed_grads():
     o, m = make_pair(35, 10)
     m = m.to(DEV)
     m.capture_embed_grads = True
-    b = _batch(CONFIGS["S"], "play", 1, 40)
+    # Empty boards are excluded HERE only: their mirror-symmetric nodes tie in the max/min pooling up to
+    # the last ulp, so WHICH of two symmetric rows receives the pooled gradient depends on rounding
+    # (torch_scatter's CPU and CUDA kernels differ the same way).  Parameter gradients are invariant
+    # to that choice (covered with empty boards in test_backward_parity); the per-row tap is not.
+    gs = [g for g in data.load_positions(CONFIGS["S"]["fixture"], maker=1) if g.x.shape[0] < 51][:40]
+    b = data.collate(gs)
     d = b.to(DEV)
     gen = torch.Generator().manual_seed(3)
     wn = torch.randn(b.x.shape[0], generator=gen)
@@ -152,17 +161,21 @@ def test_backward_other_modes_and_embed_grads():
     v_ref, c_ref = o(b.x, b.edge_index, b.batch, seperate=True)
     o.final_conv_acts.retain_grad()
     ((c_ref * wn).sum() + (v_ref * wv).sum()).backward()
+    o64 = oracle64(o)
+    v64, c64 = o64(b.x.double(), b.edge_index, b.batch, seperate=True)
+    ((c64 * wn.double()).sum() + (v64 * wv.double()).sum()).backward()
     v, c = m(d.x, d.edge_index, d.batch, d.ptr, seperate=True)
     ((c * wn.to(DEV)).sum() + (v * wv.to(DEV)).sum()).backward()
-    worst, wname = grad_errs(m, o)
-    assert worst <= REL_TOL, (worst, wname)
+    glob, worst, wname = grad_errs(m, o, o64)
+    assert glob <= REL_TOL and worst <= 1.0, (glob, worst, wname)
     assert rel_err(m.final_conv_grads, o.final_conv_acts.grad) <= REL_TOL
     # advantages_only=True
-    o.zero_grad(); m.zero_grad()
+    o.zero_grad(); m.zero_grad(); o64.zero_grad()
     (o(b.x, b.edge_index, b.batch, advantages_only=True).squeeze(1) * wn).sum().backward()
+    (o64(b.x.double(), b.edge_index, b.batch, advantages_only=True).squeeze(1) * wn.double()).sum().backward()
     (m(d.x, d.edge_index, d.batch, d.ptr, advantages_only=True).squeeze(1) * wn.to(DEV)).sum().backward()
-    worst, wname = grad_errs(m, o)
-    assert worst <= REL_TOL, (worst, wname)
+    glob, worst, wname = grad_errs(m, o, o64)
+    assert glob <= REL_TOL and worst <= 1.0, (glob, worst, wname)
 
 
 def test_deterministic_bitwise():
