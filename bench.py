@@ -36,8 +36,8 @@ FIXTURE = "pos_11x11_seed1234.npz"
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
-    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="fused", choices=["fused", "reference"])
     ap.add_argument("--workload", default="play", choices=["play", "empty"],
                     help="play: 256 seeded random-playout positions (mean 77 nodes); empty: 256 empty boards (123 nodes)")
@@ -90,8 +90,9 @@ def flops_train(batch):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+    """nvidia-smi clocks / throttle reasons sampled every 20 ms; stop(t0, t1) keeps the samples whose
+    timestamp falls inside the timed region [t0, t1] (B200_PROFILING.md clocks line)."""
+    Q = ("timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
          "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
@@ -100,15 +101,16 @@ class ClockSampler:
         self.p = None
         try:
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + self.Q,
-                                       "--format=csv,noheader,nounits", "-lms", "100"],
+                                       "--format=csv,noheader,nounits", "-lms", "20"],
                                       stdout=self.f, stderr=subprocess.DEVNULL)
         except OSError:
             self.p = None
 
-    def stop(self):
+    def stop(self, t0, t1):
+        import datetime
         if self.p is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
+        time.sleep(0.1)
         self.p.terminate()
         try:
             self.p.wait(timeout=5)
@@ -116,24 +118,29 @@ class ClockSampler:
             self.p.kill()
         self.f.flush()
         self.f.seek(0)
-        sm, mx, reasons = [], [], set()
+        rows = []
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for line in self.f.read().splitlines():
             c = [t.strip() for t in line.split(",")]
             if len(c) < 9:
                 continue
             try:
-                sm.append(float(c[1])); mx.append(float(c[2]))
+                ts = datetime.datetime.strptime(c[0], "%Y/%m/%d %H:%M:%S.%f").timestamp()
+                rows.append((ts, float(c[1]), float(c[2]), float(c[3]),
+                             [nm for nm, v in zip(names, c[5:9]) if v.lower().startswith("active")]))
             except ValueError:
                 continue
-            for nm, v in zip(names, c[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(nm)
         self.f.close()
         os.unlink(self.f.name)
-        sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+        inside = [r for r in rows if t0 - 0.02 <= r[0] <= t1 + 0.02]
+        where = "timed region"
+        if not inside:
+            inside, where = rows, "whole run (no sample fell inside the timed region)"
+        sm = sorted(r[1] for r in inside)
+        reasons = sorted({x for r in inside for x in r[4]})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max((r[2] for r in inside), default=None),
+                "power_w_max": max((r[3] for r in inside), default=None), "samples": len(inside),
+                "window": where, "reasons": reasons}
 
 
 def time_cpu_port(batch, steps, warmup, max_seconds=None):
@@ -269,13 +276,14 @@ def run_fused(args, rank, world, local_rank):
             ms = float(t.item())
         return ms
 
+    sampler = ClockSampler(local_rank) if rank == 0 else None
     for _ in range(args.warmup):
         step_resident()
     for _ in range(max(3, args.warmup // 2)):
         step_e2e()
     barrier()
 
-    sampler = ClockSampler(local_rank) if rank == 0 else None
+    t_wall0 = time.time()
     _lib.profile_enable(True)
     _lib.profile_read(0); _lib.profile_read(1)
     l0 = ops.launch_counter
@@ -285,7 +293,7 @@ def run_fused(args, rank, world, local_rank):
     bwd_ms, bwd_n = _lib.profile_read(1)
     _lib.profile_enable(False)
     ms_e2e = timed(step_e2e, args.steps, sync_each=True)
-    clocks = sampler.stop() if sampler else None
+    clocks = sampler.stop(t_wall0, time.time()) if sampler else None
 
     status = int(model.last_csr.status.item()) if getattr(model, "last_csr", None) is not None else 0
     if status:
