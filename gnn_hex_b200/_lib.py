@@ -42,7 +42,7 @@ class HexCsrLayout(C.Structure):
 
 EXPORTS = ["hexgnn_abi_version", "hexgnn_last_error", "hexgnn_param_count", "hexgnn_param_offsets",
            "hexgnn_sizes", "hexgnn_csr_layout", "hexgnn_build_csr", "hexgnn_forward", "hexgnn_backward",
-           "hexgnn_profile_enable", "hexgnn_profile_read"]
+           "hexgnn_profile_enable", "hexgnn_profile_read", "hexgnn_selftest_mma"]
 
 _lib = None
 
@@ -80,6 +80,8 @@ def lib():
     l.hexgnn_forward.argtypes = [D, p, p, i64, i64, i64, p, i32, i32, p, p, p, p, sz, p]
     l.hexgnn_backward.restype = C.c_int
     l.hexgnn_backward.argtypes = [D, p, p, i64, i64, i64, p, i32, i32, p, p, p, p, p, p, sz, p]
+    l.hexgnn_selftest_mma.restype = C.c_int
+    l.hexgnn_selftest_mma.argtypes = [p, p, p, i32, i32, i32, p]
     l.hexgnn_profile_enable.restype = C.c_int
     l.hexgnn_profile_enable.argtypes = [C.c_int]
     l.hexgnn_profile_read.restype = C.c_int

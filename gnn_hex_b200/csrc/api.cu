@@ -3,6 +3,7 @@
 #include <string.h>
 #include <vector>
 #include "common.cuh"
+#include "sage_tc.cuh"
 
 namespace hexgnn {
 
@@ -108,7 +109,7 @@ int hexgnn_sizes(const HexModelDesc* desc, int64_t N, int64_t E, int64_t B, int3
   GradLayout gl;
   grad_layout(d, &gl);
   out->csr_bytes = l.total_words * 4;
-  out->fwd_ws_bytes = pack_floats(d) * 4;
+  out->fwd_ws_bytes = (pack_floats(d) > tc_pack_floats(d) ? pack_floats(d) : tc_pack_floats(d)) * 4;
   out->stash_bytes = (int64_t)d.Lt * N * d.Hp * 4;
   out->bwd_ws_bytes = (pack_floats(d) + (int64_t)(bwd_grid_ctas() + 1) * gl.total) * 4;
   out->hidden_padded = d.Hp;
@@ -135,15 +136,22 @@ int hexgnn_forward(const HexModelDesc* desc, const float* params, const float* x
   if (!params || !x || !csr || !out_nodes || !ws || N < 1 || B < 1 || E < 0) { set_error("forward: bad argument"); return HEXGNN_E_BADARG; }
   if ((flags & HEXGNN_SEPARATE) && !out_value) { set_error("forward: SEPARATE needs out_value"); return HEXGNN_E_BADARG; }
   if (!tile_rows_ok(tile_rows) || d.NJ > 8) { set_error("forward: unsupported tile_rows=%d or hidden=%d", tile_rows, d.H); return HEXGNN_E_UNSUPPORTED; }
-  if ((int64_t)ws_bytes < pack_floats(d) * 4) { set_error("forward: workspace too small"); return HEXGNN_E_WORKSPACE; }
+  const int64_t need = (pack_floats(d) > tc_pack_floats(d) ? pack_floats(d) : tc_pack_floats(d)) * 4;
+  if ((int64_t)ws_bytes < need) { set_error("forward: workspace too small (%zu < %lld)", ws_bytes, (long long)need); return HEXGNN_E_WORKSPACE; }
   ParamMap pm;
   make_param_map(d, &pm);
-  PackView pv = pack_view(ws, d);
   cudaStream_t st = (cudaStream_t)stream;
-  int rc = launch_pack(d, pm, params, x, pv, false, st);
+  if (flags & HEXGNN_PATH_SIMT) {
+    PackView pv = pack_view(ws, d);
+    int rc = launch_pack(d, pm, params, x, pv, false, st);
+    if (rc) return rc;
+    return launch_forward_simt(d, pm, params, x, N, E, B, csr, tile_rows, flags, out_nodes, out_value, stash, pv, st);
+  }
+  // default: tcgen05 path (3xTF32, fp32 parity)
+  TcPackView tpv = tc_pack_view(ws, d);
+  int rc = launch_pack_tc(d, pm, params, x, tpv, false, st);
   if (rc) return rc;
-  if (flags & HEXGNN_PATH_TC) { set_error("forward: tcgen05 path not built for this shape"); return HEXGNN_E_UNSUPPORTED; }
-  return launch_forward_simt(d, pm, params, x, N, E, B, csr, tile_rows, flags, out_nodes, out_value, stash, pv, st);
+  return launch_forward_tc(d, pm, params, x, N, E, B, csr, flags, out_nodes, out_value, stash, tpv, st);
 }
 
 int hexgnn_backward(const HexModelDesc* desc, const float* params, const float* x, int64_t N, int64_t E, int64_t B,
@@ -173,6 +181,11 @@ int hexgnn_backward(const HexModelDesc* desc, const float* params, const float* 
   if (rc) return rc;
   CsrView cv = csr_view(const_cast<void*>(csr), N, E, B);
   return launch_reduce_grads(d, pm, x, partials, nparts, cv.ntiles, packed_sum, grad_params, st);
+}
+
+int hexgnn_selftest_mma(const float* A, const float* B, float* D, int32_t N, int32_t K, int32_t b_layout, void* stream) {
+  if (!A || !B || !D) { set_error("selftest: null pointer"); return HEXGNN_E_BADARG; }
+  return launch_tc_selftest(A, B, D, N, K, b_layout, (cudaStream_t)stream);
 }
 
 int hexgnn_profile_enable(int on) {

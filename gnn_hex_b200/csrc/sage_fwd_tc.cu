@@ -1,0 +1,427 @@
+// Fused forward of modern_two_headed on the 5th-gen tensor cores (tcgen05 + TMEM), see sage_tc.cuh.
+//
+// One persistent CTA per SM, one 128-row tile (whole graphs) at a time, three warp roles:
+//   warps 0-7  epilogue: thread = (node row, column slice); TMEM <-> registers, CSR gather in smem
+//   warp  8    producer: streams the 3xTF32 weight images of every layer through a 4-stage smem ring
+//              with 1-D bulk copies (UBLKCP) completing on mbarriers; runs ahead across layers/tiles
+//   warp  9    MMA issuer: one thread issues tcgen05.mma (A = h in TMEM, B = ring stage, D = Z in TMEM)
+// Layer 0 (2 -> H) is a rank-2 update on the CUDA cores; the dueling head (GN0/models.py:368-384,
+// 567-584) runs in the same CTA on the final activations.
+#include "sage_tc.cuh"
+
+namespace hexgnn {
+using namespace tc;
+
+struct FwdTcArgs {
+  Dims d;
+  ParamMap pm;
+  const float* params;
+  const float* x;
+  int64_t N, E, B;
+  CsrView csr;
+  int flags;
+  float* out_nodes;
+  float* out_value;
+  float* stash;
+  TcPackView pv;
+};
+
+template <int NJ>
+struct FwdTcSmem {
+  static constexpr int Hp = 16 * NJ;
+  static constexpr int N2 = 32 * NJ;
+  static constexpr int P = Hp + 4;                       // dump row pitch (floats): float4 rows conflict-free
+  static constexpr int ECAP = kEdgeCapPerRow * kTcRows;
+  static constexpr int half_bytes = kTcKC * N2 * 4;      // one tf32 half (hi or lo) of a k chunk
+  static constexpr int stage_bytes = 2 * half_bytes;
+  static constexpr int off_ring = 0;
+  static constexpr int off_dump = off_ring + kTcStages * stage_bytes;            // float [128][P]
+  static constexpr int off_rows = off_dump + kTcRows * P * 4;                    // float [6][128]: inv,x0,x1,m0,m1,adv
+  static constexpr int off_pool = off_rows + 6 * kTcRows * 4;                    // float [4*Hp]
+  static constexpr int off_hid = off_pool + 4 * Hp * 4;                          // float [Hp]
+  static constexpr int off_misc = off_hid + Hp * 4;                              // float [16]
+  static constexpr int off_rowptr = off_misc + 64;                               // int [128+4]
+  static constexpr int off_gp = off_rowptr + (kTcRows + 4) * 4;                  // int [64+4]
+  static constexpr int off_col = off_gp + (kMaxTileGraphs + 4) * 4;              // u16 [ECAP]
+  static constexpr int off_bar = off_col + ECAP * 2;                             // u64 [2*stages + 2], u32 tmem slot
+  static constexpr int off_bias = off_bar + (2 * kTcStages + 2) * 8 + 16;        // float [Lt][Hp] (runtime sized)
+  static size_t bytes(int Lt) { return (size_t)off_bias + (size_t)Lt * Hp * 4; }
+};
+
+struct TileDims { int g0, g1, r0, n, e0, ne; bool ok; };
+__device__ __forceinline__ TileDims tile_dims(const CsrView& v, int t, int ecap) {
+  TileDims d;
+  d.g0 = v.tile_g0[t];
+  d.g1 = v.tile_g0[t + 1];
+  d.r0 = v.gptr[d.g0];
+  const int r1 = v.gptr[d.g1];
+  d.n = r1 - d.r0;
+  d.e0 = v.rowptr[d.r0];
+  d.ne = v.rowptr[r1] - d.e0;
+  d.ok = d.n >= 0 && d.n <= kTcRows && d.ne >= 0 && d.ne <= ecap && (d.g1 - d.g0) <= kMaxTileGraphs;
+  return d;
+}
+
+__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"(kTcEpiThreads) : "memory"); }
+
+template <int NJ>
+__global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid_constant__ FwdTcArgs a) {
+  using S = FwdTcSmem<NJ>;
+  constexpr int Hp = S::Hp, N2 = S::N2, P = S::P;
+  constexpr int NG = 2 * NJ;                 // 8-column granules per row
+  constexpr int NQ = Hp / kTcKC;             // k chunks per layer
+  constexpr uint32_t TM_HI = 0, TM_LO = Hp, TM_D = 2 * Hp;     // TMEM columns
+  constexpr uint32_t TM_COLS = (4 * Hp <= 64) ? 64 : (4 * Hp <= 128) ? 128 : (4 * Hp <= 256) ? 256 : 512;
+  extern __shared__ __align__(128) uint8_t smem[];
+  float* dump = (float*)(smem + S::off_dump);
+  float* rows = (float*)(smem + S::off_rows);
+  float* inv_s = rows, *x0_s = rows + 128, *x1_s = rows + 256, *m0_s = rows + 384, *m1_s = rows + 512, *adv_s = rows + 640;
+  float* pool = (float*)(smem + S::off_pool);
+  float* hid = (float*)(smem + S::off_hid);
+  float* misc = (float*)(smem + S::off_misc);
+  int* rowptr_s = (int*)(smem + S::off_rowptr);
+  int* gp_s = (int*)(smem + S::off_gp);
+  unsigned short* col_s = (unsigned short*)(smem + S::off_col);
+  uint64_t* bar_full = (uint64_t*)(smem + S::off_bar);
+  uint64_t* bar_empty = bar_full + kTcStages;
+  uint64_t* bar_d = bar_empty + kTcStages;
+  uint64_t* bar_a = bar_d + 1;
+  uint32_t* tmem_slot = (uint32_t*)(bar_a + 1);
+  float* bias_s = (float*)(smem + S::off_bias);
+
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int H = a.d.H, Lt = a.d.Lt;
+  const int ntiles = *a.csr.ntiles;
+
+  if (tid == 0) {
+    for (int i = 0; i < kTcStages; ++i) { mbar_init(&bar_full[i], 1); mbar_init(&bar_empty[i], 1); }
+    mbar_init(bar_d, 1);
+    mbar_init(bar_a, kTcEpiThreads);
+    fence_mbar_init();
+  }
+  if (wid == kTcEpiWarps + 1) tmem_alloc(tmem_slot, TM_COLS);
+  for (int i = tid; i < Lt * Hp; i += kTcThreads) bias_s[i] = a.pv.bias[i];
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tbase = *tmem_slot;
+
+  if (wid == kTcEpiWarps) {
+    // ================= producer: weight images -> ring =================
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        if (!tile_dims(a.csr, t, S::ECAP).ok) continue;
+        for (int s = 1; s < Lt; ++s) {
+          const uint8_t* src = (const uint8_t*)a.pv.wimg + (size_t)(s - 1) * NQ * S::stage_bytes;
+          for (int q = 0; q < NQ; ++q, ++it) {
+            const int st = it % kTcStages;
+            mbar_wait(&bar_empty[st], ((it / kTcStages) & 1) ^ 1);
+            mbar_expect_tx(&bar_full[st], S::stage_bytes);
+            bulk_g2s(smem + S::off_ring + st * S::stage_bytes, src + (size_t)q * S::stage_bytes, S::stage_bytes,
+                     &bar_full[st]);
+          }
+        }
+      }
+    }
+  } else if (wid == kTcEpiWarps + 1) {
+    // ================= MMA issuer =================
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_tf32(kTcRows, N2, false);
+      constexpr uint32_t lbo = N2 * 16, sbo = 128;
+      uint32_t it = 0, na = 0;
+      for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        if (!tile_dims(a.csr, t, S::ECAP).ok) continue;
+        for (int s = 1; s < Lt; ++s) {
+          mbar_wait(bar_a, na & 1);   // h of this layer is in TMEM, D has been drained
+          ++na;
+          tc_fence_after();
+          for (int q = 0; q < NQ; ++q, ++it) {
+            const int st = it % kTcStages;
+            mbar_wait(&bar_full[st], (it / kTcStages) & 1);
+            tc_fence_after();
+            const uint32_t bhi = smem_u32(smem + S::off_ring + st * S::stage_bytes);
+            const uint32_t blo = bhi + S::half_bytes;
+#pragma unroll
+            for (int kk = 0; kk < kTcKC / 8; ++kk) {
+              const uint64_t dhi = make_smem_desc(bhi + kk * 2 * lbo, lbo, sbo);
+              const uint64_t dlo = make_smem_desc(blo + kk * 2 * lbo, lbo, sbo);
+              const uint32_t kcol = q * kTcKC + kk * 8;
+              mma_tf32_ts(tbase + TM_D, tbase + TM_LO + kcol, dhi, idesc, (q | kk) != 0);
+              mma_tf32_ts(tbase + TM_D, tbase + TM_HI + kcol, dlo, idesc, true);
+              mma_tf32_ts(tbase + TM_D, tbase + TM_HI + kcol, dhi, idesc, true);
+            }
+            mma_commit(&bar_empty[st]);   // stage free once these MMAs have read it
+          }
+          mma_commit(bar_d);              // Z complete
+        }
+      }
+    }
+  } else {
+    // ================= epilogue warps =================
+    const int q4 = wid & 3, slice = wid >> 2;           // TMEM lane quarter, column slice
+    const int row = q4 * 32 + lane;
+    const uint32_t trow = tbase + ((uint32_t)(q4 * 32) << 16);
+    const float flag = a.x[2];
+    const int head = (flag == 1.0f) ? 0 : 1;
+    const float* Pm = a.params;
+    uint32_t nd = 0;
+    for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+      const TileDims td = tile_dims(a.csr, t, S::ECAP);
+      const int n = td.n, r0 = td.r0, g0 = td.g0, g1 = td.g1;
+      epi_bar();   // previous tile fully consumed
+      if (!td.ok) {
+        const int r1 = a.csr.gptr[g1];
+        const float qnan = __int_as_float(0x7fc00000);
+        for (int i = r0 + tid; i < r1; i += kTcEpiThreads) a.out_nodes[i] = qnan;
+        if (a.out_value) for (int g = g0 + tid; g < g1; g += kTcEpiThreads) a.out_value[g] = qnan;
+        if (tid == 0) atomicOr(a.csr.status, HEXGNN_ST_GRAPH_TOO_LARGE);
+        continue;
+      }
+      // ---- tile CSR + features -> shared ------------------------------------------------------------
+      {
+        int bad = 0;
+        for (int i = tid; i <= kTcRows; i += kTcEpiThreads) rowptr_s[i] = (i <= n ? a.csr.rowptr[r0 + i] : a.csr.rowptr[r0 + n]) - td.e0;
+        for (int g = tid; g <= g1 - g0; g += kTcEpiThreads) gp_s[g] = a.csr.gptr[g0 + g] - r0;
+        for (int e = tid; e < td.ne; e += kTcEpiThreads) {
+          int c = a.csr.col[td.e0 + e] - r0;
+          if (c < 0 || c >= n) { bad |= HEXGNN_ST_EDGE_CROSSES; c = 0; }
+          col_s[e] = (unsigned short)c;
+        }
+        for (int i = tid; i < kTcRows; i += kTcEpiThreads) {
+          float v0 = 0.f, v1 = 0.f;
+          if (i < n) {
+            const float* xr = a.x + (int64_t)(r0 + i) * 3;
+            v0 = xr[0]; v1 = xr[1];
+            if (xr[2] != flag) bad |= HEXGNN_ST_FLAG_MIXED;
+          }
+          x0_s[i] = v0; x1_s[i] = v1;
+        }
+        if (bad) atomicOr(a.csr.status, bad);
+        epi_bar();
+        for (int i = tid; i < kTcRows; i += kTcEpiThreads) {
+          const int b = rowptr_s[i], e = rowptr_s[i + 1];
+          const int deg = e - b;
+          const float inv = 1.0f / (float)(deg > 0 ? deg : 1);
+          float s0 = 0.f, s1 = 0.f;
+          for (int p = b; p < e; ++p) { const int j = col_s[p]; s0 += x0_s[j]; s1 += x1_s[j]; }
+          inv_s[i] = inv; m0_s[i] = s0 * inv; m1_s[i] = s1 * inv;
+        }
+        epi_bar();
+      }
+      const bool live = row < n;
+      const float inv = inv_s[row];
+      const int eb = rowptr_s[row], ee = rowptr_s[row + 1];
+      // ---- layer 0 (2 -> H): rank-2 update, result -> TMEM as the first A operand --------------------------
+      {
+        const float* wl = Pm + sage_wl(a.pm, head, 0);
+        const float* bl = Pm + sage_bl(a.pm, head, 0, H);
+        const float* wr = Pm + sage_wr(a.pm, head, 0, H);
+        const float xm0 = m0_s[row], xm1 = m1_s[row], xx0 = x0_s[row], xx1 = x1_s[row];
+        for (int g = slice; g < NG; g += 2) {
+          float v[8], hi[8], lo[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int c = g * 8 + u;
+            float r = 0.f;
+            if (live && c < H)
+              r = fmaxf(wl[2 * c] * xm0 + wl[2 * c + 1] * xm1 + bl[c] + wr[2 * c] * xx0 + wr[2 * c + 1] * xx1, 0.f);
+            v[u] = r;
+            split_tf32(r, hi[u], lo[u]);
+          }
+          tmem_st8(trow + TM_HI + g * 8, hi);
+          tmem_st8(trow + TM_LO + g * 8, lo);
+          if (a.stash && live) {
+            float4* dst = (float4*)(a.stash + (int64_t)(r0 + row) * Hp + g * 8);
+            dst[0] = make_float4(v[0], v[1], v[2], v[3]);
+            dst[1] = make_float4(v[4], v[5], v[6], v[7]);
+          }
+        }
+        tmem_wait_st();
+        tc_fence_before();
+        mbar_arrive(bar_a);
+      }
+      // ---- layers 1 .. Lt-1 on the tensor cores ---------------------------------------------------------------
+      for (int s = 1; s < Lt; ++s) {
+        mbar_wait(bar_d, nd & 1);
+        ++nd;
+        tc_fence_after();
+        // phase 1: Zl -> shared (row major)
+        for (int g = slice; g < NG; g += 2) {
+          float v[8];
+          tmem_ld8(trow + TM_D + g * 8, v);
+          tmem_wait_ld();
+          float4* dst = (float4*)(dump + row * P + g * 8);
+          dst[0] = make_float4(v[0], v[1], v[2], v[3]);
+          dst[1] = make_float4(v[4], v[5], v[6], v[7]);
+        }
+        epi_bar();
+        // phase 2: h' = relu(mean_j Zl_j + Zr_i + b)
+        const bool last = (s == Lt - 1);
+        const float* bias = bias_s + s * Hp;
+        float* st = (a.stash && live) ? a.stash + ((int64_t)s * a.N + r0 + row) * Hp : nullptr;
+        for (int g = slice; g < NG; g += 2) {
+          float zr[8], acc[8], hi[8], lo[8];
+          tmem_ld8(trow + TM_D + Hp + g * 8, zr);
+#pragma unroll
+          for (int u = 0; u < 8; ++u) acc[u] = 0.f;
+          for (int p = eb; p < ee; ++p) {
+            const float4* src = (const float4*)(dump + (int)col_s[p] * P + g * 8);
+            const float4 v0 = src[0], v1 = src[1];
+            acc[0] += v0.x; acc[1] += v0.y; acc[2] += v0.z; acc[3] += v0.w;
+            acc[4] += v1.x; acc[5] += v1.y; acc[6] += v1.z; acc[7] += v1.w;
+          }
+          tmem_wait_ld();
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const float r = live ? fmaxf(fmaf(acc[u], inv, zr[u] + bias[g * 8 + u]), 0.f) : 0.f;
+            acc[u] = r;
+            split_tf32(r, hi[u], lo[u]);
+          }
+          if (st) {
+            float4* dst = (float4*)(st + g * 8);
+            dst[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+            dst[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+          }
+          if (!last) {
+            tmem_st8(trow + TM_HI + g * 8, hi);
+            tmem_st8(trow + TM_LO + g * 8, lo);
+          } else {
+            tmem_st8(trow + TM_D + g * 8, acc);   // park the exact fp32 activations in the drained Zl columns
+          }
+        }
+        tmem_wait_st();
+        if (!last) {
+          tc_fence_before();
+          mbar_arrive(bar_a);
+        }
+      }
+      // ---- final activations -> shared (row major) for the head ----------------------------------------------------
+      epi_bar();   // every gather of the last layer has finished reading the dump
+      for (int g = slice; g < NG; g += 2) {
+        float v[8];
+        tmem_ld8(trow + TM_D + g * 8, v);
+        tmem_wait_ld();
+        float4* dst = (float4*)(dump + row * P + g * 8);
+        dst[0] = make_float4(v[0], v[1], v[2], v[3]);
+        dst[1] = make_float4(v[4], v[5], v[6], v[7]);
+      }
+      tc_fence_before();
+      epi_bar();
+      // ---- advantage head: a_i = 2 tanh(w_a . g_i + b_a)  (models.py:374, 567-571) -----------------------------------
+      {
+        const float* wa = Pm + a.pm.lin_w[head];
+        const float ba = Pm[a.pm.lin_b[head]];
+        if (tid < kTcRows && tid < n) {
+          float u = 0.f;
+          const float* gr = dump + tid * P;
+          for (int c = 0; c < H; ++c) u = fmaf(wa[c], gr[c], u);
+          adv_s[tid] = 2.0f * tanhf(u + ba);
+        }
+        epi_bar();
+      }
+      if (a.flags & HEXGNN_ADV_ONLY) {
+        for (int i = tid; i < n; i += kTcEpiThreads) a.out_nodes[r0 + i] = adv_s[i];
+        continue;
+      }
+      // ---- value head per graph: pools (sum|max|min|mean) -> MLP -> tanh; dueling combine --------------------------------
+      const float* w0 = Pm + a.pm.v0_w[head];
+      const float* b0 = Pm + a.pm.v0_b[head];
+      const float* w1 = Pm + a.pm.v1_w[head];
+      const float b1 = Pm[a.pm.v1_b[head]];
+      const int H2 = a.d.H2;
+      for (int g = 0; g < g1 - g0; ++g) {
+        const int rs = gp_s[g], re = gp_s[g + 1];
+        const int ng = re - rs;
+        if (tid < H) {
+          float sum = 0.f, mx = 0.f, mn = 0.f;  // empty group -> 0 (torch_scatter semantics)
+          if (ng > 0) { mx = -INFINITY; mn = INFINITY; }
+          for (int i = rs; i < re; ++i) {
+            const float v = dump[i * P + tid];
+            sum += v; mx = fmaxf(mx, v); mn = fminf(mn, v);
+          }
+          pool[tid] = sum;
+          pool[H + tid] = mx;
+          pool[2 * H + tid] = mn;
+          pool[3 * H + tid] = sum / (float)(ng > 0 ? ng : 1);
+        }
+        epi_bar();
+        for (int k = wid; k < H2; k += kTcEpiWarps) {
+          float u = 0.f;
+          const float* wrow = w0 + (int64_t)k * 4 * H;
+          for (int q = lane; q < 4 * H; q += 32) u = fmaf(wrow[q], pool[q], u);
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) u += __shfl_xor_sync(0xffffffffu, u, o);
+          if (lane == 0) hid[k] = fmaxf(u + b0[k], 0.f);
+        }
+        epi_bar();
+        if (wid == 0) {
+          float u = 0.f;
+          for (int k = lane; k < H2; k += 32) u = fmaf(w1[k], hid[k], u);
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) u += __shfl_xor_sync(0xffffffffu, u, o);
+          if (lane == 0) misc[0] = tanhf(u + b1);
+        } else if (wid == 1) {
+          float u = 0.f;
+          for (int i = rs + lane; i < re; i += 32) u += adv_s[i];
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) u += __shfl_xor_sync(0xffffffffu, u, o);
+          if (lane == 0) misc[1] = u / (float)(ng > 0 ? ng : 1);
+        }
+        epi_bar();
+        const float val = misc[0], amean = misc[1];
+        if (a.flags & HEXGNN_SEPARATE) {
+          for (int i = rs + tid; i < re; i += kTcEpiThreads) a.out_nodes[r0 + i] = adv_s[i] - amean;
+        } else {
+          for (int i = rs + tid; i < re; i += kTcEpiThreads) a.out_nodes[r0 + i] = val + (adv_s[i] - amean);
+        }
+        if (tid == 0 && a.out_value) a.out_value[g0 + g] = val;
+        epi_bar();
+      }
+    }
+  }
+  // ---- teardown ----------------------------------------------------------------------------------------------------------
+  tc_fence_before();
+  __syncthreads();
+  if (wid == kTcEpiWarps + 1) tmem_dealloc(tbase, TM_COLS);
+}
+
+template <int NJ>
+static int launch_fwd_tc_t(const FwdTcArgs& a, cudaStream_t st) {
+  using S = FwdTcSmem<NJ>;
+  auto kern = sage_fwd_tc_kernel<NJ>;
+  const size_t smem = S::bytes(a.d.Lt);
+  if (smem > 227 * 1024) { set_error("forward(tc): %zu bytes of shared memory needed", smem); return HEXGNN_E_UNSUPPORTED; }
+  HEX_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int grid = (int)(a.B < 1 ? 1 : (a.B > bwd_grid_ctas() ? bwd_grid_ctas() : a.B));
+  {
+    ProfScope prof(0, st);
+    kern<<<grid, kTcThreads, smem, st>>>(a);
+  }
+  HEX_CUDA_CHECK(cudaGetLastError());
+  return HEXGNN_OK;
+}
+
+int launch_forward_tc(const Dims& d, const ParamMap& pm, const float* params, const float* x, int64_t N, int64_t E,
+                      int64_t B, const void* csr, int flags, float* out_nodes, float* out_value, float* stash,
+                      TcPackView pv, cudaStream_t st) {
+  FwdTcArgs a;
+  a.d = d; a.pm = pm; a.params = params; a.x = x; a.N = N; a.E = E; a.B = B;
+  a.csr = csr_view(const_cast<void*>(csr), N, E, B);
+  a.flags = flags; a.out_nodes = out_nodes; a.out_value = out_value; a.stash = stash; a.pv = pv;
+  switch (d.NJ) {
+    case 1: return launch_fwd_tc_t<1>(a, st);
+    case 2: return launch_fwd_tc_t<2>(a, st);
+    case 3: return launch_fwd_tc_t<3>(a, st);
+    case 4: return launch_fwd_tc_t<4>(a, st);
+    case 5: return launch_fwd_tc_t<5>(a, st);
+    case 6: return launch_fwd_tc_t<6>(a, st);
+    case 7: return launch_fwd_tc_t<7>(a, st);
+    case 8: return launch_fwd_tc_t<8>(a, st);
+    default: break;
+  }
+  set_error("forward(tc): unsupported hidden=%d (padded %d)", d.H, d.Hp);
+  return HEXGNN_E_UNSUPPORTED;
+}
+
+}  // namespace hexgnn

@@ -141,6 +141,11 @@ int hexgnn_backward(const HexModelDesc* desc, const float* params, const float* 
                     const float* d_value, const float* stash, float* grad_params, float* d_embeds,
                     void* ws, size_t ws_bytes, void* stream);
 
+/* Self-test of the tcgen05 building blocks the fused kernels are made of: one CTA computes
+ * D[128,N] = A[128,K] * B[K,N] (row-major device fp32, 3xTF32) with A in tensor memory and B in shared
+ * memory in canonical layout `b_layout` (0 = K-major, 1 = MN-major).  N%16==0, K%8==0, K<=128. */
+int hexgnn_selftest_mma(const float* A, const float* B, float* D, int32_t N, int32_t K, int32_t b_layout, void* stream);
+
 /* Measurement aid (bench.py `roofline`): while enabled (process-wide; NOT re-entrant, use from one
  * stream at a time), hexgnn_forward and
  * hexgnn_backward bracket their dominant kernel (which: 0 = fused forward, 1 = fused backward) with

@@ -45,6 +45,6 @@ def run(hidden, layers, fixture, count, maker=1, path="auto"):
 
 
 if __name__ == "__main__":
-    run(35, 10, "pos_7x7_seed1234.npz", 256)
-    run(35, 10, "pos_7x7_seed1234.npz", 32)
-    run(110, 15, "pos_11x11_seed1234.npz", 48)
+    for path in ("simt", "auto"):
+        run(35, 10, "pos_7x7_seed1234.npz", 256, path=path)
+        run(110, 15, "pos_11x11_seed1234.npz", 48, path=path)
