@@ -70,6 +70,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
   constexpr int Hp = S::Hp, N2 = S::N2, P = S::P;
   constexpr int NG = 2 * NJ;                 // 8-column granules per row
   constexpr int NQ = Hp / kTcKC;             // k chunks per layer
+  constexpr int MAXG = (NG + kTcSlices - 1) / kTcSlices;   // granules per epilogue thread
   constexpr uint32_t TM_HI = 0, TM_LO = Hp, TM_D = 2 * Hp;     // TMEM columns
   constexpr uint32_t TM_COLS = (4 * Hp <= 64) ? 64 : (4 * Hp <= 128) ? 128 : (4 * Hp <= 256) ? 256 : 512;
   extern __shared__ __align__(128) uint8_t smem[];
@@ -218,7 +219,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
         const float* bl = Pm + sage_bl(a.pm, head, 0, H);
         const float* wr = Pm + sage_wr(a.pm, head, 0, H);
         const float xm0 = m0_s[row], xm1 = m1_s[row], xx0 = x0_s[row], xx1 = x1_s[row];
-        for (int g = slice; g < NG; g += 2) {
+        for (int g = slice; g < NG; g += kTcSlices) {
           float v[8], hi[8], lo[8];
 #pragma unroll
           for (int u = 0; u < 8; ++u) {
@@ -246,48 +247,77 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
         mbar_wait(bar_d, nd & 1);
         ++nd;
         tc_fence_after();
-        // phase 1: Zl -> shared (row major)
-        for (int g = slice; g < NG; g += 2) {
-          float v[8];
-          tmem_ld8(trow + TM_D + g * 8, v);
+        // phase 1: Zl -> shared (row major); all TMEM loads in flight before the single wait
+        {
+          float v[MAXG][8];
+#pragma unroll
+          for (int gi = 0; gi < MAXG; ++gi) {
+            const int g = slice + gi * kTcSlices;
+            if (g < NG) tmem_ld8(trow + TM_D + g * 8, v[gi]);
+          }
           tmem_wait_ld();
-          float4* dst = (float4*)(dump + row * P + g * 8);
-          dst[0] = make_float4(v[0], v[1], v[2], v[3]);
-          dst[1] = make_float4(v[4], v[5], v[6], v[7]);
+#pragma unroll
+          for (int gi = 0; gi < MAXG; ++gi) {
+            const int g = slice + gi * kTcSlices;
+            if (g < NG) {
+              float4* dst = (float4*)(dump + row * P + g * 8);
+              dst[0] = make_float4(v[gi][0], v[gi][1], v[gi][2], v[gi][3]);
+              dst[1] = make_float4(v[gi][4], v[gi][5], v[gi][6], v[gi][7]);
+            }
+          }
         }
         epi_bar();
-        // phase 2: h' = relu(mean_j Zl_j + Zr_i + b)
+        // phase 2: h' = relu(mean_j Zl_j + Zr_i + b).  Neighbour-outer / granule-inner: one index load
+        // feeds 2*MAXG independent 16-byte shared loads (latency-bound otherwise: 4 warps per scheduler).
         const bool last = (s == Lt - 1);
         const float* bias = bias_s + s * Hp;
         float* st = (a.stash && live) ? a.stash + ((int64_t)s * a.N + r0 + row) * Hp : nullptr;
-        for (int g = slice; g < NG; g += 2) {
-          float zr[8], acc[8], hi[8], lo[8];
-          tmem_ld8(trow + TM_D + Hp + g * 8, zr);
+        float acc[MAXG][8];
 #pragma unroll
-          for (int u = 0; u < 8; ++u) acc[u] = 0.f;
+        for (int gi = 0; gi < MAXG; ++gi)
+#pragma unroll
+          for (int u = 0; u < 8; ++u) acc[gi][u] = 0.f;
+        {
+          int j = eb < ee ? (int)col_s[eb] : 0;
           for (int p = eb; p < ee; ++p) {
-            const float4* src = (const float4*)(dump + (int)col_s[p] * P + g * 8);
-            const float4 v0 = src[0], v1 = src[1];
-            acc[0] += v0.x; acc[1] += v0.y; acc[2] += v0.z; acc[3] += v0.w;
-            acc[4] += v1.x; acc[5] += v1.y; acc[6] += v1.z; acc[7] += v1.w;
-          }
-          tmem_wait_ld();
+            const int jn = (p + 1 < ee) ? (int)col_s[p + 1] : 0;
+            const float* src = dump + j * P + slice * 8;
 #pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            const float r = live ? fmaxf(fmaf(acc[u], inv, zr[u] + bias[g * 8 + u]), 0.f) : 0.f;
-            acc[u] = r;
-            split_tf32(r, hi[u], lo[u]);
+            for (int gi = 0; gi < MAXG; ++gi) {
+              if (slice + gi * kTcSlices < NG) {
+                const float4 v0 = *(const float4*)(src + gi * kTcSlices * 8);
+                const float4 v1 = *(const float4*)(src + gi * kTcSlices * 8 + 4);
+                acc[gi][0] += v0.x; acc[gi][1] += v0.y; acc[gi][2] += v0.z; acc[gi][3] += v0.w;
+                acc[gi][4] += v1.x; acc[gi][5] += v1.y; acc[gi][6] += v1.z; acc[gi][7] += v1.w;
+              }
+            }
+            j = jn;
           }
-          if (st) {
-            float4* dst = (float4*)(st + g * 8);
-            dst[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
-            dst[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
-          }
-          if (!last) {
-            tmem_st8(trow + TM_HI + g * 8, hi);
-            tmem_st8(trow + TM_LO + g * 8, lo);
-          } else {
-            tmem_st8(trow + TM_D + g * 8, acc);   // park the exact fp32 activations in the drained Zl columns
+        }
+#pragma unroll
+        for (int gi = 0; gi < MAXG; ++gi) {
+          const int g = slice + gi * kTcSlices;
+          if (g < NG) {
+            float zr[8], hi[8], lo[8];
+            tmem_ld8(trow + TM_D + Hp + g * 8, zr);
+            tmem_wait_ld();
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+              const float r = live ? fmaxf(fmaf(acc[gi][u], inv, zr[u] + bias[g * 8 + u]), 0.f) : 0.f;
+              acc[gi][u] = r;
+              split_tf32(r, hi[u], lo[u]);
+            }
+            if (st) {
+              float4* dst = (float4*)(st + g * 8);
+              dst[0] = make_float4(acc[gi][0], acc[gi][1], acc[gi][2], acc[gi][3]);
+              dst[1] = make_float4(acc[gi][4], acc[gi][5], acc[gi][6], acc[gi][7]);
+            }
+            if (!last) {
+              tmem_st8(trow + TM_HI + g * 8, hi);
+              tmem_st8(trow + TM_LO + g * 8, lo);
+            } else {
+              tmem_st8(trow + TM_D + g * 8, acc[gi]);   // park the exact fp32 activations in the drained Zl columns
+            }
           }
         }
         tmem_wait_st();
@@ -298,7 +328,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
       }
       // ---- final activations -> shared (row major) for the head ----------------------------------------------------
       epi_bar();   // every gather of the last layer has finished reading the dump
-      for (int g = slice; g < NG; g += 2) {
+      for (int g = slice; g < NG; g += kTcSlices) {
         float v[8];
         tmem_ld8(trow + TM_D + g * 8, v);
         tmem_wait_ld();

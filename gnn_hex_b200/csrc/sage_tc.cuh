@@ -17,7 +17,8 @@ namespace hexgnn {
 constexpr int kTcRows = 128;          // MMA M: node rows per tile
 constexpr int kTcKC = 16;             // k values per streamed weight chunk (2 MMA k-steps)
 constexpr int kTcStages = 4;          // ring depth
-constexpr int kTcEpiWarps = 8;        // epilogue warps: 4 lane quarters x 2 column slices
+constexpr int kTcEpiWarps = 16;       // epilogue warps: 4 TMEM lane quarters x 4 column slices
+constexpr int kTcSlices = kTcEpiWarps / 4;
 constexpr int kTcEpiThreads = kTcEpiWarps * 32;
 constexpr int kTcThreads = kTcEpiThreads + 64;  // + producer warp + MMA warp
 
