@@ -42,7 +42,7 @@ class HexCsrLayout(C.Structure):
 
 EXPORTS = ["hexgnn_abi_version", "hexgnn_last_error", "hexgnn_param_count", "hexgnn_param_offsets",
            "hexgnn_sizes", "hexgnn_csr_layout", "hexgnn_build_csr", "hexgnn_forward", "hexgnn_backward",
-           "hexgnn_profile_enable", "hexgnn_profile_read", "hexgnn_selftest_mma"]
+           "hexgnn_profile_enable", "hexgnn_profile_read", "hexgnn_selftest_mma", "hexgnn_debug_phases"]
 
 _lib = None
 
@@ -82,6 +82,8 @@ def lib():
     l.hexgnn_backward.argtypes = [D, p, p, i64, i64, i64, p, i32, i32, p, p, p, p, p, p, sz, p]
     l.hexgnn_selftest_mma.restype = C.c_int
     l.hexgnn_selftest_mma.argtypes = [p, p, p, i32, i32, i32, p]
+    l.hexgnn_debug_phases.restype = C.c_int
+    l.hexgnn_debug_phases.argtypes = [i32, C.POINTER(i64), i32]
     l.hexgnn_profile_enable.restype = C.c_int
     l.hexgnn_profile_enable.argtypes = [C.c_int]
     l.hexgnn_profile_read.restype = C.c_int
@@ -133,3 +135,10 @@ def profile_read(which):
     ms, n = C.c_double(0.0), C.c_int64(0)
     check(lib().hexgnn_profile_read(which, C.byref(ms), C.byref(n)), "hexgnn_profile_read")
     return ms.value, n.value
+
+
+def debug_phases(which):
+    """[148][16] cycle totals of the last tcgen05 launch (0 forward, 1 backward); see csrc/sage_*_tc.cu."""
+    buf = (C.c_int64 * (148 * 16))()
+    check(lib().hexgnn_debug_phases(which, buf, 148 * 16), "hexgnn_debug_phases")
+    return [list(buf[i * 16:(i + 1) * 16]) for i in range(148)]

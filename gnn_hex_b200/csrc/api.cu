@@ -183,9 +183,16 @@ int hexgnn_backward(const HexModelDesc* desc, const float* params, const float* 
   return launch_reduce_grads(d, pm, x, partials, nparts, cv.ntiles, packed_sum, grad_params, st);
 }
 
-int hexgnn_selftest_mma(const float* A, const float* B, float* D, int32_t N, int32_t K, int32_t b_layout, void* stream) {
+int hexgnn_selftest_mma(const float* A, const float* B, float* D, int32_t N, int32_t K, int32_t modes, void* stream) {
   if (!A || !B || !D) { set_error("selftest: null pointer"); return HEXGNN_E_BADARG; }
-  return launch_tc_selftest(A, B, D, N, K, b_layout, (cudaStream_t)stream);
+  return launch_tc_selftest(A, B, D, N, K, modes, (cudaStream_t)stream);
+}
+
+int hexgnn_debug_phases(int32_t which, int64_t* host_out, int32_t n) {
+  if (!host_out || n < 1) { set_error("debug_phases: bad argument"); return HEXGNN_E_BADARG; }
+  if (which == 0) return debug_read_fwd_phases((long long*)host_out, n);
+  set_error("debug_phases: unknown kernel %d", which);
+  return HEXGNN_E_BADARG;
 }
 
 int hexgnn_profile_enable(int on) {

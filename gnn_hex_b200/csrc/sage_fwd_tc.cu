@@ -48,6 +48,12 @@ struct FwdTcSmem {
   static size_t bytes(int Lt) { return (size_t)off_bias + (size_t)Lt * Hp * 4; }
 };
 
+// Phase profile (cycles, summed over the tiles of each CTA; read back by hexgnn_debug_phases):
+//   [0] epilogue: wait for Z   [1] phase 1 (Zl dump)   [2] phase 2 (gather + write-back)   [3] tile load + layer 0
+//   [4] head                   [5] MMA warp: wait for h   [6] MMA warp: wait for weights   [7] MMA warp: issue + commit
+//   [8] total kernel cycles of the CTA   [9] tiles
+__device__ long long g_fwd_phase[148 * 16];
+
 struct TileDims { int g0, g1, r0, n, e0, ne; bool ok; };
 __device__ __forceinline__ TileDims tile_dims(const CsrView& v, int t, int ecap) {
   TileDims d;
@@ -93,6 +99,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const int H = a.d.H, Lt = a.d.Lt;
   const int ntiles = *a.csr.ntiles;
+  const long long t_kernel0 = clock64();
+  long long ph0 = 0, ph1 = 0, ph2 = 0, ph3 = 0, ph4 = 0, ph5 = 0, ph6 = 0, ph7 = 0, ntl = 0;
 
   if (tid == 0) {
     for (int i = 0; i < kTcStages; ++i) { mbar_init(&bar_full[i], 1); mbar_init(&bar_empty[i], 1); }
@@ -134,12 +142,17 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
       for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
         if (!tile_dims(a.csr, t, S::ECAP).ok) continue;
         for (int s = 1; s < Lt; ++s) {
+          long long tq = clock64();
           mbar_wait(bar_a, na & 1);   // h of this layer is in TMEM, D has been drained
+          ph5 += clock64() - tq;
           ++na;
           tc_fence_after();
           for (int q = 0; q < NQ; ++q, ++it) {
             const int st = it % kTcStages;
+            tq = clock64();
             mbar_wait(&bar_full[st], (it / kTcStages) & 1);
+            ph6 += clock64() - tq;
+            tq = clock64();
             tc_fence_after();
             const uint32_t bhi = smem_u32(smem + S::off_ring + st * S::stage_bytes);
             const uint32_t blo = bhi + S::half_bytes;
@@ -153,9 +166,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
               mma_tf32_ts(tbase + TM_D, tbase + TM_HI + kcol, dhi, idesc, true);
             }
             mma_commit(&bar_empty[st]);   // stage free once these MMAs have read it
+            ph7 += clock64() - tq;
           }
           mma_commit(bar_d);              // Z complete
         }
+      }
+      if (blockIdx.x < 148) {
+        long long* o = g_fwd_phase + blockIdx.x * 16;
+        o[5] = ph5; o[6] = ph6; o[7] = ph7;
       }
     }
   } else {
@@ -171,6 +189,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
       const TileDims td = tile_dims(a.csr, t, S::ECAP);
       const int n = td.n, r0 = td.r0, g0 = td.g0, g1 = td.g1;
       epi_bar();   // previous tile fully consumed
+      long long tq = clock64();
+      ++ntl;
       if (!td.ok) {
         const int r1 = a.csr.gptr[g1];
         const float qnan = __int_as_float(0x7fc00000);
@@ -242,9 +262,13 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
         tc_fence_before();
         mbar_arrive(bar_a);
       }
+      ph3 += clock64() - tq;
       // ---- layers 1 .. Lt-1 on the tensor cores ---------------------------------------------------------------
       for (int s = 1; s < Lt; ++s) {
+        tq = clock64();
         mbar_wait(bar_d, nd & 1);
+        ph0 += clock64() - tq;
+        tq = clock64();
         ++nd;
         tc_fence_after();
         // phase 1: Zl -> shared (row major); all TMEM loads in flight before the single wait
@@ -267,6 +291,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
           }
         }
         epi_bar();
+        ph1 += clock64() - tq;
+        tq = clock64();
         // phase 2: h' = relu(mean_j Zl_j + Zr_i + b).  Neighbour-outer / granule-inner: one index load
         // feeds 2*MAXG independent 16-byte shared loads (latency-bound otherwise: 4 warps per scheduler).
         const bool last = (s == Lt - 1);
@@ -325,7 +351,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
           tc_fence_before();
           mbar_arrive(bar_a);
         }
+        ph2 += clock64() - tq;
       }
+      tq = clock64();
       // ---- final activations -> shared (row major) for the head ----------------------------------------------------
       epi_bar();   // every gather of the last layer has finished reading the dump
       for (int g = slice; g < NG; g += kTcSlices) {
@@ -352,6 +380,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
       }
       if (a.flags & HEXGNN_ADV_ONLY) {
         for (int i = tid; i < n; i += kTcEpiThreads) a.out_nodes[r0 + i] = adv_s[i];
+        ph4 += clock64() - tq;
         continue;
       }
       // ---- value head per graph: pools (sum|max|min|mean) -> MLP -> tanh; dueling combine --------------------------------
@@ -408,6 +437,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
         if (tid == 0 && a.out_value) a.out_value[g0 + g] = val;
         epi_bar();
       }
+      ph4 += clock64() - tq;
+    }
+    if (tid == 0 && blockIdx.x < 148) {
+      long long* o = g_fwd_phase + blockIdx.x * 16;
+      o[0] = ph0; o[1] = ph1; o[2] = ph2; o[3] = ph3; o[4] = ph4; o[8] = clock64() - t_kernel0; o[9] = ntl;
     }
   }
   // ---- teardown ----------------------------------------------------------------------------------------------------------
@@ -429,6 +463,12 @@ static int launch_fwd_tc_t(const FwdTcArgs& a, cudaStream_t st) {
     kern<<<grid, kTcThreads, smem, st>>>(a);
   }
   HEX_CUDA_CHECK(cudaGetLastError());
+  return HEXGNN_OK;
+}
+
+int debug_read_fwd_phases(long long* host, int n) {
+  if (n > 148 * 16) n = 148 * 16;
+  HEX_CUDA_CHECK(cudaMemcpyFromSymbol(host, g_fwd_phase, sizeof(long long) * n));
   return HEXGNN_OK;
 }
 

@@ -47,4 +47,6 @@ int launch_forward_tc(const Dims& d, const ParamMap& pm, const float* params, co
                       int64_t B, const void* csr, int flags, float* out_nodes, float* out_value, float* stash,
                       TcPackView pv, cudaStream_t st);
 
+int debug_read_fwd_phases(long long* host, int n);
+
 }  // namespace hexgnn

@@ -123,10 +123,16 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t 
   d |= (uint64_t)1 << 46;
   return d;
 }
-// Instruction descriptor, kind::tf32, fp32 accumulate, A from TMEM (K-major), dense.
-__host__ __device__ constexpr uint32_t make_idesc_tf32(int M, int N, bool b_mn_major) {
-  return (1u << 4) /*D=f32*/ | (2u << 7) /*A=tf32*/ | (2u << 10) /*B=tf32*/ | ((b_mn_major ? 1u : 0u) << 16) |
-         ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+// SWIZZLE_128B MN-major operand X[mn][k] (mn contiguous: a row-major [k][mn] tile, 32 mn = 128 bytes per
+// block row): byte(mn,k) = (mn/32)*LBO + (k/8)*SBO + (k%8)*128 + ((((mn%32)/4) ^ (k%8))*16) + (mn%4)*4,
+// SBO = 1024 for densely packed 8-row groups; the start address must be 1024-byte aligned.
+__device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  return make_smem_desc(smem_addr, lbo_bytes, sbo_bytes) | ((uint64_t)2 << 61);
+}
+// Instruction descriptor, kind::tf32, fp32 accumulate, dense.  A from TMEM is always K-major.
+__host__ __device__ constexpr uint32_t make_idesc_tf32(int M, int N, bool b_mn_major, bool a_mn_major = false) {
+  return (1u << 4) /*D=f32*/ | (2u << 7) /*A=tf32*/ | (2u << 10) /*B=tf32*/ | ((a_mn_major ? 1u : 0u) << 15) |
+         ((b_mn_major ? 1u : 0u) << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
 // D[tmem] (+)= A[tmem] * B[smem]; one thread issues.
@@ -137,6 +143,16 @@ __device__ __forceinline__ void mma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, ui
       "setp.ne.b32 p, %4, 0;\n\t"
       "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
       ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate ? 1u : 0u)
+      : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]
+__device__ __forceinline__ void mma_tf32_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                            bool accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate ? 1u : 0u)
       : "memory");
 }
 // Arrive on `bar` when every previously issued tcgen05.mma of this thread has completed

@@ -142,9 +142,16 @@ int hexgnn_backward(const HexModelDesc* desc, const float* params, const float* 
                     void* ws, size_t ws_bytes, void* stream);
 
 /* Self-test of the tcgen05 building blocks the fused kernels are made of: one CTA computes
- * D[128,N] = A[128,K] * B[K,N] (row-major device fp32, 3xTF32) with A in tensor memory and B in shared
- * memory in canonical layout `b_layout` (0 = K-major, 1 = MN-major).  N%16==0, K%8==0, K<=128. */
-int hexgnn_selftest_mma(const float* A, const float* B, float* D, int32_t N, int32_t K, int32_t b_layout, void* stream);
+ * D[128,N] = A[128,K] * B[K,N] (row-major device fp32, 3xTF32).  `modes` = a_mode*16 + b_mode selects the
+ * operand staging (a_mode 0 tensor memory | 1 smem K-major SWIZZLE_NONE | 3 smem MN-major
+ * SWIZZLE_128B_BASE32B; b_mode 0 smem K-major SWIZZLE_NONE | 3 smem MN-major SWIZZLE_128B_BASE32B).
+ * N%16==0, K%8==0, K<=128. */
+int hexgnn_selftest_mma(const float* A, const float* B, float* D, int32_t N, int32_t K, int32_t modes, void* stream);
+
+/* Phase profile of the last tcgen05 launch (which: 0 forward, 1 backward): per CTA (148 x 16 int64, HOST
+ * buffer) cycle totals of the kernel's internal phases, see the table above g_fwd_phase / g_bwd_phase.
+ * Synchronises the device.  Diagnostic only. */
+int hexgnn_debug_phases(int32_t which, int64_t* host_out, int32_t n);
 
 /* Measurement aid (bench.py `roofline`): while enabled (process-wide; NOT re-entrant, use from one
  * stream at a time), hexgnn_forward and

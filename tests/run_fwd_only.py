@@ -20,3 +20,11 @@ with torch.no_grad():
         q = m(b.x, b.edge_index, b.batch, b.ptr, csr=csr)
     e.record(); torch.cuda.synchronize()
 print("fwd ms/call", s.elapsed_time(e) / 20, "q[0]", float(q[0]))
+from gnn_hex_b200 import _lib
+ph = _lib.debug_phases(0)
+import statistics
+names = ["wait_Z", "phase1", "phase2", "load+l0", "head", "mma:wait_h", "mma:wait_w", "mma:issue", "total", "tiles"]
+for k in (1, 2):
+    rows = [r for r in ph if r[9] == k]
+    if rows:
+        print(f"CTAs with {k} tiles: {len(rows)};", ", ".join(f"{n}={statistics.mean(r[i] for r in rows)/k:.0f}" for i, n in enumerate(names[:9])), "(cycles per tile)")

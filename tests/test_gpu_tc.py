@@ -21,18 +21,26 @@ def _gemm(A, B, layout):
     return D
 
 
-# layout 1 (MN-major SWIZZLE_NONE B) returned zeros on B200 and is not used by any kernel: K-major only.
-@pytest.mark.parametrize("N,K,layout", [(224, 112, 0), (112, 112, 0), (112, 128, 0), (48, 48, 0), (96, 48, 0),
-                                        (48, 128, 0), (16, 8, 0), (256, 96, 0)])
-def test_tcgen05_3xtf32_gemm(N, K, layout):
+# MN-major tf32 operands exist only in the SWIZZLE_128B_BASE32B form (mode 3); MN-major with SWIZZLE_NONE or
+# plain SWIZZLE_128B silently produced zeros on B200 and is not used by any kernel.
+MODES = {"A tmem, B K-major": 0x00, "A tmem, B MN-major sw128/32B": 0x03, "A smem K-major, B K-major": 0x10,
+         "A smem MN-major, B MN-major (sw128/32B)": 0x33, "A smem K-major, B MN-major sw128/32B": 0x13}
+
+
+@pytest.mark.parametrize("N,K", [(224, 112), (112, 128), (48, 48), (96, 48), (16, 8), (256, 96), (128, 64)])
+@pytest.mark.parametrize("mode", list(MODES))
+def test_tcgen05_3xtf32_gemm(N, K, mode):
+    layout = MODES[mode]
+    if layout >= 0x10 and K * (N + 31) // 32 * 32 * 8 + 128 * K * 8 > 200 * 1024:
+        pytest.skip("operand images exceed shared memory")
     g = torch.Generator().manual_seed(N * 1000 + K + layout)
     A = torch.randn(128, K, generator=g).to(DEV)
     B = torch.randn(K, N, generator=g).to(DEV)
     D = _gemm(A, B, layout)
     ref = A.double() @ B.double()
     err = float((D.double() - ref).abs().max() / ref.abs().max())
-    # structured operands catch layout permutations that random data would also catch, but readably
     assert err < 2e-6, err
+    # structured operands: exact small integers, any layout permutation shows up as a wrong integer
     A2 = torch.zeros(128, K, device=DEV); A2[:, 0] = torch.arange(128, device=DEV)
     A2[:, K - 1] = 1.0
     B2 = torch.zeros(K, N, device=DEV); B2[0] = torch.arange(N, device=DEV); B2[K - 1] = 1000.0
