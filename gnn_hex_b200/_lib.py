@@ -42,7 +42,7 @@ class HexCsrLayout(C.Structure):
 
 EXPORTS = ["hexgnn_abi_version", "hexgnn_last_error", "hexgnn_param_count", "hexgnn_param_offsets",
            "hexgnn_sizes", "hexgnn_csr_layout", "hexgnn_build_csr", "hexgnn_forward", "hexgnn_backward",
-           "hexgnn_profile_enable", "hexgnn_profile_read", "hexgnn_selftest_mma", "hexgnn_debug_phases"]
+           "hexgnn_profile_enable", "hexgnn_profile_read", "hexgnn_selftest_mma", "hexgnn_debug_phases", "hexgnn_stash_embed"]
 
 _lib = None
 
@@ -82,6 +82,8 @@ def lib():
     l.hexgnn_backward.argtypes = [D, p, p, i64, i64, i64, p, i32, i32, p, p, p, p, p, p, sz, p]
     l.hexgnn_selftest_mma.restype = C.c_int
     l.hexgnn_selftest_mma.argtypes = [p, p, p, i32, i32, i32, p]
+    l.hexgnn_stash_embed.restype = C.c_int
+    l.hexgnn_stash_embed.argtypes = [D, i64, i64, i32, C.POINTER(i64), C.POINTER(i64)]
     l.hexgnn_debug_phases.restype = C.c_int
     l.hexgnn_debug_phases.argtypes = [i32, C.POINTER(i64), i32]
     l.hexgnn_profile_enable.restype = C.c_int
@@ -142,3 +144,10 @@ def debug_phases(which):
     buf = (C.c_int64 * (148 * 16))()
     check(lib().hexgnn_debug_phases(which, buf, 148 * 16), "hexgnn_debug_phases")
     return [list(buf[i * 16:(i + 1) * 16]) for i in range(148)]
+
+
+def stash_embed(desc, N, B, flags):
+    """(float offset, row pitch) of the row-major body embedding inside the forward stash."""
+    off, pitch = C.c_int64(0), C.c_int64(0)
+    check(lib().hexgnn_stash_embed(C.byref(desc), N, B, flags, C.byref(off), C.byref(pitch)), "hexgnn_stash_embed")
+    return off.value, pitch.value

@@ -59,6 +59,10 @@ ProfScope::~ProfScope() {
 
 static bool tile_rows_ok(int tile_rows) { return tile_rows == 128; }
 
+// One decision for forward AND backward (their stash formats differ): the tcgen05 kernels unless the caller
+// forces the CUDA-core path or the hidden size leaves no room for the ones-channel (Hp = 128).
+static bool use_tc(const Dims& d, int flags) { return !(flags & HEXGNN_PATH_SIMT) && tc_bwd_supported(d); }
+
 }  // namespace hexgnn
 
 using namespace hexgnn;
@@ -110,8 +114,12 @@ int hexgnn_sizes(const HexModelDesc* desc, int64_t N, int64_t E, int64_t B, int3
   grad_layout(d, &gl);
   out->csr_bytes = l.total_words * 4;
   out->fwd_ws_bytes = (pack_floats(d) > tc_pack_floats(d) ? pack_floats(d) : tc_pack_floats(d)) * 4;
-  out->stash_bytes = (int64_t)d.Lt * N * d.Hp * 4;
-  out->bwd_ws_bytes = (pack_floats(d) + (int64_t)(bwd_grid_ctas() + 1) * gl.total) * 4;
+  const int64_t simt_stash = (int64_t)d.Lt * N * d.Hp * 4;
+  const int64_t simt_bwd = (pack_floats(d) + (int64_t)(bwd_grid_ctas() + 1) * gl.total) * 4;
+  const bool tc = tc_bwd_supported(d);
+  const int64_t tc_stash = tc ? tc_stash_bytes(d, N, B) : 0, tc_bwd = tc ? tc_bwd_ws(d, B).total * 4 : 0;
+  out->stash_bytes = simt_stash > tc_stash ? simt_stash : tc_stash;
+  out->bwd_ws_bytes = simt_bwd > tc_bwd ? simt_bwd : tc_bwd;
   out->hidden_padded = d.Hp;
   return HEXGNN_OK;
 }
@@ -141,7 +149,7 @@ int hexgnn_forward(const HexModelDesc* desc, const float* params, const float* x
   ParamMap pm;
   make_param_map(d, &pm);
   cudaStream_t st = (cudaStream_t)stream;
-  if (flags & HEXGNN_PATH_SIMT) {
+  if (!use_tc(d, flags)) {
     PackView pv = pack_view(ws, d);
     int rc = launch_pack(d, pm, params, x, pv, false, st);
     if (rc) return rc;
@@ -164,23 +172,48 @@ int hexgnn_backward(const HexModelDesc* desc, const float* params, const float* 
   if (!tile_rows_ok(tile_rows) || d.NJ > 8) { set_error("backward: unsupported tile_rows=%d or hidden=%d", tile_rows, d.H); return HEXGNN_E_UNSUPPORTED; }
   GradLayout gl;
   grad_layout(d, &gl);
+  ParamMap pm;
+  make_param_map(d, &pm);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (use_tc(d, flags)) {
+    const TcBwdWs w = tc_bwd_ws(d, B);
+    if ((int64_t)ws_bytes < w.total * 4) { set_error("backward: workspace too small (%zu < %lld)", ws_bytes, (long long)w.total * 4); return HEXGNN_E_WORKSPACE; }
+    float* wsf = (float*)ws;
+    TcPackView tpv = tc_pack_view(wsf + w.pack, d);
+    int rc = launch_pack_tc(d, pm, params, x, tpv, true, st);
+    if (rc) return rc;
+    const int grid = bwd_grid_ctas();
+    rc = launch_backward_tc_chain(d, pm, params, x, N, E, B, csr, flags, d_nodes, d_value, stash, wsf + w.dz, d_embeds, tpv,
+                                  wsf + w.small_rec, grid, st);
+    if (rc) return rc;
+    rc = launch_backward_tc_dw(d, N, E, B, csr, stash, wsf + w.dz, wsf + w.big_rec, st);
+    if (rc) return rc;
+    rc = launch_reduce_tc(d, wsf + w.small_rec, grid, wsf + w.big_rec, tc_dw_groups(d), wsf + w.sum, st);
+    if (rc) return rc;
+    return launch_unpack_grads(d, pm, x, wsf + w.sum, grad_params, st);
+  }
   const int nparts = bwd_grid_ctas();
   const int64_t need = (pack_floats(d) + (int64_t)(nparts + 1) * gl.total) * 4;
   if ((int64_t)ws_bytes < need) { set_error("backward: workspace too small (%zu < %lld)", ws_bytes, (long long)need); return HEXGNN_E_WORKSPACE; }
-  ParamMap pm;
-  make_param_map(d, &pm);
   PackView pv = pack_view(ws, d);
   float* partials = (float*)ws + pack_floats(d);
   float* packed_sum = partials + (int64_t)nparts * gl.total;
-  cudaStream_t st = (cudaStream_t)stream;
   int rc = launch_pack(d, pm, params, x, pv, true, st);
   if (rc) return rc;
-  if (flags & HEXGNN_PATH_TC) { set_error("backward: tcgen05 path not built for this shape"); return HEXGNN_E_UNSUPPORTED; }
   rc = launch_backward_simt(d, pm, params, x, N, E, B, csr, tile_rows, flags, d_nodes, d_value, stash, d_embeds, pv,
                             partials, st);
   if (rc) return rc;
   CsrView cv = csr_view(const_cast<void*>(csr), N, E, B);
   return launch_reduce_grads(d, pm, x, partials, nparts, cv.ntiles, packed_sum, grad_params, st);
+}
+
+int hexgnn_stash_embed(const HexModelDesc* desc, int64_t N, int64_t B, int32_t flags, int64_t* offset_floats,
+                       int64_t* row_pitch) {
+  Dims d;
+  if (!make_dims(desc, &d) || !offset_floats || !row_pitch || N < 0 || B < 0) { set_error("stash_embed: bad argument"); return HEXGNN_E_BADARG; }
+  *row_pitch = d.Hp;
+  *offset_floats = use_tc(d, flags) ? (int64_t)d.Lt * B * tc_act_blocks(d.Hp) * (kImgBlockBytes / 4) : (int64_t)(d.L - 1) * N * d.Hp;
+  return HEXGNN_OK;
 }
 
 int hexgnn_selftest_mma(const float* A, const float* B, float* D, int32_t N, int32_t K, int32_t modes, void* stream) {
@@ -191,6 +224,7 @@ int hexgnn_selftest_mma(const float* A, const float* B, float* D, int32_t N, int
 int hexgnn_debug_phases(int32_t which, int64_t* host_out, int32_t n) {
   if (!host_out || n < 1) { set_error("debug_phases: bad argument"); return HEXGNN_E_BADARG; }
   if (which == 0) return debug_read_fwd_phases((long long*)host_out, n);
+  if (which == 1) return debug_read_bwd_phases((long long*)host_out, n);
   set_error("debug_phases: unknown kernel %d", which);
   return HEXGNN_E_BADARG;
 }

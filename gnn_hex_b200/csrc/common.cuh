@@ -205,6 +205,8 @@ int launch_backward_simt(const Dims& d, const ParamMap& pm, const float* params,
 int launch_reduce_grads(const Dims& d, const ParamMap& pm, const float* x, const float* partials, int nparts,
                         const int* ntiles, float* packed_sum, float* grad_params, cudaStream_t st);
 
+int launch_unpack_grads(const Dims& d, const ParamMap& pm, const float* x, const float* packed_sum, float* grad_params,
+                        cudaStream_t st);
 int launch_tc_selftest(const float* A, const float* B, float* D, int N, int K, int modes, cudaStream_t st);
 
 }  // namespace hexgnn

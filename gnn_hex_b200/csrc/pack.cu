@@ -117,6 +117,17 @@ __global__ void unpack_grads_kernel(Dims d, ParamMap pm, GradLayout gl, const fl
   }
 }
 
+int launch_unpack_grads(const Dims& d, const ParamMap& pm, const float* x, const float* packed_sum, float* grad_params,
+                        cudaStream_t st) {
+  GradLayout gl;
+  grad_layout(d, &gl);
+  int b2 = (int)((pm.total + 255) / 256);
+  if (b2 > 1184) b2 = 1184;
+  unpack_grads_kernel<<<b2, 256, 0, st>>>(d, pm, gl, x, packed_sum, grad_params);
+  HEX_CUDA_CHECK(cudaGetLastError());
+  return HEXGNN_OK;
+}
+
 int launch_reduce_grads(const Dims& d, const ParamMap& pm, const float* x, const float* partials, int nparts,
                         const int* ntiles, float* packed_sum, float* grad_params, cudaStream_t st) {
   GradLayout gl;

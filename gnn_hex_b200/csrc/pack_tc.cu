@@ -34,13 +34,14 @@ __global__ void pack_tc_kernel(Dims d, ParamMap pm, const float* __restrict__ pa
       pv.wimg[off + half_f] = lo;
     }
     if (with_transpose) {
-      // backward: U[i][(which,k)] = sum_c dpre[i][c] * W_which[c][k]  =>  B[n = which*Hp + k][kk = c]
-      const int nb = (n < Hp ? 0 : Hp) + k, kb = c;
-      const int q = kb / kTcKC, kq = kb % kTcKC;
-      const int64_t off = (int64_t)(s - 1) * layer_f + (int64_t)q * 2 * half_f + (int64_t)(kq / 4) * (N2 * 4) +
-                          (nb / 8) * 32 + (nb % 8) * 4 + (kq % 4);
+      // backward: dH[i][k] = sum_c dZ_which[i][c] * W_which[c][k]  =>  B[n = k][kk = c], which 0 = lin_r, 1 = lin_l
+      const int which = n < Hp ? 1 : 0;
+      const int64_t halfB = (int64_t)kTcKC * Hp;                  // floats per half of a (which, q) stage
+      const int q = c / kTcKC, cq = c % kTcKC;
+      const int64_t off = (((int64_t)(s - 1) * 2 + which) * NQ + q) * 2 * halfB + (int64_t)(cq / 4) * (Hp * 4) +
+                          (k / 8) * 32 + (k % 8) * 4 + (cq % 4);
       pv.wimgT[off] = hi;
-      pv.wimgT[off + half_f] = lo;
+      pv.wimgT[off + halfB] = lo;
     }
   }
   const int nb = d.Lt * Hp;
@@ -57,6 +58,36 @@ int launch_pack_tc(const Dims& d, const ParamMap& pm, const float* params, const
   if (blocks < 1) blocks = 1;
   if (blocks > 1184) blocks = 1184;
   pack_tc_kernel<<<blocks, 256, 0, st>>>(d, pm, params, x, pv, with_transpose ? 1 : 0);
+  HEX_CUDA_CHECK(cudaGetLastError());
+  return HEXGNN_OK;
+}
+
+// Fixed-order reduction of the tcgen05 backward's partial records into one packed record (GradLayout):
+//   gw and gb[s>=1]  <- the G group records of sage_dw_tc_kernel   (big_rec [G][gl.g0])
+//   everything else  <- the per-CTA records of sage_bwd_tc_kernel  (small_rec [nsmall][gl.total - gl.gb])
+__global__ void reduce_tc_kernel(GradLayout gl, int Hp, const float* __restrict__ small_rec, int nsmall,
+                                 const float* __restrict__ big_rec, int G, float* __restrict__ out) {
+  const int64_t nth = (int64_t)gridDim.x * blockDim.x;
+  const int64_t recn = gl.total - gl.gb;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < gl.total; i += nth) {
+    float acc = 0.f;
+    const bool from_big = i < gl.gb || (i >= gl.gb + Hp && i < gl.g0);
+    if (from_big) {
+      for (int g = 0; g < G; ++g) acc += big_rec[(int64_t)g * gl.g0 + i];
+    } else {
+      for (int p = 0; p < nsmall; ++p) acc += small_rec[(int64_t)p * recn + (i - gl.gb)];
+    }
+    out[i] = acc;
+  }
+}
+
+int launch_reduce_tc(const Dims& d, const float* small_rec, int nsmall, const float* big_rec, int G, float* packed_sum,
+                     cudaStream_t st) {
+  GradLayout gl;
+  grad_layout(d, &gl);
+  int blocks = (int)((gl.total + 255) / 256);
+  if (blocks > 1184) blocks = 1184;
+  reduce_tc_kernel<<<blocks, 256, 0, st>>>(gl, d.Hp, small_rec, nsmall, big_rec, G, packed_sum);
   HEX_CUDA_CHECK(cudaGetLastError());
   return HEXGNN_OK;
 }

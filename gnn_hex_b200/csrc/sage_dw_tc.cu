@@ -1,0 +1,207 @@
+// Fused backward on the tensor cores, part B: the weight gradients of SAGE layers 1..Lt-1,
+//     dWcat_s [Hp(+1) x 2Hp] = [h_s | 1]^T  *  [dZl_s | dpre_s]          (contraction over ALL node rows)
+// as a split-K tcgen05 GEMM.  Both operands are the row-major RM32 stash images (sage_tc.cuh) read as MN-major
+// SWIZZLE_128B_BASE32B shared-memory operands (SS mode): no transposition anywhere.  Work item = (layer s, group g):
+// the CTA walks the tiles t = g, g+G, ... and accumulates in ONE TMEM accumulator, so only G partial records per
+// layer exist (G = 148 / (Lt-1)) instead of one per CTA of the chain kernel, and they are summed in fixed order.
+// Warp roles: producer (4 KB bulk copies of 32-row k-chunks), 8 split warps (fp32 -> tf32 hi in place + lo copy,
+// 3xTF32), MMA issuer, and the split warps double as the epilogue.
+#include "sage_tc.cuh"
+
+namespace hexgnn {
+using namespace tc;
+
+constexpr int kDwSplitWarps = 8;
+constexpr int kDwSplitThreads = kDwSplitWarps * 32;
+constexpr int kDwThreads = kDwSplitThreads + 64;
+constexpr int kDwStages = 2;
+constexpr int kDwChunkRows = 32;
+
+struct DwArgs {
+  Dims d;
+  GradLayout gl;
+  int64_t B;
+  CsrView csr;
+  const float* stash;   // activations (RM32 images)
+  const float* dz;      // [dZl | dpre] (RM32 images)
+  float* big_rec;       // [G][gl.g0]
+  int G;
+};
+
+template <int NJ>
+__global__ void __launch_bounds__(kDwThreads, 1) sage_dw_tc_kernel(const __grid_constant__ DwArgs a) {
+  constexpr int Hp = 16 * NJ, N2 = 32 * NJ;
+  constexpr int ABLK = 4;                                   // A blocks addressed by the M = 128 descriptor
+  constexpr int a_bytes = ABLK * 4096, b_bytes = NJ * 4096; // one 32-row chunk of each operand (fp32)
+  constexpr int half_bytes = a_bytes + b_bytes;             // hi half; the lo half follows
+  constexpr int stage_bytes = 2 * half_bytes;
+  constexpr uint32_t TM_COLS = (N2 <= 32) ? 32 : (N2 <= 64) ? 64 : (N2 <= 128) ? 128 : 256;
+  extern __shared__ uint8_t smem_dyn[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_dyn + 1023) & ~(uintptr_t)1023);
+  __shared__ uint64_t bar_full[kDwStages], bar_split[kDwStages], bar_empty[kDwStages], bar_done;
+  __shared__ uint32_t tmem_slot;
+
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int item = blockIdx.x;
+  const int s = 1 + item / a.G, grp = item % a.G;
+  const int ntiles = *a.csr.ntiles;
+  const int CB = tc_act_blocks(Hp);
+  const size_t act_img = (size_t)CB * kImgBlockBytes, dz_img = (size_t)NJ * kImgBlockBytes;
+
+  if (tid == 0) {
+    for (int i = 0; i < kDwStages; ++i) { mbar_init(&bar_full[i], 1); mbar_init(&bar_split[i], kDwSplitThreads); mbar_init(&bar_empty[i], 1); }
+    mbar_init(&bar_done, 1);
+    fence_mbar_init();
+  }
+  if (wid == kDwSplitWarps + 1) tmem_alloc(&tmem_slot, TM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tbase = tmem_slot;
+
+  auto tile_rows32 = [&](int t) {
+    const int gA = a.csr.tile_g0[t], gB = a.csr.tile_g0[t + 1];
+    const int n = a.csr.gptr[gB] - a.csr.gptr[gA];
+    return (n < 0 || n > kTcRows) ? 0 : ((n + 31) & ~31);
+  };
+
+  if (wid == kDwSplitWarps) {
+    // ================= producer =================
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int t = grp; t < ntiles; t += a.G) {
+        const int n32 = tile_rows32(t);
+        const char* act = (const char*)a.stash + ((size_t)(s - 1) * a.B + t) * act_img;
+        const char* dzp = (const char*)a.dz + ((size_t)(s - 1) * a.B + t) * dz_img;
+        for (int c0 = 0; c0 < n32; c0 += kDwChunkRows, ++it) {
+          const int st = it % kDwStages;
+          mbar_wait(&bar_empty[st], ((it / kDwStages) & 1) ^ 1);
+          uint8_t* dstA = smem + st * stage_bytes;
+          uint8_t* dstB = dstA + a_bytes;
+          mbar_expect_tx(&bar_full[st], (uint32_t)(CB + NJ) * 4096u);
+          for (int b = 0; b < CB; ++b) bulk_g2s(dstA + b * 4096, act + (size_t)b * kImgBlockBytes + (size_t)c0 * 128, 4096, &bar_full[st]);
+          for (int b = 0; b < NJ; ++b) bulk_g2s(dstB + b * 4096, dzp + (size_t)b * kImgBlockBytes + (size_t)c0 * 128, 4096, &bar_full[st]);
+        }
+      }
+    }
+  } else if (wid == kDwSplitWarps + 1) {
+    // ================= MMA issuer =================
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_tf32(128, N2, true, true);
+      uint32_t it = 0;
+      for (int t = grp; t < ntiles; t += a.G) {
+        const int n32 = tile_rows32(t);
+        for (int c0 = 0; c0 < n32; c0 += kDwChunkRows, ++it) {
+          const int st = it % kDwStages;
+          mbar_wait(&bar_split[st], (it / kDwStages) & 1);
+          tc_fence_after();
+          const uint32_t ahi = smem_u32(smem + st * stage_bytes), bhi = ahi + a_bytes;
+          const uint32_t alo = ahi + half_bytes, blo = bhi + half_bytes;
+#pragma unroll
+          for (int ks = 0; ks < kDwChunkRows / 8; ++ks) {
+            const uint64_t one = (uint64_t)1 << 61;   // SWIZZLE_128B_BASE32B
+            const uint64_t dah = make_smem_desc(ahi + ks * 1024, 4096, 512) | one;
+            const uint64_t dal = make_smem_desc(alo + ks * 1024, 4096, 512) | one;
+            const uint64_t dbh = make_smem_desc(bhi + ks * 1024, 4096, 512) | one;
+            const uint64_t dbl = make_smem_desc(blo + ks * 1024, 4096, 512) | one;
+            mma_tf32_ss(tbase, dal, dbh, idesc, (it | ks) != 0);
+            mma_tf32_ss(tbase, dah, dbl, idesc, true);
+            mma_tf32_ss(tbase, dah, dbh, idesc, true);
+          }
+          mma_commit(&bar_empty[st]);
+        }
+      }
+      mma_commit(&bar_done);
+    }
+  } else {
+    // ================= split warps: fp32 -> (tf32 hi in place, tf32 lo copy) =================
+    uint32_t it = 0;
+    for (int t = grp; t < ntiles; t += a.G) {
+      const int n32 = tile_rows32(t);
+      for (int c0 = 0; c0 < n32; c0 += kDwChunkRows, ++it) {
+        const int st = it % kDwStages;
+        mbar_wait(&bar_full[st], (it / kDwStages) & 1);
+        float4* base = (float4*)(smem + st * stage_bytes);
+        float4* lob = (float4*)(smem + st * stage_bytes + half_bytes);
+        const int nA = CB * 256, nB = NJ * 256;       // float4 per region
+        for (int i = tid; i < nA + nB; i += kDwSplitThreads) {
+          const int idx = i < nA ? i : (ABLK * 256 + (i - nA));
+          const float4 v = base[idx];
+          float4 h, l;
+          split_tf32(v.x, h.x, l.x); split_tf32(v.y, h.y, l.y); split_tf32(v.z, h.z, l.z); split_tf32(v.w, h.w, l.w);
+          base[idx] = h;
+          lob[idx] = l;
+        }
+        fence_proxy_async();
+        mbar_arrive(&bar_split[st]);
+      }
+    }
+    // ================= epilogue: D[k][c'] -> this group's record =================
+    mbar_wait(&bar_done, 0);
+    tc_fence_after();
+    if (wid < 4) {
+      const int m = wid * 32 + lane;                       // D lane = input channel k (Hp = ones channel)
+      const uint32_t trow = tbase + ((uint32_t)(wid * 32) << 16);
+      float* rec = a.big_rec + (int64_t)grp * a.gl.g0;
+      const bool have = it > 0;
+      for (int c0 = 0; c0 < N2; c0 += 8) {
+        float v[8];
+        tmem_ld8(trow + c0, v);                            // warp-collective: every lane takes part
+        tmem_wait_ld();
+        if (!have) {
+#pragma unroll
+          for (int u = 0; u < 8; ++u) v[u] = 0.f;
+        }
+        if (m < Hp) {
+          float4* dst = (float4*)(rec + a.gl.gw + ((int64_t)(s - 1) * Hp + m) * N2 + c0);
+          dst[0] = make_float4(v[0], v[1], v[2], v[3]);
+          dst[1] = make_float4(v[4], v[5], v[6], v[7]);
+        } else if (m == Hp && c0 >= Hp) {
+          float4* dst = (float4*)(rec + a.gl.gb + (int64_t)s * Hp + (c0 - Hp));
+          dst[0] = make_float4(v[0], v[1], v[2], v[3]);
+          dst[1] = make_float4(v[4], v[5], v[6], v[7]);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (wid == kDwSplitWarps + 1) tmem_dealloc(tbase, TM_COLS);
+}
+
+int tc_dw_groups(const Dims& d) {
+  int g = bwd_grid_ctas() / (d.Lt - 1);
+  return g < 1 ? 1 : g;
+}
+
+template <int NJ>
+static int launch_dw_t(const DwArgs& a, cudaStream_t st) {
+  auto kern = sage_dw_tc_kernel<NJ>;
+  const size_t smem = (size_t)kDwStages * 2 * (4 * 4096 + NJ * 4096) + 1024;
+  HEX_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<(a.d.Lt - 1) * a.G, kDwThreads, smem, st>>>(a);
+  HEX_CUDA_CHECK(cudaGetLastError());
+  return HEXGNN_OK;
+}
+
+int launch_backward_tc_dw(const Dims& d, int64_t N, int64_t E, int64_t B, const void* csr, const float* stash,
+                          const float* dz, float* big_rec, cudaStream_t st) {
+  DwArgs a;
+  a.d = d; grad_layout(d, &a.gl); a.B = B;
+  a.csr = csr_view(const_cast<void*>(csr), N, E, B);
+  a.stash = stash; a.dz = dz; a.big_rec = big_rec; a.G = tc_dw_groups(d);
+  switch (d.NJ) {
+    case 1: return launch_dw_t<1>(a, st);
+    case 2: return launch_dw_t<2>(a, st);
+    case 3: return launch_dw_t<3>(a, st);
+    case 4: return launch_dw_t<4>(a, st);
+    case 5: return launch_dw_t<5>(a, st);
+    case 6: return launch_dw_t<6>(a, st);
+    case 7: return launch_dw_t<7>(a, st);
+    default: break;
+  }
+  set_error("backward(tc dW): unsupported hidden=%d", d.H);
+  return HEXGNN_E_UNSUPPORTED;
+}
+
+}  // namespace hexgnn

@@ -231,6 +231,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
         epi_bar();
       }
       const bool live = row < n;
+      const int n32 = (n + 31) & ~31;
+      // training stash: RM32 image of this (layer, tile), see sage_tc.cuh
+      const size_t img_bytes = (size_t)tc_act_blocks(Hp) * kImgBlockBytes;
+      char* st_img = a.stash ? (char*)a.stash + ((size_t)0 * a.B + t) * img_bytes : nullptr;
+      float* emb = a.stash ? a.stash + (size_t)Lt * a.B * (img_bytes / 4) : nullptr;
       const float inv = inv_s[row];
       const int eb = rowptr_s[row], ee = rowptr_s[row + 1];
       // ---- layer 0 (2 -> H): rank-2 update, result -> TMEM as the first A operand --------------------------
@@ -252,11 +257,21 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
           }
           tmem_st8(trow + TM_HI + g * 8, hi);
           tmem_st8(trow + TM_LO + g * 8, lo);
-          if (a.stash && live) {
-            float4* dst = (float4*)(a.stash + (int64_t)(r0 + row) * Hp + g * 8);
+          if (st_img && row < n32) {
+            float4* dst = (float4*)(st_img + rm32_granule_off(g, row));
             dst[0] = make_float4(v[0], v[1], v[2], v[3]);
             dst[1] = make_float4(v[4], v[5], v[6], v[7]);
           }
+          if (emb && a.d.L == 1 && live) {
+            float4* dst = (float4*)(emb + (int64_t)(r0 + row) * Hp + g * 8);
+            dst[0] = make_float4(v[0], v[1], v[2], v[3]);
+            dst[1] = make_float4(v[4], v[5], v[6], v[7]);
+          }
+        }
+        if (st_img && slice == 0 && row < n32) {   // ones channel (bias gradient row of h^T dZ)
+          float4* dst = (float4*)(st_img + rm32_granule_off(NG, row));
+          dst[0] = make_float4(live ? 1.f : 0.f, 0.f, 0.f, 0.f);
+          dst[1] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
         tmem_wait_st();
         tc_fence_before();
@@ -297,7 +312,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
         // feeds 2*MAXG independent 16-byte shared loads (latency-bound otherwise: 4 warps per scheduler).
         const bool last = (s == Lt - 1);
         const float* bias = bias_s + s * Hp;
-        float* st = (a.stash && live) ? a.stash + ((int64_t)s * a.N + r0 + row) * Hp : nullptr;
+        char* st = (a.stash && row < n32) ? st_img + (size_t)s * a.B * img_bytes : nullptr;
         float acc[MAXG][8];
 #pragma unroll
         for (int gi = 0; gi < MAXG; ++gi)
@@ -334,7 +349,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
               split_tf32(r, hi[u], lo[u]);
             }
             if (st) {
-              float4* dst = (float4*)(st + g * 8);
+              float4* dst = (float4*)(st + rm32_granule_off(g, row));
+              dst[0] = make_float4(acc[gi][0], acc[gi][1], acc[gi][2], acc[gi][3]);
+              dst[1] = make_float4(acc[gi][4], acc[gi][5], acc[gi][6], acc[gi][7]);
+            }
+            if (emb && s == a.d.L - 1 && live) {
+              float4* dst = (float4*)(emb + (int64_t)(r0 + row) * Hp + g * 8);
               dst[0] = make_float4(acc[gi][0], acc[gi][1], acc[gi][2], acc[gi][3]);
               dst[1] = make_float4(acc[gi][4], acc[gi][5], acc[gi][6], acc[gi][7]);
             }
@@ -345,6 +365,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
               tmem_st8(trow + TM_D + g * 8, acc[gi]);   // park the exact fp32 activations in the drained Zl columns
             }
           }
+        }
+        if (st && slice == 0) {
+          float4* dst = (float4*)(st + rm32_granule_off(NG, row));
+          dst[0] = make_float4(live ? 1.f : 0.f, 0.f, 0.f, 0.f);
+          dst[1] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
         tmem_wait_st();
         if (!last) {

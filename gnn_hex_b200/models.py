@@ -72,8 +72,8 @@ class _FusedQ(torch.autograd.Function):
         ctx.model, ctx.csr, ctx.flags, ctx.stash = model, csr, flags, stash
         ctx.save_for_backward(x)
         ctx.flat_version = model._flat_version
-        L, H = model.num_layers, model.hidden_channels
-        model.final_conv_acts = stash[(L - 1) * csr.N * hp:L * csr.N * hp].view(csr.N, hp)[:, :H]
+        off, pitch = _lib.stash_embed(model._desc, csr.N, csr.B, flags)
+        model.final_conv_acts = stash[off:off + csr.N * pitch].view(csr.N, pitch)[:, :model.hidden_channels]
         return out_nodes, out_value
 
     @staticmethod

@@ -141,6 +141,11 @@ int hexgnn_backward(const HexModelDesc* desc, const float* params, const float* 
                     const float* d_value, const float* stash, float* grad_params, float* d_embeds,
                     void* ws, size_t ws_bytes, void* stream);
 
+/* Where forward (with `flags`) leaves the body embedding h_L (`final_conv_acts`, models.py:553) inside the stash:
+ * float offset of a row-major [N, row_pitch] block.  (The two kernel paths keep different stash formats.) */
+int hexgnn_stash_embed(const HexModelDesc* desc, int64_t N, int64_t B, int32_t flags, int64_t* offset_floats,
+                       int64_t* row_pitch);
+
 /* Self-test of the tcgen05 building blocks the fused kernels are made of: one CTA computes
  * D[128,N] = A[128,K] * B[K,N] (row-major device fp32, 3xTF32).  `modes` = a_mode*16 + b_mode selects the
  * operand staging (a_mode 0 tensor memory | 1 smem K-major SWIZZLE_NONE | 3 smem MN-major
