@@ -4,7 +4,7 @@
     torchrun --nnodes=1 --nproc-per-node N ... bench.py --gpus N --steps K --warmup W
 
 One "step" = one pass of the hot path over one replay batch of 256 11x11 Hex positions per GPU:
-device CSR build + fused forward (with stash) + fused backward + deterministic gradient reduction
+device CSR build + fused forward (with stash) + fused TD loss + fused backward + deterministic gradient reduction
 (+ NCCL all-reduce of the flat gradient when N > 1).  The optimizer is NOT part of the path
  and is not timed.  Prints ONE JSON line on rank 0.
 
@@ -229,8 +229,8 @@ def run_fused(args, rank, world, local_rank):
     loss_host = torch.empty(1, dtype=torch.float32).pin_memory()
 
     def td_loss(q, ptr):
-        td_est = q[action + ptr[:-1]]
-        return torch.mean(weight * (target - td_est) ** 2) * scale
+        # rainbow.py:301-312 (PER-weighted MSE) as ONE fused launch: loss, td errors and dloss/dq
+        return ops.td_loss(q, ptr, action, target, weight, "mse", scale)[0]
 
     def step_resident():
         model.zero_grad(set_to_none=True)

@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libhexgnn.so")
-SOURCES = ["api.cu", "csr_build.cu", "pack.cu", "sage_fwd_simt.cu", "sage_bwd_simt.cu", "tc_selftest.cu", "pack_tc.cu", "sage_fwd_tc.cu", "sage_bwd_tc.cu", "sage_dw_tc.cu"]
+SOURCES = ["api.cu", "csr_build.cu", "pack.cu", "sage_fwd_simt.cu", "sage_bwd_simt.cu", "tc_selftest.cu", "pack_tc.cu", "sage_fwd_tc.cu", "sage_bwd_tc.cu", "sage_dw_tc.cu", "td_loss.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "--compiler-options", "-fPIC", "-Xptxas", "-v"]
 
@@ -27,15 +27,18 @@ def _stale():
 
 
 def build(force=False, verbose=False):
-    """Compile every CUDA source into gnn_hex_b200/libhexgnn.so (objects in build/, in parallel)."""
+    """Compile every CUDA source into gnn_hex_b200/libhexgnn.so (objects in build/, in parallel).
+    HEXGNN_PHASES=1 in the environment compiles the per-phase cycle counters in (profiling builds only)."""
     if not force and not _stale():
         return LIB
+    flags = NVCC_FLAGS + (["-DHEXGNN_PHASES"] if os.environ.get("HEXGNN_PHASES") == "1" else [])
+    flags += ["-D" + m for m in os.environ.get("HEXGNN_DEFINES", "").split() if m]   # experiment switches
     objdir = os.path.join(HERE, "..", "build")
     os.makedirs(objdir, exist_ok=True)
     procs = []
     for s in SOURCES:
         obj = os.path.join(objdir, s.replace(".cu", ".o"))
-        cmd = [_nvcc()] + NVCC_FLAGS + ["-c", os.path.join(CSRC, s), "-o", obj]
+        cmd = [_nvcc()] + flags + ["-c", os.path.join(CSRC, s), "-o", obj]
         procs.append((s, obj, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
     objs = []
     log = []

@@ -184,11 +184,11 @@ int hexgnn_backward(const HexModelDesc* desc, const float* params, const float* 
     if (rc) return rc;
     const int grid = bwd_grid_ctas();
     rc = launch_backward_tc_chain(d, pm, params, x, N, E, B, csr, flags, d_nodes, d_value, stash, wsf + w.dz, d_embeds, tpv,
-                                  wsf + w.small_rec, grid, st);
+                                  wsf + w.small_rec, wsf + w.head_rec, grid, st);
     if (rc) return rc;
     rc = launch_backward_tc_dw(d, N, E, B, csr, stash, wsf + w.dz, wsf + w.big_rec, st);
     if (rc) return rc;
-    rc = launch_reduce_tc(d, wsf + w.small_rec, grid, wsf + w.big_rec, tc_dw_groups(d), wsf + w.sum, st);
+    rc = launch_reduce_tc(d, wsf + w.small_rec, grid, wsf + w.big_rec, tc_dw_groups(d), wsf + w.head_rec, B, wsf + w.sum, st);
     if (rc) return rc;
     return launch_unpack_grads(d, pm, x, wsf + w.sum, grad_params, st);
   }
@@ -205,6 +205,14 @@ int hexgnn_backward(const HexModelDesc* desc, const float* params, const float* 
   if (rc) return rc;
   CsrView cv = csr_view(const_cast<void*>(csr), N, E, B);
   return launch_reduce_grads(d, pm, x, partials, nparts, cv.ntiles, packed_sum, grad_params, st);
+}
+
+int hexgnn_td_loss(const float* q, const int64_t* ptr, const int64_t* action, const float* target, const float* weight,
+                   int64_t N, int64_t B, int32_t kind, float scale, float* loss, float* td_err, float* d_q, void* stream) {
+  if (!q || !ptr || !action || !target || !loss || N < 1 || B < 1) { set_error("td_loss: bad argument"); return HEXGNN_E_BADARG; }
+  if (kind != HEXGNN_LOSS_MSE && kind != HEXGNN_LOSS_SMOOTH_L1) { set_error("td_loss: unknown loss kind %d", kind); return HEXGNN_E_BADARG; }
+  if (B >= (1ll << 31)) { set_error("td_loss: B exceeds int32"); return HEXGNN_E_UNSUPPORTED; }
+  return launch_td_loss(q, ptr, action, target, weight, N, B, kind, scale, loss, td_err, d_q, (cudaStream_t)stream);
 }
 
 int hexgnn_stash_embed(const HexModelDesc* desc, int64_t N, int64_t B, int32_t flags, int64_t* offset_floats,

@@ -207,6 +207,8 @@ int launch_reduce_grads(const Dims& d, const ParamMap& pm, const float* x, const
 
 int launch_unpack_grads(const Dims& d, const ParamMap& pm, const float* x, const float* packed_sum, float* grad_params,
                         cudaStream_t st);
+int launch_td_loss(const float* q, const int64_t* ptr, const int64_t* action, const float* target, const float* weight,
+                   int64_t N, int64_t B, int kind, float scale, float* loss, float* td_err, float* d_q, cudaStream_t st);
 int launch_tc_selftest(const float* A, const float* B, float* D, int N, int K, int modes, cudaStream_t st);
 
 }  // namespace hexgnn

@@ -95,24 +95,41 @@ __global__ void csr_fill_kernel(CsrView v, const int64_t* __restrict__ ei, int E
                                 int tile_edges) {
   if (blockIdx.x == gridDim.x - 1) {
     // Greedy packing of whole graphs into tiles of <= tile_rows nodes, <= tile_edges edges,
-    // <= kMaxTileGraphs graphs.  Sequential by nature; B is a few thousand at most.
-    if (threadIdx.x == 0) {
-      int t = 0, rows = 0, edges = 0, cnt = 0, status = 0;
-      v.tile_g0[0] = 0;
-      for (int g = 0; g < B; ++g) {
-        const int r0 = v.gptr[g], r1 = v.gptr[g + 1];
-        const int n = r1 - r0;
-        const int ne = v.rowptr[r1] - v.rowptr[r0];
-        if (n > tile_rows || ne > tile_edges) status |= HEXGNN_ST_GRAPH_TOO_LARGE;
-        if (cnt > 0 && (rows + n > tile_rows || edges + ne > tile_edges || cnt >= kMaxTileGraphs)) {
-          v.tile_g0[++t] = g;
-          rows = edges = cnt = 0;
-        }
-        rows += n; edges += ne; ++cnt;
+    // <= kMaxTileGraphs graphs.  The scan is sequential by nature, so the block first stages the per-graph
+    // node / edge counts in shared memory (parallel, coalesced: the dependent global loads were the whole cost),
+    // then one thread walks them.
+    constexpr int kChunk = 1024;
+    __shared__ int n_s[kChunk], ne_s[kChunk];
+    __shared__ int st_s[5];   // t, rows, edges, cnt, status
+    if (threadIdx.x == 0) { st_s[0] = 0; st_s[1] = 0; st_s[2] = 0; st_s[3] = 0; st_s[4] = 0; v.tile_g0[0] = 0; }
+    for (int gb = 0; gb < B; gb += kChunk) {
+      const int gn = (B - gb) < kChunk ? (B - gb) : kChunk;
+      __syncthreads();
+      for (int i = threadIdx.x; i < gn; i += blockDim.x) {
+        const int r0 = v.gptr[gb + i], r1 = v.gptr[gb + i + 1];
+        n_s[i] = r1 - r0;
+        ne_s[i] = v.rowptr[r1] - v.rowptr[r0];
       }
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        int t = st_s[0], rows = st_s[1], edges = st_s[2], cnt = st_s[3], status = st_s[4];
+        for (int i = 0; i < gn; ++i) {
+          const int n = n_s[i], ne = ne_s[i];
+          if (n > tile_rows || ne > tile_edges) status |= HEXGNN_ST_GRAPH_TOO_LARGE;
+          if (cnt > 0 && (rows + n > tile_rows || edges + ne > tile_edges || cnt >= kMaxTileGraphs)) {
+            v.tile_g0[++t] = gb + i;
+            rows = edges = cnt = 0;
+          }
+          rows += n; edges += ne; ++cnt;
+        }
+        st_s[0] = t; st_s[1] = rows; st_s[2] = edges; st_s[3] = cnt; st_s[4] = status;
+      }
+    }
+    if (threadIdx.x == 0) {
+      int t = st_s[0];
       if (B > 0) v.tile_g0[++t] = B;
       *v.ntiles = t;
-      if (status) atomicOr(v.status, status);
+      if (st_s[4]) atomicOr(v.status, st_s[4]);
     }
     return;
   }

@@ -10,8 +10,6 @@ __global__ void pack_tc_kernel(Dims d, ParamMap pm, const float* __restrict__ pa
   const int head = (x[2] == 1.0f) ? 0 : 1;
   const int Hp = d.Hp, H = d.H, N2 = 2 * d.Hp;
   const int NQ = Hp / kTcKC;
-  const int64_t half_f = (int64_t)kTcKC * N2;     // floats per half
-  const int64_t layer_f = 2 * half_f * NQ;        // floats per layer image
   const int64_t per_layer = (int64_t)Hp * N2;     // logical elements per layer
   const int64_t total = per_layer * (d.Lt - 1);
   const int64_t nth = (int64_t)gridDim.x * blockDim.x;
@@ -27,11 +25,13 @@ __global__ void pack_tc_kernel(Dims d, ParamMap pm, const float* __restrict__ pa
     float hi, lo;
     tc::split_tf32(val, hi, lo);
     {
-      const int q = k / kTcKC, kq = k % kTcKC;
-      const int64_t off = (int64_t)(s - 1) * layer_f + (int64_t)q * 2 * half_f + (int64_t)(kq / 4) * (N2 * 4) +
+      // forward: stage q8 = B[n][k in 8-chunk q8], n in [0,2Hp) (lin_l rows then lin_r rows), hi half then lo half
+      const int64_t halfF = (int64_t)kTcKF * N2;
+      const int q8 = k / kTcKF, kq = k % kTcKF;
+      const int64_t off = ((int64_t)(s - 1) * (Hp / kTcKF) + q8) * 2 * halfF + (int64_t)(kq / 4) * (N2 * 4) +
                           (n / 8) * 32 + (n % 8) * 4 + (kq % 4);
       pv.wimg[off] = hi;
-      pv.wimg[off + half_f] = lo;
+      pv.wimg[off + halfF] = lo;
     }
     if (with_transpose) {
       // backward: dH[i][k] = sum_c dZ_which[i][c] * W_which[c][k]  =>  B[n = k][kk = c], which 0 = lin_r, 1 = lin_l
@@ -64,12 +64,50 @@ int launch_pack_tc(const Dims& d, const ParamMap& pm, const float* params, const
 
 // Fixed-order reduction of the tcgen05 backward's partial records into one packed record (GradLayout):
 //   gw and gb[s>=1]  <- the G group records of sage_dw_tc_kernel   (big_rec [G][gl.g0])
+//   gv0              <- sum over graphs (in graph order) of dt_g (x) pooled_g from the head records
 //   everything else  <- the per-CTA records of sage_bwd_tc_kernel  (small_rec [nsmall][gl.total - gl.gb])
-__global__ void reduce_tc_kernel(GradLayout gl, int Hp, const float* __restrict__ small_rec, int nsmall,
-                                 const float* __restrict__ big_rec, int G, float* __restrict__ out) {
-  const int64_t nth = (int64_t)gridDim.x * blockDim.x;
+__global__ void __launch_bounds__(256) reduce_tc_kernel(GradLayout gl, int Hp, int H, int H2,
+                                                        const float* __restrict__ small_rec, int nsmall,
+                                                        const float* __restrict__ big_rec, int G,
+                                                        const float* __restrict__ head_rec, int hrec_n, int B, int nmain,
+                                                        float* __restrict__ out) {
+  if ((int)blockIdx.x >= nmain) {
+    // gv0[k][q] = sum_g dt_g[k] * pooled_g[q]: block = 128 q x 8 k, the two thread halves take the two halves of
+    // the graph range (sequential inside a half, halves combined in a fixed order: deterministic).
+    __shared__ float part[8][128];
+    const int H2p = (H2 + 3) & ~3, Q = 4 * H;
+    const int nqb = (Q + 127) / 128;
+    const int bid = blockIdx.x - nmain, qb = bid % nqb, kb = bid / nqb;
+    const int q = qb * 128 + (threadIdx.x & 127), half = threadIdx.x >> 7, k0 = kb * 8;
+    const int Bh = (B + 1) / 2;
+    const int ga = half * Bh, gb = (ga + Bh < B) ? ga + Bh : B;
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    if (q < Q) {
+      const float* hr = head_rec + (int64_t)ga * hrec_n;
+      for (int g = ga; g < gb; ++g, hr += hrec_n) {
+        const float pv = hr[H2p + q];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = fmaf(k0 + j < H2 ? hr[k0 + j] : 0.f, pv, acc[j]);
+      }
+    }
+    if (half == 1) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) part[j][threadIdx.x & 127] = acc[j];
+    }
+    __syncthreads();
+    if (half == 0 && q < Q) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (k0 + j < H2) out[gl.gv0 + (int64_t)(k0 + j) * Q + q] = acc[j] + part[j][threadIdx.x];
+    }
+    return;
+  }
+  const int64_t nth = (int64_t)nmain * blockDim.x;
   const int64_t recn = gl.total - gl.gb;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < gl.total; i += nth) {
+    if (i >= gl.gv0 && i < gl.gv0b) continue;   // written by the gv0 blocks
     float acc = 0.f;
     const bool from_big = i < gl.gb || (i >= gl.gb + Hp && i < gl.g0);
     if (from_big) {
@@ -81,13 +119,15 @@ __global__ void reduce_tc_kernel(GradLayout gl, int Hp, const float* __restrict_
   }
 }
 
-int launch_reduce_tc(const Dims& d, const float* small_rec, int nsmall, const float* big_rec, int G, float* packed_sum,
-                     cudaStream_t st) {
+int launch_reduce_tc(const Dims& d, const float* small_rec, int nsmall, const float* big_rec, int G,
+                     const float* head_rec, int64_t B, float* packed_sum, cudaStream_t st) {
   GradLayout gl;
   grad_layout(d, &gl);
   int blocks = (int)((gl.total + 255) / 256);
   if (blocks > 1184) blocks = 1184;
-  reduce_tc_kernel<<<blocks, 256, 0, st>>>(gl, d.Hp, small_rec, nsmall, big_rec, G, packed_sum);
+  const int gv0_blocks = ((4 * d.H + 127) / 128) * ((d.H2 + 7) / 8);
+  reduce_tc_kernel<<<blocks + gv0_blocks, 256, 0, st>>>(gl, d.Hp, d.H, d.H2, small_rec, nsmall, big_rec, G, head_rec,
+                                                        tc_head_rec_floats(d), (int)B, blocks, packed_sum);
   HEX_CUDA_CHECK(cudaGetLastError());
   return HEXGNN_OK;
 }

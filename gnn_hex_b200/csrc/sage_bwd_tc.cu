@@ -9,14 +9,19 @@
 // and [dZl | dpre] is written to the dZ stash (RM32 images) for part B (sage_dw_tc.cu), which contracts it
 // with h_s over ALL rows of ALL tiles: dW_s = h_s^T [dZl | dpre] (the bias gradient rides on the ones-channel).
 // This kernel also differentiates the dueling head and layer 0 (2 -> H) on the CUDA cores; their parameter
-// gradients go to a small per-CTA record, reduced in fixed order by reduce_tc_kernel (pack_tc.cu).
-// max/min pooling route their gradient to the FIRST row attaining the extremum (torch_scatter CPU semantics).
+// gradients accumulate in shared memory and leave as one small per-CTA record, except the value MLP's first
+// weight (H/2 x 4H): each graph emits [dt | pooled] and reduce_tc_kernel (pack_tc.cu) sums the outer products in
+// graph order.  max/min pooling route their gradient to the FIRST row attaining the extremum (torch_scatter CPU
+// semantics).  The ReLU masks come from the forward's sign-mask words (sage_tc.cuh): the chain never reads the
+// activation images except the last layer's (the head input).
+// Epilogue mappings: E1/E3 thread = (node row, column slice) for TMEM traffic; E2 (the CSR gather) warp = row,
+// lane = 4 channels, so every shared-memory access is a contiguous row.
 #include "sage_tc.cuh"
 
 namespace hexgnn {
 using namespace tc;
 
-constexpr int kBwdStages = 6;
+constexpr int kBwdStages = 5;
 
 struct BwdTcArgs {
   Dims d;
@@ -33,7 +38,8 @@ struct BwdTcArgs {
   float* dz;              // dZ stash written here: [Lt-1][B][dz_blocks * 16 KB]
   float* d_embeds;
   TcPackView pv;
-  float* small_rec;       // [gridDim.x][gl.total - gl.gb]
+  float* small_rec;       // [gridDim.x][gl.total - gl.gb]  (the gv0 range stays unwritten)
+  float* head_rec;        // [B][tc_head_rec_floats]: per graph [dt (H2, padded) | pooled (4H)]
 };
 
 template <int NJ>
@@ -45,15 +51,20 @@ struct BwdTcSmem {
   static constexpr int stage_bytes = 2 * half_bytes;
   static constexpr int off_ring = 0;
   static constexpr int off_dump = off_ring + kBwdStages * stage_bytes;           // float [128][P]
-  static constexpr int off_rows = off_dump + kTcRows * P * 4;                    // float [7][128]
+  static constexpr int off_agg = off_dump + (kTcRows + 1) * P * 4;               // float [128][P]  (dump row 128 = zeros)
+  static constexpr int off_rows = off_agg + kTcRows * P * 4;                     // float [7][128]
   static constexpr int off_pool = off_rows + 7 * kTcRows * 4;                    // float [4*Hp]
   static constexpr int off_hid = off_pool + 4 * Hp * 4;                          // float [Hp]
   static constexpr int off_arg = off_hid + Hp * 4;                               // int [2*Hp]
-  static constexpr int off_misc = off_arg + 2 * Hp * 4;                          // float [16]
+  static constexpr int off_part = off_agg;                                       // float [4][6][Hp] row-part partials
+                                                                                 // (head / layer 0 only: aliases agg)
+  static constexpr int off_acc = off_arg + 2 * Hp * 4;                           // float [8*Hp + 16] CTA accumulators
+  static constexpr int off_misc = off_acc + (8 * Hp + 16) * 4;                   // float [16]
   static constexpr int off_rowptr = off_misc + 64;                               // int [128+4]
   static constexpr int off_gp = off_rowptr + (kTcRows + 4) * 4;                  // int [64+4]
   static constexpr int off_col = off_gp + (kMaxTileGraphs + 4) * 4;              // u16 [ECAP]
-  static constexpr int off_bar = off_col + ECAP * 2;                             // u64 [2*stages + 3], u32 slot
+  static constexpr int off_gtab = (off_col + ECAP * 2 + 15) & ~15;               // gather table (sage_tc.cuh)
+  static constexpr int off_bar = off_gtab + gather_tab_bytes();                  // u64 [2*stages + 3], u32 slot
   static constexpr int bytes = off_bar + (2 * kBwdStages + 3) * 8 + 16;
 };
 
@@ -88,10 +99,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
   constexpr int NG = 2 * NJ;
   constexpr int NQ = Hp / kTcKC;
   constexpr int MAXG = (NG + kTcSlices - 1) / kTcSlices;
+  constexpr int NV = Hp / 4, PV = P / 4;
   constexpr uint32_t TM_HI = 0, TM_LO = Hp, TM_D = 2 * Hp;
   constexpr uint32_t TM_COLS = (3 * Hp <= 64) ? 64 : (3 * Hp <= 128) ? 128 : (3 * Hp <= 256) ? 256 : 512;
   extern __shared__ __align__(128) uint8_t smem[];
   float* dump = (float*)(smem + S::off_dump);
+  float* agg = (float*)(smem + S::off_agg);
+  float* partb = (float*)(smem + S::off_part);
+  float* accs = (float*)(smem + S::off_acc);
   float* rows = (float*)(smem + S::off_rows);
   float *inv_s = rows, *x0_s = rows + 128, *x1_s = rows + 256, *m0_s = rows + 384, *m1_s = rows + 512,
         *adv_s = rows + 640, *th_s = rows + 768;
@@ -102,6 +117,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
   int* rowptr_s = (int*)(smem + S::off_rowptr);
   int* gp_s = (int*)(smem + S::off_gp);
   unsigned short* col_s = (unsigned short*)(smem + S::off_col);
+  const GatherTab gtab = gather_tab_view(smem + S::off_gtab);
   uint64_t* bar_full = (uint64_t*)(smem + S::off_bar);
   uint64_t* bar_empty = bar_full + kBwdStages;
   uint64_t* bar_a = bar_empty + kBwdStages;
@@ -112,7 +128,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const int H = a.d.H, H2 = a.d.H2, Lt = a.d.Lt;
   const int ntiles = *a.csr.ntiles;
-  const long long t_kernel0 = clock64();
+  const long long t_kernel0 = PH_NOW();
   long long ph0 = 0, ph1 = 0, ph2 = 0, ph3 = 0, ph4 = 0, ph5 = 0, ntl = 0;
 
   if (tid == 0) {
@@ -191,7 +207,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
     const float* Pm = a.params;
     const int64_t recn = a.gl.total - a.gl.gb;
     float* rec = a.small_rec + (int64_t)blockIdx.x * recn - a.gl.gb;   // index with GradLayout offsets (>= gl.gb)
-    for (int64_t i = a.gl.gb + tid; i < a.gl.total; i += kTcEpiThreads) rec[i] = 0.f;
+    // CTA-lifetime accumulators of the small parameter gradients (every element has ONE owner thread)
+    constexpr int A_GB0 = 0, A_G0 = Hp, A_GLIN = 5 * Hp, A_GLINB = 6 * Hp, A_GV0B = 6 * Hp + 4, A_GV1 = 7 * Hp + 4,
+                  A_GV1B = 8 * Hp + 4, A_N = 8 * Hp + 16;
+    for (int i = tid; i < A_N; i += kTcEpiThreads) accs[i] = 0.f;
+    for (int i = tid; i < P; i += kTcEpiThreads) dump[kTcRows * P + i] = 0.f;   // the gather's zero row
     const float* wa = Pm + a.pm.lin_w[head];
     const float ba = Pm[a.pm.lin_b[head]];
     const float* w0 = Pm + a.pm.v0_w[head];
@@ -200,15 +220,20 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
     const float b1 = Pm[a.pm.v1_b[head]];
     const size_t act_img = (size_t)tc_act_blocks(Hp) * kImgBlockBytes;
     const size_t dz_img = (size_t)tc_dz_blocks(Hp) * kImgBlockBytes;
+    const uint32_t* mask_base = (const uint32_t*)(a.stash + tc_stash_mask_off_floats(a.d, a.N, a.B));
+    const size_t mask_layer = (size_t)a.B * kTcSlices * kTcRows;
+    const int hrec_n = tc_head_rec_floats(a.d), H2p = (H2 + 3) & ~3;
+    const int part = tid >> 7, pc = tid & 127;      // row quarter / channel of the column-parallel loops
     uint32_t nr = 0, nd = 0;
     for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
       const TileDimsB td = tile_dims_b(a.csr, t, S::ECAP);
       const int n = td.n, r0 = td.r0, g0 = td.g0, g1 = td.g1;
       epi_bar_b();
-      long long tq = clock64();
+      long long tq = PH_NOW();
       ++ntl;
       if (!td.ok) {
-        if (tid == 0) { rec[a.gl.gb] = __int_as_float(0x7fc00000); atomicOr(a.csr.status, HEXGNN_ST_GRAPH_TOO_LARGE); }
+        if (tid == 0) { accs[A_GB0] = __int_as_float(0x7fc00000); atomicOr(a.csr.status, HEXGNN_ST_GRAPH_TOO_LARGE); }
+        for (int i = tid; i < (g1 - g0) * hrec_n; i += kTcEpiThreads) a.head_rec[(int64_t)g0 * hrec_n + i] = 0.f;
         continue;
       }
       // ---- tile CSR + features -> shared ------------------------------------------------------------
@@ -227,23 +252,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
           x0_s[i] = v0; x1_s[i] = v1;
         }
         if (bad) atomicOr(a.csr.status, bad);
-        epi_bar_b();
-        for (int i = tid; i < kTcRows; i += kTcEpiThreads) {
-          const int b = rowptr_s[i], e = rowptr_s[i + 1];
-          const int deg = e - b;
-          const float inv = 1.0f / (float)(deg > 0 ? deg : 1);
-          float s0 = 0.f, s1 = 0.f;
-          for (int p = b; p < e; ++p) { const int j = col_s[p]; s0 += x0_s[j]; s1 += x1_s[j]; }
-          inv_s[i] = inv; m0_s[i] = s0 * inv; m1_s[i] = s1 * inv;
-        }
-        epi_bar_b();
       }
       const bool live = row < n;
       const int n32 = (n + 31) & ~31;
-      const float inv = inv_s[row];
-      const int eb = rowptr_s[row], ee = rowptr_s[row + 1];
       const char* act_t = (const char*)a.stash + (size_t)t * act_img;         // + layer * B * act_img
       char* dz_t = (char*)a.dz + (size_t)t * dz_img;                           // + (s-1) * B * dz_img
+      const uint32_t* mask_t = mask_base + ((size_t)t * kTcSlices + slice) * kTcRows + row;
       // ---- g = h_Lt -> dump (row major) -----------------------------------------------------------------
       {
         const char* img = act_t + (size_t)(Lt - 1) * a.B * act_img;
@@ -255,19 +269,41 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
         }
       }
       epi_bar_b();
-      if (tid < kTcRows && tid < n) {
+      gather_build<NJ>(gtab, rowptr_s, col_s, n, tid);
+      for (int i = tid; i < kTcRows; i += kTcEpiThreads) {
+        const int b = rowptr_s[i], e = rowptr_s[i + 1];
+        const int deg = e - b;
+        const float inv = 1.0f / (float)(deg > 0 ? deg : 1);
+        float s0 = 0.f, s1 = 0.f;
+        for (int p = b; p < e; ++p) { const int j = col_s[p]; s0 += x0_s[j]; s1 += x1_s[j]; }
+        inv_s[i] = inv; m0_s[i] = s0 * inv; m1_s[i] = s1 * inv;
+      }
+      // th_i = tanh(w_a . g_i + b_a): warp = row, lane = 4 channels
+      for (int r = wid; r < n; r += kTcEpiWarps) {
         float u = 0.f;
-        const float* gr = dump + tid * P;
-        for (int c = 0; c < H; ++c) u = fmaf(wa[c], gr[c], u);
-        th_s[tid] = tanhf(u + ba);
+        if (lane < NV) {
+          const float4 v = ((const float4*)dump)[r * PV + lane];
+          const int c = lane * 4;
+          if (c < H) u = fmaf(wa[c], v.x, u);
+          if (c + 1 < H) u = fmaf(wa[c + 1], v.y, u);
+          if (c + 2 < H) u = fmaf(wa[c + 2], v.z, u);
+          if (c + 3 < H) u = fmaf(wa[c + 3], v.w, u);
+        }
+        u = warp_sum_b(u);
+        if (lane == 0) th_s[r] = tanhf(u + ba);
       }
       epi_bar_b();
+      const float inv = inv_s[row];
       // ---- head backward per graph: dump rows become dL/dg in place -----------------------------------------
       for (int g = 0; g < g1 - g0; ++g) {
         const int rs = gp_s[g], re = gp_s[g + 1];
         const int ng = re - rs;
-        if (ng <= 0) continue;
+        float* hrec = a.head_rec + (int64_t)(g0 + g) * hrec_n;
         const bool adv_only = (a.flags & HEXGNN_ADV_ONLY) != 0;
+        if (ng <= 0 || adv_only) {
+          for (int i = tid; i < hrec_n; i += kTcEpiThreads) hrec[i] = 0.f;
+          if (ng <= 0) continue;
+        }
         float sumdq = 0.f;
         if (!adv_only) {
           if (wid == 0) {
@@ -275,18 +311,6 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
             for (int i = rs + lane; i < re; i += 32) u += a.d_nodes[r0 + i];
             u = warp_sum_b(u);
             if (lane == 0) misc[0] = u;
-          }
-          if (tid < H) {
-            float sum = 0.f, mx = -INFINITY, mn = INFINITY;
-            int amx = rs, amn = rs;
-            for (int i = rs; i < re; ++i) {
-              const float v = dump[i * P + tid];
-              sum += v;
-              if (v > mx) { mx = v; amx = i; }
-              if (v < mn) { mn = v; amn = i; }
-            }
-            pool[tid] = sum; pool[H + tid] = mx; pool[2 * H + tid] = mn; pool[3 * H + tid] = sum / (float)ng;
-            arg_s[tid] = amx; arg_s[Hp + tid] = amn;
           }
           epi_bar_b();
           sumdq = misc[0];
@@ -296,6 +320,46 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
           const float dn = a.d_nodes[r0 + i];
           adv_s[i] = (adv_only ? dn : dn - sumdq / (float)ng) * 2.0f * (1.0f - th * th);
         }
+        epi_bar_b();
+        // column-parallel pass over the graph's rows, 4 row quarters: pools, arg rows, d head.linear.weight
+        if (pc < H) {
+          const int chunk = (ng + 3) >> 2;
+          const int ia = rs + part * chunk, ib = (ia + chunk < re) ? ia + chunk : re;
+          float sum = 0.f, mx = -INFINITY, mn = INFINITY, gl_ = 0.f;
+          int amx = rs, amn = rs;
+          for (int i = ia; i < ib; ++i) {
+            const float v = dump[i * P + pc];
+            sum += v;
+            gl_ = fmaf(adv_s[i], v, gl_);
+            if (v > mx) { mx = v; amx = i; }
+            if (v < mn) { mn = v; amn = i; }
+          }
+          float* pp = partb + (part * 6) * Hp + pc;
+          pp[0] = sum; pp[Hp] = mx; pp[2 * Hp] = mn; pp[3 * Hp] = gl_;
+          pp[4 * Hp] = __int_as_float(amx); pp[5 * Hp] = __int_as_float(amn);
+        }
+        epi_bar_b();
+        if (tid < H) {
+          float sum = 0.f, mx = -INFINITY, mn = INFINITY, gl_ = 0.f;
+          int amx = rs, amn = rs;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const float* pp = partb + (q * 6) * Hp + tid;
+            sum += pp[0];
+            gl_ += pp[3 * Hp];
+            if (pp[Hp] > mx) { mx = pp[Hp]; amx = __float_as_int(pp[4 * Hp]); }
+            if (pp[2 * Hp] < mn) { mn = pp[2 * Hp]; amn = __float_as_int(pp[5 * Hp]); }
+          }
+          pool[tid] = sum; pool[H + tid] = mx; pool[2 * H + tid] = mn; pool[3 * H + tid] = sum / (float)ng;
+          arg_s[tid] = amx; arg_s[Hp + tid] = amn;
+          accs[A_GLIN + tid] += gl_;
+        } else if (wid == kTcEpiWarps - 1) {
+          float u = 0.f;
+          for (int i = rs + lane; i < re; i += 32) u += adv_s[i];
+          u = warp_sum_b(u);
+          if (lane == 0) accs[A_GLINB] += u;
+        }
+        epi_bar_b();
         if (!adv_only) {
           for (int k = wid; k < H2; k += kTcEpiWarps) {
             float u = 0.f;
@@ -304,19 +368,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
             u = warp_sum_b(u);
             if (lane == 0) hid[k] = fmaxf(u + b0[k], 0.f);
           }
-        }
-        epi_bar_b();
-        // head.linear grads need g (still in dump) and du
-        if (tid < H) {
-          float u = 0.f;
-          for (int i = rs; i < re; ++i) u = fmaf(adv_s[i], dump[i * P + tid], u);
-          rec[a.gl.glin + tid] += u;
-        } else if (tid == H) {
-          float u = 0.f;
-          for (int i = rs; i < re; ++i) u += adv_s[i];
-          rec[a.gl.glinb] += u;
-        }
-        if (!adv_only) {
+          epi_bar_b();
           if (wid == kTcEpiWarps - 1) {
             float u = 0.f;
             for (int k = lane; k < H2; k += 32) u = fmaf(w1[k], hid[k], u);
@@ -331,26 +383,24 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
           const float ds = misc[1];
           if (tid < H2) {
             const float hk = hid[tid];
-            rec[a.gl.gv1 + tid] += ds * hk;
+            accs[A_GV1 + tid] += ds * hk;
             const float dt = hk > 0.f ? ds * w1[tid] : 0.f;
-            rec[a.gl.gv0b + tid] += dt;
+            accs[A_GV0B + tid] += dt;
             hid[tid] = dt;
           }
-          if (tid == 0) rec[a.gl.gv1b] += ds;
+          if (tid == 0) accs[A_GV1B] += ds;
           epi_bar_b();
-          for (int idx = tid; idx < H2 * 4 * H; idx += kTcEpiThreads) {
-            const int k = idx / (4 * H), q = idx - k * 4 * H;
-            rec[a.gl.gv0 + idx] += hid[k] * pool[q];
-          }
-          epi_bar_b();  // pool (P) fully consumed before it becomes dP
+          // graph record [dt | pooled]: the reduction kernel sums dt (x) pooled over graphs in graph order
+          for (int i = tid; i < hrec_n; i += kTcEpiThreads)
+            hrec[i] = i < H2p ? (i < H2 ? hid[i] : 0.f) : (i - H2p < 4 * H ? pool[i - H2p] : 0.f);
           float dp = 0.f;
           if (tid < 4 * H) {
             for (int k = 0; k < H2; ++k) dp = fmaf(w0[(int64_t)k * 4 * H + tid], hid[k], dp);
           }
-          epi_bar_b();
+          epi_bar_b();  // pooled values fully consumed before they become their own gradient
           if (tid < 4 * H) pool[tid] = dp;
+          epi_bar_b();
         }
-        epi_bar_b();
         for (int idx = tid; idx < ng * Hp; idx += kTcEpiThreads) {
           const int i = rs + idx / Hp, c = idx % Hp;
           float v = 0.f;
@@ -366,11 +416,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
         }
         epi_bar_b();
       }
-      ph4 += clock64() - tq;
+      PH_ADD(ph4, tq);
       // ---- SAGE layers Lt-1 .. 1 on the tensor cores ---------------------------------------------------------
       for (int s = Lt - 1; s >= 1; --s) {
         const bool first = (s == Lt - 1);
-        tq = clock64();
+        tq = PH_NOW();
+        const uint32_t mw = mask_t[(size_t)s * mask_layer];   // signs of h_{s+1}; in flight during the wait below
         float dh[MAXG][8];
         if (first) {
 #pragma unroll
@@ -383,13 +434,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
               dh[gi][4] = v1.x; dh[gi][5] = v1.y; dh[gi][6] = v1.z; dh[gi][7] = v1.w;
             }
           }
-          epi_bar_b();   // everyone holds its dH before the dump is reused
         } else {
           mbar_wait(bar_d, nd & 1);   // dH_{s+1} complete in TMEM
           ++nd;
           tc_fence_after();
-          ph0 += clock64() - tq;
-          tq = clock64();
+          PH_ADD(ph0, tq);
+          tq = PH_NOW();
 #pragma unroll
           for (int gi = 0; gi < MAXG; ++gi) {
             const int g = slice + gi * kTcSlices;
@@ -399,7 +449,6 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
         }
         // E1: ReLU mask, dpre -> TMEM (A of dpre*W_r), dump (pre-scaled by 1/deg for the gather), dZ stash
         {
-          const char* himg = act_t + (size_t)s * a.B * act_img;          // h_{s+1}
           char* zimg = dz_t + (size_t)(s - 1) * a.B * dz_img;
 #pragma unroll
           for (int gi = 0; gi < MAXG; ++gi) {
@@ -410,16 +459,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
                 de[0] = make_float4(dh[gi][0], dh[gi][1], dh[gi][2], dh[gi][3]);
                 de[1] = make_float4(dh[gi][4], dh[gi][5], dh[gi][6], dh[gi][7]);
               }
-              float hv[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-              if (live) {
-                const float4* src = (const float4*)(himg + rm32_granule_off(g, row));
-                const float4 v0 = src[0], v1 = src[1];
-                hv[0] = v0.x; hv[1] = v0.y; hv[2] = v0.z; hv[3] = v0.w; hv[4] = v1.x; hv[5] = v1.y; hv[6] = v1.z; hv[7] = v1.w;
-              }
               float hi[8], lo[8], sc[8];
 #pragma unroll
               for (int u = 0; u < 8; ++u) {
-                const float r = hv[u] > 0.f ? dh[gi][u] : 0.f;
+                const float r = ((mw >> (gi * 8 + u)) & 1u) ? dh[gi][u] : 0.f;
                 dh[gi][u] = r;
                 sc[u] = r * inv;
                 split_tf32(r, hi[u], lo[u]);
@@ -441,69 +484,55 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
           mbar_arrive(bar_a);        // -> MMA: dH_s = dpre * W_r
         }
         epi_bar_b();                 // dump (dpre / deg) complete
-        ph1 += clock64() - tq;
-        tq = clock64();
-        // E2: dZl_j = sum_{i in N(j)} dpre_i / deg(i)
-        float acc[MAXG][8];
-#pragma unroll
-        for (int gi = 0; gi < MAXG; ++gi)
-#pragma unroll
-          for (int u = 0; u < 8; ++u) acc[gi][u] = 0.f;
-        {
-          int j = eb < ee ? (int)col_s[eb] : 0;
-          for (int p = eb; p < ee; ++p) {
-            const int jn = (p + 1 < ee) ? (int)col_s[p + 1] : 0;
-            const float* src = dump + j * P + slice * 8;
-#pragma unroll
-            for (int gi = 0; gi < MAXG; ++gi) {
-              if (slice + gi * kTcSlices < NG) {
-                const float4 v0 = *(const float4*)(src + gi * kTcSlices * 8);
-                const float4 v1 = *(const float4*)(src + gi * kTcSlices * 8 + 4);
-                acc[gi][0] += v0.x; acc[gi][1] += v0.y; acc[gi][2] += v0.z; acc[gi][3] += v0.w;
-                acc[gi][4] += v1.x; acc[gi][5] += v1.y; acc[gi][6] += v1.z; acc[gi][7] += v1.w;
-              }
-            }
-            j = jn;
-          }
-        }
+        PH_ADD(ph1, tq);
+        tq = PH_NOW();
+        // E2: dZl_j = sum_{i in N(j)} dpre_i / deg(i) (tile_gather, sage_tc.cuh); runs under the dpre * W_r MMAs.
+        tile_gather<NJ>(gtab, dump, agg, n, wid, lane);
+        epi_bar_b();
+        PH_ADD(ph2, tq);
+        tq = PH_NOW();
+        // E3: dZl -> dZ stash, then (once dpre * W_r has read the A columns) -> TMEM as the next A operand
         {
           char* zimg = dz_t + (size_t)(s - 1) * a.B * dz_img;
-          if (row < n32) {
+          float acc[MAXG][8];
 #pragma unroll
-            for (int gi = 0; gi < MAXG; ++gi) {
-              const int g = slice + gi * kTcSlices;
-              if (g < NG) {
+          for (int gi = 0; gi < MAXG; ++gi) {
+            const int g = slice + gi * kTcSlices;
+            if (g < NG) {
+              float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
+              if (live) { const float4* src = (const float4*)(agg + row * P + g * 8); v0 = src[0]; v1 = src[1]; }
+              acc[gi][0] = v0.x; acc[gi][1] = v0.y; acc[gi][2] = v0.z; acc[gi][3] = v0.w;
+              acc[gi][4] = v1.x; acc[gi][5] = v1.y; acc[gi][6] = v1.z; acc[gi][7] = v1.w;
+              if (row < n32) {
                 float4* dst = (float4*)(zimg + rm32_granule_off(g, row));
-                dst[0] = make_float4(acc[gi][0], acc[gi][1], acc[gi][2], acc[gi][3]);
-                dst[1] = make_float4(acc[gi][4], acc[gi][5], acc[gi][6], acc[gi][7]);
+                dst[0] = v0; dst[1] = v1;
               }
             }
           }
-        }
-        ph2 += clock64() - tq;
-        tq = clock64();
-        mbar_wait(bar_r, nr & 1);      // dpre * W_r has finished reading the A columns
-        ++nr;
-        tc_fence_after();
+          mbar_wait(bar_r, nr & 1);      // dpre * W_r has finished reading the A columns
+          ++nr;
+          tc_fence_after();
 #pragma unroll
-        for (int gi = 0; gi < MAXG; ++gi) {
-          const int g = slice + gi * kTcSlices;
-          if (g < NG) {
-            float hi[8], lo[8];
+          for (int gi = 0; gi < MAXG; ++gi) {
+            const int g = slice + gi * kTcSlices;
+            if (g < NG) {
+              float hi[8], lo[8];
 #pragma unroll
-            for (int u = 0; u < 8; ++u) split_tf32(acc[gi][u], hi[u], lo[u]);
-            tmem_st8(trow + TM_HI + g * 8, hi);
-            tmem_st8(trow + TM_LO + g * 8, lo);
+              for (int u = 0; u < 8; ++u) split_tf32(acc[gi][u], hi[u], lo[u]);
+              tmem_st8(trow + TM_HI + g * 8, hi);
+              tmem_st8(trow + TM_LO + g * 8, lo);
+            }
           }
+          tmem_wait_st();
+          tc_fence_before();
+          mbar_arrive(bar_a);            // -> MMA: dH_s += dZl * W_l
         }
-        tmem_wait_st();
-        tc_fence_before();
-        mbar_arrive(bar_a);            // -> MMA: dH_s += dZl * W_l
-        ph3 += clock64() - tq;
+        PH_ADD(ph3, tq);
       }
       // ---- layer 0 (2 -> H): dpre_0 = dH_1 (.) (h_1 > 0); rank-2 weight gradients on the CUDA cores -------------------
-      tq = clock64();
+      tq = PH_NOW();
       {
+        const uint32_t mw = mask_t[0];
         float dh[MAXG][8];
         if (Lt == 1) {
 #pragma unroll
@@ -516,7 +545,6 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
               dh[gi][4] = v1.x; dh[gi][5] = v1.y; dh[gi][6] = v1.z; dh[gi][7] = v1.w;
             }
           }
-          epi_bar_b();
         } else {
           mbar_wait(bar_d, nd & 1);
           ++nd;
@@ -528,7 +556,6 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
           }
           tmem_wait_ld();
         }
-        const char* himg = act_t;   // h_1
 #pragma unroll
         for (int gi = 0; gi < MAXG; ++gi) {
           const int g = slice + gi * kTcSlices;
@@ -538,43 +565,50 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
               de[0] = make_float4(dh[gi][0], dh[gi][1], dh[gi][2], dh[gi][3]);
               de[1] = make_float4(dh[gi][4], dh[gi][5], dh[gi][6], dh[gi][7]);
             }
-            float hv[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-            if (live) {
-              const float4* src = (const float4*)(himg + rm32_granule_off(g, row));
-              const float4 v0 = src[0], v1 = src[1];
-              hv[0] = v0.x; hv[1] = v0.y; hv[2] = v0.z; hv[3] = v0.w; hv[4] = v1.x; hv[5] = v1.y; hv[6] = v1.z; hv[7] = v1.w;
-            }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) dh[gi][u] = ((mw >> (gi * 8 + u)) & 1u) ? dh[gi][u] : 0.f;
             float4* dd = (float4*)(dump + row * P + g * 8);
-            dd[0] = make_float4(hv[0] > 0.f ? dh[gi][0] : 0.f, hv[1] > 0.f ? dh[gi][1] : 0.f, hv[2] > 0.f ? dh[gi][2] : 0.f,
-                                hv[3] > 0.f ? dh[gi][3] : 0.f);
-            dd[1] = make_float4(hv[4] > 0.f ? dh[gi][4] : 0.f, hv[5] > 0.f ? dh[gi][5] : 0.f, hv[6] > 0.f ? dh[gi][6] : 0.f,
-                                hv[7] > 0.f ? dh[gi][7] : 0.f);
+            dd[0] = make_float4(dh[gi][0], dh[gi][1], dh[gi][2], dh[gi][3]);
+            dd[1] = make_float4(dh[gi][4], dh[gi][5], dh[gi][6], dh[gi][7]);
           }
         }
         tc_fence_before();
         epi_bar_b();
-        if (tid < Hp) {
+        // column-parallel over 4 row quarters, combined in quarter order (fixed summation order)
+        if (pc < Hp) {
+          const int chunk = (n + 3) >> 2;
+          const int ia = part * chunk, ib = (ia + chunk < n) ? ia + chunk : n;
           float ub = 0.f, u0 = 0.f, u1 = 0.f, u2 = 0.f, u3 = 0.f;
-          for (int i = 0; i < n; ++i) {
-            const float dpv = dump[i * P + tid];
+          for (int i = ia; i < ib; ++i) {
+            const float dpv = dump[i * P + pc];
             ub += dpv;
             u0 = fmaf(dpv, m0_s[i], u0);
             u1 = fmaf(dpv, m1_s[i], u1);
             u2 = fmaf(dpv, x0_s[i], u2);
             u3 = fmaf(dpv, x1_s[i], u3);
           }
-          rec[a.gl.gb + tid] += ub;
-          rec[a.gl.g0 + 0 * Hp + tid] += u0;
-          rec[a.gl.g0 + 1 * Hp + tid] += u1;
-          rec[a.gl.g0 + 2 * Hp + tid] += u2;
-          rec[a.gl.g0 + 3 * Hp + tid] += u3;
+          float* pp = partb + (part * 6) * Hp + pc;
+          pp[0] = ub; pp[Hp] = u0; pp[2 * Hp] = u1; pp[3 * Hp] = u2; pp[4 * Hp] = u3;
+        }
+        epi_bar_b();
+        for (int i = tid; i < 5 * Hp; i += kTcEpiThreads) {   // i = k*Hp + c: k 0 -> gb0, 1..4 -> g0 rows
+          float u = 0.f;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) u += partb[(q * 6) * Hp + i];
+          accs[i] += u;                                        // A_GB0 = 0, A_G0 = Hp: contiguous
         }
       }
-      ph5 += clock64() - tq;
+      PH_ADD(ph5, tq);
     }
+    // ---- CTA accumulators -> this CTA's small record (GradLayout offsets) ------------------------------------------
+    epi_bar_b();
+    for (int i = tid; i < Hp; i += kTcEpiThreads) { rec[a.gl.gb + i] = accs[A_GB0 + i]; rec[a.gl.glin + i] = accs[A_GLIN + i]; }
+    for (int i = tid; i < 4 * Hp; i += kTcEpiThreads) rec[a.gl.g0 + i] = accs[A_G0 + i];
+    for (int i = tid; i < H2; i += kTcEpiThreads) { rec[a.gl.gv0b + i] = accs[A_GV0B + i]; rec[a.gl.gv1 + i] = accs[A_GV1 + i]; }
+    if (tid == 0) { rec[a.gl.glinb] = accs[A_GLINB]; rec[a.gl.gv1b] = accs[A_GV1B]; }
     if (tid == 0 && blockIdx.x < 148) {
       long long* o = g_bwd_phase + blockIdx.x * 16;
-      o[0] = ph0; o[1] = ph1; o[2] = ph2; o[3] = ph3; o[4] = ph4; o[5] = ph5; o[8] = clock64() - t_kernel0; o[9] = ntl;
+      o[0] = ph0; o[1] = ph1; o[2] = ph2; o[3] = ph3; o[4] = ph4; o[5] = ph5; o[8] = PH_NOW() - t_kernel0; o[9] = ntl;
     }
   }
   // ---- teardown ----------------------------------------------------------------------------------------------------------
@@ -604,14 +638,14 @@ static int launch_bwd_tc_t(const BwdTcArgs& a, int grid, cudaStream_t st) {
 
 int launch_backward_tc_chain(const Dims& d, const ParamMap& pm, const float* params, const float* x, int64_t N, int64_t E,
                              int64_t B, const void* csr, int flags, const float* d_nodes, const float* d_value,
-                             const float* stash, float* dz, float* d_embeds, TcPackView pv, float* small_rec, int grid,
-                             cudaStream_t st) {
+                             const float* stash, float* dz, float* d_embeds, TcPackView pv, float* small_rec,
+                             float* head_rec, int grid, cudaStream_t st) {
   BwdTcArgs a;
   a.d = d; a.pm = pm; grad_layout(d, &a.gl);
   a.params = params; a.x = x; a.N = N; a.E = E; a.B = B;
   a.csr = csr_view(const_cast<void*>(csr), N, E, B);
   a.flags = flags; a.d_nodes = d_nodes; a.d_value = d_value; a.stash = stash; a.dz = dz; a.d_embeds = d_embeds;
-  a.pv = pv; a.small_rec = small_rec;
+  a.pv = pv; a.small_rec = small_rec; a.head_rec = head_rec;
   switch (d.NJ) {
     case 1: return launch_bwd_tc_t<1>(a, grid, st);
     case 2: return launch_bwd_tc_t<2>(a, grid, st);

@@ -4,7 +4,7 @@
 // SWIZZLE_128B_BASE32B shared-memory operands (SS mode): no transposition anywhere.  Work item = (layer s, group g):
 // the CTA walks the tiles t = g, g+G, ... and accumulates in ONE TMEM accumulator, so only G partial records per
 // layer exist (G = 148 / (Lt-1)) instead of one per CTA of the chain kernel, and they are summed in fixed order.
-// Warp roles: producer (4 KB bulk copies of 32-row k-chunks), 8 split warps (fp32 -> tf32 hi in place + lo copy,
+// Warp roles: producer (2 KB bulk copies of 16-row k-chunks), 8 split warps (fp32 -> tf32 hi in place + lo copy,
 // 3xTF32), MMA issuer, and the split warps double as the epilogue.
 #include "sage_tc.cuh"
 
@@ -14,8 +14,9 @@ using namespace tc;
 constexpr int kDwSplitWarps = 8;
 constexpr int kDwSplitThreads = kDwSplitWarps * 32;
 constexpr int kDwThreads = kDwSplitThreads + 64;
-constexpr int kDwStages = 2;
-constexpr int kDwChunkRows = 32;
+constexpr int kDwStages = 4;
+constexpr int kDwChunkRows = 16;              // node rows (= MMA k) per ring stage
+constexpr int kDwBlk = kDwChunkRows * 128;     // bytes of one 32-channel block of a chunk
 
 struct DwArgs {
   Dims d;
@@ -32,7 +33,7 @@ template <int NJ>
 __global__ void __launch_bounds__(kDwThreads, 1) sage_dw_tc_kernel(const __grid_constant__ DwArgs a) {
   constexpr int Hp = 16 * NJ, N2 = 32 * NJ;
   constexpr int ABLK = 4;                                   // A blocks addressed by the M = 128 descriptor
-  constexpr int a_bytes = ABLK * 4096, b_bytes = NJ * 4096; // one 32-row chunk of each operand (fp32)
+  constexpr int a_bytes = ABLK * kDwBlk, b_bytes = NJ * kDwBlk; // one row chunk of each operand (fp32)
   constexpr int half_bytes = a_bytes + b_bytes;             // hi half; the lo half follows
   constexpr int stage_bytes = 2 * half_bytes;
   constexpr uint32_t TM_COLS = (N2 <= 32) ? 32 : (N2 <= 64) ? 64 : (N2 <= 128) ? 128 : 256;
@@ -62,7 +63,7 @@ __global__ void __launch_bounds__(kDwThreads, 1) sage_dw_tc_kernel(const __grid_
   auto tile_rows32 = [&](int t) {
     const int gA = a.csr.tile_g0[t], gB = a.csr.tile_g0[t + 1];
     const int n = a.csr.gptr[gB] - a.csr.gptr[gA];
-    return (n < 0 || n > kTcRows) ? 0 : ((n + 31) & ~31);
+    return (n < 0 || n > kTcRows) ? 0 : ((n + kDwChunkRows - 1) & ~(kDwChunkRows - 1));   // rows [n, ceil32(n)) are zeros
   };
 
   if (wid == kDwSplitWarps) {
@@ -78,9 +79,9 @@ __global__ void __launch_bounds__(kDwThreads, 1) sage_dw_tc_kernel(const __grid_
           mbar_wait(&bar_empty[st], ((it / kDwStages) & 1) ^ 1);
           uint8_t* dstA = smem + st * stage_bytes;
           uint8_t* dstB = dstA + a_bytes;
-          mbar_expect_tx(&bar_full[st], (uint32_t)(CB + NJ) * 4096u);
-          for (int b = 0; b < CB; ++b) bulk_g2s(dstA + b * 4096, act + (size_t)b * kImgBlockBytes + (size_t)c0 * 128, 4096, &bar_full[st]);
-          for (int b = 0; b < NJ; ++b) bulk_g2s(dstB + b * 4096, dzp + (size_t)b * kImgBlockBytes + (size_t)c0 * 128, 4096, &bar_full[st]);
+          mbar_expect_tx(&bar_full[st], (uint32_t)(CB + NJ) * (uint32_t)kDwBlk);
+          for (int b = 0; b < CB; ++b) bulk_g2s(dstA + b * kDwBlk, act + (size_t)b * kImgBlockBytes + (size_t)c0 * 128, kDwBlk, &bar_full[st]);
+          for (int b = 0; b < NJ; ++b) bulk_g2s(dstB + b * kDwBlk, dzp + (size_t)b * kImgBlockBytes + (size_t)c0 * 128, kDwBlk, &bar_full[st]);
         }
       }
     }
@@ -100,10 +101,10 @@ __global__ void __launch_bounds__(kDwThreads, 1) sage_dw_tc_kernel(const __grid_
 #pragma unroll
           for (int ks = 0; ks < kDwChunkRows / 8; ++ks) {
             const uint64_t one = (uint64_t)1 << 61;   // SWIZZLE_128B_BASE32B
-            const uint64_t dah = make_smem_desc(ahi + ks * 1024, 4096, 512) | one;
-            const uint64_t dal = make_smem_desc(alo + ks * 1024, 4096, 512) | one;
-            const uint64_t dbh = make_smem_desc(bhi + ks * 1024, 4096, 512) | one;
-            const uint64_t dbl = make_smem_desc(blo + ks * 1024, 4096, 512) | one;
+            const uint64_t dah = make_smem_desc(ahi + ks * 1024, kDwBlk, 512) | one;
+            const uint64_t dal = make_smem_desc(alo + ks * 1024, kDwBlk, 512) | one;
+            const uint64_t dbh = make_smem_desc(bhi + ks * 1024, kDwBlk, 512) | one;
+            const uint64_t dbl = make_smem_desc(blo + ks * 1024, kDwBlk, 512) | one;
             mma_tf32_ss(tbase, dal, dbh, idesc, (it | ks) != 0);
             mma_tf32_ss(tbase, dah, dbl, idesc, true);
             mma_tf32_ss(tbase, dah, dbh, idesc, true);
@@ -123,9 +124,9 @@ __global__ void __launch_bounds__(kDwThreads, 1) sage_dw_tc_kernel(const __grid_
         mbar_wait(&bar_full[st], (it / kDwStages) & 1);
         float4* base = (float4*)(smem + st * stage_bytes);
         float4* lob = (float4*)(smem + st * stage_bytes + half_bytes);
-        const int nA = CB * 256, nB = NJ * 256;       // float4 per region
+        const int nA = CB * (kDwBlk / 16), nB = NJ * (kDwBlk / 16);       // float4 per region
         for (int i = tid; i < nA + nB; i += kDwSplitThreads) {
-          const int idx = i < nA ? i : (ABLK * 256 + (i - nA));
+          const int idx = i < nA ? i : (ABLK * (kDwBlk / 16) + (i - nA));
           const float4 v = base[idx];
           float4 h, l;
           split_tf32(v.x, h.x, l.x); split_tf32(v.y, h.y, l.y); split_tf32(v.z, h.z, l.z); split_tf32(v.w, h.w, l.w);
@@ -177,7 +178,7 @@ int tc_dw_groups(const Dims& d) {
 template <int NJ>
 static int launch_dw_t(const DwArgs& a, cudaStream_t st) {
   auto kern = sage_dw_tc_kernel<NJ>;
-  const size_t smem = (size_t)kDwStages * 2 * (4 * 4096 + NJ * 4096) + 1024;
+  const size_t smem = (size_t)kDwStages * 2 * (4 * kDwBlk + NJ * kDwBlk) + 1024;
   HEX_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   kern<<<(a.d.Lt - 1) * a.G, kDwThreads, smem, st>>>(a);
   HEX_CUDA_CHECK(cudaGetLastError());

@@ -1,10 +1,12 @@
 // Fused forward of modern_two_headed on the 5th-gen tensor cores (tcgen05 + TMEM), see sage_tc.cuh.
 //
 // One persistent CTA per SM, one 128-row tile (whole graphs) at a time, three warp roles:
-//   warps 0-7  epilogue: thread = (node row, column slice); TMEM <-> registers, CSR gather in smem
-//   warp  8    producer: streams the 3xTF32 weight images of every layer through a 4-stage smem ring
+//   warps 0-15 epilogue.  Phases 1/3: thread = (node row, column slice), TMEM <-> registers.
+//              Phase 2 (CSR gather): warp = node row, lane = 4 channels -- every shared-memory access is a
+//              contiguous row (no bank conflicts, no degree divergence inside a warp).
+//   warp  16   producer: streams the 3xTF32 weight images of every layer through a shared-memory ring
 //              with 1-D bulk copies (UBLKCP) completing on mbarriers; runs ahead across layers/tiles
-//   warp  9    MMA issuer: one thread issues tcgen05.mma (A = h in TMEM, B = ring stage, D = Z in TMEM)
+//   warp  17   MMA issuer: one thread issues tcgen05.mma (A = h in TMEM, B = ring stage, D = [Zl | Zr] in TMEM)
 // Layer 0 (2 -> H) is a rank-2 update on the CUDA cores; the dueling head (GN0/models.py:368-384,
 // 567-584) runs in the same CTA on the final activations.
 #include "sage_tc.cuh"
@@ -29,29 +31,34 @@ struct FwdTcArgs {
 template <int NJ>
 struct FwdTcSmem {
   static constexpr int Hp = 16 * NJ;
-  static constexpr int N2 = 32 * NJ;
-  static constexpr int P = Hp + 4;                       // dump row pitch (floats): float4 rows conflict-free
+  static constexpr int P = Hp + 4;                       // row pitch (floats): float4 rows conflict-free
   static constexpr int ECAP = kEdgeCapPerRow * kTcRows;
-  static constexpr int half_bytes = kTcKC * N2 * 4;      // one tf32 half (hi or lo) of a k chunk
+  static constexpr int stages = NJ <= 7 ? 5 : 3;         // ring depth
+  static constexpr int N2 = 32 * NJ;
+  static constexpr int half_bytes = kTcKF * N2 * 4;      // one tf32 half (hi or lo) of a k-chunk stage
   static constexpr int stage_bytes = 2 * half_bytes;
   static constexpr int off_ring = 0;
-  static constexpr int off_dump = off_ring + kTcStages * stage_bytes;            // float [128][P]
-  static constexpr int off_rows = off_dump + kTcRows * P * 4;                    // float [6][128]: inv,x0,x1,m0,m1,adv
+  static constexpr int off_dump = off_ring + stages * stage_bytes;               // float [128][P]  Zl rows
+  static constexpr int off_agg = off_dump + (kTcRows + 1) * P * 4;               // float [128][P]  sum_j Zl_j
+                                                                                 // (dump row 128 = zeros)
+  static constexpr int off_rows = off_agg + kTcRows * P * 4;                     // float [6][128]: inv,x0,x1,m0,m1,adv
   static constexpr int off_pool = off_rows + 6 * kTcRows * 4;                    // float [4*Hp]
   static constexpr int off_hid = off_pool + 4 * Hp * 4;                          // float [Hp]
   static constexpr int off_misc = off_hid + Hp * 4;                              // float [16]
   static constexpr int off_rowptr = off_misc + 64;                               // int [128+4]
   static constexpr int off_gp = off_rowptr + (kTcRows + 4) * 4;                  // int [64+4]
   static constexpr int off_col = off_gp + (kMaxTileGraphs + 4) * 4;              // u16 [ECAP]
-  static constexpr int off_bar = off_col + ECAP * 2;                             // u64 [2*stages + 2], u32 tmem slot
-  static constexpr int off_bias = off_bar + (2 * kTcStages + 2) * 8 + 16;        // float [Lt][Hp] (runtime sized)
+  static constexpr int off_gtab = (off_col + ECAP * 2 + 15) & ~15;               // gather table (sage_tc.cuh)
+  static constexpr int off_bar = off_gtab + gather_tab_bytes();                  // u64 [2*stages + 6], u32 tmem slot
+  static constexpr int off_bias = off_bar + (2 * stages + 6) * 8 + 16;           // float [Lt][Hp] (runtime sized)
   static size_t bytes(int Lt) { return (size_t)off_bias + (size_t)Lt * Hp * 4; }
 };
 
 // Phase profile (cycles, summed over the tiles of each CTA; read back by hexgnn_debug_phases):
-//   [0] epilogue: wait for Z   [1] phase 1 (Zl dump)   [2] phase 2 (gather + write-back)   [3] tile load + layer 0
+//   [0] epilogue: wait for Zl  [1] phase 1 (Zl dump)   [2] phase 2 (gather)   [3] tile load + layer 0
 //   [4] head                   [5] MMA warp: wait for h   [6] MMA warp: wait for weights   [7] MMA warp: issue + commit
-//   [8] total kernel cycles of the CTA   [9] tiles
+//   [8] total kernel cycles of the CTA   [9] tiles   [10] wait for Zr   [11] phase 3 (combine + write-back)
+//   [12] phase 3 up to the Zr TMEM load   [13] phase 3 up to the last store issued (cumulative inside [11])
 __device__ long long g_fwd_phase[148 * 16];
 
 struct TileDims { int g0, g1, r0, n, e0, ne; bool ok; };
@@ -73,14 +80,15 @@ __device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"
 template <int NJ>
 __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid_constant__ FwdTcArgs a) {
   using S = FwdTcSmem<NJ>;
-  constexpr int Hp = S::Hp, N2 = S::N2, P = S::P;
+  constexpr int Hp = S::Hp, P = S::P, kStages = S::stages;
   constexpr int NG = 2 * NJ;                 // 8-column granules per row
-  constexpr int NQ = Hp / kTcKC;             // k chunks per layer
+  constexpr int NQ = Hp / kTcKF;             // k chunks (ring stages) per layer
   constexpr int MAXG = (NG + kTcSlices - 1) / kTcSlices;   // granules per epilogue thread
   constexpr uint32_t TM_HI = 0, TM_LO = Hp, TM_D = 2 * Hp;     // TMEM columns
   constexpr uint32_t TM_COLS = (4 * Hp <= 64) ? 64 : (4 * Hp <= 128) ? 128 : (4 * Hp <= 256) ? 256 : 512;
   extern __shared__ __align__(128) uint8_t smem[];
   float* dump = (float*)(smem + S::off_dump);
+  float* agg = (float*)(smem + S::off_agg);
   float* rows = (float*)(smem + S::off_rows);
   float* inv_s = rows, *x0_s = rows + 128, *x1_s = rows + 256, *m0_s = rows + 384, *m1_s = rows + 512, *adv_s = rows + 640;
   float* pool = (float*)(smem + S::off_pool);
@@ -89,27 +97,29 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
   int* rowptr_s = (int*)(smem + S::off_rowptr);
   int* gp_s = (int*)(smem + S::off_gp);
   unsigned short* col_s = (unsigned short*)(smem + S::off_col);
+  const GatherTab gtab = gather_tab_view(smem + S::off_gtab);
   uint64_t* bar_full = (uint64_t*)(smem + S::off_bar);
-  uint64_t* bar_empty = bar_full + kTcStages;
-  uint64_t* bar_d = bar_empty + kTcStages;
-  uint64_t* bar_a = bar_d + 1;
-  uint32_t* tmem_slot = (uint32_t*)(bar_a + 1);
+  uint64_t* bar_empty = bar_full + kStages;
+  uint64_t* bar_z = bar_empty + kStages;
+  uint64_t* bar_a = bar_z + 2;               // [4]: column quarter gi of the next A operand is in TMEM
+  uint32_t* tmem_slot = (uint32_t*)(bar_a + 4);
   float* bias_s = (float*)(smem + S::off_bias);
 
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const int H = a.d.H, Lt = a.d.Lt;
   const int ntiles = *a.csr.ntiles;
-  const long long t_kernel0 = clock64();
-  long long ph0 = 0, ph1 = 0, ph2 = 0, ph3 = 0, ph4 = 0, ph5 = 0, ph6 = 0, ph7 = 0, ntl = 0;
+  const long long t_kernel0 = PH_NOW();
+  long long ph0 = 0, ph1 = 0, ph2 = 0, ph3 = 0, ph4 = 0, ph5 = 0, ph6 = 0, ph7 = 0, ph10 = 0, ph11 = 0, ph12 = 0, ph13 = 0, ntl = 0;
 
   if (tid == 0) {
-    for (int i = 0; i < kTcStages; ++i) { mbar_init(&bar_full[i], 1); mbar_init(&bar_empty[i], 1); }
-    mbar_init(bar_d, 1);
-    mbar_init(bar_a, kTcEpiThreads);
+    for (int i = 0; i < kStages; ++i) { mbar_init(&bar_full[i], 1); mbar_init(&bar_empty[i], 1); }
+    mbar_init(bar_z, 1);
+    for (int i = 0; i < 4; ++i) mbar_init(&bar_a[i], kTcEpiWarps);
     fence_mbar_init();
   }
   if (wid == kTcEpiWarps + 1) tmem_alloc(tmem_slot, TM_COLS);
   for (int i = tid; i < Lt * Hp; i += kTcThreads) bias_s[i] = a.pv.bias[i];
+  for (int i = tid; i < P; i += kTcThreads) dump[kTcRows * P + i] = 0.f;   // the gather's zero row
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -124,8 +134,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
         for (int s = 1; s < Lt; ++s) {
           const uint8_t* src = (const uint8_t*)a.pv.wimg + (size_t)(s - 1) * NQ * S::stage_bytes;
           for (int q = 0; q < NQ; ++q, ++it) {
-            const int st = it % kTcStages;
-            mbar_wait(&bar_empty[st], ((it / kTcStages) & 1) ^ 1);
+            const int st = it % kStages;
+            mbar_wait(&bar_empty[st], ((it / kStages) & 1) ^ 1);
             mbar_expect_tx(&bar_full[st], S::stage_bytes);
             bulk_g2s(smem + S::off_ring + st * S::stage_bytes, src + (size_t)q * S::stage_bytes, S::stage_bytes,
                      &bar_full[st]);
@@ -136,39 +146,40 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
   } else if (wid == kTcEpiWarps + 1) {
     // ================= MMA issuer =================
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_tf32(kTcRows, N2, false);
-      constexpr uint32_t lbo = N2 * 16, sbo = 128;
+      constexpr uint32_t idesc = make_idesc_tf32(kTcRows, S::N2, false);
+      constexpr uint32_t lbo = S::N2 * 16, sbo = 128;
       uint32_t it = 0, na = 0;
       for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
         if (!tile_dims(a.csr, t, S::ECAP).ok) continue;
         for (int s = 1; s < Lt; ++s) {
-          long long tq = clock64();
-          mbar_wait(bar_a, na & 1);   // h of this layer is in TMEM, D has been drained
-          ph5 += clock64() - tq;
-          ++na;
-          tc_fence_after();
+          long long tq;
           for (int q = 0; q < NQ; ++q, ++it) {
-            const int st = it % kTcStages;
-            tq = clock64();
-            mbar_wait(&bar_full[st], (it / kTcStages) & 1);
-            ph6 += clock64() - tq;
-            tq = clock64();
+            if ((q % kTcSlices) == 0) {
+              // granules [q, q + kTcSlices) of h (k-steps q .. q+3) are in TMEM; for q = 0 also: D has been drained.
+              // The epilogue releases h quarter by quarter, so these MMAs run under the rest of its phase 3.
+              tq = PH_NOW();
+              mbar_wait(&bar_a[q / kTcSlices], na & 1);
+              PH_ADD(ph5, tq);
+              tc_fence_after();
+            }
+            const int st = it % kStages;
+            tq = PH_NOW();
+            mbar_wait(&bar_full[st], (it / kStages) & 1);
+            PH_ADD(ph6, tq);
+            tq = PH_NOW();
             tc_fence_after();
             const uint32_t bhi = smem_u32(smem + S::off_ring + st * S::stage_bytes);
-            const uint32_t blo = bhi + S::half_bytes;
-#pragma unroll
-            for (int kk = 0; kk < kTcKC / 8; ++kk) {
-              const uint64_t dhi = make_smem_desc(bhi + kk * 2 * lbo, lbo, sbo);
-              const uint64_t dlo = make_smem_desc(blo + kk * 2 * lbo, lbo, sbo);
-              const uint32_t kcol = q * kTcKC + kk * 8;
-              mma_tf32_ts(tbase + TM_D, tbase + TM_LO + kcol, dhi, idesc, (q | kk) != 0);
-              mma_tf32_ts(tbase + TM_D, tbase + TM_HI + kcol, dlo, idesc, true);
-              mma_tf32_ts(tbase + TM_D, tbase + TM_HI + kcol, dhi, idesc, true);
-            }
+            const uint64_t dhi = make_smem_desc(bhi, lbo, sbo);
+            const uint64_t dlo = make_smem_desc(bhi + S::half_bytes, lbo, sbo);
+            const uint32_t kcol = q * kTcKF;
+            mma_tf32_ts(tbase + TM_D, tbase + TM_LO + kcol, dhi, idesc, q != 0);
+            mma_tf32_ts(tbase + TM_D, tbase + TM_HI + kcol, dlo, idesc, true);
+            mma_tf32_ts(tbase + TM_D, tbase + TM_HI + kcol, dhi, idesc, true);
             mma_commit(&bar_empty[st]);   // stage free once these MMAs have read it
-            ph7 += clock64() - tq;
+            PH_ADD(ph7, tq);
           }
-          mma_commit(bar_d);              // Z complete
+          mma_commit(bar_z);              // Z complete
+          ++na;
         }
       }
       if (blockIdx.x < 148) {
@@ -189,7 +200,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
       const TileDims td = tile_dims(a.csr, t, S::ECAP);
       const int n = td.n, r0 = td.r0, g0 = td.g0, g1 = td.g1;
       epi_bar();   // previous tile fully consumed
-      long long tq = clock64();
+      long long tq = PH_NOW();
       ++ntl;
       if (!td.ok) {
         const int r1 = a.csr.gptr[g1];
@@ -220,6 +231,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
         }
         if (bad) atomicOr(a.csr.status, bad);
         epi_bar();
+        gather_build<NJ>(gtab, rowptr_s, col_s, n, tid);
         for (int i = tid; i < kTcRows; i += kTcEpiThreads) {
           const int b = rowptr_s[i], e = rowptr_s[i + 1];
           const int deg = e - b;
@@ -236,15 +248,19 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
       const size_t img_bytes = (size_t)tc_act_blocks(Hp) * kImgBlockBytes;
       char* st_img = a.stash ? (char*)a.stash + ((size_t)0 * a.B + t) * img_bytes : nullptr;
       float* emb = a.stash ? a.stash + (size_t)Lt * a.B * (img_bytes / 4) : nullptr;
+      // sign masks: word (layer, tile, slice, row), see sage_tc.cuh
+      uint32_t* mask_t = a.stash ? (uint32_t*)(a.stash + tc_stash_mask_off_floats(a.d, a.N, a.B)) +
+                                       ((size_t)t * kTcSlices + slice) * kTcRows + row : nullptr;
+      const size_t mask_layer = (size_t)a.B * kTcSlices * kTcRows;
       const float inv = inv_s[row];
-      const int eb = rowptr_s[row], ee = rowptr_s[row + 1];
       // ---- layer 0 (2 -> H): rank-2 update, result -> TMEM as the first A operand --------------------------
       {
         const float* wl = Pm + sage_wl(a.pm, head, 0);
         const float* bl = Pm + sage_bl(a.pm, head, 0, H);
         const float* wr = Pm + sage_wr(a.pm, head, 0, H);
         const float xm0 = m0_s[row], xm1 = m1_s[row], xx0 = x0_s[row], xx1 = x1_s[row];
-        for (int g = slice; g < NG; g += kTcSlices) {
+        uint32_t mw = 0;
+        for (int g = slice, gi = 0; g < NG; g += kTcSlices, ++gi) {
           float v[8], hi[8], lo[8];
 #pragma unroll
           for (int u = 0; u < 8; ++u) {
@@ -253,6 +269,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
             if (live && c < H)
               r = fmaxf(wl[2 * c] * xm0 + wl[2 * c + 1] * xm1 + bl[c] + wr[2 * c] * xx0 + wr[2 * c + 1] * xx1, 0.f);
             v[u] = r;
+            if (r > 0.f) mw |= 1u << (gi * 8 + u);
             split_tf32(r, hi[u], lo[u]);
           }
           tmem_st8(trow + TM_HI + g * 8, hi);
@@ -273,18 +290,23 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
           dst[0] = make_float4(live ? 1.f : 0.f, 0.f, 0.f, 0.f);
           dst[1] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
+        if (mask_t) mask_t[0] = mw;
         tmem_wait_st();
         tc_fence_before();
-        mbar_arrive(bar_a);
+        __syncwarp();
+        if (lane == 0) {
+#pragma unroll
+          for (int gi = 0; gi < MAXG; ++gi) mbar_arrive(&bar_a[gi]);
+        }
       }
-      ph3 += clock64() - tq;
+      PH_ADD(ph3, tq);
       // ---- layers 1 .. Lt-1 on the tensor cores ---------------------------------------------------------------
       for (int s = 1; s < Lt; ++s) {
-        tq = clock64();
-        mbar_wait(bar_d, nd & 1);
-        ph0 += clock64() - tq;
-        tq = clock64();
+        tq = PH_NOW();
+        mbar_wait(bar_z, nd & 1);
         ++nd;
+        PH_ADD(ph0, tq);
+        tq = PH_NOW();
         tc_fence_after();
         // phase 1: Zl -> shared (row major); all TMEM loads in flight before the single wait
         {
@@ -306,79 +328,83 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
           }
         }
         epi_bar();
-        ph1 += clock64() - tq;
-        tq = clock64();
-        // phase 2: h' = relu(mean_j Zl_j + Zr_i + b).  Neighbour-outer / granule-inner: one index load
-        // feeds 2*MAXG independent 16-byte shared loads (latency-bound otherwise: 4 warps per scheduler).
+        PH_ADD(ph1, tq);
+        tq = PH_NOW();
+        // phase 2: agg_i = sum_{j -> i} Zl_j in CSR order (tile_gather, sage_tc.cuh)
+#ifndef HEXGNN_EXP_NO_GATHER
+        tile_gather<NJ>(gtab, dump, agg, n, wid, lane);
+#endif
+        epi_bar();
+        PH_ADD(ph2, tq);
+        tq = PH_NOW();
+        // phase 3: h' = relu(agg_i / deg_i + Zr_i + b) -> TMEM (next A operand), stash image, sign mask
         const bool last = (s == Lt - 1);
         const float* bias = bias_s + s * Hp;
         char* st = (a.stash && row < n32) ? st_img + (size_t)s * a.B * img_bytes : nullptr;
-        float acc[MAXG][8];
-#pragma unroll
-        for (int gi = 0; gi < MAXG; ++gi)
-#pragma unroll
-          for (int u = 0; u < 8; ++u) acc[gi][u] = 0.f;
         {
-          int j = eb < ee ? (int)col_s[eb] : 0;
-          for (int p = eb; p < ee; ++p) {
-            const int jn = (p + 1 < ee) ? (int)col_s[p + 1] : 0;
-            const float* src = dump + j * P + slice * 8;
+          float zr[MAXG][8];
 #pragma unroll
-            for (int gi = 0; gi < MAXG; ++gi) {
-              if (slice + gi * kTcSlices < NG) {
-                const float4 v0 = *(const float4*)(src + gi * kTcSlices * 8);
-                const float4 v1 = *(const float4*)(src + gi * kTcSlices * 8 + 4);
-                acc[gi][0] += v0.x; acc[gi][1] += v0.y; acc[gi][2] += v0.z; acc[gi][3] += v0.w;
-                acc[gi][4] += v1.x; acc[gi][5] += v1.y; acc[gi][6] += v1.z; acc[gi][7] += v1.w;
+          for (int gi = 0; gi < MAXG; ++gi) {
+            const int g = slice + gi * kTcSlices;
+            if (g < NG) tmem_ld8(trow + TM_D + Hp + g * 8, zr[gi]);
+          }
+          tmem_wait_ld();
+          PH_ADD(ph12, tq);
+          uint32_t mw = 0;
+#pragma unroll
+          for (int gi = 0; gi < MAXG; ++gi) {
+            const int g = slice + gi * kTcSlices;
+            if (g < NG) {
+              float acc[8], hi[8], lo[8];
+              if (live) {
+                const float4* src = (const float4*)(agg + row * P + g * 8);
+                const float4 v0 = src[0], v1 = src[1];
+                acc[0] = v0.x; acc[1] = v0.y; acc[2] = v0.z; acc[3] = v0.w;
+                acc[4] = v1.x; acc[5] = v1.y; acc[6] = v1.z; acc[7] = v1.w;
+              }
+#pragma unroll
+              for (int u = 0; u < 8; ++u) {
+                const float r = live ? fmaxf(fmaf(acc[u], inv, zr[gi][u] + bias[g * 8 + u]), 0.f) : 0.f;
+                acc[u] = r;
+                if (r > 0.f) mw |= 1u << (gi * 8 + u);
+                split_tf32(r, hi[u], lo[u]);
+              }
+              if (st) {
+                float4* dst = (float4*)(st + rm32_granule_off(g, row));
+                dst[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+                dst[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+              }
+              if (emb && s == a.d.L - 1 && live) {
+                float4* dst = (float4*)(emb + (int64_t)(r0 + row) * Hp + g * 8);
+                dst[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+                dst[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+              }
+              if (!last) {
+                tmem_st8(trow + TM_HI + g * 8, hi);
+                tmem_st8(trow + TM_LO + g * 8, lo);
+              } else {
+                tmem_st8(trow + TM_D + g * 8, acc);   // park the exact fp32 activations in the drained Zl columns
               }
             }
-            j = jn;
-          }
-        }
-#pragma unroll
-        for (int gi = 0; gi < MAXG; ++gi) {
-          const int g = slice + gi * kTcSlices;
-          if (g < NG) {
-            float zr[8], hi[8], lo[8];
-            tmem_ld8(trow + TM_D + Hp + g * 8, zr);
-            tmem_wait_ld();
-#pragma unroll
-            for (int u = 0; u < 8; ++u) {
-              const float r = live ? fmaxf(fmaf(acc[gi][u], inv, zr[u] + bias[g * 8 + u]), 0.f) : 0.f;
-              acc[gi][u] = r;
-              split_tf32(r, hi[u], lo[u]);
-            }
-            if (st) {
-              float4* dst = (float4*)(st + rm32_granule_off(g, row));
-              dst[0] = make_float4(acc[gi][0], acc[gi][1], acc[gi][2], acc[gi][3]);
-              dst[1] = make_float4(acc[gi][4], acc[gi][5], acc[gi][6], acc[gi][7]);
-            }
-            if (emb && s == a.d.L - 1 && live) {
-              float4* dst = (float4*)(emb + (int64_t)(r0 + row) * Hp + g * 8);
-              dst[0] = make_float4(acc[gi][0], acc[gi][1], acc[gi][2], acc[gi][3]);
-              dst[1] = make_float4(acc[gi][4], acc[gi][5], acc[gi][6], acc[gi][7]);
-            }
-            if (!last) {
-              tmem_st8(trow + TM_HI + g * 8, hi);
-              tmem_st8(trow + TM_LO + g * 8, lo);
-            } else {
-              tmem_st8(trow + TM_D + g * 8, acc[gi]);   // park the exact fp32 activations in the drained Zl columns
+            if (!last) {   // release column quarter gi of the next A operand to the MMA warp (one arrival per warp)
+              tmem_wait_st();
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(&bar_a[gi]);
             }
           }
+          if (mask_t) mask_t[(size_t)s * mask_layer] = mw;
         }
         if (st && slice == 0) {
           float4* dst = (float4*)(st + rm32_granule_off(NG, row));
           dst[0] = make_float4(live ? 1.f : 0.f, 0.f, 0.f, 0.f);
           dst[1] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
+        PH_ADD(ph13, tq);
         tmem_wait_st();
-        if (!last) {
-          tc_fence_before();
-          mbar_arrive(bar_a);
-        }
-        ph2 += clock64() - tq;
+        PH_ADD(ph11, tq);
       }
-      tq = clock64();
+      tq = PH_NOW();
       // ---- final activations -> shared (row major) for the head ----------------------------------------------------
       epi_bar();   // every gather of the last layer has finished reading the dump
       for (int g = slice; g < NG; g += kTcSlices) {
@@ -405,7 +431,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
       }
       if (a.flags & HEXGNN_ADV_ONLY) {
         for (int i = tid; i < n; i += kTcEpiThreads) a.out_nodes[r0 + i] = adv_s[i];
-        ph4 += clock64() - tq;
+        PH_ADD(ph4, tq);
         continue;
       }
       // ---- value head per graph: pools (sum|max|min|mean) -> MLP -> tanh; dueling combine --------------------------------
@@ -462,11 +488,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
         if (tid == 0 && a.out_value) a.out_value[g0 + g] = val;
         epi_bar();
       }
-      ph4 += clock64() - tq;
+      PH_ADD(ph4, tq);
     }
     if (tid == 0 && blockIdx.x < 148) {
       long long* o = g_fwd_phase + blockIdx.x * 16;
-      o[0] = ph0; o[1] = ph1; o[2] = ph2; o[3] = ph3; o[4] = ph4; o[8] = clock64() - t_kernel0; o[9] = ntl;
+      o[0] = ph0; o[1] = ph1; o[2] = ph2; o[3] = ph3; o[4] = ph4; o[8] = PH_NOW() - t_kernel0; o[9] = ntl;
+      o[10] = ph10; o[11] = ph11; o[12] = ph12; o[13] = ph13;
     }
   }
   // ---- teardown ----------------------------------------------------------------------------------------------------------

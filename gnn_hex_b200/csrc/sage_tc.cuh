@@ -12,6 +12,16 @@
 #include "common.cuh"
 #include "tc_common.cuh"
 
+// Phase profile of the fused kernels (hexgnn_debug_phases, tools/phase_profile.py): compiled in only with
+// -DHEXGNN_PHASES (HEXGNN_PHASES=1 python -m gnn_hex_b200.build --force); the counters cost ~24 registers.
+#ifdef HEXGNN_PHASES
+#define PH_NOW() clock64()
+#define PH_ADD(acc, t0) do { (acc) += clock64() - (t0); } while (0)
+#else
+#define PH_NOW() 0ll
+#define PH_ADD(acc, t0) do { (void)(t0); } while (0)
+#endif
+
 namespace hexgnn {
 
 constexpr int kTcRows = 128;          // MMA M: node rows per tile
@@ -23,9 +33,13 @@ constexpr int kTcEpiThreads = kTcEpiWarps * 32;
 constexpr int kTcThreads = kTcEpiThreads + 64;  // + producer warp + MMA warp
 
 // Weight images for the forward, one per SAGE layer s = 1..Lt-1 of the taken head:
-//   img[s-1][q][half][...]  q = k chunk (Hp/16 of them), half 0 = tf32 hi, 1 = tf32 lo
-//   inside a half: K-major SWIZZLE_NONE canonical B operand, B[n][k], n in [0,2Hp), k in [16q,16q+16):
-//   byte = ((k%16)/4) * (2Hp*16) + (n/8)*128 + (n%8)*16 + (k%4)*4
+//   img[s-1][q8][half][...]  q8 = 8-wide k chunk (Hp/8 of them) = one ring stage = one contiguous bulk copy = the
+//   operand of one 3xTF32 MMA triple; half 0 = tf32 hi, 1 = tf32 lo
+//   inside a half: K-major SWIZZLE_NONE canonical B operand, B[n][k], n in [0,2Hp), k in [8 q8, 8 q8 + 8):
+//   byte = ((k%8)/4) * (2Hp*16) + (n/8)*128 + (n%8)*16 + (k%4)*4
+// One N = 2Hp instruction per k-step: splitting N (Zl / Zr) was measured on B200 and is a loss -- an N = 112 tf32 MMA
+// costs ~100 cycles against ~124 for N = 224.
+constexpr int kTcKF = 8;              // k values per forward ring stage (one MMA k-step)
 struct TcPackView {
   float* wimg;    // forward images   (Lt-1) * Hp * 2Hp * 2 floats
   float* wimgT;   // backward images  (same size), layout above tc_imgB_floats
@@ -57,9 +71,17 @@ __device__ __forceinline__ uint32_t rm32_granule_off(int g, int row) {   // 8-ch
   return (uint32_t)(g >> 2) * kImgBlockBytes + (uint32_t)(row >> 2) * 512u + (uint32_t)(row & 3) * 128u +
          ((uint32_t)((g & 3) ^ (row & 3)) << 5);
 }
+// ReLU sign masks of every layer output: one u32 per (layer, tile, column slice, row); bit gi*8+u is set iff
+// h[row][(slice + gi*kTcSlices)*8 + u] > 0 -- the (row, slice) thread mapping of both epilogues, so the backward
+// chain reads ONE coalesced word per thread and layer instead of the activation image.
+inline int64_t tc_mask_words(const Dims& d, int64_t B) { return (int64_t)d.Lt * B * kTcSlices * kTcRows; }
 // forward stash: [Lt][B tiles][act_blocks*16KB] images + row-major embedding copy [N][Hp] (final_conv_acts)
+// + sign masks [Lt][B][kTcSlices][128] u32
+__host__ __device__ inline int64_t tc_stash_mask_off_floats(const Dims& d, int64_t N, int64_t B) {
+  return (int64_t)d.Lt * B * tc_act_blocks(d.Hp) * (kImgBlockBytes / 4) + N * d.Hp;
+}
 inline int64_t tc_stash_bytes(const Dims& d, int64_t N, int64_t B) {
-  return (int64_t)d.Lt * B * tc_act_blocks(d.Hp) * kImgBlockBytes + N * d.Hp * 4;
+  return (tc_stash_mask_off_floats(d, N, B) + tc_mask_words(d, B)) * 4;
 }
 inline int64_t tc_dz_bytes(const Dims& d, int64_t B) { return (int64_t)(d.Lt - 1) * B * tc_dz_blocks(d.Hp) * kImgBlockBytes; }
 inline bool tc_bwd_supported(const Dims& d) { return d.Hp + 1 <= 128; }   // the ones-channel must fit M = 128
@@ -68,6 +90,124 @@ inline bool tc_bwd_supported(const Dims& d) { return d.Hp + 1 <= 128; }   // the
 // (the contraction index of dH = dZ * W), hi half then lo half; inside a half the K-major SWIZZLE_NONE form
 //   B[n = k (in channel)][kk = c]:  float = ((c%16)/4)*(Hp*4) + (k/8)*32 + (k%8)*4 + (c%4)
 inline int64_t tc_imgB_floats(const Dims& d) { return (int64_t)(d.Lt - 1) * 2 * d.Hp * d.Hp * 2; }
+
+// ---- the CSR gather of both fused kernels -----------------------------------------------------------------------
+// agg[r] = sum over the CSR row r of src[col], r < n, for a [128 + 1][P] row-major shared tile whose row 128 is zeros.
+// The kernels are instruction-issue bound, so the gather runs off a per-tile TABLE built once and replayed by every
+// layer: warp w owns the row groups {w + 16 (4 it + i), i < 4}, it = 0, 1; step k of a group is ONE int4 of byte
+// offsets (neighbour k of each of its 4 rows; rows that have run out point at the zero row).  Per step: one broadcast
+// 16-byte table load, four contiguous-row float4 loads (lane = one float4: no bank conflicts whatever the ids), eight
+// packed FADD2.  Summation order per row = CSR order (deterministic).
+constexpr int kGatherGroups = 2 * kTcEpiWarps;       // 32 groups of 4 rows
+struct GatherTab {
+  int4* tab;        // [<= kEdgeCapPerRow * kTcRows] steps
+  int* gstart;      // [kGatherGroups]
+  int* glen;        // [kGatherGroups]
+};
+__host__ __device__ constexpr int gather_tab_bytes() { return kEdgeCapPerRow * kTcRows * 16 + 2 * kGatherGroups * 4; }
+__device__ __forceinline__ GatherTab gather_tab_view(uint8_t* base) {
+  GatherTab g;
+  g.tab = (int4*)base;
+  g.gstart = (int*)(base + kEdgeCapPerRow * kTcRows * 16);
+  g.glen = g.gstart + kGatherGroups;
+  return g;
+}
+// Build the table of one tile (all epilogue threads; rowptr_s / col_s complete; ends with the epilogue barrier).
+template <int NJ>
+__device__ __forceinline__ void gather_build(const GatherTab& g, const int* __restrict__ rowptr_s,
+                                             const unsigned short* __restrict__ col_s, int n, int tid) {
+  constexpr int PB = (16 * NJ + 4) * 4;   // row pitch in bytes
+  const int wid = tid >> 5, lane = tid & 31;
+  if (wid == 0) {   // lane = group: length = longest of its 4 rows, exclusive scan over the groups
+    const int w = lane & (kTcEpiWarps - 1), it = lane / kTcEpiWarps;
+    int len = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int r = w + kTcEpiWarps * (4 * it + i);
+      const int d = r < n ? rowptr_s[r + 1] - rowptr_s[r] : 0;
+      len = d > len ? d : len;
+    }
+    int inc = len;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += t;
+    }
+    g.gstart[lane] = inc - len;
+    g.glen[lane] = len;
+  }
+  asm volatile("bar.sync 1, %0;" ::"n"(kTcEpiThreads) : "memory");
+#pragma unroll
+  for (int it = 0; it < 2; ++it) {
+    const int gi = it * kTcEpiWarps + wid;
+    const int len = g.glen[gi], st = g.gstart[gi];
+    int b[4], d[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int r = wid + kTcEpiWarps * (4 * it + i);
+      b[i] = r < n ? rowptr_s[r] : 0;
+      d[i] = r < n ? rowptr_s[r + 1] - b[i] : 0;
+    }
+    for (int k = lane; k < len; k += 32) {
+      int4 o;
+      o.x = (k < d[0] ? (int)col_s[b[0] + k] : kTcRows) * PB;
+      o.y = (k < d[1] ? (int)col_s[b[1] + k] : kTcRows) * PB;
+      o.z = (k < d[2] ? (int)col_s[b[2] + k] : kTcRows) * PB;
+      o.w = (k < d[3] ? (int)col_s[b[3] + k] : kTcRows) * PB;
+      g.tab[st + k] = o;
+    }
+  }
+  asm volatile("bar.sync 1, %0;" ::"n"(kTcEpiThreads) : "memory");
+}
+__device__ __forceinline__ void fadd2x2(float4& a, const float4& b) {   // a += b as two packed f32x2 adds
+  unsigned long long a0, a1, b0, b1;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(a0) : "f"(a.x), "f"(a.y));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(a1) : "f"(a.z), "f"(a.w));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(b0) : "f"(b.x), "f"(b.y));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(b1) : "f"(b.z), "f"(b.w));
+  asm("add.rn.f32x2 %0, %0, %1;" : "+l"(a0) : "l"(b0));
+  asm("add.rn.f32x2 %0, %0, %1;" : "+l"(a1) : "l"(b1));
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(a.x), "=f"(a.y) : "l"(a0));
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(a.z), "=f"(a.w) : "l"(a1));
+}
+template <int NJ>
+__device__ __forceinline__ void tile_gather(const GatherTab& g, const float* __restrict__ src, float* __restrict__ agg,
+                                            int n, int wid, int lane) {
+  constexpr int Hp = 16 * NJ, PV = (Hp + 4) / 4, NV = Hp / 4;
+  if (lane >= NV) return;                       // warp-uniform loops below: no collective inside
+  const char* sb = (const char*)src + lane * 16;
+  float4* a4 = (float4*)agg + lane;
+#pragma unroll
+  for (int it = 0; it < 2; ++it) {
+    const int gi = it * kTcEpiWarps + wid;
+    const int len = g.glen[gi];
+    const int4* tp = g.tab + g.gstart[gi];
+    float4 acc[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    int k = 0;
+    for (; k + 2 <= len; k += 2) {
+      const int4 o0 = tp[k], o1 = tp[k + 1];
+      const float4 v0 = *(const float4*)(sb + o0.x), v1 = *(const float4*)(sb + o0.y);
+      const float4 v2 = *(const float4*)(sb + o0.z), v3 = *(const float4*)(sb + o0.w);
+      const float4 u0 = *(const float4*)(sb + o1.x), u1 = *(const float4*)(sb + o1.y);
+      const float4 u2 = *(const float4*)(sb + o1.z), u3 = *(const float4*)(sb + o1.w);
+      fadd2x2(acc[0], v0); fadd2x2(acc[1], v1); fadd2x2(acc[2], v2); fadd2x2(acc[3], v3);
+      fadd2x2(acc[0], u0); fadd2x2(acc[1], u1); fadd2x2(acc[2], u2); fadd2x2(acc[3], u3);
+    }
+    if (k < len) {
+      const int4 o0 = tp[k];
+      const float4 v0 = *(const float4*)(sb + o0.x), v1 = *(const float4*)(sb + o0.y);
+      const float4 v2 = *(const float4*)(sb + o0.z), v3 = *(const float4*)(sb + o0.w);
+      fadd2x2(acc[0], v0); fadd2x2(acc[1], v1); fadd2x2(acc[2], v2); fadd2x2(acc[3], v3);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int r = wid + kTcEpiWarps * (4 * it + i);
+      if (r < n) a4[r * PV] = acc[i];
+    }
+  }
+}
 
 int launch_pack_tc(const Dims& d, const ParamMap& pm, const float* params, const float* x, TcPackView pv,
                    bool with_transpose, cudaStream_t st);
@@ -80,15 +220,19 @@ int debug_read_bwd_phases(long long* host, int n);
 int tc_dw_groups(const Dims& d);
 int launch_backward_tc_chain(const Dims& d, const ParamMap& pm, const float* params, const float* x, int64_t N, int64_t E,
                              int64_t B, const void* csr, int flags, const float* d_nodes, const float* d_value,
-                             const float* stash, float* dz, float* d_embeds, TcPackView pv, float* small_rec, int grid,
-                             cudaStream_t st);
+                             const float* stash, float* dz, float* d_embeds, TcPackView pv, float* small_rec,
+                             float* head_rec, int grid, cudaStream_t st);
 int launch_backward_tc_dw(const Dims& d, int64_t N, int64_t E, int64_t B, const void* csr, const float* stash,
                           const float* dz, float* big_rec, cudaStream_t st);
-int launch_reduce_tc(const Dims& d, const float* small_rec, int nsmall, const float* big_rec, int G, float* packed_sum,
-                     cudaStream_t st);
+int launch_reduce_tc(const Dims& d, const float* small_rec, int nsmall, const float* big_rec, int G,
+                     const float* head_rec, int64_t B, float* packed_sum, cudaStream_t st);
 
-// Workspace of the tcgen05 backward (floats): weight images | dZ stash | small records | group records | packed sum
-struct TcBwdWs { int64_t pack, dz, small_rec, big_rec, sum, total; };
+// Per-graph record of the value head's backward: [dt (H/2 padded to 4) | pooled (4H padded to 4)]; the gradient of
+// value_head.layers.0.weight is sum_g dt_g (x) pooled_g, summed in graph order by reduce_tc_kernel.
+__host__ __device__ inline int tc_head_rec_floats(const Dims& d) { return ((d.H2 + 3) & ~3) + ((4 * d.H + 3) & ~3); }
+// Workspace of the tcgen05 backward (floats): weight images | dZ stash | small records | group records | head
+// records | packed sum
+struct TcBwdWs { int64_t pack, dz, small_rec, big_rec, head_rec, sum, total; };
 inline TcBwdWs tc_bwd_ws(const Dims& d, int64_t B) {
   GradLayout gl;
   grad_layout(d, &gl);
@@ -98,6 +242,7 @@ inline TcBwdWs tc_bwd_ws(const Dims& d, int64_t B) {
   w.dz = o; o += tc_dz_bytes(d, B) / 4;
   w.small_rec = o; o += align_up((int64_t)bwd_grid_ctas() * (gl.total - gl.gb), 4);
   w.big_rec = o; o += (int64_t)tc_dw_groups(d) * gl.g0;
+  w.head_rec = o; o += align_up(B * tc_head_rec_floats(d), 4);
   w.sum = o; o += gl.total;
   w.total = o;
   return w;

@@ -1,0 +1,60 @@
+// Rainbow learner loss on device: the glue between the fused forward and the fused backward
+// (GN0/RainbowDQN/Rainbow/common/rainbow.py:301-312):
+//     td_est[g] = Q[ptr[g] + action[g]]                     rainbow.py:301,303
+//     td_err[g] = td_est[g] - td_tgt[g]                     rainbow.py:307 (PER priorities = |td_err| + 1e-6)
+//     loss      = scale * mean_g( w[g] * l(td_tgt[g], td_est[g]) ),  l = MSE or SmoothL1(beta=1)   rainbow.py:85,311-312
+// and dloss/dQ, which is zero except at the B selected rows, is written in the same launch, so the learner step
+// needs no index / elementwise / reduction kernels between the two fused kernels.  One CTA; the mean is a
+// fixed-order tree (deterministic).
+#include "common.cuh"
+
+namespace hexgnn {
+
+__global__ void __launch_bounds__(1024) td_loss_kernel(const float* __restrict__ q, const int64_t* __restrict__ ptr,
+                                                       const int64_t* __restrict__ action,
+                                                       const float* __restrict__ target, const float* __restrict__ weight,
+                                                       int64_t N, int B, int kind, float scale, float* __restrict__ loss,
+                                                       float* __restrict__ td_err, float* __restrict__ d_q) {
+  __shared__ float red[1024];
+  const int tid = threadIdx.x;
+  if (d_q) {
+    float4* d4 = (float4*)d_q;
+    const int64_t n4 = N >> 2;
+    for (int64_t i = tid; i < n4; i += 1024) d4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int64_t i = (n4 << 2) + tid; i < N; i += 1024) d_q[i] = 0.f;
+  }
+  __syncthreads();   // the zero fill is ordered before the B scattered entries (same CTA)
+  float part = 0.f;
+  const float invB = scale / (float)B;
+  for (int g = tid; g < B; g += 1024) {
+    const int64_t idx = ptr[g] + action[g];
+    const float w = weight ? weight[g] : 1.f;
+    float l, dl, e;
+    if (idx < 0 || idx >= N) {
+      e = l = dl = __int_as_float(0x7fc00000);   // out-of-range action: poison instead of reading out of bounds
+    } else {
+      e = q[idx] - target[g];
+      if (kind == 0) { l = e * e; dl = 2.f * e; }
+      else { const float a = fabsf(e); l = a < 1.f ? 0.5f * e * e : a - 0.5f; dl = a < 1.f ? e : (e > 0.f ? 1.f : -1.f); }
+      if (d_q) d_q[idx] += w * dl * invB;        // two graphs never share a row; += keeps even that case exact
+    }
+    if (td_err) td_err[g] = e;
+    part += w * l;
+  }
+  red[tid] = part;
+  __syncthreads();
+  for (int o = 512; o > 0; o >>= 1) {
+    if (tid < o) red[tid] += red[tid + o];
+    __syncthreads();
+  }
+  if (tid == 0) loss[0] = red[0] * invB;
+}
+
+int launch_td_loss(const float* q, const int64_t* ptr, const int64_t* action, const float* target, const float* weight,
+                   int64_t N, int64_t B, int kind, float scale, float* loss, float* td_err, float* d_q, cudaStream_t st) {
+  td_loss_kernel<<<1, 1024, 0, st>>>(q, ptr, action, target, weight, N, (int)B, kind, scale, loss, td_err, d_q);
+  HEX_CUDA_CHECK(cudaGetLastError());
+  return HEXGNN_OK;
+}
+
+}  // namespace hexgnn

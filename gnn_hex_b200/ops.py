@@ -10,7 +10,7 @@ from ._lib import HEXGNN_ADV_ONLY, HEXGNN_SEPARATE, HEXGNN_PATH_SIMT, HEXGNN_PAT
 
 # kernels launched by each C-ABI call (csr: init, hist, scan, fill, sort; forward: pack, fused;
 # backward: pack, fused, reduce, unpack) -- bench.py's `gpu_launches` is read off this counter.
-LAUNCHES = {"build_csr": 5, "forward": 2, "backward": 4}
+LAUNCHES = {"build_csr": 5, "forward": 2, "backward": 5, "td_loss": 1}
 launch_counter = 0
 
 
@@ -160,3 +160,52 @@ def fused_backward(desc, flat_params, x, csr, flags, d_nodes, d_value, stash, wa
     _lib.check(rc, "hexgnn_backward")
     _count("backward")
     return grad_out, d_embeds
+
+
+LOSS_KINDS = {"mse": 0, "smooth_l1": 1, "huber": 1}
+
+
+class _TDLoss(torch.autograd.Function):
+    """hexgnn_td_loss behind autograd: forward computes loss, td errors AND d loss / d q in one launch;
+    backward only scales the stored gradient by the incoming scalar."""
+
+    @staticmethod
+    def forward(ctx, q, ptr, action, target, weight, kind, scale):
+        _require_cuda(q, "q")
+        dev = q.device
+        q = q.contiguous().float()
+        N, B = int(q.shape[0]), int(action.shape[0])
+        ptr = ptr.to(dev, non_blocking=True).contiguous()
+        action = action.to(dev, non_blocking=True).contiguous()
+        target = target.to(dev, non_blocking=True).contiguous().float()
+        if weight is not None:
+            weight = weight.to(dev, non_blocking=True).contiguous().float()
+        if ptr.dtype != torch.int64 or action.dtype != torch.int64 or ptr.numel() != B + 1 or target.numel() != B:
+            raise _lib.HexGnnError("td_loss: ptr [B+1] int64, action [B] int64, target [B] expected")
+        loss = torch.empty(1, dtype=torch.float32, device=dev)
+        td_err = torch.empty(B, dtype=torch.float32, device=dev)
+        need_grad = ctx.needs_input_grad[0]
+        d_q = torch.empty(N, dtype=torch.float32, device=dev) if need_grad else None
+        rc = _lib.lib().hexgnn_td_loss(_ptr(q), _ptr(ptr), _ptr(action), _ptr(target), _ptr(weight), N, B, int(kind),
+                                       float(scale), _ptr(loss), _ptr(td_err), _ptr(d_q), _stream(dev))
+        _lib.check(rc, "hexgnn_td_loss")
+        _count("td_loss")
+        ctx.d_q = d_q
+        ctx.mark_non_differentiable(td_err)
+        return loss.reshape(()), td_err
+
+    @staticmethod
+    def backward(ctx, g_loss, _g_err):
+        d_q = ctx.d_q
+        ctx.d_q = None
+        return (d_q * g_loss if d_q is not None else None), None, None, None, None, None, None
+
+
+def td_loss(q, ptr, action, target, weight=None, kind="mse", scale=1.0):
+    """Rainbow learner loss on device (rainbow.py:301-312): returns (loss, td_err) with
+    ``td_est = q[action + ptr[:-1]]``, ``td_err = td_est - target`` (PER priorities = |td_err| + 1e-6) and
+    ``loss = scale * mean(weight * l(target, td_est))``, l = MSE ("mse") or SmoothL1 ("smooth_l1").
+    Differentiable w.r.t. ``q``; one kernel launch forward, one elementwise scale backward."""
+    if kind not in LOSS_KINDS:
+        raise _lib.HexGnnError(f"td_loss: unknown loss kind {kind!r}")
+    return _TDLoss.apply(q, ptr, action, target, weight, LOSS_KINDS[kind], scale)

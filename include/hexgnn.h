@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define HEXGNN_ABI_VERSION 3
+#define HEXGNN_ABI_VERSION 4
 
 enum {
   HEXGNN_OK = 0,
@@ -140,6 +140,17 @@ int hexgnn_backward(const HexModelDesc* desc, const float* params, const float* 
                     int64_t B, const void* csr, int32_t tile_rows, int32_t flags, const float* d_nodes,
                     const float* d_value, const float* stash, float* grad_params, float* d_embeds,
                     void* ws, size_t ws_bytes, void* stream);
+
+/* Learner loss glue on device (replaces the index / loss / mean kernels of rainbow.py:301-312 and their autograd):
+ *   td_est[g] = q[ptr[g] + action[g]];  td_err[g] = td_est[g] - target[g]  (PER priorities = |td_err| + 1e-6, :307-308)
+ *   loss[0]   = scale * mean_g( weight[g] * l(target[g], td_est[g]) ),  kind 0: l = MSE, 1: l = SmoothL1 (beta 1), :85
+ *   d_q [N]   = d loss / d q (zero except the B selected rows), OVERWRITTEN; may be NULL (evaluation only)
+ * q [N] f32, ptr [B+1] i64, action [B] i64, target [B] f32, weight [B] f32 or NULL (uniform), td_err [B] or NULL.
+ * `scale` = 1/world_size for data-parallel shards (the mean is over the GLOBAL batch).  One launch, deterministic. */
+#define HEXGNN_LOSS_MSE 0
+#define HEXGNN_LOSS_SMOOTH_L1 1
+int hexgnn_td_loss(const float* q, const int64_t* ptr, const int64_t* action, const float* target, const float* weight,
+                   int64_t N, int64_t B, int32_t kind, float scale, float* loss, float* td_err, float* d_q, void* stream);
 
 /* Where forward (with `flags`) leaves the body embedding h_L (`final_conv_acts`, models.py:553) inside the stash:
  * float offset of a row-major [N, row_pitch] block.  (The two kernel paths keep different stash formats.) */

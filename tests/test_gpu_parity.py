@@ -221,3 +221,27 @@ def test_cpu_tensors_are_rejected_loudly():
     b = _batch(CONFIGS["S"], "play", 1, 2)
     with pytest.raises(_lib.HexGnnError):
         m(b.x, b.edge_index, b.batch, b.ptr)
+
+
+@pytest.mark.parametrize("kind", ["mse", "smooth_l1"])
+@pytest.mark.parametrize("weighted", [True, False])
+def test_td_loss_matches_torch(kind, weighted):
+    """hexgnn_td_loss (rainbow.py:301-312 on device) vs the same expression in torch: loss, td errors, dloss/dq."""
+    from gnn_hex_b200 import ops
+    b = data.collate(data.load_positions("pos_7x7_seed1234.npz", maker=1)[:97])
+    action, target, weight = loss_inputs(b)
+    g = torch.Generator().manual_seed(5)
+    q = (torch.randn(b.x.shape[0], generator=g) * 1.5).requires_grad_(True)   # |err| on both sides of 1
+    w = weight if weighted else None
+    td_est = q[action + b.ptr[:-1]]
+    fn = torch.nn.MSELoss(reduction="none") if kind == "mse" else torch.nn.SmoothL1Loss(reduction="none")
+    losses = fn(target, td_est)
+    ref = torch.mean(w * losses) if weighted else torch.mean(losses)
+    (ref * 0.5).backward()
+    qd = q.detach().to(DEV).requires_grad_(True)
+    loss, err = ops.td_loss(qd, b.ptr.to(DEV), action.to(DEV), target.to(DEV), None if w is None else w.to(DEV), kind, 0.5)
+    loss.backward()
+    assert abs(float(loss) - 0.5 * float(ref)) <= 1e-6 * max(1.0, abs(float(ref)))
+    assert torch.allclose(err.cpu(), (td_est - target).detach(), atol=1e-6)
+    assert torch.allclose(qd.grad.cpu(), q.grad, atol=1e-7, rtol=1e-5)
+    assert int((qd.grad != 0).sum()) <= b.num_graphs
