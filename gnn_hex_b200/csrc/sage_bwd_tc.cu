@@ -64,8 +64,8 @@ struct BwdTcSmem {
   static constexpr int off_gp = off_rowptr + (kTcRows + 4) * 4;                  // int [64+4]
   static constexpr int off_col = off_gp + (kMaxTileGraphs + 4) * 4;              // u16 [ECAP]
   static constexpr int off_gtab = (off_col + ECAP * 2 + 15) & ~15;               // gather table (sage_tc.cuh)
-  static constexpr int off_bar = off_gtab + gather_tab_bytes();                  // u64 [2*stages + 3], u32 slot
-  static constexpr int bytes = off_bar + (2 * kBwdStages + 3) * 8 + 16;
+  static constexpr int off_bar = off_gtab + gather_tab_bytes();                  // u64 [2*stages + 6], u32 slot
+  static constexpr int bytes = off_bar + (2 * kBwdStages + 6) * 8 + 16;
 };
 
 struct TileDimsB { int g0, g1, r0, n, e0, ne; bool ok; };
@@ -120,8 +120,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
   const GatherTab gtab = gather_tab_view(smem + S::off_gtab);
   uint64_t* bar_full = (uint64_t*)(smem + S::off_bar);
   uint64_t* bar_empty = bar_full + kBwdStages;
-  uint64_t* bar_a = bar_empty + kBwdStages;
-  uint64_t* bar_r = bar_a + 1;
+  uint64_t* bar_a = bar_empty + kBwdStages;   // [4]: column quarter gi of the A operand is in TMEM
+  uint64_t* bar_r = bar_a + 4;
   uint64_t* bar_d = bar_r + 1;
   uint32_t* tmem_slot = (uint32_t*)(bar_d + 1);
 
@@ -133,7 +133,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
 
   if (tid == 0) {
     for (int i = 0; i < kBwdStages; ++i) { mbar_init(&bar_full[i], 1); mbar_init(&bar_empty[i], 1); }
-    mbar_init(bar_a, kTcEpiThreads);
+    for (int i = 0; i < 4; ++i) mbar_init(&bar_a[i], kTcEpiWarps);
     mbar_init(bar_r, 1);
     mbar_init(bar_d, 1);
     fence_mbar_init();
@@ -172,10 +172,13 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
         if (!tile_dims_b(a.csr, t, S::ECAP).ok) continue;
         for (int s = Lt - 1; s >= 1; --s) {
           for (int which = 0; which < 2; ++which) {
-            mbar_wait(bar_a, na & 1);   // A operand (dpre, then dZl) is in TMEM
-            ++na;
-            tc_fence_after();
             for (int q = 0; q < NQ; ++q, ++it) {
+              if ((q & 1) == 0) {
+                // granules 2q .. 2q+3 of the A operand (dpre, then dZl) are in TMEM; the epilogue releases it quarter
+                // by quarter, so these MMAs run under the rest of its E1 / E3
+                mbar_wait(&bar_a[q >> 1], na & 1);
+                tc_fence_after();
+              }
               const int st = it % kBwdStages;
               mbar_wait(&bar_full[st], (it / kBwdStages) & 1);
               tc_fence_after();
@@ -193,6 +196,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
               mma_commit(&bar_empty[st]);
             }
             mma_commit(which == 0 ? bar_r : bar_d);
+            ++na;
           }
         }
       }
@@ -473,15 +477,15 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
               dd[0] = make_float4(sc[0], sc[1], sc[2], sc[3]);
               dd[1] = make_float4(sc[4], sc[5], sc[6], sc[7]);
               if (row < n32) {
-                float4* dst = (float4*)(zimg + rm32_granule_off(NG + g, row));
-                dst[0] = make_float4(dh[gi][0], dh[gi][1], dh[gi][2], dh[gi][3]);
-                dst[1] = make_float4(dh[gi][4], dh[gi][5], dh[gi][6], dh[gi][7]);
+                st_global_v8(zimg + rm32_granule_off(NG + g, row), dh[gi][0], dh[gi][1], dh[gi][2], dh[gi][3], dh[gi][4],
+                             dh[gi][5], dh[gi][6], dh[gi][7]);
               }
             }
+            tmem_wait_st();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bar_a[gi]);   // -> MMA: dH_s = dpre * W_r, column quarter gi
           }
-          tmem_wait_st();
-          tc_fence_before();
-          mbar_arrive(bar_a);        // -> MMA: dH_s = dpre * W_r
         }
         epi_bar_b();                 // dump (dpre / deg) complete
         PH_ADD(ph1, tq);
@@ -504,8 +508,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
               acc[gi][0] = v0.x; acc[gi][1] = v0.y; acc[gi][2] = v0.z; acc[gi][3] = v0.w;
               acc[gi][4] = v1.x; acc[gi][5] = v1.y; acc[gi][6] = v1.z; acc[gi][7] = v1.w;
               if (row < n32) {
-                float4* dst = (float4*)(zimg + rm32_granule_off(g, row));
-                dst[0] = v0; dst[1] = v1;
+                st_global_v8(zimg + rm32_granule_off(g, row), v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w);
               }
             }
           }
@@ -522,10 +525,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
               tmem_st8(trow + TM_HI + g * 8, hi);
               tmem_st8(trow + TM_LO + g * 8, lo);
             }
+            tmem_wait_st();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bar_a[gi]);   // -> MMA: dH_s += dZl * W_l, column quarter gi
           }
-          tmem_wait_st();
-          tc_fence_before();
-          mbar_arrive(bar_a);            // -> MMA: dH_s += dZl * W_l
         }
         PH_ADD(ph3, tq);
       }

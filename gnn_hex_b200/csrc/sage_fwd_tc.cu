@@ -275,9 +275,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
           tmem_st8(trow + TM_HI + g * 8, hi);
           tmem_st8(trow + TM_LO + g * 8, lo);
           if (st_img && row < n32) {
-            float4* dst = (float4*)(st_img + rm32_granule_off(g, row));
-            dst[0] = make_float4(v[0], v[1], v[2], v[3]);
-            dst[1] = make_float4(v[4], v[5], v[6], v[7]);
+            st_global_v8(st_img + rm32_granule_off(g, row), v[0], v[1], v[2], v[3], v[4], v[5], v[6], v[7]);
           }
           if (emb && a.d.L == 1 && live) {
             float4* dst = (float4*)(emb + (int64_t)(r0 + row) * Hp + g * 8);
@@ -286,9 +284,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
           }
         }
         if (st_img && slice == 0 && row < n32) {   // ones channel (bias gradient row of h^T dZ)
-          float4* dst = (float4*)(st_img + rm32_granule_off(NG, row));
-          dst[0] = make_float4(live ? 1.f : 0.f, 0.f, 0.f, 0.f);
-          dst[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+          st_global_v8(st_img + rm32_granule_off(NG, row), live ? 1.f : 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f);
         }
         if (mask_t) mask_t[0] = mw;
         tmem_wait_st();
@@ -370,9 +366,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
                 split_tf32(r, hi[u], lo[u]);
               }
               if (st) {
-                float4* dst = (float4*)(st + rm32_granule_off(g, row));
-                dst[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
-                dst[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+                st_global_v8(st + rm32_granule_off(g, row), acc[0], acc[1], acc[2], acc[3], acc[4], acc[5], acc[6], acc[7]);
               }
               if (emb && s == a.d.L - 1 && live) {
                 float4* dst = (float4*)(emb + (int64_t)(r0 + row) * Hp + g * 8);
@@ -396,9 +390,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
           if (mask_t) mask_t[(size_t)s * mask_layer] = mw;
         }
         if (st && slice == 0) {
-          float4* dst = (float4*)(st + rm32_granule_off(NG, row));
-          dst[0] = make_float4(live ? 1.f : 0.f, 0.f, 0.f, 0.f);
-          dst[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+          st_global_v8(st + rm32_granule_off(NG, row), live ? 1.f : 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f);
         }
         PH_ADD(ph13, tq);
         tmem_wait_st();

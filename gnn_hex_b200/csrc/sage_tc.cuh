@@ -93,24 +93,43 @@ inline int64_t tc_imgB_floats(const Dims& d) { return (int64_t)(d.Lt - 1) * 2 * 
 
 // ---- the CSR gather of both fused kernels -----------------------------------------------------------------------
 // agg[r] = sum over the CSR row r of src[col], r < n, for a [128 + 1][P] row-major shared tile whose row 128 is zeros.
-// The kernels are instruction-issue bound, so the gather runs off a per-tile TABLE built once and replayed by every
-// layer: warp w owns the row groups {w + 16 (4 it + i), i < 4}, it = 0, 1; step k of a group is ONE int4 of byte
-// offsets (neighbour k of each of its 4 rows; rows that have run out point at the zero row).  Per step: one broadcast
-// 16-byte table load, four contiguous-row float4 loads (lane = one float4: no bank conflicts whatever the ids), eight
-// packed FADD2.  Summation order per row = CSR order (deterministic).
-constexpr int kGatherGroups = 2 * kTcEpiWarps;       // 32 groups of 4 rows
+// The kernels are issue / shared-bandwidth bound, so the gather runs off a per-tile TABLE built once and replayed by
+// every layer.  A group = 4 accumulator slots walked in lock step; step k of a group is ONE int4 of byte offsets
+// (the k-th neighbour of each slot; slots that have run out point at the zero row).  Normal groups hold 4 rows; a LONG
+// row (degree > kGatherLong: the two terminal nodes of every Hex graph reach 20-30) gets a group of its own whose 4
+// slots are 4 contiguous segments of its neighbour list, summed ((s0+s1)+s2)+s3 at the end -- otherwise one warp
+// would walk 25 steps while fifteen wait at the barrier.  Groups go round-robin over the 16 epilogue warps.
+// Per step: one broadcast 16-byte table load, four contiguous-row float4 loads (lane = one float4: no bank conflicts
+// whatever the ids), eight packed FADD2.  Summation order is fixed (deterministic).
+constexpr int kGatherMaxGroups = 48;                  // <= 16 long rows + 32 normal groups
+constexpr int kGatherLong = 8;
+constexpr int kGatherMaxLong = 16;
 struct GatherTab {
   int4* tab;        // [<= kEdgeCapPerRow * kTcRows] steps
-  int* gstart;      // [kGatherGroups]
-  int* glen;        // [kGatherGroups]
+  int* gstart;      // [kGatherMaxGroups]
+  int* glen;        // [kGatherMaxGroups]
+  int4* grow;       // [kGatherMaxGroups] destination row per slot (-1 none; y == -2: long row x in 4 segments)
+  int* ngroups;     // [1]
 };
-__host__ __device__ constexpr int gather_tab_bytes() { return kEdgeCapPerRow * kTcRows * 16 + 2 * kGatherGroups * 4; }
+__host__ __device__ constexpr int gather_tab_bytes() {
+  return kEdgeCapPerRow * kTcRows * 16 + kGatherMaxGroups * (4 + 4 + 16) + 16;
+}
 __device__ __forceinline__ GatherTab gather_tab_view(uint8_t* base) {
   GatherTab g;
   g.tab = (int4*)base;
-  g.gstart = (int*)(base + kEdgeCapPerRow * kTcRows * 16);
-  g.glen = g.gstart + kGatherGroups;
+  g.grow = (int4*)(base + kEdgeCapPerRow * kTcRows * 16);
+  g.gstart = (int*)(g.grow + kGatherMaxGroups);
+  g.glen = g.gstart + kGatherMaxGroups;
+  g.ngroups = g.glen + kGatherMaxGroups;
   return g;
+}
+__device__ __forceinline__ int warp_scan_incl(int v, int lane) {
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, v, o);
+    if (lane >= o) v += t;
+  }
+  return v;
 }
 // Build the table of one tile (all epilogue threads; rowptr_s / col_s complete; ends with the epilogue barrier).
 template <int NJ>
@@ -118,35 +137,70 @@ __device__ __forceinline__ void gather_build(const GatherTab& g, const int* __re
                                              const unsigned short* __restrict__ col_s, int n, int tid) {
   constexpr int PB = (16 * NJ + 4) * 4;   // row pitch in bytes
   const int wid = tid >> 5, lane = tid & 31;
-  if (wid == 0) {   // lane = group: length = longest of its 4 rows, exclusive scan over the groups
-    const int w = lane & (kTcEpiWarps - 1), it = lane / kTcEpiWarps;
-    int len = 0;
+  for (int i = tid; i < kGatherMaxGroups; i += kTcEpiThreads) { g.glen[i] = 0; g.grow[i] = make_int4(-1, -1, -1, -1); }
+  asm volatile("bar.sync 1, %0;" ::"n"(kTcEpiThreads) : "memory");
+  if (wid == 0) {   // lane = rows 4*lane .. 4*lane+3: classify, then place every row into (group, slot)
+    int deg[4], cl = 0, cn = 0;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int r = w + kTcEpiWarps * (4 * it + i);
-      const int d = r < n ? rowptr_s[r + 1] - rowptr_s[r] : 0;
-      len = d > len ? d : len;
+    for (int j = 0; j < 4; ++j) {
+      const int r = 4 * lane + j;
+      deg[j] = r < n ? rowptr_s[r + 1] - rowptr_s[r] : -1;
+      cl += deg[j] > kGatherLong;
+      cn += deg[j] >= 0;
     }
-    int inc = len;
+    const int totl = warp_scan_incl(cl, lane);
+    const int L_all = __shfl_sync(0xffffffffu, totl, 31);
+    const int thr = L_all <= kGatherMaxLong ? kGatherLong : 0x7fffffff;   // too many long rows: split none
+    cl = 0;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int t = __shfl_up_sync(0xffffffffu, inc, o);
-      if (lane >= o) inc += t;
+    for (int j = 0; j < 4; ++j) cl += deg[j] > thr;
+    cn -= cl;
+    const int v = (cl << 16) | cn;
+    const int inc = warp_scan_incl(v, lane);
+    const int tot = __shfl_sync(0xffffffffu, inc, 31);
+    const int L = tot >> 16, NN = tot & 0xffff;
+    int li = (inc - v) >> 16, ni = (inc - v) & 0xffff;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int r = 4 * lane + j, d = deg[j];
+      if (d < 0) continue;
+      if (d > thr) {
+        g.grow[li] = make_int4(r, -2, -2, -2);
+        g.glen[li] = (d + 3) >> 2;
+        ++li;
+      } else {
+        const int grp = L + (ni >> 2);
+        ((int*)&g.grow[grp])[ni & 3] = r;
+        atomicMax(&g.glen[grp], d);
+        ++ni;
+      }
     }
-    g.gstart[lane] = inc - len;
-    g.glen[lane] = len;
+    if (lane == 0) *g.ngroups = L + ((NN + 3) >> 2);
+    __syncwarp();
+    // exclusive scan of the group lengths (48 groups: lanes take group l and group 32 + l)
+    const int l0 = g.glen[lane], l1 = lane < kGatherMaxGroups - 32 ? g.glen[32 + lane] : 0;
+    const int i0 = warp_scan_incl(l0, lane), i1 = warp_scan_incl(l1, lane);
+    const int t0 = __shfl_sync(0xffffffffu, i0, 31);
+    g.gstart[lane] = i0 - l0;
+    if (lane < kGatherMaxGroups - 32) g.gstart[32 + lane] = t0 + i1 - l1;
   }
   asm volatile("bar.sync 1, %0;" ::"n"(kTcEpiThreads) : "memory");
-#pragma unroll
-  for (int it = 0; it < 2; ++it) {
-    const int gi = it * kTcEpiWarps + wid;
+  const int ng = *g.ngroups;
+  for (int gi = wid; gi < ng; gi += kTcEpiWarps) {
     const int len = g.glen[gi], st = g.gstart[gi];
+    const int4 rw = g.grow[gi];
     int b[4], d[4];
+    if (rw.y == -2) {   // long row: slot i = neighbours [i*len, (i+1)*len)
+      const int b0 = rowptr_s[rw.x], d0 = rowptr_s[rw.x + 1] - b0;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int r = wid + kTcEpiWarps * (4 * it + i);
-      b[i] = r < n ? rowptr_s[r] : 0;
-      d[i] = r < n ? rowptr_s[r + 1] - b[i] : 0;
+      for (int i = 0; i < 4; ++i) { b[i] = b0 + i * len; d[i] = d0 - i * len; d[i] = d[i] > len ? len : d[i]; }
+    } else {
+      const int rr[4] = {rw.x, rw.y, rw.z, rw.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        b[i] = rr[i] >= 0 ? rowptr_s[rr[i]] : 0;
+        d[i] = rr[i] >= 0 ? rowptr_s[rr[i] + 1] - b[i] : 0;
+      }
     }
     for (int k = lane; k < len; k += 32) {
       int4 o;
@@ -177,11 +231,11 @@ __device__ __forceinline__ void tile_gather(const GatherTab& g, const float* __r
   if (lane >= NV) return;                       // warp-uniform loops below: no collective inside
   const char* sb = (const char*)src + lane * 16;
   float4* a4 = (float4*)agg + lane;
-#pragma unroll
-  for (int it = 0; it < 2; ++it) {
-    const int gi = it * kTcEpiWarps + wid;
+  const int ng = *g.ngroups;
+  for (int gi = wid; gi < ng; gi += kTcEpiWarps) {
     const int len = g.glen[gi];
     const int4* tp = g.tab + g.gstart[gi];
+    const int4 rw = g.grow[gi];
     float4 acc[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -201,10 +255,14 @@ __device__ __forceinline__ void tile_gather(const GatherTab& g, const float* __r
       const float4 v2 = *(const float4*)(sb + o0.z), v3 = *(const float4*)(sb + o0.w);
       fadd2x2(acc[0], v0); fadd2x2(acc[1], v1); fadd2x2(acc[2], v2); fadd2x2(acc[3], v3);
     }
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int r = wid + kTcEpiWarps * (4 * it + i);
-      if (r < n) a4[r * PV] = acc[i];
+    if (rw.y == -2) {
+      fadd2x2(acc[0], acc[1]); fadd2x2(acc[0], acc[2]); fadd2x2(acc[0], acc[3]);
+      a4[rw.x * PV] = acc[0];
+    } else {
+      if (rw.x >= 0) a4[rw.x * PV] = acc[0];
+      if (rw.y >= 0) a4[rw.y * PV] = acc[1];
+      if (rw.z >= 0) a4[rw.z * PV] = acc[2];
+      if (rw.w >= 0) a4[rw.w * PV] = acc[3];
     }
   }
 }

@@ -94,6 +94,13 @@ __device__ __forceinline__ void tmem_st8(uint32_t taddr, const float (&v)[8]) {
                : "memory");
 }
 
+// ---- 256-bit global store (sm_100+: STG.256): one full 32-byte sector per thread and instruction -----------------
+__device__ __forceinline__ void st_global_v8(void* p, float v0, float v1, float v2, float v3, float v4, float v5,
+                                             float v6, float v7) {
+  asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(v0), "f"(v1), "f"(v2), "f"(v3),
+               "f"(v4), "f"(v5), "f"(v6), "f"(v7) : "memory");
+}
+
 // ---- 3xTF32 split -----------------------------------------------------------------------------------
 // hi = rn_tf32(a), lo = rn_tf32(a - hi): a = hi + lo up to 2^-23 |a|; the tensor core sees exact tf32.
 __device__ __forceinline__ float tf32_rn(float a) {
