@@ -32,13 +32,13 @@ int bwd_grid_ctas() {
 // ---- profiling: thread-local event pairs --------------------------------------------------------
 struct ProfState {
   bool on = false;
-  std::vector<cudaEvent_t> ev[2];  // start, stop, start, stop, ...
-  size_t used[2] = {0, 0};
+  std::vector<cudaEvent_t> ev[3];  // start, stop, start, stop, ...
+  size_t used[3] = {0, 0, 0};
 };
 static ProfState g_prof;  // process-wide: autograd runs hexgnn_backward on its own thread
 
 ProfScope::ProfScope(int which, cudaStream_t st) : slot_(-1), st_(st) {
-  if (!g_prof.on || which < 0 || which > 1) return;
+  if (!g_prof.on || which < 0 || which > 2) return;
   auto& v = g_prof.ev[which];
   size_t& u = g_prof.used[which];
   if (u + 2 > v.size()) {
@@ -239,12 +239,12 @@ int hexgnn_debug_phases(int32_t which, int64_t* host_out, int32_t n) {
 
 int hexgnn_profile_enable(int on) {
   g_prof.on = on != 0;
-  if (!on) g_prof.used[0] = g_prof.used[1] = 0;
+  if (!on) g_prof.used[0] = g_prof.used[1] = g_prof.used[2] = 0;
   return HEXGNN_OK;
 }
 
 int hexgnn_profile_read(int which, double* total_ms, int64_t* launches) {
-  if (which < 0 || which > 1 || !total_ms || !launches) { set_error("profile_read: bad argument"); return HEXGNN_E_BADARG; }
+  if (which < 0 || which > 2 || !total_ms || !launches) { set_error("profile_read: bad argument"); return HEXGNN_E_BADARG; }
   double tot = 0.0;
   const size_t u = g_prof.used[which];
   for (size_t i = 0; i + 1 < u; i += 2) {

@@ -66,41 +66,49 @@ int launch_pack_tc(const Dims& d, const ParamMap& pm, const float* params, const
 //   gw and gb[s>=1]  <- the G group records of sage_dw_tc_kernel   (big_rec [G][gl.g0])
 //   gv0              <- sum over graphs (in graph order) of dt_g (x) pooled_g from the head records
 //   everything else  <- the per-CTA records of sage_bwd_tc_kernel  (small_rec [nsmall][gl.total - gl.gb])
-__global__ void __launch_bounds__(256) reduce_tc_kernel(GradLayout gl, int Hp, int H, int H2,
-                                                        const float* __restrict__ small_rec, int nsmall,
-                                                        const float* __restrict__ big_rec, int G,
-                                                        const float* __restrict__ head_rec, int hrec_n, int B, int nmain,
-                                                        float* __restrict__ out) {
+constexpr int kRedThreads = 1024;   // gv0 blocks: 128 q x 8 graph slices
+__global__ void __launch_bounds__(kRedThreads) reduce_tc_kernel(GradLayout gl, int Hp, int H, int H2,
+                                                                const float* __restrict__ small_rec, int nsmall,
+                                                                const float* __restrict__ big_rec, int G,
+                                                                const float* __restrict__ head_rec, int hrec_n, int B,
+                                                                int nmain, float* __restrict__ out) {
   if ((int)blockIdx.x >= nmain) {
-    // gv0[k][q] = sum_g dt_g[k] * pooled_g[q]: block = 128 q x 8 k, the two thread halves take the two halves of
-    // the graph range (sequential inside a half, halves combined in a fixed order: deterministic).
-    __shared__ float part[8][128];
+    // gv0[k][q] = sum_g dt_g[k] * pooled_g[q]: block = 128 q x 8 k; the 8 thread slices take 8 contiguous ranges of
+    // the graphs (sequential inside a range, ranges combined in slice order: deterministic).  Many short independent
+    // chains: the loop is DRAM/L2-latency bound otherwise (the records were just written by the chain kernel).
+    __shared__ float part[8][8][128];
     const int H2p = (H2 + 3) & ~3, Q = 4 * H;
     const int nqb = (Q + 127) / 128;
     const int bid = blockIdx.x - nmain, qb = bid % nqb, kb = bid / nqb;
-    const int q = qb * 128 + (threadIdx.x & 127), half = threadIdx.x >> 7, k0 = kb * 8;
-    const int Bh = (B + 1) / 2;
-    const int ga = half * Bh, gb = (ga + Bh < B) ? ga + Bh : B;
+    const int ql = threadIdx.x & 127, q = qb * 128 + ql, sl = threadIdx.x >> 7, k0 = kb * 8;
+    const int Bs = (B + 7) / 8;
+    const int ga = sl * Bs, gb = (ga + Bs < B) ? ga + Bs : B;
     float acc[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[j] = 0.f;
     if (q < Q) {
       const float* hr = head_rec + (int64_t)ga * hrec_n;
+#pragma unroll 4
       for (int g = ga; g < gb; ++g, hr += hrec_n) {
         const float pv = hr[H2p + q];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] = fmaf(k0 + j < H2 ? hr[k0 + j] : 0.f, pv, acc[j]);
+        const float4 d0 = *(const float4*)(hr + k0), d1 = *(const float4*)(hr + k0 + 4);   // padded with zeros
+        acc[0] = fmaf(d0.x, pv, acc[0]); acc[1] = fmaf(d0.y, pv, acc[1]);
+        acc[2] = fmaf(d0.z, pv, acc[2]); acc[3] = fmaf(d0.w, pv, acc[3]);
+        acc[4] = fmaf(d1.x, pv, acc[4]); acc[5] = fmaf(d1.y, pv, acc[5]);
+        acc[6] = fmaf(d1.z, pv, acc[6]); acc[7] = fmaf(d1.w, pv, acc[7]);
       }
     }
-    if (half == 1) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) part[j][threadIdx.x & 127] = acc[j];
-    }
+    for (int j = 0; j < 8; ++j) part[sl][j][ql] = acc[j];
     __syncthreads();
-    if (half == 0 && q < Q) {
+    if (sl == 0 && q < Q) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j)
-        if (k0 + j < H2) out[gl.gv0 + (int64_t)(k0 + j) * Q + q] = acc[j] + part[j][threadIdx.x];
+      for (int j = 0; j < 8; ++j) {
+        float u = part[0][j][ql];
+#pragma unroll
+        for (int t = 1; t < 8; ++t) u += part[t][j][ql];
+        if (k0 + j < H2) out[gl.gv0 + (int64_t)(k0 + j) * Q + q] = u;
+      }
     }
     return;
   }
@@ -113,7 +121,15 @@ __global__ void __launch_bounds__(256) reduce_tc_kernel(GradLayout gl, int Hp, i
     if (from_big) {
       for (int g = 0; g < G; ++g) acc += big_rec[(int64_t)g * gl.g0 + i];
     } else {
-      for (int p = 0; p < nsmall; ++p) acc += small_rec[(int64_t)p * recn + (i - gl.gb)];
+      float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;   // 4 interleaved chains, fixed combination order
+      const float* sp = small_rec + (i - gl.gb);
+      int p = 0;
+      for (; p + 4 <= nsmall; p += 4) {
+        a0 += sp[(int64_t)p * recn]; a1 += sp[(int64_t)(p + 1) * recn];
+        a2 += sp[(int64_t)(p + 2) * recn]; a3 += sp[(int64_t)(p + 3) * recn];
+      }
+      for (; p < nsmall; ++p) a0 += sp[(int64_t)p * recn];
+      acc = (a0 + a1) + (a2 + a3);
     }
     out[i] = acc;
   }
@@ -123,10 +139,10 @@ int launch_reduce_tc(const Dims& d, const float* small_rec, int nsmall, const fl
                      const float* head_rec, int64_t B, float* packed_sum, cudaStream_t st) {
   GradLayout gl;
   grad_layout(d, &gl);
-  int blocks = (int)((gl.total + 255) / 256);
-  if (blocks > 1184) blocks = 1184;
+  int blocks = (int)((gl.total + kRedThreads - 1) / kRedThreads);
+  if (blocks > 592) blocks = 592;
   const int gv0_blocks = ((4 * d.H + 127) / 128) * ((d.H2 + 7) / 8);
-  reduce_tc_kernel<<<blocks + gv0_blocks, 256, 0, st>>>(gl, d.Hp, d.H, d.H2, small_rec, nsmall, big_rec, G, head_rec,
+  reduce_tc_kernel<<<blocks + gv0_blocks, kRedThreads, 0, st>>>(gl, d.Hp, d.H, d.H2, small_rec, nsmall, big_rec, G, head_rec,
                                                         tc_head_rec_floats(d), (int)B, blocks, packed_sum);
   HEX_CUDA_CHECK(cudaGetLastError());
   return HEXGNN_OK;

@@ -180,7 +180,10 @@ static int launch_dw_t(const DwArgs& a, cudaStream_t st) {
   auto kern = sage_dw_tc_kernel<NJ>;
   const size_t smem = (size_t)kDwStages * 2 * (4 * kDwBlk + NJ * kDwBlk) + 1024;
   HEX_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  kern<<<(a.d.Lt - 1) * a.G, kDwThreads, smem, st>>>(a);
+  {
+    ProfScope prof(2, st);
+    kern<<<(a.d.Lt - 1) * a.G, kDwThreads, smem, st>>>(a);
+  }
   HEX_CUDA_CHECK(cudaGetLastError());
   return HEXGNN_OK;
 }

@@ -171,7 +171,7 @@ int hexgnn_debug_phases(int32_t which, int64_t* host_out, int32_t n);
 
 /* Measurement aid (bench.py `roofline`): while enabled (process-wide; NOT re-entrant, use from one
  * stream at a time), hexgnn_forward and
- * hexgnn_backward bracket their dominant kernel (which: 0 = fused forward, 1 = fused backward) with
+ * hexgnn_backward bracket their kernels (which: 0 = fused forward, 1 = backward dH chain, 2 = backward dW GEMM) with
  * CUDA events recorded on `stream`.  hexgnn_profile_read synchronises on the recorded events, returns
  * the summed device time (ms) and the number of bracketed launches since the last read, and resets.
  * This is the only mutable state the library keeps besides the thread-local error string. */
