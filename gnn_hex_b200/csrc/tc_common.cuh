@@ -103,10 +103,10 @@ __device__ __forceinline__ void st_global_v8(void* p, float v0, float v1, float 
 
 // ---- 3xTF32 split -----------------------------------------------------------------------------------
 // hi = rn_tf32(a), lo = rn_tf32(a - hi): a = hi + lo up to 2^-23 |a|; the tensor core sees exact tf32.
+// Round-to-nearest, ties away from zero (== cvt.rna.tf32.f32 for finite inputs) on the integer pipe: the conversion
+// unit behind cvt.rna is a low-throughput pipe and was the top stall of the split warps (ncu: stall_math on the cvt).
 __device__ __forceinline__ float tf32_rn(float a) {
-  uint32_t r;
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(a));
-  return __uint_as_float(r);
+  return __uint_as_float((__float_as_uint(a) + 0x1000u) & 0xffffe000u);
 }
 __device__ __forceinline__ void split_tf32(float a, float& hi, float& lo) {
   hi = tf32_rn(a);
