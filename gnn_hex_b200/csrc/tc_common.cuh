@@ -26,12 +26,27 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// Bounded wait: a protocol bug must fault (trap -> cudaErrorLaunchFailure), never hang the GPU.
+// try_wait with a suspend-time hint (ns): the hardware parks the thread until the phase completes or the hint
+// expires, instead of returning at once -- a waiting warp then costs (almost) no issue slots.
+__device__ __forceinline__ bool mbar_try_wait_hint(uint64_t* bar, uint32_t parity, uint32_t ns) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity), "r"(ns)
+      : "memory");
+  return ok != 0;
+}
+// Bounded wait: a protocol bug must fault (trap -> cudaErrorLaunchFailure), never hang the GPU.  The clock is read
+// once per 1024 polls so the poll loop itself stays three instructions long.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   const long long t0 = clock64();
-  while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > 8000000000ll) __trap();   // ~4 s at 2 GHz
+  uint32_t polls = 0;
+  while (!mbar_try_wait_hint(bar, parity, 20000u)) {
+    if ((++polls & 1023u) == 0 && clock64() - t0 > 8000000000ll) __trap();   // ~4 s at 2 GHz
   }
 }
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
