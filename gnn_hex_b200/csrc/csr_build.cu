@@ -45,48 +45,57 @@ __global__ void csr_hist_kernel(CsrView v, const int64_t* __restrict__ ei, int E
 }
 
 // ---- 3. exclusive scan of the histogram (single CTA; N is a few 10^4..10^5) ----------------------
+// Warp w owns a contiguous range (a multiple of 128 entries); inside it a step is one coalesced int4 per lane.
+// Pass 1: every lane sums its int4s of all steps (independent loads, all in flight), warp reduce, the 32 warp totals
+// are scanned; pass 2 re-reads (cache hot), does the in-step scan with shuffles and writes rowptr.
 __global__ void __launch_bounds__(1024) csr_scan_kernel(CsrView v, int N) {
   __shared__ int warp_sums[32];
-  __shared__ int carry_s;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  if (tid == 0) carry_s = 0;
+  const int M = N + 1;
+  const int per_warp = ((M + 31) / 32 + 127) / 128 * 128;
+  const int w0 = wid * per_warp, w1 = (w0 + per_warp < M) ? w0 + per_warp : M;
+  const int4* c4 = (const int4*)v.cursor;
+  int tsum = 0;
+  for (int base = w0; base < w1; base += 128) {
+    const int i = base + lane * 4;
+    if (i + 3 < M) { const int4 a = c4[i >> 2]; tsum += a.x + a.y + a.z + a.w; }
+    else { for (int k = 0; k < 4; ++k) if (i + k < M) tsum += v.cursor[i + k]; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) tsum += __shfl_xor_sync(0xffffffffu, tsum, o);
+  if (lane == 0) warp_sums[wid] = tsum;
   __syncthreads();
-  // each iteration scans 1024*4 entries
-  for (int base = 0; base <= N; base += 4096) {
-    const int i0 = base + tid * 4;
+  if (wid == 0) {
+    const int ws = warp_sums[lane];
+    int winc = ws;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      int t = __shfl_up_sync(0xffffffffu, winc, o);
+      if (lane >= o) winc += t;
+    }
+    warp_sums[lane] = winc - ws;  // exclusive
+  }
+  __syncthreads();
+  int carry = warp_sums[wid];
+  for (int base = w0; base < w1; base += 128) {
+    const int i = base + lane * 4;
     int a[4];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) a[k] = (i0 + k <= N) ? v.cursor[i0 + k] : 0;
-    const int tsum = a[0] + a[1] + a[2] + a[3];
-    int inc = tsum;
+    for (int k = 0; k < 4; ++k) a[k] = (i + k < M) ? v.cursor[i + k] : 0;
+    const int ls = a[0] + a[1] + a[2] + a[3];
+    int inc = ls;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
       int t = __shfl_up_sync(0xffffffffu, inc, o);
       if (lane >= o) inc += t;
     }
-    if (lane == 31) warp_sums[wid] = inc;
-    __syncthreads();
-    if (wid == 0) {
-      int ws = warp_sums[lane];
-      int winc = ws;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        int t = __shfl_up_sync(0xffffffffu, winc, o);
-        if (lane >= o) winc += t;
-      }
-      warp_sums[lane] = winc - ws;  // exclusive
-    }
-    __syncthreads();
-    const int carry = carry_s;
-    int ex = carry + warp_sums[wid] + inc - tsum;
+    int ex = carry + inc - ls;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      if (i0 + k <= N) { v.rowptr[i0 + k] = ex; v.cursor[i0 + k] = 0; }
+      if (i + k < M) { v.rowptr[i + k] = ex; v.cursor[i + k] = 0; }
       ex += a[k];
     }
-    __syncthreads();
-    if (tid == 1023) carry_s = ex;
-    __syncthreads();
+    carry += __shfl_sync(0xffffffffu, inc, 31);
   }
 }
 
@@ -142,19 +151,20 @@ __global__ void csr_fill_kernel(CsrView v, const int64_t* __restrict__ ei, int E
   }
 }
 
-// ---- 5. per-row sort by edge id (=> stable), emit sources ----------------------------------------
-__global__ void csr_sort_kernel(CsrView v, const int64_t* __restrict__ ei, int N) {
+// ---- 5. stable order inside every row: one thread per CSR slot ------------------------------------
+// Slot p holds edge id eid[p] of row d = dst(eid[p]); its final position is the number of edge ids of the same row
+// that are smaller (input order == stable sort by destination).  All threads independent: no dependent
+// read-modify-write chains in global memory (the per-row insertion sort this replaces was latency bound).
+__global__ void csr_rank_kernel(CsrView v, const int64_t* __restrict__ ei, int E, int N) {
   const int nth = gridDim.x * blockDim.x;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += nth) {
-    const int b = v.rowptr[i], e = v.rowptr[i + 1];
-    // insertion sort: rows hold <= ~25 entries for Hex graphs
-    for (int p = b + 1; p < e; ++p) {
-      const int key = v.eid[p];
-      int q = p - 1;
-      while (q >= b && v.eid[q] > key) { v.eid[q + 1] = v.eid[q]; --q; }
-      v.eid[q + 1] = key;
-    }
-    for (int p = b; p < e; ++p) v.col[p] = (int)ei[v.eid[p]];
+  const int filled = v.rowptr[N];   // < E only when edges were rejected (status flagged): those slots hold no id
+  for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < filled; p += nth) {
+    const int me = v.eid[p];
+    const int d = (int)ei[(int64_t)E + me];
+    const int b = v.rowptr[d], e = v.rowptr[d + 1];
+    int rank = 0;
+    for (int q = b; q < e; ++q) rank += v.eid[q] < me;
+    v.col[b + rank] = (int)ei[me];
   }
 }
 
@@ -169,7 +179,7 @@ int launch_build_csr(const int64_t* edge_index, int64_t E, const int64_t* batch,
   csr_scan_kernel<<<1, 1024, 0, st>>>(v, (int)N);
   csr_fill_kernel<<<blocks(E) + 1, threads, 0, st>>>(v, edge_index, (int)E, (int)N, (int)B, tile_rows,
                                                     tile_rows * kEdgeCapPerRow);
-  if (N > 0) csr_sort_kernel<<<blocks(N), threads, 0, st>>>(v, edge_index, (int)N);
+  if (E > 0) csr_rank_kernel<<<blocks(E), threads, 0, st>>>(v, edge_index, (int)E, (int)N);
   HEX_CUDA_CHECK(cudaGetLastError());
   return HEXGNN_OK;
 }

@@ -214,6 +214,10 @@ __device__ __forceinline__ void gather_build(const GatherTab& g, const int* __re
   asm volatile("bar.sync 1, %0;" ::"n"(kTcEpiThreads) : "memory");
 }
 __device__ __forceinline__ void fadd2x2(float4& a, const float4& b) {   // a += b as two packed f32x2 adds
+#ifdef HEXGNN_EXP_SCALAR_FADD
+  a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+  return;
+#endif
   unsigned long long a0, a1, b0, b1;
   asm("mov.b64 %0, {%1, %2};" : "=l"(a0) : "f"(a.x), "f"(a.y));
   asm("mov.b64 %0, {%1, %2};" : "=l"(a1) : "f"(a.z), "f"(a.w));
