@@ -5,5 +5,5 @@ or falls back: a missing library raises on first use (python -m gnn_hex_b200.bui
 """
 from ._lib import HexGnnError  # noqa: F401
 from .models import ModernTwoHeaded, get_pre_defined  # noqa: F401
-from .ops import CsrBlob, build_csr, fused_backward, fused_forward, td_loss  # noqa: F401
+from .ops import CsrBlob, build_csr, fused_backward, fused_forward, mask_argmax, td_loss, td_target  # noqa: F401
 from . import data  # noqa: F401

@@ -215,6 +215,34 @@ int hexgnn_td_loss(const float* q, const int64_t* ptr, const int64_t* action, co
   return launch_td_loss(q, ptr, action, target, weight, N, B, kind, scale, loss, td_err, d_q, (cudaStream_t)stream);
 }
 
+int hexgnn_forward_big(const HexModelDesc* desc, const float* params, const float* x, int64_t N, int64_t E, int64_t B,
+                       const void* csr, int32_t tile_rows, int32_t flags, int32_t max_rows, float* out_nodes,
+                       float* out_value, void* ws, size_t ws_bytes, void* stream) {
+  Dims d;
+  if (!make_dims(desc, &d)) { set_error("forward_big: bad model descriptor"); return HEXGNN_E_BADARG; }
+  if (!params || !x || !csr || !out_nodes || !ws || N < 1 || B < 1 || E < 0 || max_rows < 1) { set_error("forward_big: bad argument"); return HEXGNN_E_BADARG; }
+  if ((flags & HEXGNN_SEPARATE) && !out_value) { set_error("forward_big: SEPARATE needs out_value"); return HEXGNN_E_BADARG; }
+  if (!tile_rows_ok(tile_rows) || max_rows > 65535 * 32 || B > 0x7fffffff) { set_error("forward_big: unsupported tile_rows / max_rows"); return HEXGNN_E_UNSUPPORTED; }
+  const int64_t need = 2 * N * d.Hp * 4;
+  if ((int64_t)ws_bytes < need) { set_error("forward_big: workspace too small (%zu < %lld)", ws_bytes, (long long)need); return HEXGNN_E_WORKSPACE; }
+  ParamMap pm;
+  make_param_map(d, &pm);
+  return launch_forward_big(d, pm, params, x, N, E, B, csr, tile_rows, flags, max_rows, out_nodes, out_value, (float*)ws,
+                            (cudaStream_t)stream);
+}
+
+int hexgnn_mask_argmax(float* q, const int64_t* ptr, int64_t N, int64_t B, int32_t mask_terminals, float mask_value,
+                       float* out_max, int64_t* out_arg, void* stream) {
+  if (!q || !ptr || N < 1 || B < 1 || B >= (1ll << 26)) { set_error("mask_argmax: bad argument"); return HEXGNN_E_BADARG; }
+  return launch_mask_argmax(q, ptr, N, B, mask_terminals, mask_value, out_max, out_arg, (cudaStream_t)stream);
+}
+
+int hexgnn_td_target(const float* q_target, const int64_t* best, const float* reward, const float* done, float gamma_n,
+                     int64_t N, int64_t B, float* target, void* stream) {
+  if (!q_target || !best || !reward || !done || !target || N < 1 || B < 1 || B >= (1ll << 31)) { set_error("td_target: bad argument"); return HEXGNN_E_BADARG; }
+  return launch_td_target(q_target, best, reward, done, gamma_n, N, B, target, (cudaStream_t)stream);
+}
+
 int hexgnn_stash_embed(const HexModelDesc* desc, int64_t N, int64_t B, int32_t flags, int64_t* offset_floats,
                        int64_t* row_pitch) {
   Dims d;

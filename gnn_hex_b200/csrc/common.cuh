@@ -209,6 +209,13 @@ int launch_unpack_grads(const Dims& d, const ParamMap& pm, const float* x, const
                         cudaStream_t st);
 int launch_td_loss(const float* q, const int64_t* ptr, const int64_t* action, const float* target, const float* weight,
                    int64_t N, int64_t B, int kind, float scale, float* loss, float* td_err, float* d_q, cudaStream_t st);
+int launch_forward_big(const Dims& d, const ParamMap& pm, const float* params, const float* x, int64_t N, int64_t E,
+                       int64_t B, const void* csr, int tile_rows, int flags, int max_rows, float* out_nodes,
+                       float* out_value, float* ws, cudaStream_t st);
+int launch_mask_argmax(float* q, const int64_t* ptr, int64_t N, int64_t B, int mask_terminals, float mask_value,
+                       float* out_max, int64_t* out_arg, cudaStream_t st);
+int launch_td_target(const float* q_target, const int64_t* best, const float* reward, const float* done, float gamma_n,
+                     int64_t N, int64_t B, float* target, cudaStream_t st);
 int launch_tc_selftest(const float* A, const float* B, float* D, int N, int K, int modes, cudaStream_t st);
 
 }  // namespace hexgnn

@@ -58,3 +58,61 @@ int launch_td_loss(const float* q, const int64_t* ptr, const int64_t* action, co
 }
 
 }  // namespace hexgnn
+
+// ---- acting / target glue (rainbow.py:222-225 act, 263-269 td_target) -------------------------------------------
+namespace hexgnn {
+
+// One warp per graph: mask the two terminal rows, then (max, first arg max) over the graph's rows.
+__global__ void mask_argmax_kernel(float* __restrict__ q, const int64_t* __restrict__ ptr, int64_t N, int B,
+                                   int mask_terminals, float mask_value, float* __restrict__ out_max,
+                                   int64_t* __restrict__ out_arg) {
+  const int lane = threadIdx.x & 31;
+  const int g = (int)((blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5);
+  if (g >= B) return;
+  const int64_t r0 = ptr[g], r1 = ptr[g + 1];
+  float best = -INFINITY;
+  int64_t arg = N;   // empty graph: out-of-range index (torch_scatter's fill for empty groups)
+  for (int64_t i = r0 + lane; i < r1; i += 32) {
+    float v = q[i];
+    if (mask_terminals && i < r0 + 2) { v = mask_value; q[i] = v; }
+    if (v > best || (v == best && i < arg)) { best = v; arg = i; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+    const int64_t oa = __shfl_xor_sync(0xffffffffu, arg, o);
+    if (ob > best || (ob == best && oa < arg)) { best = ob; arg = oa; }
+  }
+  if (lane == 0) {
+    if (out_max) out_max[g] = r1 > r0 ? best : 0.f;
+    if (out_arg) out_arg[g] = arg;
+  }
+}
+
+__global__ void td_target_kernel(const float* __restrict__ q_target, const int64_t* __restrict__ best,
+                                 const float* __restrict__ reward, const float* __restrict__ done, float gamma_n,
+                                 int64_t N, int B, float* __restrict__ target) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= B) return;
+  const int64_t i = best[g];
+  const float nq = (i >= 0 && i < N) ? q_target[i] : __int_as_float(0x7fc00000);
+  target[g] = reward[g] + gamma_n * nq * (1.f - done[g]);
+}
+
+int launch_mask_argmax(float* q, const int64_t* ptr, int64_t N, int64_t B, int mask_terminals, float mask_value,
+                       float* out_max, int64_t* out_arg, cudaStream_t st) {
+  const int threads = 256;
+  const int64_t blocks = (B * 32 + threads - 1) / threads;
+  mask_argmax_kernel<<<(unsigned)blocks, threads, 0, st>>>(q, ptr, N, (int)B, mask_terminals, mask_value, out_max, out_arg);
+  HEX_CUDA_CHECK(cudaGetLastError());
+  return HEXGNN_OK;
+}
+
+int launch_td_target(const float* q_target, const int64_t* best, const float* reward, const float* done, float gamma_n,
+                     int64_t N, int64_t B, float* target, cudaStream_t st) {
+  td_target_kernel<<<(unsigned)((B + 255) / 256), 256, 0, st>>>(q_target, best, reward, done, gamma_n, N, (int)B, target);
+  HEX_CUDA_CHECK(cudaGetLastError());
+  return HEXGNN_OK;
+}
+
+}  // namespace hexgnn

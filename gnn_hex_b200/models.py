@@ -112,7 +112,7 @@ class ModernTwoHeaded(nn.Module):
     supports_cache = True  # class attribute in the reference (models.py:148,486); read at train.py:98
 
     def __init__(self, hidden_channels: int, num_layers: int, num_head_layers: int = 2, tile_rows: int = 128,
-                 strict: bool = False, path: str = "auto"):
+                 strict: bool = False, path: str = "auto", max_graph_nodes: int = 0):
         super().__init__()
         self.hidden_channels = int(hidden_channels)
         self.num_layers = int(num_layers)
@@ -121,6 +121,9 @@ class ModernTwoHeaded(nn.Module):
         self.strict = strict                  # True: sync + raise on device-side status after each forward
         self.path = path                      # "auto" | "simt" | "tc"
         self.capture_embed_grads = False      # True: fill final_conv_grads (rl_loop/explain.py:41)
+        # > tile_rows: inference calls also run the oversize-graph path (hexgnn_forward_big) for graphs of up to this
+        # many nodes (board-size transfer: 13x13 -> 171, evaluate_elo.py:229-251); 0 = such graphs are flagged only
+        self.max_graph_nodes = int(max_graph_nodes)
         self.gnn = _SageParams(2, hidden_channels, num_layers)
         self.maker_head = _HeadParams(hidden_channels, num_head_layers)
         self.breaker_head = _HeadParams(hidden_channels, num_head_layers)
@@ -293,6 +296,8 @@ class ModernTwoHeaded(nn.Module):
         else:
             out_nodes, out_value, _, _ = ops.fused_forward(self._desc, self._flat, x, csr, flags, want_stash=False,
                                                            ws=self._fwd_ws(csr))
+            if self.max_graph_nodes > self.tile_rows:
+                ops.forward_big(self._desc, self._flat, x, csr, flags, self.max_graph_nodes, out_nodes, out_value)
         if self.strict:
             csr.raise_on_error()
         if advantages_only:

@@ -10,7 +10,7 @@ from ._lib import HEXGNN_ADV_ONLY, HEXGNN_SEPARATE, HEXGNN_PATH_SIMT, HEXGNN_PAT
 
 # kernels launched by each C-ABI call (csr: init, hist, scan, fill, sort; forward: pack, fused;
 # backward: pack, fused, reduce, unpack) -- bench.py's `gpu_launches` is read off this counter.
-LAUNCHES = {"build_csr": 5, "forward": 2, "backward": 5, "td_loss": 1}
+LAUNCHES = {"build_csr": 5, "forward": 2, "backward": 5, "td_loss": 1, "mask_argmax": 1, "td_target": 1, "forward_big": 0}
 launch_counter = 0
 
 
@@ -209,3 +209,59 @@ def td_loss(q, ptr, action, target, weight=None, kind="mse", scale=1.0):
     if kind not in LOSS_KINDS:
         raise _lib.HexGnnError(f"td_loss: unknown loss kind {kind!r}")
     return _TDLoss.apply(q, ptr, action, target, weight, LOSS_KINDS[kind], scale)
+
+
+@torch.no_grad()
+def mask_argmax(q, ptr, mask_terminals=True, mask_value=-5.0):
+    """rainbow.py:222-225 / 263-266 on device, one launch: overwrite the two terminal rows of every graph in ``q``
+    (in place) with ``mask_value`` and return (max [B], argmax [B] as GLOBAL row ids; ties -> lowest index).
+    Local actions are ``argmax - ptr[:-1]``."""
+    _require_cuda(q, "q")
+    if q.dtype != torch.float32 or not q.is_contiguous() or q.dim() != 1:
+        raise _lib.HexGnnError("mask_argmax: q must be a contiguous float32 [N] tensor (it is masked in place)")
+    dev = q.device
+    ptr = ptr.to(dev, non_blocking=True).contiguous()
+    N, B = int(q.shape[0]), int(ptr.shape[0]) - 1
+    mx = torch.empty(B, dtype=torch.float32, device=dev)
+    arg = torch.empty(B, dtype=torch.int64, device=dev)
+    rc = _lib.lib().hexgnn_mask_argmax(_ptr(q), _ptr(ptr), N, B, 1 if mask_terminals else 0, float(mask_value),
+                                       _ptr(mx), _ptr(arg), _stream(dev))
+    _lib.check(rc, "hexgnn_mask_argmax")
+    _count("mask_argmax")
+    return mx, arg
+
+
+@torch.no_grad()
+def td_target(q_target, best, reward, done, gamma_n):
+    """rainbow.py:268-269 on device: ``reward + gamma_n * q_target[best] * (1 - done)``."""
+    _require_cuda(q_target, "q_target")
+    dev = q_target.device
+    q_target = q_target.contiguous().float()
+    best = best.to(dev).contiguous()
+    reward = reward.to(dev).contiguous().float()
+    done = done.to(dev).contiguous().float()
+    B = int(best.shape[0])
+    out = torch.empty(B, dtype=torch.float32, device=dev)
+    rc = _lib.lib().hexgnn_td_target(_ptr(q_target), _ptr(best), _ptr(reward), _ptr(done), float(gamma_n),
+                                     int(q_target.shape[0]), B, _ptr(out), _stream(dev))
+    _lib.check(rc, "hexgnn_td_target")
+    _count("td_target")
+    return out
+
+
+def forward_big(desc, flat_params, x, csr, flags, max_rows, out_nodes, out_value, ws=None):
+    """hexgnn_forward_big: after fused_forward, evaluate the graphs that do not fit one tile (inference only) and
+    overwrite their rows of ``out_nodes`` / ``out_value`` in place.  Launches 2 + num_layers + num_head_layers kernels."""
+    N, E, B = csr.N, csr.E, csr.B
+    dev = x.device
+    hp = (int(desc.hidden) + 15) // 16 * 16
+    need = 2 * N * hp
+    if ws is None or ws.numel() < need:
+        ws = torch.empty(need, dtype=torch.float32, device=dev)
+    rc = _lib.lib().hexgnn_forward_big(C.byref(desc), _ptr(flat_params), _ptr(x.contiguous()), N, E, B, _ptr(csr.blob),
+                                       csr.tile_rows, flags, int(max_rows), _ptr(out_nodes), _ptr(out_value), _ptr(ws),
+                                       ws.numel() * 4, _stream(dev))
+    _lib.check(rc, "hexgnn_forward_big")
+    global launch_counter
+    launch_counter += 2 + int(desc.num_layers) + int(desc.num_head_layers)
+    return ws

@@ -141,6 +141,15 @@ int hexgnn_backward(const HexModelDesc* desc, const float* params, const float* 
                     const float* d_value, const float* stash, float* grad_params, float* d_embeds,
                     void* ws, size_t ws_bytes, void* stream);
 
+/* Oversize graphs (board-size transfer, evaluate_elo.py:229-251: 12x12 / 13x13 boards have 146 / 171 nodes).  Call AFTER
+ * hexgnn_forward, same stream, same arguments: every graph the fused kernel refused (more than tile_rows nodes or
+ * tile_rows*8 edges; its outputs were poisoned with NaN) is evaluated by a CUDA-core path, one launch per SAGE layer,
+ * and its rows of out_nodes / out_value are overwritten; HEXGNN_ST_GRAPH_TOO_LARGE is cleared unless a graph exceeds
+ * max_rows.  Inference only (no stash).  ws: 2 * N * hidden_padded floats. */
+int hexgnn_forward_big(const HexModelDesc* desc, const float* params, const float* x, int64_t N, int64_t E, int64_t B,
+                       const void* csr, int32_t tile_rows, int32_t flags, int32_t max_rows, float* out_nodes,
+                       float* out_value, void* ws, size_t ws_bytes, void* stream);
+
 /* Learner loss glue on device (replaces the index / loss / mean kernels of rainbow.py:301-312 and their autograd):
  *   td_est[g] = q[ptr[g] + action[g]];  td_err[g] = td_est[g] - target[g]  (PER priorities = |td_err| + 1e-6, :307-308)
  *   loss[0]   = scale * mean_g( weight[g] * l(target[g], td_est[g]) ),  kind 0: l = MSE, 1: l = SmoothL1 (beta 1), :85
@@ -151,6 +160,18 @@ int hexgnn_backward(const HexModelDesc* desc, const float* params, const float* 
 #define HEXGNN_LOSS_SMOOTH_L1 1
 int hexgnn_td_loss(const float* q, const int64_t* ptr, const int64_t* action, const float* target, const float* weight,
                    int64_t N, int64_t B, int32_t kind, float scale, float* loss, float* td_err, float* d_q, void* stream);
+
+/* Acting / target-network glue (rainbow.py:222-225 `act`, :263-269 `td_target`): when mask_terminals != 0 the two
+ * terminal rows of every graph (q[ptr[g]], q[ptr[g]+1]: not actions) are overwritten with mask_value (-5 in the
+ * reference), then out_max[g] / out_arg[g] = maximum of graph g and the GLOBAL row index attaining it (ties: the lowest
+ * index -- torch_scatter.scatter_max leaves ties unspecified; an empty graph gives 0 and N like torch_scatter).
+ * q [N] f32 in/out, ptr [B+1] i64, out_max [B] f32 or NULL, out_arg [B] i64 or NULL.  One launch, one warp per graph. */
+int hexgnn_mask_argmax(float* q, const int64_t* ptr, int64_t N, int64_t B, int32_t mask_terminals, float mask_value,
+                       float* out_max, int64_t* out_arg, void* stream);
+/* n-step double-DQN target (rainbow.py:268-269): target[g] = reward[g] + gamma_n * q_target[best[g]] * (1 - done[g]),
+ * best [B] i64 global row ids (hexgnn_mask_argmax of the policy net), reward / done / target [B] f32. */
+int hexgnn_td_target(const float* q_target, const int64_t* best, const float* reward, const float* done, float gamma_n,
+                     int64_t N, int64_t B, float* target, void* stream);
 
 /* Where forward (with `flags`) leaves the body embedding h_L (`final_conv_acts`, models.py:553) inside the stash:
  * float offset of a row-major [N, row_pitch] block.  (The two kernel paths keep different stash formats.) */

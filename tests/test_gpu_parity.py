@@ -245,3 +245,58 @@ def test_td_loss_matches_torch(kind, weighted):
     assert torch.allclose(err.cpu(), (td_est - target).detach(), atol=1e-6)
     assert torch.allclose(qd.grad.cpu(), q.grad, atol=1e-7, rtol=1e-5)
     assert int((qd.grad != 0).sum()) <= b.num_graphs
+
+
+def test_mask_argmax_and_td_target_match_torch():
+    """hexgnn_mask_argmax / hexgnn_td_target vs rainbow.py:222-225,263-269 written with torch ops."""
+    b = data.collate(data.load_positions("pos_mix_5_13_seed1234.npz", maker=1)[:120])
+    g = torch.Generator().manual_seed(9)
+    q = torch.randn(b.x.shape[0], generator=g)
+    ref = q.clone()
+    ref[b.ptr[:-1]] = -5
+    ref[b.ptr[:-1] + 1] = -5
+    mx_ref = torch.stack([ref[b.ptr[i]:b.ptr[i + 1]].max() for i in range(b.num_graphs)])
+    arg_ref = torch.stack([ref[b.ptr[i]:b.ptr[i + 1]].argmax() + b.ptr[i] for i in range(b.num_graphs)])
+    qd = q.to(DEV)
+    mx, arg = ops.mask_argmax(qd, b.ptr.to(DEV))
+    assert torch.equal(qd.cpu(), ref) and torch.equal(mx.cpu(), mx_ref) and torch.equal(arg.cpu(), arg_ref)
+    qt = torch.randn(b.x.shape[0], generator=g)
+    reward = torch.randn(b.num_graphs, generator=g)
+    done = (torch.rand(b.num_graphs, generator=g) < 0.3).float()
+    tgt = ops.td_target(qt.to(DEV), arg, reward.to(DEV), done.to(DEV), 0.97)
+    assert torch.allclose(tgt.cpu(), reward + 0.97 * qt[arg_ref] * (1 - done), atol=1e-6)
+    # ties resolve to the lowest row; all-masked two-node graphs return the mask value
+    z = torch.zeros(7, device=DEV)
+    mx2, arg2 = ops.mask_argmax(z, torch.tensor([0, 2, 7]), mask_value=-5.0)
+    assert mx2.tolist() == [-5.0, 0.0] and arg2.tolist() == [0, 4]
+
+
+@pytest.mark.parametrize("mode", ["q", "adv", "sep"])
+def test_oversize_graphs_board_size_transfer(mode):
+    """BASELINE configs[3]: a mixed 5x5..13x13 batch; the 12x12 / 13x13 positions (up to 171 nodes) do not fit one
+    128-row tile and go through hexgnn_forward_big.  Every graph must match the oracle; the status word ends clean."""
+    o, m = make_pair(110, 15)
+    m = m.to(DEV)
+    m.max_graph_nodes = 256
+    m.strict = True
+    gs = data.load_positions("pos_mix_5_13_seed1234.npz", maker=1)
+    big = [g for g in gs if g.x.shape[0] > 128]
+    assert len(big) >= 4
+    mix = big[:6] + [g for g in gs if g.x.shape[0] <= 128][:26] + big[6:10]
+    b = data.collate(mix)
+    d = b.to(DEV)
+    kw = {"advantages_only": mode == "adv", "seperate": mode == "sep"}
+    with torch.no_grad():
+        out = m(d.x, d.edge_index, d.batch, d.ptr, **kw)
+        ref = o(b.x, b.edge_index, b.batch, b.ptr, **kw)
+    if mode == "sep":
+        # adv - mean(adv) is a difference of nearly equal numbers for random-init weights: scale by the value range
+        scale = float(max(ref[0].abs().max(), ref[1].abs().max()))
+        assert rel_err(out[0], ref[0]) <= REL_TOL
+        assert float((out[1].cpu() - ref[1]).abs().max()) <= REL_TOL * scale
+    else:
+        assert out.shape == ref.shape and rel_err(out, ref) <= REL_TOL
+    # a graph beyond max_graph_nodes is still refused loudly
+    m.max_graph_nodes = 140
+    with torch.no_grad(), pytest.raises(_lib.HexGnnError):
+        m(d.x, d.edge_index, d.batch, d.ptr)

@@ -1,0 +1,69 @@
+"""Secondary configurations of BASELINE.json (not the headline: bench.py measures configs[1]).  One JSON line each:
+  gnn_s     configs[0]  GNN-S (hidden 35, 10+2 layers) fwd+bwd, 256 7x7 positions
+  selfplay  configs[2]  GNN-L forward only, 128 11x11 positions, advantages_only + terminal mask + per-graph argmax
+  ragged    configs[3]  GNN-L forward, 256 graphs of mixed 5x5..13x13 boards (ragged CSR)
+CUDA events, inputs resident, 256 MiB L2 flush between iterations.   python tools/bench_configs.py [iters]"""
+import json, os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from gnn_hex_b200 import ModernTwoHeaded, data, ops
+
+iters = int(sys.argv[1]) if len(sys.argv) > 1 else 100
+dev = torch.device("cuda", 0)
+flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+
+def timed(fn):
+    for _ in range(10):
+        fn()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(iters)]
+    torch.cuda.synchronize()
+    for s, e in evs:
+        flush.fill_(1)
+        s.record(); fn(); e.record()
+    torch.cuda.synchronize()
+    return sum(s.elapsed_time(e) for s, e in evs) / iters
+
+
+def loss_inputs(b):
+    g = torch.Generator().manual_seed(1)
+    n = b.ptr[1:] - b.ptr[:-1]
+    u = torch.rand(b.num_graphs, generator=g)
+    action = (2 + (u * (n - 2).clamp(min=1)).long()).clamp(max=n - 1).clamp(min=0)
+    return action.to(dev), (torch.rand(b.num_graphs, generator=g) * 2 - 1).to(dev), torch.ones(b.num_graphs, device=dev)
+
+
+torch.manual_seed(0)
+out = []
+# configs[0]
+m = ModernTwoHeaded(35, 10, 2).to(dev)
+b = data.collate(data.load_positions("pos_7x7_seed1234.npz", maker=1)[:256]); d = b.to(dev)
+a, t, w = loss_inputs(b)
+def step_s():
+    m.zero_grad(set_to_none=True)
+    q = m(d.x, d.edge_index, d.batch, d.ptr)
+    ops.td_loss(q, d.ptr, a, t, w)[0].backward()
+ms = timed(step_s)
+out.append({"config": "gnn_s fwd+bwd, 256 7x7 positions", "nodes": int(b.x.shape[0]), "ms": ms, "graphs_per_s": 256 / ms * 1e3})
+# configs[2]
+m = ModernTwoHeaded(110, 15, 2).to(dev)
+b = data.collate(data.load_positions("pos_11x11_seed1234.npz", maker=1)[:128]); d = b.to(dev)
+def act():
+    with torch.no_grad():
+        adv = m(d.x, d.edge_index, d.batch, d.ptr, advantages_only=True).reshape(-1)
+        return ops.mask_argmax(adv, d.ptr)[1]
+ms = timed(act)
+out.append({"config": "selfplay: GNN-L forward (advantages_only) + mask + argmax, 128 11x11 positions", "nodes": int(b.x.shape[0]),
+            "ms": ms, "graphs_per_s": 128 / ms * 1e3})
+# configs[3]
+b = data.collate(data.load_positions("pos_mix_5_13_seed1234.npz", maker=1)[:256]); d = b.to(dev)
+m.max_graph_nodes = 256   # 12x12 / 13x13 positions (146 / 171 nodes) take the oversize-graph path
+def fwd():
+    with torch.no_grad():
+        return m(d.x, d.edge_index, d.batch, d.ptr)
+ms = timed(fwd)
+status = int(m.last_csr.status.item()) if getattr(m, "last_csr", None) is not None else 0
+out.append({"config": "ragged: GNN-L forward, 256 graphs of 5x5..13x13 boards (oversize graphs via hexgnn_forward_big)", "nodes": int(b.x.shape[0]), "graphs": b.num_graphs,
+            "ms": ms, "graphs_per_s": b.num_graphs / ms * 1e3, "device_status": status})
+for o in out:
+    print(json.dumps(o))
