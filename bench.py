@@ -42,6 +42,9 @@ def parse():
     ap.add_argument("--workload", default="play", choices=["play", "empty"],
                     help="play: 256 seeded random-playout positions (mean 77 nodes); empty: 256 empty boards (123 nodes)")
     ap.add_argument("--path", default="auto", choices=["auto", "simt", "tc"])
+    ap.add_argument("--allreduce", default="nccl", choices=["p2p", "nccl"],
+                    help="N > 1: NCCL (default: measured faster for the 1.95 MB gradient), or the library's own one-shot "
+                         "all-reduce kernel over NVLink peer memory")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     return ap.parse_args()
@@ -220,6 +223,10 @@ def run_fused(args, rank, world, local_rank):
 
     torch.manual_seed(0)
     model = ModernTwoHeaded(HIDDEN, LAYERS, HEAD_LAYERS, path=args.path).to(dev)
+    collective = "none"
+    if world > 1:
+        collective = "p2p (hexgnn_allreduce_p2p over NVLink peer memory)" if (
+            args.allreduce == "p2p" and model.enable_p2p_allreduce()) else "nccl all_reduce"
     batch = make_batch(args.workload, rank)
     hb = batch.pin_memory()                      # HOST copy of the step's inputs (e2e arm)
     db = batch.to(dev)                           # resident copy (value arm)
@@ -325,7 +332,7 @@ def run_fused(args, rank, world, local_rank):
         "metric": METRIC, "value": graphs * args.steps / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args, batch, world),
+        "config": dict(workload_config(args, batch, world), collective=collective),
         "clocks": clocks,
         "e2e": {"value": graphs * args.steps / (ms_e2e * 1e-3), "unit": UNIT,
                 "h2d_bytes_per_step": int(sum(t.numel() * t.element_size() for t in (hb.x, hb.edge_index, hb.batch, hb.ptr))),

@@ -43,7 +43,7 @@ class HexCsrLayout(C.Structure):
 EXPORTS = ["hexgnn_abi_version", "hexgnn_last_error", "hexgnn_param_count", "hexgnn_param_offsets",
            "hexgnn_sizes", "hexgnn_csr_layout", "hexgnn_build_csr", "hexgnn_forward", "hexgnn_backward",
            "hexgnn_profile_enable", "hexgnn_profile_read", "hexgnn_selftest_mma", "hexgnn_debug_phases", "hexgnn_stash_embed", "hexgnn_td_loss",
-           "hexgnn_mask_argmax", "hexgnn_td_target", "hexgnn_forward_big"]
+           "hexgnn_mask_argmax", "hexgnn_td_target", "hexgnn_forward_big", "hexgnn_allreduce_p2p"]
 
 _lib = None
 
@@ -89,6 +89,8 @@ def lib():
     l.hexgnn_td_loss.argtypes = [p, p, p, p, p, i64, i64, i32, C.c_float, p, p, p, p]
     l.hexgnn_forward_big.restype = C.c_int
     l.hexgnn_forward_big.argtypes = [D, p, p, i64, i64, i64, p, i32, i32, i32, p, p, p, sz, p]
+    l.hexgnn_allreduce_p2p.restype = C.c_int
+    l.hexgnn_allreduce_p2p.argtypes = [p, i32, i64, p, p]
     l.hexgnn_mask_argmax.restype = C.c_int
     l.hexgnn_mask_argmax.argtypes = [p, p, i64, i64, i32, C.c_float, p, p, p]
     l.hexgnn_td_target.restype = C.c_int

@@ -231,6 +231,12 @@ int hexgnn_forward_big(const HexModelDesc* desc, const float* params, const floa
                             (cudaStream_t)stream);
 }
 
+int hexgnn_allreduce_p2p(const float* const* peer_bufs, int32_t world, int64_t n, float* out, void* stream) {
+  if (!peer_bufs || !out || world < 1 || world > 64 || n < 1) { set_error("allreduce_p2p: bad argument"); return HEXGNN_E_BADARG; }
+  if (((uintptr_t)out & 15) != 0) { set_error("allreduce_p2p: out must be 16-byte aligned"); return HEXGNN_E_BADARG; }
+  return launch_allreduce_p2p(peer_bufs, world, n, out, (cudaStream_t)stream);
+}
+
 int hexgnn_mask_argmax(float* q, const int64_t* ptr, int64_t N, int64_t B, int32_t mask_terminals, float mask_value,
                        float* out_max, int64_t* out_arg, void* stream) {
   if (!q || !ptr || N < 1 || B < 1 || B >= (1ll << 26)) { set_error("mask_argmax: bad argument"); return HEXGNN_E_BADARG; }

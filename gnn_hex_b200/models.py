@@ -136,6 +136,7 @@ class ModernTwoHeaded(nn.Module):
         self._slices = None
         self._ws = {}
         self._flat_grad = None
+        self._p2p = None
         self.last_csr = None
 
     # ---- parameter order == include/hexgnn.h flat layout ---------------------------------------------
@@ -193,6 +194,10 @@ class ModernTwoHeaded(nn.Module):
     def _flat_grad_buffer(self):
         if self._flat_grad is None or self._flat_grad.device != self._flat.device:
             self._flat_grad = torch.zeros_like(self._flat)
+        if self._p2p is not None:
+            # peer-mapped, double-buffered: the backward writes where the peers will read; buffer k is reused two steps
+            # later, after the next step's barrier has proven that every rank finished reading it
+            self._flat_grad = self._p2p["bufs"][self._p2p["k"]]
         return self._flat_grad
 
     def _grad_scratch(self):
@@ -237,12 +242,55 @@ class ModernTwoHeaded(nn.Module):
         """The flat fp32 gradient all `p.grad` alias (None before the first backward)."""
         return self._flat_grad
 
-    def allreduce_gradients(self, group=None):
-        """Data-parallel learner step (BASELINE config 5): ONE all-reduce (sum) of the flat gradient
-        over NCCL; the caller scales its loss by 1/world_size.  No reference counterpart."""
+    def enable_p2p_allreduce(self, group=None):
+        """Put the flat gradient into NVLink peer-mapped (symmetric) memory so `allreduce_gradients` can run the
+        library's own one-shot all-reduce kernel (`hexgnn_allreduce_p2p`: every rank reads all peers over NVLink /
+        NVSwitch and sums in rank order) instead of NCCL.  Collective: every rank of `group` must call it, after
+        `.to(device)` and before the first backward.  Returns False (and keeps NCCL) where symmetric memory is
+        unavailable."""
         import torch.distributed as dist
-        if self._flat_grad is not None and dist.is_initialized() and dist.get_world_size(group) > 1:
-            dist.all_reduce(self._flat_grad, op=dist.ReduceOp.SUM, group=group)
+        self._ensure_flat()
+        if not (dist.is_initialized() and dist.get_world_size(group) > 1 and self._flat.is_cuda):
+            return False
+        try:
+            import torch.distributed._symmetric_memory as symm
+            g = group if group is not None else dist.group.WORLD
+            bufs, hdls = [], []
+            for _ in range(2):
+                buf = symm.empty(self._flat.numel(), dtype=torch.float32, device=self._flat.device)
+                hdls.append(symm.rendezvous(buf, g))
+                buf.zero_()
+                bufs.append(buf)
+        except Exception as e:  # noqa: BLE001 -- any failure here means "no peer memory": stay on NCCL, say so
+            import warnings
+            warnings.warn(f"gnn_hex_b200: symmetric memory unavailable ({e!r}); gradients stay on NCCL all-reduce")
+            return False
+        self._p2p = {"bufs": bufs, "hdls": hdls, "red": torch.zeros_like(self._flat), "k": 0}
+        self._flat_grad = None          # next backward adopts a peer-mapped buffer
+        for p in self._params_cache:
+            p.grad = None
+        return True
+
+    def allreduce_gradients(self, group=None):
+        """Data-parallel learner step (BASELINE config 5): ONE all-reduce (sum) of the flat gradient; the caller
+        scales its loss by 1/world_size.  After `enable_p2p_allreduce()`: one cross-rank barrier, then
+        `hexgnn_allreduce_p2p` (own kernel over NVLink peer memory, rank-ordered sum) into a private buffer the
+        `p.grad` views are re-pointed to; the two peer-mapped buffers alternate so no second barrier is needed.
+        Gradients accumulated over several backwards (p.grad kept alive) fall back to NCCL.  No reference counterpart."""
+        import torch.distributed as dist
+        if self._flat_grad is None or not dist.is_initialized() or dist.get_world_size(group) <= 1:
+            return
+        p2p = self._p2p
+        if p2p is not None and self._flat_grad.data_ptr() == p2p["bufs"][p2p["k"]].data_ptr():
+            k = p2p["k"]
+            hdl = p2p["hdls"][k]
+            hdl.barrier(channel=0)      # every rank's backward has written its gradient into its buffer k
+            ops.allreduce_p2p(hdl.buffer_ptrs_dev, hdl.world_size, self._flat_grad.numel(), p2p["red"])
+            self._flat_grad = p2p["red"]          # p.grad now alias the reduced (private) buffer
+            self._point_grads()
+            p2p["k"] = k ^ 1
+            return
+        dist.all_reduce(self._flat_grad, op=dist.ReduceOp.SUM, group=group)
 
     @property
     def flat_parameters(self):

@@ -10,7 +10,7 @@ from ._lib import HEXGNN_ADV_ONLY, HEXGNN_SEPARATE, HEXGNN_PATH_SIMT, HEXGNN_PAT
 
 # kernels launched by each C-ABI call (csr: init, hist, scan, fill, sort; forward: pack, fused;
 # backward: pack, fused, reduce, unpack) -- bench.py's `gpu_launches` is read off this counter.
-LAUNCHES = {"build_csr": 5, "forward": 2, "backward": 5, "td_loss": 1, "mask_argmax": 1, "td_target": 1, "forward_big": 0}
+LAUNCHES = {"build_csr": 5, "forward": 2, "backward": 5, "td_loss": 1, "mask_argmax": 1, "td_target": 1, "forward_big": 0, "allreduce_p2p": 1}
 launch_counter = 0
 
 
@@ -265,3 +265,13 @@ def forward_big(desc, flat_params, x, csr, flags, max_rows, out_nodes, out_value
     global launch_counter
     launch_counter += 2 + int(desc.num_layers) + int(desc.num_head_layers)
     return ws
+
+
+def allreduce_p2p(peer_ptrs_dev, world, n, out):
+    """hexgnn_allreduce_p2p: out[n] = sum over ranks (in rank order) of the peer-mapped buffers whose device pointers
+    are stored in the DEVICE array at address `peer_ptrs_dev`.  The caller provides the cross-rank barriers."""
+    _require_cuda(out, "out")
+    rc = _lib.lib().hexgnn_allreduce_p2p(C.c_void_p(int(peer_ptrs_dev)), int(world), int(n), _ptr(out), _stream(out.device))
+    _lib.check(rc, "hexgnn_allreduce_p2p")
+    _count("allreduce_p2p")
+    return out

@@ -173,6 +173,13 @@ int hexgnn_mask_argmax(float* q, const int64_t* ptr, int64_t N, int64_t B, int32
 int hexgnn_td_target(const float* q_target, const int64_t* best, const float* reward, const float* done, float gamma_n,
                      int64_t N, int64_t B, float* target, void* stream);
 
+/* Data-parallel gradient all-reduce over NVLink peer memory (no reference counterpart).  peer_bufs is a
+ * DEVICE array of `world` pointers, entry r = rank r's flat gradient of n floats in peer-mapped (symmetric) memory,
+ * 16-byte aligned; out [n] (private, NOT one of the peer buffers) = their sum in rank order, bit-identical on every
+ * rank.  The caller brackets the call with cross-rank barriers: all ranks have written before it, none overwrites its
+ * buffer until all have returned from it (torch.distributed._symmetric_memory.barrier in the Python host side). */
+int hexgnn_allreduce_p2p(const float* const* peer_bufs, int32_t world, int64_t n, float* out, void* stream);
+
 /* Where forward (with `flags`) leaves the body embedding h_L (`final_conv_acts`, models.py:553) inside the stash:
  * float offset of a row-major [N, row_pitch] block.  (The two kernel paths keep different stash formats.) */
 int hexgnn_stash_embed(const HexModelDesc* desc, int64_t N, int64_t B, int32_t flags, int64_t* offset_floats,
