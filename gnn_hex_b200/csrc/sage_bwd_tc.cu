@@ -89,7 +89,7 @@ __device__ __forceinline__ float warp_sum_b(float v) {
 }
 
 // Phase profile (cycles per CTA): [0] wait dH (MMA_l)  [1] E1 (mask, dpre)  [2] E2 gather  [3] wait MMA_r + A write
-// [4] head + load  [5] layer 0  [8] total  [9] tiles
+// [4] head + load (cumulative: [6] up to the tile load, [7] up to table build + tanh)  [5] layer 0  [8] total  [9] tiles
 __device__ long long g_bwd_phase[148 * 16];
 
 template <int NJ>
@@ -129,7 +129,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
   const int H = a.d.H, H2 = a.d.H2, Lt = a.d.Lt;
   const int ntiles = *a.csr.ntiles;
   const long long t_kernel0 = PH_NOW();
-  long long ph0 = 0, ph1 = 0, ph2 = 0, ph3 = 0, ph4 = 0, ph5 = 0, ntl = 0;
+  long long ph0 = 0, ph1 = 0, ph2 = 0, ph3 = 0, ph4 = 0, ph5 = 0, ph6 = 0, ph7 = 0, ntl = 0;
 
   if (tid == 0) {
     for (int i = 0; i < kBwdStages; ++i) { mbar_init(&bar_full[i], 1); mbar_init(&bar_empty[i], 1); }
@@ -273,6 +273,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
         }
       }
       epi_bar_b();
+      PH_ADD(ph6, tq);
       gather_build<NJ>(gtab, rowptr_s, col_s, n, tid);
       for (int i = tid; i < kTcRows; i += kTcEpiThreads) {
         const int b = rowptr_s[i], e = rowptr_s[i + 1];
@@ -297,6 +298,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
         if (lane == 0) th_s[r] = tanhf(u + ba);
       }
       epi_bar_b();
+      PH_ADD(ph7, tq);
       const float inv = inv_s[row];
       // ---- head backward per graph: dump rows become dL/dg in place -----------------------------------------
       for (int g = 0; g < g1 - g0; ++g) {
@@ -612,7 +614,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
     if (tid == 0) { rec[a.gl.glinb] = accs[A_GLINB]; rec[a.gl.gv1b] = accs[A_GV1B]; }
     if (tid == 0 && blockIdx.x < 148) {
       long long* o = g_bwd_phase + blockIdx.x * 16;
-      o[0] = ph0; o[1] = ph1; o[2] = ph2; o[3] = ph3; o[4] = ph4; o[5] = ph5; o[8] = PH_NOW() - t_kernel0; o[9] = ntl;
+      o[0] = ph0; o[1] = ph1; o[2] = ph2; o[3] = ph3; o[4] = ph4; o[5] = ph5; o[6] = ph6; o[7] = ph7; o[8] = PH_NOW() - t_kernel0; o[9] = ntl;
     }
   }
   // ---- teardown ----------------------------------------------------------------------------------------------------------

@@ -4,7 +4,7 @@
 // SWIZZLE_128B_BASE32B shared-memory operands (SS mode): no transposition anywhere.  Work item = (layer s, group g):
 // the CTA walks the tiles t = g, g+G, ... and accumulates in ONE TMEM accumulator, so only G partial records per
 // layer exist (G = 148 / (Lt-1)) instead of one per CTA of the chain kernel, and they are summed in fixed order.
-// Warp roles: producer (2 KB bulk copies of 16-row k-chunks), 8 split warps (fp32 -> tf32 hi in place + lo copy,
+// Warp roles: producer (2 KB bulk copies of 16-row k-chunks), 8 split warps (lo = a - trunc_tf32(a) copy; hi = the fp32 image,
 // 3xTF32), MMA issuer, and the split warps double as the epilogue.
 #include "sage_tc.cuh"
 
@@ -128,9 +128,11 @@ __global__ void __launch_bounds__(kDwThreads, 1) sage_dw_tc_kernel(const __grid_
         for (int i = tid; i < nA + nB; i += kDwSplitThreads) {
           const int idx = i < nA ? i : (ABLK * (kDwBlk / 16) + (i - nA));
           const float4 v = base[idx];
-          float4 h, l;
-          split_tf32(v.x, h.x, l.x); split_tf32(v.y, h.y, l.y); split_tf32(v.z, h.z, l.z); split_tf32(v.w, h.w, l.w);
-          base[idx] = h;
+          // hi = the fp32 image itself: the tensor core reads tf32 operands by ignoring the low 13 mantissa bits
+          // (truncation), so only lo = rn_tf32(a - trunc_tf32(a)) has to be produced: a = hi + lo to 2^-22 |a|
+          float4 l;
+          l.x = tf32_rn(v.x - tf32_trunc(v.x)); l.y = tf32_rn(v.y - tf32_trunc(v.y));
+          l.z = tf32_rn(v.z - tf32_trunc(v.z)); l.w = tf32_rn(v.w - tf32_trunc(v.w));
           lob[idx] = l;
         }
         fence_proxy_async();

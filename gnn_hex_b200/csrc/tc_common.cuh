@@ -123,6 +123,7 @@ __device__ __forceinline__ void st_global_v8(void* p, float v0, float v1, float 
 __device__ __forceinline__ float tf32_rn(float a) {
   return __uint_as_float((__float_as_uint(a) + 0x1000u) & 0xffffe000u);
 }
+__device__ __forceinline__ float tf32_trunc(float a) { return __uint_as_float(__float_as_uint(a) & 0xffffe000u); }
 __device__ __forceinline__ void split_tf32(float a, float& hi, float& lo) {
   hi = tf32_rn(a);
   lo = tf32_rn(a - hi);
