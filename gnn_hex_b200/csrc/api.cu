@@ -183,11 +183,18 @@ int hexgnn_backward(const HexModelDesc* desc, const float* params, const float* 
     int rc = launch_pack_tc(d, pm, params, x, tpv, true, st);
     if (rc) return rc;
     const int grid = bwd_grid_ctas();
-    rc = launch_backward_tc_chain(d, pm, params, x, N, E, B, csr, flags, d_nodes, d_value, stash, wsf + w.dz, d_embeds, tpv,
-                                  wsf + w.small_rec, wsf + w.head_rec, grid, st);
-    if (rc) return rc;
-    rc = launch_backward_tc_dw(d, N, E, B, csr, stash, wsf + w.dz, wsf + w.big_rec, st);
-    if (rc) return rc;
+    int* sync = (int*)(wsf + w.sync);
+    HEX_CUDA_CHECK(cudaMemsetAsync(sync, 0, (size_t)tc_sync_ints(d, B) * 4, st));
+    {
+      // The dH chain and the dW GEMM overlap (programmatic dependent launch, per-tile flags): ONE event pair around
+      // the two launches -- an event between them would serialise them.
+      ProfScope prof(1, st);
+      rc = launch_backward_tc_chain(d, pm, params, x, N, E, B, csr, flags, d_nodes, d_value, stash, wsf + w.dz, d_embeds,
+                                    tpv, wsf + w.small_rec, wsf + w.head_rec, sync, grid, st);
+      if (rc) return rc;
+      rc = launch_backward_tc_dw(d, N, E, B, csr, stash, wsf + w.dz, wsf + w.big_rec, sync, st);
+      if (rc) return rc;
+    }
     rc = launch_reduce_tc(d, wsf + w.small_rec, grid, wsf + w.big_rec, tc_dw_groups(d), wsf + w.head_rec, B, wsf + w.sum, st);
     if (rc) return rc;
     return launch_unpack_grads(d, pm, x, wsf + w.sum, grad_params, st);

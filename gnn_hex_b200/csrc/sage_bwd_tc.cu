@@ -40,6 +40,7 @@ struct BwdTcArgs {
   TcPackView pv;
   float* small_rec;       // [gridDim.x][gl.total - gl.gb]  (the gv0 range stays unwritten)
   float* head_rec;        // [B][tc_head_rec_floats]: per graph [dt (H2, padded) | pooled (4H)]
+  int* tile_flag;         // [B]: set (release) once every dZ image of the tile is in memory -- the dW kernel's cue
 };
 
 template <int NJ>
@@ -143,6 +144,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
   __syncthreads();
   tc_fence_after();
   const uint32_t tbase = *tmem_slot;
+  // Every CTA of this grid is resident by now (persistent grid <= SM count): let the weight-gradient GEMM's CTAs take
+  // the SMs of CTAs that run out of tiles; they consume tiles as the flags below are released.
+  pdl_launch_dependents();
 
   if (wid == kTcEpiWarps) {
     // ================= producer: backward weight images -> ring =================
@@ -238,6 +242,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
       if (!td.ok) {
         if (tid == 0) { accs[A_GB0] = __int_as_float(0x7fc00000); atomicOr(a.csr.status, HEXGNN_ST_GRAPH_TOO_LARGE); }
         for (int i = tid; i < (g1 - g0) * hrec_n; i += kTcEpiThreads) a.head_rec[(int64_t)g0 * hrec_n + i] = 0.f;
+        if (tid == 0) flag_release(a.tile_flag + t, 1);
         continue;
       }
       // ---- tile CSR + features -> shared ------------------------------------------------------------
@@ -605,6 +610,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
         }
       }
       PH_ADD(ph5, tq);
+      // ---- hand the tile to the dW GEMM: all dZ stores of all epilogue threads, then one release ----------------------
+      fence_proxy_async_global();          // the consumer reads with bulk copies (async proxy)
+      epi_bar_b();
+      if (tid == 0) { __threadfence(); flag_release(a.tile_flag + t, 1); }
     }
     // ---- CTA accumulators -> this CTA's small record (GradLayout offsets) ------------------------------------------
     epi_bar_b();
@@ -612,6 +621,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
     for (int i = tid; i < 4 * Hp; i += kTcEpiThreads) rec[a.gl.g0 + i] = accs[A_G0 + i];
     for (int i = tid; i < H2; i += kTcEpiThreads) { rec[a.gl.gv0b + i] = accs[A_GV0B + i]; rec[a.gl.gv1 + i] = accs[A_GV1 + i]; }
     if (tid == 0) { rec[a.gl.glinb] = accs[A_GLINB]; rec[a.gl.gv1b] = accs[A_GV1B]; }
+    // the dW kernel's last ticket waits for every chain CTA's record, so "dW complete" implies "chain complete"
+    epi_bar_b();
+    if (tid == 0) { __threadfence(); atomicAdd(a.tile_flag - kSyncTileOff + 1, 1); }
     if (tid == 0 && blockIdx.x < 148) {
       long long* o = g_bwd_phase + blockIdx.x * 16;
       o[0] = ph0; o[1] = ph1; o[2] = ph2; o[3] = ph3; o[4] = ph4; o[5] = ph5; o[6] = ph6; o[7] = ph7; o[8] = PH_NOW() - t_kernel0; o[9] = ntl;
@@ -634,10 +646,7 @@ static int launch_bwd_tc_t(const BwdTcArgs& a, int grid, cudaStream_t st) {
   using S = BwdTcSmem<NJ>;
   auto kern = sage_bwd_tc_kernel<NJ>;
   HEX_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::bytes));
-  {
-    ProfScope prof(1, st);
-    kern<<<grid, kTcThreads, S::bytes, st>>>(a);
-  }
+  kern<<<grid, kTcThreads, S::bytes, st>>>(a);
   HEX_CUDA_CHECK(cudaGetLastError());
   return HEXGNN_OK;
 }
@@ -645,13 +654,13 @@ static int launch_bwd_tc_t(const BwdTcArgs& a, int grid, cudaStream_t st) {
 int launch_backward_tc_chain(const Dims& d, const ParamMap& pm, const float* params, const float* x, int64_t N, int64_t E,
                              int64_t B, const void* csr, int flags, const float* d_nodes, const float* d_value,
                              const float* stash, float* dz, float* d_embeds, TcPackView pv, float* small_rec,
-                             float* head_rec, int grid, cudaStream_t st) {
+                             float* head_rec, int* sync, int grid, cudaStream_t st) {
   BwdTcArgs a;
   a.d = d; a.pm = pm; grad_layout(d, &a.gl);
   a.params = params; a.x = x; a.N = N; a.E = E; a.B = B;
   a.csr = csr_view(const_cast<void*>(csr), N, E, B);
   a.flags = flags; a.d_nodes = d_nodes; a.d_value = d_value; a.stash = stash; a.dz = dz; a.d_embeds = d_embeds;
-  a.pv = pv; a.small_rec = small_rec; a.head_rec = head_rec;
+  a.pv = pv; a.small_rec = small_rec; a.head_rec = head_rec; a.tile_flag = sync + kSyncTileOff;
   switch (d.NJ) {
     case 1: return launch_bwd_tc_t<1>(a, grid, st);
     case 2: return launch_bwd_tc_t<2>(a, grid, st);

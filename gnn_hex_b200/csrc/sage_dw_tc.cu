@@ -4,6 +4,11 @@
 // SWIZZLE_128B_BASE32B shared-memory operands (SS mode): no transposition anywhere.  Work item = (layer s, group g):
 // the CTA walks the tiles t = g, g+G, ... and accumulates in ONE TMEM accumulator, so only G partial records per
 // layer exist (G = 148 / (Lt-1)) instead of one per CTA of the chain kernel, and they are summed in fixed order.
+// The kernel is launched as a programmatic dependent of the chain kernel: its CTAs become resident on the SMs of chain
+// CTAs that have run out of tiles (148 persistent CTAs, e.g. 209 tiles: 87 SMs idle through the second round), take a
+// ticket, and consume tiles as the chain releases their flags.  Items are ordered by ticket: phase A = the tiles of all
+// complete chain rounds (finished before any chain CTA retires), phase B = the last round's tiles; the phase-B CTA of
+// (layer, group) adds its accumulator onto the phase-A record in a fixed order, so results stay bit-reproducible.
 // Warp roles: producer (2 KB bulk copies of 16-row k-chunks), 8 split warps (lo = a - trunc_tf32(a) copy; hi = the fp32 image,
 // 3xTF32), MMA issuer, and the split warps double as the epilogue.
 #include "sage_tc.cuh"
@@ -27,6 +32,8 @@ struct DwArgs {
   const float* dz;      // [dZl | dpre] (RM32 images)
   float* big_rec;       // [G][gl.g0]
   int G;
+  int chain_grid;       // CTAs of the chain kernel (tiles of one chain round)
+  int* sync;            // sage_tc.cuh: ticket | tile flags | item flags
 };
 
 template <int NJ>
@@ -41,11 +48,21 @@ __global__ void __launch_bounds__(kDwThreads, 1) sage_dw_tc_kernel(const __grid_
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_dyn + 1023) & ~(uintptr_t)1023);
   __shared__ uint64_t bar_full[kDwStages], bar_split[kDwStages], bar_empty[kDwStages], bar_done;
   __shared__ uint32_t tmem_slot;
+  __shared__ int ticket_s;
 
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  const int item = blockIdx.x;
+  if (tid == 0) ticket_s = atomicAdd(a.sync, 1);
+  __syncthreads();
+  const int nitems = (int)gridDim.x >> 1;                  // (Lt-1) * G items per phase
+  const int phase = ticket_s >= nitems, item = ticket_s - phase * nitems;
   const int s = 1 + item / a.G, grp = item % a.G;
   const int ntiles = *a.csr.ntiles;
+  // phase A: tiles [0, TA) = all complete chain rounds but the last; phase B: the last round [TA, ntiles)
+  const int TA = ntiles > 0 ? ((ntiles - 1) / a.chain_grid) * a.chain_grid : 0;
+  const int t_begin = (phase ? TA : 0) + grp, t_end = phase ? ntiles : TA;
+  const int* tile_flag = a.sync + kSyncTileOff;
+  int* item_flag = a.sync + kSyncTileOff + a.B + item;
+  if (phase == 0 && TA == 0) return;                       // nothing before the last round: phase B writes the record
   const int CB = tc_act_blocks(Hp);
   const size_t act_img = (size_t)CB * kImgBlockBytes, dz_img = (size_t)NJ * kImgBlockBytes;
 
@@ -70,8 +87,9 @@ __global__ void __launch_bounds__(kDwThreads, 1) sage_dw_tc_kernel(const __grid_
     // ================= producer =================
     if (lane == 0) {
       uint32_t it = 0;
-      for (int t = grp; t < ntiles; t += a.G) {
+      for (int t = t_begin; t < t_end; t += a.G) {
         const int n32 = tile_rows32(t);
+        if (n32 > 0) { flag_wait(tile_flag + t); fence_proxy_async_global(); }
         const char* act = (const char*)a.stash + ((size_t)(s - 1) * a.B + t) * act_img;
         const char* dzp = (const char*)a.dz + ((size_t)(s - 1) * a.B + t) * dz_img;
         for (int c0 = 0; c0 < n32; c0 += kDwChunkRows, ++it) {
@@ -90,7 +108,7 @@ __global__ void __launch_bounds__(kDwThreads, 1) sage_dw_tc_kernel(const __grid_
     if (lane == 0) {
       constexpr uint32_t idesc = make_idesc_tf32(128, N2, true, true);
       uint32_t it = 0;
-      for (int t = grp; t < ntiles; t += a.G) {
+      for (int t = t_begin; t < t_end; t += a.G) {
         const int n32 = tile_rows32(t);
         for (int c0 = 0; c0 < n32; c0 += kDwChunkRows, ++it) {
           const int st = it % kDwStages;
@@ -117,7 +135,7 @@ __global__ void __launch_bounds__(kDwThreads, 1) sage_dw_tc_kernel(const __grid_
   } else {
     // ================= split warps: fp32 -> (tf32 hi in place, tf32 lo copy) =================
     uint32_t it = 0;
-    for (int t = grp; t < ntiles; t += a.G) {
+    for (int t = t_begin; t < t_end; t += a.G) {
       const int n32 = tile_rows32(t);
       for (int c0 = 0; c0 < n32; c0 += kDwChunkRows, ++it) {
         const int st = it % kDwStages;
@@ -142,6 +160,9 @@ __global__ void __launch_bounds__(kDwThreads, 1) sage_dw_tc_kernel(const __grid_
     // ================= epilogue: D[k][c'] -> this group's record =================
     mbar_wait(&bar_done, 0);
     tc_fence_after();
+    const bool add = phase == 1 && TA > 0;                 // phase B adds onto the phase-A record (fixed order: A + B)
+    if (add && tid == 0) flag_wait(item_flag);
+    asm volatile("bar.sync 2, %0;" ::"n"(kDwSplitThreads) : "memory");
     if (wid < 4) {
       const int m = wid * 32 + lane;                       // D lane = input channel k (Hp = ones channel)
       const uint32_t trow = tbase + ((uint32_t)(wid * 32) << 16);
@@ -155,16 +176,30 @@ __global__ void __launch_bounds__(kDwThreads, 1) sage_dw_tc_kernel(const __grid_
 #pragma unroll
           for (int u = 0; u < 8; ++u) v[u] = 0.f;
         }
-        if (m < Hp) {
-          float4* dst = (float4*)(rec + a.gl.gw + ((int64_t)(s - 1) * Hp + m) * N2 + c0);
-          dst[0] = make_float4(v[0], v[1], v[2], v[3]);
-          dst[1] = make_float4(v[4], v[5], v[6], v[7]);
-        } else if (m == Hp && c0 >= Hp) {
-          float4* dst = (float4*)(rec + a.gl.gb + (int64_t)s * Hp + (c0 - Hp));
+        float4* dst = nullptr;
+        if (m < Hp) dst = (float4*)(rec + a.gl.gw + ((int64_t)(s - 1) * Hp + m) * N2 + c0);
+        else if (m == Hp && c0 >= Hp) dst = (float4*)(rec + a.gl.gb + (int64_t)s * Hp + (c0 - Hp));
+        if (dst) {
+          if (add) {
+            const float4 p0 = __ldcg(dst), p1 = __ldcg(dst + 1);
+            v[0] += p0.x; v[1] += p0.y; v[2] += p0.z; v[3] += p0.w;
+            v[4] += p1.x; v[5] += p1.y; v[6] += p1.z; v[7] += p1.w;
+          }
           dst[0] = make_float4(v[0], v[1], v[2], v[3]);
           dst[1] = make_float4(v[4], v[5], v[6], v[7]);
         }
       }
+    }
+    if (phase == 0) {                                      // record complete: release it to the phase-B CTA of this item
+      asm volatile("bar.sync 2, %0;" ::"n"(kDwSplitThreads) : "memory");
+      if (tid == 0) { __threadfence(); flag_release(item_flag, 1); }
+    }
+  }
+  if (ticket_s == (int)gridDim.x - 1 && tid == 0) {        // see the end of sage_bwd_tc_kernel
+    const long long t0 = clock64();
+    while (flag_acquire(a.sync + 1) < a.chain_grid) {
+      __nanosleep(500);
+      if (clock64() - t0 > 8000000000ll) __trap();
     }
   }
   tc_fence_before();
@@ -182,20 +217,27 @@ static int launch_dw_t(const DwArgs& a, cudaStream_t st) {
   auto kern = sage_dw_tc_kernel<NJ>;
   const size_t smem = (size_t)kDwStages * 2 * (4 * kDwBlk + NJ * kDwBlk) + 1024;
   HEX_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  {
-    ProfScope prof(2, st);
-    kern<<<(a.d.Lt - 1) * a.G, kDwThreads, smem, st>>>(a);
-  }
-  HEX_CUDA_CHECK(cudaGetLastError());
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * (a.d.Lt - 1) * a.G);              // phase A + phase B items, ordered by ticket
+  cfg.blockDim = dim3(kDwThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;   // may start while the chain kernel still runs
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  HEX_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, a));
   return HEXGNN_OK;
 }
 
 int launch_backward_tc_dw(const Dims& d, int64_t N, int64_t E, int64_t B, const void* csr, const float* stash,
-                          const float* dz, float* big_rec, cudaStream_t st) {
+                          const float* dz, float* big_rec, int* sync, cudaStream_t st) {
   DwArgs a;
   a.d = d; grad_layout(d, &a.gl); a.B = B;
   a.csr = csr_view(const_cast<void*>(csr), N, E, B);
   a.stash = stash; a.dz = dz; a.big_rec = big_rec; a.G = tc_dw_groups(d);
+  a.chain_grid = bwd_grid_ctas(); a.sync = sync;
   switch (d.NJ) {
     case 1: return launch_dw_t<1>(a, st);
     case 2: return launch_dw_t<2>(a, st);

@@ -283,9 +283,9 @@ int tc_dw_groups(const Dims& d);
 int launch_backward_tc_chain(const Dims& d, const ParamMap& pm, const float* params, const float* x, int64_t N, int64_t E,
                              int64_t B, const void* csr, int flags, const float* d_nodes, const float* d_value,
                              const float* stash, float* dz, float* d_embeds, TcPackView pv, float* small_rec,
-                             float* head_rec, int grid, cudaStream_t st);
+                             float* head_rec, int* sync, int grid, cudaStream_t st);
 int launch_backward_tc_dw(const Dims& d, int64_t N, int64_t E, int64_t B, const void* csr, const float* stash,
-                          const float* dz, float* big_rec, cudaStream_t st);
+                          const float* dz, float* big_rec, int* sync, cudaStream_t st);
 int launch_reduce_tc(const Dims& d, const float* small_rec, int nsmall, const float* big_rec, int G,
                      const float* head_rec, int64_t B, float* packed_sum, cudaStream_t st);
 
@@ -294,7 +294,11 @@ int launch_reduce_tc(const Dims& d, const float* small_rec, int nsmall, const fl
 __host__ __device__ inline int tc_head_rec_floats(const Dims& d) { return ((d.H2 + 3) & ~3) + ((4 * d.H + 3) & ~3); }
 // Workspace of the tcgen05 backward (floats): weight images | dZ stash | small records | group records | head
 // records | packed sum
-struct TcBwdWs { int64_t pack, dz, small_rec, big_rec, head_rec, sum, total; };
+// `sync` (ints): [0] ticket counter of the dW kernel, [4 .. 4+B) one "dZ of this tile is complete" flag per tile,
+// then one "phase-A record written" flag per (layer, group) item of the dW kernel; zeroed before the chain launch.
+constexpr int kSyncTileOff = 4;
+inline int64_t tc_sync_ints(const Dims& d, int64_t B) { return align_up(kSyncTileOff + B + (int64_t)(d.Lt - 1) * tc_dw_groups(d), 4); }
+struct TcBwdWs { int64_t pack, dz, small_rec, big_rec, head_rec, sum, sync, total; };
 inline TcBwdWs tc_bwd_ws(const Dims& d, int64_t B) {
   GradLayout gl;
   grad_layout(d, &gl);
@@ -305,7 +309,8 @@ inline TcBwdWs tc_bwd_ws(const Dims& d, int64_t B) {
   w.small_rec = o; o += align_up((int64_t)bwd_grid_ctas() * (gl.total - gl.gb), 4);
   w.big_rec = o; o += (int64_t)tc_dw_groups(d) * gl.g0;
   w.head_rec = o; o += align_up(B * tc_head_rec_floats(d), 4);
-  w.sum = o; o += gl.total;
+  w.sum = o; o += align_up(gl.total, 4);
+  w.sync = o; o += tc_sync_ints(d, B);
   w.total = o;
   return w;
 }

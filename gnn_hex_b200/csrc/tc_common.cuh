@@ -65,6 +65,31 @@ __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gmem_src, u
 // generic-proxy shared-memory writes -> visible to the async proxy (tensor core operand reads)
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+// ---- kernel-to-kernel hand-off inside one stream (programmatic dependent launch + flags in global memory) ----------
+// The producer kernel lets the next kernel's CTAs become resident as its own CTAs retire; data is handed over per
+// unit through a release / acquire flag, never through kernel completion.  A waiter only ever waits on a CTA of an
+// EARLIER launch (or an earlier ticket of its own launch), all of which are resident or finished: no deadlock.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async_global() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
+__device__ __forceinline__ void flag_release(int* flag, int v) {
+  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(flag), "r"(v) : "memory");
+}
+__device__ __forceinline__ int flag_acquire(const int* flag) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+  return v;
+}
+// Bounded like mbar_wait: a protocol bug traps instead of hanging the GPU.
+__device__ __forceinline__ void flag_wait(const int* flag) {
+  if (flag_acquire(flag) != 0) return;
+  const long long t0 = clock64();
+  uint32_t polls = 0;
+  while (flag_acquire(flag) == 0) {
+    __nanosleep(200);
+    if ((++polls & 1023u) == 0 && clock64() - t0 > 8000000000ll) __trap();
+  }
+}
+
 // ---- tensor memory --------------------------------------------------------------------------------
 // One full warp allocates `ncols` (power of two >= 32) columns; the base address lands in *smem_slot.
 __device__ __forceinline__ void tmem_alloc(uint32_t* smem_slot, uint32_t ncols) {
