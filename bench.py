@@ -45,6 +45,9 @@ def parse():
     ap.add_argument("--allreduce", default="nccl", choices=["p2p", "nccl"],
                     help="N > 1: NCCL (default: measured faster for the 1.95 MB gradient), or the library's own one-shot "
                          "all-reduce kernel over NVLink peer memory")
+    ap.add_argument("--api", default="train_step", choices=["train_step", "autograd"],
+                    help="train_step: model.train_step (hexgnn_train_step: forward + TD loss + backward in one call, the "
+                         "three tensor-core kernels overlapped); autograd: model(...) -> ops.td_loss -> loss.backward()")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     return ap.parse_args()
@@ -239,11 +242,21 @@ def run_fused(args, rank, world, local_rank):
         # rainbow.py:301-312 (PER-weighted MSE) as ONE fused launch: loss, td errors and dloss/dq
         return ops.td_loss(q, ptr, action, target, weight, "mse", scale)[0]
 
+    fused_api = args.api == "train_step" and args.path != "simt"
+
+    def fwd_loss_bwd(b):
+        if fused_api:
+            # rainbow.py:301-316 in one call; sets p.grad exactly like the autograd route (bit-identical, tested)
+            return model.train_step(b.x, b.edge_index, b.batch, b.ptr, action=action, target=target, weight=weight,
+                                    kind="mse", scale=scale)[0]
+        q = model(b.x, b.edge_index, b.batch, b.ptr)
+        loss = td_loss(q, b.ptr)
+        loss.backward()
+        return loss
+
     def step_resident():
         model.zero_grad(set_to_none=True)
-        q = model(db.x, db.edge_index, db.batch, db.ptr)
-        loss = td_loss(q, db.ptr)
-        loss.backward()
+        loss = fwd_loss_bwd(db)
         if world > 1:
             model.allreduce_gradients()
         return loss
@@ -251,9 +264,7 @@ def run_fused(args, rank, world, local_rank):
     def step_e2e():
         model.zero_grad(set_to_none=True)
         b = hb.to(dev, non_blocking=True)
-        q = model(b.x, b.edge_index, b.batch, b.ptr)
-        loss = td_loss(q, b.ptr)
-        loss.backward()
+        loss = fwd_loss_bwd(b)
         if world > 1:
             model.allreduce_gradients()
         loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
@@ -292,12 +303,13 @@ def run_fused(args, rank, world, local_rank):
 
     t_wall0 = time.time()
     _lib.profile_enable(True)
-    _lib.profile_read(0); _lib.profile_read(1)
+    _lib.profile_read(0); _lib.profile_read(1); _lib.profile_read(2)
     l0 = ops.launch_counter
     ms_total = timed(step_resident, args.steps)
     launches = ops.launch_counter - l0
     fwd_ms, fwd_n = _lib.profile_read(0)
     bwd_ms, bwd_n = _lib.profile_read(1)
+    trio_ms, trio_n = _lib.profile_read(2)
     _lib.profile_enable(False)
     ms_e2e = timed(step_e2e, args.steps, sync_each=True)
     clocks = sampler.stop(t_wall0, time.time()) if sampler else None
@@ -317,17 +329,31 @@ def run_fused(args, rank, world, local_rank):
     # the node-linear contractions run in fp32 (SIMT) or 3xTF32 (tcgen05); the tensor-pipe roofline of
     # an fp32-exact result is the TF32 dense peak = 1/2 of the measured bf16 peak (B200_PROFILING.md).
     tf32_peak = 0.5 * pk["bf16_tflops"]
-    # Dominant launch = the backward GEMM pair: the dH chain (sage_bwd_tc_kernel, dX = dZ W: ONE forward's worth of
-    # algorithmic FLOPs) and the weight-gradient GEMM (sage_dw_tc_kernel, a second forward's worth).  The dW kernel is
-    # a programmatic dependent launch of the chain and runs on the SMs the chain's last round leaves idle, so the two
-    # are ONE timed unit (one CUDA-event pair; an event between them would serialise them): 2 x F_fwd per launch pair.
-    # The forward kernel (F_fwd) is reported beside it against the same peak.
-    bwd_avg_ms = bwd_ms / max(bwd_n, 1)
-    fwd_avg_ms = fwd_ms / max(fwd_n, 1)
+    # Timed unit of the roofline (one CUDA-event pair inside the library, live in the timed region):
+    #  * api train_step: the forward kernel, the backward dH chain and the dW GEMM are programmatic dependent launches
+    #    of each other and overlap (tiles handed over through flags), so the TRIO is the unit: 3 x F_fwd algorithmic
+    #    FLOPs (forward, dX = dZ W, dW = h^T dZ -- one forward's worth each) per trio;
+    #  * api autograd: forward alone (F_fwd) and the overlapped backward pair chain + dW (2 x F_fwd).
+    # An event between overlapped kernels would serialise them; per-kernel times are in the ncu launch list (profiles/).
     tf = lambda flops, ms: (flops / (ms * 1e-3) / 1e12) if ms > 0 else None
-    achieved = tf(2 * f_fwd, bwd_avg_ms) if bwd_n else None
-    # ncu --set full, profiles/ncu_full_r1c_tc.csv (same workload): dram read + write of the chain kernel per launch
-    traffic = 300.2e6 if (args.workload == "play" and args.path != "simt") else None
+    fwd_avg_ms = fwd_ms / max(fwd_n, 1)
+    bwd_avg_ms = bwd_ms / max(bwd_n, 1)
+    trio_avg_ms = trio_ms / max(trio_n, 1)
+    if trio_n:
+        unit_name = ("sage_fwd_tc_kernel + sage_bwd_tc_kernel + sage_dw_tc_kernel (forward, backward dH chain, dW GEMM; "
+                     "overlapped by programmatic dependent launch: one event pair)")
+        unit_flops, unit_ms, kernels_ms = 3 * f_fwd, trio_avg_ms, trio_ms
+        parts = None
+    else:
+        unit_name = "sage_bwd_tc_kernel + sage_dw_tc_kernel (backward dH chain and dW GEMM, overlapped: one event pair)"
+        unit_flops, unit_ms, kernels_ms = 2 * f_fwd, bwd_avg_ms, bwd_ms + fwd_ms
+        parts = {"avg_launch_ms": fwd_avg_ms, "flops_per_launch": f_fwd, "achieved": tf(f_fwd, fwd_avg_ms),
+                 "frac": (tf(f_fwd, fwd_avg_ms) or 0) / tf32_peak}
+    achieved = tf(unit_flops, unit_ms)
+    # ncu --set full (same workload): dram read + write per launch, summed over the kernels of the unit
+    traffic = None
+    if args.workload == "play" and args.path != "simt":
+        traffic = (156.7e6 + 300.1e6 + 481.9e6) if trio_n else (300.1e6 + 481.9e6)
     line = {
         "metric": METRIC, "value": graphs * args.steps / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
@@ -338,19 +364,20 @@ def run_fused(args, rank, world, local_rank):
                 "h2d_bytes_per_step": int(sum(t.numel() * t.element_size() for t in (hb.x, hb.edge_index, hb.batch, hb.ptr))),
                 "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "tensor", "kernel": "sage_bwd_tc_kernel + sage_dw_tc_kernel (backward dH chain and dW GEMM, overlapped: one event pair)",
+        "roofline": {"bound": "tensor", "kernel": unit_name,
                      "achieved": achieved, "peak": tf32_peak, "unit": "TFLOP/s",
                      "frac": (achieved / tf32_peak) if achieved else None, "traffic": traffic,
                      "traffic_source": "ncu dram__bytes_read+write per launch, profiles/ncu_full_r1c_tc.csv",
                      "peak_source": f"0.5 x bf16_tflops ({pk['source']}) = dense TF32",
                      "arithmetic": "3xTF32 (3 tensor-core passes per algorithmic FLOP: ceiling 1/3 of peak)",
-                     "flops_per_launch": 2 * f_fwd, "avg_launch_ms": bwd_avg_ms,
-                     "fwd_kernel": {"avg_launch_ms": fwd_avg_ms, "flops_per_launch": f_fwd,
-                                    "achieved": tf(f_fwd, fwd_avg_ms),
-                                    "frac": (tf(f_fwd, fwd_avg_ms) or 0) / tf32_peak},
+                     "flops_per_launch": unit_flops, "avg_launch_ms": unit_ms,
                      "step_frac": tf(f_train, ms_total / args.steps) / tf32_peak,
-                     "kernel_share_of_step": (bwd_ms + fwd_ms) / ms_total},
+                     "kernel_share_of_step": kernels_ms / ms_total},
     }
+    if parts:
+        line["roofline"]["fwd_kernel"] = parts
+    line["config"]["api"] = ("model.train_step (hexgnn_train_step)" if fused_api
+                             else "model.forward -> ops.td_loss -> loss.backward()")
     if not args.no_cpu_baseline:
         v, done, cores, dt = time_cpu_port(batch, 1000, 2, max_seconds=args.cpu_seconds)
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",

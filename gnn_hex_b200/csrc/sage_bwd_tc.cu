@@ -41,6 +41,7 @@ struct BwdTcArgs {
   float* small_rec;       // [gridDim.x][gl.total - gl.gb]  (the gv0 range stays unwritten)
   float* head_rec;        // [B][tc_head_rec_floats]: per graph [dt (H2, padded) | pooled (4H)]
   int* tile_flag;         // [B]: set (release) once every dZ image of the tile is in memory -- the dW kernel's cue
+  TdFuse td;              // hexgnn_train_step: forward-tile flags + the TD loss whose dL/dQ replaces d_nodes
 };
 
 template <int NJ>
@@ -53,8 +54,8 @@ struct BwdTcSmem {
   static constexpr int off_ring = 0;
   static constexpr int off_dump = off_ring + kBwdStages * stage_bytes;           // float [128][P]
   static constexpr int off_agg = off_dump + (kTcRows + 1) * P * 4;               // float [128][P]  (dump row 128 = zeros)
-  static constexpr int off_rows = off_agg + kTcRows * P * 4;                     // float [7][128]
-  static constexpr int off_pool = off_rows + 7 * kTcRows * 4;                    // float [4*Hp]
+  static constexpr int off_rows = off_agg + kTcRows * P * 4;                     // float [8][128]
+  static constexpr int off_pool = off_rows + 8 * kTcRows * 4;                    // float [4*Hp]
   static constexpr int off_hid = off_pool + 4 * Hp * 4;                          // float [Hp]
   static constexpr int off_arg = off_hid + Hp * 4;                               // int [2*Hp]
   static constexpr int off_part = off_agg;                                       // float [4][6][Hp] row-part partials
@@ -110,7 +111,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
   float* accs = (float*)(smem + S::off_acc);
   float* rows = (float*)(smem + S::off_rows);
   float *inv_s = rows, *x0_s = rows + 128, *x1_s = rows + 256, *m0_s = rows + 384, *m1_s = rows + 512,
-        *adv_s = rows + 640, *th_s = rows + 768;
+        *adv_s = rows + 640, *th_s = rows + 768, *dq_s = rows + 896;
   float* pool = (float*)(smem + S::off_pool);
   float* hid = (float*)(smem + S::off_hid);
   int* arg_s = (int*)(smem + S::off_arg);
@@ -236,6 +237,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
     for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
       const TileDimsB td = tile_dims_b(a.csr, t, S::ECAP);
       const int n = td.n, r0 = td.r0, g0 = td.g0, g1 = td.g1;
+      if (a.td.fwd_flag && tid == 0) flag_wait(a.td.fwd_flag + t);   // acquire; the barrier extends it to the CTA
       epi_bar_b();
       long long tq = PH_NOW();
       ++ntl;
@@ -259,6 +261,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
           float v0 = 0.f, v1 = 0.f;
           if (i < n) { const float* xr = a.x + (int64_t)(r0 + i) * 3; v0 = xr[0]; v1 = xr[1]; }
           x0_s[i] = v0; x1_s[i] = v1;
+          dq_s[i] = (a.td.action || i >= n) ? 0.f : a.d_nodes[r0 + i];
         }
         if (bad) atomicOr(a.csr.status, bad);
       }
@@ -279,6 +282,22 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
       }
       epi_bar_b();
       PH_ADD(ph6, tq);
+      if (a.td.action) {
+        // dL/dQ of the TD loss (td_loss.cu): zero except at row ptr[g] + action[g] of every graph
+        const float invB = a.td.scale / (float)a.B;
+        for (int g = tid; g < g1 - g0; g += kTcEpiThreads) {
+          const int64_t act = a.td.action[g0 + g];
+          const int i = gp_s[g] + (int)act;
+          if (act >= 0 && i < gp_s[g + 1]) {
+            const float e = a.td.q[r0 + i] - a.td.target[g0 + g];
+            const float w = a.td.weight ? a.td.weight[g0 + g] : 1.f;
+            float dl;
+            if (a.td.kind == 0) dl = 2.f * e;
+            else { const float ab = fabsf(e); dl = ab < 1.f ? e : (e > 0.f ? 1.f : -1.f); }
+            dq_s[i] += w * dl * invB;
+          }
+        }
+      }
       gather_build<NJ>(gtab, rowptr_s, col_s, n, tid);
       for (int i = tid; i < kTcRows; i += kTcEpiThreads) {
         const int b = rowptr_s[i], e = rowptr_s[i + 1];
@@ -319,7 +338,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
         if (!adv_only) {
           if (wid == 0) {
             float u = 0.f;
-            for (int i = rs + lane; i < re; i += 32) u += a.d_nodes[r0 + i];
+            for (int i = rs + lane; i < re; i += 32) u += dq_s[i];
             u = warp_sum_b(u);
             if (lane == 0) misc[0] = u;
           }
@@ -328,7 +347,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
         }
         for (int i = rs + tid; i < re; i += kTcEpiThreads) {
           const float th = th_s[i];
-          const float dn = a.d_nodes[r0 + i];
+          const float dn = dq_s[i];
           adv_s[i] = (adv_only ? dn : dn - sumdq / (float)ng) * 2.0f * (1.0f - th * th);
         }
         epi_bar_b();
@@ -644,23 +663,34 @@ int debug_read_bwd_phases(long long* host, int n) {
 template <int NJ>
 static int launch_bwd_tc_t(const BwdTcArgs& a, int grid, cudaStream_t st) {
   using S = BwdTcSmem<NJ>;
+  static_assert(S::bytes <= 227 * 1024, "chain kernel shared memory");
   auto kern = sage_bwd_tc_kernel<NJ>;
   HEX_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::bytes));
-  kern<<<grid, kTcThreads, S::bytes, st>>>(a);
-  HEX_CUDA_CHECK(cudaGetLastError());
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kTcThreads);
+  cfg.dynamicSmemBytes = S::bytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;   // train_step: may start under the forward kernel
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = a.td.fwd_flag ? 1 : 0;
+  HEX_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, a));
   return HEXGNN_OK;
 }
 
 int launch_backward_tc_chain(const Dims& d, const ParamMap& pm, const float* params, const float* x, int64_t N, int64_t E,
                              int64_t B, const void* csr, int flags, const float* d_nodes, const float* d_value,
                              const float* stash, float* dz, float* d_embeds, TcPackView pv, float* small_rec,
-                             float* head_rec, int* sync, int grid, cudaStream_t st) {
+                             float* head_rec, int* sync, int grid, cudaStream_t st, const TdFuse* fuse) {
   BwdTcArgs a;
   a.d = d; a.pm = pm; grad_layout(d, &a.gl);
   a.params = params; a.x = x; a.N = N; a.E = E; a.B = B;
   a.csr = csr_view(const_cast<void*>(csr), N, E, B);
   a.flags = flags; a.d_nodes = d_nodes; a.d_value = d_value; a.stash = stash; a.dz = dz; a.d_embeds = d_embeds;
   a.pv = pv; a.small_rec = small_rec; a.head_rec = head_rec; a.tile_flag = sync + kSyncTileOff;
+  if (fuse) a.td = *fuse; else a.td = TdFuse{nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0.f};
   switch (d.NJ) {
     case 1: return launch_bwd_tc_t<1>(a, grid, st);
     case 2: return launch_bwd_tc_t<2>(a, grid, st);

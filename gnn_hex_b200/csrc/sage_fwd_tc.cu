@@ -26,6 +26,7 @@ struct FwdTcArgs {
   float* out_value;
   float* stash;
   TcPackView pv;
+  int* tile_flag;   // hexgnn_train_step: released per finished tile (the backward chain starts under the last round)
 };
 
 template <int NJ>
@@ -124,6 +125,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
   __syncthreads();
   tc_fence_after();
   const uint32_t tbase = *tmem_slot;
+  pdl_launch_dependents();   // hexgnn_train_step: the chain kernel's CTAs may take the SMs this grid's last round leaves idle
 
   if (wid == kTcEpiWarps) {
     // ================= producer: weight images -> ring =================
@@ -208,6 +210,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
         for (int i = r0 + tid; i < r1; i += kTcEpiThreads) a.out_nodes[i] = qnan;
         if (a.out_value) for (int g = g0 + tid; g < g1; g += kTcEpiThreads) a.out_value[g] = qnan;
         if (tid == 0) atomicOr(a.csr.status, HEXGNN_ST_GRAPH_TOO_LARGE);
+        if (a.tile_flag) { epi_bar(); if (tid == 0) { __threadfence(); flag_release(a.tile_flag + t, 1); } }
         continue;
       }
       // ---- tile CSR + features -> shared ------------------------------------------------------------
@@ -481,6 +484,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
         epi_bar();
       }
       PH_ADD(ph4, tq);
+      if (a.tile_flag) {                   // Q, stash images and mask words of the tile are written: hand it over
+        fence_proxy_async_global();
+        epi_bar();
+        if (tid == 0) { __threadfence(); flag_release(a.tile_flag + t, 1); }
+      }
     }
     if (tid == 0 && blockIdx.x < 148) {
       long long* o = g_fwd_phase + blockIdx.x * 16;
@@ -518,8 +526,9 @@ int debug_read_fwd_phases(long long* host, int n) {
 
 int launch_forward_tc(const Dims& d, const ParamMap& pm, const float* params, const float* x, int64_t N, int64_t E,
                       int64_t B, const void* csr, int flags, float* out_nodes, float* out_value, float* stash,
-                      TcPackView pv, cudaStream_t st) {
+                      TcPackView pv, cudaStream_t st, int* tile_flag) {
   FwdTcArgs a;
+  a.tile_flag = tile_flag;
   a.d = d; a.pm = pm; a.params = params; a.x = x; a.N = N; a.E = E; a.B = B;
   a.csr = csr_view(const_cast<void*>(csr), N, E, B);
   a.flags = flags; a.out_nodes = out_nodes; a.out_value = out_value; a.stash = stash; a.pv = pv;

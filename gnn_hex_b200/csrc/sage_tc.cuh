@@ -275,15 +275,16 @@ int launch_pack_tc(const Dims& d, const ParamMap& pm, const float* params, const
                    bool with_transpose, cudaStream_t st);
 int launch_forward_tc(const Dims& d, const ParamMap& pm, const float* params, const float* x, int64_t N, int64_t E,
                       int64_t B, const void* csr, int flags, float* out_nodes, float* out_value, float* stash,
-                      TcPackView pv, cudaStream_t st);
+                      TcPackView pv, cudaStream_t st, int* tile_flag = nullptr);
 
 int debug_read_fwd_phases(long long* host, int n);
 int debug_read_bwd_phases(long long* host, int n);
 int tc_dw_groups(const Dims& d);
+struct TdFuse;
 int launch_backward_tc_chain(const Dims& d, const ParamMap& pm, const float* params, const float* x, int64_t N, int64_t E,
                              int64_t B, const void* csr, int flags, const float* d_nodes, const float* d_value,
                              const float* stash, float* dz, float* d_embeds, TcPackView pv, float* small_rec,
-                             float* head_rec, int* sync, int grid, cudaStream_t st);
+                             float* head_rec, int* sync, int grid, cudaStream_t st, const TdFuse* fuse = nullptr);
 int launch_backward_tc_dw(const Dims& d, int64_t N, int64_t E, int64_t B, const void* csr, const float* stash,
                           const float* dz, float* big_rec, int* sync, cudaStream_t st);
 int launch_reduce_tc(const Dims& d, const float* small_rec, int nsmall, const float* big_rec, int G,
@@ -295,9 +296,22 @@ __host__ __device__ inline int tc_head_rec_floats(const Dims& d) { return ((d.H2
 // Workspace of the tcgen05 backward (floats): weight images | dZ stash | small records | group records | head
 // records | packed sum
 // `sync` (ints): [0] ticket counter of the dW kernel, [4 .. 4+B) one "dZ of this tile is complete" flag per tile,
-// then one "phase-A record written" flag per (layer, group) item of the dW kernel; zeroed before the chain launch.
+// then one "phase-A record written" flag per (layer, group) item of the dW kernel, then [B] "forward of this tile is
+// complete" flags (hexgnn_train_step only: the chain starts under the forward's last round); zeroed per call.
 constexpr int kSyncTileOff = 4;
-inline int64_t tc_sync_ints(const Dims& d, int64_t B) { return align_up(kSyncTileOff + B + (int64_t)(d.Lt - 1) * tc_dw_groups(d), 4); }
+inline int64_t tc_sync_fwd_off(const Dims& d, int64_t B) { return kSyncTileOff + B + (int64_t)(d.Lt - 1) * tc_dw_groups(d); }
+inline int64_t tc_sync_ints(const Dims& d, int64_t B) { return align_up(tc_sync_fwd_off(d, B) + B, 4); }
+
+// Fused TD loss of hexgnn_train_step: the chain kernel derives dL/dQ itself (td_loss.cu's formula, same fp32 operations).
+struct TdFuse {
+  const int64_t* action;   // [B] local action per graph; nullptr = dL/dQ comes in as d_nodes
+  const float* target;     // [B]
+  const float* weight;     // [B] or nullptr
+  const float* q;          // [N] forward output
+  const int* fwd_flag;     // [tiles] released by the forward kernel, or nullptr
+  int kind;
+  float scale;
+};
 struct TcBwdWs { int64_t pack, dz, small_rec, big_rec, head_rec, sum, sync, total; };
 inline TcBwdWs tc_bwd_ws(const Dims& d, int64_t B) {
   GradLayout gl;

@@ -354,6 +354,35 @@ class ModernTwoHeaded(nn.Module):
             return out_value, out_nodes             # (value[B], adv - mean[N]) (models.py:580-581)
         return out_nodes                            # [N] (models.py:584)
 
+    def train_step(self, x, edge_index, graph_indices=None, ptr=None, action=None, target=None, weight=None,
+                   kind="mse", scale=1.0, num_graphs: Optional[int] = None, csr: Optional[ops.CsrBlob] = None):
+        """The learner's ``loss.backward()`` block in one call (rainbow.py:301-316):
+
+            q = model(x, edge_index, graph_indices, ptr); td_est = q[action + ptr[:-1]]
+            loss = scale * mean(weight * l(target, td_est)); loss.backward()
+
+        Returns ``(loss, td_err, q)``; every ``p.grad`` is set (accumulated when gradients are still in place) exactly as
+        by the autograd route, bit for bit.  Because the loss gradient is derived inside the backward kernel, forward,
+        dH chain and dW GEMM overlap (hexgnn_train_step).  ``ptr`` is required; tensor-core path, default Q output."""
+        if ptr is None or action is None or target is None:
+            raise _lib.HexGnnError("train_step: ptr, action and target are required")
+        self._ensure_flat()
+        if csr is None:
+            csr = self.build_csr(edge_index, graph_indices, ptr, num_nodes=int(x.shape[0]), num_graphs=num_graphs)
+        self.last_csr = csr
+        self.final_conv_acts = None
+        accumulate = self._grads_in_place()
+        out = self._grad_scratch() if accumulate else self._flat_grad_buffer()
+        loss, td_err, q, grad = ops.fused_train_step(self._desc, self._flat, x, csr, ptr, action, target, weight, kind, scale,
+                                                     grad_out=out, fwd_ws=self._fwd_ws(csr), bwd_ws=self._bwd_ws(csr))
+        if accumulate:
+            self._flat_grad.add_(grad)
+        else:
+            self._point_grads()
+        if self.strict:
+            csr.raise_on_error()
+        return loss, td_err, q
+
     def simple_forward(self, data):
         if getattr(data, "batch", None) is not None:
             return self.forward(data.x, data.edge_index, data.batch, getattr(data, "ptr", None))

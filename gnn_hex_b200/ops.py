@@ -10,7 +10,7 @@ from ._lib import HEXGNN_ADV_ONLY, HEXGNN_SEPARATE, HEXGNN_PATH_SIMT, HEXGNN_PAT
 
 # kernels launched by each C-ABI call (csr: init, hist, scan, fill, sort; forward: pack, fused;
 # backward: pack, fused, reduce, unpack) -- bench.py's `gpu_launches` is read off this counter.
-LAUNCHES = {"build_csr": 5, "forward": 2, "backward": 5, "td_loss": 1, "mask_argmax": 1, "td_target": 1, "forward_big": 0, "allreduce_p2p": 1}
+LAUNCHES = {"build_csr": 5, "forward": 2, "backward": 5, "td_loss": 1, "train_step": 8, "mask_argmax": 1, "td_target": 1, "forward_big": 0, "allreduce_p2p": 1}
 launch_counter = 0
 
 
@@ -163,6 +163,47 @@ def fused_backward(desc, flat_params, x, csr, flags, d_nodes, d_value, stash, wa
 
 
 LOSS_KINDS = {"mse": 0, "smooth_l1": 1, "huber": 1}
+
+
+def fused_train_step(desc, flat_params, x, csr, ptr, action, target, weight=None, kind="mse", scale=1.0, grad_out=None,
+                     fwd_ws=None, bwd_ws=None):
+    """hexgnn_train_step: forward + TD loss + backward + gradient reduction in one call (rainbow.py:301-316).
+    Returns (loss [], td_err [B], q [N], flat gradient [P]).  Launches pack x2, forward, chain, dW, reduce, unpack, loss."""
+    _require_cuda(x, "x")
+    _require_cuda(flat_params, "parameters")
+    if kind not in LOSS_KINDS:
+        raise _lib.HexGnnError(f"train_step: unknown loss kind {kind!r}")
+    if x.dtype != torch.float32 or x.dim() != 2 or x.shape[1] != 3:
+        raise _lib.HexGnnError("x must be float32 [N,3]")
+    x = x.contiguous()
+    N, E, B = csr.N, csr.E, csr.B
+    dev = x.device
+    ptr = ptr.to(dev, non_blocking=True).contiguous()
+    action = action.to(dev, non_blocking=True).contiguous()
+    target = target.to(dev, non_blocking=True).contiguous().float()
+    if weight is not None:
+        weight = weight.to(dev, non_blocking=True).contiguous().float()
+    if ptr.dtype != torch.int64 or action.dtype != torch.int64 or ptr.numel() != B + 1 or target.numel() != B or \
+            action.numel() != B or x.shape[0] != N:
+        raise _lib.HexGnnError("train_step: x [N,3], ptr [B+1] int64, action [B] int64, target [B] expected")
+    sz = _lib.sizes(desc, N, E, B, csr.tile_rows)
+    if fwd_ws is None or fwd_ws.numel() * 4 < sz.fwd_ws_bytes:
+        fwd_ws = torch.empty(sz.fwd_ws_bytes // 4, dtype=torch.float32, device=dev)
+    if bwd_ws is None or bwd_ws.numel() * 4 < sz.bwd_ws_bytes:
+        bwd_ws = torch.empty(sz.bwd_ws_bytes // 4, dtype=torch.float32, device=dev)
+    if grad_out is None:
+        grad_out = torch.empty(flat_params.numel(), dtype=torch.float32, device=dev)
+    q = torch.empty(N, dtype=torch.float32, device=dev)
+    loss = torch.empty(1, dtype=torch.float32, device=dev)
+    td_err = torch.empty(B, dtype=torch.float32, device=dev)
+    stash = torch.empty(sz.stash_bytes // 4, dtype=torch.float32, device=dev)
+    rc = _lib.lib().hexgnn_train_step(C.byref(desc), _ptr(flat_params), _ptr(x), N, E, B, _ptr(csr.blob), csr.tile_rows, 0,
+                                      _ptr(ptr), _ptr(action), _ptr(target), _ptr(weight), LOSS_KINDS[kind], float(scale),
+                                      _ptr(q), _ptr(loss), _ptr(td_err), _ptr(stash), _ptr(grad_out),
+                                      _ptr(fwd_ws), fwd_ws.numel() * 4, _ptr(bwd_ws), bwd_ws.numel() * 4, _stream(dev))
+    _lib.check(rc, "hexgnn_train_step")
+    _count("train_step")
+    return loss.reshape(()), td_err, q, grad_out
 
 
 class _TDLoss(torch.autograd.Function):

@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define HEXGNN_ABI_VERSION 4
+#define HEXGNN_ABI_VERSION 5
 
 enum {
   HEXGNN_OK = 0,
@@ -150,6 +150,21 @@ int hexgnn_forward_big(const HexModelDesc* desc, const float* params, const floa
                        const void* csr, int32_t tile_rows, int32_t flags, int32_t max_rows, float* out_nodes,
                        float* out_value, void* ws, size_t ws_bytes, void* stream);
 
+/* One learner step in one call (replaces rainbow.py:301-316: Q = model(states); td_est = Q[action + ptr[:-1]];
+ * loss = mean(w * l(td_tgt, td_est)); loss.backward()): forward with stash, TD loss, backward and the deterministic
+ * gradient reduction.  Same results as hexgnn_forward + hexgnn_td_loss + hexgnn_backward (bit-identical gradients),
+ * but because dL/dQ is derived inside the backward kernel, the three tensor-core kernels are chained by programmatic
+ * dependent launch and hand 128-row tiles to each other through release/acquire flags: the dH chain starts on the SMs
+ * the forward's last round of tiles leaves idle, the dW GEMM on those the chain leaves idle.
+ *   q [N] (out) Q-values; loss [1] (out); td_err [B] (out, or NULL); grad_params (out, OVERWRITTEN); stash = stash_bytes;
+ *   fwd_ws = fwd_ws_bytes, bwd_ws = bwd_ws_bytes of hexgnn_sizes.  flags must be 0 (default Q output, tensor-core path).
+ *   ptr [B+1] i64, action [B] i64, target [B] f32, weight [B] f32 or NULL, kind / scale as in hexgnn_td_loss.          */
+int hexgnn_train_step(const HexModelDesc* desc, const float* params, const float* x, int64_t N, int64_t E, int64_t B,
+                      const void* csr, int32_t tile_rows, int32_t flags, const int64_t* ptr, const int64_t* action,
+                      const float* target, const float* weight, int32_t kind, float scale, float* q, float* loss,
+                      float* td_err, float* stash, float* grad_params, void* fwd_ws, size_t fwd_ws_bytes, void* bwd_ws,
+                      size_t bwd_ws_bytes, void* stream);
+
 /* Learner loss glue on device (replaces the index / loss / mean kernels of rainbow.py:301-312 and their autograd):
  *   td_est[g] = q[ptr[g] + action[g]];  td_err[g] = td_est[g] - target[g]  (PER priorities = |td_err| + 1e-6, :307-308)
  *   loss[0]   = scale * mean_g( weight[g] * l(target[g], td_est[g]) ),  kind 0: l = MSE, 1: l = SmoothL1 (beta 1), :85
@@ -199,7 +214,8 @@ int hexgnn_debug_phases(int32_t which, int64_t* host_out, int32_t n);
 
 /* Measurement aid (bench.py `roofline`): while enabled (process-wide; NOT re-entrant, use from one
  * stream at a time), hexgnn_forward and
- * hexgnn_backward bracket their kernels (which: 0 = fused forward, 1 = backward dH chain, 2 = backward dW GEMM) with
+ * hexgnn_backward bracket their kernels (which: 0 = fused forward, 1 = backward dH chain + dW GEMM (overlapped, one
+ * pair), 2 = the forward + chain + dW trio of hexgnn_train_step) with
  * CUDA events recorded on `stream`.  hexgnn_profile_read synchronises on the recorded events, returns
  * the summed device time (ms) and the number of bracketed launches since the last read, and resets.
  * This is the only mutable state the library keeps besides the thread-local error string. */

@@ -300,3 +300,40 @@ def test_oversize_graphs_board_size_transfer(mode):
     m.max_graph_nodes = 140
     with torch.no_grad(), pytest.raises(_lib.HexGnnError):
         m(d.x, d.edge_index, d.batch, d.ptr)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("size,count,kind,weighted", [
+    ("L", 256, "mse", True),          # 209 tiles on 148 CTAs: forward / chain / dW overlap through the tile flags
+    ("L", 40, "smooth_l1", False),    # fewer tiles than CTAs: no phase-A items, nothing to overlap
+    ("S", 256, "mse", True),
+])
+def test_train_step_equals_autograd_route(size, count, kind, weighted):
+    """hexgnn_train_step (forward + TD loss + backward chained by programmatic dependent launch, the loss gradient derived
+    inside the chain kernel) against forward -> td_loss -> backward as separate calls: the same bits (rainbow.py:301-316)."""
+    cfg = CONFIGS[size]
+    _, m = make_pair(cfg["hidden"], cfg["layers"])
+    m = m.to(DEV)
+    gs = data.load_positions(cfg["fixture"], maker=1)[:count]
+    hb = data.collate(gs)
+    b = hb.to(DEV)
+    action, target, weight = [t.to(DEV) for t in loss_inputs(hb)]
+    if not weighted:
+        weight = None
+    m.zero_grad(set_to_none=True)
+    q_ref = m(b.x, b.edge_index, b.batch, b.ptr)
+    loss_ref, err_ref = ops.td_loss(q_ref, b.ptr, action, target, weight, kind=kind, scale=0.5)
+    loss_ref.backward()
+    g_ref = m.flat_gradient.clone()
+    for _ in range(3):   # repeated: the flags / tickets are reset per call, results are bit-reproducible
+        m.zero_grad(set_to_none=True)
+        loss, err, q = m.train_step(b.x, b.edge_index, b.batch, b.ptr, action=action, target=target, weight=weight,
+                                    kind=kind, scale=0.5)
+        assert int(m.last_csr.status.item()) == 0
+        assert torch.equal(q, q_ref.detach())
+        assert torch.equal(loss, loss_ref.detach()) and torch.equal(err, err_ref)
+        assert torch.equal(m.flat_gradient, g_ref)
+    # gradients still in place: the next step accumulates, like autograd's +=
+    loss, err, q = m.train_step(b.x, b.edge_index, b.batch, b.ptr, action=action, target=target, weight=weight,
+                                kind=kind, scale=0.5)
+    assert torch.allclose(m.flat_gradient, 2 * g_ref, rtol=1e-6, atol=0)
