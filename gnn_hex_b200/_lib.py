@@ -87,7 +87,7 @@ def lib():
     l.hexgnn_stash_embed.argtypes = [D, i64, i64, i32, C.POINTER(i64), C.POINTER(i64)]
     l.hexgnn_train_step.restype = C.c_int
     l.hexgnn_train_step.argtypes = [p, p, p, i64, i64, i64, p, i32, i32, p, p, p, p, i32, C.c_float, p, p, p, p, p,
-                                    p, C.c_size_t, p, C.c_size_t, p]
+                                    p, C.c_size_t, p]
     l.hexgnn_td_loss.restype = C.c_int
     l.hexgnn_td_loss.argtypes = [p, p, p, p, p, i64, i64, i32, C.c_float, p, p, p, p]
     l.hexgnn_forward_big.restype = C.c_int

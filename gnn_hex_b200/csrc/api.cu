@@ -218,28 +218,25 @@ int hexgnn_backward(const HexModelDesc* desc, const float* params, const float* 
 int hexgnn_train_step(const HexModelDesc* desc, const float* params, const float* x, int64_t N, int64_t E, int64_t B,
                       const void* csr, int32_t tile_rows, int32_t flags, const int64_t* ptr, const int64_t* action,
                       const float* target, const float* weight, int32_t kind, float scale, float* q, float* loss,
-                      float* td_err, float* stash, float* grad_params, void* fwd_ws, size_t fwd_ws_bytes, void* bwd_ws,
-                      size_t bwd_ws_bytes, void* stream) {
+                      float* td_err, float* stash, float* grad_params, void* ws, size_t ws_bytes, void* stream) {
   Dims d;
   if (!make_dims(desc, &d)) { set_error("train_step: bad model descriptor"); return HEXGNN_E_BADARG; }
-  if (!params || !x || !csr || !ptr || !action || !target || !q || !loss || !stash || !grad_params || !fwd_ws || !bwd_ws ||
+  if (!params || !x || !csr || !ptr || !action || !target || !q || !loss || !stash || !grad_params || !ws ||
       N < 1 || B < 1 || E < 0) { set_error("train_step: bad argument"); return HEXGNN_E_BADARG; }
   if (kind != HEXGNN_LOSS_MSE && kind != HEXGNN_LOSS_SMOOTH_L1) { set_error("train_step: unknown loss kind %d", kind); return HEXGNN_E_BADARG; }
   if (flags & (HEXGNN_ADV_ONLY | HEXGNN_SEPARATE | HEXGNN_PATH_SIMT)) { set_error("train_step: only the default Q output on the tensor-core path"); return HEXGNN_E_UNSUPPORTED; }
   if (!tile_rows_ok(tile_rows) || !tc_bwd_supported(d)) { set_error("train_step: unsupported tile_rows=%d or hidden=%d", tile_rows, d.H); return HEXGNN_E_UNSUPPORTED; }
   const TcBwdWs w = tc_bwd_ws(d, B);
-  if ((int64_t)fwd_ws_bytes < tc_pack_floats(d) * 4 || (int64_t)bwd_ws_bytes < w.total * 4) { set_error("train_step: workspace too small"); return HEXGNN_E_WORKSPACE; }
+  if ((int64_t)ws_bytes < w.total * 4) { set_error("train_step: workspace too small (%zu < %lld)", ws_bytes, (long long)w.total * 4); return HEXGNN_E_WORKSPACE; }
   ParamMap pm;
   make_param_map(d, &pm);
   cudaStream_t st = (cudaStream_t)stream;
-  float* wsf = (float*)bwd_ws;
+  float* wsf = (float*)ws;
   int* sync = (int*)(wsf + w.sync);
   // everything the three overlapped kernels need besides each other's tiles is produced first
   HEX_CUDA_CHECK(cudaMemsetAsync(sync, 0, (size_t)tc_sync_ints(d, B) * 4, st));
-  TcPackView fpv = tc_pack_view(fwd_ws, d), bpv = tc_pack_view(wsf + w.pack, d);
-  int rc = launch_pack_tc(d, pm, params, x, fpv, false, st);
-  if (rc) return rc;
-  rc = launch_pack_tc(d, pm, params, x, bpv, true, st);
+  TcPackView tpv = tc_pack_view(wsf + w.pack, d);   // one pack launch writes the forward AND the backward images
+  int rc = launch_pack_tc(d, pm, params, x, tpv, true, st);
   if (rc) return rc;
   const int grid = bwd_grid_ctas();
   int* fwd_flag = sync + tc_sync_fwd_off(d, B);
@@ -249,9 +246,9 @@ int hexgnn_train_step(const HexModelDesc* desc, const float* params, const float
     // through flags: ONE event pair around the three (slot 2)
     ProfScope prof(2, st);
     ++g_prof_mute;
-    rc = launch_forward_tc(d, pm, params, x, N, E, B, csr, flags, q, nullptr, stash, fpv, st, fwd_flag);
+    rc = launch_forward_tc(d, pm, params, x, N, E, B, csr, flags, q, nullptr, stash, tpv, st, fwd_flag);
     if (!rc) rc = launch_backward_tc_chain(d, pm, params, x, N, E, B, csr, flags, nullptr, nullptr, stash, wsf + w.dz, nullptr,
-                                           bpv, wsf + w.small_rec, wsf + w.head_rec, sync, grid, st, &fuse);
+                                           tpv, wsf + w.small_rec, wsf + w.head_rec, sync, grid, st, &fuse);
     if (!rc) rc = launch_backward_tc_dw(d, N, E, B, csr, stash, wsf + w.dz, wsf + w.big_rec, sync, st);
     --g_prof_mute;
     if (rc) return rc;

@@ -82,6 +82,9 @@ inline void make_param_map(const Dims& d, ParamMap* pm) {
 // ---- csr blob ---------------------------------------------------------------------------
 inline int64_t align_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
 
+constexpr int kScanBlockElems = 1024;   // csr_scan_kernel: 256 threads x int4
+__host__ __device__ inline int64_t csr_scan_blocks(int64_t N) { return (N + 1 + kScanBlockElems - 1) / kScanBlockElems; }
+
 inline void csr_layout(int64_t N, int64_t E, int64_t B, HexCsrLayout* o) {
   int64_t w = 0;
   o->status = w; w += 1;
@@ -92,6 +95,8 @@ inline void csr_layout(int64_t N, int64_t E, int64_t B, HexCsrLayout* o) {
   o->col = w; w += E; w = align_up(w, 4);
   o->tile_g0 = w; w += B + 1; w = align_up(w, 4);
   o->scratch = w; w += (N + 1) + E; w = align_up(w, 4);  // cursor[N+1], edge ids [E]
+  w += 4 + 2 * csr_scan_blocks(N);                       // scan ticket + one 64-bit look-back state per scan block
+  w = align_up(w, 4);
   o->total_words = w;
 }
 
@@ -105,6 +110,8 @@ struct CsrView {
   int* tile_g0;
   int* cursor;
   int* eid;
+  int* scan_ticket;                 // [4] (only [0] used)
+  unsigned long long* scan_state;   // [csr_scan_blocks(N)]: flag << 32 | value
 };
 
 inline CsrView csr_view(void* blob, int64_t N, int64_t E, int64_t B) {
@@ -120,6 +127,8 @@ inline CsrView csr_view(void* blob, int64_t N, int64_t E, int64_t B) {
   v.tile_g0 = w + l.tile_g0;
   v.cursor = w + l.scratch;
   v.eid = w + l.scratch + (N + 1);
+  v.scan_ticket = w + align_up(l.scratch + (N + 1) + E, 4);
+  v.scan_state = (unsigned long long*)(v.scan_ticket + 4);
   return v;
 }
 

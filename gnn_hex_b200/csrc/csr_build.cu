@@ -15,7 +15,8 @@ __global__ void csr_init_kernel(CsrView v, const int64_t* __restrict__ batch, co
                                 int N, int B) {
   const int tid = blockIdx.x * blockDim.x + threadIdx.x;
   const int nth = gridDim.x * blockDim.x;
-  if (tid == 0) { *v.status = 0; *v.ntiles = 0; }
+  if (tid == 0) { *v.status = 0; *v.ntiles = 0; v.scan_ticket[0] = 0; }
+  for (int i = tid; i < (int)csr_scan_blocks(N); i += nth) v.scan_state[i] = 0ull;
   for (int i = tid; i <= N; i += nth) v.cursor[i] = 0;  // cursor doubles as the degree histogram
   if (ptr) {
     for (int g = tid; g <= B; g += nth) v.gptr[g] = (int)ptr[g];
@@ -44,58 +45,72 @@ __global__ void csr_hist_kernel(CsrView v, const int64_t* __restrict__ ei, int E
   }
 }
 
-// ---- 3. exclusive scan of the histogram (single CTA; N is a few 10^4..10^5) ----------------------
-// Warp w owns a contiguous range (a multiple of 128 entries); inside it a step is one coalesced int4 per lane.
-// Pass 1: every lane sums its int4s of all steps (independent loads, all in flight), warp reduce, the 32 warp totals
-// are scanned; pass 2 re-reads (cache hot), does the in-step scan with shuffles and writes rowptr.
-__global__ void __launch_bounds__(1024) csr_scan_kernel(CsrView v, int N) {
-  __shared__ int warp_sums[32];
+// ---- 3. exclusive scan of the histogram: single pass, decoupled look-back ---------------------------------------
+// Block (by ticket, so every predecessor is resident or done) = 1024 entries, one int4 per thread.  It publishes its
+// aggregate, looks back over the predecessors' states (flag 1 = aggregate, 2 = inclusive prefix) one warp-wide window
+// at a time, publishes its inclusive prefix, and writes rowptr.  All blocks run concurrently: two or three L2 round
+// trips in total instead of one CTA walking the whole array (16 us for 20 k entries).
+__global__ void __launch_bounds__(256) csr_scan_kernel(CsrView v, int N) {
+  __shared__ int warp_sums[8];
+  __shared__ int bid_s, prefix_s;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  if (tid == 0) bid_s = atomicAdd(v.scan_ticket, 1);
+  __syncthreads();
+  const int bid = bid_s;
   const int M = N + 1;
-  const int per_warp = ((M + 31) / 32 + 127) / 128 * 128;
-  const int w0 = wid * per_warp, w1 = (w0 + per_warp < M) ? w0 + per_warp : M;
-  const int4* c4 = (const int4*)v.cursor;
-  int tsum = 0;
-  for (int base = w0; base < w1; base += 128) {
-    const int i = base + lane * 4;
-    if (i + 3 < M) { const int4 a = c4[i >> 2]; tsum += a.x + a.y + a.z + a.w; }
-    else { for (int k = 0; k < 4; ++k) if (i + k < M) tsum += v.cursor[i + k]; }
-  }
+  const int i0 = bid * kScanBlockElems + tid * 4;
+  int a[4] = {0, 0, 0, 0};
+  if (i0 + 3 < M) { const int4 t = *(const int4*)(v.cursor + i0); a[0] = t.x; a[1] = t.y; a[2] = t.z; a[3] = t.w; }
+  else { for (int k = 0; k < 4; ++k) if (i0 + k < M) a[k] = v.cursor[i0 + k]; }
+  const int ls = a[0] + a[1] + a[2] + a[3];
+  int inc = ls;
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) tsum += __shfl_xor_sync(0xffffffffu, tsum, o);
-  if (lane == 0) warp_sums[wid] = tsum;
+  for (int o = 1; o < 32; o <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
+  }
+  if (lane == 31) warp_sums[wid] = inc;
   __syncthreads();
+  int wbase = 0, agg = 0;
+#pragma unroll
+  for (int w = 0; w < 8; ++w) { const int t = warp_sums[w]; if (w < wid) wbase += t; agg += t; }
   if (wid == 0) {
-    const int ws = warp_sums[lane];
-    int winc = ws;
+    volatile unsigned long long* st = v.scan_state;
+    int prefix = 0;
+    if (bid > 0) {
+      if (lane == 0) { st[bid] = (1ull << 32) | (unsigned)agg; }
+      int hi = bid - 1;                                   // look-back window [hi-31, hi]
+      while (true) {
+        const int j = hi - lane;
+        unsigned long long sv = 2ull << 32;               // out-of-range lanes: a zero prefix
+        if (j >= 0) { do { sv = st[j]; } while ((sv >> 32) == 0); }
+        const unsigned full = __ballot_sync(0xffffffffu, (sv >> 32) == 2);
+        const int stop = full ? (__ffs(full) - 1) : 32;   // nearest predecessor that already has its prefix
+        int val = (lane <= stop) ? (int)(unsigned)sv : 0;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      int t = __shfl_up_sync(0xffffffffu, winc, o);
-      if (lane >= o) winc += t;
+        for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(0xffffffffu, val, o);
+        prefix += val;
+        if (full) break;
+        hi -= 32;
+      }
     }
-    warp_sums[lane] = winc - ws;  // exclusive
+    if (lane == 0) {
+      __threadfence();
+      st[bid] = (2ull << 32) | (unsigned)(prefix + agg);
+      prefix_s = prefix;
+    }
   }
   __syncthreads();
-  int carry = warp_sums[wid];
-  for (int base = w0; base < w1; base += 128) {
-    const int i = base + lane * 4;
-    int a[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) a[k] = (i + k < M) ? v.cursor[i + k] : 0;
-    const int ls = a[0] + a[1] + a[2] + a[3];
-    int inc = ls;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      int t = __shfl_up_sync(0xffffffffu, inc, o);
-      if (lane >= o) inc += t;
-    }
-    int ex = carry + inc - ls;
-#pragma unroll
+  int ex = prefix_s + wbase + inc - ls;
+  if (i0 + 3 < M) {
+    int4 r; r.x = ex; r.y = ex + a[0]; r.z = r.y + a[1]; r.w = r.z + a[2];
+    *(int4*)(v.rowptr + i0) = r;
+    *(int4*)(v.cursor + i0) = make_int4(0, 0, 0, 0);
+  } else {
     for (int k = 0; k < 4; ++k) {
-      if (i + k < M) { v.rowptr[i + k] = ex; v.cursor[i + k] = 0; }
+      if (i0 + k < M) { v.rowptr[i0 + k] = ex; v.cursor[i0 + k] = 0; }
       ex += a[k];
     }
-    carry += __shfl_sync(0xffffffffu, inc, 31);
   }
 }
 
@@ -103,43 +118,45 @@ __global__ void __launch_bounds__(1024) csr_scan_kernel(CsrView v, int N) {
 __global__ void csr_fill_kernel(CsrView v, const int64_t* __restrict__ ei, int E, int N, int B, int tile_rows,
                                 int tile_edges) {
   if (blockIdx.x == gridDim.x - 1) {
-    // Greedy packing of whole graphs into tiles of <= tile_rows nodes, <= tile_edges edges,
-    // <= kMaxTileGraphs graphs.  The scan is sequential by nature, so the block first stages the per-graph
-    // node / edge counts in shared memory (parallel, coalesced: the dependent global loads were the whole cost),
-    // then one thread walks them.
-    constexpr int kChunk = 1024;
-    __shared__ int n_s[kChunk], ne_s[kChunk];
-    __shared__ int st_s[5];   // t, rows, edges, cnt, status
-    if (threadIdx.x == 0) { st_s[0] = 0; st_s[1] = 0; st_s[2] = 0; st_s[3] = 0; st_s[4] = 0; v.tile_g0[0] = 0; }
+    // Greedy packing of whole graphs into tiles of <= tile_rows nodes, <= tile_edges edges, <= kMaxTileGraphs graphs:
+    // tile starts s_0 = 0, s_{k+1} = next[s_k], where next[i] = first graph that no longer fits a tile opened at graph i
+    // (graph i itself is always taken, also when it is too large on its own).  next[] is computed by all threads in
+    // parallel from staged per-graph counts (a tile holds at most kMaxTileGraphs graphs, so the look-ahead is bounded);
+    // one thread then only chases the pointers (one shared-memory load per TILE instead of a dependent
+    // compare-and-add chain per GRAPH).
+    constexpr int kChunk = 1024, kAhead = kMaxTileGraphs;
+    __shared__ int n_s[kChunk + kAhead], ne_s[kChunk + kAhead], next_s[kChunk];
+    __shared__ int st_s[2];   // next tile start, tiles so far
+    if (threadIdx.x == 0) { st_s[0] = 0; st_s[1] = 0; v.tile_g0[0] = 0; }
+    int status = 0;
     for (int gb = 0; gb < B; gb += kChunk) {
       const int gn = (B - gb) < kChunk ? (B - gb) : kChunk;
+      const int gl = (B - gb) < kChunk + kAhead ? (B - gb) : kChunk + kAhead;   // staged incl. look-ahead
       __syncthreads();
-      for (int i = threadIdx.x; i < gn; i += blockDim.x) {
+      for (int i = threadIdx.x; i < gl; i += blockDim.x) {
         const int r0 = v.gptr[gb + i], r1 = v.gptr[gb + i + 1];
         n_s[i] = r1 - r0;
         ne_s[i] = v.rowptr[r1] - v.rowptr[r0];
       }
       __syncthreads();
-      if (threadIdx.x == 0) {
-        int t = st_s[0], rows = st_s[1], edges = st_s[2], cnt = st_s[3], status = st_s[4];
-        for (int i = 0; i < gn; ++i) {
-          const int n = n_s[i], ne = ne_s[i];
-          if (n > tile_rows || ne > tile_edges) status |= HEXGNN_ST_GRAPH_TOO_LARGE;
-          if (cnt > 0 && (rows + n > tile_rows || edges + ne > tile_edges || cnt >= kMaxTileGraphs)) {
-            v.tile_g0[++t] = gb + i;
-            rows = edges = cnt = 0;
-          }
-          rows += n; edges += ne; ++cnt;
+      for (int i = threadIdx.x; i < gn; i += blockDim.x) {
+        int rows = n_s[i], edges = ne_s[i], cnt = 1, j = i + 1;
+        if (rows > tile_rows || edges > tile_edges) status |= HEXGNN_ST_GRAPH_TOO_LARGE;
+        while (j < gl && cnt < kMaxTileGraphs && rows + n_s[j] <= tile_rows && edges + ne_s[j] <= tile_edges) {
+          rows += n_s[j]; edges += ne_s[j]; ++cnt; ++j;
         }
-        st_s[0] = t; st_s[1] = rows; st_s[2] = edges; st_s[3] = cnt; st_s[4] = status;
+        next_s[i] = gb + j;
+      }
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        int g = st_s[0], t = st_s[1];
+        while (g < gb + gn) { g = next_s[g - gb]; v.tile_g0[++t] = g; }
+        st_s[0] = g; st_s[1] = t;
       }
     }
-    if (threadIdx.x == 0) {
-      int t = st_s[0];
-      if (B > 0) v.tile_g0[++t] = B;
-      *v.ntiles = t;
-      if (st_s[4]) atomicOr(v.status, st_s[4]);
-    }
+    if (status) atomicOr(v.status, status);
+    __syncthreads();
+    if (threadIdx.x == 0) *v.ntiles = st_s[1];
     return;
   }
   const int nth = (gridDim.x - 1) * blockDim.x;
@@ -176,7 +193,7 @@ int launch_build_csr(const int64_t* edge_index, int64_t E, const int64_t* batch,
   const int64_t init_n = (N + 1 > B + 1) ? N + 1 : B + 1;
   csr_init_kernel<<<blocks(init_n), threads, 0, st>>>(v, batch, ptr, (int)N, (int)B);
   if (E > 0) csr_hist_kernel<<<blocks(E), threads, 0, st>>>(v, edge_index, (int)E, (int)N);
-  csr_scan_kernel<<<1, 1024, 0, st>>>(v, (int)N);
+  csr_scan_kernel<<<(int)csr_scan_blocks(N), 256, 0, st>>>(v, (int)N);
   csr_fill_kernel<<<blocks(E) + 1, threads, 0, st>>>(v, edge_index, (int)E, (int)N, (int)B, tile_rows,
                                                     tile_rows * kEdgeCapPerRow);
   if (E > 0) csr_rank_kernel<<<blocks(E), threads, 0, st>>>(v, edge_index, (int)E, (int)N);

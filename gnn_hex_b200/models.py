@@ -374,7 +374,7 @@ class ModernTwoHeaded(nn.Module):
         accumulate = self._grads_in_place()
         out = self._grad_scratch() if accumulate else self._flat_grad_buffer()
         loss, td_err, q, grad = ops.fused_train_step(self._desc, self._flat, x, csr, ptr, action, target, weight, kind, scale,
-                                                     grad_out=out, fwd_ws=self._fwd_ws(csr), bwd_ws=self._bwd_ws(csr))
+                                                     grad_out=out, ws=self._bwd_ws(csr))
         if accumulate:
             self._flat_grad.add_(grad)
         else:

@@ -10,7 +10,7 @@ from ._lib import HEXGNN_ADV_ONLY, HEXGNN_SEPARATE, HEXGNN_PATH_SIMT, HEXGNN_PAT
 
 # kernels launched by each C-ABI call (csr: init, hist, scan, fill, sort; forward: pack, fused;
 # backward: pack, fused, reduce, unpack) -- bench.py's `gpu_launches` is read off this counter.
-LAUNCHES = {"build_csr": 5, "forward": 2, "backward": 5, "td_loss": 1, "train_step": 8, "mask_argmax": 1, "td_target": 1, "forward_big": 0, "allreduce_p2p": 1}
+LAUNCHES = {"build_csr": 5, "forward": 2, "backward": 5, "td_loss": 1, "train_step": 7, "mask_argmax": 1, "td_target": 1, "forward_big": 0, "allreduce_p2p": 1}
 launch_counter = 0
 
 
@@ -166,9 +166,9 @@ LOSS_KINDS = {"mse": 0, "smooth_l1": 1, "huber": 1}
 
 
 def fused_train_step(desc, flat_params, x, csr, ptr, action, target, weight=None, kind="mse", scale=1.0, grad_out=None,
-                     fwd_ws=None, bwd_ws=None):
+                     ws=None):
     """hexgnn_train_step: forward + TD loss + backward + gradient reduction in one call (rainbow.py:301-316).
-    Returns (loss [], td_err [B], q [N], flat gradient [P]).  Launches pack x2, forward, chain, dW, reduce, unpack, loss."""
+    Returns (loss [], td_err [B], q [N], flat gradient [P]).  Launches pack, forward, chain, dW, reduce, unpack, loss."""
     _require_cuda(x, "x")
     _require_cuda(flat_params, "parameters")
     if kind not in LOSS_KINDS:
@@ -187,10 +187,8 @@ def fused_train_step(desc, flat_params, x, csr, ptr, action, target, weight=None
             action.numel() != B or x.shape[0] != N:
         raise _lib.HexGnnError("train_step: x [N,3], ptr [B+1] int64, action [B] int64, target [B] expected")
     sz = _lib.sizes(desc, N, E, B, csr.tile_rows)
-    if fwd_ws is None or fwd_ws.numel() * 4 < sz.fwd_ws_bytes:
-        fwd_ws = torch.empty(sz.fwd_ws_bytes // 4, dtype=torch.float32, device=dev)
-    if bwd_ws is None or bwd_ws.numel() * 4 < sz.bwd_ws_bytes:
-        bwd_ws = torch.empty(sz.bwd_ws_bytes // 4, dtype=torch.float32, device=dev)
+    if ws is None or ws.numel() * 4 < sz.bwd_ws_bytes:
+        ws = torch.empty(sz.bwd_ws_bytes // 4, dtype=torch.float32, device=dev)
     if grad_out is None:
         grad_out = torch.empty(flat_params.numel(), dtype=torch.float32, device=dev)
     q = torch.empty(N, dtype=torch.float32, device=dev)
@@ -200,7 +198,7 @@ def fused_train_step(desc, flat_params, x, csr, ptr, action, target, weight=None
     rc = _lib.lib().hexgnn_train_step(C.byref(desc), _ptr(flat_params), _ptr(x), N, E, B, _ptr(csr.blob), csr.tile_rows, 0,
                                       _ptr(ptr), _ptr(action), _ptr(target), _ptr(weight), LOSS_KINDS[kind], float(scale),
                                       _ptr(q), _ptr(loss), _ptr(td_err), _ptr(stash), _ptr(grad_out),
-                                      _ptr(fwd_ws), fwd_ws.numel() * 4, _ptr(bwd_ws), bwd_ws.numel() * 4, _stream(dev))
+                                      _ptr(ws), ws.numel() * 4, _stream(dev))
     _lib.check(rc, "hexgnn_train_step")
     _count("train_step")
     return loss.reshape(()), td_err, q, grad_out

@@ -157,13 +157,12 @@ int hexgnn_forward_big(const HexModelDesc* desc, const float* params, const floa
  * dependent launch and hand 128-row tiles to each other through release/acquire flags: the dH chain starts on the SMs
  * the forward's last round of tiles leaves idle, the dW GEMM on those the chain leaves idle.
  *   q [N] (out) Q-values; loss [1] (out); td_err [B] (out, or NULL); grad_params (out, OVERWRITTEN); stash = stash_bytes;
- *   fwd_ws = fwd_ws_bytes, bwd_ws = bwd_ws_bytes of hexgnn_sizes.  flags must be 0 (default Q output, tensor-core path).
+ *   ws = bwd_ws_bytes of hexgnn_sizes.  flags must be 0 (default Q output, tensor-core path).
  *   ptr [B+1] i64, action [B] i64, target [B] f32, weight [B] f32 or NULL, kind / scale as in hexgnn_td_loss.          */
 int hexgnn_train_step(const HexModelDesc* desc, const float* params, const float* x, int64_t N, int64_t E, int64_t B,
                       const void* csr, int32_t tile_rows, int32_t flags, const int64_t* ptr, const int64_t* action,
                       const float* target, const float* weight, int32_t kind, float scale, float* q, float* loss,
-                      float* td_err, float* stash, float* grad_params, void* fwd_ws, size_t fwd_ws_bytes, void* bwd_ws,
-                      size_t bwd_ws_bytes, void* stream);
+                      float* td_err, float* stash, float* grad_params, void* ws, size_t ws_bytes, void* stream);
 
 /* Learner loss glue on device (replaces the index / loss / mean kernels of rainbow.py:301-312 and their autograd):
  *   td_est[g] = q[ptr[g] + action[g]];  td_err[g] = td_est[g] - target[g]  (PER priorities = |td_err| + 1e-6, :307-308)
