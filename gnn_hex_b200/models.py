@@ -136,6 +136,7 @@ class ModernTwoHeaded(nn.Module):
         self._slices = None
         self._ws = {}
         self._flat_grad = None
+        self._grad_views = {}
         self._p2p = None
         self.last_csr = None
 
@@ -175,6 +176,7 @@ class ModernTwoHeaded(nn.Module):
         self._flat_version += 1
         self._ws = {}
         self._flat_grad = None
+        self._grad_views = {}
         self._params_cache = ps
 
     def _ensure_flat(self):
@@ -233,9 +235,31 @@ class ModernTwoHeaded(nn.Module):
 
     def _point_grads(self):
         fg = self._flat_grad
-        for p, (o, n, shp) in zip(self._params_cache, self._slices):
+        key = (fg.data_ptr(), self._flat_version)
+        views = self._grad_views.get(key)
+        if views is None:
+            # the views of a flat buffer are built once per buffer (P2P mode alternates between two buffers): a step
+            # then costs one attribute store per parameter instead of two tensor constructions
+            views = [fg[o:o + n].view(shp) for (o, n, shp) in self._slices]
+            if len(self._grad_views) > 4:
+                self._grad_views.clear()
+            self._grad_views[key] = views
+        for p, g in zip(self._params_cache, views):
             if p.requires_grad:
-                p.grad = fg[o:o + n].view(shp)
+                p.grad = g
+
+    def zero_grad(self, set_to_none: bool = True):
+        """nn.Module.zero_grad over the cached parameter list (the generic version walks the module tree: ~0.1 ms of
+        host time per learner step, more than the device spends on the CSR build)."""
+        if self._flat is None or getattr(self, "_params_cache", None) is None:
+            return super().zero_grad(set_to_none=set_to_none)
+        if set_to_none:
+            for p in self._params_cache:
+                p.grad = None
+        elif self._grads_in_place():
+            self._flat_grad.zero_()
+        else:
+            super().zero_grad(set_to_none=False)
 
     @property
     def flat_gradient(self):
