@@ -4,6 +4,7 @@ The package is a thin host layer over libhexgnn.so (include/hexgnn.h).  Importin
 or falls back: a missing library raises on first use (python -m gnn_hex_b200.build).
 """
 from ._lib import HexGnnError  # noqa: F401
-from .models import ModernTwoHeaded, get_pre_defined  # noqa: F401
-from .ops import CsrBlob, build_csr, fused_backward, fused_forward, mask_argmax, td_loss, td_target  # noqa: F401
+from .models import FusedAdam, ModernTwoHeaded, get_pre_defined  # noqa: F401
+from .ops import (CsrBlob, adam_step, build_csr, fused_backward, fused_forward, fused_train_step, mask_argmax,  # noqa: F401
+                  td_loss, td_target)
 from . import data  # noqa: F401

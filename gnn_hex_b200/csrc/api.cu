@@ -260,6 +260,22 @@ int hexgnn_train_step(const HexModelDesc* desc, const float* params, const float
   return launch_td_loss(q, ptr, action, target, weight, N, B, kind, scale, loss, td_err, nullptr, st);
 }
 
+int64_t hexgnn_adam_ws_bytes(void) { return (int64_t)adam_ws_floats() * 4; }
+
+int hexgnn_adam_step(const HexModelDesc* desc, float* params, float* grads, float* exp_avg, float* exp_avg_sq,
+                     int32_t* state, const float* x, float lr, float beta1, float beta2, float eps, float max_grad_norm,
+                     int32_t flags, float* grad_norm, void* ws, size_t ws_bytes, void* stream) {
+  Dims d;
+  if (!make_dims(desc, &d)) { set_error("adam_step: bad model descriptor"); return HEXGNN_E_BADARG; }
+  if (!params || !grads || !exp_avg || !exp_avg_sq || !state || !x || !ws) { set_error("adam_step: bad argument"); return HEXGNN_E_BADARG; }
+  if (!(lr >= 0.f) || !(beta1 >= 0.f && beta1 < 1.f) || !(beta2 >= 0.f && beta2 < 1.f) || !(eps >= 0.f)) { set_error("adam_step: bad hyper-parameter"); return HEXGNN_E_BADARG; }
+  if ((int64_t)ws_bytes < hexgnn_adam_ws_bytes()) { set_error("adam_step: workspace too small"); return HEXGNN_E_WORKSPACE; }
+  ParamMap pm;
+  make_param_map(d, &pm);
+  return launch_adam_step(d, pm, params, grads, exp_avg, exp_avg_sq, state, x, lr, beta1, beta2, eps, max_grad_norm,
+                          (flags & HEXGNN_ADAM_SKIP_UNTAKEN) ? 1 : 0, grad_norm, (float*)ws, (cudaStream_t)stream);
+}
+
 int hexgnn_td_loss(const float* q, const int64_t* ptr, const int64_t* action, const float* target, const float* weight,
                    int64_t N, int64_t B, int32_t kind, float scale, float* loss, float* td_err, float* d_q, void* stream) {
   if (!q || !ptr || !action || !target || !loss || N < 1 || B < 1) { set_error("td_loss: bad argument"); return HEXGNN_E_BADARG; }

@@ -218,6 +218,10 @@ int launch_unpack_grads(const Dims& d, const ParamMap& pm, const float* x, const
                         cudaStream_t st);
 int launch_td_loss(const float* q, const int64_t* ptr, const int64_t* action, const float* target, const float* weight,
                    int64_t N, int64_t B, int kind, float scale, float* loss, float* td_err, float* d_q, cudaStream_t st);
+int launch_adam_step(const Dims& d, const ParamMap& pm, float* params, float* grads, float* exp_avg, float* exp_avg_sq,
+                     int* state, const float* x, float lr, float beta1, float beta2, float eps, float max_norm,
+                     int skip_untaken, float* grad_norm, float* ws, cudaStream_t st);
+int adam_ws_floats();
 int launch_forward_big(const Dims& d, const ParamMap& pm, const float* params, const float* x, int64_t N, int64_t E,
                        int64_t B, const void* csr, int tile_rows, int flags, int max_rows, float* out_nodes,
                        float* out_value, float* ws, cudaStream_t st);

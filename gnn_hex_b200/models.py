@@ -407,6 +407,16 @@ class ModernTwoHeaded(nn.Module):
             csr.raise_on_error()
         return loss, td_err, q
 
+    @torch.no_grad()
+    def copy_parameters_from(self, other):
+        """`q_target.load_state_dict(q_policy.state_dict())` (rainbow.py:163-164) as ONE device-to-device copy of the flat
+        parameter buffer."""
+        self._ensure_flat()
+        other._ensure_flat()
+        if other._flat.numel() != self._flat.numel():
+            raise _lib.HexGnnError("copy_parameters_from: different architectures")
+        self._flat.copy_(other._flat, non_blocking=True)
+
     def simple_forward(self, data):
         if getattr(data, "batch", None) is not None:
             return self.forward(data.x, data.edge_index, data.batch, getattr(data, "ptr", None))
@@ -423,6 +433,61 @@ class ModernTwoHeaded(nn.Module):
         raise NotImplementedError("grow_width/grow_depth (GN0/models.py:494-508) are outside the fused path")
 
     grow_depth = grow_width
+
+
+class FusedAdam:
+    """`nn.utils.clip_grad_norm_` + `torch.optim.Adam(model.parameters(), lr, eps=...)` of the learner
+    (rainbow.py:79,320,325-326) as two launches over the model's flat parameter / gradient buffers.
+
+        opt = FusedAdam(model, lr=args.lr, eps=args.adam_eps, max_grad_norm=args.max_grad_norm)
+        loss, td_err, q = model.train_step(...)        # or loss.backward()
+        grad_norm = opt.step(x)                        # x: the batch features (x[0,2] tells which head was trained)
+        model.zero_grad()
+
+    `skip_untaken=False` reproduces the reference environment (torch 1.13: `opt.zero_grad()` keeps zero gradients, so a
+    head that is not trained in a step still receives its Adam momentum); True gives torch >= 2 `set_to_none` behaviour.
+    `state_dict()` / `load_state_dict()` carry exp_avg, exp_avg_sq and the three step counters."""
+
+    def __init__(self, model, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, max_grad_norm=0.0, skip_untaken=False):
+        self.model, self.lr, self.betas, self.eps = model, float(lr), tuple(betas), float(eps)
+        self.max_grad_norm, self.skip_untaken = float(max_grad_norm), bool(skip_untaken)
+        self._version = -1
+        self.exp_avg = self.exp_avg_sq = self.state = self._ws = None
+
+    def _ensure(self):
+        m = self.model
+        m._ensure_flat()
+        if self._version != m._flat_version or self.exp_avg is None or self.exp_avg.device != m._flat.device:
+            old = (self.exp_avg, self.exp_avg_sq, self.state)
+            self.exp_avg = torch.zeros_like(m._flat)
+            self.exp_avg_sq = torch.zeros_like(m._flat)
+            self.state = torch.zeros(4, dtype=torch.int32, device=m._flat.device)
+            if old[0] is not None and old[0].numel() == m._flat.numel():   # parameters moved (.to()): keep the moments
+                self.exp_avg.copy_(old[0]); self.exp_avg_sq.copy_(old[1]); self.state.copy_(old[2])
+            self._version = m._flat_version
+
+    @torch.no_grad()
+    def step(self, x):
+        self._ensure()
+        g = self.model.flat_gradient
+        if g is None:
+            raise _lib.HexGnnError("FusedAdam.step: no gradient (run train_step or backward first)")
+        return ops.adam_step(self.model._desc, self.model._flat, g, self.exp_avg, self.exp_avg_sq, self.state, x, self.lr,
+                             self.betas, self.eps, self.max_grad_norm, self.skip_untaken)
+
+    def zero_grad(self, set_to_none=True):
+        self.model.zero_grad(set_to_none=set_to_none)
+
+    def state_dict(self):
+        self._ensure()
+        return {"exp_avg": self.exp_avg.clone(), "exp_avg_sq": self.exp_avg_sq.clone(), "steps": self.state.clone(),
+                "lr": self.lr, "betas": self.betas, "eps": self.eps, "max_grad_norm": self.max_grad_norm}
+
+    def load_state_dict(self, sd):
+        self._ensure()
+        self.exp_avg.copy_(sd["exp_avg"]); self.exp_avg_sq.copy_(sd["exp_avg_sq"]); self.state.copy_(sd["steps"])
+        self.lr, self.betas, self.eps = float(sd["lr"]), tuple(sd["betas"]), float(sd["eps"])
+        self.max_grad_norm = float(sd.get("max_grad_norm", self.max_grad_norm))
 
 
 def get_pre_defined(name, args=None):

@@ -10,7 +10,7 @@ from ._lib import HEXGNN_ADV_ONLY, HEXGNN_SEPARATE, HEXGNN_PATH_SIMT, HEXGNN_PAT
 
 # kernels launched by each C-ABI call (csr: init, hist, scan, fill, sort; forward: pack, fused;
 # backward: pack, fused, reduce, unpack) -- bench.py's `gpu_launches` is read off this counter.
-LAUNCHES = {"build_csr": 5, "forward": 2, "backward": 5, "td_loss": 1, "train_step": 7, "mask_argmax": 1, "td_target": 1, "forward_big": 0, "allreduce_p2p": 1}
+LAUNCHES = {"build_csr": 5, "forward": 2, "backward": 5, "td_loss": 1, "train_step": 7, "adam_step": 2, "mask_argmax": 1, "td_target": 1, "forward_big": 0, "allreduce_p2p": 1}
 launch_counter = 0
 
 
@@ -314,3 +314,29 @@ def allreduce_p2p(peer_ptrs_dev, world, n, out):
     _lib.check(rc, "hexgnn_allreduce_p2p")
     _count("allreduce_p2p")
     return out
+
+
+@torch.no_grad()
+def adam_step(desc, flat_params, flat_grad, exp_avg, exp_avg_sq, state, x, lr, betas=(0.9, 0.999), eps=1e-8,
+              max_grad_norm=0.0, skip_untaken=False, grad_norm_out=None, ws=None):
+    """hexgnn_adam_step over the flat buffers (rainbow.py:320-326): clip_grad_norm_ + Adam.step in two launches.
+    `state` is a zero-initialised int32 [4] device tensor; returns the pre-clip gradient norm as a device scalar."""
+    for t, name in ((flat_params, "parameters"), (flat_grad, "gradient"), (exp_avg, "exp_avg"), (exp_avg_sq, "exp_avg_sq")):
+        _require_cuda(t, name)
+        if t.dtype != torch.float32 or not t.is_contiguous() or t.numel() != flat_params.numel():
+            raise _lib.HexGnnError(f"adam_step: {name} must be a contiguous float32 buffer of the flat parameter size")
+    if state.dtype != torch.int32 or state.numel() < 4 or not state.is_cuda:
+        raise _lib.HexGnnError("adam_step: state must be an int32 [4] CUDA tensor")
+    dev = flat_params.device
+    need = int(_lib.lib().hexgnn_adam_ws_bytes()) // 4
+    if ws is None or ws.numel() < need:
+        ws = torch.empty(need, dtype=torch.float32, device=dev)
+    if grad_norm_out is None:
+        grad_norm_out = torch.empty(1, dtype=torch.float32, device=dev)
+    rc = _lib.lib().hexgnn_adam_step(C.byref(desc), _ptr(flat_params), _ptr(flat_grad), _ptr(exp_avg), _ptr(exp_avg_sq),
+                                     _ptr(state), _ptr(x), float(lr), float(betas[0]), float(betas[1]), float(eps),
+                                     float(max_grad_norm), 1 if skip_untaken else 0, _ptr(grad_norm_out), _ptr(ws),
+                                     ws.numel() * 4, _stream(dev))
+    _lib.check(rc, "hexgnn_adam_step")
+    _count("adam_step")
+    return grad_norm_out.reshape(())

@@ -164,6 +164,21 @@ int hexgnn_train_step(const HexModelDesc* desc, const float* params, const float
                       const float* target, const float* weight, int32_t kind, float scale, float* q, float* loss,
                       float* td_err, float* stash, float* grad_params, void* ws, size_t ws_bytes, void* stream);
 
+/* Optimizer step over the flat buffers, two launches (replaces nn.utils.clip_grad_norm_ + torch.optim.Adam.step over
+ * ~70 tensors, rainbow.py:79,320,325): total L2 norm of `grads` -> grad_norm[0] (may be NULL); when max_grad_norm > 0
+ * the gradient is scaled IN PLACE by min(1, max_grad_norm / (norm + 1e-6)); then Adam (no weight decay, no amsgrad)
+ * updates params / exp_avg / exp_avg_sq in place.  `state` = 4 int32 (zero them once): step counters of the body, the
+ * maker head and the breaker head, and the head taken last.  torch keeps a step counter per parameter and skips
+ * parameters without gradient; here a head's counter starts with the first step that takes it (x[0,2], models.py:556)
+ * and then advances every step -- torch 1.13 `opt.zero_grad()` (rainbow.py:326) leaves zero gradients, so Adam keeps
+ * applying that head's momentum -- unless HEXGNN_ADAM_SKIP_UNTAKEN is set (torch >= 2 set_to_none semantics).
+ * ws = hexgnn_adam_ws_bytes().  Deterministic. */
+#define HEXGNN_ADAM_SKIP_UNTAKEN 1
+int64_t hexgnn_adam_ws_bytes(void);
+int hexgnn_adam_step(const HexModelDesc* desc, float* params, float* grads, float* exp_avg, float* exp_avg_sq,
+                     int32_t* state, const float* x, float lr, float beta1, float beta2, float eps, float max_grad_norm,
+                     int32_t flags, float* grad_norm, void* ws, size_t ws_bytes, void* stream);
+
 /* Learner loss glue on device (replaces the index / loss / mean kernels of rainbow.py:301-312 and their autograd):
  *   td_est[g] = q[ptr[g] + action[g]];  td_err[g] = td_est[g] - target[g]  (PER priorities = |td_err| + 1e-6, :307-308)
  *   loss[0]   = scale * mean_g( weight[g] * l(target[g], td_est[g]) ),  kind 0: l = MSE, 1: l = SmoothL1 (beta 1), :85

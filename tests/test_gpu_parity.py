@@ -337,3 +337,50 @@ def test_train_step_equals_autograd_route(size, count, kind, weighted):
     loss, err, q = m.train_step(b.x, b.edge_index, b.batch, b.ptr, action=action, target=target, weight=weight,
                                 kind=kind, scale=0.5)
     assert torch.allclose(m.flat_gradient, 2 * g_ref, rtol=1e-6, atol=0)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("skip_untaken", [False, True])
+def test_fused_adam_matches_torch_adam_with_clipping(skip_untaken):
+    """hexgnn_adam_step against nn.utils.clip_grad_norm_ + torch.optim.Adam on the same gradients (rainbow.py:79,320-326),
+    over steps that alternate the trained head: the untrained head keeps receiving zero-gradient Adam updates once it
+    has been trained (torch 1.13 zero_grad, the reference environment) or is left alone (set_to_none semantics)."""
+    from gnn_hex_b200 import FusedAdam
+    cfg = CONFIGS["S"]
+    _, m = make_pair(cfg["hidden"], cfg["layers"])
+    m = m.to(DEV)
+    # torch twin: the same parameter values as separate leaf tensors
+    ref_params = [p.detach().clone().requires_grad_(True) for p in m._ordered_params()]
+    ref_opt = torch.optim.Adam(ref_params, lr=3e-3, eps=1.5e-4)
+    opt = FusedAdam(m, lr=3e-3, eps=1.5e-4, max_grad_norm=0.05, skip_untaken=skip_untaken)
+    for step, maker in enumerate([1, 1, 0, 1, 0, 0]):
+        hb = data.collate(data.load_positions(cfg["fixture"], maker=maker)[step * 8:step * 8 + 24])
+        b = hb.to(DEV)
+        action, target, weight = [t.to(DEV) for t in loss_inputs(hb)]
+        m.zero_grad(set_to_none=True)
+        m.train_step(b.x, b.edge_index, b.batch, b.ptr, action=action, target=target, weight=weight)
+        g = m.flat_gradient.clone()
+        n_body, n_head = 3 * cfg["layers"], 3 * 2 + 6          # tensors of the body / of one head
+        for j, (rp, (o, n, shp)) in enumerate(zip(ref_params, m._slices)):
+            gi = g[o:o + n].view(shp).clone()
+            taken = j < n_body or ((j - n_body) // n_head == (0 if maker else 1))
+            if taken:
+                rp.grad = gi
+            elif skip_untaken or rp.grad is None:
+                rp.grad = None                                 # never trained yet, or torch >= 2 set_to_none
+            else:
+                rp.grad = torch.zeros_like(rp)                 # torch 1.13 opt.zero_grad(): the tensor stays, zeroed
+        live = [rp for rp in ref_params if rp.grad is not None]
+        norm_ref = torch.nn.utils.clip_grad_norm_(live, 0.05)
+        ref_opt.step()
+        norm = opt.step(b.x)
+        assert abs(float(norm) - float(norm_ref)) <= 2e-6 * float(norm_ref)
+        flat_ref = torch.cat([rp.detach().reshape(-1) for rp in ref_params])
+        err = (m.flat_parameters - flat_ref).abs().max().item()
+        assert err <= 2e-6, (step, err)
+    # target sync: one D2D copy
+    _, tgt = make_pair(cfg["hidden"], cfg["layers"], seed=5)
+    tgt = tgt.to(DEV)
+    tgt.copy_parameters_from(m)
+    assert torch.equal(tgt.flat_parameters, m.flat_parameters)
+    assert torch.equal(tgt.gnn.convs[3].lin_l.weight, m.gnn.convs[3].lin_l.weight)
