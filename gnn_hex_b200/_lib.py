@@ -42,7 +42,7 @@ class HexCsrLayout(C.Structure):
 
 EXPORTS = ["hexgnn_abi_version", "hexgnn_last_error", "hexgnn_param_count", "hexgnn_param_offsets",
            "hexgnn_sizes", "hexgnn_csr_layout", "hexgnn_build_csr", "hexgnn_forward", "hexgnn_backward",
-           "hexgnn_profile_enable", "hexgnn_profile_read", "hexgnn_selftest_mma", "hexgnn_debug_phases", "hexgnn_stash_embed", "hexgnn_td_loss", "hexgnn_train_step", "hexgnn_adam_step", "hexgnn_adam_ws_bytes",
+           "hexgnn_profile_enable", "hexgnn_profile_read", "hexgnn_selftest_mma", "hexgnn_debug_phases", "hexgnn_stash_embed", "hexgnn_td_loss", "hexgnn_train_step", "hexgnn_adam_step", "hexgnn_adam_ws_bytes", "hexgnn_collate", "hexgnn_collate_ws_bytes",
            "hexgnn_mask_argmax", "hexgnn_td_target", "hexgnn_forward_big", "hexgnn_allreduce_p2p"]
 
 _lib = None
@@ -88,6 +88,10 @@ def lib():
     l.hexgnn_train_step.restype = C.c_int
     l.hexgnn_train_step.argtypes = [p, p, p, i64, i64, i64, p, i32, i32, p, p, p, p, i32, C.c_float, p, p, p, p, p,
                                     p, C.c_size_t, p]
+    l.hexgnn_collate_ws_bytes.restype = i64
+    l.hexgnn_collate_ws_bytes.argtypes = [i64]
+    l.hexgnn_collate.restype = C.c_int
+    l.hexgnn_collate.argtypes = [p, p, p, p, i64, p, p, p, p, p, C.c_size_t, p, C.c_size_t, p]
     l.hexgnn_adam_ws_bytes.restype = i64
     l.hexgnn_adam_ws_bytes.argtypes = []
     l.hexgnn_adam_step.restype = C.c_int

@@ -260,6 +260,22 @@ int hexgnn_train_step(const HexModelDesc* desc, const float* params, const float
   return launch_td_loss(q, ptr, action, target, weight, N, B, kind, scale, loss, td_err, nullptr, st);
 }
 
+int64_t hexgnn_collate_ws_bytes(int64_t B) { return B < 0 ? 0 : collate_ws_bytes(B); }
+
+int hexgnn_collate(const float* const* x_ptrs, const int64_t* const* ei_ptrs, const int64_t* n_nodes, const int64_t* n_edges,
+                   int64_t B, float* x_out, int64_t* ei_out, int64_t* batch_out, int64_t* ptr_out, void* ws, size_t ws_bytes,
+                   void* host_ws, size_t host_ws_bytes, void* stream) {
+  if (!x_ptrs || !ei_ptrs || !n_nodes || !n_edges || B < 1 || !x_out || !batch_out || !ptr_out || !ws || !host_ws) { set_error("collate: bad argument"); return HEXGNN_E_BADARG; }
+  if ((int64_t)ws_bytes < collate_ws_bytes(B) || (int64_t)host_ws_bytes < collate_ws_bytes(B)) { set_error("collate: workspace too small"); return HEXGNN_E_WORKSPACE; }
+  int64_t E = 0;
+  for (int64_t g = 0; g < B; ++g) {
+    if (n_nodes[g] < 0 || n_edges[g] < 0 || (n_nodes[g] > 0 && !x_ptrs[g]) || (n_edges[g] > 0 && !ei_ptrs[g])) { set_error("collate: bad graph %lld", (long long)g); return HEXGNN_E_BADARG; }
+    E += n_edges[g];
+  }
+  if (E > 0 && !ei_out) { set_error("collate: ei_out is NULL"); return HEXGNN_E_BADARG; }
+  return launch_collate(x_ptrs, ei_ptrs, n_nodes, n_edges, B, x_out, ei_out, batch_out, ptr_out, ws, host_ws, (cudaStream_t)stream);
+}
+
 int64_t hexgnn_adam_ws_bytes(void) { return (int64_t)adam_ws_floats() * 4; }
 
 int hexgnn_adam_step(const HexModelDesc* desc, float* params, float* grads, float* exp_avg, float* exp_avg_sq,

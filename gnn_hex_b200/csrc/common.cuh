@@ -222,6 +222,10 @@ int launch_adam_step(const Dims& d, const ParamMap& pm, float* params, float* gr
                      int* state, const float* x, float lr, float beta1, float beta2, float eps, float max_norm,
                      int skip_untaken, float* grad_norm, float* ws, cudaStream_t st);
 int adam_ws_floats();
+int64_t collate_ws_bytes(int64_t B);
+int launch_collate(const float* const* x_ptrs, const int64_t* const* ei_ptrs, const int64_t* n_nodes, const int64_t* n_edges,
+                   int64_t B, float* x_out, int64_t* ei_out, int64_t* batch_out, int64_t* ptr_out, void* ws, void* host_ws,
+                   cudaStream_t st);
 int launch_forward_big(const Dims& d, const ParamMap& pm, const float* params, const float* x, int64_t N, int64_t E,
                        int64_t B, const void* csr, int tile_rows, int flags, int max_rows, float* out_nodes,
                        float* out_value, float* ws, cudaStream_t st);

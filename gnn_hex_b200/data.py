@@ -87,3 +87,60 @@ def collate(graphs: Sequence[HexGraph]) -> HexBatch:
     edge_index = torch.cat([g.edge_index + int(o) for g, o in zip(graphs, ptr[:-1])], 1)
     batch = torch.repeat_interleave(torch.arange(len(graphs), dtype=torch.long), torch.tensor(ns, dtype=torch.long))
     return HexBatch(x=x, edge_index=edge_index, batch=batch, ptr=ptr, num_graphs=len(graphs))
+
+
+class DeviceCollator:
+    """`Batch.from_data_list` over graphs that already live on the GPU (the learner's replay-buffer samples,
+    replay_buffer.py:116-117,215-216) as ONE kernel launch (hexgnn_collate) instead of 2 B small cat / add kernels
+    issued from a Python loop.  Keeps one pinned table + one device table per slot and alternates between `slots` of them,
+    so a table is not rewritten while an earlier call may still be reading it."""
+
+    def __init__(self, device, max_graphs=4096, slots=4):
+        import ctypes as C
+        from . import _lib
+        self._C, self._lib = C, _lib
+        self.device = torch.device(device)
+        self.max_graphs = int(max_graphs)
+        nbytes = int(_lib.lib().hexgnn_collate_ws_bytes(self.max_graphs))
+        self._host = [torch.empty(nbytes, dtype=torch.uint8).pin_memory() for _ in range(slots)]
+        self._dev = [torch.empty(nbytes, dtype=torch.uint8, device=self.device) for _ in range(slots)]
+        self._events = [None] * slots
+        self._k = 0
+
+    def __call__(self, graphs: Sequence[HexGraph]) -> HexBatch:
+        C, _lib = self._C, self._lib
+        B = len(graphs)
+        if B < 1 or B > self.max_graphs:
+            raise _lib.HexGnnError(f"collate: 1..{self.max_graphs} graphs expected, got {B}")
+        xs, eis = [], []
+        for g in graphs:
+            x, ei = g.x, g.edge_index
+            if not (x.is_cuda and ei.is_cuda) or x.dtype != torch.float32 or ei.dtype != torch.int64:
+                raise _lib.HexGnnError("collate: every graph needs CUDA x float32 [n,3] and edge_index int64 [2,e]")
+            xs.append(x.contiguous())
+            eis.append(ei.contiguous())
+        n_nodes = (C.c_int64 * B)(*[int(x.shape[0]) for x in xs])
+        n_edges = (C.c_int64 * B)(*[int(e.shape[1]) for e in eis])
+        x_ptrs = (C.c_void_p * B)(*[x.data_ptr() for x in xs])
+        ei_ptrs = (C.c_void_p * B)(*[e.data_ptr() for e in eis])
+        N, E = sum(n_nodes), sum(n_edges)
+        dev = self.device
+        x_out = torch.empty((N, 3), dtype=torch.float32, device=dev)
+        ei_out = torch.empty((2, E), dtype=torch.int64, device=dev)
+        batch = torch.empty(N, dtype=torch.int64, device=dev)
+        ptr = torch.empty(B + 1, dtype=torch.int64, device=dev)
+        k = self._k
+        self._k = (k + 1) % len(self._host)
+        if self._events[k] is not None:
+            self._events[k].synchronize()          # the table of this slot has been consumed
+        stream = torch.cuda.current_stream(dev)
+        rc = _lib.lib().hexgnn_collate(x_ptrs, ei_ptrs, n_nodes, n_edges, B, C.c_void_p(x_out.data_ptr()),
+                                       C.c_void_p(ei_out.data_ptr()), C.c_void_p(batch.data_ptr()),
+                                       C.c_void_p(ptr.data_ptr()), C.c_void_p(self._dev[k].data_ptr()),
+                                       self._dev[k].numel(), C.c_void_p(self._host[k].data_ptr()), self._host[k].numel(),
+                                       C.c_void_p(stream.cuda_stream))
+        _lib.check(rc, "hexgnn_collate")
+        ev = torch.cuda.Event()
+        ev.record(stream)
+        self._events[k] = ev
+        return HexBatch(x=x_out, edge_index=ei_out, batch=batch, ptr=ptr, num_graphs=B)

@@ -164,6 +164,18 @@ int hexgnn_train_step(const HexModelDesc* desc, const float* params, const float
                       const float* target, const float* weight, int32_t kind, float scale, float* q, float* loss,
                       float* td_err, float* stash, float* grad_params, void* ws, size_t ws_bytes, void* stream);
 
+/* Collate B device-resident graphs into one batch in ONE launch (replaces Batch.from_data_list over GPU-resident
+ * replay-buffer entries, replay_buffer.py:116-117,215-216, and C++ collate_batch, cpp_hex/hex_graph_game/util.cpp:22-41):
+ *   x_out [N,3] = cat(x_g);  ei_out [2,E] = cat(edge_index_g + node_offset_g, dim 1);  batch_out [N] = graph id per node;
+ *   ptr_out [B+1] = node prefix sums.   N = sum n_nodes, E = sum n_edges (the caller sizes the outputs).
+ * x_ptrs / ei_ptrs / n_nodes / n_edges are HOST arrays of length B; x_ptrs[g] -> device [n_g,3] f32, ei_ptrs[g] -> device
+ * [2,e_g] i64 row-major.  ws: device, host_ws: host (pinned preferred; it must stay untouched until the stream has
+ * passed this call), both hexgnn_collate_ws_bytes(B).  Bit-exact. */
+int64_t hexgnn_collate_ws_bytes(int64_t B);
+int hexgnn_collate(const float* const* x_ptrs, const int64_t* const* ei_ptrs, const int64_t* n_nodes, const int64_t* n_edges,
+                   int64_t B, float* x_out, int64_t* ei_out, int64_t* batch_out, int64_t* ptr_out, void* ws, size_t ws_bytes,
+                   void* host_ws, size_t host_ws_bytes, void* stream);
+
 /* Optimizer step over the flat buffers, two launches (replaces nn.utils.clip_grad_norm_ + torch.optim.Adam.step over
  * ~70 tensors, rainbow.py:79,320,325): total L2 norm of `grads` -> grad_norm[0] (may be NULL); when max_grad_norm > 0
  * the gradient is scaled IN PLACE by min(1, max_grad_norm / (norm + 1e-6)); then Adam (no weight decay, no amsgrad)

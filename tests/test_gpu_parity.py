@@ -384,3 +384,22 @@ def test_fused_adam_matches_torch_adam_with_clipping(skip_untaken):
     tgt.copy_parameters_from(m)
     assert torch.equal(tgt.flat_parameters, m.flat_parameters)
     assert torch.equal(tgt.gnn.convs[3].lin_l.weight, m.gnn.convs[3].lin_l.weight)
+
+
+@pytest.mark.gpu
+def test_device_collate_bit_exact():
+    """hexgnn_collate (one launch over device-resident graphs) == host collate == Batch.from_data_list layout
+    (replay_buffer.py:215-216, util.cpp:22-41), including an edgeless single-node graph and repeated use of the slots."""
+    col = data.DeviceCollator(DEV, max_graphs=512, slots=2)
+    gs = data.load_positions("pos_mix_5_13_seed1234.npz", maker=1)[:200]
+    lone = data.HexGraph(x=torch.tensor([[0.0, 1.0, 1.0]]), edge_index=torch.zeros((2, 0), dtype=torch.long))
+    for lo, hi in [(0, 200), (3, 4), (50, 97), (100, 101), (7, 150)]:
+        part = gs[lo:hi] + ([lone] if hi - lo > 1 else [])
+        ref = data.collate(part)
+        out = col([g.to(DEV) for g in part])
+        assert out.num_graphs == ref.num_graphs
+        for name in ("x", "edge_index", "batch", "ptr"):
+            a, b = getattr(out, name).cpu(), getattr(ref, name)
+            assert a.dtype == b.dtype and a.shape == b.shape and torch.equal(a, b), name
+    with pytest.raises(_lib.HexGnnError):
+        col([gs[0]])          # host tensors are refused: no CPU path
