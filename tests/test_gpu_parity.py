@@ -403,3 +403,59 @@ def test_device_collate_bit_exact():
             assert a.dtype == b.dtype and a.shape == b.shape and torch.equal(a, b), name
     with pytest.raises(_lib.HexGnnError):
         col([gs[0]])          # host tensors are refused: no CPU path
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("double_dqn", [True, False])
+def test_rainbow_learner_step_matches_reference_formulas(double_dqn):
+    """RainbowLearner.train (CSR x2, 3 forwards, mask/argmax, TD target, train_step, clip + Adam: all on the device) against
+    the same step written with the oracle modules exactly as rainbow.py:259-277,301-326 writes it."""
+    from gnn_hex_b200 import RainbowLearner
+    cfg = CONFIGS["S"]
+    o_pol, m_pol = make_pair(cfg["hidden"], cfg["layers"], seed=0)
+    o_tgt, m_tgt = make_pair(cfg["hidden"], cfg["layers"], seed=5)
+    m_pol, m_tgt = m_pol.to(DEV), m_tgt.to(DEV)
+    gs = data.load_positions(cfg["fixture"], maker=1)
+    hs, hn = data.collate(gs[:64]), data.collate(gs[64:128])
+    g = torch.Generator().manual_seed(3)
+    action = torch.stack([torch.randint(2, int(n), (1,), generator=g)[0] for n in (hs.ptr[1:] - hs.ptr[:-1])])
+    reward = (torch.rand(64, generator=g) < 0.2).float() * torch.sign(torch.randn(64, generator=g))
+    done = (torch.rand(64, generator=g) < 0.3).float()
+    weights = torch.rand(64, generator=g) * 0.5 + 0.5
+    lr, eps, max_norm, gamma, n_step = 1e-3, 1.5e-4, 0.02, 0.97, 2
+    # ---- reference formulas on the oracle (CPU) ----
+    with torch.no_grad():
+        if double_dqn:
+            adv = o_pol(hn.x, hn.edge_index, hn.batch, hn.ptr, advantages_only=True).clone()
+            adv[hn.ptr[:-1]] = -5
+            adv[hn.ptr[:-1] + 1] = -5
+            best = torch.stack([hn.ptr[i] + adv[hn.ptr[i]:hn.ptr[i + 1]].reshape(-1).argmax() for i in range(64)])
+            next_q = o_tgt(hn.x, hn.edge_index, hn.batch, hn.ptr).squeeze()[best]
+        else:
+            qt = o_tgt(hn.x, hn.edge_index, hn.batch, hn.ptr).clone()
+            qt[hn.ptr[:-1]] = -5
+            qt[hn.ptr[:-1] + 1] = -5
+            next_q = torch.stack([qt[hn.ptr[i]:hn.ptr[i + 1]].max() for i in range(64)])
+        td_tgt = reward + gamma ** n_step * next_q * (1 - done)
+    opt = torch.optim.Adam(o_pol.parameters(), lr=lr, eps=eps)
+    opt.zero_grad()
+    p_res = o_pol(hs.x, hs.edge_index, hs.batch, hs.ptr)
+    td_est = p_res[action + hs.ptr[:-1]]
+    loss_ref = torch.mean(weights * (td_tgt - td_est) ** 2)
+    loss_ref.backward()
+    live = [p for p in o_pol.parameters() if p.grad is not None]
+    norm_ref = torch.nn.utils.clip_grad_norm_(live, max_norm)
+    opt.step()
+    # ---- the device step ----
+    lrn = RainbowLearner(m_pol, m_tgt, lr=lr, adam_eps=eps, max_grad_norm=max_norm, gamma=gamma, n_step=n_step,
+                         double_dqn=double_dqn, loss_fn="mse")
+    out = lrn.train(hs.to(DEV), hn.to(DEV), action.to(DEV), reward.to(DEV), done.to(DEV), weights.to(DEV))
+    assert rel_err(out["td_target"], td_tgt) <= REL_TOL
+    assert abs(float(out["loss"]) - float(loss_ref)) <= 1e-5 * max(abs(float(loss_ref)), 1e-3)
+    assert abs(float(out["grad_norm"]) - float(norm_ref)) <= 2e-5 * float(norm_ref)
+    assert torch.allclose(out["priorities"].cpu(), (td_est - td_tgt).detach().abs() + 1e-6, atol=2e-6)
+    ref_sd = dict(o_pol.named_parameters())
+    for name, p in m_pol.named_parameters():
+        assert torch.allclose(p.detach().cpu(), ref_sd[name].detach(), atol=1e-5, rtol=0), name
+    lrn.sync_Q_target()
+    assert torch.equal(m_tgt.flat_parameters, m_pol.flat_parameters)
