@@ -308,7 +308,7 @@ int hexgnn_forward_big(const HexModelDesc* desc, const float* params, const floa
   if (!params || !x || !csr || !out_nodes || !ws || N < 1 || B < 1 || E < 0 || max_rows < 1) { set_error("forward_big: bad argument"); return HEXGNN_E_BADARG; }
   if ((flags & HEXGNN_SEPARATE) && !out_value) { set_error("forward_big: SEPARATE needs out_value"); return HEXGNN_E_BADARG; }
   if (!tile_rows_ok(tile_rows) || max_rows > 65535 * 32 || B > 0x7fffffff) { set_error("forward_big: unsupported tile_rows / max_rows"); return HEXGNN_E_UNSUPPORTED; }
-  const int64_t need = 2 * N * d.Hp * 4;
+  const int64_t need = (2 * N * d.Hp + pack_floats(d)) * 4;
   if ((int64_t)ws_bytes < need) { set_error("forward_big: workspace too small (%zu < %lld)", ws_bytes, (long long)need); return HEXGNN_E_WORKSPACE; }
   ParamMap pm;
   make_param_map(d, &pm);

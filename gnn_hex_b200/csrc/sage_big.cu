@@ -21,6 +21,8 @@ struct BigArgs {
   float* hout;
   float* out_nodes;
   float* out_value;
+  const float* wcat;   // pack.cu: [Lt-1][Hp][2Hp], wcat[k][c] = lin_l.W[c][k], wcat[k][Hp + c] = lin_r.W[c][k]
+  const float* bias;   // [Lt][Hp]
 };
 
 __device__ __forceinline__ bool big_graph(const BigArgs& a, int g, int* r0, int* n) {
@@ -34,7 +36,7 @@ __global__ void big_begin_kernel(CsrView v) { atomicAnd(v.status, ~HEXGNN_ST_GRA
 
 // One SAGE layer for rows [32*blockIdx.y, +32) of graph blockIdx.x: out = relu(W_l mean_j(h_j) + b + W_r h_i).
 __global__ void __launch_bounds__(kBigThreads) big_layer_kernel(const __grid_constant__ BigArgs a) {
-  extern __shared__ float A[];   // [kBigRows][2*Cin]: mean | self
+  extern __shared__ __align__(16) float A[];   // [kBigRows][2*Cp]: mean | self, Cp = Cin rounded up to 4 (zero padded)
   int r0, n;
   if (!big_graph(a, blockIdx.x, &r0, &n)) return;
   if (n > a.max_rows) {
@@ -46,36 +48,77 @@ __global__ void __launch_bounds__(kBigThreads) big_layer_kernel(const __grid_con
   const int rows = (n - i0) < kBigRows ? (n - i0) : kBigRows;
   const int H = a.d.H, Hp = a.d.Hp, s = a.s;
   const int Cin = s == 0 ? 2 : H;
+  const int Cp = (Cin + 3) & ~3;
   const int head = (a.x[2] == 1.0f) ? 0 : 1;
-  for (int idx = threadIdx.x; idx < rows * Cin; idx += kBigThreads) {
-    const int i = idx / Cin, k = idx - i * Cin;
-    const int row = r0 + i0 + i;
-    const int b = a.csr.rowptr[row], e = a.csr.rowptr[row + 1];
-    float sum = 0.f;
-    for (int p = b; p < e; ++p) {
-      const int j = a.csr.col[p];
-      sum += s == 0 ? a.x[(int64_t)j * 3 + k] : a.hin[(int64_t)j * Hp + k];
+  for (int idx = threadIdx.x; idx < kBigRows * Cp; idx += kBigThreads) {
+    const int i = idx / Cp, k = idx - i * Cp;
+    float mean = 0.f, self = 0.f;
+    if (i < rows && k < Cin) {
+      const int row = r0 + i0 + i;
+      const int b = a.csr.rowptr[row], e = a.csr.rowptr[row + 1];
+      float sum = 0.f;
+      for (int p = b; p < e; ++p) {
+        const int j = a.csr.col[p];
+        sum += s == 0 ? a.x[(int64_t)j * 3 + k] : a.hin[(int64_t)j * Hp + k];
+      }
+      mean = sum / (float)(e - b > 0 ? e - b : 1);
+      self = s == 0 ? a.x[(int64_t)row * 3 + k] : a.hin[(int64_t)row * Hp + k];
     }
-    A[i * 2 * Cin + k] = sum / (float)(e - b > 0 ? e - b : 1);
-    A[i * 2 * Cin + Cin + k] = s == 0 ? a.x[(int64_t)row * 3 + k] : a.hin[(int64_t)row * Hp + k];
+    A[i * 2 * Cp + k] = mean;
+    A[i * 2 * Cp + Cp + k] = self;
   }
   __syncthreads();
-  const float* wl = a.params + sage_wl(a.pm, head, s);
-  const float* bl = a.params + sage_bl(a.pm, head, s, H);
-  const float* wr = a.params + sage_wr(a.pm, head, s, H);
-  for (int idx = threadIdx.x; idx < rows * Hp; idx += kBigThreads) {
-    const int i = idx / Hp, c = idx - i * Hp;
-    float acc = 0.f;
-    if (c < H) {
-      const float* ar = A + i * 2 * Cin;
-      const float* wlr = wl + (int64_t)c * Cin;
-      const float* wrr = wr + (int64_t)c * Cin;
-      acc = bl[c];
-      for (int k = 0; k < Cin; ++k) acc = fmaf(wlr[k], ar[k], acc);
-      for (int k = 0; k < Cin; ++k) acc = fmaf(wrr[k], ar[Cin + k], acc);
-      acc = fmaxf(acc, 0.f);
+  if (s == 0) {
+    // 2 input channels: read the parameters directly
+    const float* wl = a.params + sage_wl(a.pm, head, s);
+    const float* bl = a.params + sage_bl(a.pm, head, s, H);
+    const float* wr = a.params + sage_wr(a.pm, head, s, H);
+    for (int idx = threadIdx.x; idx < rows * Hp; idx += kBigThreads) {
+      const int i = idx / Hp, c = idx - i * Hp;
+      float acc = 0.f;
+      if (c < H) {
+        const float* ar = A + i * 2 * Cp;
+        acc = bl[c];
+        for (int k = 0; k < Cin; ++k) acc = fmaf(wl[c * Cin + k], ar[k], acc);
+        for (int k = 0; k < Cin; ++k) acc = fmaf(wr[c * Cin + k], ar[Cp + k], acc);
+        acc = fmaxf(acc, 0.f);
+      }
+      a.hout[(int64_t)(r0 + i0 + i) * Hp + c] = acc;
     }
-    a.hout[(int64_t)(r0 + i0 + i) * Hp + c] = acc;
+    return;
+  }
+  // H -> H layers: thread = (output channel c, half of the rows); the k-major packed weights wcat[k][c | Hp + c]
+  // (pack.cu) make the weight loads coalesced, the activations come as float4 broadcasts from shared memory.
+  // Summation order per output: bias, then k ascending with the lin_l and lin_r terms interleaved.
+  constexpr int R = kBigRows / 2;
+  const int c = threadIdx.x & 127, rg = threadIdx.x >> 7;
+  if (c >= Hp) return;
+  const float* wcat = a.wcat + (int64_t)(s - 1) * Hp * 2 * Hp;
+  float acc[R];
+  const float b0 = a.bias[s * Hp + c];
+#pragma unroll
+  for (int r = 0; r < R; ++r) acc[r] = b0;
+  const float* Ar = A + (rg * R) * 2 * Cp;
+  for (int k = 0; k < Cp; k += 4) {
+    float wl[4], wr[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) { wl[u] = wcat[(int64_t)(k + u) * 2 * Hp + c]; wr[u] = wcat[(int64_t)(k + u) * 2 * Hp + Hp + c]; }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const float4 m = *(const float4*)(Ar + r * 2 * Cp + k);
+      const float4 h = *(const float4*)(Ar + r * 2 * Cp + Cp + k);
+      float v = acc[r];
+      v = fmaf(wl[0], m.x, v); v = fmaf(wr[0], h.x, v);
+      v = fmaf(wl[1], m.y, v); v = fmaf(wr[1], h.y, v);
+      v = fmaf(wl[2], m.z, v); v = fmaf(wr[2], h.z, v);
+      v = fmaf(wl[3], m.w, v); v = fmaf(wr[3], h.w, v);
+      acc[r] = v;
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const int i = rg * R + r;
+    if (i < rows) a.hout[(int64_t)(r0 + i0 + i) * Hp + c] = c < H ? fmaxf(acc[r], 0.f) : 0.f;
   }
 }
 
@@ -156,13 +199,17 @@ int launch_forward_big(const Dims& d, const ParamMap& pm, const float* params, c
   a.B = (int)B; a.max_rows = max_rows; a.tile_rows = tile_rows; a.flags = flags;
   a.out_nodes = out_nodes; a.out_value = out_value;
   float* buf[2] = {ws, ws + N * d.Hp};
+  PackView pv = pack_view(ws + 2 * N * d.Hp, d);
+  int rc = launch_pack(d, pm, params, x, pv, false, st);
+  if (rc) return rc;
+  a.wcat = pv.wcat; a.bias = pv.bias;
   big_begin_kernel<<<1, 1, 0, st>>>(a.csr);
   const dim3 grid((unsigned)B, (unsigned)((max_rows + kBigRows - 1) / kBigRows));
   for (int s = 0; s < d.Lt; ++s) {
     a.s = s;
     a.hin = s == 0 ? nullptr : buf[(s - 1) & 1];
     a.hout = buf[s & 1];
-    const size_t smem = (size_t)kBigRows * 2 * (s == 0 ? 2 : d.H) * sizeof(float);
+    const size_t smem = (size_t)kBigRows * 2 * (s == 0 ? 4 : ((d.H + 3) & ~3)) * sizeof(float);
     big_layer_kernel<<<grid, kBigThreads, smem, st>>>(a);
   }
   a.hin = buf[(d.Lt - 1) & 1];

@@ -294,7 +294,8 @@ def forward_big(desc, flat_params, x, csr, flags, max_rows, out_nodes, out_value
     N, E, B = csr.N, csr.E, csr.B
     dev = x.device
     hp = (int(desc.hidden) + 15) // 16 * 16
-    need = 2 * N * hp
+    lt = int(desc.num_layers) + int(desc.num_head_layers)
+    need = 2 * N * hp + (lt - 1) * hp * 2 * hp * 2 + lt * hp      # activations ping-pong + packed weights (pack.cu)
     if ws is None or ws.numel() < need:
         ws = torch.empty(need, dtype=torch.float32, device=dev)
     rc = _lib.lib().hexgnn_forward_big(C.byref(desc), _ptr(flat_params), _ptr(x.contiguous()), N, E, B, _ptr(csr.blob),
@@ -302,7 +303,7 @@ def forward_big(desc, flat_params, x, csr, flags, max_rows, out_nodes, out_value
                                        ws.numel() * 4, _stream(dev))
     _lib.check(rc, "hexgnn_forward_big")
     global launch_counter
-    launch_counter += 2 + int(desc.num_layers) + int(desc.num_head_layers)
+    launch_counter += 3 + int(desc.num_layers) + int(desc.num_head_layers)
     return ws
 
 

@@ -145,7 +145,8 @@ int hexgnn_backward(const HexModelDesc* desc, const float* params, const float* 
  * hexgnn_forward, same stream, same arguments: every graph the fused kernel refused (more than tile_rows nodes or
  * tile_rows*8 edges; its outputs were poisoned with NaN) is evaluated by a CUDA-core path, one launch per SAGE layer,
  * and its rows of out_nodes / out_value are overwritten; HEXGNN_ST_GRAPH_TOO_LARGE is cleared unless a graph exceeds
- * max_rows.  Inference only (no stash).  ws: 2 * N * hidden_padded floats. */
+ * max_rows.  Inference only (no stash).  ws: 2 * N * hidden_padded floats (activations) + fwd_ws_bytes of
+ * hexgnn_sizes (k-major packed weights, rebuilt per call). */
 int hexgnn_forward_big(const HexModelDesc* desc, const float* params, const float* x, int64_t N, int64_t E, int64_t B,
                        const void* csr, int32_t tile_rows, int32_t flags, int32_t max_rows, float* out_nodes,
                        float* out_value, void* ws, size_t ws_bytes, void* stream);

@@ -2,6 +2,8 @@
   gnn_s     configs[0]  GNN-S (hidden 35, 10+2 layers) fwd+bwd, 256 7x7 positions
   selfplay  configs[2]  GNN-L forward only, 128 11x11 positions, advantages_only + terminal mask + per-graph argmax
   ragged    configs[3]  GNN-L forward, 256 graphs of mixed 5x5..13x13 boards (ragged CSR)
+  learner   SURVEY 8 f1+f2: the whole Rainbow learner step on GNN-L, 256 + 256 positions (RainbowLearner.train:
+            2 CSR builds, 3 forwards, mask/argmax, TD target, train_step, clip + Adam)
 CUDA events, inputs resident, 256 MiB L2 flush between iterations.   python tools/bench_configs.py [iters]"""
 import json, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -41,8 +43,7 @@ b = data.collate(data.load_positions("pos_7x7_seed1234.npz", maker=1)[:256]); d 
 a, t, w = loss_inputs(b)
 def step_s():
     m.zero_grad(set_to_none=True)
-    q = m(d.x, d.edge_index, d.batch, d.ptr)
-    ops.td_loss(q, d.ptr, a, t, w)[0].backward()
+    m.train_step(d.x, d.edge_index, d.batch, d.ptr, action=a, target=t, weight=w)
 ms = timed(step_s)
 out.append({"config": "gnn_s fwd+bwd, 256 7x7 positions", "nodes": int(b.x.shape[0]), "ms": ms, "graphs_per_s": 256 / ms * 1e3})
 # configs[2]
@@ -65,5 +66,20 @@ ms = timed(fwd)
 status = int(m.last_csr.status.item()) if getattr(m, "last_csr", None) is not None else 0
 out.append({"config": "ragged: GNN-L forward, 256 graphs of 5x5..13x13 boards (oversize graphs via hexgnn_forward_big)", "nodes": int(b.x.shape[0]), "graphs": b.num_graphs,
             "ms": ms, "graphs_per_s": b.num_graphs / ms * 1e3, "device_status": status})
+# learner step (f1 + f2)
+from gnn_hex_b200 import RainbowLearner
+pol, tgt = ModernTwoHeaded(110, 15, 2).to(dev), ModernTwoHeaded(110, 15, 2).to(dev)
+lrn = RainbowLearner(pol, tgt, lr=1e-4, adam_eps=1.5e-4, max_grad_norm=10.0, gamma=0.97, n_step=2)
+gs = data.load_positions("pos_11x11_seed1234.npz", maker=1)
+hs, hn = data.collate(gs[:256]), data.collate(gs[128:256] + gs[:128])
+ds, dn = hs.to(dev), hn.to(dev)
+a, _, w = loss_inputs(hs)
+g = torch.Generator().manual_seed(2)
+reward = (torch.rand(256, generator=g) < 0.1).float().to(dev)
+done = (torch.rand(256, generator=g) < 0.1).float().to(dev)
+ms = timed(lambda: lrn.train(ds, dn, a, reward, done, w))
+out.append({"config": "learner: RainbowLearner.train, GNN-L, 256 state + 256 next_state 11x11 positions (double DQN, PER weights, "
+                      "clip + Adam)", "nodes": int(hs.x.shape[0] + hn.x.shape[0]), "ms": ms, "steps_per_s": 1e3 / ms,
+            "graphs_per_s": 256 / ms * 1e3})
 for o in out:
     print(json.dumps(o))
