@@ -196,7 +196,7 @@ int hexgnn_backward(const HexModelDesc* desc, const float* params, const float* 
       rc = launch_backward_tc_dw(d, N, E, B, csr, stash, wsf + w.dz, wsf + w.big_rec, sync, st);
       if (rc) return rc;
     }
-    rc = launch_reduce_tc(d, wsf + w.small_rec, grid, wsf + w.big_rec, tc_dw_groups(d), wsf + w.head_rec, B, wsf + w.sum, st);
+    rc = launch_reduce_tc(d, wsf + w.small_rec, csr_view(const_cast<void*>(csr), N, E, B).ntiles, wsf + w.big_rec, tc_dw_groups(d), wsf + w.head_rec, B, wsf + w.sum, st);
     if (rc) return rc;
     return launch_unpack_grads(d, pm, x, wsf + w.sum, grad_params, st);
   }
@@ -253,7 +253,7 @@ int hexgnn_train_step(const HexModelDesc* desc, const float* params, const float
     --g_prof_mute;
     if (rc) return rc;
   }
-  rc = launch_reduce_tc(d, wsf + w.small_rec, grid, wsf + w.big_rec, tc_dw_groups(d), wsf + w.head_rec, B, wsf + w.sum, st);
+  rc = launch_reduce_tc(d, wsf + w.small_rec, csr_view(const_cast<void*>(csr), N, E, B).ntiles, wsf + w.big_rec, tc_dw_groups(d), wsf + w.head_rec, B, wsf + w.sum, st);
   if (rc) return rc;
   rc = launch_unpack_grads(d, pm, x, wsf + w.sum, grad_params, st);
   if (rc) return rc;

@@ -97,6 +97,7 @@ inline void csr_layout(int64_t N, int64_t E, int64_t B, HexCsrLayout* o) {
   o->scratch = w; w += (N + 1) + E; w = align_up(w, 4);  // cursor[N+1], edge ids [E]
   w += 4 + 2 * csr_scan_blocks(N);                       // scan ticket + one 64-bit look-back state per scan block
   w = align_up(w, 4);
+  w += B + 1; w = align_up(w, 4);                        // tile_order[B]: processing order of the tiles (heaviest first)
   o->total_words = w;
 }
 
@@ -112,6 +113,7 @@ struct CsrView {
   int* eid;
   int* scan_ticket;                 // [4] (only [0] used)
   unsigned long long* scan_state;   // [csr_scan_blocks(N)]: flag << 32 | value
+  int* tile_order;                  // [ntiles]: position -> tile, by descending cost (8 * rows + edges), ties by index
 };
 
 inline CsrView csr_view(void* blob, int64_t N, int64_t E, int64_t B) {
@@ -129,6 +131,7 @@ inline CsrView csr_view(void* blob, int64_t N, int64_t E, int64_t B) {
   v.eid = w + l.scratch + (N + 1);
   v.scan_ticket = w + align_up(l.scratch + (N + 1) + E, 4);
   v.scan_state = (unsigned long long*)(v.scan_ticket + 4);
+  v.tile_order = v.scan_ticket + align_up(4 + 2 * csr_scan_blocks(N), 4);
   return v;
 }
 

@@ -156,7 +156,28 @@ __global__ void csr_fill_kernel(CsrView v, const int64_t* __restrict__ ei, int E
     }
     if (status) atomicOr(v.status, status);
     __syncthreads();
-    if (threadIdx.x == 0) *v.ntiles = st_s[1];
+    const int T = st_s[1];
+    if (threadIdx.x == 0) *v.ntiles = T;
+    // Processing order of the tiles: heaviest first (cost ~ 8 * rows + edges), so that the LAST round of the persistent
+    // kernels -- the one that ends the forward -> chain -> dW pipeline -- gets the lightest tiles.  Deterministic rank
+    // sort (ties by tile index): the order decides which tiles a CTA accumulates, i.e. the gradient's summation order.
+    constexpr int kMaxSorted = 2048;
+    __shared__ int key_s[kMaxSorted];
+    if (T <= kMaxSorted) {
+      for (int t = threadIdx.x; t < T; t += blockDim.x) {
+        const int r0 = v.gptr[v.tile_g0[t]], r1 = v.gptr[v.tile_g0[t + 1]];
+        key_s[t] = 8 * (r1 - r0) + (v.rowptr[r1] - v.rowptr[r0]);
+      }
+      __syncthreads();
+      for (int t = threadIdx.x; t < T; t += blockDim.x) {
+        const int k = key_s[t];
+        int rank = 0;
+        for (int j = 0; j < T; ++j) { const int kj = key_s[j]; rank += (kj > k) || (kj == k && j < t); }
+        v.tile_order[rank] = t;
+      }
+    } else {
+      for (int t = threadIdx.x; t < T; t += blockDim.x) v.tile_order[t] = t;
+    }
     return;
   }
   const int nth = (gridDim.x - 1) * blockDim.x;

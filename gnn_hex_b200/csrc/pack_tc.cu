@@ -65,13 +65,46 @@ int launch_pack_tc(const Dims& d, const ParamMap& pm, const float* params, const
 // Fixed-order reduction of the tcgen05 backward's partial records into one packed record (GradLayout):
 //   gw and gb[s>=1]  <- the G group records of sage_dw_tc_kernel   (big_rec [G][gl.g0])
 //   gv0              <- sum over graphs (in graph order) of dt_g (x) pooled_g from the head records
-//   everything else  <- the per-CTA records of sage_bwd_tc_kernel  (small_rec [nsmall][gl.total - gl.gb])
+//   everything else  <- the per-TILE records of sage_bwd_tc_kernel  (small_rec [ntiles][gl.total - gl.gb])
 constexpr int kRedThreads = 1024;   // gv0 blocks: 128 q x 8 graph slices
 __global__ void __launch_bounds__(kRedThreads) reduce_tc_kernel(GradLayout gl, int Hp, int H, int H2,
-                                                                const float* __restrict__ small_rec, int nsmall,
+                                                                const float* __restrict__ small_rec, const int* __restrict__ ntiles,
                                                                 const float* __restrict__ big_rec, int G,
                                                                 const float* __restrict__ head_rec, int hrec_n, int B,
-                                                                int nmain, float* __restrict__ out) {
+                                                                int nmain, int ngv0, float* __restrict__ out) {
+  if ((int)blockIdx.x >= nmain + ngv0) {
+    // per-tile records of the chain kernel: block = 128 elements x 8 record slices (contiguous ranges of tiles, 4
+    // interleaved chains inside a slice, slices combined in slice order): a fixed summation order that does not depend
+    // on the kernels' tile schedule, and 8 x 4 short chains instead of one long latency-bound one per element
+    __shared__ float sp_part[8][128];
+    const int sb = blockIdx.x - nmain - ngv0;
+    const int ql = threadIdx.x & 127, sl = threadIdx.x >> 7;
+    const int64_t i = gl.gb + (int64_t)sb * 128 + ql;
+    const bool mine = i < gl.total && !(i >= gl.gv0 && i < gl.gv0b) && !(i >= gl.gb + Hp && i < gl.g0);
+    const int64_t recn = gl.total - gl.gb;
+    const int nsmall = *ntiles;
+    const int per = (nsmall + 7) / 8;
+    const int pa = sl * per, pb = (pa + per < nsmall) ? pa + per : nsmall;
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    if (mine) {
+      const float* sp = small_rec + (i - gl.gb);
+      int p = pa;
+      for (; p + 4 <= pb; p += 4) {
+        a0 += sp[(int64_t)p * recn]; a1 += sp[(int64_t)(p + 1) * recn];
+        a2 += sp[(int64_t)(p + 2) * recn]; a3 += sp[(int64_t)(p + 3) * recn];
+      }
+      for (; p < pb; ++p) a0 += sp[(int64_t)p * recn];
+    }
+    sp_part[sl][ql] = (a0 + a1) + (a2 + a3);
+    __syncthreads();
+    if (sl == 0 && mine) {
+      float u = sp_part[0][ql];
+#pragma unroll
+      for (int t = 1; t < 8; ++t) u += sp_part[t][ql];
+      out[i] = u;
+    }
+    return;
+  }
   if ((int)blockIdx.x >= nmain) {
     // gv0[k][q] = sum_g dt_g[k] * pooled_g[q]: block = 128 q x 8 k; the 8 thread slices take 8 contiguous ranges of
     // the graphs (sequential inside a range, ranges combined in slice order: deterministic).  Many short independent
@@ -113,37 +146,26 @@ __global__ void __launch_bounds__(kRedThreads) reduce_tc_kernel(GradLayout gl, i
     return;
   }
   const int64_t nth = (int64_t)nmain * blockDim.x;
-  const int64_t recn = gl.total - gl.gb;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < gl.total; i += nth) {
-    if (i >= gl.gv0 && i < gl.gv0b) continue;   // written by the gv0 blocks
-    float acc = 0.f;
     const bool from_big = i < gl.gb || (i >= gl.gb + Hp && i < gl.g0);
-    if (from_big) {
-      for (int g = 0; g < G; ++g) acc += big_rec[(int64_t)g * gl.g0 + i];
-    } else {
-      float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;   // 4 interleaved chains, fixed combination order
-      const float* sp = small_rec + (i - gl.gb);
-      int p = 0;
-      for (; p + 4 <= nsmall; p += 4) {
-        a0 += sp[(int64_t)p * recn]; a1 += sp[(int64_t)(p + 1) * recn];
-        a2 += sp[(int64_t)(p + 2) * recn]; a3 += sp[(int64_t)(p + 3) * recn];
-      }
-      for (; p < nsmall; ++p) a0 += sp[(int64_t)p * recn];
-      acc = (a0 + a1) + (a2 + a3);
-    }
+    if (!from_big) continue;                       // gv0 blocks / small-record blocks
+    float acc = 0.f;
+    for (int g = 0; g < G; ++g) acc += big_rec[(int64_t)g * gl.g0 + i];
     out[i] = acc;
   }
 }
 
-int launch_reduce_tc(const Dims& d, const float* small_rec, int nsmall, const float* big_rec, int G,
+int launch_reduce_tc(const Dims& d, const float* small_rec, const int* ntiles, const float* big_rec, int G,
                      const float* head_rec, int64_t B, float* packed_sum, cudaStream_t st) {
   GradLayout gl;
   grad_layout(d, &gl);
   int blocks = (int)((gl.total + kRedThreads - 1) / kRedThreads);
   if (blocks > 592) blocks = 592;
   const int gv0_blocks = ((4 * d.H + 127) / 128) * ((d.H2 + 7) / 8);
-  reduce_tc_kernel<<<blocks + gv0_blocks, kRedThreads, 0, st>>>(gl, d.Hp, d.H, d.H2, small_rec, nsmall, big_rec, G, head_rec,
-                                                        tc_head_rec_floats(d), (int)B, blocks, packed_sum);
+  const int small_blocks = (int)((gl.total - gl.gb + 127) / 128);
+  reduce_tc_kernel<<<blocks + gv0_blocks + small_blocks, kRedThreads, 0, st>>>(gl, d.Hp, d.H, d.H2, small_rec, ntiles, big_rec, G,
+                                                                       head_rec, tc_head_rec_floats(d), (int)B, blocks,
+                                                                       gv0_blocks, packed_sum);
   HEX_CUDA_CHECK(cudaGetLastError());
   return HEXGNN_OK;
 }

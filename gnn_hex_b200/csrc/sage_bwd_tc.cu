@@ -38,7 +38,8 @@ struct BwdTcArgs {
   float* dz;              // dZ stash written here: [Lt-1][B][dz_blocks * 16 KB]
   float* d_embeds;
   TcPackView pv;
-  float* small_rec;       // [gridDim.x][gl.total - gl.gb]  (the gv0 range stays unwritten)
+  float* small_rec;       // [tiles][gl.total - gl.gb]  (the gv0 range stays unwritten): one record per TILE, so the
+                          // gradient bits do not depend on which CTA processed which tile (schedule-independent)
   float* head_rec;        // [B][tc_head_rec_floats]: per graph [dt (H2, padded) | pooled (4H)]
   int* tile_flag;         // [B]: set (release) once every dZ image of the tile is in memory -- the dW kernel's cue
   TdFuse td;              // hexgnn_train_step: forward-tile flags + the TD loss whose dL/dQ replaces d_nodes
@@ -153,7 +154,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
     // ================= producer: backward weight images -> ring =================
     if (lane == 0) {
       uint32_t it = 0;
-      for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+      for (int rnd = 0; rnd * (int)gridDim.x < ntiles; ++rnd) {
+      const int ti = tile_position(rnd, blockIdx.x, gridDim.x, a.td.fwd_flag == nullptr);
+      if (ti >= ntiles) continue;
+      const int t = a.csr.tile_order[ti];
         if (!tile_dims_b(a.csr, t, S::ECAP).ok) continue;
         for (int s = Lt - 1; s >= 1; --s) {
           const uint8_t* src = (const uint8_t*)a.pv.wimgT + (size_t)(s - 1) * 2 * NQ * S::stage_bytes;
@@ -173,7 +177,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
       constexpr uint32_t idesc = make_idesc_tf32(kTcRows, Hp, false);
       constexpr uint32_t lbo = Hp * 16, sbo = 128;
       uint32_t it = 0, na = 0;
-      for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+      for (int rnd = 0; rnd * (int)gridDim.x < ntiles; ++rnd) {
+      const int ti = tile_position(rnd, blockIdx.x, gridDim.x, a.td.fwd_flag == nullptr);
+      if (ti >= ntiles) continue;
+      const int t = a.csr.tile_order[ti];
         if (!tile_dims_b(a.csr, t, S::ECAP).ok) continue;
         for (int s = Lt - 1; s >= 1; --s) {
           for (int which = 0; which < 2; ++which) {
@@ -215,10 +222,19 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
     const int head = (flag == 1.0f) ? 0 : 1;
     const float* Pm = a.params;
     const int64_t recn = a.gl.total - a.gl.gb;
-    float* rec = a.small_rec + (int64_t)blockIdx.x * recn - a.gl.gb;   // index with GradLayout offsets (>= gl.gb)
-    // CTA-lifetime accumulators of the small parameter gradients (every element has ONE owner thread)
     constexpr int A_GB0 = 0, A_G0 = Hp, A_GLIN = 5 * Hp, A_GLINB = 6 * Hp, A_GV0B = 6 * Hp + 4, A_GV1 = 7 * Hp + 4,
                   A_GV1B = 8 * Hp + 4, A_N = 8 * Hp + 16;
+    // per-tile accumulators of the small parameter gradients (every element has ONE owner thread), flushed to the
+    // tile's record and cleared at the end of the tile
+    auto flush_tile_record = [&](int t) {
+      float* rec = a.small_rec + (int64_t)t * recn - a.gl.gb;   // index with GradLayout offsets (>= gl.gb)
+      for (int i = tid; i < Hp; i += kTcEpiThreads) { rec[a.gl.gb + i] = accs[A_GB0 + i]; rec[a.gl.glin + i] = accs[A_GLIN + i]; }
+      for (int i = tid; i < 4 * Hp; i += kTcEpiThreads) rec[a.gl.g0 + i] = accs[A_G0 + i];
+      for (int i = tid; i < H2; i += kTcEpiThreads) { rec[a.gl.gv0b + i] = accs[A_GV0B + i]; rec[a.gl.gv1 + i] = accs[A_GV1 + i]; }
+      if (tid == 0) { rec[a.gl.glinb] = accs[A_GLINB]; rec[a.gl.gv1b] = accs[A_GV1B]; }
+      epi_bar_b();
+      for (int i = tid; i < A_N; i += kTcEpiThreads) accs[i] = 0.f;
+    };
     for (int i = tid; i < A_N; i += kTcEpiThreads) accs[i] = 0.f;
     for (int i = tid; i < P; i += kTcEpiThreads) dump[kTcRows * P + i] = 0.f;   // the gather's zero row
     const float* wa = Pm + a.pm.lin_w[head];
@@ -234,7 +250,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
     const int hrec_n = tc_head_rec_floats(a.d), H2p = (H2 + 3) & ~3;
     const int part = tid >> 7, pc = tid & 127;      // row quarter / channel of the column-parallel loops
     uint32_t nr = 0, nd = 0;
-    for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    for (int rnd = 0; rnd * (int)gridDim.x < ntiles; ++rnd) {
+      const int ti = tile_position(rnd, blockIdx.x, gridDim.x, a.td.fwd_flag == nullptr);
+      if (ti >= ntiles) continue;
+      const int t = a.csr.tile_order[ti];
       const TileDimsB td = tile_dims_b(a.csr, t, S::ECAP);
       const int n = td.n, r0 = td.r0, g0 = td.g0, g1 = td.g1;
       if (a.td.fwd_flag && tid == 0) flag_wait(a.td.fwd_flag + t);   // acquire; the barrier extends it to the CTA
@@ -244,6 +263,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
       if (!td.ok) {
         if (tid == 0) { accs[A_GB0] = __int_as_float(0x7fc00000); atomicOr(a.csr.status, HEXGNN_ST_GRAPH_TOO_LARGE); }
         for (int i = tid; i < (g1 - g0) * hrec_n; i += kTcEpiThreads) a.head_rec[(int64_t)g0 * hrec_n + i] = 0.f;
+        epi_bar_b();
+        flush_tile_record(t);               // poisoned record
         if (tid == 0) flag_release(a.tile_flag + t, 1);
         continue;
       }
@@ -633,13 +654,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
       fence_proxy_async_global();          // the consumer reads with bulk copies (async proxy)
       epi_bar_b();
       if (tid == 0) { __threadfence(); flag_release(a.tile_flag + t, 1); }
+      flush_tile_record(t);
     }
-    // ---- CTA accumulators -> this CTA's small record (GradLayout offsets) ------------------------------------------
-    epi_bar_b();
-    for (int i = tid; i < Hp; i += kTcEpiThreads) { rec[a.gl.gb + i] = accs[A_GB0 + i]; rec[a.gl.glin + i] = accs[A_GLIN + i]; }
-    for (int i = tid; i < 4 * Hp; i += kTcEpiThreads) rec[a.gl.g0 + i] = accs[A_G0 + i];
-    for (int i = tid; i < H2; i += kTcEpiThreads) { rec[a.gl.gv0b + i] = accs[A_GV0B + i]; rec[a.gl.gv1 + i] = accs[A_GV1 + i]; }
-    if (tid == 0) { rec[a.gl.glinb] = accs[A_GLINB]; rec[a.gl.gv1b] = accs[A_GV1B]; }
     // the dW kernel's last ticket waits for every chain CTA's record, so "dW complete" implies "chain complete"
     epi_bar_b();
     if (tid == 0) { __threadfence(); atomicAdd(a.tile_flag - kSyncTileOff + 1, 1); }

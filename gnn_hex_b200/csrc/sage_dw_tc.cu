@@ -57,7 +57,8 @@ __global__ void __launch_bounds__(kDwThreads, 1) sage_dw_tc_kernel(const __grid_
   const int phase = ticket_s >= nitems, item = ticket_s - phase * nitems;
   const int s = 1 + item / a.G, grp = item % a.G;
   const int ntiles = *a.csr.ntiles;
-  // phase A: tiles [0, TA) = all complete chain rounds but the last; phase B: the last round [TA, ntiles)
+  // positions in the chain's processing order (csr.tile_order): phase A = [0, TA) = all complete chain rounds but the
+  // last; phase B = the last round [TA, ntiles)
   const int TA = ntiles > 0 ? ((ntiles - 1) / a.chain_grid) * a.chain_grid : 0;
   const int t_begin = (phase ? TA : 0) + grp, t_end = phase ? ntiles : TA;
   const int* tile_flag = a.sync + kSyncTileOff;
@@ -87,7 +88,8 @@ __global__ void __launch_bounds__(kDwThreads, 1) sage_dw_tc_kernel(const __grid_
     // ================= producer =================
     if (lane == 0) {
       uint32_t it = 0;
-      for (int t = t_begin; t < t_end; t += a.G) {
+      for (int ti = t_begin; ti < t_end; ti += a.G) {
+        const int t = a.csr.tile_order[ti];
         const int n32 = tile_rows32(t);
         if (n32 > 0) { flag_wait(tile_flag + t); fence_proxy_async_global(); }
         const char* act = (const char*)a.stash + ((size_t)(s - 1) * a.B + t) * act_img;
@@ -108,7 +110,8 @@ __global__ void __launch_bounds__(kDwThreads, 1) sage_dw_tc_kernel(const __grid_
     if (lane == 0) {
       constexpr uint32_t idesc = make_idesc_tf32(128, N2, true, true);
       uint32_t it = 0;
-      for (int t = t_begin; t < t_end; t += a.G) {
+      for (int ti = t_begin; ti < t_end; ti += a.G) {
+        const int t = a.csr.tile_order[ti];
         const int n32 = tile_rows32(t);
         for (int c0 = 0; c0 < n32; c0 += kDwChunkRows, ++it) {
           const int st = it % kDwStages;
@@ -135,7 +138,8 @@ __global__ void __launch_bounds__(kDwThreads, 1) sage_dw_tc_kernel(const __grid_
   } else {
     // ================= split warps: fp32 -> (tf32 hi in place, tf32 lo copy) =================
     uint32_t it = 0;
-    for (int t = t_begin; t < t_end; t += a.G) {
+    for (int ti = t_begin; ti < t_end; ti += a.G) {
+        const int t = a.csr.tile_order[ti];
       const int n32 = tile_rows32(t);
       for (int c0 = 0; c0 < n32; c0 += kDwChunkRows, ++it) {
         const int st = it % kDwStages;

@@ -131,7 +131,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
     // ================= producer: weight images -> ring =================
     if (lane == 0) {
       uint32_t it = 0;
-      for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+      for (int rnd = 0; rnd * (int)gridDim.x < ntiles; ++rnd) {
+      const int ti = tile_position(rnd, blockIdx.x, gridDim.x, a.tile_flag == nullptr);
+      if (ti >= ntiles) continue;
+      const int t = a.csr.tile_order[ti];
         if (!tile_dims(a.csr, t, S::ECAP).ok) continue;
         for (int s = 1; s < Lt; ++s) {
           const uint8_t* src = (const uint8_t*)a.pv.wimg + (size_t)(s - 1) * NQ * S::stage_bytes;
@@ -151,7 +154,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
       constexpr uint32_t idesc = make_idesc_tf32(kTcRows, S::N2, false);
       constexpr uint32_t lbo = S::N2 * 16, sbo = 128;
       uint32_t it = 0, na = 0;
-      for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+      for (int rnd = 0; rnd * (int)gridDim.x < ntiles; ++rnd) {
+      const int ti = tile_position(rnd, blockIdx.x, gridDim.x, a.tile_flag == nullptr);
+      if (ti >= ntiles) continue;
+      const int t = a.csr.tile_order[ti];
         if (!tile_dims(a.csr, t, S::ECAP).ok) continue;
         for (int s = 1; s < Lt; ++s) {
           long long tq;
@@ -198,7 +204,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
     const int head = (flag == 1.0f) ? 0 : 1;
     const float* Pm = a.params;
     uint32_t nd = 0;
-    for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    for (int rnd = 0; rnd * (int)gridDim.x < ntiles; ++rnd) {
+      const int ti = tile_position(rnd, blockIdx.x, gridDim.x, a.tile_flag == nullptr);
+      if (ti >= ntiles) continue;
+      const int t = a.csr.tile_order[ti];
       const TileDims td = tile_dims(a.csr, t, S::ECAP);
       const int n = td.n, r0 = td.r0, g0 = td.g0, g1 = td.g1;
       epi_bar();   // previous tile fully consumed

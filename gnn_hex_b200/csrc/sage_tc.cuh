@@ -281,13 +281,22 @@ int debug_read_fwd_phases(long long* host, int n);
 int debug_read_bwd_phases(long long* host, int n);
 int tc_dw_groups(const Dims& d);
 struct TdFuse;
+// Persistent-CTA schedule of the tcgen05 forward / chain kernels: tiles are visited in csr.tile_order (heaviest first).
+// Stand-alone launch (zig = true): CTA c takes position rnd * G + c in even rounds and rnd * G + (G - 1 - c) in odd rounds
+// (boustrophedon: the CTA with the heaviest tile of one round gets the lightest of the next -- measured forward 0.292 ->
+// 0.285 ms).  Inside hexgnn_train_step (zig = false) the kernels are chained by programmatic dependent launch and the NEXT
+// kernel's CTAs become resident in blockIdx order as this one's retire, so the low CTAs, which start first, keep the
+// second round (boustrophedon there: trio 0.597 -> 0.642 ms).
+__host__ __device__ inline int tile_position(int rnd, int cta, int G, bool zig) {
+  return rnd * G + ((zig && (rnd & 1)) ? (G - 1 - cta) : cta);
+}
 int launch_backward_tc_chain(const Dims& d, const ParamMap& pm, const float* params, const float* x, int64_t N, int64_t E,
                              int64_t B, const void* csr, int flags, const float* d_nodes, const float* d_value,
                              const float* stash, float* dz, float* d_embeds, TcPackView pv, float* small_rec,
                              float* head_rec, int* sync, int grid, cudaStream_t st, const TdFuse* fuse = nullptr);
 int launch_backward_tc_dw(const Dims& d, int64_t N, int64_t E, int64_t B, const void* csr, const float* stash,
                           const float* dz, float* big_rec, int* sync, cudaStream_t st);
-int launch_reduce_tc(const Dims& d, const float* small_rec, int nsmall, const float* big_rec, int G,
+int launch_reduce_tc(const Dims& d, const float* small_rec, const int* ntiles, const float* big_rec, int G,
                      const float* head_rec, int64_t B, float* packed_sum, cudaStream_t st);
 
 // Per-graph record of the value head's backward: [dt (H/2 padded to 4) | pooled (4H padded to 4)]; the gradient of
@@ -320,7 +329,7 @@ inline TcBwdWs tc_bwd_ws(const Dims& d, int64_t B) {
   int64_t o = 0;
   w.pack = o; o += align_up(tc_pack_floats(d), 256);
   w.dz = o; o += tc_dz_bytes(d, B) / 4;
-  w.small_rec = o; o += align_up((int64_t)bwd_grid_ctas() * (gl.total - gl.gb), 4);
+  w.small_rec = o; o += align_up(B * (gl.total - gl.gb), 4);          // one record per tile (tiles <= B)
   w.big_rec = o; o += (int64_t)tc_dw_groups(d) * gl.g0;
   w.head_rec = o; o += align_up(B * tc_head_rec_floats(d), 4);
   w.sum = o; o += align_up(gl.total, 4);
