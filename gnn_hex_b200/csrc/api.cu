@@ -181,11 +181,10 @@ int hexgnn_backward(const HexModelDesc* desc, const float* params, const float* 
     if ((int64_t)ws_bytes < w.total * 4) { set_error("backward: workspace too small (%zu < %lld)", ws_bytes, (long long)w.total * 4); return HEXGNN_E_WORKSPACE; }
     float* wsf = (float*)ws;
     TcPackView tpv = tc_pack_view(wsf + w.pack, d);
-    int rc = launch_pack_tc(d, pm, params, x, tpv, true, st);
+    int* sync = (int*)(wsf + w.sync);
+    int rc = launch_pack_tc(d, pm, params, x, tpv, true, st, sync, (int)tc_sync_ints(d, B));   // also zeroes the flags
     if (rc) return rc;
     const int grid = bwd_grid_ctas();
-    int* sync = (int*)(wsf + w.sync);
-    HEX_CUDA_CHECK(cudaMemsetAsync(sync, 0, (size_t)tc_sync_ints(d, B) * 4, st));
     {
       // The dH chain and the dW GEMM overlap (programmatic dependent launch, per-tile flags): ONE event pair around
       // the two launches -- an event between them would serialise them.
@@ -234,9 +233,8 @@ int hexgnn_train_step(const HexModelDesc* desc, const float* params, const float
   float* wsf = (float*)ws;
   int* sync = (int*)(wsf + w.sync);
   // everything the three overlapped kernels need besides each other's tiles is produced first
-  HEX_CUDA_CHECK(cudaMemsetAsync(sync, 0, (size_t)tc_sync_ints(d, B) * 4, st));
   TcPackView tpv = tc_pack_view(wsf + w.pack, d);   // one pack launch writes the forward AND the backward images
-  int rc = launch_pack_tc(d, pm, params, x, tpv, true, st);
+  int rc = launch_pack_tc(d, pm, params, x, tpv, true, st, sync, (int)tc_sync_ints(d, B));   // ... and zeroes the flags
   if (rc) return rc;
   const int grid = bwd_grid_ctas();
   int* fwd_flag = sync + tc_sync_fwd_off(d, B);
@@ -253,11 +251,11 @@ int hexgnn_train_step(const HexModelDesc* desc, const float* params, const float
     --g_prof_mute;
     if (rc) return rc;
   }
-  rc = launch_reduce_tc(d, wsf + w.small_rec, csr_view(const_cast<void*>(csr), N, E, B).ntiles, wsf + w.big_rec, tc_dw_groups(d), wsf + w.head_rec, B, wsf + w.sum, st);
+  // the loss value and the TD errors are one more block of the reduction kernel
+  const TdLossArgs tdl{q, ptr, action, target, weight, N, (int)B, kind, scale, loss, td_err, nullptr};
+  rc = launch_reduce_tc(d, wsf + w.small_rec, csr_view(const_cast<void*>(csr), N, E, B).ntiles, wsf + w.big_rec, tc_dw_groups(d), wsf + w.head_rec, B, wsf + w.sum, st, &tdl);
   if (rc) return rc;
-  rc = launch_unpack_grads(d, pm, x, wsf + w.sum, grad_params, st);
-  if (rc) return rc;
-  return launch_td_loss(q, ptr, action, target, weight, N, B, kind, scale, loss, td_err, nullptr, st);
+  return launch_unpack_grads(d, pm, x, wsf + w.sum, grad_params, st);
 }
 
 int64_t hexgnn_collate_ws_bytes(int64_t B) { return B < 0 ? 0 : collate_ws_bytes(B); }

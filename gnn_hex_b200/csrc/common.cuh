@@ -219,6 +219,10 @@ int launch_reduce_grads(const Dims& d, const ParamMap& pm, const float* x, const
 
 int launch_unpack_grads(const Dims& d, const ParamMap& pm, const float* x, const float* packed_sum, float* grad_params,
                         cudaStream_t st);
+struct TdLossArgs {
+  const float* q; const int64_t* ptr; const int64_t* action; const float* target; const float* weight;
+  int64_t N; int B, kind; float scale; float* loss; float* td_err; float* d_q;
+};
 int launch_td_loss(const float* q, const int64_t* ptr, const int64_t* action, const float* target, const float* weight,
                    int64_t N, int64_t B, int kind, float scale, float* loss, float* td_err, float* d_q, cudaStream_t st);
 int launch_adam_step(const Dims& d, const ParamMap& pm, float* params, float* grads, float* exp_avg, float* exp_avg_sq,

@@ -2,11 +2,14 @@
 // per 16-wide k chunk, a tf32-hi half and a tf32-lo half in the K-major SWIZZLE_NONE canonical form the
 // tensor core reads, so the kernels fetch each ring stage with ONE contiguous bulk copy.
 #include "sage_tc.cuh"
+#include "td_loss.cuh"
 
 namespace hexgnn {
 
 __global__ void pack_tc_kernel(Dims d, ParamMap pm, const float* __restrict__ params, const float* __restrict__ x,
-                               TcPackView pv, int with_transpose) {
+                               TcPackView pv, int with_transpose, int* __restrict__ zero_ints, int n_zero) {
+  // hexgnn_train_step / hexgnn_backward: the hand-off flags and tickets of this call start at zero (saves a memset node)
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_zero; i += (int64_t)gridDim.x * blockDim.x) zero_ints[i] = 0;
   const int head = (x[2] == 1.0f) ? 0 : 1;
   const int Hp = d.Hp, H = d.H, N2 = 2 * d.Hp;
   const int NQ = Hp / kTcKC;
@@ -52,12 +55,12 @@ __global__ void pack_tc_kernel(Dims d, ParamMap pm, const float* __restrict__ pa
 }
 
 int launch_pack_tc(const Dims& d, const ParamMap& pm, const float* params, const float* x, TcPackView pv,
-                   bool with_transpose, cudaStream_t st) {
+                   bool with_transpose, cudaStream_t st, int* zero_ints, int n_zero) {
   const int64_t total = (int64_t)(d.Lt - 1) * d.Hp * 2 * d.Hp;
   int blocks = (int)((total + 255) / 256);
   if (blocks < 1) blocks = 1;
   if (blocks > 1184) blocks = 1184;
-  pack_tc_kernel<<<blocks, 256, 0, st>>>(d, pm, params, x, pv, with_transpose ? 1 : 0);
+  pack_tc_kernel<<<blocks, 256, 0, st>>>(d, pm, params, x, pv, with_transpose ? 1 : 0, zero_ints, n_zero);
   HEX_CUDA_CHECK(cudaGetLastError());
   return HEXGNN_OK;
 }
@@ -71,7 +74,12 @@ __global__ void __launch_bounds__(kRedThreads) reduce_tc_kernel(GradLayout gl, i
                                                                 const float* __restrict__ small_rec, const int* __restrict__ ntiles,
                                                                 const float* __restrict__ big_rec, int G,
                                                                 const float* __restrict__ head_rec, int hrec_n, int B,
-                                                                int nmain, int ngv0, float* __restrict__ out) {
+                                                                int nmain, int ngv0, float* __restrict__ out,
+                                                                const TdLossArgs td) {
+  if (blockIdx.x == gridDim.x - 1 && td.q) {   // hexgnn_train_step: loss value + TD errors ride along (no extra launch)
+    td_loss_block(td);
+    return;
+  }
   if ((int)blockIdx.x >= nmain + ngv0) {
     // per-tile records of the chain kernel: block = 128 elements x 8 record slices (contiguous ranges of tiles, 4
     // interleaved chains inside a slice, slices combined in slice order): a fixed summation order that does not depend
@@ -156,16 +164,18 @@ __global__ void __launch_bounds__(kRedThreads) reduce_tc_kernel(GradLayout gl, i
 }
 
 int launch_reduce_tc(const Dims& d, const float* small_rec, const int* ntiles, const float* big_rec, int G,
-                     const float* head_rec, int64_t B, float* packed_sum, cudaStream_t st) {
+                     const float* head_rec, int64_t B, float* packed_sum, cudaStream_t st, const TdLossArgs* td) {
   GradLayout gl;
   grad_layout(d, &gl);
   int blocks = (int)((gl.total + kRedThreads - 1) / kRedThreads);
   if (blocks > 592) blocks = 592;
   const int gv0_blocks = ((4 * d.H + 127) / 128) * ((d.H2 + 7) / 8);
   const int small_blocks = (int)((gl.total - gl.gb + 127) / 128);
-  reduce_tc_kernel<<<blocks + gv0_blocks + small_blocks, kRedThreads, 0, st>>>(gl, d.Hp, d.H, d.H2, small_rec, ntiles, big_rec, G,
-                                                                       head_rec, tc_head_rec_floats(d), (int)B, blocks,
-                                                                       gv0_blocks, packed_sum);
+  TdLossArgs tdl{};
+  if (td) tdl = *td;
+  reduce_tc_kernel<<<blocks + gv0_blocks + small_blocks + (td ? 1 : 0), kRedThreads, 0, st>>>(
+      gl, d.Hp, d.H, d.H2, small_rec, ntiles, big_rec, G, head_rec, tc_head_rec_floats(d), (int)B, blocks, gv0_blocks,
+      packed_sum, tdl);
   HEX_CUDA_CHECK(cudaGetLastError());
   return HEXGNN_OK;
 }

@@ -272,7 +272,7 @@ __device__ __forceinline__ void tile_gather(const GatherTab& g, const float* __r
 }
 
 int launch_pack_tc(const Dims& d, const ParamMap& pm, const float* params, const float* x, TcPackView pv,
-                   bool with_transpose, cudaStream_t st);
+                   bool with_transpose, cudaStream_t st, int* zero_ints = nullptr, int n_zero = 0);
 int launch_forward_tc(const Dims& d, const ParamMap& pm, const float* params, const float* x, int64_t N, int64_t E,
                       int64_t B, const void* csr, int flags, float* out_nodes, float* out_value, float* stash,
                       TcPackView pv, cudaStream_t st, int* tile_flag = nullptr);
@@ -297,7 +297,7 @@ int launch_backward_tc_chain(const Dims& d, const ParamMap& pm, const float* par
 int launch_backward_tc_dw(const Dims& d, int64_t N, int64_t E, int64_t B, const void* csr, const float* stash,
                           const float* dz, float* big_rec, int* sync, cudaStream_t st);
 int launch_reduce_tc(const Dims& d, const float* small_rec, const int* ntiles, const float* big_rec, int G,
-                     const float* head_rec, int64_t B, float* packed_sum, cudaStream_t st);
+                     const float* head_rec, int64_t B, float* packed_sum, cudaStream_t st, const TdLossArgs* td = nullptr);
 
 // Per-graph record of the value head's backward: [dt (H/2 padded to 4) | pooled (4H padded to 4)]; the gradient of
 // value_head.layers.0.weight is sum_g dt_g (x) pooled_g, summed in graph order by reduce_tc_kernel.

@@ -10,7 +10,7 @@ from ._lib import HEXGNN_ADV_ONLY, HEXGNN_SEPARATE, HEXGNN_PATH_SIMT, HEXGNN_PAT
 
 # kernels launched by each C-ABI call (csr: init, hist, scan, fill, sort; forward: pack, fused;
 # backward: pack, fused, reduce, unpack) -- bench.py's `gpu_launches` is read off this counter.
-LAUNCHES = {"build_csr": 5, "forward": 2, "backward": 5, "td_loss": 1, "train_step": 7, "adam_step": 2, "mask_argmax": 1, "td_target": 1, "forward_big": 0, "allreduce_p2p": 1}
+LAUNCHES = {"build_csr": 5, "forward": 2, "backward": 5, "td_loss": 1, "train_step": 6, "adam_step": 2, "mask_argmax": 1, "td_target": 1, "forward_big": 0, "allreduce_p2p": 1}
 launch_counter = 0
 
 
@@ -168,7 +168,7 @@ LOSS_KINDS = {"mse": 0, "smooth_l1": 1, "huber": 1}
 def fused_train_step(desc, flat_params, x, csr, ptr, action, target, weight=None, kind="mse", scale=1.0, grad_out=None,
                      ws=None):
     """hexgnn_train_step: forward + TD loss + backward + gradient reduction in one call (rainbow.py:301-316).
-    Returns (loss [], td_err [B], q [N], flat gradient [P]).  Launches pack, forward, chain, dW, reduce, unpack, loss."""
+    Returns (loss [], td_err [B], q [N], flat gradient [P]).  Launches pack, forward, chain, dW, reduce (+ loss block), unpack."""
     _require_cuda(x, "x")
     _require_cuda(flat_params, "parameters")
     if kind not in LOSS_KINDS:
