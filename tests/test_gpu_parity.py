@@ -459,3 +459,33 @@ def test_rainbow_learner_step_matches_reference_formulas(double_dqn):
         assert torch.allclose(p.detach().cpu(), ref_sd[name].detach(), atol=1e-5, rtol=0), name
     lrn.sync_Q_target()
     assert torch.equal(m_tgt.flat_parameters, m_pol.flat_parameters)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("count", [1, 3, 700])
+def test_train_step_batch_extremes(count):
+    """hexgnn_train_step on a single graph, on three graphs (fewer tiles than CTAs: every CTA but a few idles, the dW kernel
+    has no phase-A items) and on 700 graphs (5 rounds of tiles: multi-round phase A, ranked tile order): loss against the
+    fp32 oracle, gradients bit-identical to the forward -> td_loss -> backward route and repeatable."""
+    cfg = CONFIGS["L"]
+    o, m = make_pair(cfg["hidden"], cfg["layers"])
+    m = m.to(DEV)
+    gs = data.load_positions(cfg["fixture"], maker=1)
+    gs = (gs * 3)[:count]
+    hb = data.collate(gs)
+    b = hb.to(DEV)
+    action, target, weight = loss_inputs(hb)
+    with torch.no_grad():
+        loss_ref = orc.rainbow_loss(o(hb.x, hb.edge_index, hb.batch, hb.ptr), hb.ptr, action, target, weight)
+    action, target, weight = action.to(DEV), target.to(DEV), weight.to(DEV)
+    m.zero_grad(set_to_none=True)
+    q_ref = m(b.x, b.edge_index, b.batch, b.ptr)
+    ops.td_loss(q_ref, b.ptr, action, target, weight)[0].backward()
+    g_ref = m.flat_gradient.clone()
+    for _ in range(2):
+        m.zero_grad(set_to_none=True)
+        loss, err, q = m.train_step(b.x, b.edge_index, b.batch, b.ptr, action=action, target=target, weight=weight)
+        assert int(m.last_csr.status.item()) == 0
+        assert torch.equal(q, q_ref.detach()) and torch.equal(m.flat_gradient, g_ref)
+        assert abs(float(loss) - float(loss_ref)) <= 1e-5 * max(abs(float(loss_ref)), 1e-3)
+    assert torch.isfinite(g_ref).all() and float(g_ref.abs().max()) > 0
