@@ -133,6 +133,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
   const int ntiles = *a.csr.ntiles;
   const long long t_kernel0 = PH_NOW();
   long long ph0 = 0, ph1 = 0, ph2 = 0, ph3 = 0, ph4 = 0, ph5 = 0, ph6 = 0, ph7 = 0, ntl = 0;
+  long long hq0 = 0, hq1 = 0, hq2 = 0, hq3 = 0, hq4 = 0, hq5 = 0;   // head sub-phases (per graph loop)
 
   if (tid == 0) {
     for (int i = 0; i < kBwdStages; ++i) { mbar_init(&bar_full[i], 1); mbar_init(&bar_empty[i], 1); }
@@ -355,6 +356,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
           for (int i = tid; i < hrec_n; i += kTcEpiThreads) hrec[i] = 0.f;
           if (ng <= 0) continue;
         }
+        long long th = PH_NOW();
         float sumdq = 0.f;
         if (!adv_only) {
           if (wid == 0) {
@@ -372,6 +374,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
           adv_s[i] = (adv_only ? dn : dn - sumdq / (float)ng) * 2.0f * (1.0f - th * th);
         }
         epi_bar_b();
+        PH_ADD(hq0, th); th = PH_NOW();
         // column-parallel pass over the graph's rows, 4 row quarters: pools, arg rows, d head.linear.weight
         if (pc < H) {
           const int chunk = (ng + 3) >> 2;
@@ -411,15 +414,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
           if (lane == 0) accs[A_GLINB] += u;
         }
         epi_bar_b();
+        PH_ADD(hq1, th); th = PH_NOW();
         if (!adv_only) {
-          for (int k = wid; k < H2; k += kTcEpiWarps) {
-            float u = 0.f;
-            const float* wrow = w0 + (int64_t)k * 4 * H;
-            for (int q = lane; q < 4 * H; q += 32) u = fmaf(wrow[q], pool[q], u);
-            u = warp_sum_b(u);
-            if (lane == 0) hid[k] = fmaxf(u + b0[k], 0.f);
-          }
+          // hidden activations of the value MLP: stashed by the forward (same bits as recomputing them)
+          if (tid < H2) hid[tid] = a.stash[tc_stash_hid_off_floats(a.d, a.N, a.B) + (int64_t)(g0 + g) * H2p + tid];
           epi_bar_b();
+          PH_ADD(hq2, th); th = PH_NOW();
           if (wid == kTcEpiWarps - 1) {
             float u = 0.f;
             for (int k = lane; k < H2; k += 32) u = fmaf(w1[k], hid[k], u);
@@ -441,6 +441,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
           }
           if (tid == 0) accs[A_GV1B] += ds;
           epi_bar_b();
+          PH_ADD(hq3, th); th = PH_NOW();
           // graph record [dt | pooled]: the reduction kernel sums dt (x) pooled over graphs in graph order
           for (int i = tid; i < hrec_n; i += kTcEpiThreads)
             hrec[i] = i < H2p ? (i < H2 ? hid[i] : 0.f) : (i - H2p < 4 * H ? pool[i - H2p] : 0.f);
@@ -451,21 +452,38 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
           epi_bar_b();  // pooled values fully consumed before they become their own gradient
           if (tid < 4 * H) pool[tid] = dp;
           epi_bar_b();
+          PH_ADD(hq4, th); th = PH_NOW();
         }
-        for (int idx = tid; idx < ng * Hp; idx += kTcEpiThreads) {
-          const int i = rs + idx / Hp, c = idx % Hp;
-          float v = 0.f;
-          if (c < H) {
-            v = adv_s[i] * wa[c];
+        // dump rows become dL/dg: thread = (row quarter, channel), the per-channel terms live in registers
+        if (pc < Hp) {
+          const int chunk = (ng + 3) >> 2;
+          const int ia = rs + part * chunk, ib = (ia + chunk < re) ? ia + chunk : re;
+          const bool cv = pc < H;
+          float wa_c = 0.f, base = 0.f, vmx = 0.f, vmn = 0.f;
+          int amx = -1, amn = -1;
+          if (cv) {
+            wa_c = wa[pc];
             if (!adv_only) {
-              v += pool[c] + pool[3 * H + c] / (float)ng;
-              if (arg_s[c] == i) v += pool[H + c];
-              if (arg_s[Hp + c] == i) v += pool[2 * H + c];
+              base = pool[pc] + pool[3 * H + pc] / (float)ng;
+              amx = arg_s[pc]; amn = arg_s[Hp + pc];
+              vmx = pool[H + pc]; vmn = pool[2 * H + pc];
             }
           }
-          dump[i * P + c] = v;
+          for (int i = ia; i < ib; ++i) {
+            float v = 0.f;
+            if (cv) {
+              v = adv_s[i] * wa_c;
+              if (!adv_only) {
+                v += base;
+                if (amx == i) v += vmx;
+                if (amn == i) v += vmn;
+              }
+            }
+            dump[i * P + pc] = v;
+          }
         }
         epi_bar_b();
+        PH_ADD(hq5, th);
       }
       PH_ADD(ph4, tq);
       // ---- SAGE layers Lt-1 .. 1 on the tensor cores ---------------------------------------------------------
@@ -662,6 +680,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
     if (tid == 0 && blockIdx.x < 148) {
       long long* o = g_bwd_phase + blockIdx.x * 16;
       o[0] = ph0; o[1] = ph1; o[2] = ph2; o[3] = ph3; o[4] = ph4; o[5] = ph5; o[6] = ph6; o[7] = ph7; o[8] = PH_NOW() - t_kernel0; o[9] = ntl;
+      o[10] = hq0; o[11] = hq1; o[12] = hq2; o[13] = hq3; o[14] = hq4; o[15] = hq5;
     }
   }
   // ---- teardown ----------------------------------------------------------------------------------------------------------

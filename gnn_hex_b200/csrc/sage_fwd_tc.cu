@@ -339,9 +339,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
         PH_ADD(ph1, tq);
         tq = PH_NOW();
         // phase 2: agg_i = sum_{j -> i} Zl_j in CSR order (tile_gather, sage_tc.cuh)
-#ifndef HEXGNN_EXP_NO_GATHER
         tile_gather<NJ>(gtab, dump, agg, n, wid, lane);
-#endif
         epi_bar();
         PH_ADD(ph2, tq);
         tq = PH_NOW();
@@ -469,6 +467,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
           if (lane == 0) hid[k] = fmaxf(u + b0[k], 0.f);
         }
         epi_bar();
+        if (a.stash && tid < H2)   // kept for the backward (tc_stash_hid_off_floats)
+          a.stash[tc_stash_hid_off_floats(a.d, a.N, a.B) + (int64_t)(g0 + g) * ((H2 + 3) & ~3) + tid] = hid[tid];
         if (wid == 0) {
           float u = 0.f;
           for (int k = lane; k < H2; k += 32) u = fmaf(w1[k], hid[k], u);

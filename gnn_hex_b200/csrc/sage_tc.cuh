@@ -80,8 +80,13 @@ inline int64_t tc_mask_words(const Dims& d, int64_t B) { return (int64_t)d.Lt * 
 __host__ __device__ inline int64_t tc_stash_mask_off_floats(const Dims& d, int64_t N, int64_t B) {
   return (int64_t)d.Lt * B * tc_act_blocks(d.Hp) * (kImgBlockBytes / 4) + N * d.Hp;
 }
+// + the value MLP's hidden activations [B graphs][H/2 padded to 4] (the backward reads them instead of recomputing
+// relu(W0 pooled + b0): 97 KB of weights per graph)
+__host__ __device__ inline int64_t tc_stash_hid_off_floats(const Dims& d, int64_t N, int64_t B) {
+  return tc_stash_mask_off_floats(d, N, B) + (int64_t)d.Lt * B * kTcSlices * kTcRows;
+}
 inline int64_t tc_stash_bytes(const Dims& d, int64_t N, int64_t B) {
-  return (tc_stash_mask_off_floats(d, N, B) + tc_mask_words(d, B)) * 4;
+  return (tc_stash_hid_off_floats(d, N, B) + B * (int64_t)((d.H2 + 3) & ~3)) * 4;
 }
 inline int64_t tc_dz_bytes(const Dims& d, int64_t B) { return (int64_t)(d.Lt - 1) * B * tc_dz_blocks(d.Hp) * kImgBlockBytes; }
 inline bool tc_bwd_supported(const Dims& d) { return d.Hp + 1 <= 128; }   // the ones-channel must fit M = 128
@@ -214,10 +219,6 @@ __device__ __forceinline__ void gather_build(const GatherTab& g, const int* __re
   asm volatile("bar.sync 1, %0;" ::"n"(kTcEpiThreads) : "memory");
 }
 __device__ __forceinline__ void fadd2x2(float4& a, const float4& b) {   // a += b as two packed f32x2 adds
-#ifdef HEXGNN_EXP_SCALAR_FADD
-  a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
-  return;
-#endif
   unsigned long long a0, a1, b0, b1;
   asm("mov.b64 %0, {%1, %2};" : "=l"(a0) : "f"(a.x), "f"(a.y));
   asm("mov.b64 %0, {%1, %2};" : "=l"(a1) : "f"(a.z), "f"(a.w));

@@ -26,7 +26,8 @@ f, fn = _lib.profile_read(0); bw, bn = _lib.profile_read(1)
 print(f"step ms {s.elapsed_time(e)/20:.4f}  fwd kernel {f/max(fn,1):.4f}  bwd chain kernel {bw/max(bn,1):.4f}")
 NAMES = {0: ["wait_Zl", "phase1", "gather", "load+l0", "head", "mma:wait_h", "mma:wait_w", "mma:issue", "total", "tiles",
              "wait_Zr", "phase3", "p3:ld", "p3:issued"],
-         1: ["wait_dH", "E1", "E2_gather", "wait_r+A", "head+load", "layer0", "hl:load", "hl:+build+tanh", "total", "tiles"]}
+         1: ["wait_dH", "E1", "E2_gather", "wait_r+A", "head+load", "layer0", "hl:load", "hl:+build+tanh", "total", "tiles",
+             "hd:dq+adv", "hd:colpass", "hd:mlp_fwd", "hd:mlp_bwd", "hd:hrec+dp", "hd:rows"]}
 for which in (0, 1):
     ph = _lib.debug_phases(which)
     print("forward" if which == 0 else "backward chain")
