@@ -447,7 +447,16 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
             hrec[i] = i < H2p ? (i < H2 ? hid[i] : 0.f) : (i - H2p < 4 * H ? pool[i - H2p] : 0.f);
           float dp = 0.f;
           if (tid < 4 * H) {
-            for (int k = 0; k < H2; ++k) dp = fmaf(w0[(int64_t)k * 4 * H + tid], hid[k], dp);
+            // 8 independent L2 loads in flight per batch (the weights are 97 KB: they do not live in L1); k ascending
+            int k = 0;
+            for (; k + 8 <= H2; k += 8) {
+              float wv[8];
+#pragma unroll
+              for (int u = 0; u < 8; ++u) wv[u] = w0[(int64_t)(k + u) * 4 * H + tid];
+#pragma unroll
+              for (int u = 0; u < 8; ++u) dp = fmaf(wv[u], hid[k + u], dp);
+            }
+            for (; k < H2; ++k) dp = fmaf(w0[(int64_t)k * 4 * H + tid], hid[k], dp);
           }
           epi_bar_b();  // pooled values fully consumed before they become their own gradient
           if (tid < 4 * H) pool[tid] = dp;

@@ -458,13 +458,37 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
           pool[3 * H + tid] = sum / (float)(ng > 0 ? ng : 1);
         }
         epi_bar();
-        for (int k = wid; k < H2; k += kTcEpiWarps) {
-          float u = 0.f;
-          const float* wrow = w0 + (int64_t)k * 4 * H;
-          for (int q = lane; q < 4 * H; q += 32) u = fmaf(wrow[q], pool[q], u);
+        {
+          // hid[k] = relu(w0[k] . pooled + b0[k]): warp = rows k = wid, wid + 16, ...; two rows per batch with all their
+          // weight loads (L2) in flight before the first FMA; per row the same summation order as a plain lane-strided loop
+          constexpr int JMAX = (4 * Hp + 31) / 32;
+          float pl[JMAX];
 #pragma unroll
-          for (int o = 16; o > 0; o >>= 1) u += __shfl_xor_sync(0xffffffffu, u, o);
-          if (lane == 0) hid[k] = fmaxf(u + b0[k], 0.f);
+          for (int j = 0; j < JMAX; ++j) { const int q = lane + 32 * j; pl[j] = q < 4 * H ? pool[q] : 0.f; }
+          for (int k0 = wid; k0 < H2; k0 += 2 * kTcEpiWarps) {
+            const int k1 = k0 + kTcEpiWarps;
+            const float* r0p = w0 + (int64_t)k0 * 4 * H;
+            const float* r1p = w0 + (int64_t)(k1 < H2 ? k1 : k0) * 4 * H;
+            float wa0[JMAX], wa1[JMAX];
+#pragma unroll
+            for (int j = 0; j < JMAX; ++j) {
+              const int q = lane + 32 * j;
+              wa0[j] = q < 4 * H ? r0p[q] : 0.f;
+              wa1[j] = q < 4 * H ? r1p[q] : 0.f;
+            }
+            float u0 = 0.f, u1 = 0.f;
+#pragma unroll
+            for (int j = 0; j < JMAX; ++j) { u0 = fmaf(wa0[j], pl[j], u0); u1 = fmaf(wa1[j], pl[j], u1); }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+              u0 += __shfl_xor_sync(0xffffffffu, u0, o);
+              u1 += __shfl_xor_sync(0xffffffffu, u1, o);
+            }
+            if (lane == 0) {
+              hid[k0] = fmaxf(u0 + b0[k0], 0.f);
+              if (k1 < H2) hid[k1] = fmaxf(u1 + b0[k1], 0.f);
+            }
+          }
         }
         epi_bar();
         if (a.stash && tid < H2)   // kept for the backward (tc_stash_hid_off_floats)
