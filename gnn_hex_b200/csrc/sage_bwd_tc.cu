@@ -329,20 +329,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
         for (int p = b; p < e; ++p) { const int j = col_s[p]; s0 += x0_s[j]; s1 += x1_s[j]; }
         inv_s[i] = inv; m0_s[i] = s0 * inv; m1_s[i] = s1 * inv;
       }
-      // th_i = tanh(w_a . g_i + b_a): warp = row, lane = 4 channels
-      for (int r = wid; r < n; r += kTcEpiWarps) {
-        float u = 0.f;
-        if (lane < NV) {
-          const float4 v = ((const float4*)dump)[r * PV + lane];
-          const int c = lane * 4;
-          if (c < H) u = fmaf(wa[c], v.x, u);
-          if (c + 1 < H) u = fmaf(wa[c + 1], v.y, u);
-          if (c + 2 < H) u = fmaf(wa[c + 2], v.z, u);
-          if (c + 3 < H) u = fmaf(wa[c + 3], v.w, u);
-        }
-        u = warp_sum_b(u);
-        if (lane == 0) th_s[r] = tanhf(u + ba);
-      }
+      // th_i = tanh(w_a . g_i + b_a): stashed by the forward
+      for (int i = tid; i < kTcRows; i += kTcEpiThreads)
+        th_s[i] = a.stash[tc_stash_th_off_floats(a.d, a.N, a.B) + (int64_t)t * kTcRows + i];
       epi_bar_b();
       PH_ADD(ph7, tq);
       const float inv = inv_s[row];
@@ -447,16 +436,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
             hrec[i] = i < H2p ? (i < H2 ? hid[i] : 0.f) : (i - H2p < 4 * H ? pool[i - H2p] : 0.f);
           float dp = 0.f;
           if (tid < 4 * H) {
-            // 8 independent L2 loads in flight per batch (the weights are 97 KB: they do not live in L1); k ascending
-            int k = 0;
-            for (; k + 8 <= H2; k += 8) {
-              float wv[8];
+            // 14 independent L2 loads in flight per batch (the weights are 97 KB: they do not live in L1); k ascending
+            for (int k = 0; k < H2; k += 14) {
+              float wv[14];
 #pragma unroll
-              for (int u = 0; u < 8; ++u) wv[u] = w0[(int64_t)(k + u) * 4 * H + tid];
+              for (int u = 0; u < 14; ++u) wv[u] = (k + u < H2) ? w0[(int64_t)(k + u) * 4 * H + tid] : 0.f;
 #pragma unroll
-              for (int u = 0; u < 8; ++u) dp = fmaf(wv[u], hid[k + u], dp);
+              for (int u = 0; u < 14; ++u) dp = fmaf(wv[u], (k + u < H2) ? hid[k + u] : 0.f, dp);
             }
-            for (; k < H2; ++k) dp = fmaf(w0[(int64_t)k * 4 * H + tid], hid[k], dp);
           }
           epi_bar_b();  // pooled values fully consumed before they become their own gradient
           if (tid < 4 * H) pool[tid] = dp;

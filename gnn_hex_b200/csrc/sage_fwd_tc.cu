@@ -423,11 +423,28 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
       {
         const float* wa = Pm + a.pm.lin_w[head];
         const float ba = Pm[a.pm.lin_b[head]];
-        if (tid < kTcRows && tid < n) {
+        // thread = (row, quarter of the channels); inside a quarter the channel order is rotated by the lane so that the
+        // 32 rows of a warp hit 32 different banks (row pitch Hp + 4 words); quarters combined in fixed order
+        constexpr int CQ = Hp / 4;
+        {
+          const int r = tid & (kTcRows - 1), part = tid >> 7;
           float u = 0.f;
-          const float* gr = dump + tid * P;
-          for (int c = 0; c < H; ++c) u = fmaf(wa[c], gr[c], u);
-          adv_s[tid] = 2.0f * tanhf(u + ba);
+          if (r < n) {
+            const float* gr = dump + r * P + part * CQ;
+            const float* wq = wa + part * CQ;
+            for (int j = 0; j < CQ; ++j) {
+              const int c = (j + lane) % CQ;
+              if (part * CQ + c < H) u = fmaf(wq[c], gr[c], u);
+            }
+          }
+          agg[part * kTcRows + r] = u;           // agg is free here: partial sums [4][128]
+        }
+        epi_bar();
+        if (tid < kTcRows) {
+          float th = 0.f;
+          if (tid < n) th = tanhf(((agg[tid] + agg[kTcRows + tid]) + (agg[2 * kTcRows + tid] + agg[3 * kTcRows + tid])) + ba);
+          adv_s[tid] = 2.0f * th;
+          if (a.stash) a.stash[tc_stash_th_off_floats(a.d, a.N, a.B) + (int64_t)t * kTcRows + tid] = th;   // for the backward
         }
         epi_bar();
       }

@@ -85,8 +85,12 @@ __host__ __device__ inline int64_t tc_stash_mask_off_floats(const Dims& d, int64
 __host__ __device__ inline int64_t tc_stash_hid_off_floats(const Dims& d, int64_t N, int64_t B) {
   return tc_stash_mask_off_floats(d, N, B) + (int64_t)d.Lt * B * kTcSlices * kTcRows;
 }
+// + tanh(w_a . g_i + b_a) of every row [B tiles][128] (half the advantage: the backward needs 1 - th^2)
+__host__ __device__ inline int64_t tc_stash_th_off_floats(const Dims& d, int64_t N, int64_t B) {
+  return tc_stash_hid_off_floats(d, N, B) + B * (int64_t)((d.H2 + 3) & ~3);
+}
 inline int64_t tc_stash_bytes(const Dims& d, int64_t N, int64_t B) {
-  return (tc_stash_hid_off_floats(d, N, B) + B * (int64_t)((d.H2 + 3) & ~3)) * 4;
+  return (tc_stash_th_off_floats(d, N, B) + B * (int64_t)kTcRows) * 4;
 }
 inline int64_t tc_dz_bytes(const Dims& d, int64_t B) { return (int64_t)(d.Lt - 1) * B * tc_dz_blocks(d.Hp) * kImgBlockBytes; }
 inline bool tc_bwd_supported(const Dims& d) { return d.Hp + 1 <= 128; }   // the ones-channel must fit M = 128
