@@ -22,7 +22,7 @@ STATUS_NAMES = {
     ST_FLAG_MIXED: "x[:,2] is not constant over the batch (reference asserts this, GN0/models.py:538)",
 }
 
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 
 class HexModelDesc(C.Structure):
@@ -43,7 +43,8 @@ class HexCsrLayout(C.Structure):
 EXPORTS = ["hexgnn_abi_version", "hexgnn_last_error", "hexgnn_param_count", "hexgnn_param_offsets",
            "hexgnn_sizes", "hexgnn_csr_layout", "hexgnn_build_csr", "hexgnn_forward", "hexgnn_backward",
            "hexgnn_profile_enable", "hexgnn_profile_read", "hexgnn_selftest_mma", "hexgnn_debug_phases", "hexgnn_stash_embed", "hexgnn_td_loss", "hexgnn_train_step", "hexgnn_adam_step", "hexgnn_adam_ws_bytes", "hexgnn_collate", "hexgnn_collate_ws_bytes",
-           "hexgnn_mask_argmax", "hexgnn_td_target", "hexgnn_forward_big", "hexgnn_allreduce_p2p"]
+           "hexgnn_mask_argmax", "hexgnn_td_target", "hexgnn_forward_big", "hexgnn_allreduce_p2p",
+           "hexgnn_noisy_compose", "hexgnn_noisy_grads"]
 
 _lib = None
 
@@ -97,6 +98,10 @@ def lib():
     l.hexgnn_adam_step.restype = C.c_int
     l.hexgnn_adam_step.argtypes = [p, p, p, p, p, p, p, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, i32, p, p,
                                    C.c_size_t, p]
+    l.hexgnn_noisy_compose.restype = C.c_int
+    l.hexgnn_noisy_compose.argtypes = [D, p, p, p]
+    l.hexgnn_noisy_grads.restype = C.c_int
+    l.hexgnn_noisy_grads.argtypes = [D, p, p, p, i32, p]
     l.hexgnn_td_loss.restype = C.c_int
     l.hexgnn_td_loss.argtypes = [p, p, p, p, p, i64, i64, i32, C.c_float, p, p, p, p]
     l.hexgnn_forward_big.restype = C.c_int

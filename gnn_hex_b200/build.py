@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libhexgnn.so")
-SOURCES = ["api.cu", "csr_build.cu", "pack.cu", "sage_fwd_simt.cu", "sage_bwd_simt.cu", "tc_selftest.cu", "pack_tc.cu", "sage_fwd_tc.cu", "sage_bwd_tc.cu", "sage_dw_tc.cu", "td_loss.cu", "sage_big.cu", "optim.cu", "collate.cu"]
+SOURCES = ["api.cu", "csr_build.cu", "pack.cu", "sage_fwd_simt.cu", "sage_bwd_simt.cu", "tc_selftest.cu", "pack_tc.cu", "sage_fwd_tc.cu", "sage_bwd_tc.cu", "sage_dw_tc.cu", "td_loss.cu", "sage_big.cu", "optim.cu", "collate.cu", "noisy.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "--compiler-options", "-fPIC", "-Xptxas", "-v"]
 

@@ -290,6 +290,25 @@ int hexgnn_adam_step(const HexModelDesc* desc, float* params, float* grads, floa
                           (flags & HEXGNN_ADAM_SKIP_UNTAKEN) ? 1 : 0, grad_norm, (float*)ws, (cudaStream_t)stream);
 }
 
+int hexgnn_noisy_compose(const HexModelDesc* desc, float* params, const float* noisy, void* stream) {
+  Dims d;
+  if (!make_dims(desc, &d)) { set_error("noisy_compose: bad model descriptor"); return HEXGNN_E_BADARG; }
+  if (!params || !noisy) { set_error("noisy_compose: bad argument"); return HEXGNN_E_BADARG; }
+  ParamMap pm;
+  make_param_map(d, &pm);
+  return launch_noisy_compose(d, pm, params, noisy, (cudaStream_t)stream);
+}
+
+int hexgnn_noisy_grads(const HexModelDesc* desc, const float* grads, const float* noisy, float* d_noisy, int32_t accumulate,
+                       void* stream) {
+  Dims d;
+  if (!make_dims(desc, &d)) { set_error("noisy_grads: bad model descriptor"); return HEXGNN_E_BADARG; }
+  if (!grads || !noisy || !d_noisy) { set_error("noisy_grads: bad argument"); return HEXGNN_E_BADARG; }
+  ParamMap pm;
+  make_param_map(d, &pm);
+  return launch_noisy_grads(d, pm, grads, noisy, d_noisy, accumulate ? 1 : 0, (cudaStream_t)stream);
+}
+
 int hexgnn_td_loss(const float* q, const int64_t* ptr, const int64_t* action, const float* target, const float* weight,
                    int64_t N, int64_t B, int32_t kind, float scale, float* loss, float* td_err, float* d_q, void* stream) {
   if (!q || !ptr || !action || !target || !loss || N < 1 || B < 1) { set_error("td_loss: bad argument"); return HEXGNN_E_BADARG; }

@@ -229,6 +229,9 @@ int launch_adam_step(const Dims& d, const ParamMap& pm, float* params, float* gr
                      int* state, const float* x, float lr, float beta1, float beta2, float eps, float max_norm,
                      int skip_untaken, float* grad_norm, float* ws, cudaStream_t st);
 int adam_ws_floats();
+int launch_noisy_compose(const Dims& d, const ParamMap& pm, float* params, const float* noisy, cudaStream_t st);
+int launch_noisy_grads(const Dims& d, const ParamMap& pm, const float* grads, const float* noisy, float* d_noisy,
+                       int accumulate, cudaStream_t st);
 int64_t collate_ws_bytes(int64_t B);
 int launch_collate(const float* const* x_ptrs, const int64_t* const* ei_ptrs, const int64_t* n_nodes, const int64_t* n_edges,
                    int64_t B, float* x_out, int64_t* ei_out, int64_t* batch_out, int64_t* ptr_out, void* ws, void* host_ws,

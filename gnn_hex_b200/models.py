@@ -36,6 +36,44 @@ class _SageParams(nn.Module):
         self.has_cache = False
         self.convs = nn.ModuleList([_Conv(in_channels if i == 0 else hidden, hidden) for i in range(num_layers)])
 
+    @torch.no_grad()
+    def grow_depth(self, additional_layers):
+        """GN0/models.py:166-185: append layers that start as the identity (lin_l = 0, lin_r = I; the input is a ReLU
+        output, so relu(I x) = x and the network's function is unchanged)."""
+        dev = self.convs[0].lin_l.weight.device
+        H = self.hidden_channels
+        for _ in range(int(additional_layers)):
+            c = _Conv(H, H).to(dev)
+            c.lin_l.weight.zero_()
+            c.lin_l.bias.zero_()
+            c.lin_r.weight.copy_(torch.eye(H, device=dev))
+            self.convs.append(c)
+        self.num_layers += int(additional_layers)
+        self.has_cache = False
+
+    @torch.no_grad()
+    def grow_width(self, new_width, new_in_channels=None):
+        """GN0/models.py:187-238: freshly initialised wider layers whose top-left block is the old layer; the old rows see
+        nothing of the new input columns (zeros), the new rows keep their random init."""
+        if self.num_layers < 2:
+            raise NotImplementedError("grow_width of a one-layer stack")
+        dev = self.convs[0].lin_l.weight.device
+        old, H = self.convs, self.hidden_channels
+        old_in = self.in_channels
+        if new_in_channels is not None:
+            self.in_channels = int(new_in_channels)
+        new = nn.ModuleList([_Conv(self.in_channels if i == 0 else new_width, new_width).to(dev)
+                             for i in range(self.num_layers)])
+        for i, (c, o) in enumerate(zip(new, old)):
+            cin_old = (old_in if i == 0 else H)
+            for lin, lin_o in ((c.lin_l, o.lin_l), (c.lin_r, o.lin_r)):
+                lin.weight[:H, :cin_old] = lin_o.weight
+                lin.weight[:H, cin_old:] = 0
+            c.lin_l.bias[:H] = o.lin_l.bias
+        self.convs = new
+        self.has_cache = False
+        self.hidden_channels = int(new_width)
+
 
 class _MLPParams(nn.Module):
     """Holder named like `MLP(hidden//2, 1, 4*hidden, 1)` (GN0/models.py:36-49): `.layers.{0,1}`."""
@@ -43,18 +81,110 @@ class _MLPParams(nn.Module):
     def __init__(self, hidden, num_input, num_output):
         super().__init__()
         self.layers = nn.ModuleList([nn.Linear(num_input, hidden), nn.Linear(hidden, num_output)])
+        self.hidden_channels, self.num_input, self.num_output = hidden, num_input, num_output
+
+    @torch.no_grad()
+    def grow_input_width(self, new_input_width, new_hidden_channels):
+        """GN0/models.py:52-73 for the one-hidden-layer MLP: zero-filled wider layers with the old weights in the top-left
+        block.  As in the reference the old input columns keep their POSITIONS (the pooled vector is [sum | max | min |
+        mean] of the new width, so they no longer line up with the old pooling blocks)."""
+        dev = self.layers[0].weight.device
+        l0, l1 = self.layers[0], self.layers[1]
+        n0 = nn.Linear(new_input_width, new_hidden_channels).to(dev)
+        n0.weight.zero_()
+        n0.bias.zero_()
+        n0.weight[:self.hidden_channels, :self.num_input] = l0.weight
+        n0.bias[:self.hidden_channels] = l0.bias
+        n1 = nn.Linear(new_hidden_channels, 1).to(dev)
+        n1.weight.zero_()
+        n1.weight[:, :self.hidden_channels] = l1.weight
+        n1.bias[:] = l1.bias
+        self.layers[0], self.layers[1] = n0, n1
+        self.num_input, self.hidden_channels = int(new_input_width), int(new_hidden_channels)
+
+
+class FactorizedNoisyLinear(nn.Module):
+    """Parameter / noise holder named like the reference's noisy-nets layer (GN0/models.py:84-141): `weight_mu`,
+    `weight_sigma`, `bias_mu`, `bias_sigma` parameters and `weight_epsilon`, `bias_epsilon` buffers, with the reference's
+    `reset_parameters` / `reset_noise` / `disable_noise` (called by rainbow.py:167-192).  The layer has no forward of its
+    own: the owning model composes `mu + sigma * epsilon` into the fused kernels' weight slot (hexgnn_noisy_compose) and
+    chains the gradient back (hexgnn_noisy_grads)."""
+
+    def __init__(self, in_features: int, out_features: int, sigma_0: float):
+        super().__init__()
+        if out_features != 1:
+            raise NotImplementedError("the fused path has the noisy layer on the advantage Linear(H, 1) only")
+        self.in_features, self.out_features, self.sigma_0 = in_features, out_features, sigma_0
+        self.weight_mu = nn.Parameter(torch.empty(out_features, in_features))
+        self.weight_sigma = nn.Parameter(torch.empty(out_features, in_features))
+        self.register_buffer("weight_epsilon", torch.empty(out_features, in_features))
+        self.bias_mu = nn.Parameter(torch.empty(out_features))
+        self.bias_sigma = nn.Parameter(torch.empty(out_features))
+        self.register_buffer("bias_epsilon", torch.empty(out_features))
+        # the composed weights' slots of the flat parameter buffer (derived values: neither parameters nor buffers)
+        self._w_eff = torch.zeros(out_features, in_features)
+        self._b_eff = torch.zeros(out_features)
+        self.reset_parameters()
+        self.reset_noise()
+
+    @torch.no_grad()
+    def reset_parameters(self) -> None:          # models.py:105-114
+        scale = 1 / self.in_features ** 0.5
+        nn.init.uniform_(self.weight_mu, -scale, scale)
+        nn.init.uniform_(self.bias_mu, -scale, scale)
+        nn.init.constant_(self.weight_sigma, self.sigma_0 * scale)
+        nn.init.constant_(self.bias_sigma, self.sigma_0 * scale)
+
+    @torch.no_grad()
+    def _get_noise(self, size: int):             # models.py:116-120: f(x) = sgn(x) sqrt(|x|)
+        noise = torch.randn(size, device=self.weight_mu.device)
+        return noise.sign().mul_(noise.abs().sqrt_())
+
+    @torch.no_grad()
+    def reset_noise(self) -> None:               # models.py:122-128
+        epsilon_in = self._get_noise(self.in_features)
+        epsilon_out = self._get_noise(self.out_features)
+        self.weight_epsilon.copy_(epsilon_out.outer(epsilon_in))
+        self.bias_epsilon.copy_(epsilon_out)
+
+    @torch.no_grad()
+    def disable_noise(self) -> None:             # models.py:130-133
+        self.weight_epsilon[:] = 0
+        self.bias_epsilon[:] = 0
+
+    def forward(self, input):
+        raise _lib.HexGnnError("FactorizedNoisyLinear is evaluated inside the fused kernels (call the owning model)")
 
 
 class _HeadParams(nn.Module):
     """Holder named like `HeadNetwork` (GN0/models.py:318-334): gnn, linear, value_head."""
     supports_cache = True
 
-    def __init__(self, hidden, num_layers):
+    def __init__(self, hidden, num_layers, noisy_dqn=False, noise_sigma=0.0):
         super().__init__()
         self.gnn = _SageParams(hidden, hidden, num_layers)
-        self.linear = nn.Linear(hidden, 1)
+        self.linear = FactorizedNoisyLinear(hidden, 1, noise_sigma) if noisy_dqn else nn.Linear(hidden, 1)
         self.value_head = _MLPParams(hidden // 2, 4 * hidden, 1)
         self.hidden_channels = hidden
+
+    @torch.no_grad()
+    def grow_width(self, new_width, new_in_channels=None):
+        """GN0/models.py:336-358."""
+        if not isinstance(self.linear, nn.Linear):
+            raise AssertionError("grow_width needs a plain advantage Linear (models.py:337)")
+        H = self.hidden_channels
+        self.gnn.grow_width(new_width, new_in_channels=new_in_channels)
+        old = self.linear
+        self.linear = nn.Linear(new_width, 1).to(old.weight.device)
+        self.linear.weight.zero_()
+        self.linear.weight[:, :H] = old.weight
+        self.linear.bias[:] = old.bias
+        self.value_head.grow_input_width(new_width * 4, new_width // 2)
+        self.hidden_channels = int(new_width)
+
+    def grow_depth(self, additional_layers):
+        """GN0/models.py:360-361 (train.py:306-309 grows both heads)."""
+        self.gnn.grow_depth(additional_layers)
 
 
 class _FusedQ(torch.autograd.Function):
@@ -95,6 +225,7 @@ class _FusedQ(torch.autograd.Function):
             model._flat_grad.add_(grad)
         else:
             model._point_grads()
+        model._noisy_backward(grad)
         if d_emb is not None:
             model.final_conv_grads = d_emb[:, :model.hidden_channels]
         return None, None, None, None, None
@@ -112,7 +243,8 @@ class ModernTwoHeaded(nn.Module):
     supports_cache = True  # class attribute in the reference (models.py:148,486); read at train.py:98
 
     def __init__(self, hidden_channels: int, num_layers: int, num_head_layers: int = 2, tile_rows: int = 128,
-                 strict: bool = False, path: str = "auto", max_graph_nodes: int = 0):
+                 strict: bool = False, path: str = "auto", max_graph_nodes: int = 0, noisy_dqn: bool = False,
+                 noisy_sigma0: float = 0.5):
         super().__init__()
         self.hidden_channels = int(hidden_channels)
         self.num_layers = int(num_layers)
@@ -125,8 +257,9 @@ class ModernTwoHeaded(nn.Module):
         # many nodes (board-size transfer: 13x13 -> 171, evaluate_elo.py:229-251); 0 = such graphs are flagged only
         self.max_graph_nodes = int(max_graph_nodes)
         self.gnn = _SageParams(2, hidden_channels, num_layers)
-        self.maker_head = _HeadParams(hidden_channels, num_head_layers)
-        self.breaker_head = _HeadParams(hidden_channels, num_head_layers)
+        self.noisy_dqn = bool(noisy_dqn)      # args.noisy_dqn / args.noisy_sigma0 (models.py:944-945)
+        self.maker_head = _HeadParams(hidden_channels, num_head_layers, self.noisy_dqn, noisy_sigma0)
+        self.breaker_head = _HeadParams(hidden_channels, num_head_layers, self.noisy_dqn, noisy_sigma0)
         self.after_embed_norm = None
         self.final_conv_acts = None
         self.final_conv_grads = None
@@ -138,6 +271,9 @@ class ModernTwoHeaded(nn.Module):
         self._flat_grad = None
         self._grad_views = {}
         self._p2p = None
+        self._noisy = self._noisy_grad = None
+        self._noisy_params = []
+        self._shape_sig = self._shape_signature()
         self.last_csr = None
 
     # ---- parameter order == include/hexgnn.h flat layout ---------------------------------------------
@@ -148,8 +284,8 @@ class ModernTwoHeaded(nn.Module):
         for head in (self.maker_head, self.breaker_head):
             for c in head.gnn.convs:
                 ps += [c.lin_l.weight, c.lin_l.bias, c.lin_r.weight]
-            ps += [head.linear.weight, head.linear.bias,
-                   head.value_head.layers[0].weight, head.value_head.layers[0].bias,
+            ps += [head.linear._w_eff, head.linear._b_eff] if self.noisy_dqn else [head.linear.weight, head.linear.bias]
+            ps += [head.value_head.layers[0].weight, head.value_head.layers[0].bias,
                    head.value_head.layers[1].weight, head.value_head.layers[1].bias]
         return ps
 
@@ -178,8 +314,41 @@ class ModernTwoHeaded(nn.Module):
         self._flat_grad = None
         self._grad_views = {}
         self._params_cache = ps
+        self._noisy = self._noisy_grad = None
+        self._noisy_params = []
+        if self.noisy_dqn:
+            # mu / sigma / epsilon of both heads in one [2, 3, H+1] buffer (weight row, then the bias): the C-ABI's `noisy`
+            H = self.hidden_channels
+            nz = torch.empty(2, 3, H + 1, dtype=torch.float32, device=dev)
+            with torch.no_grad():
+                for h, head in enumerate((self.maker_head, self.breaker_head)):
+                    lin = head.linear
+                    for r, (w, b) in enumerate(((lin.weight_mu, lin.bias_mu), (lin.weight_sigma, lin.bias_sigma),
+                                                (lin.weight_epsilon, lin.bias_epsilon))):
+                        nz[h, r, :H].copy_(w.detach().reshape(-1))
+                        nz[h, r, H:].copy_(b.detach().reshape(-1))
+                        w.data = nz[h, r, :H].view(1, H)
+                        b.data = nz[h, r, H:]
+                    self._noisy_params += [(lin.weight_mu, h, 0, True), (lin.bias_mu, h, 0, False),
+                                           (lin.weight_sigma, h, 1, True), (lin.bias_sigma, h, 1, False)]
+            self._noisy = nz
+
+    def _shape_signature(self):
+        return (self.gnn.hidden_channels, len(self.gnn.convs), len(self.maker_head.gnn.convs),
+                len(self.breaker_head.gnn.convs), self.maker_head.hidden_channels, self.breaker_head.hidden_channels)
 
     def _ensure_flat(self):
+        sig = self._shape_signature()
+        if sig != self._shape_sig:
+            # grow_width / grow_depth changed the architecture (GN0/models.py:494-508, train.py:301-309)
+            H, L, Lm, Lb, Hm, Hb = sig
+            if Lm != Lb or Hm != H or Hb != H:
+                raise _lib.HexGnnError(f"maker / breaker heads differ in shape ({Lm} vs {Lb} layers, widths {H}/{Hm}/{Hb}): "
+                                       "grow both before the next forward")
+            self.hidden_channels, self.num_layers, self.num_head_layers = H, L, Lm
+            self._desc = _lib.make_desc(H, L, Lm)
+            self._shape_sig = sig
+            self._flat = None
         if self._flat is None or self._flat.device != self.gnn.convs[0].lin_l.weight.device:
             self._flatten()
 
@@ -215,8 +384,11 @@ class ModernTwoHeaded(nn.Module):
         if self._flat_grad is None:
             return False
         base = self._flat_grad.data_ptr()
-        n_set = 0
+        n_set = n_skip = 0
         for p, (o, n, _) in zip(self._params_cache, self._slices):
+            if not p.requires_grad:     # frozen, or the composed noisy weights (a derived slot, not a parameter)
+                n_skip += 1
+                continue
             g = p.grad
             if g is None:
                 continue
@@ -226,9 +398,9 @@ class ModernTwoHeaded(nn.Module):
             n_set += 1
         if n_set == 0:
             return False
-        if n_set != len(self._slices):
+        if n_set != len(self._slices) - n_skip:
             for p, (o, n, _) in zip(self._params_cache, self._slices):
-                if p.grad is None:
+                if p.grad is None and p.requires_grad:
                     self._flat_grad[o:o + n].zero_()
         self._point_grads()
         return True
@@ -256,10 +428,36 @@ class ModernTwoHeaded(nn.Module):
         if set_to_none:
             for p in self._params_cache:
                 p.grad = None
+            for p, *_ in self._noisy_params:
+                p.grad = None
         elif self._grads_in_place():
             self._flat_grad.zero_()
+            if self._noisy_grad is not None:
+                self._noisy_grad.zero_()
         else:
             super().zero_grad(set_to_none=False)
+
+    # ---- noisy-nets advantage layer (`noisy_dqn=True`): compose in front of the kernels, chain rule behind them -------
+    def _compose_noisy(self):
+        if self.noisy_dqn:
+            ops.noisy_compose(self._desc, self._flat, self._noisy)
+
+    def _noisy_backward(self, grad):
+        """d_mu = g, d_sigma = g * epsilon from this backward's flat gradient; `+=` when the noisy parameters' .grad still
+        are our views (a second backward before the optimizer step), like autograd."""
+        if not self.noisy_dqn:
+            return
+        H = self.hidden_channels
+        if self._noisy_grad is None or self._noisy_grad.device != self._noisy.device:
+            self._noisy_grad = torch.zeros(2, 2, H + 1, dtype=torch.float32, device=self._noisy.device)
+            self._noisy_views = [self._noisy_grad[h, r, :H].view(1, H) if is_w else self._noisy_grad[h, r, H:]
+                                 for (_, h, r, is_w) in self._noisy_params]
+        views = self._noisy_views
+        acc = all(p.grad is not None and p.grad.data_ptr() == v.data_ptr() for (p, *_), v in zip(self._noisy_params, views))
+        ops.noisy_grads(self._desc, grad, self._noisy, self._noisy_grad, acc)
+        for (p, *_), v in zip(self._noisy_params, views):
+            if p.requires_grad:
+                p.grad = v
 
     @property
     def flat_gradient(self):
@@ -349,6 +547,7 @@ class ModernTwoHeaded(nn.Module):
                 set_cache: bool = False, advantages_only=False, seperate=False, num_graphs: Optional[int] = None,
                 csr: Optional[ops.CsrBlob] = None):
         self._ensure_flat()
+        self._compose_noisy()
         if csr is None:
             csr = self.build_csr(edge_index, graph_indices, ptr, num_nodes=int(x.shape[0]), num_graphs=num_graphs)
         flags = 0
@@ -391,6 +590,7 @@ class ModernTwoHeaded(nn.Module):
         if ptr is None or action is None or target is None:
             raise _lib.HexGnnError("train_step: ptr, action and target are required")
         self._ensure_flat()
+        self._compose_noisy()
         if csr is None:
             csr = self.build_csr(edge_index, graph_indices, ptr, num_nodes=int(x.shape[0]), num_graphs=num_graphs)
         self.last_csr = csr
@@ -403,6 +603,7 @@ class ModernTwoHeaded(nn.Module):
             self._flat_grad.add_(grad)
         else:
             self._point_grads()
+        self._noisy_backward(grad)
         if self.strict:
             csr.raise_on_error()
         return loss, td_err, q
@@ -416,6 +617,10 @@ class ModernTwoHeaded(nn.Module):
         if other._flat.numel() != self._flat.numel():
             raise _lib.HexGnnError("copy_parameters_from: different architectures")
         self._flat.copy_(other._flat, non_blocking=True)
+        if self.noisy_dqn != other.noisy_dqn:
+            raise _lib.HexGnnError("copy_parameters_from: noisy_dqn differs")
+        if self.noisy_dqn:
+            self._noisy.copy_(other._noisy, non_blocking=True)   # mu, sigma and the epsilon buffers (state_dict has all three)
 
     def simple_forward(self, data):
         if getattr(data, "batch", None) is not None:
@@ -429,10 +634,16 @@ class ModernTwoHeaded(nn.Module):
     def import_norm_cache(self, *args):
         return None
 
-    def grow_width(self, *a, **k):
-        raise NotImplementedError("grow_width/grow_depth (GN0/models.py:494-508) are outside the fused path")
+    def grow_depth(self, additional_layers):
+        """GN0/models.py:494-495 (train.py:302,304): more body layers, function unchanged.  The fused kernels pick the new
+        shape up at the next call (`_ensure_flat` re-reads the module structure)."""
+        self.gnn.grow_depth(additional_layers)
 
-    grow_depth = grow_width
+    def grow_width(self, new_width):
+        """GN0/models.py:497-508 (train.py:301,303): wider body and heads."""
+        self.gnn.grow_width(new_width)
+        self.maker_head.grow_width(new_width, new_in_channels=new_width)
+        self.breaker_head.grow_width(new_width, new_in_channels=new_width)
 
 
 class FusedAdam:
@@ -457,6 +668,9 @@ class FusedAdam:
     def _ensure(self):
         m = self.model
         m._ensure_flat()
+        if m.noisy_dqn:
+            raise NotImplementedError("FusedAdam steps the flat parameter buffer; with noisy_dqn=True the advantage layer's "
+                                      "mu / sigma live outside it: use torch.optim.Adam(model.parameters())")
         if self._version != m._flat_version or self.exp_avg is None or self.exp_avg.device != m._flat.device:
             old = (self.exp_avg, self.exp_avg_sq, self.state)
             self.exp_avg = torch.zeros_like(m._flat)
@@ -494,7 +708,9 @@ def get_pre_defined(name, args=None):
     """`GN0/models.py:892` for the one name this package implements."""
     if name != "modern_two_headed":
         raise NotImplementedError(f"gnn_hex_b200 implements only 'modern_two_headed', not {name!r}")
-    if getattr(args, "norm", False) or getattr(args, "noisy_dqn", False):
-        raise NotImplementedError("norm=True / noisy_dqn=True are not on the fused path (SURVEY.md §8 f4)")
+    if getattr(args, "norm", False):
+        raise NotImplementedError("norm=True (PyG LayerNorm over the whole batch) is not on the fused path (SURVEY.md §8 f4)")
     return ModernTwoHeaded(args.hidden_channels, args.num_layers,
-                           args.num_head_layers if hasattr(args, "num_head_layers") else 2)
+                           args.num_head_layers if hasattr(args, "num_head_layers") else 2,
+                           noisy_dqn=bool(getattr(args, "noisy_dqn", False)),
+                           noisy_sigma0=float(getattr(args, "noisy_sigma0", 0.5)))

@@ -10,7 +10,7 @@ from ._lib import HEXGNN_ADV_ONLY, HEXGNN_SEPARATE, HEXGNN_PATH_SIMT, HEXGNN_PAT
 
 # kernels launched by each C-ABI call (csr: init, hist, scan, fill, sort; forward: pack, fused;
 # backward: pack, fused, reduce, unpack) -- bench.py's `gpu_launches` is read off this counter.
-LAUNCHES = {"build_csr": 5, "forward": 2, "backward": 5, "td_loss": 1, "train_step": 6, "adam_step": 2, "mask_argmax": 1, "td_target": 1, "forward_big": 0, "allreduce_p2p": 1}
+LAUNCHES = {"build_csr": 5, "forward": 2, "backward": 5, "td_loss": 1, "train_step": 6, "adam_step": 2, "mask_argmax": 1, "td_target": 1, "forward_big": 0, "allreduce_p2p": 1, "noisy": 1}
 launch_counter = 0
 
 
@@ -341,3 +341,29 @@ def adam_step(desc, flat_params, flat_grad, exp_avg, exp_avg_sq, state, x, lr, b
     _lib.check(rc, "hexgnn_adam_step")
     _count("adam_step")
     return grad_norm_out.reshape(())
+
+
+def noisy_compose(desc, flat_params, noisy):
+    """hexgnn_noisy_compose: write `mu + sigma * epsilon` of both heads' FactorizedNoisyLinear (GN0/models.py:134-141) into
+    the advantage-Linear slots of the flat parameter buffer.  noisy: [2, 3, H+1] f32 CUDA."""
+    _require_cuda(flat_params, "parameters")
+    _require_cuda(noisy, "noisy")
+    if noisy.dtype != torch.float32 or not noisy.is_contiguous() or noisy.numel() != 6 * (desc.hidden + 1):
+        raise _lib.HexGnnError("noisy_compose: noisy must be a contiguous float32 [2, 3, hidden + 1] tensor")
+    _lib.check(_lib.lib().hexgnn_noisy_compose(C.byref(desc), _ptr(flat_params), _ptr(noisy), _stream(flat_params.device)),
+               "hexgnn_noisy_compose")
+    _count("noisy")
+
+
+def noisy_grads(desc, flat_grad, noisy, d_noisy, accumulate):
+    """hexgnn_noisy_grads: d_mu = g, d_sigma = g * epsilon from the composed weights' slice of the flat gradient.
+    d_noisy: [2, 2, H+1] f32 CUDA, overwritten or (accumulate) added to."""
+    for t, name in ((flat_grad, "gradient"), (noisy, "noisy"), (d_noisy, "d_noisy")):
+        _require_cuda(t, name)
+        if t.dtype != torch.float32 or not t.is_contiguous():
+            raise _lib.HexGnnError(f"noisy_grads: {name} must be contiguous float32")
+    if noisy.numel() != 6 * (desc.hidden + 1) or d_noisy.numel() != 4 * (desc.hidden + 1):
+        raise _lib.HexGnnError("noisy_grads: noisy is [2, 3, hidden + 1], d_noisy is [2, 2, hidden + 1]")
+    _lib.check(_lib.lib().hexgnn_noisy_grads(C.byref(desc), _ptr(flat_grad), _ptr(noisy), _ptr(d_noisy),
+                                             1 if accumulate else 0, _stream(flat_grad.device)), "hexgnn_noisy_grads")
+    _count("noisy")

@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define HEXGNN_ABI_VERSION 5
+#define HEXGNN_ABI_VERSION 6
 
 enum {
   HEXGNN_OK = 0,
@@ -191,6 +191,18 @@ int64_t hexgnn_adam_ws_bytes(void);
 int hexgnn_adam_step(const HexModelDesc* desc, float* params, float* grads, float* exp_avg, float* exp_avg_sq,
                      int32_t* state, const float* x, float lr, float beta1, float beta2, float eps, float max_grad_norm,
                      int32_t flags, float* grad_norm, void* ws, size_t ws_bytes, void* stream);
+
+/* FactorizedNoisyLinear on the advantage Linear(H,1) of both heads, `--noisy_dqn=True` (GN0/models.py:84-141 the layer,
+ * :331-334 HeadNetwork uses it for `self.linear`, :944-945 factory arguments; Rainbow resets / disables the noise at
+ * rainbow.py:167-192).  The fused kernels read the advantage weights from the flat parameter buffer, so:
+ *   hexgnn_noisy_compose: params[linear.W | linear.b of head h] = mu + sigma * epsilon            (models.py:134-141)
+ *   hexgnn_noisy_grads:   d_mu = g, d_sigma = g * epsilon, g = the composed weights' slice of the flat gradient `grads`;
+ *                         accumulate != 0 adds into d_noisy (autograd `+=`), else overwrites.
+ * noisy [2][3][H+1] f32: per head (maker, breaker) the rows mu, sigma, epsilon, each = weight[H] then the bias;
+ * d_noisy [2][2][H+1]: per head the rows d_mu, d_sigma.  One launch each, element-wise, deterministic. */
+int hexgnn_noisy_compose(const HexModelDesc* desc, float* params, const float* noisy, void* stream);
+int hexgnn_noisy_grads(const HexModelDesc* desc, const float* grads, const float* noisy, float* d_noisy, int32_t accumulate,
+                       void* stream);
 
 /* Learner loss glue on device (replaces the index / loss / mean kernels of rainbow.py:301-312 and their autograd):
  *   td_est[g] = q[ptr[g] + action[g]];  td_err[g] = td_est[g] - target[g]  (PER priorities = |td_err| + 1e-6, :307-308)

@@ -250,6 +250,53 @@ class _SageStack(torch.nn.Module):
             x = F.relu(sage_conv(x, edge_index, c.lin_l.weight, c.lin_l.bias, c.lin_r.weight))
         return x
 
+    @staticmethod
+    def _new_conv(cin, cout):
+        c = torch.nn.Module()
+        c.lin_l = torch.nn.Linear(cin, cout, bias=True)
+        c.lin_r = torch.nn.Linear(cin, cout, bias=False)
+        return c
+
+    def grow_depth(self, additional_layers):
+        """GN0/models.py:166-185: identity layers (lin_l weight and bias 0, lin_r = eye)."""
+        for _ in range(additional_layers):
+            c = self._new_conv(self.hidden_channels, self.hidden_channels)
+            c.lin_l.weight.data[:] = 0
+            c.lin_l.bias.data[:] = 0
+            c.lin_r.weight.data[:] = torch.eye(self.hidden_channels)
+            self.convs.append(c)
+        self.num_layers += additional_layers
+
+    def grow_width(self, new_width, new_in_channels=None):
+        """GN0/models.py:187-238 (has_output False, no norms)."""
+        old_convs, h = self.convs, self.hidden_channels
+        in_channels = self.convs[0].lin_l.weight.shape[1]
+        old_in_channels = in_channels
+        if new_in_channels is not None:
+            in_channels = new_in_channels
+        self.convs = torch.nn.ModuleList()
+        self.convs.append(self._new_conv(in_channels, new_width))                       # :197
+        for _ in range(self.num_layers - 2):                                           # :198-199
+            self.convs.append(self._new_conv(new_width, new_width))
+        self.convs.append(self._new_conv(new_width, new_width))                        # :205-206
+        for i, (conv, old_conv) in enumerate(zip(self.convs, old_convs)):              # :207-224
+            if i == 0:
+                if new_in_channels is None:
+                    conv.lin_l.weight.data[:h, :] = old_conv.lin_l.weight.data
+                    conv.lin_r.weight.data[:h, :] = old_conv.lin_r.weight.data
+                else:
+                    conv.lin_l.weight.data[:h, :old_in_channels] = old_conv.lin_l.weight.data
+                    conv.lin_r.weight.data[:h, :old_in_channels] = old_conv.lin_r.weight.data
+                    conv.lin_l.weight.data[:h, old_in_channels:] = 0
+                    conv.lin_r.weight.data[:h, old_in_channels:] = 0
+            else:
+                conv.lin_l.weight.data[:h, :h] = old_conv.lin_l.weight.data
+                conv.lin_r.weight.data[:h, :h] = old_conv.lin_r.weight.data
+                conv.lin_l.weight.data[:h, h:] = 0
+                conv.lin_r.weight.data[:h, h:] = 0
+            conv.lin_l.bias.data[:h] = old_conv.lin_l.bias.data
+        self.hidden_channels = new_width
+
 
 class _MLP(torch.nn.Module):
     """GN0/models.py:36-49,75-82 with num_hidden_layers=1, no output activation."""
@@ -258,19 +305,94 @@ class _MLP(torch.nn.Module):
         super().__init__()
         self.layers = torch.nn.ModuleList([torch.nn.Linear(num_input, hidden), torch.nn.Linear(hidden, num_output)])
 
+        self.hidden_channels, self.num_input = hidden, num_input
+
     def forward(self, x):
         return self.layers[1](F.relu(self.layers[0](x)))
+
+    def grow_input_width(self, new_input_width, new_hidden_channels):
+        """GN0/models.py:52-73 (the middle loop runs zero times for two layers)."""
+        old_layer = self.layers[0]
+        self.layers[0] = torch.nn.Linear(new_input_width, new_hidden_channels)
+        self.layers[0].weight.data.fill_(0)
+        self.layers[0].bias.data.fill_(0)
+        self.layers[0].weight.data[:self.hidden_channels, :self.num_input] = old_layer.weight.data
+        self.layers[0].bias.data[:self.hidden_channels] = old_layer.bias.data[:]
+        old_layer = self.layers[-1]
+        self.layers[-1] = torch.nn.Linear(new_hidden_channels, 1)
+        self.layers[-1].weight.data.fill_(0)
+        self.layers[-1].weight.data[:, :self.hidden_channels] = old_layer.weight.data
+        self.layers[-1].bias.data[:] = old_layer.bias.data[:]
+        self.num_input = new_input_width
+        self.hidden_channels = new_hidden_channels
+
+
+class NoisyLinearOracle(torch.nn.Module):
+    """``FactorizedNoisyLinear`` (GN0/models.py:84-141): w = mu_w + sigma_w * eps_w, b = mu_b + sigma_b * eps_b with
+    factorised noise eps_w = f(eps_out) f(eps_in)^T, eps_b = f(eps_out), f(x) = sgn(x) sqrt(|x|)."""
+
+    def __init__(self, in_features: int, out_features: int, sigma_0: float):
+        super().__init__()
+        self.in_features, self.out_features, self.sigma_0 = in_features, out_features, sigma_0
+        self.weight_mu = torch.nn.Parameter(torch.empty(out_features, in_features))
+        self.weight_sigma = torch.nn.Parameter(torch.empty(out_features, in_features))
+        self.register_buffer('weight_epsilon', torch.empty(out_features, in_features))
+        self.bias_mu = torch.nn.Parameter(torch.empty(out_features))
+        self.bias_sigma = torch.nn.Parameter(torch.empty(out_features))
+        self.register_buffer('bias_epsilon', torch.empty(out_features))
+        with torch.no_grad():
+            scale = 1 / math.sqrt(in_features)                                         # :105-114
+            self.weight_mu.uniform_(-scale, scale)
+            self.bias_mu.uniform_(-scale, scale)
+            self.weight_sigma.fill_(sigma_0 * scale)
+            self.bias_sigma.fill_(sigma_0 * scale)
+        self.reset_noise()
+
+    @torch.no_grad()
+    def reset_noise(self):                                                             # :116-128
+        def f(size):
+            noise = torch.randn(size)
+            return noise.sign() * noise.abs().sqrt()
+        eps_in = f(self.in_features)
+        eps_out = f(self.out_features)
+        self.weight_epsilon.copy_(eps_out.outer(eps_in))
+        self.bias_epsilon.copy_(eps_out)
+
+    @torch.no_grad()
+    def disable_noise(self):                                                           # :130-133
+        self.weight_epsilon[:] = 0
+        self.bias_epsilon[:] = 0
+
+    def forward(self, x):                                                              # :135-141
+        return F.linear(x, self.weight_mu + self.weight_sigma * self.weight_epsilon,
+                        self.bias_mu + self.bias_sigma * self.bias_epsilon)
 
 
 class _Head(torch.nn.Module):
     """``HeadNetwork`` (GN0/models.py:318-334,368-384) with value_head_type='mlp',
-    value_aggr_types=('sum','max','min','mean'), noisy_dqn=False."""
+    value_aggr_types=('sum','max','min','mean'); ``noisy_dqn`` swaps the advantage Linear (:331-334)."""
 
-    def __init__(self, hidden: int, num_layers: int):
+    def __init__(self, hidden: int, num_layers: int, noisy_dqn: bool = False, noise_sigma: float = 0.0):
         super().__init__()
         self.gnn = _SageStack(hidden, hidden, num_layers)
-        self.linear = torch.nn.Linear(hidden, 1)
+        self.linear = NoisyLinearOracle(hidden, 1, noise_sigma) if noisy_dqn else torch.nn.Linear(hidden, 1)
         self.value_head = _MLP(hidden // 2, 4 * hidden, 1)
+        self.hidden_channels = hidden
+
+    def grow_width(self, new_width, new_in_channels=None):
+        """GN0/models.py:336-358."""
+        assert isinstance(self.linear, torch.nn.Linear)
+        self.gnn.grow_width(new_width, new_in_channels=new_in_channels)
+        old_linear = self.linear
+        self.linear = torch.nn.Linear(new_width, 1)
+        self.linear.weight.data.fill_(0)
+        self.linear.weight.data[:, :self.hidden_channels] = old_linear.weight.data
+        self.linear.bias.data[:] = old_linear.bias.data[:]
+        self.value_head.grow_input_width(new_width * 4, new_width // 2)
+        self.hidden_channels = new_width
+
+    def grow_depth(self, additional_layers):
+        self.gnn.grow_depth(additional_layers)
 
     def forward(self, x, edge_index, graph_indices, num_graphs, advantages_only=False):
         x = self.gnn(x, edge_index)
@@ -286,12 +408,21 @@ class ModernTwoHeadedOracle(torch.nn.Module):
     (GN0/models.py:928-947 -> DuellingTwoHeaded :477-590).  Parameter names follow PyG 2.2.0 /
     the reference attribute accesses so state_dicts interchange with the product module."""
 
-    def __init__(self, hidden_channels: int, num_layers: int, num_head_layers: int = 2):
+    def __init__(self, hidden_channels: int, num_layers: int, num_head_layers: int = 2, noisy_dqn: bool = False,
+                 noisy_sigma0: float = 0.5):
         super().__init__()
         self.gnn = _SageStack(2, hidden_channels, num_layers)
-        self.maker_head = _Head(hidden_channels, num_head_layers)
-        self.breaker_head = _Head(hidden_channels, num_head_layers)
+        self.maker_head = _Head(hidden_channels, num_head_layers, noisy_dqn, noisy_sigma0)
+        self.breaker_head = _Head(hidden_channels, num_head_layers, noisy_dqn, noisy_sigma0)
         self.final_conv_acts = None
+
+    def grow_depth(self, additional_layers):                                   # models.py:494-495
+        self.gnn.grow_depth(additional_layers)
+
+    def grow_width(self, new_width):                                           # models.py:497-508 (no norm)
+        self.gnn.grow_width(new_width)
+        self.maker_head.grow_width(new_width, new_in_channels=new_width)
+        self.breaker_head.grow_width(new_width, new_in_channels=new_width)
 
     def forward(self, x, edge_index, graph_indices=None, ptr=None, set_cache=False,
                 advantages_only=False, seperate=False):

@@ -16,11 +16,11 @@ ROUNDOFF_FACTOR = 16.0
 PER_TENSOR_TOL = 4e-5
 
 
-def make_pair(hidden, layers, head_layers=2, seed=0, dtype=torch.float32):
+def make_pair(hidden, layers, head_layers=2, seed=0, dtype=torch.float32, noisy_dqn=False, noisy_sigma0=0.5):
     """Oracle + product module with identical weights (default torch init, seeded)."""
     torch.manual_seed(seed)
-    o = orc.ModernTwoHeadedOracle(hidden, layers, head_layers)
-    m = ModernTwoHeaded(hidden, layers, head_layers)
+    o = orc.ModernTwoHeadedOracle(hidden, layers, head_layers, noisy_dqn=noisy_dqn, noisy_sigma0=noisy_sigma0)
+    m = ModernTwoHeaded(hidden, layers, head_layers, noisy_dqn=noisy_dqn, noisy_sigma0=noisy_sigma0)
     m.load_state_dict(o.state_dict())
     if dtype != torch.float32:
         o = o.to(dtype)
@@ -49,7 +49,8 @@ def rel_err(a, b):
 def oracle64(o):
     """fp64 copy of an oracle module: the arbiter of fp32 round-off."""
     h = o.gnn.hidden_channels
-    o64 = orc.ModernTwoHeadedOracle(h, o.gnn.num_layers, o.maker_head.gnn.num_layers).double()
+    noisy = isinstance(o.maker_head.linear, orc.NoisyLinearOracle)
+    o64 = orc.ModernTwoHeadedOracle(h, o.gnn.num_layers, o.maker_head.gnn.num_layers, noisy_dqn=noisy).double()
     o64.load_state_dict({k: v.double() for k, v in o.state_dict().items()})
     return o64
 

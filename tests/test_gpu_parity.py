@@ -489,3 +489,126 @@ def test_train_step_batch_extremes(count):
         assert torch.equal(q, q_ref.detach()) and torch.equal(m.flat_gradient, g_ref)
         assert abs(float(loss) - float(loss_ref)) <= 1e-5 * max(abs(float(loss_ref)), 1e-3)
     assert torch.isfinite(g_ref).all() and float(g_ref.abs().max()) > 0
+
+
+def _loss_backward_pair(o, m, b, maker_unused=None):
+    """Same rainbow loss through the oracle (fp32 + fp64) and the product module; returns (o64, loss, loss_ref)."""
+    d = b.to(DEV)
+    action, target, weight = loss_inputs(b)
+    loss_ref = orc.rainbow_loss(o(b.x, b.edge_index, b.batch, b.ptr), b.ptr, action, target, weight)
+    loss_ref.backward()
+    o64 = oracle64(o)
+    orc.rainbow_loss(o64(b.x.double(), b.edge_index, b.batch, b.ptr), b.ptr, action, target.double(),
+                     weight.double()).backward()
+    q = m(d.x, d.edge_index, d.batch, d.ptr)
+    loss = orc.rainbow_loss(q, d.ptr, action.to(DEV), target.to(DEV), weight.to(DEV))
+    loss.backward()
+    return o64, loss, loss_ref
+
+
+@pytest.mark.parametrize("maker", [1, 0])
+def test_noisy_dqn_forward_backward_parity(maker):
+    """`--noisy_dqn=True` (models.py:84-141,331-334): composed advantage weights in front of the fused kernels, d_mu / d_sigma
+    behind them; reset_noise / disable_noise (rainbow.py:167-192) take effect at the next call."""
+    o, m = make_pair(35, 10, noisy_dqn=True)
+    m = m.to(DEV)
+    b = _batch(CONFIGS["S"], "play", maker, 48)
+    d = b.to(DEV)
+    with torch.no_grad():
+        q_ref = o(b.x, b.edge_index, b.batch, b.ptr)
+        a_ref = o(b.x, b.edge_index, b.batch, advantages_only=True)
+        q = m(d.x, d.edge_index, d.batch, d.ptr)
+        a = m(d.x, d.edge_index, d.batch, d.ptr, advantages_only=True)
+    assert rel_err(q, q_ref) <= REL_TOL and rel_err(a, a_ref) <= REL_TOL
+    o64, loss, loss_ref = _loss_backward_pair(o, m, b)
+    assert rel_err(loss, loss_ref) <= REL_TOL
+    glob, worst, wname = grad_errs(m, o, o64)
+    assert glob <= REL_TOL, glob
+    assert worst <= 1.0, (worst, wname)
+    head = m.maker_head if maker == 1 else m.breaker_head
+    head_o = o.maker_head if maker == 1 else o.breaker_head
+    assert float(head.linear.weight_sigma.grad.abs().max()) > 0
+    # d_sigma = d_mu * epsilon exactly (one fp32 product)
+    assert torch.equal(head.linear.weight_sigma.grad, head.linear.weight_mu.grad * head.linear.weight_epsilon)
+    # a second backward without zero_grad accumulates, like autograd
+    g1 = head.linear.weight_sigma.grad.clone()
+    b1 = head.gnn.convs[0].lin_l.weight.grad.clone()
+    action, target, weight = loss_inputs(b)
+    orc.rainbow_loss(m(d.x, d.edge_index, d.batch, d.ptr), d.ptr, action.to(DEV), target.to(DEV), weight.to(DEV)).backward()
+    assert torch.allclose(head.linear.weight_sigma.grad, 2 * g1, rtol=1e-6, atol=0)
+    assert torch.allclose(head.gnn.convs[0].lin_l.weight.grad, 2 * b1, rtol=1e-6, atol=0)
+    m.zero_grad()
+    assert head.linear.weight_sigma.grad is None and head.linear.bias_mu.grad is None
+    # train_step == the autograd route, bit for bit, noisy parameters included
+    m.zero_grad()
+    ops.td_loss(m(d.x, d.edge_index, d.batch, d.ptr), d.ptr, action.to(DEV), target.to(DEV), weight.to(DEV))[0].backward()
+    want = {k: p.grad.clone() for k, p in m.named_parameters()}
+    m.zero_grad()
+    m.train_step(d.x, d.edge_index, d.batch, d.ptr, action=action.to(DEV), target=target.to(DEV), weight=weight.to(DEV))
+    for k, p in m.named_parameters():
+        assert torch.equal(p.grad, want[k]), k
+    # new noise -> different advantages, still equal to the oracle with the same noise; no noise -> plain mu
+    torch.manual_seed(9)
+    head.linear.reset_noise()
+    head_o.linear.weight_epsilon.copy_(head.linear.weight_epsilon.cpu())
+    head_o.linear.bias_epsilon.copy_(head.linear.bias_epsilon.cpu())
+    with torch.no_grad():
+        a2 = m(d.x, d.edge_index, d.batch, d.ptr, advantages_only=True)
+        assert rel_err(a2, o(b.x, b.edge_index, b.batch, advantages_only=True)) <= REL_TOL
+        assert not torch.equal(a2, a)
+        head.linear.disable_noise()
+        head_o.linear.disable_noise()
+        a3 = m(d.x, d.edge_index, d.batch, d.ptr, advantages_only=True)
+        assert rel_err(a3, o(b.x, b.edge_index, b.batch, advantages_only=True)) <= REL_TOL
+    # target-network sync carries mu, sigma and the noise (state_dict has all three, rainbow.py:163-164)
+    _, t = make_pair(35, 10, seed=3, noisy_dqn=True)
+    t = t.to(DEV)
+    t.copy_parameters_from(m)
+    with torch.no_grad():
+        assert torch.equal(t(d.x, d.edge_index, d.batch, d.ptr, advantages_only=True), a3)
+    # the flat-buffer optimizer does not cover mu / sigma: it must say so, torch.optim.Adam works on the named parameters
+    from gnn_hex_b200 import FusedAdam
+    with pytest.raises(NotImplementedError):
+        FusedAdam(m).step(d.x)
+    opt = torch.optim.Adam(m.parameters(), lr=1e-3)
+    m.zero_grad()
+    m.train_step(d.x, d.edge_index, d.batch, d.ptr, action=action.to(DEV), target=target.to(DEV), weight=weight.to(DEV))
+    mu0 = head.linear.weight_mu.detach().clone()
+    opt.step()
+    assert not torch.equal(head.linear.weight_mu.detach(), mu0)
+
+
+def test_grown_model_parity():
+    """grow_depth / grow_width (models.py:166-238,336-361,494-508; train.py:301-309): the fused path follows the new shape."""
+    o, m = make_pair(20, 4)
+    m = m.to(DEV)
+    b = _batch(CONFIGS["S"], "play", 1, 40)
+    d = b.to(DEV)
+    with torch.no_grad():
+        q0 = m(d.x, d.edge_index, d.batch, d.ptr)
+    torch.manual_seed(21)
+    o.grow_depth(2)
+    m.grow_depth(2)
+    with torch.no_grad():
+        q1 = m(d.x, d.edge_index, d.batch, d.ptr)
+    assert rel_err(q1, q0) <= REL_TOL                      # identity layers: same function
+    torch.manual_seed(22)
+    o.grow_width(35)
+    o.maker_head.grow_depth(1); o.breaker_head.grow_depth(1)
+    torch.manual_seed(22)
+    m.grow_width(35)
+    m.maker_head.grow_depth(1)
+    with pytest.raises(_lib.HexGnnError):                  # heads of different depth: refused, not silently wrong
+        m(d.x, d.edge_index, d.batch, d.ptr)
+    m.breaker_head.grow_depth(1)
+    m.load_state_dict(o.state_dict())                      # (grow_width draws on the device RNG here, on the CPU there)
+    with torch.no_grad():
+        q_ref = o(b.x, b.edge_index, b.batch, b.ptr)
+        q2 = m(d.x, d.edge_index, d.batch, d.ptr)
+    assert (m.hidden_channels, m.num_layers, m.num_head_layers) == (35, 6, 3)
+    assert rel_err(q2, q_ref) <= REL_TOL
+    o64, loss, loss_ref = _loss_backward_pair(o, m, b)
+    assert rel_err(loss, loss_ref) <= REL_TOL
+    glob, worst, wname = grad_errs(m, o, o64)
+    assert glob <= REL_TOL, glob
+    assert worst <= 1.0, (worst, wname)

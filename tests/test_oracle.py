@@ -153,3 +153,88 @@ def test_csr_by_destination_is_stable():
 def test_flops_formula_matches_survey():
     assert orc.flops_forward(1, 0, 110, 15, advantages_only=True) == 775500
     assert orc.flops_forward(1, 0, 35, 10, advantages_only=True) == 54250
+
+
+def test_noisy_linear_known_answer():
+    """FactorizedNoisyLinear (GN0/models.py:84-141): init constants, factorised noise, w = mu + sigma * eps."""
+    torch.manual_seed(4)
+    l = orc.NoisyLinearOracle(9, 1, 0.5)
+    scale = 1 / 3.0
+    assert float(l.weight_mu.abs().max()) <= scale and torch.all(l.weight_sigma == 0.5 * scale) and torch.all(l.bias_sigma == 0.5 * scale)
+    # factorised: weight_epsilon = eps_out (x) eps_in with eps_out = bias_epsilon, and |f(x)| = sqrt|x|
+    eps_in = l.weight_epsilon[0] / l.bias_epsilon[0]
+    torch.manual_seed(11)
+    l.reset_noise()
+    torch.manual_seed(11)
+    n_in, n_out = torch.randn(9), torch.randn(1)
+    f = lambda v: v.sign() * v.abs().sqrt()
+    assert torch.equal(l.bias_epsilon, f(n_out)) and torch.equal(l.weight_epsilon, f(n_out).outer(f(n_in)))
+    x = torch.arange(18, dtype=torch.float32).reshape(2, 9) / 7
+    want = x @ (l.weight_mu + l.weight_sigma * l.weight_epsilon).t() + (l.bias_mu + l.bias_sigma * l.bias_epsilon)
+    assert torch.allclose(l(x), want, atol=1e-7)
+    l.disable_noise()
+    assert torch.allclose(l(x), x @ l.weight_mu.t() + l.bias_mu, atol=1e-7)
+    del eps_in
+
+
+def test_noisy_model_names_and_product_holder():
+    """`noisy_dqn=True` swaps only the advantage Linear (models.py:331-334); names interchange with the product module."""
+    from gnn_hex_b200 import ModernTwoHeaded, get_pre_defined
+    from types import SimpleNamespace
+    torch.manual_seed(0)
+    o = orc.ModernTwoHeadedOracle(12, 3, 2, noisy_dqn=True, noisy_sigma0=0.5)
+    m = get_pre_defined("modern_two_headed", SimpleNamespace(hidden_channels=12, num_layers=3, num_head_layers=2, norm=False,
+                                                             noisy_dqn=True, noisy_sigma0=0.5))
+    assert isinstance(m, ModernTwoHeaded) and m.noisy_dqn
+    assert list(o.state_dict().keys()) == list(m.state_dict().keys())
+    assert "maker_head.linear.weight_mu" in m.state_dict() and "breaker_head.linear.bias_epsilon" in m.state_dict()
+    assert "maker_head.linear.weight" not in m.state_dict()
+    m.load_state_dict(o.state_dict())
+    lin = m.maker_head.linear
+    torch.manual_seed(5)
+    lin.reset_noise()
+    torch.manual_seed(5)
+    o.maker_head.linear.reset_noise()
+    assert torch.equal(lin.weight_epsilon, o.maker_head.linear.weight_epsilon) and torch.equal(lin.bias_epsilon, o.maker_head.linear.bias_epsilon)
+    lin.disable_noise()
+    assert not lin.weight_epsilon.any() and not lin.bias_epsilon.any()
+
+
+def test_grow_depth_keeps_the_function_and_grow_width_layout():
+    """grow_depth appends identity layers (models.py:166-185): same Q-values; grow_width (models.py:187-238,336-358,52-73):
+    old weights in the top-left block, zeros right of them, product holder == oracle bit for bit under the same seed."""
+    from gnn_hex_b200 import ModernTwoHeaded
+    torch.manual_seed(0)
+    o = orc.ModernTwoHeadedOracle(10, 3, 2)
+    m = ModernTwoHeaded(10, 3, 2)
+    m.load_state_dict(o.state_dict())
+    gs, b = _small_batch(3)
+    with torch.no_grad():
+        q0 = o(b.x, b.edge_index, b.batch, b.ptr)
+    torch.manual_seed(21)
+    o.grow_depth(2)
+    torch.manual_seed(21)
+    m.grow_depth(2)
+    assert o.gnn.num_layers == 5 and len(m.gnn.convs) == 5
+    with torch.no_grad():
+        assert torch.allclose(o(b.x, b.edge_index, b.batch, b.ptr), q0, atol=1e-6)
+    w_old = o.gnn.convs[1].lin_l.weight.clone()
+    v_old = o.maker_head.value_head.layers[0].weight.clone()
+    torch.manual_seed(22)
+    o.grow_width(14)
+    o.maker_head.grow_depth(1); o.breaker_head.grow_depth(1)
+    torch.manual_seed(22)
+    m.grow_width(14)
+    m.maker_head.grow_depth(1); m.breaker_head.grow_depth(1)
+    sd_o, sd_m = o.state_dict(), m.state_dict()
+    assert list(sd_o.keys()) == list(sd_m.keys())
+    for k in sd_o:
+        assert torch.equal(sd_o[k], sd_m[k]), k
+    w = o.gnn.convs[1].lin_l.weight
+    assert w.shape == (14, 14) and torch.equal(w[:10, :10], w_old) and not w[:10, 10:].any() and w[10:, :].any()
+    v = o.maker_head.value_head.layers[0].weight
+    assert v.shape == (7, 56) and torch.equal(v[:5, :40], v_old) and not v[5:, :].any() and not v[:, 40:].any()
+    assert o.maker_head.linear.weight.shape == (1, 14) and not o.maker_head.linear.weight[:, 10:].any()
+    m._ensure_flat()
+    assert (m.hidden_channels, m.num_layers, m.num_head_layers) == (14, 5, 3)
+    assert m.flat_parameters.numel() == sum(p.numel() for p in o.parameters())
