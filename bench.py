@@ -149,9 +149,11 @@ class ClockSampler:
                 "window": where, "reasons": reasons}
 
 
-def time_cpu_port(batch, steps, warmup, max_seconds=None):
+def time_cpu_port(batch, steps, warmup, max_seconds=None, device=None):
     """fwd+bwd of the CPU restatement of the reference PyG path (oracle/, test infrastructure used
-    here only as the reported CPU baseline) on all host threads.  Returns (graphs/s, steps run, cores)."""
+    here only as the reported CPU baseline) on all host threads.  Returns (graphs/s, steps run, cores).
+    `device` = a CUDA device: the same torch-ops restatement on the GPU's STOCK kernels (index_select / index_add /
+    addmm ...), the "reference-equivalent on the same box" bar of SURVEY.md 8(d) -- reported beside the CPU number."""
     import torch
     from oracle import hexgnn_oracle as orc
     cores = os.cpu_count() or 1
@@ -159,13 +161,17 @@ def time_cpu_port(batch, steps, warmup, max_seconds=None):
     torch.manual_seed(0)
     o = orc.ModernTwoHeadedOracle(HIDDEN, LAYERS, HEAD_LAYERS)
     action, target, weight = loss_inputs(batch)
+    if device is not None:
+        o = o.to(device)
+        batch = batch.to(device)
+        action, target, weight = action.to(device), target.to(device), weight.to(device)
 
     def step():
         o.zero_grad(set_to_none=True)
         q = o(batch.x, batch.edge_index, batch.batch, batch.ptr)
         loss = orc.rainbow_loss(q, batch.ptr, action, target, weight)
         loss.backward()
-        return float(loss.detach())
+        return float(loss.detach())      # (on the GPU: the host sync that ends the step)
 
     for _ in range(warmup):
         step()
@@ -353,7 +359,7 @@ def run_fused(args, rank, world, local_rank):
     # ncu --set full (same workload): dram read + write per launch, summed over the kernels of the unit
     traffic = None
     if args.workload == "play" and args.path != "simt":
-        traffic = (156.1e6 + 302.3e6 + 502.6e6) if trio_n else (302.3e6 + 502.6e6)
+        traffic = (157.0e6 + 302.4e6 + 502.5e6) if trio_n else (302.4e6 + 502.5e6)
     line = {
         "metric": METRIC, "value": graphs * args.steps / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
@@ -361,13 +367,14 @@ def run_fused(args, rank, world, local_rank):
         "config": dict(workload_config(args, batch, world), collective=collective),
         "clocks": clocks,
         "e2e": {"value": graphs * args.steps / (ms_e2e * 1e-3), "unit": UNIT,
-                "h2d_bytes_per_step": int(sum(t.numel() * t.element_size() for t in (hb.x, hb.edge_index, hb.batch, hb.ptr))),
+                "h2d_bytes_per_step": int(hb._packed.numel()) if getattr(hb, "_packed", None) is not None else
+                int(sum(t.numel() * t.element_size() for t in (hb.x, hb.edge_index, hb.batch, hb.ptr))),
                 "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": int(launches),
         "roofline": {"bound": "tensor", "kernel": unit_name,
                      "achieved": achieved, "peak": tf32_peak, "unit": "TFLOP/s",
                      "frac": (achieved / tf32_peak) if achieved else None, "traffic": traffic,
-                     "traffic_source": "ncu dram__bytes_read+write per launch, summed over the unit's kernels, profiles/ncu_full_r1f_tc.csv",
+                     "traffic_source": "ncu dram__bytes_read+write per launch, summed over the unit's kernels, profiles/ncu_full_r1g_tc.csv",
                      "peak_source": f"0.5 x bf16_tflops ({pk['source']}) = dense TF32",
                      "arithmetic": "3xTF32 (3 tensor-core passes per algorithmic FLOP: ceiling 1/3 of peak)",
                      "flops_per_launch": unit_flops, "avg_launch_ms": unit_ms,
@@ -378,11 +385,17 @@ def run_fused(args, rank, world, local_rank):
         line["roofline"]["fwd_kernel"] = parts
     line["config"]["api"] = ("model.train_step (hexgnn_train_step)" if fused_api
                              else "model.forward -> ops.td_loss -> loss.backward()")
-    if not args.no_cpu_baseline:
+    if not args.no_cpu_baseline and world == 1:
         v, done, cores, dt = time_cpu_port(batch, 1000, 2, max_seconds=args.cpu_seconds)
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                 "sample": f"{done} fwd+bwd steps of the same {batch.num_graphs}-graph batch "
                                           f"({dt:.1f} s), torch fp32 restatement of the PyG path"}
+        try:   # the same restatement on this GPU's stock torch kernels (not the product, not the target)
+            gv, gdone, _, gdt = time_cpu_port(batch, 50, 5, max_seconds=10.0, device=dev)
+            line["cpu_baseline"]["same_port_on_this_gpu_stock_kernels"] = {
+                "value": gv, "unit": UNIT, "ms_per_step": 1e3 * gdt / gdone, "steps": gdone}
+        except Exception as e:  # noqa: BLE001 -- a baseline leg must not take the bench line down
+            line["cpu_baseline"]["same_port_on_this_gpu_stock_kernels"] = {"error": repr(e)[:200]}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -8,4 +8,5 @@ from .models import FusedAdam, ModernTwoHeaded, get_pre_defined  # noqa: F401
 from .ops import (CsrBlob, adam_step, build_csr, fused_backward, fused_forward, fused_train_step, mask_argmax,  # noqa: F401
                   td_loss, td_target)
 from . import data  # noqa: F401
+from . import custom_ops  # noqa: F401  (registers torch.ops.hexgnn.*)
 from .learner import RainbowLearner  # noqa: F401

@@ -27,14 +27,46 @@ class HexBatch(SimpleNamespace):
     """x, edge_index, batch, ptr, num_graphs -- the fields of a PyG `Batch` the model reads."""
 
     def to(self, device, non_blocking=False):
+        buf = getattr(self, "_packed", None)
+        if buf is not None and torch.device(device).type == "cuda":
+            # a pinned, packed batch travels as ONE host-to-device copy; the fields are views of the device buffer
+            return HexBatch._views(buf.to(device, non_blocking=non_blocking), self.x.shape[0], self.edge_index.shape[1],
+                                   self.num_graphs)
         return HexBatch(x=self.x.to(device, non_blocking=non_blocking),
                         edge_index=self.edge_index.to(device, non_blocking=non_blocking),
                         batch=self.batch.to(device, non_blocking=non_blocking),
                         ptr=self.ptr.to(device, non_blocking=non_blocking), num_graphs=self.num_graphs)
 
+    @staticmethod
+    def _views(buf, N, E, B):
+        """Fields as views of one byte buffer laid out [edge_index i64 2E | batch i64 N | ptr i64 B+1 | x f32 3N] (`_offsets`)."""
+        o1, o2, o3, _ = HexBatch._offsets(N, E, B)
+        out = HexBatch(x=buf[o3:o3 + 12 * N].view(torch.float32).view(N, 3),
+                       edge_index=buf[:16 * E].view(torch.int64).view(2, E), batch=buf[o1:o1 + 8 * N].view(torch.int64),
+                       ptr=buf[o2:o2 + 8 * (B + 1)].view(torch.int64), num_graphs=B)
+        out._packed = buf
+        return out
+
+    @staticmethod
+    def _offsets(N, E, B):
+        """Byte offsets of batch, ptr, x and the total size; every field starts on a 256-byte boundary (the alignment a
+        separate device allocation would have)."""
+        up = lambda v: (v + 255) // 256 * 256
+        o1 = up(16 * E)
+        o2 = o1 + up(8 * N)
+        o3 = o2 + up(8 * (B + 1))
+        return o1, o2, o3, o3 + 12 * N
+
     def pin_memory(self):
-        return HexBatch(x=self.x.pin_memory(), edge_index=self.edge_index.pin_memory(),
-                        batch=self.batch.pin_memory(), ptr=self.ptr.pin_memory(), num_graphs=self.num_graphs)
+        """Pinned host copy of the batch, packed into one buffer so that `.to(cuda)` is a single copy."""
+        N, E, B = int(self.x.shape[0]), int(self.edge_index.shape[1]), int(self.num_graphs)
+        if self.x.dtype != torch.float32 or self.edge_index.dtype != torch.int64 or int(self.ptr.shape[0]) != B + 1:
+            return HexBatch(x=self.x.pin_memory(), edge_index=self.edge_index.pin_memory(),
+                            batch=self.batch.pin_memory(), ptr=self.ptr.pin_memory(), num_graphs=self.num_graphs)
+        buf = torch.empty(HexBatch._offsets(N, E, B)[3], dtype=torch.uint8).pin_memory()
+        out = HexBatch._views(buf, N, E, B)
+        out.x.copy_(self.x); out.edge_index.copy_(self.edge_index); out.batch.copy_(self.batch); out.ptr.copy_(self.ptr)
+        return out
 
 
 def graph_from_directed(n: int, src: np.ndarray, dst: np.ndarray, maker: int) -> HexGraph:

@@ -53,3 +53,28 @@ def test_state_dict_names_match_reference_convention(lib_built):
     assert "maker_head.value_head.layers.0.weight" in keys and "maker_head.value_head.layers.1.bias" in keys
     assert tuple(m.maker_head.value_head.layers[0].weight.shape) == (17, 140)
     assert m.supports_cache and not m.gnn.has_cache and m.gnn.hidden_channels == 35
+
+
+def test_custom_ops_registered_with_fake_kernels(lib_built):
+    """torch.ops.hexgnn.{build_csr, fused_forward, fused_backward}: schemas and shape inference, no compute."""
+    import torch
+    import gnn_hex_b200  # noqa: F401
+    from torch._subclasses.fake_tensor import FakeTensorMode
+    for name in ("build_csr", "fused_forward", "fused_backward"):
+        assert hasattr(torch.ops.hexgnn, name)
+    desc = _lib.make_desc(35, 10, 2)
+    P = _lib.lib().hexgnn_param_count(desc)
+    with FakeTensorMode():
+        ei = torch.empty(2, 500, dtype=torch.int64, device="cuda")
+        x = torch.empty(100, 3, device="cuda")
+        ptr = torch.empty(5, dtype=torch.int64, device="cuda")
+        params = torch.empty(P, device="cuda")
+        csr = torch.ops.hexgnn.build_csr(ei, None, ptr, 100, 4, 128)
+        assert csr.dtype == torch.int32 and csr.numel() == _lib.csr_layout(100, 500, 4).total_words
+        qn, qv, st = torch.ops.hexgnn.fused_forward(params, x, csr, 500, 4, 35, 10, 2, 128, 0, True)
+        assert qn.shape == (100,) and qv.shape == (4,)
+        assert st.numel() * 4 == _lib.sizes(desc, 100, 500, 4, 128).stash_bytes
+        _, _, st0 = torch.ops.hexgnn.fused_forward(params, x, csr, 500, 4, 35, 10, 2, 128, 1, False)
+        assert st0.numel() == 0
+        g = torch.ops.hexgnn.fused_backward(params, x, csr, st, qn, None, 500, 4, 35, 10, 2, 128, 0)
+        assert g.shape == (P,)

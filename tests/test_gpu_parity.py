@@ -612,3 +612,57 @@ def test_grown_model_parity():
     glob, worst, wname = grad_errs(m, o, o64)
     assert glob <= REL_TOL, glob
     assert worst <= 1.0, (worst, wname)
+
+
+def test_custom_ops_match_the_module():
+    """torch.ops.hexgnn.* (functional, flat parameters) == the nn.Module route, bit for bit, gradient included."""
+    _, m = make_pair(35, 10)
+    m = m.to(DEV)
+    hb = _batch(CONFIGS["S"], "play", 1, 64)
+    b = hb.to(DEV)
+    action, target, weight = [t.to(DEV) for t in loss_inputs(hb)]
+    N, E, B = b.x.shape[0], b.edge_index.shape[1], hb.num_graphs
+    m.zero_grad()
+    q_ref = m(b.x, b.edge_index, b.batch, b.ptr)
+    ops.td_loss(q_ref, b.ptr, action, target, weight)[0].backward()
+    g_ref = m.flat_gradient.clone()
+    csr = torch.ops.hexgnn.build_csr(b.edge_index, b.batch, b.ptr, N, B, 128)
+    mine = ops.CsrBlob(csr, N, E, B, 128)         # (compare the CSR's fields: padding / builder scratch words are unset)
+    assert csr.numel() == m.last_csr.blob.numel()
+    for f in ("status", "ntiles", "gptr", "rowptr", "col"):
+        assert torch.equal(getattr(mine, f), getattr(m.last_csr, f)), f
+    params = m.flat_parameters.detach().clone().requires_grad_(True)
+    q, v, stash = torch.ops.hexgnn.fused_forward(params, b.x, csr, E, B, 35, 10, 2, 128, 0, True)
+    assert torch.equal(q, q_ref.detach())
+    ops.td_loss(q, b.ptr, action, target, weight)[0].backward()
+    assert torch.equal(params.grad, g_ref)
+    with torch.no_grad():
+        a, _, s0 = torch.ops.hexgnn.fused_forward(params, b.x, csr, E, B, 35, 10, 2, 128, ops.HEXGNN_ADV_ONLY, False)
+        assert s0.numel() == 0
+        assert torch.equal(a, m(b.x, b.edge_index, b.batch, b.ptr, advantages_only=True).reshape(-1))
+    torch.library.opcheck(torch.ops.hexgnn.fused_forward, (params, b.x, csr, E, B, 35, 10, 2, 128, 0, True),
+                          test_utils=("test_schema", "test_faketensor", "test_autograd_registration"))
+    torch.library.opcheck(torch.ops.hexgnn.build_csr, (b.edge_index, b.batch, b.ptr, N, B, 128),
+                          test_utils=("test_schema", "test_faketensor"))
+
+
+def test_packed_pinned_batch_is_one_copy_and_bit_exact():
+    """HexBatch.pin_memory() packs the four fields into one pinned buffer; .to(cuda) is a single copy whose views feed the
+    same kernels: identical CSR and Q-values."""
+    _, m = make_pair(35, 10)
+    m = m.to(DEV)
+    hb = _batch(CONFIGS["S"], "play", 0, 33)
+    pb = hb.pin_memory()
+    assert pb._packed.is_pinned() and pb.x.data_ptr() >= pb._packed.data_ptr()
+    d0, d1 = hb.to(DEV), pb.to(DEV, non_blocking=True)
+    for f in ("x", "edge_index", "batch", "ptr"):
+        assert torch.equal(getattr(d0, f), getattr(d1, f)) and getattr(d1, f).data_ptr() % 256 == 0
+    assert d1._packed.data_ptr() == d1.edge_index.data_ptr()
+    with torch.no_grad():
+        q0 = m(d0.x, d0.edge_index, d0.batch, d0.ptr)
+        csr0 = m.last_csr.blob.clone()
+        q1 = m(d1.x, d1.edge_index, d1.batch, d1.ptr)
+    assert torch.equal(q0, q1)
+    c0 = ops.CsrBlob(csr0, m.last_csr.N, m.last_csr.E, m.last_csr.B, 128)
+    for f in ("status", "ntiles", "gptr", "rowptr", "col"):
+        assert torch.equal(getattr(c0, f), getattr(m.last_csr, f)), f
