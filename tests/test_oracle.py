@@ -1,6 +1,7 @@
 """CPU: pin the oracle (oracle/hexgnn_oracle.py) -- golden fixtures from the reference's C++ game,
 a hand-computed known answer, fp64 gradcheck and the structural invariants of the model."""
 import numpy as np
+import pytest
 import torch
 
 from gnn_hex_b200 import data
@@ -238,3 +239,25 @@ def test_grow_depth_keeps_the_function_and_grow_width_layout():
     m._ensure_flat()
     assert (m.hidden_channels, m.num_layers, m.num_head_layers) == (14, 5, 3)
     assert m.flat_parameters.numel() == sum(p.numel() for p in o.parameters())
+
+
+def test_oracle_against_real_pyg_when_installed():
+    """torch_geometric 2.2.0 / torch_scatter 2.1.0 are absent from this image (no network), so the model
+    half of the oracle is pinned by known answers only.  Wherever they ARE importable this test pins the two third-party
+    semantics the oracle restates: SAGEConv (mean aggregation, lin_l with bias on the neighbours, lin_r without bias on the
+    root; message flow edge_index[0] -> edge_index[1]) and scatter(sum / max / min / mean) with empty groups = 0."""
+    tg = pytest.importorskip("torch_geometric")
+    ts = pytest.importorskip("torch_scatter")
+    from torch_geometric.nn import SAGEConv
+    torch.manual_seed(0)
+    g = data.load_positions("pos_7x7_seed1234.npz", maker=1)[3]
+    x = torch.randn(g.x.shape[0], 6)
+    conv = SAGEConv(6, 5)
+    want = conv(x, g.edge_index)
+    got = orc.sage_conv(x, g.edge_index, conv.lin_l.weight, conv.lin_l.bias, conv.lin_r.weight)
+    assert torch.allclose(got, want, atol=1e-6)
+    idx = torch.tensor([0, 0, 2, 2, 2, 4])
+    src = torch.randn(6, 3)
+    for red in ("sum", "max", "min", "mean"):
+        assert torch.allclose(orc.scatter(src, idx, 5, red), ts.scatter(src, idx, dim=0, dim_size=5, reduce=red), atol=1e-6), red
+    del tg
