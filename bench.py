@@ -204,7 +204,7 @@ def run_reference(args, rank, world):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def workload_config(args, batch, world):
@@ -396,9 +396,30 @@ def run_fused(args, rank, world, local_rank):
                 "value": gv, "unit": UNIT, "ms_per_step": 1e3 * gdt / gdone, "steps": gdone}
         except Exception as e:  # noqa: BLE001 -- a baseline leg must not take the bench line down
             line["cpu_baseline"]["same_port_on_this_gpu_stock_kernels"] = {"error": repr(e)[:200]}
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
+
+
+_JSON_FD = None
+
+
+def protect_stdout():
+    """The contract is ONE JSON line on stdout.  Native libraries write there too (NCCL prints its version line when the
+    box exports NCCL_DEBUG), so fd 1 is pointed at stderr for the whole run and the line goes to the saved descriptor."""
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
 
 
 def main():
@@ -412,6 +433,7 @@ def main():
                "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29531"),
                os.path.abspath(__file__)] + sys.argv[1:]
         raise SystemExit(subprocess.call(cmd))
+    protect_stdout()
     if args.impl == "reference":
         run_reference(args, rank, world)
     else:
