@@ -22,7 +22,7 @@ STATUS_NAMES = {
     ST_FLAG_MIXED: "x[:,2] is not constant over the batch (reference asserts this, GN0/models.py:538)",
 }
 
-ABI_VERSION = 6
+ABI_VERSION = 7
 
 
 class HexModelDesc(C.Structure):
@@ -44,7 +44,7 @@ EXPORTS = ["hexgnn_abi_version", "hexgnn_last_error", "hexgnn_param_count", "hex
            "hexgnn_sizes", "hexgnn_csr_layout", "hexgnn_build_csr", "hexgnn_forward", "hexgnn_backward",
            "hexgnn_profile_enable", "hexgnn_profile_read", "hexgnn_selftest_mma", "hexgnn_debug_phases", "hexgnn_stash_embed", "hexgnn_td_loss", "hexgnn_train_step", "hexgnn_adam_step", "hexgnn_adam_ws_bytes", "hexgnn_collate", "hexgnn_collate_ws_bytes",
            "hexgnn_mask_argmax", "hexgnn_td_target", "hexgnn_forward_big", "hexgnn_allreduce_p2p",
-           "hexgnn_noisy_compose", "hexgnn_noisy_grads"]
+           "hexgnn_noisy_compose", "hexgnn_noisy_grads", "hexgnn_backward_dx"]
 
 _lib = None
 
@@ -82,6 +82,8 @@ def lib():
     l.hexgnn_forward.argtypes = [D, p, p, i64, i64, i64, p, i32, i32, p, p, p, p, sz, p]
     l.hexgnn_backward.restype = C.c_int
     l.hexgnn_backward.argtypes = [D, p, p, i64, i64, i64, p, i32, i32, p, p, p, p, p, p, sz, p]
+    l.hexgnn_backward_dx.restype = C.c_int
+    l.hexgnn_backward_dx.argtypes = [D, p, p, i64, i64, i64, p, i32, i32, p, p, p, p, p, p, p, sz, p]
     l.hexgnn_selftest_mma.restype = C.c_int
     l.hexgnn_selftest_mma.argtypes = [p, p, p, i32, i32, i32, p]
     l.hexgnn_stash_embed.restype = C.c_int

@@ -163,10 +163,32 @@ int hexgnn_forward(const HexModelDesc* desc, const float* params, const float* x
   return launch_forward_tc(d, pm, params, x, N, E, B, csr, flags, out_nodes, out_value, stash, tpv, st);
 }
 
+static int backward_impl(const HexModelDesc* desc, const float* params, const float* x, int64_t N, int64_t E, int64_t B,
+                         const void* csr, int32_t tile_rows, int32_t flags, const float* d_nodes, const float* d_value,
+                         const float* stash, float* grad_params, float* d_embeds, float* d_x, void* ws, size_t ws_bytes,
+                         void* stream);
+
 int hexgnn_backward(const HexModelDesc* desc, const float* params, const float* x, int64_t N, int64_t E, int64_t B,
                     const void* csr, int32_t tile_rows, int32_t flags, const float* d_nodes, const float* d_value,
                     const float* stash, float* grad_params, float* d_embeds, void* ws, size_t ws_bytes,
                     void* stream) {
+  return backward_impl(desc, params, x, N, E, B, csr, tile_rows, flags, d_nodes, d_value, stash, grad_params, d_embeds,
+                       nullptr, ws, ws_bytes, stream);
+}
+
+int hexgnn_backward_dx(const HexModelDesc* desc, const float* params, const float* x, int64_t N, int64_t E, int64_t B,
+                       const void* csr, int32_t tile_rows, int32_t flags, const float* d_nodes, const float* d_value,
+                       const float* stash, float* grad_params, float* d_embeds, float* d_x, void* ws, size_t ws_bytes,
+                       void* stream) {
+  if (!d_x) { set_error("backward_dx: d_x is NULL (use hexgnn_backward)"); return HEXGNN_E_BADARG; }
+  return backward_impl(desc, params, x, N, E, B, csr, tile_rows, flags, d_nodes, d_value, stash, grad_params, d_embeds,
+                       d_x, ws, ws_bytes, stream);
+}
+
+static int backward_impl(const HexModelDesc* desc, const float* params, const float* x, int64_t N, int64_t E, int64_t B,
+                         const void* csr, int32_t tile_rows, int32_t flags, const float* d_nodes, const float* d_value,
+                         const float* stash, float* grad_params, float* d_embeds, float* d_x, void* ws, size_t ws_bytes,
+                         void* stream) {
   Dims d;
   if (!make_dims(desc, &d)) { set_error("backward: bad model descriptor"); return HEXGNN_E_BADARG; }
   if (!params || !x || !csr || !d_nodes || !stash || !grad_params || !ws || N < 1 || B < 1 || E < 0) { set_error("backward: bad argument"); return HEXGNN_E_BADARG; }
@@ -190,7 +212,7 @@ int hexgnn_backward(const HexModelDesc* desc, const float* params, const float* 
       // the two launches -- an event between them would serialise them.
       ProfScope prof(1, st);
       rc = launch_backward_tc_chain(d, pm, params, x, N, E, B, csr, flags, d_nodes, d_value, stash, wsf + w.dz, d_embeds,
-                                    tpv, wsf + w.small_rec, wsf + w.head_rec, sync, grid, st);
+                                    tpv, wsf + w.small_rec, wsf + w.head_rec, sync, grid, st, nullptr, d_x);
       if (rc) return rc;
       rc = launch_backward_tc_dw(d, N, E, B, csr, stash, wsf + w.dz, wsf + w.big_rec, sync, st);
       if (rc) return rc;
@@ -199,6 +221,7 @@ int hexgnn_backward(const HexModelDesc* desc, const float* params, const float* 
     if (rc) return rc;
     return launch_unpack_grads(d, pm, x, wsf + w.sum, grad_params, st);
   }
+  if (d_x) { set_error("backward_dx: the input gradient is produced by the tensor-core path only"); return HEXGNN_E_UNSUPPORTED; }
   const int nparts = bwd_grid_ctas();
   const int64_t need = (pack_floats(d) + (int64_t)(nparts + 1) * gl.total) * 4;
   if ((int64_t)ws_bytes < need) { set_error("backward: workspace too small (%zu < %lld)", ws_bytes, (long long)need); return HEXGNN_E_WORKSPACE; }

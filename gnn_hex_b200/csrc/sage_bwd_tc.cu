@@ -37,6 +37,7 @@ struct BwdTcArgs {
   const float* stash;     // forward stash (RM32 images + embedding copy)
   float* dz;              // dZ stash written here: [Lt-1][B][dz_blocks * 16 KB]
   float* d_embeds;
+  float* d_x;             // [N,3] dL/dx (rl_loop/explain.py:26-36 saliency), or NULL
   TcPackView pv;
   float* small_rec;       // [tiles][gl.total - gl.gb]  (the gv0 range stays unwritten): one record per TILE, so the
                           // gradient bits do not depend on which CTA processed which tile (schedule-independent)
@@ -662,6 +663,35 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
           for (int q = 0; q < 4; ++q) u += partb[(q * 6) * Hp + i];
           accs[i] += u;                                        // A_GB0 = 0, A_G0 = Hp: contiguous
         }
+        if (a.d_x) {
+          // dL/dx of the tile (input saliency, rl_loop/explain.py:26-36): with dpre_0 in `dump`,
+          //   r_i = W_r0^T dpre_0[i],  u_i = W_l0^T dpre_0[i] / deg(i),  dx_i = r_i + sum_{j in N(i)} u_j
+          // (the graph is symmetric: the adjoint of the mean-gather is a gather).  x[:,2] is the head selector: zero.
+          // 4 threads per row, one of (u_0, u_1, r_0, r_1) each; the x / mean staging rows are free by now.
+          const int i = tid >> 2, k = tid & 3;
+          const float* w = a.params + (k < 2 ? sage_wl(a.pm, 0, 0) + k : sage_wr(a.pm, 0, 0, H) + (k - 2));
+          float sacc = 0.f;
+          if (i < n) {
+            const float* dp = dump + i * P;
+            for (int c = 0; c < H; ++c) sacc = fmaf(dp[c], __ldg(w + 2 * c), sacc);
+            if (k < 2) sacc *= inv_s[i];
+          }
+          float* dst = k == 0 ? m0_s : k == 1 ? m1_s : k == 2 ? x0_s : x1_s;
+          dst[i] = sacc;
+          epi_bar_b();
+          if (tid < 2 * kTcRows) {
+            const int r = tid >> 1, q = tid & 1;
+            if (r < n) {
+              const float* us = q ? m1_s : m0_s;
+              float v = (q ? x1_s : x0_s)[r];
+              for (int p = rowptr_s[r]; p < rowptr_s[r + 1]; ++p) v += us[col_s[p]];
+              a.d_x[(int64_t)(r0 + r) * 3 + q] = v;
+            }
+          } else if (tid < 3 * kTcRows) {
+            const int r = tid - 2 * kTcRows;
+            if (r < n) a.d_x[(int64_t)(r0 + r) * 3 + 2] = 0.f;
+          }
+        }
       }
       PH_ADD(ph5, tq);
       // ---- hand the tile to the dW GEMM: all dZ stores of all epilogue threads, then one release ----------------------
@@ -714,12 +744,13 @@ static int launch_bwd_tc_t(const BwdTcArgs& a, int grid, cudaStream_t st) {
 int launch_backward_tc_chain(const Dims& d, const ParamMap& pm, const float* params, const float* x, int64_t N, int64_t E,
                              int64_t B, const void* csr, int flags, const float* d_nodes, const float* d_value,
                              const float* stash, float* dz, float* d_embeds, TcPackView pv, float* small_rec,
-                             float* head_rec, int* sync, int grid, cudaStream_t st, const TdFuse* fuse) {
+                             float* head_rec, int* sync, int grid, cudaStream_t st, const TdFuse* fuse, float* d_x) {
   BwdTcArgs a;
   a.d = d; a.pm = pm; grad_layout(d, &a.gl);
   a.params = params; a.x = x; a.N = N; a.E = E; a.B = B;
   a.csr = csr_view(const_cast<void*>(csr), N, E, B);
   a.flags = flags; a.d_nodes = d_nodes; a.d_value = d_value; a.stash = stash; a.dz = dz; a.d_embeds = d_embeds;
+  a.d_x = d_x;
   a.pv = pv; a.small_rec = small_rec; a.head_rec = head_rec; a.tile_flag = sync + kSyncTileOff;
   if (fuse) a.td = *fuse; else a.td = TdFuse{nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0.f};
   switch (d.NJ) {

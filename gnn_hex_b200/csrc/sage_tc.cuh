@@ -298,7 +298,8 @@ __host__ __device__ inline int tile_position(int rnd, int cta, int G, bool zig) 
 int launch_backward_tc_chain(const Dims& d, const ParamMap& pm, const float* params, const float* x, int64_t N, int64_t E,
                              int64_t B, const void* csr, int flags, const float* d_nodes, const float* d_value,
                              const float* stash, float* dz, float* d_embeds, TcPackView pv, float* small_rec,
-                             float* head_rec, int* sync, int grid, cudaStream_t st, const TdFuse* fuse = nullptr);
+                             float* head_rec, int* sync, int grid, cudaStream_t st, const TdFuse* fuse = nullptr,
+                             float* d_x = nullptr);
 int launch_backward_tc_dw(const Dims& d, int64_t N, int64_t E, int64_t B, const void* csr, const float* stash,
                           const float* dz, float* big_rec, int* sync, cudaStream_t st);
 int launch_reduce_tc(const Dims& d, const float* small_rec, const int* ntiles, const float* big_rec, int G,

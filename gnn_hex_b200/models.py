@@ -217,10 +217,12 @@ class _FusedQ(torch.autograd.Function):
         use_dv = bool(ctx.flags & ops.HEXGNN_SEPARATE) and d_value is not None
         accumulate = model._grads_in_place()
         out = model._grad_scratch() if accumulate else model._flat_grad_buffer()
+        # x.requires_grad: the caller wants dL/dx (`input.grad`, rl_loop/explain.py:26-36)
+        d_x = torch.zeros_like(x, dtype=torch.float32) if ctx.needs_input_grad[1] else None
         grad, d_emb = ops.fused_backward(model._desc, model._flat, x, ctx.csr, ctx.flags, d_nodes,
                                          d_value if use_dv else None, ctx.stash,
                                          want_d_embeds=model.capture_embed_grads, ws=model._bwd_ws(ctx.csr),
-                                         grad_out=out)
+                                         grad_out=out, d_x=d_x)
         if accumulate:
             model._flat_grad.add_(grad)
         else:
@@ -228,7 +230,7 @@ class _FusedQ(torch.autograd.Function):
         model._noisy_backward(grad)
         if d_emb is not None:
             model.final_conv_grads = d_emb[:, :model.hidden_channels]
-        return None, None, None, None, None
+        return None, d_x, None, None, None
 
 
 class ModernTwoHeaded(nn.Module):

@@ -140,8 +140,9 @@ def fused_forward(desc, flat_params, x, csr, flags=0, want_stash=False, ws=None)
 
 
 def fused_backward(desc, flat_params, x, csr, flags, d_nodes, d_value, stash, want_d_embeds=False, ws=None,
-                   grad_out=None):
-    """hexgnn_backward.  Returns (flat gradient [P], d_embeds [N,Hp] or None)."""
+                   grad_out=None, d_x=None):
+    """hexgnn_backward.  Returns (flat gradient [P], d_embeds [N,Hp] or None).  `d_x` ([N,3] f32 CUDA, optional): also
+    receives dL/dx (hexgnn_backward_dx; zero-initialised by the caller for rows of graphs the kernels refuse)."""
     N, E, B = csr.N, csr.E, csr.B
     sz = _lib.sizes(desc, N, E, B, csr.tile_rows)
     dev = x.device
@@ -154,6 +155,15 @@ def fused_backward(desc, flat_params, x, csr, flags, d_nodes, d_value, stash, wa
     if d_value is not None:
         d_value = d_value.contiguous().float()
     d_embeds = torch.empty((N, int(sz.hidden_padded)), dtype=torch.float32, device=dev) if want_d_embeds else None
+    if d_x is not None:
+        if not d_x.is_cuda or d_x.dtype != torch.float32 or not d_x.is_contiguous() or tuple(d_x.shape) != (N, 3):
+            raise _lib.HexGnnError("fused_backward: d_x must be a contiguous float32 CUDA tensor [N,3]")
+        rc = _lib.lib().hexgnn_backward_dx(C.byref(desc), _ptr(flat_params), _ptr(x), N, E, B, _ptr(csr.blob), csr.tile_rows,
+                                           flags, _ptr(d_nodes), _ptr(d_value), _ptr(stash), _ptr(grad_out), _ptr(d_embeds),
+                                           _ptr(d_x), _ptr(ws), ws.numel() * 4, _stream(dev))
+        _lib.check(rc, "hexgnn_backward_dx")
+        _count("backward")
+        return grad_out, d_embeds
     rc = _lib.lib().hexgnn_backward(C.byref(desc), _ptr(flat_params), _ptr(x), N, E, B, _ptr(csr.blob), csr.tile_rows,
                                     flags, _ptr(d_nodes), _ptr(d_value), _ptr(stash), _ptr(grad_out), _ptr(d_embeds),
                                     _ptr(ws), ws.numel() * 4, _stream(dev))

@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define HEXGNN_ABI_VERSION 6
+#define HEXGNN_ABI_VERSION 7
 
 enum {
   HEXGNN_OK = 0,
@@ -140,6 +140,15 @@ int hexgnn_backward(const HexModelDesc* desc, const float* params, const float* 
                     int64_t B, const void* csr, int32_t tile_rows, int32_t flags, const float* d_nodes,
                     const float* d_value, const float* stash, float* grad_params, float* d_embeds,
                     void* ws, size_t ws_bytes, void* stream);
+
+/* hexgnn_backward that also writes the input gradient d_x [N,3] f32 = dL/dx (saliency maps, rl_loop/explain.py:26-36:
+ * `input.grad` after `loss.backward()`); column 2 (the head selector x[:,2], never a network input, models.py:539-540) is
+ * zero.  Every row of a graph the kernels processed is written; tensor-core path only (HEXGNN_E_UNSUPPORTED otherwise).
+ * All other arguments as in hexgnn_backward. */
+int hexgnn_backward_dx(const HexModelDesc* desc, const float* params, const float* x, int64_t N, int64_t E, int64_t B,
+                       const void* csr, int32_t tile_rows, int32_t flags, const float* d_nodes, const float* d_value,
+                       const float* stash, float* grad_params, float* d_embeds, float* d_x, void* ws, size_t ws_bytes,
+                       void* stream);
 
 /* Oversize graphs (board-size transfer, evaluate_elo.py:229-251: 12x12 / 13x13 boards have 146 / 171 nodes).  Call AFTER
  * hexgnn_forward, same stream, same arguments: every graph the fused kernel refused (more than tile_rows nodes or

@@ -666,3 +666,32 @@ def test_packed_pinned_batch_is_one_copy_and_bit_exact():
     c0 = ops.CsrBlob(csr0, m.last_csr.N, m.last_csr.E, m.last_csr.B, 128)
     for f in ("status", "ntiles", "gptr", "rowptr", "col"):
         assert torch.equal(getattr(c0, f), getattr(m.last_csr, f)), f
+
+
+@pytest.mark.parametrize("name,maker,count", [("S", 1, 64), ("L", 0, 24)])
+def test_input_gradient_parity(name, maker, count):
+    """dL/dx (`input.grad` after loss.backward(), rl_loop/explain.py:26-36) through hexgnn_backward_dx, against the fp64 oracle;
+    column 2 (head selector) gets zero; the parameter gradient is the same bits as without the input gradient."""
+    cfg = CONFIGS[name]
+    o, m = make_pair(cfg["hidden"], cfg["layers"])
+    m = m.to(DEV)
+    b = _batch(cfg, "play", maker, count)
+    d = b.to(DEV)
+    action, target, weight = loss_inputs(b)
+    o64 = oracle64(o)
+    x64 = b.x.double().requires_grad_(True)
+    orc.rainbow_loss(o64(x64, b.edge_index, b.batch, b.ptr), b.ptr, action, target.double(), weight.double()).backward()
+    x32 = b.x.clone().requires_grad_(True)
+    orc.rainbow_loss(o(x32, b.edge_index, b.batch, b.ptr), b.ptr, action, target, weight).backward()
+    m.zero_grad()
+    ops.td_loss(m(d.x, d.edge_index, d.batch, d.ptr), d.ptr, action.to(DEV), target.to(DEV), weight.to(DEV))[0].backward()
+    g_plain = m.flat_gradient.clone()
+    m.zero_grad()
+    xg = d.x.clone().requires_grad_(True)
+    ops.td_loss(m(xg, d.edge_index, d.batch, d.ptr), d.ptr, action.to(DEV), target.to(DEV), weight.to(DEV))[0].backward()
+    assert xg.grad is not None and xg.grad.shape == d.x.shape
+    assert torch.equal(m.flat_gradient, g_plain)
+    assert float(xg.grad[:, 2].abs().max()) == 0.0 and float(x64.grad[:, 2].abs().max()) == 0.0
+    err = rel_err(xg.grad, x64.grad)
+    err32 = rel_err(x32.grad, x64.grad)
+    assert err <= max(4e-5, 16 * err32), (err, err32)
