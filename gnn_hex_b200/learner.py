@@ -26,7 +26,15 @@ class RainbowLearner:
         self.n_step_gamma = float(gamma) ** int(n_step)            # rainbow.py:75
         self.loss_fn = "mse" if loss_fn == "mse" else "smooth_l1"   # rainbow.py:84-85
         self.world_size = int(world_size)
-        self.opt = FusedAdam(q_policy, lr=lr, eps=adam_eps, max_grad_norm=max_grad_norm, skip_untaken=skip_untaken)
+        self.max_grad_norm = float(max_grad_norm)
+        if getattr(q_policy, "noisy_dqn", False):
+            # noisy nets: the advantage layer's mu / sigma live outside the flat parameter block FusedAdam walks, so the
+            # optimizer is the reference's own pair (rainbow.py:79,320-326) over the named parameters
+            self.opt = torch.optim.Adam(q_policy.parameters(), lr=lr, eps=adam_eps)
+            self._fused_opt = False
+        else:
+            self.opt = FusedAdam(q_policy, lr=lr, eps=adam_eps, max_grad_norm=max_grad_norm, skip_untaken=skip_untaken)
+            self._fused_opt = True
 
     def sync_Q_target(self):
         """rainbow.py:163-164."""
@@ -36,6 +44,8 @@ class RainbowLearner:
     def td_target(self, reward, next_state, done):
         """rainbow.py:259-277.  `next_state`: x, edge_index, batch, ptr on the device."""
         ns = next_state
+        if getattr(self.q_target, "noisy_dqn", False):
+            self.q_target.reset_noise()                              # rainbow.py:261
         csr = self.q_policy.build_csr(ns.edge_index, ns.batch, ns.ptr, num_nodes=int(ns.x.shape[0]),
                                       num_graphs=int(ns.ptr.shape[0]) - 1)
         q_t = self.q_target(ns.x, ns.edge_index, ns.batch, ns.ptr, csr=csr)
@@ -45,6 +55,25 @@ class RainbowLearner:
             return ops.td_target(q_t, best, reward, done, self.n_step_gamma)
         mx, _ = ops.mask_argmax(q_t, ns.ptr, mask_terminals=True, mask_value=-5.0)
         return reward.float() + self.n_step_gamma * mx * (1.0 - done.float())
+
+    @torch.no_grad()
+    def act(self, batch, eps: float = 0.0):
+        """rainbow.py:214-239 on an already collated device batch: greedy action per graph from the advantages with the two
+        terminal rows masked (-5), as LOCAL node indices; `eps` > 0 replaces actions by uniform random legal nodes on the
+        host exactly like the reference's loop (one sync).  Returns (actions [B] int64 on the device, exploratories np.bool)."""
+        import random
+        import numpy as np
+        adv = self.q_policy(batch.x, batch.edge_index, batch.batch, batch.ptr, advantages_only=True).reshape(-1)
+        _, best = ops.mask_argmax(adv, batch.ptr, mask_terminals=True, mask_value=-5.0)
+        actions = best - batch.ptr[:-1].to(best.device)
+        exploratories = np.zeros(actions.shape[0], dtype=bool)
+        if eps > 0:
+            sizes = (batch.ptr[1:] - batch.ptr[:-1]).tolist()
+            for i, n in enumerate(sizes):
+                if random.random() < eps and n > 2:
+                    actions[i] = random.randint(2, n - 1)
+                    exploratories[i] = True
+        return actions, exploratories
 
     def train(self, state, next_state, action, reward, done, weights=None):
         """rainbow.py:279-338 without the buffer: returns a dict of DEVICE tensors (no sync):
@@ -56,7 +85,11 @@ class RainbowLearner:
                                                    scale=1.0 / self.world_size)
         if self.world_size > 1:
             self.q_policy.allreduce_gradients()
-        grad_norm = self.opt.step(state.x)
+        if self._fused_opt:
+            grad_norm = self.opt.step(state.x)
+        else:
+            grad_norm = torch.nn.utils.clip_grad_norm_(self.q_policy.parameters(), self.max_grad_norm)   # rainbow.py:320
+            self.opt.step()
         td_est = td_err + td_tgt
         return {"loss": loss, "grad_norm": grad_norm, "priorities": td_err.abs() + 1e-6,
                 "est_mean": td_est.mean(), "gt_mean": td_tgt.mean(), "td_target": td_tgt, "q": q}

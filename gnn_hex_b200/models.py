@@ -439,6 +439,19 @@ class ModernTwoHeaded(nn.Module):
         else:
             super().zero_grad(set_to_none=False)
 
+    def reset_noise(self):
+        """`Rainbow.reset_noise(net)` (rainbow.py:167-179) for this model: fresh factorised noise in both heads' advantage
+        layers (the reference visits the two heads twice, i.e. draws twice; the distribution is the same)."""
+        if self.noisy_dqn:
+            self.maker_head.linear.reset_noise()
+            self.breaker_head.linear.reset_noise()
+
+    def disable_noise(self):
+        """`Rainbow.disable_noise(net)` (rainbow.py:181-192): evaluation with the mean weights."""
+        if self.noisy_dqn:
+            self.maker_head.linear.disable_noise()
+            self.breaker_head.linear.disable_noise()
+
     # ---- noisy-nets advantage layer (`noisy_dqn=True`): compose in front of the kernels, chain rule behind them -------
     def _compose_noisy(self):
         if self.noisy_dqn:

@@ -695,3 +695,66 @@ def test_input_gradient_parity(name, maker, count):
     err = rel_err(xg.grad, x64.grad)
     err32 = rel_err(x32.grad, x64.grad)
     assert err <= max(4e-5, 16 * err32), (err, err32)
+
+
+def test_rainbow_learner_noisy_nets_and_act():
+    """RainbowLearner with `noisy_dqn=True`: td_target resets the target net's noise (rainbow.py:261), the step uses the
+    reference's clip_grad_norm_ + torch Adam over the named parameters (mu / sigma included); `act` (rainbow.py:214-239)."""
+    from gnn_hex_b200 import RainbowLearner
+    cfg = CONFIGS["S"]
+    o_pol, m_pol = make_pair(cfg["hidden"], cfg["layers"], seed=0, noisy_dqn=True)
+    o_tgt, m_tgt = make_pair(cfg["hidden"], cfg["layers"], seed=5, noisy_dqn=True)
+    m_pol, m_tgt = m_pol.to(DEV), m_tgt.to(DEV)
+    gs = data.load_positions(cfg["fixture"], maker=1)
+    hs, hn = data.collate(gs[:48]), data.collate(gs[48:96])
+    g = torch.Generator().manual_seed(3)
+    action = torch.stack([torch.randint(2, int(n), (1,), generator=g)[0] for n in (hs.ptr[1:] - hs.ptr[:-1])])
+    reward = (torch.rand(48, generator=g) < 0.2).float()
+    done = (torch.rand(48, generator=g) < 0.3).float()
+    weights = torch.rand(48, generator=g) * 0.5 + 0.5
+    lr, eps, max_norm, gamma, n_step = 1e-3, 1.5e-4, 0.02, 0.97, 2
+    lrn = RainbowLearner(m_pol, m_tgt, lr=lr, adam_eps=eps, max_grad_norm=max_norm, gamma=gamma, n_step=n_step)
+    eps_before = m_tgt.maker_head.linear.weight_epsilon.clone()
+    out = lrn.train(hs.to(DEV), hn.to(DEV), action.to(DEV), reward.to(DEV), done.to(DEV), weights.to(DEV))
+    assert not torch.equal(m_tgt.maker_head.linear.weight_epsilon, eps_before)      # the target's noise was redrawn
+    for ho, hm in ((o_tgt.maker_head, m_tgt.maker_head), (o_tgt.breaker_head, m_tgt.breaker_head)):
+        ho.linear.weight_epsilon.copy_(hm.linear.weight_epsilon.cpu())
+        ho.linear.bias_epsilon.copy_(hm.linear.bias_epsilon.cpu())
+    with torch.no_grad():
+        adv = o_pol(hn.x, hn.edge_index, hn.batch, hn.ptr, advantages_only=True).clone()
+        adv[hn.ptr[:-1]] = -5
+        adv[hn.ptr[:-1] + 1] = -5
+        best = torch.stack([hn.ptr[i] + adv[hn.ptr[i]:hn.ptr[i + 1]].reshape(-1).argmax() for i in range(48)])
+        td_tgt = reward + gamma ** n_step * o_tgt(hn.x, hn.edge_index, hn.batch, hn.ptr).squeeze()[best] * (1 - done)
+    opt = torch.optim.Adam(o_pol.parameters(), lr=lr, eps=eps)
+    opt.zero_grad()
+    td_est = o_pol(hs.x, hs.edge_index, hs.batch, hs.ptr)[action + hs.ptr[:-1]]
+    loss_ref = torch.mean(weights * (td_tgt - td_est) ** 2)
+    loss_ref.backward()
+    norm_ref = torch.nn.utils.clip_grad_norm_([p for p in o_pol.parameters() if p.grad is not None], max_norm)
+    opt.step()
+    assert rel_err(out["td_target"], td_tgt) <= REL_TOL
+    assert abs(float(out["loss"]) - float(loss_ref)) <= 1e-5 * max(abs(float(loss_ref)), 1e-3)
+    assert abs(float(out["grad_norm"]) - float(norm_ref)) <= 2e-5 * float(norm_ref)
+    ref_sd = dict(o_pol.named_parameters())
+    for name, p in m_pol.named_parameters():
+        assert torch.allclose(p.detach().cpu(), ref_sd[name].detach(), atol=1e-5, rtol=0), name
+    assert not torch.equal(m_pol.maker_head.linear.weight_sigma.detach().cpu(),
+                           torch.full_like(ref_sd["maker_head.linear.weight_sigma"], 0.5 / cfg["hidden"] ** 0.5))
+    # act: greedy == arg-max of the oracle's masked advantages (noise disabled on both sides); eps = 1 explores everywhere
+    m_pol.disable_noise()
+    for h in (o_pol.maker_head, o_pol.breaker_head):
+        h.linear.disable_noise()
+    dn = hn.to(DEV)
+    actions, expl = lrn.act(dn, eps=0.0)
+    with torch.no_grad():
+        adv = o_pol(hn.x, hn.edge_index, hn.batch, hn.ptr, advantages_only=True).clone().reshape(-1)
+    adv[hn.ptr[:-1]] = -5
+    adv[hn.ptr[:-1] + 1] = -5
+    want = torch.stack([adv[hn.ptr[i]:hn.ptr[i + 1]].argmax() for i in range(48)])
+    top2 = [adv[hn.ptr[i]:hn.ptr[i + 1]].topk(2).values for i in range(48)]
+    clear = torch.tensor([float(t[0] - t[1]) > 1e-4 for t in top2])
+    assert torch.equal(actions.cpu()[clear], want[clear]) and not expl.any() and int(actions.min()) >= 2
+    actions, expl = lrn.act(dn, eps=1.0)
+    n = (hn.ptr[1:] - hn.ptr[:-1])
+    assert expl.all() and bool(((actions.cpu() >= 2) & (actions.cpu() < n)).all())
