@@ -268,33 +268,23 @@ class _SageStack(torch.nn.Module):
         self.num_layers += additional_layers
 
     def grow_width(self, new_width, new_in_channels=None):
-        """GN0/models.py:187-238 (has_output False, no norms)."""
-        old_convs, h = self.convs, self.hidden_channels
-        in_channels = self.convs[0].lin_l.weight.shape[1]
-        old_in_channels = in_channels
-        if new_in_channels is not None:
-            in_channels = new_in_channels
-        self.convs = torch.nn.ModuleList()
-        self.convs.append(self._new_conv(in_channels, new_width))                       # :197
-        for _ in range(self.num_layers - 2):                                           # :198-199
-            self.convs.append(self._new_conv(new_width, new_width))
-        self.convs.append(self._new_conv(new_width, new_width))                        # :205-206
-        for i, (conv, old_conv) in enumerate(zip(self.convs, old_convs)):              # :207-224
-            if i == 0:
-                if new_in_channels is None:
-                    conv.lin_l.weight.data[:h, :] = old_conv.lin_l.weight.data
-                    conv.lin_r.weight.data[:h, :] = old_conv.lin_r.weight.data
-                else:
-                    conv.lin_l.weight.data[:h, :old_in_channels] = old_conv.lin_l.weight.data
-                    conv.lin_r.weight.data[:h, :old_in_channels] = old_conv.lin_r.weight.data
-                    conv.lin_l.weight.data[:h, old_in_channels:] = 0
-                    conv.lin_r.weight.data[:h, old_in_channels:] = 0
-            else:
-                conv.lin_l.weight.data[:h, :h] = old_conv.lin_l.weight.data
-                conv.lin_r.weight.data[:h, :h] = old_conv.lin_r.weight.data
-                conv.lin_l.weight.data[:h, h:] = 0
-                conv.lin_r.weight.data[:h, h:] = 0
-            conv.lin_l.bias.data[:h] = old_conv.lin_l.bias.data
+        """GN0/models.py:187-238 (has_output False, no norms).  Every layer is re-created at the new width with default
+        init; then, per layer, the old matrix goes into the top-left block and the remainder of the OLD rows is zeroed
+        (new input columns do not feed old channels), the new rows keep their fresh init; old lin_l biases are kept."""
+        h, old = self.hidden_channels, list(self.convs)
+        old_in = old[0].lin_l.weight.shape[1]
+        cin0 = old_in if new_in_channels is None else new_in_channels
+        widths_in = [cin0] + [new_width] * (self.num_layers - 1)          # :197-206: first, middle and last layer
+        fresh = [self._new_conv(ci, new_width) for ci in widths_in]
+        with torch.no_grad():
+            for i, (c, o) in enumerate(zip(fresh, old)):                   # :207-224
+                k = old_in if i == 0 else h
+                for name in ("lin_l", "lin_r"):
+                    w_new, w_old = getattr(c, name).weight, getattr(o, name).weight
+                    w_new[:h, :k] = w_old
+                    w_new[:h, k:] = 0
+                c.lin_l.bias[:h] = o.lin_l.bias
+        self.convs = torch.nn.ModuleList(fresh)
         self.hidden_channels = new_width
 
 
@@ -311,20 +301,29 @@ class _MLP(torch.nn.Module):
         return self.layers[1](F.relu(self.layers[0](x)))
 
     def grow_input_width(self, new_input_width, new_hidden_channels):
-        """GN0/models.py:52-73 (the middle loop runs zero times for two layers)."""
-        old_layer = self.layers[0]
-        self.layers[0] = torch.nn.Linear(new_input_width, new_hidden_channels)
-        self.layers[0].weight.data.fill_(0)
-        self.layers[0].bias.data.fill_(0)
-        self.layers[0].weight.data[:self.hidden_channels, :self.num_input] = old_layer.weight.data
-        self.layers[0].bias.data[:self.hidden_channels] = old_layer.bias.data[:]
-        old_layer = self.layers[-1]
-        self.layers[-1] = torch.nn.Linear(new_hidden_channels, 1)
-        self.layers[-1].weight.data.fill_(0)
-        self.layers[-1].weight.data[:, :self.hidden_channels] = old_layer.weight.data
-        self.layers[-1].bias.data[:] = old_layer.bias.data[:]
-        self.num_input = new_input_width
-        self.hidden_channels = new_hidden_channels
+        """GN0/models.py:52-73 for two layers (the middle loop runs zero times): both layers become zero matrices of the new
+        shape carrying the old weights in their top-left block; the first layer's bias is zero-extended, the output bias kept.
+        The old input columns keep their positions 0 .. 4*old_H-1 although the pooled vector is laid out for the new width."""
+        first = _zero_extended_linear(self.layers[0], new_hidden_channels, new_input_width, zero_bias=True)
+        last = _zero_extended_linear(self.layers[1], 1, new_hidden_channels, zero_bias=False)
+        self.layers[0], self.layers[1] = first, last
+        self.num_input, self.hidden_channels = new_input_width, new_hidden_channels
+
+
+def _zero_extended_linear(old: torch.nn.Linear, n_out: int, n_in: int, zero_bias: bool) -> torch.nn.Linear:
+    """A fresh Linear(n_in, n_out) (default init is drawn, then discarded, as in the reference) whose weight is zero except
+    for `old.weight` in the top-left block; bias = old bias, zero-extended when `zero_bias` else copied over the whole."""
+    lin = torch.nn.Linear(n_in, n_out)
+    o, i = old.weight.shape
+    with torch.no_grad():
+        lin.weight.zero_()
+        lin.weight[:o, :i] = old.weight
+        if zero_bias:
+            lin.bias.zero_()
+            lin.bias[:o] = old.bias
+        else:
+            lin.bias.copy_(old.bias)
+    return lin
 
 
 class NoisyLinearOracle(torch.nn.Module):
@@ -380,14 +379,10 @@ class _Head(torch.nn.Module):
         self.hidden_channels = hidden
 
     def grow_width(self, new_width, new_in_channels=None):
-        """GN0/models.py:336-358."""
+        """GN0/models.py:336-358: wider head stack, advantage Linear zero-extended over the new channels, value MLP widened."""
         assert isinstance(self.linear, torch.nn.Linear)
         self.gnn.grow_width(new_width, new_in_channels=new_in_channels)
-        old_linear = self.linear
-        self.linear = torch.nn.Linear(new_width, 1)
-        self.linear.weight.data.fill_(0)
-        self.linear.weight.data[:, :self.hidden_channels] = old_linear.weight.data
-        self.linear.bias.data[:] = old_linear.bias.data[:]
+        self.linear = _zero_extended_linear(self.linear, 1, new_width, zero_bias=False)
         self.value_head.grow_input_width(new_width * 4, new_width // 2)
         self.hidden_channels = new_width
 
