@@ -76,16 +76,25 @@ __global__ void __launch_bounds__(kRedThreads) reduce_tc_kernel(GradLayout gl, i
                                                                 const float* __restrict__ head_rec, int hrec_n, int B,
                                                                 int nmain, int ngv0, float* __restrict__ out,
                                                                 const TdLossArgs td) {
-  if (blockIdx.x == gridDim.x - 1 && td.q) {   // hexgnn_train_step: loss value + TD errors ride along (no extra launch)
+  // Block order = schedule order: the latency-bound sections go FIRST (TD-loss block, then the per-graph gv0 chains, then
+  // the per-tile record chains) so that they run under the waves of the short one-element `main` blocks instead of after
+  // them.  `bx` is the block's index in the section layout [main | gv0 | small | td] the code below is written in.
+  const int nfront = (int)gridDim.x - nmain;                 // td + gv0 + small blocks
+  const int has_td = td.q ? 1 : 0;
+  int bx;
+  if ((int)blockIdx.x >= nfront) bx = (int)blockIdx.x - nfront;                              // main
+  else if ((int)blockIdx.x < has_td) bx = (int)gridDim.x - 1;                                // td
+  else bx = nmain + ((int)blockIdx.x - has_td);                                              // gv0, then small
+  if (bx == (int)gridDim.x - 1 && td.q) {   // hexgnn_train_step: loss value + TD errors ride along (no extra launch)
     td_loss_block(td);
     return;
   }
-  if ((int)blockIdx.x >= nmain + ngv0) {
+  if (bx >= nmain + ngv0) {
     // per-tile records of the chain kernel: block = 128 elements x 8 record slices (contiguous ranges of tiles, 4
     // interleaved chains inside a slice, slices combined in slice order): a fixed summation order that does not depend
     // on the kernels' tile schedule, and 8 x 4 short chains instead of one long latency-bound one per element
     __shared__ float sp_part[8][128];
-    const int sb = blockIdx.x - nmain - ngv0;
+    const int sb = bx - nmain - ngv0;
     const int ql = threadIdx.x & 127, sl = threadIdx.x >> 7;
     const int64_t i = gl.gb + (int64_t)sb * 128 + ql;
     const bool mine = i < gl.total && !(i >= gl.gv0 && i < gl.gv0b) && !(i >= gl.gb + Hp && i < gl.g0);
@@ -113,14 +122,14 @@ __global__ void __launch_bounds__(kRedThreads) reduce_tc_kernel(GradLayout gl, i
     }
     return;
   }
-  if ((int)blockIdx.x >= nmain) {
+  if (bx >= nmain) {
     // gv0[k][q] = sum_g dt_g[k] * pooled_g[q]: block = 128 q x 8 k; the 8 thread slices take 8 contiguous ranges of
     // the graphs (sequential inside a range, ranges combined in slice order: deterministic).  Many short independent
     // chains: the loop is DRAM/L2-latency bound otherwise (the records were just written by the chain kernel).
     __shared__ float part[8][8][128];
     const int H2p = (H2 + 3) & ~3, Q = 4 * H;
     const int nqb = (Q + 127) / 128;
-    const int bid = blockIdx.x - nmain, qb = bid % nqb, kb = bid / nqb;
+    const int bid = bx - nmain, qb = bid % nqb, kb = bid / nqb;
     const int ql = threadIdx.x & 127, q = qb * 128 + ql, sl = threadIdx.x >> 7, k0 = kb * 8;
     const int Bs = (B + 7) / 8;
     const int ga = sl * Bs, gb = (ga + Bs < B) ? ga + Bs : B;
@@ -154,7 +163,7 @@ __global__ void __launch_bounds__(kRedThreads) reduce_tc_kernel(GradLayout gl, i
     return;
   }
   const int64_t nth = (int64_t)nmain * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < gl.total; i += nth) {
+  for (int64_t i = (int64_t)bx * blockDim.x + threadIdx.x; i < gl.total; i += nth) {
     const bool from_big = i < gl.gb || (i >= gl.gb + Hp && i < gl.g0);
     if (!from_big) continue;                       // gv0 blocks / small-record blocks
     float acc = 0.f;
