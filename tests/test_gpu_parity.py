@@ -758,3 +758,47 @@ def test_rainbow_learner_noisy_nets_and_act():
     actions, expl = lrn.act(dn, eps=1.0)
     n = (hn.ptr[1:] - hn.ptr[:-1])
     assert expl.all() and bool(((actions.cpu() >= 2) & (actions.cpu() < n)).all())
+
+
+def test_full_size_headline_batch_properties():
+    """BASELINE configs[1] at its full size (GNN-L, 256 11x11 positions), through the properties the domain offers:
+    Q and loss against the fp32 oracle and the whole gradient against the fp64 arbiter; graphs are independent, so permuting
+    the GRAPH order of the batch permutes Q (to round-off: tiles are re-packed) and moves the gradient only by summation
+    order; the gradient is linear in the loss scale (a power of two: bit-exact)."""
+    cfg = CONFIGS["L"]
+    o, m = make_pair(cfg["hidden"], cfg["layers"])
+    m = m.to(DEV)
+    gs = data.load_positions(cfg["fixture"], maker=1)[:256]
+    hb = data.collate(gs)
+    b = hb.to(DEV)
+    action, target, weight = loss_inputs(hb)
+    dev_in = [t.to(DEV) for t in (action, target, weight)]
+    m.zero_grad()
+    loss, td_err, q = m.train_step(b.x, b.edge_index, b.batch, b.ptr, action=dev_in[0], target=dev_in[1], weight=dev_in[2])
+    g1 = m.flat_gradient.clone()
+    assert int(m.last_csr.status.item()) == 0
+    q_ref = o(hb.x, hb.edge_index, hb.batch, hb.ptr)
+    loss_ref = orc.rainbow_loss(q_ref, hb.ptr, action, target, weight)
+    loss_ref.backward()
+    o64 = oracle64(o)
+    orc.rainbow_loss(o64(hb.x.double(), hb.edge_index, hb.batch, hb.ptr), hb.ptr, action, target.double(),
+                     weight.double()).backward()
+    assert rel_err(q, q_ref) <= REL_TOL and rel_err(loss, loss_ref) <= REL_TOL
+    glob, worst, wname = grad_errs(m, o, o64)
+    assert glob <= REL_TOL, glob
+    assert worst <= 1.0, (worst, wname)
+    # linearity in the loss scale
+    m.zero_grad()
+    m.train_step(b.x, b.edge_index, b.batch, b.ptr, action=dev_in[0], target=dev_in[1], weight=dev_in[2], scale=0.25)
+    assert torch.equal(m.flat_gradient, 0.25 * g1)
+    # permutation of the graph order
+    perm = torch.randperm(256, generator=torch.Generator().manual_seed(11)).tolist()
+    hp = data.collate([gs[i] for i in perm])
+    p = hp.to(DEV)
+    pa, pt, pw = [t[perm].to(DEV) for t in (action, target, weight)]
+    m.zero_grad()
+    loss_p, _, q_p = m.train_step(p.x, p.edge_index, p.batch, p.ptr, action=pa, target=pt, weight=pw)
+    q_back = torch.cat([q[hb.ptr[i]:hb.ptr[i + 1]] for i in perm])
+    assert rel_err(q_p, q_back) <= 2e-6           # (not bit-exact: a row's position in its tile sets the order of its sums)
+    assert rel_err(m.flat_gradient, g1) <= REL_TOL
+    assert abs(float(loss_p) - float(loss)) <= 1e-6 * abs(float(loss))
