@@ -166,8 +166,15 @@ __global__ void __launch_bounds__(kRedThreads) reduce_tc_kernel(GradLayout gl, i
   for (int64_t i = (int64_t)bx * blockDim.x + threadIdx.x; i < gl.total; i += nth) {
     const bool from_big = i < gl.gb || (i >= gl.gb + Hp && i < gl.g0);
     if (!from_big) continue;                       // gv0 blocks / small-record blocks
+    // all G loads requested before the first add (summed in group order: the bits are unchanged)
+    constexpr int kBatch = 12;
+    float vbuf[kBatch];
+#pragma unroll
+    for (int g = 0; g < kBatch; ++g) vbuf[g] = g < G ? __ldg(big_rec + (int64_t)g * gl.g0 + i) : 0.f;
     float acc = 0.f;
-    for (int g = 0; g < G; ++g) acc += big_rec[(int64_t)g * gl.g0 + i];
+#pragma unroll
+    for (int g = 0; g < kBatch; ++g) if (g < G) acc += vbuf[g];
+    for (int g = kBatch; g < G; ++g) acc += big_rec[(int64_t)g * gl.g0 + i];
     out[i] = acc;
   }
 }
