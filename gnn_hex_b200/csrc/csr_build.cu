@@ -6,15 +6,15 @@
 //   rowptr[i]  = #edges with destination < i
 //   col[...]   = sources of the edges stably sorted by destination (ties keep input order)
 // Integer work, HBM/L2-latency bound: 16 B per edge in, 4 B per edge + 4 B per node out.
+#include <cooperative_groups.h>
 #include "common.cuh"
 
 namespace hexgnn {
+namespace cg = cooperative_groups;
 
 // ---- 1. init: status, gptr, zero the degree histogram ------------------------------------------
-__global__ void csr_init_kernel(CsrView v, const int64_t* __restrict__ batch, const int64_t* __restrict__ ptr,
-                                int N, int B) {
-  const int tid = blockIdx.x * blockDim.x + threadIdx.x;
-  const int nth = gridDim.x * blockDim.x;
+__device__ __forceinline__ void csr_init_dev(CsrView v, const int64_t* __restrict__ batch, const int64_t* __restrict__ ptr,
+                                             int N, int B, int tid, int nth) {
   if (tid == 0) { *v.status = 0; *v.ntiles = 0; v.scan_ticket[0] = 0; }
   for (int i = tid; i < (int)csr_scan_blocks(N); i += nth) v.scan_state[i] = 0ull;
   for (int i = tid; i <= N; i += nth) v.cursor[i] = 0;  // cursor doubles as the degree histogram
@@ -35,14 +35,21 @@ __global__ void csr_init_kernel(CsrView v, const int64_t* __restrict__ batch, co
   }
 }
 
+__global__ void csr_init_kernel(CsrView v, const int64_t* __restrict__ batch, const int64_t* __restrict__ ptr,
+                                int N, int B) {
+  csr_init_dev(v, batch, ptr, N, B, blockIdx.x * blockDim.x + threadIdx.x, gridDim.x * blockDim.x);
+}
+
 // ---- 2. in-degree histogram ---------------------------------------------------------------------
-__global__ void csr_hist_kernel(CsrView v, const int64_t* __restrict__ ei, int E, int N) {
-  const int nth = gridDim.x * blockDim.x;
-  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < E; e += nth) {
+__device__ __forceinline__ void csr_hist_dev(CsrView v, const int64_t* __restrict__ ei, int E, int N, int tid, int nth) {
+  for (int e = tid; e < E; e += nth) {
     const long long s = ei[e], d = ei[(int64_t)E + e];
     if (s < 0 || s >= N || d < 0 || d >= N) { atomicOr(v.status, HEXGNN_ST_EDGE_CROSSES); continue; }
     atomicAdd(&v.cursor[d], 1);
   }
+}
+__global__ void csr_hist_kernel(CsrView v, const int64_t* __restrict__ ei, int E, int N) {
+  csr_hist_dev(v, ei, E, N, blockIdx.x * blockDim.x + threadIdx.x, gridDim.x * blockDim.x);
 }
 
 // ---- 3. exclusive scan of the histogram: single pass, decoupled look-back ---------------------------------------
@@ -50,7 +57,7 @@ __global__ void csr_hist_kernel(CsrView v, const int64_t* __restrict__ ei, int E
 // aggregate, looks back over the predecessors' states (flag 1 = aggregate, 2 = inclusive prefix) one warp-wide window
 // at a time, publishes its inclusive prefix, and writes rowptr.  All blocks run concurrently: two or three L2 round
 // trips in total instead of one CTA walking the whole array (16 us for 20 k entries).
-__global__ void __launch_bounds__(256) csr_scan_kernel(CsrView v, int N) {
+__device__ __forceinline__ void csr_scan_dev(CsrView v, int N) {
   __shared__ int warp_sums[8];
   __shared__ int bid_s, prefix_s;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -114,10 +121,11 @@ __global__ void __launch_bounds__(256) csr_scan_kernel(CsrView v, int N) {
   }
 }
 
+__global__ void __launch_bounds__(256) csr_scan_kernel(CsrView v, int N) { csr_scan_dev(v, N); }
+
 // ---- 4. unstable fill with edge ids + greedy tile packing (last block) ----------------------------
-__global__ void csr_fill_kernel(CsrView v, const int64_t* __restrict__ ei, int E, int N, int B, int tile_rows,
-                                int tile_edges) {
-  if (blockIdx.x == gridDim.x - 1) {
+__device__ __forceinline__ void csr_tiles_dev(CsrView v, int B, int tile_rows, int tile_edges) {
+  {
     // Greedy packing of whole graphs into tiles of <= tile_rows nodes, <= tile_edges edges, <= kMaxTileGraphs graphs:
     // tile starts s_0 = 0, s_{k+1} = next[s_k], where next[i] = first graph that no longer fits a tile opened at graph i
     // (graph i itself is always taken, also when it is too large on its own).  next[] is computed by all threads in
@@ -178,10 +186,11 @@ __global__ void csr_fill_kernel(CsrView v, const int64_t* __restrict__ ei, int E
     } else {
       for (int t = threadIdx.x; t < T; t += blockDim.x) v.tile_order[t] = t;
     }
-    return;
   }
-  const int nth = (gridDim.x - 1) * blockDim.x;
-  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < E; e += nth) {
+}
+
+__device__ __forceinline__ void csr_fill_dev(CsrView v, const int64_t* __restrict__ ei, int E, int N, int tid, int nth) {
+  for (int e = tid; e < E; e += nth) {
     const long long s = ei[e], d = ei[(int64_t)E + e];
     if (s < 0 || s >= N || d < 0 || d >= N) continue;
     const int pos = atomicAdd(&v.cursor[d], 1);
@@ -189,14 +198,19 @@ __global__ void csr_fill_kernel(CsrView v, const int64_t* __restrict__ ei, int E
   }
 }
 
+__global__ void csr_fill_kernel(CsrView v, const int64_t* __restrict__ ei, int E, int N, int B, int tile_rows,
+                                int tile_edges) {
+  if (blockIdx.x == gridDim.x - 1) { csr_tiles_dev(v, B, tile_rows, tile_edges); return; }
+  csr_fill_dev(v, ei, E, N, blockIdx.x * blockDim.x + threadIdx.x, (gridDim.x - 1) * blockDim.x);
+}
+
 // ---- 5. stable order inside every row: one thread per CSR slot ------------------------------------
 // Slot p holds edge id eid[p] of row d = dst(eid[p]); its final position is the number of edge ids of the same row
 // that are smaller (input order == stable sort by destination).  All threads independent: no dependent
 // read-modify-write chains in global memory (the per-row insertion sort this replaces was latency bound).
-__global__ void csr_rank_kernel(CsrView v, const int64_t* __restrict__ ei, int E, int N) {
-  const int nth = gridDim.x * blockDim.x;
+__device__ __forceinline__ void csr_rank_dev(CsrView v, const int64_t* __restrict__ ei, int E, int N, int tid, int nth) {
   const int filled = v.rowptr[N];   // < E only when edges were rejected (status flagged): those slots hold no id
-  for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < filled; p += nth) {
+  for (int p = tid; p < filled; p += nth) {
     const int me = v.eid[p];
     const int d = (int)ei[(int64_t)E + me];
     const int b = v.rowptr[d], e = v.rowptr[d + 1];
@@ -205,6 +219,42 @@ __global__ void csr_rank_kernel(CsrView v, const int64_t* __restrict__ ei, int E
     v.col[b + rank] = (int)ei[me];
   }
 }
+__global__ void csr_rank_kernel(CsrView v, const int64_t* __restrict__ ei, int E, int N) {
+  csr_rank_dev(v, ei, E, N, blockIdx.x * blockDim.x + threadIdx.x, gridDim.x * blockDim.x);
+}
+
+// ---- all five phases in ONE cooperative launch (grid-wide barriers instead of kernel boundaries) ----------------------
+// The builder is 2.4 MB of integer work: five dependent launches cost more in launch / drain latency than in memory time
+// (36 us for 103 k edges).  Here every phase is a grid-stride loop of the same resident grid; the tile packing (one block,
+// the longest dependent chain) runs in the LAST phase beside the row ranking, which does not need it.
+__global__ void __launch_bounds__(256) csr_build_fused_kernel(CsrView v, const int64_t* __restrict__ ei,
+                                                              const int64_t* __restrict__ batch, const int64_t* __restrict__ ptr,
+                                                              int N, int E, int B, int tile_rows, int tile_edges, int nscan) {
+  cg::grid_group grid = cg::this_grid();
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+  csr_init_dev(v, batch, ptr, N, B, tid, nth);
+  grid.sync();
+  csr_hist_dev(v, ei, E, N, tid, nth);
+  grid.sync();
+  if ((int)blockIdx.x < nscan) csr_scan_dev(v, N);     // ticket-ordered look-back: every scan block is resident
+  grid.sync();
+  // rowptr is final: the last block packs and ranks the tiles (one block, the longest dependent chain of the build) while
+  // the others fill and rank the rows.  Those G-1 blocks meet at their own barrier -- the scan's ticket counter, which
+  // stands at nscan now, counts them in -- so the tile block is not waited for before the kernel ends.
+  if (blockIdx.x == gridDim.x - 1) { csr_tiles_dev(v, B, tile_rows, tile_edges); return; }
+  const int nth1 = (gridDim.x - 1) * blockDim.x;
+  csr_fill_dev(v, ei, E, N, tid, nth1);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicAdd(v.scan_ticket, 1);
+    const int target = nscan + (int)gridDim.x - 1;
+    while (*(volatile int*)v.scan_ticket < target) {}
+    __threadfence();
+  }
+  __syncthreads();
+  csr_rank_dev(v, ei, E, N, tid, nth1);
+}
 
 int launch_build_csr(const int64_t* edge_index, int64_t E, const int64_t* batch, const int64_t* ptr, int64_t N,
                      int64_t B, int tile_rows, void* csr, cudaStream_t st) {
@@ -212,6 +262,32 @@ int launch_build_csr(const int64_t* edge_index, int64_t E, const int64_t* batch,
   const int threads = 256;
   auto blocks = [&](int64_t n) { int64_t b = (n + threads - 1) / threads; return (int)(b < 1 ? 1 : (b > 1184 ? 1184 : b)); };
   const int64_t init_n = (N + 1 > B + 1) ? N + 1 : B + 1;
+  {
+    // one cooperative launch when the whole grid can be resident (always, short of ~300 k nodes per call)
+    static int coop_max = -1;     // resident 256-thread blocks of the fused kernel on this device, 0 = unsupported
+    if (coop_max < 0) {
+      int dev = 0, coop = 0, sms = 0, per_sm = 0;
+      if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev) == cudaSuccess &&
+          coop && cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess &&
+          cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, csr_build_fused_kernel, threads, 0) == cudaSuccess)
+        coop_max = sms * (per_sm > 2 ? 2 : per_sm);      // two blocks per SM: more only lengthens the barriers
+      else
+        coop_max = 0;
+      (void)cudaGetLastError();
+    }
+    const int nscan = (int)csr_scan_blocks(N);
+    int64_t want = (E > init_n ? E : init_n);
+    want = (want + threads - 1) / threads + 1;
+    if (want < nscan + 1) want = nscan + 1;
+    int grid = (int)(want < coop_max ? want : coop_max);
+    if (grid < 2) grid = 2;
+    if (coop_max >= 2 && nscan < grid && grid <= coop_max) {
+      int Ni = (int)N, Ei = (int)E, Bi = (int)B, te = tile_rows * kEdgeCapPerRow, ns = nscan;
+      void* args[] = {&v, (void*)&edge_index, (void*)&batch, (void*)&ptr, &Ni, &Ei, &Bi, &tile_rows, &te, &ns};
+      HEX_CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)csr_build_fused_kernel, dim3(grid), dim3(threads), args, 0, st));
+      return HEXGNN_OK;
+    }
+  }
   csr_init_kernel<<<blocks(init_n), threads, 0, st>>>(v, batch, ptr, (int)N, (int)B);
   if (E > 0) csr_hist_kernel<<<blocks(E), threads, 0, st>>>(v, edge_index, (int)E, (int)N);
   csr_scan_kernel<<<(int)csr_scan_blocks(N), 256, 0, st>>>(v, (int)N);

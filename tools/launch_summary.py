@@ -14,7 +14,7 @@ for row in csv.DictReader(lines):
 tot = sum(a[1] for a in agg.values())
 for k, a in sorted(agg.items(), key=lambda kv: -kv[1][1])[:14]:
     print(f"{a[0]:4d} {a[1]:10.1f} us {100*a[1]/tot:5.1f}%  avg {a[1]/a[0]:8.1f}  {k}")
-idx = [i for i, (k, v) in enumerate(seq) if 'csr_init' in k]
+idx = [i for i, (k, v) in enumerate(seq) if 'csr_init' in k or 'csr_build_fused' in k]
 if len(idx) > 2:
     i0, i1 = idx[-3], idx[-2]
     print("one step:", i1 - i0, "launches,", f"{sum(v for k, v in seq[i0:i1]):.1f} us")
