@@ -134,6 +134,7 @@ __device__ __forceinline__ void csr_tiles_dev(CsrView v, int B, int tile_rows, i
     // compare-and-add chain per GRAPH).
     constexpr int kChunk = 1024, kAhead = kMaxTileGraphs;
     __shared__ int n_s[kChunk + kAhead], ne_s[kChunk + kAhead], next_s[kChunk];
+    __shared__ int hop2_s[kChunk], hop3_s[kChunk], hop4_s[kChunk];   // tile start 2 / 3 / 4 tiles on (-1: beyond this chunk)
     __shared__ int st_s[2];   // next tile start, tiles so far
     if (threadIdx.x == 0) { st_s[0] = 0; st_s[1] = 0; v.tile_g0[0] = 0; }
     int status = 0;
@@ -156,9 +157,27 @@ __device__ __forceinline__ void csr_tiles_dev(CsrView v, int B, int tile_rows, i
         next_s[i] = gb + j;
       }
       __syncthreads();
+      // 2-, 3- and 4-tile look-ahead of every graph, in parallel: the serial chase below then advances four tiles per
+      // dependent shared-memory round trip instead of one
+      for (int i = threadIdx.x; i < gn; i += blockDim.x) {
+        const int end = gb + gn;
+        const int a = next_s[i];
+        const int b = a < end ? next_s[a - gb] : -1;
+        const int c = (b >= 0 && b < end) ? next_s[b - gb] : -1;
+        const int d = (c >= 0 && c < end) ? next_s[c - gb] : -1;
+        hop2_s[i] = b; hop3_s[i] = c; hop4_s[i] = d;
+      }
+      __syncthreads();
       if (threadIdx.x == 0) {
         int g = st_s[0], t = st_s[1];
-        while (g < gb + gn) { g = next_s[g - gb]; v.tile_g0[++t] = g; }
+        while (g < gb + gn) {
+          const int l = g - gb;
+          const int a = next_s[l], b = hop2_s[l], c = hop3_s[l], d = hop4_s[l];
+          v.tile_g0[++t] = a; g = a;
+          if (b >= 0) { v.tile_g0[++t] = b; g = b; }
+          if (c >= 0) { v.tile_g0[++t] = c; g = c; }
+          if (d >= 0) { v.tile_g0[++t] = d; g = d; }
+        }
         st_s[0] = g; st_s[1] = t;
       }
     }
