@@ -7,6 +7,7 @@
 //   col[...]   = sources of the edges stably sorted by destination (ties keep input order)
 // Integer work, HBM/L2-latency bound: 16 B per edge in, 4 B per edge + 4 B per node out.
 #include <cooperative_groups.h>
+#include <stdlib.h>
 #include "common.cuh"
 
 namespace hexgnn {
@@ -289,7 +290,11 @@ int launch_build_csr(const int64_t* edge_index, int64_t E, const int64_t* batch,
       if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev) == cudaSuccess &&
           coop && cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess &&
           cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, csr_build_fused_kernel, threads, 0) == cudaSuccess)
-        coop_max = sms * (per_sm > 2 ? 2 : per_sm);      // two blocks per SM: more only lengthens the barriers
+      {
+        int cap = 2;                                       // two blocks per SM: more only lengthens the barriers
+        if (const char* e = getenv("HEXGNN_CSR_BLOCKS_PER_SM")) { const int c = atoi(e); if (c >= 1 && c <= 8) cap = c; }
+        coop_max = sms * (per_sm > cap ? cap : per_sm);
+      }
       else
         coop_max = 0;
       (void)cudaGetLastError();
