@@ -370,7 +370,7 @@ def run_fused(args, rank, world, local_rank):
     # ncu --set full (same workload): dram read + write per launch, summed over the kernels of the unit
     traffic = None
     if args.workload == "play" and args.path != "simt":
-        traffic = (157.0e6 + 302.4e6 + 502.5e6) if trio_n else (302.4e6 + 502.5e6)
+        traffic = (157.8e6 + 302.0e6 + 503.4e6) if trio_n else (302.0e6 + 503.4e6)
     line = {
         "metric": METRIC, "value": graphs * args.steps / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
@@ -385,7 +385,7 @@ def run_fused(args, rank, world, local_rank):
         "roofline": {"bound": "tensor", "kernel": unit_name,
                      "achieved": achieved, "peak": tf32_peak, "unit": "TFLOP/s",
                      "frac": (achieved / tf32_peak) if achieved else None, "traffic": traffic,
-                     "traffic_source": "ncu dram__bytes_read+write per launch, summed over the unit's kernels, profiles/ncu_full_r1g_tc.csv",
+                     "traffic_source": "ncu dram__bytes_read+write per launch, summed over the unit's kernels, profiles/ncu_full_r1h_tc.csv",
                      "peak_source": f"0.5 x bf16_tflops ({pk['source']}) = dense TF32",
                      "arithmetic": "3xTF32 (3 tensor-core passes per algorithmic FLOP: ceiling 1/3 of peak)",
                      "flops_per_launch": unit_flops, "avg_launch_ms": unit_ms,
