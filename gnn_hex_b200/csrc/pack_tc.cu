@@ -69,8 +69,8 @@ int launch_pack_tc(const Dims& d, const ParamMap& pm, const float* params, const
 //   gw and gb[s>=1]  <- the G group records of sage_dw_tc_kernel   (big_rec [G][gl.g0])
 //   gv0              <- sum over graphs (in graph order) of dt_g (x) pooled_g from the head records
 //   everything else  <- the per-TILE records of sage_bwd_tc_kernel  (small_rec [ntiles][gl.total - gl.gb])
-constexpr int kRedThreads = 1024;   // gv0 blocks: 128 q x 8 graph slices
-__global__ void __launch_bounds__(kRedThreads) reduce_tc_kernel(GradLayout gl, int Hp, int H, int H2,
+constexpr int kRedThreads = 1024;   // gv0 blocks: 32 q x 32 graph ranges
+__global__ void __launch_bounds__(kRedThreads, 2) reduce_tc_kernel(GradLayout gl, int Hp, int H, int H2,
                                                                 const float* __restrict__ small_rec, const int* __restrict__ ntiles,
                                                                 const float* __restrict__ big_rec, int G,
                                                                 const float* __restrict__ head_rec, int hrec_n, int B,
@@ -85,23 +85,33 @@ __global__ void __launch_bounds__(kRedThreads) reduce_tc_kernel(GradLayout gl, i
   if ((int)blockIdx.x >= nfront) bx = (int)blockIdx.x - nfront;                              // main
   else if ((int)blockIdx.x < has_td) bx = (int)gridDim.x - 1;                                // td
   else bx = nmain + ((int)blockIdx.x - has_td);                                              // gv0, then small
+#ifndef HEXGNN_RED_SKIP
+#define HEXGNN_RED_SKIP 0      // profiling builds only: bit 0 td block, 1 gv0, 2 per-tile records, 3 group records skipped
+#endif
   if (bx == (int)gridDim.x - 1 && td.q) {   // hexgnn_train_step: loss value + TD errors ride along (no extra launch)
-    td_loss_block(td);
+    if (!(HEXGNN_RED_SKIP & 1)) td_loss_block(td);
     return;
   }
+  if ((HEXGNN_RED_SKIP & 2) && bx >= nmain && bx < nmain + ngv0) return;
+  if ((HEXGNN_RED_SKIP & 4) && bx >= nmain + ngv0) return;
+  if ((HEXGNN_RED_SKIP & 8) && bx < nmain) return;
   if (bx >= nmain + ngv0) {
-    // per-tile records of the chain kernel: block = 128 elements x 8 record slices (contiguous ranges of tiles, 4
-    // interleaved chains inside a slice, slices combined in slice order): a fixed summation order that does not depend
-    // on the kernels' tile schedule, and 8 x 4 short chains instead of one long latency-bound one per element
-    __shared__ float sp_part[8][128];
+    // per-tile records of the chain kernel.  Only three short ranges of the record are live here -- layer-0 bias
+    // [gb, gb+Hp), layer-0 weights + head linear [g0, gv0), value-MLP biases and output layer [gv0b, total) -- so the blocks
+    // index those ~1 k elements compactly: block = 32 elements x 32 contiguous ranges of tiles (4 interleaved chains inside
+    // a range, ranges combined in range order): a fixed summation order that does not depend on the kernels' tile
+    // schedule, and two dependent round trips per thread for 209 tiles instead of seven.
+    __shared__ float sp_part[32][32];
     const int sb = bx - nmain - ngv0;
-    const int ql = threadIdx.x & 127, sl = threadIdx.x >> 7;
-    const int64_t i = gl.gb + (int64_t)sb * 128 + ql;
-    const bool mine = i < gl.total && !(i >= gl.gv0 && i < gl.gv0b) && !(i >= gl.gb + Hp && i < gl.g0);
+    const int ql = threadIdx.x & 31, sl = threadIdx.x >> 5;
+    const int64_t n1 = Hp, n2 = gl.gv0 - gl.g0, n3 = gl.total - gl.gv0b;
+    const int64_t e = (int64_t)sb * 32 + ql;
+    const bool mine = e < n1 + n2 + n3;
+    const int64_t i = e < n1 ? gl.gb + e : (e < n1 + n2 ? gl.g0 + (e - n1) : gl.gv0b + (e - n1 - n2));
     const int64_t recn = gl.total - gl.gb;
     const int nsmall = *ntiles;
-    const int per = (nsmall + 7) / 8;
-    const int pa = sl * per, pb = (pa + per < nsmall) ? pa + per : nsmall;
+    const int per = (nsmall + 31) / 32;
+    const int pa = sl * per < nsmall ? sl * per : nsmall, pb = (pa + per < nsmall) ? pa + per : nsmall;
     float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
     if (mine) {
       const float* sp = small_rec + (i - gl.gb);
@@ -117,22 +127,23 @@ __global__ void __launch_bounds__(kRedThreads) reduce_tc_kernel(GradLayout gl, i
     if (sl == 0 && mine) {
       float u = sp_part[0][ql];
 #pragma unroll
-      for (int t = 1; t < 8; ++t) u += sp_part[t][ql];
+      for (int t = 1; t < 32; ++t) u += sp_part[t][ql];
       out[i] = u;
     }
     return;
   }
   if (bx >= nmain) {
-    // gv0[k][q] = sum_g dt_g[k] * pooled_g[q]: block = 128 q x 8 k; the 8 thread slices take 8 contiguous ranges of
-    // the graphs (sequential inside a range, ranges combined in slice order: deterministic).  Many short independent
-    // chains: the loop is DRAM/L2-latency bound otherwise (the records were just written by the chain kernel).
-    __shared__ float part[8][8][128];
+    // gv0[k][q] = sum_g dt_g[k] * pooled_g[q]: block = 32 q x 8 k; its 32 warps take 32 contiguous ranges of the graphs
+    // (sequential inside a range, ranges combined in range order: deterministic).  The per-thread chain of dependent-looking
+    // L2 round trips is what bounds this kernel (measured by compiling sections out: 17.1 us with, 10.7 us without this
+    // section when a thread walked 32 graphs), so the ranges are short -- B/32 graphs -- and there are 4x the blocks.
+    __shared__ float part[32][8][32];
     const int H2p = (H2 + 3) & ~3, Q = 4 * H;
-    const int nqb = (Q + 127) / 128;
+    const int nqb = (Q + 31) / 32;
     const int bid = bx - nmain, qb = bid % nqb, kb = bid / nqb;
-    const int ql = threadIdx.x & 127, q = qb * 128 + ql, sl = threadIdx.x >> 7, k0 = kb * 8;
-    const int Bs = (B + 7) / 8;
-    const int ga = sl * Bs, gb = (ga + Bs < B) ? ga + Bs : B;
+    const int ql = threadIdx.x & 31, q = qb * 32 + ql, sl = threadIdx.x >> 5, k0 = kb * 8;
+    const int Bs = (B + 31) / 32;
+    const int ga = sl * Bs < B ? sl * Bs : B, gb = (ga + Bs < B) ? ga + Bs : B;
     float acc[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[j] = 0.f;
@@ -151,14 +162,12 @@ __global__ void __launch_bounds__(kRedThreads) reduce_tc_kernel(GradLayout gl, i
 #pragma unroll
     for (int j = 0; j < 8; ++j) part[sl][j][ql] = acc[j];
     __syncthreads();
-    if (sl == 0 && q < Q) {
+    if (sl < 8 && q < Q) {                   // warp j sums output row k0 + j over the 32 ranges, in range order
+      const int j = sl;
+      float u = part[0][j][ql];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        float u = part[0][j][ql];
-#pragma unroll
-        for (int t = 1; t < 8; ++t) u += part[t][j][ql];
-        if (k0 + j < H2) out[gl.gv0 + (int64_t)(k0 + j) * Q + q] = u;
-      }
+      for (int t = 1; t < 32; ++t) u += part[t][j][ql];
+      if (k0 + j < H2) out[gl.gv0 + (int64_t)(k0 + j) * Q + q] = u;
     }
     return;
   }
@@ -185,8 +194,8 @@ int launch_reduce_tc(const Dims& d, const float* small_rec, const int* ntiles, c
   grad_layout(d, &gl);
   int blocks = (int)((gl.total + kRedThreads - 1) / kRedThreads);
   if (blocks > 592) blocks = 592;
-  const int gv0_blocks = ((4 * d.H + 127) / 128) * ((d.H2 + 7) / 8);
-  const int small_blocks = (int)((gl.total - gl.gb + 127) / 128);
+  const int gv0_blocks = ((4 * d.H + 31) / 32) * ((d.H2 + 7) / 8);
+  const int small_blocks = (int)((d.Hp + (gl.gv0 - gl.g0) + (gl.total - gl.gv0b) + 31) / 32);   // the live ranges, compact
   TdLossArgs tdl{};
   if (td) tdl = *td;
   reduce_tc_kernel<<<blocks + gv0_blocks + small_blocks + (td ? 1 : 0), kRedThreads, 0, st>>>(
