@@ -35,3 +35,9 @@ al, tl, wl = [u.to(dev) for u in loss_inputs(gl)]
 l3 = big_l.train_step(bl.x, bl.edge_index, bl.batch, bl.ptr, action=al, target=tl, weight=wl)[0]
 torch.cuda.synchronize()
 print("ok", float(loss), float(out["loss"]), float(l3), int(cb.x.shape[0]), bool(torch.isfinite(qb).all()))
+# round-1 additions: noisy-nets advantage layer (compose / chain-rule kernels) and the input gradient (hexgnn_backward_dx)
+nz = ModernTwoHeaded(35, 10, 2, noisy_dqn=True).to(dev)
+xg = b.x.clone().requires_grad_(True)
+ops.td_loss(nz(xg, b.edge_index, b.batch, b.ptr), b.ptr, a, tg, w)[0].backward()
+torch.cuda.synchronize()
+print("ok noisy + dx", float(xg.grad.abs().max()), float(nz.maker_head.linear.weight_sigma.grad.abs().max()))
