@@ -308,8 +308,10 @@ int launch_build_csr(const int64_t* edge_index, int64_t E, const int64_t* batch,
     if (coop_max >= 2 && nscan < grid && grid <= coop_max) {
       int Ni = (int)N, Ei = (int)E, Bi = (int)B, te = tile_rows * kEdgeCapPerRow, ns = nscan;
       void* args[] = {&v, (void*)&edge_index, (void*)&batch, (void*)&ptr, &Ni, &Ei, &Bi, &tile_rows, &te, &ns};
-      HEX_CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)csr_build_fused_kernel, dim3(grid), dim3(threads), args, 0, st));
-      return HEXGNN_OK;
+      if (cudaLaunchCooperativeKernel((const void*)csr_build_fused_kernel, dim3(grid), dim3(threads), args, 0, st) == cudaSuccess)
+        return HEXGNN_OK;
+      (void)cudaGetLastError();   // refused (e.g. a context that cannot guarantee co-residency): use the five-launch path
+      coop_max = 0;               // from now on
     }
   }
   csr_init_kernel<<<blocks(init_n), threads, 0, st>>>(v, batch, ptr, (int)N, (int)B);
