@@ -292,7 +292,7 @@ int launch_build_csr(const int64_t* edge_index, int64_t E, const int64_t* batch,
           cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, csr_build_fused_kernel, threads, 0) == cudaSuccess)
       {
         int cap = 2;                                       // two blocks per SM: more only lengthens the barriers
-        if (const char* e = getenv("HEXGNN_CSR_BLOCKS_PER_SM")) { const int c = atoi(e); if (c >= 1 && c <= 8) cap = c; }
+        if (const char* e = getenv("HEXGNN_CSR_BLOCKS_PER_SM")) { const int c = atoi(e); if (c >= 0 && c <= 8) cap = c; }   // 0: five-launch path only
         coop_max = sms * (per_sm > cap ? cap : per_sm);
       }
       else

@@ -802,3 +802,25 @@ def test_full_size_headline_batch_properties():
     assert rel_err(q_p, q_back) <= 2e-6           # (not bit-exact: a row's position in its tile sets the order of its sums)
     assert rel_err(m.flat_gradient, g1) <= REL_TOL
     assert abs(float(loss_p) - float(loss)) <= 1e-6 * abs(float(loss))
+
+
+def test_csr_five_launch_path_in_subprocess():
+    """The builder's fallback (five phase kernels, used when a cooperative launch is refused or the grid cannot be
+    co-resident) stays bit-exact: HEXGNN_CSR_BLOCKS_PER_SM=0 disables the fused kernel for one process."""
+    import os, subprocess, sys
+    code = (
+        "import sys, torch; sys.path.insert(0, 'tests')\n"
+        "from gnn_hex_b200 import data, ops\n"
+        "from oracle import hexgnn_oracle as orc\n"
+        "for f in ('pos_11x11_seed1234.npz', 'pos_mix_5_13_seed1234.npz'):\n"
+        "    b = data.collate(data.load_positions(f, maker=1)); d = b.to('cuda:0')\n"
+        "    c0 = ops.launch_counter\n"
+        "    csr = ops.build_csr(d.edge_index, d.batch, d.ptr, num_nodes=b.x.shape[0])\n"
+        "    rowptr, col = orc.csr_by_destination(b.edge_index, b.x.shape[0])\n"
+        "    assert torch.equal(csr.rowptr.cpu(), rowptr) and torch.equal(csr.col.cpu(), col)\n"
+        "    assert torch.equal(csr.gptr.cpu().long(), b.ptr) and int(csr.ntiles.item()) > 0\n"
+        "print('FIVE_LAUNCH_OK')\n")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, HEXGNN_CSR_BLOCKS_PER_SM="0", PYTHONPATH=root)
+    r = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=300)
+    assert "FIVE_LAUNCH_OK" in r.stdout, r.stdout + r.stderr
