@@ -3,14 +3,21 @@
 Pure torch (no torch_geometric / torch_scatter: neither is installable here), fp32 or fp64.
 Every function cites the reference lines it restates (paths relative to /root/reference).
 
-Parity status: the reference holds NO golden vector for the model numerics, and
-torch_geometric 2.2.0 / torch_scatter 2.1.0 (environment.yml:139,151) are absent, so the model
-half of this oracle is **parity unpinned** against the real PyG kernels.  It is pinned instead by
-(i) a hand-computed known answer on the reference's ``Debugging_manager`` graph
-(graph_game/multi_env_manager.py:170-175), (ii) fp64 gradcheck, (iii) batched == per-graph,
-permutation equivariance and edge-order invariance (tests/test_oracle.py).  The graph half
-(topology, edge_index, collate) IS pinned: fixtures under tests/golden/ come from the reference's
-own C++ game compiled unchanged (oracle/refgame/Makefile -> oracle/_ref/hexgen).
+Parity status.  The reference holds NO golden vector for the model numerics, so the
+pin is made here: the reference's OWN module code (GN0/models.py, unmodified, where it lies) is executed on a
+test-only stand-in for torch_geometric / torch_scatter (oracle/pyg_stub/) and (a) its outputs and gradients
+on the committed positions are committed as golden vectors (tests/golden/model_*.npz, made by
+tests/golden/make_model_fixtures.py) which this oracle must reproduce (tests/test_reference_pin.py, runs
+anywhere), and (b) wherever /root/reference is mounted the same tests run the reference classes live
+(`DuellingTwoHeaded`, `cachify_gnn(GraphSAGE)`, `HeadNetwork`, `MLP`, `FactorizedNoisyLinear`, growth).
+What stays **unpinned** is only the third-party PRIMITIVES the stub restates: PyG 2.2.0
+`SAGEConv.propagate` (the reference's own restatement: GN0/torch_script_models.py:52-73), `LayerNorm`
+and torch_scatter 2.1.0 `scatter` -- those libraries (environment.yml:139,151) are not installable here.
+Further self-checks: a hand-computed known answer on the reference's ``Debugging_manager`` graph
+(graph_game/multi_env_manager.py:170-175), fp64 gradcheck, batched == per-graph, permutation
+equivariance and edge-order invariance (tests/test_oracle.py).  The graph half (topology, edge_index,
+collate) is pinned by fixtures from the reference's own C++ game compiled unchanged
+(oracle/refgame/Makefile -> oracle/_ref/hexgen).
 """
 from __future__ import annotations
 
@@ -227,11 +234,33 @@ def sage_conv(x, edge_index, w_l, b_l, w_r):
     return F.linear(mean, w_l, b_l) + F.linear(x, w_r)
 
 
-class _SageStack(torch.nn.Module):
-    """``cachify_gnn(GraphSAGE)`` with norm=None, dropout=0, act='relu', out_channels=None
-    (GN0/models.py:144-160,261-294): ReLU after EVERY layer incl. the last."""
+def layer_norm_graph(x, weight, bias, eps: float = 1e-5):
+    """PyG 2.2.0 ``LayerNorm(mode='graph')`` called WITHOUT a batch vector, as the reference does
+    (GN0/models.py:285 ``self.norms[i](x)``, :551 ``self.after_embed_norm(embeds)``): the statistics run over
+    ALL nodes and channels of the batch; eps is added to the standard deviation, not the variance."""
+    x = x - x.mean()
+    out = x / (x.std(unbiased=False) + eps)
+    return out * weight + bias
 
-    def __init__(self, in_channels: int, hidden: int, num_layers: int):
+
+class _NormParams(torch.nn.Module):
+    """Affine parameters named like PyG ``LayerNorm``: weight (ones), bias (zeros)."""
+
+    def __init__(self, channels: int):
+        super().__init__()
+        self.weight = torch.nn.Parameter(torch.ones(channels))
+        self.bias = torch.nn.Parameter(torch.zeros(channels))
+
+    def forward(self, x):
+        return layer_norm_graph(x, self.weight, self.bias)
+
+
+class _SageStack(torch.nn.Module):
+    """``cachify_gnn(GraphSAGE)`` with dropout=0, act='relu', act_first=False, out_channels=None
+    (GN0/models.py:144-160,261-294): per layer conv -> [norm] -> ReLU, after EVERY layer incl. the last
+    (with ``norm`` the subclass appends one more norm for the last layer, :158-162)."""
+
+    def __init__(self, in_channels: int, hidden: int, num_layers: int, norm: bool = False):
         super().__init__()
         self.hidden_channels = hidden
         self.num_layers = num_layers
@@ -244,10 +273,14 @@ class _SageStack(torch.nn.Module):
             c.lin_l = torch.nn.Linear(cin, hidden, bias=True)
             c.lin_r = torch.nn.Linear(cin, hidden, bias=False)
             self.convs.append(c)
+        self.norms = torch.nn.ModuleList([_NormParams(hidden) for _ in range(num_layers)]) if norm else None
 
     def forward(self, x, edge_index):
-        for c in self.convs:
-            x = F.relu(sage_conv(x, edge_index, c.lin_l.weight, c.lin_l.bias, c.lin_r.weight))
+        for i, c in enumerate(self.convs):
+            x = sage_conv(x, edge_index, c.lin_l.weight, c.lin_l.bias, c.lin_r.weight)
+            if self.norms is not None:
+                x = self.norms[i](x)
+            x = F.relu(x)
         return x
 
     @staticmethod
@@ -371,9 +404,10 @@ class _Head(torch.nn.Module):
     """``HeadNetwork`` (GN0/models.py:318-334,368-384) with value_head_type='mlp',
     value_aggr_types=('sum','max','min','mean'); ``noisy_dqn`` swaps the advantage Linear (:331-334)."""
 
-    def __init__(self, hidden: int, num_layers: int, noisy_dqn: bool = False, noise_sigma: float = 0.0):
+    def __init__(self, hidden: int, num_layers: int, noisy_dqn: bool = False, noise_sigma: float = 0.0,
+                 norm: bool = False):
         super().__init__()
-        self.gnn = _SageStack(hidden, hidden, num_layers)
+        self.gnn = _SageStack(hidden, hidden, num_layers, norm=norm)
         self.linear = NoisyLinearOracle(hidden, 1, noise_sigma) if noisy_dqn else torch.nn.Linear(hidden, 1)
         self.value_head = _MLP(hidden // 2, 4 * hidden, 1)
         self.hidden_channels = hidden
@@ -399,16 +433,18 @@ class _Head(torch.nn.Module):
 
 
 class ModernTwoHeadedOracle(torch.nn.Module):
-    """``get_pre_defined('modern_two_headed', args)`` with norm=False, noisy_dqn=False
-    (GN0/models.py:928-947 -> DuellingTwoHeaded :477-590).  Parameter names follow PyG 2.2.0 /
+    """``get_pre_defined('modern_two_headed', args)`` (GN0/models.py:928-947 -> DuellingTwoHeaded :477-590),
+    incl. ``args.norm`` (PyG LayerNorm, whole-batch statistics) and ``args.noisy_dqn``.  Parameter names follow PyG 2.2.0 /
     the reference attribute accesses so state_dicts interchange with the product module."""
 
     def __init__(self, hidden_channels: int, num_layers: int, num_head_layers: int = 2, noisy_dqn: bool = False,
-                 noisy_sigma0: float = 0.5):
+                 noisy_sigma0: float = 0.5, norm: bool = False):
         super().__init__()
-        self.gnn = _SageStack(2, hidden_channels, num_layers)
-        self.maker_head = _Head(hidden_channels, num_head_layers, noisy_dqn, noisy_sigma0)
-        self.breaker_head = _Head(hidden_channels, num_head_layers, noisy_dqn, noisy_sigma0)
+        self.gnn = _SageStack(2, hidden_channels, num_layers, norm=norm)
+        # models.py:480-483: with ``norm`` one more LayerNorm between body and heads (:550-551), no ReLU after it
+        self.after_embed_norm = _NormParams(hidden_channels) if norm else None
+        self.maker_head = _Head(hidden_channels, num_head_layers, noisy_dqn, noisy_sigma0, norm=norm)
+        self.breaker_head = _Head(hidden_channels, num_head_layers, noisy_dqn, noisy_sigma0, norm=norm)
         self.final_conv_acts = None
 
     def grow_depth(self, additional_layers):                                   # models.py:494-495
@@ -428,6 +464,8 @@ class ModernTwoHeadedOracle(torch.nn.Module):
             graph_indices = torch.zeros(x.size(0), dtype=torch.long, device=x.device)
         num_graphs = int(graph_indices.max()) + 1 if graph_indices.numel() else 0
         embeds = self.gnn(x, edge_index)
+        if self.after_embed_norm is not None:                                  # models.py:550-551
+            embeds = self.after_embed_norm(embeds)
         self.final_conv_acts = embeds
         head = self.maker_head if is_maker == 1 else self.breaker_head        # models.py:556-565
         res = head(embeds, edge_index, graph_indices, num_graphs, advantages_only=advantages_only)

@@ -1,8 +1,18 @@
 """Shared helpers for the parity tests (test infrastructure; may import oracle/)."""
+import os
+import sys
+import zlib
+
+import numpy as np
 import torch
 
 from gnn_hex_b200 import ModernTwoHeaded, data
 from oracle import hexgnn_oracle as orc
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
+REFERENCE_ROOT = "/root/reference"
+PYG_STUB = os.path.join(ROOT, "oracle", "pyg_stub")
 
 REL_TOL = 1e-5  # BASELINE.json north_star: 1e-5 relative (fp32) on Q-values and gradients
 # Per-tensor bound on the kernel's distance from the fp64 truth, in units of the fp32 ORACLE's own
@@ -85,3 +95,63 @@ def grad_errs(model, oracle, oracle_fp64=None):
         if e > worst:
             worst, name_worst = e, name
     return glob, worst, name_worst
+
+
+# ---- the reference's own module code (GN0/models.py, unmodified) on the test-only PyG stand-in -----------------------
+def import_reference_models():
+    """`GN0.models` of the reference, imported where it lies with oracle/pyg_stub/ standing in for torch_geometric /
+    torch_scatter (absent from the image).  Returns None when /root/reference is not mounted (the GPU box): callers skip
+    and rely on the committed golden vectors (tests/golden/model_*.npz) instead."""
+    if not os.path.isdir(os.path.join(REFERENCE_ROOT, "GN0")):
+        return None
+    for p in (REFERENCE_ROOT, PYG_STUB):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import GN0.models as ref_models
+    return ref_models
+
+
+def hash_uniform(name: str, shape, seed: int = 0) -> torch.Tensor:
+    """U(-1, 1) values that depend only on (name, seed, element index): splitmix64 in integer arithmetic, so the golden
+    weights are reproducible on any box / library version without being stored."""
+    n = int(np.prod(shape)) if len(shape) else 1
+    start = (zlib.crc32(name.encode()) * 0x9E3779B97F4A7C15 + seed * 0xD1B54A32D192ED03) & 0xFFFFFFFFFFFFFFFF
+    with np.errstate(over="ignore"):
+        z = np.arange(n, dtype=np.uint64) * np.uint64(0x9E3779B97F4A7C15) + np.uint64(start)
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        z = z ^ (z >> np.uint64(31))
+    u = (z >> np.uint64(11)).astype(np.float64) * (2.0 ** -53)
+    return torch.from_numpy((2.0 * u - 1.0).astype(np.float32)).reshape(tuple(shape))
+
+
+@torch.no_grad()
+def set_hash_weights(module: torch.nn.Module, seed: int = 0) -> None:
+    """Fill every parameter / buffer of `module` by NAME (same names in the reference model, the oracle and the product
+    module): matrices U(+-1/sqrt(fan_in)) like the default init, vectors U(+-0.1), LayerNorm weights 1 + U(+-0.2)."""
+    for name, t in list(module.named_parameters()) + list(module.named_buffers()):
+        u = hash_uniform(name, t.shape, seed)
+        if t.dim() >= 2:
+            v = u / float(t.shape[-1]) ** 0.5
+        elif "norm" in name and name.endswith("weight"):
+            v = 1.0 + 0.2 * u
+        else:
+            v = 0.1 * u
+        t.copy_(v.to(t.dtype))
+
+
+def load_model_fixture(tag: str):
+    """tests/golden/model_<tag>.npz as a dict (made by tests/golden/make_model_fixtures.py from the reference's code)."""
+    z = np.load(os.path.join(GOLDEN_DIR, f"model_{tag}.npz"), allow_pickle=False)
+    return {k: z[k] for k in z.files}
+
+
+def flat_named(module, what="grad", names=None):
+    """Concatenate `p.grad` (zeros for None) or `p` over named_parameters, in sorted-name order -> float64 numpy."""
+    d = dict(module.named_parameters())
+    out = []
+    for k in (names if names is not None else sorted(d)):
+        p = d[k]
+        t = p if what == "param" else (p.grad if p.grad is not None else torch.zeros_like(p))
+        out.append(t.detach().double().cpu().reshape(-1))
+    return torch.cat(out).numpy()
