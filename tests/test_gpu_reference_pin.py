@@ -1,0 +1,58 @@
+"""GPU: the CUDA path (through the C-ABI) against the golden vectors the reference's OWN module code produced
+(tests/golden/model_*.npz, made by tests/golden/make_model_fixtures.py from GN0/models.py on the test-only PyG stand-in).
+No oracle in between: same hashed weights, same committed positions, the reference's outputs and gradients."""
+import numpy as np
+import pytest
+import torch
+
+import helpers
+from gnn_hex_b200 import ModernTwoHeaded, data
+
+pytestmark = pytest.mark.gpu
+
+CASES = {
+    "S": (35, 10, 2, False, "pos_7x7_seed1234.npz"),
+    "L": (110, 15, 2, False, "pos_11x11_seed1234.npz"),
+    "S_noisy": (35, 10, 2, True, "pos_7x7_seed1234.npz"),
+}
+TOL = 1e-5   # BASELINE.json north_star: 1e-5 relative (fp32) on Q-values and gradients
+
+
+def rel(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-30))
+
+
+@pytest.mark.parametrize("tag", list(CASES))
+@pytest.mark.parametrize("maker", [1, 0])
+def test_cuda_path_equals_reference_golden_vectors(tag, maker):
+    H, L, Lh, noisy, pos = CASES[tag]
+    fx = helpers.load_model_fixture(tag)
+    b = data.collate(data.load_positions(pos, maker=maker)[:int(fx["count"])])
+    m = ModernTwoHeaded(H, L, Lh, noisy_dqn=noisy, noisy_sigma0=0.5)
+    helpers.set_hash_weights(m, seed=0)
+    names = [str(n) for n in fx["names"]]
+    assert sorted(dict(m.named_parameters())) == names
+    m = m.cuda()
+    d = b.to("cuda")
+    action, target, weight = (torch.from_numpy(fx[k]).cuda() for k in ("action", "target", "weight"))
+    q = m(d.x, d.edge_index, d.batch, d.ptr)
+    emb = m.final_conv_acts.detach().cpu().numpy()
+    loss = torch.mean(weight * (target - q[action + d.ptr[:-1]]) ** 2)      # rainbow.py:301-312
+    loss.backward()
+    with torch.no_grad():
+        adv = m(d.x, d.edge_index, d.batch, d.ptr, advantages_only=True)
+        v, c = m(d.x, d.edge_index, d.batch, d.ptr, seperate=True)
+    torch.cuda.synchronize()
+    assert int(m.last_csr.status.item()) == 0
+    assert rel(q.detach().cpu().numpy(), fx[f"q_{maker}"]) <= TOL
+    assert rel(q.detach().cpu().numpy(), fx[f"q64_{maker}"]) <= TOL
+    assert adv.shape == (b.x.shape[0], 1) and rel(adv.cpu().numpy(), fx[f"adv_{maker}"]) <= TOL
+    assert rel(v.cpu().numpy(), fx[f"value_{maker}"]) <= TOL and rel(c.cpu().numpy(), fx[f"centred_{maker}"]) <= TOL
+    assert rel(emb[:: max(1, emb.shape[0] // 64)], fx[f"embeds_{maker}"]) <= TOL
+    assert rel(loss.detach().cpu().numpy(), fx[f"loss_{maker}"]) <= TOL
+    g = helpers.flat_named(m, "grad", names)[:: int(fx["gstride"])]
+    gmax = float(fx[f"gradmax_{maker}"])
+    err = float(np.abs(g - fx[f"grad64_{maker}"]).max()) / gmax          # the fp64 reference run is the truth
+    assert err <= TOL, err
+    assert float(np.abs(g - fx[f"grad_{maker}"]).max()) / gmax <= TOL
