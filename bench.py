@@ -26,6 +26,8 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
+if os.path.join(ROOT, "tests") not in sys.path:
+    sys.path.insert(1, os.path.join(ROOT, "tests"))     # tests/positions.py: the committed position fixtures (bench inputs)
 
 METRIC = "Hex graphs/sec (fwd+bwd, GNN-L 11x11 b256)"
 UNIT = "graphs/s"
@@ -66,10 +68,11 @@ def peaks():
 def make_batch(workload, rank=0):
     """256 positions per rank.  Rank r rotates the fixture by 32*r so shards differ."""
     from gnn_hex_b200 import data
+    import positions
     if workload == "empty":
-        gs = [data.empty_board(11, 1)] * BATCH
+        gs = [positions.empty_board(11, 1)] * BATCH
     else:
-        gs = data.load_positions(FIXTURE, maker=1)
+        gs = positions.load_positions(FIXTURE, maker=1)
         k = (32 * rank) % len(gs)
         gs = (gs[k:] + gs[:k])[:BATCH]
     return data.collate(gs)

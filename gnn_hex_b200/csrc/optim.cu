@@ -12,6 +12,10 @@
 // every step (the reference's torch 1.13 `opt.zero_grad()` leaves ZERO gradients, not None: Adam keeps applying the
 // momentum) unless HEXGNN_ADAM_SKIP_UNTAKEN is set (torch >= 2.0 `set_to_none=True` semantics: untouched while not taken).
 // Deterministic: fixed-order two-level sum of squares, every block re-reduces the same partials.
+// Guard (no reference counterpart; the reference has no size limit to trip over): a non-finite global norm -- e.g. the NaN
+// record a tile poisons when a graph exceeds the tile capacity -- skips the WHOLE step: parameters, moments, the in-place
+// clip and the step counters stay untouched, `grad_norm` reports the non-finite value.  The norm kernel therefore only
+// PROPOSES the new counters (in the workspace); block 0 of the apply kernel commits them once the norm is known.
 #include "common.cuh"
 
 namespace hexgnn {
@@ -21,8 +25,8 @@ constexpr int kOptBlocks = 296;   // 2 x 148
 
 // state (int32): [0] body steps, [1] maker-head steps, [2] breaker-head steps, [3] spare
 __global__ void __launch_bounds__(kOptThreads) adam_norm_kernel(const float* __restrict__ g, int64_t n, const float* __restrict__ x,
-                                                                int* __restrict__ state, int skip_untaken,
-                                                                float* __restrict__ partial) {
+                                                                const int* __restrict__ state, int skip_untaken,
+                                                                float* __restrict__ partial, int* __restrict__ proposed) {
   __shared__ float red[kOptThreads];
   const int tid = threadIdx.x;
   const int64_t per = (n + gridDim.x - 1) / gridDim.x;
@@ -43,19 +47,22 @@ __global__ void __launch_bounds__(kOptThreads) adam_norm_kernel(const float* __r
   if (tid == 0) partial[blockIdx.x] = red[0];
   if (blockIdx.x == 0 && tid == 0) {
     const int taken = (x[2] == 1.0f) ? 1 : 2;           // maker head : breaker head (models.py:556)
-    state[0] += 1;
+    proposed[0] = state[0] + 1;
     for (int h = 1; h <= 2; ++h) {
-      if (h == taken) state[h] += 1;
-      else if (state[h] > 0 && !skip_untaken) state[h] += 1;
+      int t = state[h];
+      if (h == taken) t += 1;
+      else if (t > 0 && !skip_untaken) t += 1;
+      proposed[h] = t;
     }
-    state[3] = taken;
+    proposed[3] = taken;
   }
 }
 
 struct AdamArgs {
   float* p; float* g; float* m; float* v;
   int64_t n, seg1, seg2;          // [0, seg1) body, [seg1, seg2) maker head, [seg2, n) breaker head
-  const int* state;
+  int* state;
+  const int* proposed;            // counters of THIS step (adam_norm_kernel), committed to `state` when the norm is finite
   const float* partial; int nparts;
   float lr, beta1, beta2, eps, max_norm;
   int skip_untaken;
@@ -65,6 +72,7 @@ struct AdamArgs {
 __global__ void __launch_bounds__(kOptThreads) adam_apply_kernel(const AdamArgs a) {
   __shared__ float red[kOptThreads];
   __shared__ float clip_s;
+  __shared__ int ok_s;
   const int tid = threadIdx.x;
   float s = 0.f;
   for (int i = tid; i < a.nparts; i += kOptThreads) s += a.partial[i];   // same order in every block
@@ -79,17 +87,23 @@ __global__ void __launch_bounds__(kOptThreads) adam_apply_kernel(const AdamArgs 
     float c = 1.f;
     if (a.max_norm > 0.f) { c = a.max_norm / (norm + 1e-6f); if (c > 1.f) c = 1.f; }
     clip_s = c;
+    ok_s = isfinite(norm) ? 1 : 0;
     if (blockIdx.x == 0 && a.grad_norm) a.grad_norm[0] = norm;
+    if (blockIdx.x == 0 && ok_s) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) a.state[k] = a.proposed[k];   // nobody reads `state` in this launch
+    }
   }
   __syncthreads();
+  if (!ok_s) return;                                            // non-finite gradient: the step does not happen
   const float clip = clip_s;
   // per-segment scalars, computed in double like the Python side of torch.optim.Adam
   float step_size[3], bc2s[3];
   bool on[3];
-  const int taken = a.state[3];
+  const int taken = a.proposed[3];
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
-    const int t = a.state[k];
+    const int t = a.proposed[k];
     on[k] = t > 0 && !(a.skip_untaken && k > 0 && k != taken);
     const double bc1 = 1.0 - pow((double)a.beta1, (double)(t > 0 ? t : 1));
     const double bc2 = 1.0 - pow((double)a.beta2, (double)(t > 0 ? t : 1));
@@ -114,11 +128,12 @@ __global__ void __launch_bounds__(kOptThreads) adam_apply_kernel(const AdamArgs 
 int launch_adam_step(const Dims& d, const ParamMap& pm, float* params, float* grads, float* exp_avg, float* exp_avg_sq,
                      int* state, const float* x, float lr, float beta1, float beta2, float eps, float max_norm,
                      int skip_untaken, float* grad_norm, float* ws, cudaStream_t st) {
-  adam_norm_kernel<<<kOptBlocks, kOptThreads, 0, st>>>(grads, pm.total, x, state, skip_untaken, ws);
+  int* proposed = (int*)(ws + kOptBlocks);
+  adam_norm_kernel<<<kOptBlocks, kOptThreads, 0, st>>>(grads, pm.total, x, state, skip_untaken, ws, proposed);
   AdamArgs a;
   a.p = params; a.g = grads; a.m = exp_avg; a.v = exp_avg_sq;
   a.n = pm.total; a.seg1 = sage_wl(pm, 0, d.L); a.seg2 = sage_wl(pm, 1, d.L);
-  a.state = state; a.partial = ws; a.nparts = kOptBlocks;
+  a.state = state; a.proposed = proposed; a.partial = ws; a.nparts = kOptBlocks;
   a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.max_norm = max_norm;
   a.skip_untaken = skip_untaken; a.grad_norm = grad_norm;
   adam_apply_kernel<<<kOptBlocks, kOptThreads, 0, st>>>(a);
@@ -126,6 +141,6 @@ int launch_adam_step(const Dims& d, const ParamMap& pm, float* params, float* gr
   return HEXGNN_OK;
 }
 
-int adam_ws_floats() { return kOptBlocks; }
+int adam_ws_floats() { return kOptBlocks + 4; }
 
 }  // namespace hexgnn

@@ -1,5 +1,5 @@
 """Host-side data plumbing of the hot path: Hex position graphs in the reference's tensor layout,
-the PyG-style collate, and the committed position fixtures.
+and the PyG-style collate (host and device).
 
 Layout mirrors `convert_node_switching_game(..., old_style=True)` (GN0/util/convert_graph.py:77-85,
 99-117): x[n,3] = [degree, is_terminal (rows 0,1), maker flag], edge_index = cat(E, flip(E)) int64,
@@ -11,9 +11,6 @@ from typing import List, Sequence
 
 import numpy as np
 import torch
-
-GOLDEN_DIR = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
-
 
 class HexGraph(SimpleNamespace):
     """x [n,3] float32, edge_index [2,E] int64 (symmetric)."""
@@ -82,32 +79,6 @@ def graph_from_directed(n: int, src: np.ndarray, dst: np.ndarray, maker: int) ->
     x[1, 1] = 1
     x[:, 2] = float(maker)
     return HexGraph(x=x, edge_index=edge_index)
-
-
-def load_positions(name: str, maker=None) -> List[HexGraph]:
-    """Load tests/golden/<name>.npz (positions played by the reference's own C++ game)."""
-    path = name if os.path.exists(name) else os.path.join(GOLDEN_DIR, name)
-    z = np.load(path)
-    out, eo = [], 0
-    for g in range(len(z["n"])):
-        ne = int(z["ne"][g])
-        m = int(z["maker"][g]) if maker is None else int(maker)
-        out.append(graph_from_directed(int(z["n"][g]), z["src"][eo:eo + ne], z["dst"][eo:eo + ne], m))
-        eo += ne
-    return out
-
-
-def empty_board(size: int, maker: int = 1) -> HexGraph:
-    """Empty size x size board (graph_game/hex_board_game.py:214-232, red graph), from the
-    committed reference dump for sizes 3..13."""
-    z = np.load(os.path.join(GOLDEN_DIR, "empty_boards_3_13.npz"))
-    sizes = list(z["size"])
-    if size not in sizes:
-        raise ValueError(f"no committed empty board of size {size}")
-    g = sizes.index(size)
-    eo = int(z["ne"][:g].sum())
-    ne = int(z["ne"][g])
-    return graph_from_directed(int(z["n"][g]), z["src"][eo:eo + ne], z["dst"][eo:eo + ne], maker)
 
 
 def collate(graphs: Sequence[HexGraph]) -> HexBatch:

@@ -128,29 +128,31 @@ class FactorizedNoisyLinear(nn.Module):
         self.reset_noise()
 
     @torch.no_grad()
-    def reset_parameters(self) -> None:          # models.py:105-114
-        scale = 1 / self.in_features ** 0.5
-        nn.init.uniform_(self.weight_mu, -scale, scale)
-        nn.init.uniform_(self.bias_mu, -scale, scale)
-        nn.init.constant_(self.weight_sigma, self.sigma_0 * scale)
-        nn.init.constant_(self.bias_sigma, self.sigma_0 * scale)
+    def reset_parameters(self) -> None:
+        """Reference init (models.py:105-114): mu ~ U(+-1/sqrt(fan_in)), sigma = sigma_0 / sqrt(fan_in); weight first,
+        then bias, so a seeded construction draws the same numbers as the reference class."""
+        bound = self.in_features ** -0.5
+        for mu, sigma in ((self.weight_mu, self.weight_sigma), (self.bias_mu, self.bias_sigma)):
+            mu.uniform_(-bound, bound)
+            sigma.fill_(self.sigma_0 * bound)
 
     @torch.no_grad()
-    def _get_noise(self, size: int):             # models.py:116-120: f(x) = sgn(x) sqrt(|x|)
-        noise = torch.randn(size, device=self.weight_mu.device)
-        return noise.sign().mul_(noise.abs().sqrt_())
+    def reset_noise(self) -> None:
+        """Fresh factorised Gaussian noise (models.py:116-128; NoisyNets eq. 10-11): with f(z) = sgn(z) sqrt|z|,
+        eps_w = f(z_out) f(z_in)^T and eps_b = f(z_out); z_in is drawn before z_out, as in the reference."""
+        dev = self.weight_mu.device
+        z_in = torch.randn(self.in_features, device=dev)
+        z_out = torch.randn(self.out_features, device=dev)
+        f_in = torch.copysign(z_in.abs().sqrt(), z_in)
+        f_out = torch.copysign(z_out.abs().sqrt(), z_out)
+        torch.outer(f_out, f_in, out=self.weight_epsilon)
+        self.bias_epsilon.copy_(f_out)
 
     @torch.no_grad()
-    def reset_noise(self) -> None:               # models.py:122-128
-        epsilon_in = self._get_noise(self.in_features)
-        epsilon_out = self._get_noise(self.out_features)
-        self.weight_epsilon.copy_(epsilon_out.outer(epsilon_in))
-        self.bias_epsilon.copy_(epsilon_out)
-
-    @torch.no_grad()
-    def disable_noise(self) -> None:             # models.py:130-133
-        self.weight_epsilon[:] = 0
-        self.bias_epsilon[:] = 0
+    def disable_noise(self) -> None:
+        """Evaluation with the mean weights (models.py:130-133)."""
+        self.weight_epsilon.zero_()
+        self.bias_epsilon.zero_()
 
     def forward(self, input):
         raise _lib.HexGnnError("FactorizedNoisyLinear is evaluated inside the fused kernels (call the owning model)")
@@ -351,8 +353,45 @@ class ModernTwoHeaded(nn.Module):
             self._desc = _lib.make_desc(H, L, Lm)
             self._shape_sig = sig
             self._flat = None
-        if self._flat is None or self._flat.device != self.gnn.convs[0].lin_l.weight.device:
+        if self._flat is None or self._flat.device != self.gnn.convs[0].lin_l.weight.device or not self._aliased():
             self._flatten()
+
+    def _aliased(self):
+        """True while the named parameters still ARE views of the flat buffer.  `copy.deepcopy(model)` / pickling clone
+        every Parameter (`Parameter.__deepcopy__`), after which `load_state_dict`, optimizers and target syncs would
+        change the names while the kernels kept reading a stale buffer: detected here (two pointer compares per call)
+        and repaired by re-flattening."""
+        ps, sl, base = getattr(self, "_params_cache", None), self._slices, self._flat.data_ptr()
+        if not ps or not sl or len(ps) != len(sl):
+            return False
+        now = self._ordered_params()
+        for i in (0, len(ps) - 1):
+            if now[i] is not ps[i] or ps[i].data_ptr() != base + 4 * sl[i][0]:
+                return False
+        if self._noisy is not None:
+            lin = self.maker_head.linear
+            if lin.weight_mu.data_ptr() != self._noisy.data_ptr():
+                return False
+        return True
+
+    def __deepcopy__(self, memo):
+        """A deep copy starts un-flattened (its first call re-flattens its own parameter clones) and shares no workspace,
+        gradient buffer or peer-memory handle with the original."""
+        import copy
+        cls = self.__class__
+        new = cls.__new__(cls)
+        memo[id(self)] = new
+        skip = {"_flat", "_slices", "_ws", "_flat_grad", "_grad_views", "_p2p", "_noisy", "_noisy_grad", "_noisy_params",
+                "_noisy_views", "_params_cache", "last_csr", "final_conv_acts", "final_conv_grads"}
+        for k, v in self.__dict__.items():
+            if k not in skip:
+                new.__dict__[k] = copy.deepcopy(v, memo)
+        new._flat = new._slices = new._flat_grad = new._p2p = new._noisy = new._noisy_grad = None
+        new._ws, new._grad_views, new._noisy_params, new._params_cache = {}, {}, [], None
+        new.last_csr = new.final_conv_acts = new.final_conv_grads = None
+        for p in new.parameters():
+            p.grad = None
+        return new
 
     def _apply(self, fn, *args, **kwargs):
         out = super()._apply(fn, *args, **kwargs)
@@ -526,8 +565,18 @@ class ModernTwoHeaded(nn.Module):
             self._flat_grad = p2p["red"]          # p.grad now alias the reduced (private) buffer
             self._point_grads()
             p2p["k"] = k ^ 1
+            self._allreduce_noisy(group)
             return
         dist.all_reduce(self._flat_grad, op=dist.ReduceOp.SUM, group=group)
+        self._allreduce_noisy(group)
+
+    def _allreduce_noisy(self, group=None):
+        """noisy_dqn: the advantage layers' d_mu / d_sigma live outside the flat gradient (`_noisy_grad`, formed from the
+        LOCAL gradient and the rank's own epsilon by `_noisy_backward`), so they need their own (tiny) all-reduce --
+        otherwise every rank would step mu / sigma with its shard's gradient and the replicas would drift apart."""
+        import torch.distributed as dist
+        if self.noisy_dqn and self._noisy_grad is not None:
+            dist.all_reduce(self._noisy_grad, op=dist.ReduceOp.SUM, group=group)
 
     @property
     def flat_parameters(self):

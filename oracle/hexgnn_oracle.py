@@ -372,28 +372,24 @@ class NoisyLinearOracle(torch.nn.Module):
         self.bias_mu = torch.nn.Parameter(torch.empty(out_features))
         self.bias_sigma = torch.nn.Parameter(torch.empty(out_features))
         self.register_buffer('bias_epsilon', torch.empty(out_features))
-        with torch.no_grad():
-            scale = 1 / math.sqrt(in_features)                                         # :105-114
-            self.weight_mu.uniform_(-scale, scale)
-            self.bias_mu.uniform_(-scale, scale)
-            self.weight_sigma.fill_(sigma_0 * scale)
-            self.bias_sigma.fill_(sigma_0 * scale)
+        with torch.no_grad():                                                          # :105-114
+            bound = 1 / math.sqrt(in_features)
+            for mu, sigma in ((self.weight_mu, self.weight_sigma), (self.bias_mu, self.bias_sigma)):
+                mu.uniform_(-bound, bound)
+                sigma.fill_(sigma_0 * bound)
         self.reset_noise()
 
     @torch.no_grad()
-    def reset_noise(self):                                                             # :116-128
-        def f(size):
-            noise = torch.randn(size)
-            return noise.sign() * noise.abs().sqrt()
-        eps_in = f(self.in_features)
-        eps_out = f(self.out_features)
-        self.weight_epsilon.copy_(eps_out.outer(eps_in))
-        self.bias_epsilon.copy_(eps_out)
+    def reset_noise(self):                                                             # :116-128, z_in drawn first
+        z_in, z_out = torch.randn(self.in_features), torch.randn(self.out_features)
+        f_in, f_out = torch.copysign(z_in.abs().sqrt(), z_in), torch.copysign(z_out.abs().sqrt(), z_out)
+        self.weight_epsilon.copy_(f_out.unsqueeze(1) * f_in.unsqueeze(0))
+        self.bias_epsilon.copy_(f_out)
 
     @torch.no_grad()
     def disable_noise(self):                                                           # :130-133
-        self.weight_epsilon[:] = 0
-        self.bias_epsilon[:] = 0
+        self.weight_epsilon.zero_()
+        self.bias_epsilon.zero_()
 
     def forward(self, x):                                                              # :135-141
         return F.linear(x, self.weight_mu + self.weight_sigma * self.weight_epsilon,

@@ -27,6 +27,7 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 import helpers  # noqa: E402
+import positions  # noqa: E402
 from gnn_hex_b200 import data  # noqa: E402
 
 CASES = {
@@ -44,7 +45,7 @@ def args_of(case):
 
 
 def batch_of(case, maker):
-    return data.collate(data.load_positions(case[5], maker=maker)[:case[6]])
+    return data.collate(positions.load_positions(case[5], maker=maker)[:case[6]])
 
 
 def run_case(ref, tag):

@@ -6,6 +6,7 @@ import pytest
 import torch
 
 from gnn_hex_b200 import ModernTwoHeaded, data, ops, _lib
+import positions
 from oracle import hexgnn_oracle as orc
 from helpers import REL_TOL, grad_errs, loss_inputs, make_pair, oracle64, rel_err
 
@@ -26,7 +27,7 @@ def _csr_check(b, **kw):
 
 @pytest.mark.parametrize("fixture", ["pos_11x11_seed1234.npz", "pos_7x7_seed1234.npz"])
 def test_csr_bit_exact(fixture):
-    gs = data.load_positions(fixture, maker=1)
+    gs = positions.load_positions(fixture, maker=1)
     b = data.collate(gs)
     _csr_check(b, batch="batch", ptr="ptr", num_nodes=b.x.shape[0])
     _csr_check(b, batch="batch", num_nodes=b.x.shape[0], num_graphs=b.num_graphs)
@@ -44,7 +45,7 @@ def test_csr_bit_exact(fixture):
 
 
 def test_csr_single_graph_and_empty_graphs():
-    g = data.empty_board(11)
+    g = positions.empty_board(11)
     d = g.to(DEV)
     csr = ops.build_csr(d.edge_index, num_nodes=123)
     rowptr, col = orc.csr_by_destination(g.edge_index, 123)
@@ -59,7 +60,7 @@ def test_csr_single_graph_and_empty_graphs():
 
 
 def test_csr_flags_bad_input():
-    g = data.empty_board(5)
+    g = positions.empty_board(5)
     ei = g.edge_index.clone()
     ei[0, 0] = 10_000
     csr = ops.build_csr(ei.to(DEV), num_nodes=27)
@@ -79,9 +80,9 @@ CONFIGS = {
 
 def _batch(cfg, kind, maker, count):
     if kind == "empty":
-        gs = [data.empty_board(cfg["board"], maker)] * count
+        gs = [positions.empty_board(cfg["board"], maker)] * count
     else:
-        gs = data.load_positions(cfg["fixture"], maker=maker)[:count]
+        gs = positions.load_positions(cfg["fixture"], maker=maker)[:count]
     return data.collate(gs)
 
 
@@ -187,7 +188,7 @@ def test_deterministic_bitwise():
     _, m = make_pair(110, 15)
     m = m.to(DEV)
     b = _batch(CONFIGS["L"], "play", 1, 96).to(DEV)
-    action, target, weight = [t.to(DEV) for t in loss_inputs(data.collate(data.load_positions(CONFIGS["L"]["fixture"], maker=1)[:96]))]
+    action, target, weight = [t.to(DEV) for t in loss_inputs(data.collate(positions.load_positions(CONFIGS["L"]["fixture"], maker=1)[:96]))]
     outs = []
     for _ in range(3):
         m.zero_grad()
@@ -201,7 +202,7 @@ def test_deterministic_bitwise():
 def test_ragged_mix_forward_and_oversize_flag():
     o, m = make_pair(110, 15)
     m = m.to(DEV)
-    gs = data.load_positions("pos_mix_5_13_seed1234.npz", maker=1)
+    gs = positions.load_positions("pos_mix_5_13_seed1234.npz", maker=1)
     small = [g for g in gs if g.x.shape[0] <= 128 and g.edge_index.shape[1] <= 1024][:96]
     b = data.collate(small)
     d = b.to(DEV)
@@ -228,7 +229,7 @@ def test_cpu_tensors_are_rejected_loudly():
 def test_td_loss_matches_torch(kind, weighted):
     """hexgnn_td_loss (rainbow.py:301-312 on device) vs the same expression in torch: loss, td errors, dloss/dq."""
     from gnn_hex_b200 import ops
-    b = data.collate(data.load_positions("pos_7x7_seed1234.npz", maker=1)[:97])
+    b = data.collate(positions.load_positions("pos_7x7_seed1234.npz", maker=1)[:97])
     action, target, weight = loss_inputs(b)
     g = torch.Generator().manual_seed(5)
     q = (torch.randn(b.x.shape[0], generator=g) * 1.5).requires_grad_(True)   # |err| on both sides of 1
@@ -249,7 +250,7 @@ def test_td_loss_matches_torch(kind, weighted):
 
 def test_mask_argmax_and_td_target_match_torch():
     """hexgnn_mask_argmax / hexgnn_td_target vs rainbow.py:222-225,263-269 written with torch ops."""
-    b = data.collate(data.load_positions("pos_mix_5_13_seed1234.npz", maker=1)[:120])
+    b = data.collate(positions.load_positions("pos_mix_5_13_seed1234.npz", maker=1)[:120])
     g = torch.Generator().manual_seed(9)
     q = torch.randn(b.x.shape[0], generator=g)
     ref = q.clone()
@@ -279,7 +280,7 @@ def test_oversize_graphs_board_size_transfer(mode):
     m = m.to(DEV)
     m.max_graph_nodes = 256
     m.strict = True
-    gs = data.load_positions("pos_mix_5_13_seed1234.npz", maker=1)
+    gs = positions.load_positions("pos_mix_5_13_seed1234.npz", maker=1)
     big = [g for g in gs if g.x.shape[0] > 128]
     assert len(big) >= 4
     mix = big[:6] + [g for g in gs if g.x.shape[0] <= 128][:26] + big[6:10]
@@ -314,7 +315,7 @@ def test_train_step_equals_autograd_route(size, count, kind, weighted):
     cfg = CONFIGS[size]
     _, m = make_pair(cfg["hidden"], cfg["layers"])
     m = m.to(DEV)
-    gs = data.load_positions(cfg["fixture"], maker=1)[:count]
+    gs = positions.load_positions(cfg["fixture"], maker=1)[:count]
     hb = data.collate(gs)
     b = hb.to(DEV)
     action, target, weight = [t.to(DEV) for t in loss_inputs(hb)]
@@ -354,7 +355,7 @@ def test_fused_adam_matches_torch_adam_with_clipping(skip_untaken):
     ref_opt = torch.optim.Adam(ref_params, lr=3e-3, eps=1.5e-4)
     opt = FusedAdam(m, lr=3e-3, eps=1.5e-4, max_grad_norm=0.05, skip_untaken=skip_untaken)
     for step, maker in enumerate([1, 1, 0, 1, 0, 0]):
-        hb = data.collate(data.load_positions(cfg["fixture"], maker=maker)[step * 8:step * 8 + 24])
+        hb = data.collate(positions.load_positions(cfg["fixture"], maker=maker)[step * 8:step * 8 + 24])
         b = hb.to(DEV)
         action, target, weight = [t.to(DEV) for t in loss_inputs(hb)]
         m.zero_grad(set_to_none=True)
@@ -391,7 +392,7 @@ def test_device_collate_bit_exact():
     """hexgnn_collate (one launch over device-resident graphs) == host collate == Batch.from_data_list layout
     (replay_buffer.py:215-216, util.cpp:22-41), including an edgeless single-node graph and repeated use of the slots."""
     col = data.DeviceCollator(DEV, max_graphs=512, slots=2)
-    gs = data.load_positions("pos_mix_5_13_seed1234.npz", maker=1)[:200]
+    gs = positions.load_positions("pos_mix_5_13_seed1234.npz", maker=1)[:200]
     lone = data.HexGraph(x=torch.tensor([[0.0, 1.0, 1.0]]), edge_index=torch.zeros((2, 0), dtype=torch.long))
     for lo, hi in [(0, 200), (3, 4), (50, 97), (100, 101), (7, 150)]:
         part = gs[lo:hi] + ([lone] if hi - lo > 1 else [])
@@ -415,7 +416,7 @@ def test_rainbow_learner_step_matches_reference_formulas(double_dqn):
     o_pol, m_pol = make_pair(cfg["hidden"], cfg["layers"], seed=0)
     o_tgt, m_tgt = make_pair(cfg["hidden"], cfg["layers"], seed=5)
     m_pol, m_tgt = m_pol.to(DEV), m_tgt.to(DEV)
-    gs = data.load_positions(cfg["fixture"], maker=1)
+    gs = positions.load_positions(cfg["fixture"], maker=1)
     hs, hn = data.collate(gs[:64]), data.collate(gs[64:128])
     g = torch.Generator().manual_seed(3)
     action = torch.stack([torch.randint(2, int(n), (1,), generator=g)[0] for n in (hs.ptr[1:] - hs.ptr[:-1])])
@@ -470,7 +471,7 @@ def test_train_step_batch_extremes(count):
     cfg = CONFIGS["L"]
     o, m = make_pair(cfg["hidden"], cfg["layers"])
     m = m.to(DEV)
-    gs = data.load_positions(cfg["fixture"], maker=1)
+    gs = positions.load_positions(cfg["fixture"], maker=1)
     gs = (gs * 3)[:count]
     hb = data.collate(gs)
     b = hb.to(DEV)
@@ -705,7 +706,7 @@ def test_rainbow_learner_noisy_nets_and_act():
     o_pol, m_pol = make_pair(cfg["hidden"], cfg["layers"], seed=0, noisy_dqn=True)
     o_tgt, m_tgt = make_pair(cfg["hidden"], cfg["layers"], seed=5, noisy_dqn=True)
     m_pol, m_tgt = m_pol.to(DEV), m_tgt.to(DEV)
-    gs = data.load_positions(cfg["fixture"], maker=1)
+    gs = positions.load_positions(cfg["fixture"], maker=1)
     hs, hn = data.collate(gs[:48]), data.collate(gs[48:96])
     g = torch.Generator().manual_seed(3)
     action = torch.stack([torch.randint(2, int(n), (1,), generator=g)[0] for n in (hs.ptr[1:] - hs.ptr[:-1])])
@@ -768,7 +769,7 @@ def test_full_size_headline_batch_properties():
     cfg = CONFIGS["L"]
     o, m = make_pair(cfg["hidden"], cfg["layers"])
     m = m.to(DEV)
-    gs = data.load_positions(cfg["fixture"], maker=1)[:256]
+    gs = positions.load_positions(cfg["fixture"], maker=1)[:256]
     hb = data.collate(gs)
     b = hb.to(DEV)
     action, target, weight = loss_inputs(hb)
@@ -811,9 +812,10 @@ def test_csr_five_launch_path_in_subprocess():
     code = (
         "import sys, torch; sys.path.insert(0, 'tests')\n"
         "from gnn_hex_b200 import data, ops\n"
+        "import positions\n"
         "from oracle import hexgnn_oracle as orc\n"
         "for f in ('pos_11x11_seed1234.npz', 'pos_mix_5_13_seed1234.npz'):\n"
-        "    b = data.collate(data.load_positions(f, maker=1)); d = b.to('cuda:0')\n"
+        "    b = data.collate(positions.load_positions(f, maker=1)); d = b.to('cuda:0')\n"
         "    c0 = ops.launch_counter\n"
         "    csr = ops.build_csr(d.edge_index, d.batch, d.ptr, num_nodes=b.x.shape[0])\n"
         "    rowptr, col = orc.csr_by_destination(b.edge_index, b.x.shape[0])\n"

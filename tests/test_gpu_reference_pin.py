@@ -7,6 +7,7 @@ import torch
 
 import helpers
 from gnn_hex_b200 import ModernTwoHeaded, data
+import positions
 
 pytestmark = pytest.mark.gpu
 
@@ -28,7 +29,7 @@ def rel(a, b):
 def test_cuda_path_equals_reference_golden_vectors(tag, maker):
     H, L, Lh, noisy, pos = CASES[tag]
     fx = helpers.load_model_fixture(tag)
-    b = data.collate(data.load_positions(pos, maker=maker)[:int(fx["count"])])
+    b = data.collate(positions.load_positions(pos, maker=maker)[:int(fx["count"])])
     m = ModernTwoHeaded(H, L, Lh, noisy_dqn=noisy, noisy_sigma0=0.5)
     helpers.set_hash_weights(m, seed=0)
     names = [str(n) for n in fx["names"]]

@@ -5,12 +5,13 @@ import pytest
 import torch
 
 from gnn_hex_b200 import data
+import positions
 from oracle import hexgnn_oracle as orc
 
 
 def test_empty_board_matches_reference_cpp_game():
     """hex_board_undirected_edges (restating hex_board_game.py:214-232) == the compiled C++ game."""
-    z = np.load(data.GOLDEN_DIR + "/empty_boards_3_13.npz")
+    z = np.load(positions.GOLDEN_DIR + "/empty_boards_3_13.npz")
     eo = 0
     for g, size in enumerate(z["size"]):
         n, ne = int(z["n"][g]), int(z["ne"][g])
@@ -27,7 +28,7 @@ def test_empty_board_matches_reference_cpp_game():
 
 def test_fixture_graphs_are_valid_and_symmetric():
     for name in ("pos_11x11_seed1234.npz", "pos_7x7_seed1234.npz", "pos_mix_5_13_seed1234.npz"):
-        gs = data.load_positions(name)
+        gs = positions.load_positions(name)
         assert len(gs) == 256
         for g in gs[:40]:
             ei = g.edge_index
@@ -42,7 +43,7 @@ def test_fixture_graphs_are_valid_and_symmetric():
 
 
 def test_collate_matches_cpp_collate_batch_semantics():
-    gs = data.load_positions("pos_7x7_seed1234.npz")[:5]
+    gs = positions.load_positions("pos_7x7_seed1234.npz")[:5]
     b = data.collate(gs)
     o = orc.collate(gs)
     for k in ("x", "edge_index", "batch", "ptr"):
@@ -90,7 +91,7 @@ def test_known_answer_debugging_manager_graph():
 
 
 def _small_batch(k=3):
-    gs = data.load_positions("pos_7x7_seed1234.npz", maker=1)[:k]
+    gs = positions.load_positions("pos_7x7_seed1234.npz", maker=1)[:k]
     return gs, data.collate(gs)
 
 
@@ -111,7 +112,7 @@ def test_batched_equals_per_graph_and_output_modes():
 def test_permutation_equivariance_and_edge_order_invariance():
     torch.manual_seed(0)
     m = orc.ModernTwoHeadedOracle(10, 3, 2).double()
-    g = data.load_positions("pos_7x7_seed1234.npz", maker=0)[7]
+    g = positions.load_positions("pos_7x7_seed1234.npz", maker=0)[7]
     x, ei = g.x.double(), g.edge_index
     q = m(x, ei)
     gen = torch.Generator().manual_seed(3)
@@ -250,7 +251,7 @@ def test_oracle_against_real_pyg_when_installed():
     ts = pytest.importorskip("torch_scatter")
     from torch_geometric.nn import SAGEConv
     torch.manual_seed(0)
-    g = data.load_positions("pos_7x7_seed1234.npz", maker=1)[3]
+    g = positions.load_positions("pos_7x7_seed1234.npz", maker=1)[3]
     x = torch.randn(g.x.shape[0], 6)
     conv = SAGEConv(6, 5)
     want = conv(x, g.edge_index)

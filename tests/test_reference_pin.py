@@ -17,6 +17,7 @@ import torch
 
 import helpers
 from gnn_hex_b200 import data
+import positions
 from oracle import hexgnn_oracle as orc
 
 CASES = {
@@ -36,7 +37,7 @@ def oracle_of(tag, dtype=torch.float32):
 
 
 def batch_of(tag, fx, maker):
-    return data.collate(data.load_positions(CASES[tag][5], maker=maker)[:int(fx["count"])])
+    return data.collate(positions.load_positions(CASES[tag][5], maker=maker)[:int(fx["count"])])
 
 
 def max_rel(a, b):
@@ -135,7 +136,7 @@ def test_live_reference_model_equals_oracle(norm, noisy):
     helpers.set_hash_weights(m, 3)
     helpers.set_hash_weights(o, 3)
     assert_same_state(m, o)
-    gs = data.load_positions("pos_7x7_seed1234.npz", maker=1)[:5]
+    gs = positions.load_positions("pos_7x7_seed1234.npz", maker=1)[:5]
     b = data.collate(gs)
     for maker in (1.0, 0.0):
         x = b.x.clone()
@@ -206,7 +207,7 @@ def test_live_growth_of_the_whole_model():
     p = ModernTwoHeaded(10, 3, 2)
     for mod in (m, o, p):
         helpers.set_hash_weights(mod, 5)
-    b = data.collate(data.load_positions("pos_7x7_seed1234.npz", maker=1)[:3])
+    b = data.collate(positions.load_positions("pos_7x7_seed1234.npz", maker=1)[:3])
     q0 = m(b.x, b.edge_index, b.batch, b.ptr)
     for mod in (m, o, p):
         torch.manual_seed(21)
@@ -235,7 +236,7 @@ def test_live_head_network_alone():
     o = orc.ModernTwoHeadedOracle(8, 2, 2)
     helpers.set_hash_weights(m, 9)
     helpers.set_hash_weights(o, 9)
-    b = data.collate(data.load_positions("pos_7x7_seed1234.npz", maker=1)[:4])
+    b = data.collate(positions.load_positions("pos_7x7_seed1234.npz", maker=1)[:4])
     emb = torch.rand(b.x.shape[0], 8)
     ar, vr = m.maker_head(emb, b.edge_index, b.batch)
     ao, vo = o.maker_head(emb, b.edge_index, b.batch, 4)

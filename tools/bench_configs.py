@@ -8,7 +8,9 @@ CUDA events, inputs resident, 256 MiB L2 flush between iterations.   python tool
 import json, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
 from gnn_hex_b200 import ModernTwoHeaded, data, ops
+import positions  # noqa: E402
 
 iters = int(sys.argv[1]) if len(sys.argv) > 1 else 100
 dev = torch.device("cuda", 0)
@@ -39,7 +41,7 @@ torch.manual_seed(0)
 out = []
 # configs[0]
 m = ModernTwoHeaded(35, 10, 2).to(dev)
-b = data.collate(data.load_positions("pos_7x7_seed1234.npz", maker=1)[:256]); d = b.to(dev)
+b = data.collate(positions.load_positions("pos_7x7_seed1234.npz", maker=1)[:256]); d = b.to(dev)
 a, t, w = loss_inputs(b)
 def step_s():
     m.zero_grad(set_to_none=True)
@@ -48,7 +50,7 @@ ms = timed(step_s)
 out.append({"config": "gnn_s fwd+bwd, 256 7x7 positions", "nodes": int(b.x.shape[0]), "ms": ms, "graphs_per_s": 256 / ms * 1e3})
 # configs[2]
 m = ModernTwoHeaded(110, 15, 2).to(dev)
-b = data.collate(data.load_positions("pos_11x11_seed1234.npz", maker=1)[:128]); d = b.to(dev)
+b = data.collate(positions.load_positions("pos_11x11_seed1234.npz", maker=1)[:128]); d = b.to(dev)
 def act():
     with torch.no_grad():
         adv = m(d.x, d.edge_index, d.batch, d.ptr, advantages_only=True).reshape(-1)
@@ -57,7 +59,7 @@ ms = timed(act)
 out.append({"config": "selfplay: GNN-L forward (advantages_only) + mask + argmax, 128 11x11 positions", "nodes": int(b.x.shape[0]),
             "ms": ms, "graphs_per_s": 128 / ms * 1e3})
 # configs[3]
-b = data.collate(data.load_positions("pos_mix_5_13_seed1234.npz", maker=1)[:256]); d = b.to(dev)
+b = data.collate(positions.load_positions("pos_mix_5_13_seed1234.npz", maker=1)[:256]); d = b.to(dev)
 m.max_graph_nodes = 256   # 12x12 / 13x13 positions (146 / 171 nodes) take the oversize-graph path
 def fwd():
     with torch.no_grad():
@@ -70,7 +72,7 @@ out.append({"config": "ragged: GNN-L forward, 256 graphs of 5x5..13x13 boards (o
 from gnn_hex_b200 import RainbowLearner
 pol, tgt = ModernTwoHeaded(110, 15, 2).to(dev), ModernTwoHeaded(110, 15, 2).to(dev)
 lrn = RainbowLearner(pol, tgt, lr=1e-4, adam_eps=1.5e-4, max_grad_norm=10.0, gamma=0.97, n_step=2)
-gs = data.load_positions("pos_11x11_seed1234.npz", maker=1)
+gs = positions.load_positions("pos_11x11_seed1234.npz", maker=1)
 hs, hn = data.collate(gs[:256]), data.collate(gs[128:256] + gs[:128])
 ds, dn = hs.to(dev), hn.to(dev)
 a, _, w = loss_inputs(hs)

@@ -12,7 +12,9 @@ import json, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import torch.distributed as dist
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
 from gnn_hex_b200 import ModernTwoHeaded, RainbowLearner, data
+import positions  # noqa: E402
 
 iters = int(sys.argv[1]) if len(sys.argv) > 1 else 50
 global_batch = int(sys.argv[2]) if len(sys.argv) > 2 else 2048
@@ -23,7 +25,7 @@ if world > 1:
     dist.init_process_group("nccl", device_id=dev)
 per = global_batch // world
 
-gs = data.load_positions("pos_11x11_seed1234.npz", maker=1)
+gs = positions.load_positions("pos_11x11_seed1234.npz", maker=1)
 
 
 def shard(offset):

@@ -4,13 +4,15 @@ import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import torch.distributed as dist
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
 from gnn_hex_b200 import ModernTwoHeaded, data, ops
+import positions  # noqa: E402
 
 rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
 torch.cuda.set_device(lr)
 dev = torch.device("cuda", lr)
 dist.init_process_group("nccl", device_id=dev)
-gs = data.load_positions("pos_11x11_seed1234.npz", maker=1)
+gs = positions.load_positions("pos_11x11_seed1234.npz", maker=1)
 k = (32 * rank) % len(gs)
 b = data.collate((gs[k:] + gs[:k])[:64]).to(dev)
 action = torch.full((b.num_graphs,), 2, dtype=torch.long, device=dev)

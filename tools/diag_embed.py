@@ -3,12 +3,14 @@ import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 import torch
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
 from gnn_hex_b200 import data
+import positions  # noqa: E402
 from helpers import make_pair
 DEV = "cuda:0"
 o, m = make_pair(35, 10)
 m = m.to(DEV); m.capture_embed_grads = True
-b = data.collate(data.load_positions("pos_7x7_seed1234.npz", maker=1)[:40]); d = b.to(DEV)
+b = data.collate(positions.load_positions("pos_7x7_seed1234.npz", maker=1)[:40]); d = b.to(DEV)
 gen = torch.Generator().manual_seed(3)
 wn = torch.randn(b.x.shape[0], generator=gen); wv = torch.randn(b.num_graphs, generator=gen)
 for mode in ("q", "sep", "adv"):

@@ -5,7 +5,9 @@ import torch
 import os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
 from gnn_hex_b200 import data  # noqa: E402
+import positions  # noqa: E402
 from oracle import hexgnn_oracle as orc  # noqa: E402
 from helpers import make_pair, loss_inputs  # noqa: E402
 
@@ -18,7 +20,7 @@ def run(hidden, layers, fixture, count, maker=1, path="auto"):
     o64.load_state_dict({k: v.double() for k, v in o.state_dict().items()})
     m = m.to(DEV)
     m.path = path
-    b = data.collate(data.load_positions(fixture, maker=maker)[:count])
+    b = data.collate(positions.load_positions(fixture, maker=maker)[:count])
     d = b.to(DEV)
     action, target, weight = loss_inputs(b)
     orc.rainbow_loss(o(b.x, b.edge_index, b.batch, b.ptr), b.ptr, action, target, weight).backward()

@@ -3,11 +3,13 @@
 import os, sys, statistics
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
 from gnn_hex_b200 import ModernTwoHeaded, data, _lib
+import positions  # noqa: E402
 mode = sys.argv[1] if len(sys.argv) > 1 else "play"
 torch.manual_seed(0)
 m = ModernTwoHeaded(110, 15, 2).to("cuda:0")
-gs = data.load_positions("pos_11x11_seed1234.npz", maker=1)[:256] if mode == "play" else [data.empty_board(11, 1)] * 256
+gs = positions.load_positions("pos_11x11_seed1234.npz", maker=1)[:256] if mode == "play" else [positions.empty_board(11, 1)] * 256
 b = data.collate(gs).to("cuda:0")
 for _ in range(5):
     m.zero_grad(set_to_none=True)

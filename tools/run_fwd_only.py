@@ -2,12 +2,14 @@
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
 from gnn_hex_b200 import ModernTwoHeaded, data
+import positions  # noqa: E402
 reps = int(sys.argv[1]) if len(sys.argv) > 1 else 5
 mode = sys.argv[2] if len(sys.argv) > 2 else "play"
 torch.manual_seed(0)
 m = ModernTwoHeaded(110, 15, 2).to("cuda:0")
-gs = data.load_positions("pos_11x11_seed1234.npz", maker=1) if mode == "play" else [data.empty_board(11, 1)] * 256
+gs = positions.load_positions("pos_11x11_seed1234.npz", maker=1) if mode == "play" else [positions.empty_board(11, 1)] * 256
 b = data.collate(gs).to("cuda:0")
 with torch.no_grad():
     csr = m.build_csr(b.edge_index, b.batch, b.ptr, num_nodes=b.x.shape[0])

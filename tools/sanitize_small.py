@@ -6,12 +6,13 @@ import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
 from gnn_hex_b200 import ModernTwoHeaded, RainbowLearner, data, ops  # noqa: E402
+import positions  # noqa: E402
 from helpers import loss_inputs  # noqa: E402
 
 dev = torch.device("cuda", 0)
 torch.manual_seed(0)
 m, t = ModernTwoHeaded(35, 10, 2).to(dev), ModernTwoHeaded(35, 10, 2).to(dev)
-gs = data.load_positions("pos_7x7_seed1234.npz", maker=1)
+gs = positions.load_positions("pos_7x7_seed1234.npz", maker=1)
 hb = data.collate(gs[:200])          # > 148 tiles? 7x7 graphs pack several per tile; still exercises two rounds of items
 b = hb.to(dev)
 a, tg, w = [u.to(dev) for u in loss_inputs(hb)]
@@ -24,12 +25,12 @@ hn = data.collate(gs[50:250]).to(dev)
 out = lrn.train(b, hn, a, torch.zeros(200, device=dev), torch.zeros(200, device=dev), w)
 col = data.DeviceCollator(dev, max_graphs=64)
 cb = col([g.to(dev) for g in gs[:40]])
-mix = data.collate(data.load_positions("pos_mix_5_13_seed1234.npz", maker=1)[:40]).to(dev)
+mix = data.collate(positions.load_positions("pos_mix_5_13_seed1234.npz", maker=1)[:40]).to(dev)
 big = ModernTwoHeaded(110, 15, 2, max_graph_nodes=256).to(dev)
 with torch.no_grad():
     qb = big(mix.x, mix.edge_index, mix.batch, mix.ptr)
 big_l = ModernTwoHeaded(110, 15, 2).to(dev)
-gl = data.collate(data.load_positions("pos_11x11_seed1234.npz", maker=1)[:180])   # 148+ tiles: both dW phases, 2 rounds
+gl = data.collate(positions.load_positions("pos_11x11_seed1234.npz", maker=1)[:180])   # 148+ tiles: both dW phases, 2 rounds
 bl = gl.to(dev)
 al, tl, wl = [u.to(dev) for u in loss_inputs(gl)]
 l3 = big_l.train_step(bl.x, bl.edge_index, bl.batch, bl.ptr, action=al, target=tl, weight=wl)[0]
