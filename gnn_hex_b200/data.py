@@ -137,11 +137,12 @@ class DeviceCollator:
         if self._events[k] is not None:
             self._events[k].synchronize()          # the table of this slot has been consumed
         stream = torch.cuda.current_stream(dev)
-        rc = _lib.lib().hexgnn_collate(x_ptrs, ei_ptrs, n_nodes, n_edges, B, C.c_void_p(x_out.data_ptr()),
-                                       C.c_void_p(ei_out.data_ptr()), C.c_void_p(batch.data_ptr()),
-                                       C.c_void_p(ptr.data_ptr()), C.c_void_p(self._dev[k].data_ptr()),
-                                       self._dev[k].numel(), C.c_void_p(self._host[k].data_ptr()), self._host[k].numel(),
-                                       C.c_void_p(stream.cuda_stream))
+        with torch.cuda.device(dev):
+            rc = _lib.lib().hexgnn_collate(x_ptrs, ei_ptrs, n_nodes, n_edges, B, C.c_void_p(x_out.data_ptr()),
+                                           C.c_void_p(ei_out.data_ptr()), C.c_void_p(batch.data_ptr()),
+                                           C.c_void_p(ptr.data_ptr()), C.c_void_p(self._dev[k].data_ptr()),
+                                           self._dev[k].numel(), C.c_void_p(self._host[k].data_ptr()), self._host[k].numel(),
+                                           C.c_void_p(stream.cuda_stream))
         _lib.check(rc, "hexgnn_collate")
         ev = torch.cuda.Event()
         ev.record(stream)

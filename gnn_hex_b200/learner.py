@@ -89,7 +89,18 @@ class RainbowLearner:
             grad_norm = self.opt.step(state.x)
         else:
             grad_norm = torch.nn.utils.clip_grad_norm_(self.q_policy.parameters(), self.max_grad_norm)   # rainbow.py:320
+            # same guard as the fused optimizer, without a host sync: a non-finite norm zeroes the gradients, which leaves
+            # Adam's parameters untouched up to its momentum (torch.optim.Adam has no device-side skip)
+            ok = torch.isfinite(grad_norm)
+            for p in self.q_policy.parameters():
+                if p.grad is not None:
+                    p.grad.mul_(ok).nan_to_num_(nan=0.0, posinf=0.0, neginf=0.0)
             self.opt.step()
         td_est = td_err + td_tgt
+        # `status` (device int32 [1], read it lazily): non-zero when a kernel flagged the batch -- bit 1 = a graph exceeds
+        # the tile capacity (128 nodes / 1024 directed edges / 64 graphs per tile: its rows come back NaN).  The fused
+        # optimizer skips a step whose gradient norm is not finite (parameters, moments and step counters untouched), so
+        # one oversize position cannot poison the network; `grad_norm` then reports the non-finite value.
         return {"loss": loss, "grad_norm": grad_norm, "priorities": td_err.abs() + 1e-6,
-                "est_mean": td_est.mean(), "gt_mean": td_tgt.mean(), "td_target": td_tgt, "q": q}
+                "est_mean": td_est.mean(), "gt_mean": td_tgt.mean(), "td_target": td_tgt, "q": q,
+                "status": self.q_policy.last_csr.status}

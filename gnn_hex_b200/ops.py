@@ -27,6 +27,28 @@ def _stream(device):
     return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
 
 
+def _on_tensor_device(fn):
+    """Run a C-ABI wrapper with the CUDA device of its first CUDA argument current: the library launches on the current
+    device and passes `torch.cuda.current_stream(tensor.device)`, so a model on cuda:1 called while cuda:0 is current
+    would otherwise hand a stream of one device to a launch on another.  Costs nothing when the device already is
+    current (the normal one-process-per-GPU case)."""
+    import functools
+
+    @functools.wraps(fn)
+    def wrapped(*args, **kwargs):
+        idx = -1
+        for a in args:
+            t = a.blob if isinstance(a, CsrBlob) else a
+            if isinstance(t, torch.Tensor) and t.is_cuda:
+                idx = t.device.index
+                break
+        if idx < 0 or idx == torch.cuda.current_device():
+            return fn(*args, **kwargs)
+        with torch.cuda.device(idx):
+            return fn(*args, **kwargs)
+    return wrapped
+
+
 def _require_cuda(t, name):
     if not t.is_cuda:
         raise _lib.HexGnnError(f"{name} must be a CUDA tensor: the fused path has no CPU fallback")
@@ -74,6 +96,7 @@ class CsrBlob:
             raise _lib.HexGnnError("hexgnn device status %d: %s" % (st, "; ".join(msgs)))
 
 
+@_on_tensor_device
 def build_csr(edge_index, batch=None, ptr=None, num_nodes=None, num_graphs=None, tile_rows=128):
     """Device CSR builder (hexgnn_build_csr).  edge_index [2,E] int64 CUDA; batch [N] int64 and/or
     ptr [B+1] int64; neither => single graph.  No host sync."""
@@ -114,6 +137,7 @@ def build_csr(edge_index, batch=None, ptr=None, num_nodes=None, num_graphs=None,
     return CsrBlob(blob, N, E, B, tile_rows)
 
 
+@_on_tensor_device
 def fused_forward(desc, flat_params, x, csr, flags=0, want_stash=False, ws=None):
     """hexgnn_forward.  Returns (out_nodes [N], out_value [B], stash or None, hidden_padded)."""
     _require_cuda(x, "x")
@@ -139,6 +163,7 @@ def fused_forward(desc, flat_params, x, csr, flags=0, want_stash=False, ws=None)
     return out_nodes, out_value, stash, int(sz.hidden_padded)
 
 
+@_on_tensor_device
 def fused_backward(desc, flat_params, x, csr, flags, d_nodes, d_value, stash, want_d_embeds=False, ws=None,
                    grad_out=None, d_x=None):
     """hexgnn_backward.  Returns (flat gradient [P], d_embeds [N,Hp] or None).  `d_x` ([N,3] f32 CUDA, optional): also
@@ -175,6 +200,7 @@ def fused_backward(desc, flat_params, x, csr, flags, d_nodes, d_value, stash, wa
 LOSS_KINDS = {"mse": 0, "smooth_l1": 1, "huber": 1}
 
 
+@_on_tensor_device
 def fused_train_step(desc, flat_params, x, csr, ptr, action, target, weight=None, kind="mse", scale=1.0, grad_out=None,
                      ws=None):
     """hexgnn_train_step: forward + TD loss + backward + gradient reduction in one call (rainbow.py:301-316).
@@ -235,8 +261,9 @@ class _TDLoss(torch.autograd.Function):
         td_err = torch.empty(B, dtype=torch.float32, device=dev)
         need_grad = ctx.needs_input_grad[0]
         d_q = torch.empty(N, dtype=torch.float32, device=dev) if need_grad else None
-        rc = _lib.lib().hexgnn_td_loss(_ptr(q), _ptr(ptr), _ptr(action), _ptr(target), _ptr(weight), N, B, int(kind),
-                                       float(scale), _ptr(loss), _ptr(td_err), _ptr(d_q), _stream(dev))
+        with torch.cuda.device(dev):
+            rc = _lib.lib().hexgnn_td_loss(_ptr(q), _ptr(ptr), _ptr(action), _ptr(target), _ptr(weight), N, B, int(kind),
+                                           float(scale), _ptr(loss), _ptr(td_err), _ptr(d_q), _stream(dev))
         _lib.check(rc, "hexgnn_td_loss")
         _count("td_loss")
         ctx.d_q = d_q
@@ -261,6 +288,7 @@ def td_loss(q, ptr, action, target, weight=None, kind="mse", scale=1.0):
 
 
 @torch.no_grad()
+@_on_tensor_device
 def mask_argmax(q, ptr, mask_terminals=True, mask_value=-5.0):
     """rainbow.py:222-225 / 263-266 on device, one launch: overwrite the two terminal rows of every graph in ``q``
     (in place) with ``mask_value`` and return (max [B], argmax [B] as GLOBAL row ids; ties -> lowest index).
@@ -281,6 +309,7 @@ def mask_argmax(q, ptr, mask_terminals=True, mask_value=-5.0):
 
 
 @torch.no_grad()
+@_on_tensor_device
 def td_target(q_target, best, reward, done, gamma_n):
     """rainbow.py:268-269 on device: ``reward + gamma_n * q_target[best] * (1 - done)``."""
     _require_cuda(q_target, "q_target")
@@ -298,6 +327,7 @@ def td_target(q_target, best, reward, done, gamma_n):
     return out
 
 
+@_on_tensor_device
 def forward_big(desc, flat_params, x, csr, flags, max_rows, out_nodes, out_value, ws=None):
     """hexgnn_forward_big: after fused_forward, evaluate the graphs that do not fit one tile (inference only) and
     overwrite their rows of ``out_nodes`` / ``out_value`` in place.  Launches 2 + num_layers + num_head_layers kernels."""
@@ -317,6 +347,7 @@ def forward_big(desc, flat_params, x, csr, flags, max_rows, out_nodes, out_value
     return ws
 
 
+@_on_tensor_device
 def allreduce_p2p(peer_ptrs_dev, world, n, out):
     """hexgnn_allreduce_p2p: out[n] = sum over ranks (in rank order) of the peer-mapped buffers whose device pointers
     are stored in the DEVICE array at address `peer_ptrs_dev`.  The caller provides the cross-rank barriers."""
@@ -328,6 +359,7 @@ def allreduce_p2p(peer_ptrs_dev, world, n, out):
 
 
 @torch.no_grad()
+@_on_tensor_device
 def adam_step(desc, flat_params, flat_grad, exp_avg, exp_avg_sq, state, x, lr, betas=(0.9, 0.999), eps=1e-8,
               max_grad_norm=0.0, skip_untaken=False, grad_norm_out=None, ws=None):
     """hexgnn_adam_step over the flat buffers (rainbow.py:320-326): clip_grad_norm_ + Adam.step in two launches.
@@ -353,6 +385,7 @@ def adam_step(desc, flat_params, flat_grad, exp_avg, exp_avg_sq, state, x, lr, b
     return grad_norm_out.reshape(())
 
 
+@_on_tensor_device
 def noisy_compose(desc, flat_params, noisy):
     """hexgnn_noisy_compose: write `mu + sigma * epsilon` of both heads' FactorizedNoisyLinear (GN0/models.py:134-141) into
     the advantage-Linear slots of the flat parameter buffer.  noisy: [2, 3, H+1] f32 CUDA."""
@@ -365,6 +398,7 @@ def noisy_compose(desc, flat_params, noisy):
     _count("noisy")
 
 
+@_on_tensor_device
 def noisy_grads(desc, flat_grad, noisy, d_noisy, accumulate):
     """hexgnn_noisy_grads: d_mu = g, d_sigma = g * epsilon from the composed weights' slice of the flat gradient.
     d_noisy: [2, 2, H+1] f32 CUDA, overwritten or (accumulate) added to."""

@@ -78,3 +78,33 @@ def test_custom_ops_registered_with_fake_kernels(lib_built):
         assert st0.numel() == 0
         g = torch.ops.hexgnn.fused_backward(params, x, csr, st, qn, None, 500, 4, 35, 10, 2, 128, 0)
         assert g.shape == (P,)
+
+
+def test_deepcopy_and_pickle_reflatten(lib_built):
+    """`copy.deepcopy(model)` / pickling clone every Parameter, so the copy's names no longer alias its flat
+    buffer; the module must notice and re-flatten instead of feeding stale weights to the kernels."""
+    import copy
+    import io
+    import torch
+    from gnn_hex_b200 import ModernTwoHeaded
+    torch.manual_seed(0)
+    m = ModernTwoHeaded(12, 3, 2)
+    m._ensure_flat()
+    assert m._aliased()
+    for clone in (copy.deepcopy(m), None):
+        if clone is None:
+            buf = io.BytesIO()
+            torch.save(m, buf)
+            buf.seek(0)
+            clone = torch.load(buf, weights_only=False)
+        clone.load_state_dict({k: v + 1 for k, v in m.state_dict().items()})
+        clone._ensure_flat()
+        assert clone._aliased() and clone._flat.data_ptr() != m._flat.data_ptr()
+        w = clone.gnn.convs[1].lin_r.weight
+        off = clone._slices[5][0]
+        assert torch.equal(clone._flat[off:off + w.numel()], w.reshape(-1))
+        assert torch.equal(w, m.gnn.convs[1].lin_r.weight + 1)
+        with torch.no_grad():
+            w.add_(1)                                   # an optimizer step on the names moves the kernels' buffer too
+        assert torch.equal(clone._flat[off:off + w.numel()], ((m.gnn.convs[1].lin_r.weight + 1) + 1).reshape(-1))
+    assert m._aliased()

@@ -40,8 +40,17 @@ def _worker(rank, world, port, out):
         w = m.gnn.convs[3].lin_l.weight
         ok_alias = w.grad.data_ptr() == m.flat_gradient.data_ptr() + 4 * m._slices[9][0] and torch.equal(
             w.grad.reshape(-1), want[m._slices[9][0]:m._slices[9][0] + w.numel()])
+        # noisy nets: the advantage layers' mu / sigma gradients live outside the flat buffer and are reduced with it
+        mn = ModernTwoHeaded(12, 3, 2, noisy_dqn=True)
+        mn._flatten()
+        mn._flat_grad_buffer().fill_(float(rank + 1))
+        mn._point_grads()
+        mn._noisy_grad = torch.full((2, 2, 13), float(10 * (rank + 1)))
+        mn.allreduce_gradients()
+        tot = float(sum(r + 1 for r in range(world)))
+        ok_noisy = bool(torch.all(mn._noisy_grad == 10 * tot)) and bool(torch.all(mn.flat_gradient == tot))
         b = bench.make_batch("play", rank)
-        out[rank] = (ok_sum, ok_alias, int(b.num_graphs), int(b.x.shape[0]), float(b.x[:, 0].sum()))
+        out[rank] = (ok_sum, ok_alias and ok_noisy, int(b.num_graphs), int(b.x.shape[0]), float(b.x[:, 0].sum()))
     finally:
         dist.destroy_process_group()
 
