@@ -4,7 +4,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libhexgnn.so")
+LIB_PATH = os.environ.get("HEXGNN_LIB") or os.path.join(_HERE, "libhexgnn.so")
 
 HEXGNN_ADV_ONLY = 1
 HEXGNN_SEPARATE = 2

@@ -5,7 +5,8 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-LIB = os.path.join(HERE, "libhexgnn.so")
+# HEXGNN_LIB: build / load another file instead (e.g. a -DHEXGNN_PHASES profiling build beside the product build)
+LIB = os.environ.get("HEXGNN_LIB") or os.path.join(HERE, "libhexgnn.so")
 SOURCES = ["api.cu", "csr_build.cu", "pack.cu", "sage_fwd_simt.cu", "sage_bwd_simt.cu", "tc_selftest.cu", "pack_tc.cu", "sage_fwd_tc.cu", "sage_bwd_tc.cu", "sage_dw_tc.cu", "td_loss.cu", "sage_big.cu", "optim.cu", "collate.cu", "noisy.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "--compiler-options", "-fPIC", "-Xptxas", "-v"]
@@ -33,7 +34,7 @@ def build(force=False, verbose=False):
         return LIB
     flags = NVCC_FLAGS + (["-DHEXGNN_PHASES"] if os.environ.get("HEXGNN_PHASES") == "1" else [])
     flags += ["-D" + m for m in os.environ.get("HEXGNN_DEFINES", "").split() if m]   # experiment switches
-    objdir = os.path.join(HERE, "..", "build")
+    objdir = os.path.join(HERE, "..", "build" if not os.environ.get("HEXGNN_LIB") else "build_alt")
     os.makedirs(objdir, exist_ok=True)
     procs = []
     for s in SOURCES:

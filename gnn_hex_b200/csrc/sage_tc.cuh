@@ -71,12 +71,12 @@ __device__ __forceinline__ uint32_t rm32_granule_off(int g, int row) {   // 8-ch
   return (uint32_t)(g >> 2) * kImgBlockBytes + (uint32_t)(row >> 2) * 512u + (uint32_t)(row & 3) * 128u +
          ((uint32_t)((g & 3) ^ (row & 3)) << 5);
 }
-// ReLU sign masks of every layer output: one u32 per (layer, tile, column slice, row); bit gi*8+u is set iff
-// h[row][(slice + gi*kTcSlices)*8 + u] > 0 -- the (row, slice) thread mapping of both epilogues, so the backward
-// chain reads ONE coalesced word per thread and layer instead of the activation image.
+// ReLU sign masks of every layer output: four u32 per (layer, tile, row) -- the four warp ballots of the forward's
+// (warp = row, lane = 4 channels) combine pass: bit l of word c is set iff h[row][4 l + c] > 0 -- so the backward chain
+// reads ONE 16-byte word group per thread and layer instead of the activation image.
 inline int64_t tc_mask_words(const Dims& d, int64_t B) { return (int64_t)d.Lt * B * kTcSlices * kTcRows; }
 // forward stash: [Lt][B tiles][act_blocks*16KB] images + row-major embedding copy [N][Hp] (final_conv_acts)
-// + sign masks [Lt][B][kTcSlices][128] u32
+// + sign masks [Lt][B][128] uint4
 __host__ __device__ inline int64_t tc_stash_mask_off_floats(const Dims& d, int64_t N, int64_t B) {
   return (int64_t)d.Lt * B * tc_act_blocks(d.Hp) * (kImgBlockBytes / 4) + N * d.Hp;
 }
