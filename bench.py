@@ -65,17 +65,21 @@ def peaks():
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
 
 
-def make_batch(workload, rank=0):
-    """256 positions per rank.  Rank r rotates the fixture by 32*r so shards differ."""
+def make_batch(workload, rank=0, world=1):
+    """This rank's shard of the global replay batch of 256 * world positions (weak scaling: 256 per GPU).  The global
+    batch is the fixture repeated once per rank, rotated by 32 positions each time so the shards differ; it is split into
+    contiguous graph ranges balanced by node count (data.shard_by_nodes)."""
     from gnn_hex_b200 import data
     import positions
     if workload == "empty":
-        gs = [positions.empty_board(11, 1)] * BATCH
+        base = [positions.empty_board(11, 1)] * BATCH
     else:
-        gs = positions.load_positions(FIXTURE, maker=1)
-        k = (32 * rank) % len(gs)
-        gs = (gs[k:] + gs[:k])[:BATCH]
-    return data.collate(gs)
+        base = positions.load_positions(FIXTURE, maker=1)[:BATCH]
+    gs = []
+    for r in range(world):
+        k = (32 * r) % len(base)
+        gs += base[k:] + base[:k]
+    return data.collate(data.shard_graphs(gs, world, rank))
 
 
 def loss_inputs(batch, seed=1):
@@ -150,6 +154,35 @@ class ClockSampler:
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max((r[2] for r in inside), default=None),
                 "power_w_max": max((r[3] for r in inside), default=None), "samples": len(inside),
                 "window": where, "reasons": reasons}
+
+
+def read_ncu_summary():
+    """Newest profiles/ncu_full_r*.csv (written by tools/ncu_summary.py from an `ncu --set full` capture of this command):
+    per kernel the DRAM bytes per launch and sm__pipe_tensor_cycles_active (% of peak while the SM is active)."""
+    import csv
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "ncu_full_r*.csv")), key=os.path.getmtime)
+    for path in reversed(sorted(files, key=lambda f: os.path.basename(f))):
+        try:
+            with open(path) as f:
+                rows = list(csv.reader(f))
+            head = rows[0]
+            table = {r[0]: r for r in rows[1:] if r}
+            out = {}
+            for col in range(2, len(head)):
+                name = head[col]
+                for key in ("sage_fwd_tc_kernel", "sage_bwd_tc_kernel", "sage_dw_tc_kernel", "csr_build_fused_kernel", "reduce_tc_kernel"):
+                    if key in name:
+                        rd, wr = float(table["dram__bytes_read.sum"][col]), float(table["dram__bytes_write.sum"][col])
+                        unit = table["dram__bytes_read.sum"][1].lower()
+                        mul = 1e6 if unit.startswith("mbyte") else 1e3 if unit.startswith("kbyte") else 1e9 if unit.startswith("gbyte") else 1.0
+                        out[key] = {"dram_bytes": (rd + wr) * mul,
+                                    "tensor_pct": float(table["sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active"][col])}
+            if out:
+                return {"file": os.path.relpath(path, ROOT), "kernels": out}
+        except (OSError, KeyError, ValueError, IndexError):
+            continue
+    return None
 
 
 def time_cpu_port(batch, steps, warmup, max_seconds=None, device=None):
@@ -239,33 +272,36 @@ def run_fused(args, rank, world, local_rank):
     if world > 1:
         collective = "p2p (hexgnn_allreduce_p2p over NVLink peer memory)" if (
             args.allreduce == "p2p" and model.enable_p2p_allreduce()) else "nccl all_reduce"
-    batch = make_batch(args.workload, rank)
+    batch = make_batch(args.workload, rank, world)
     hb = batch.pin_memory()                      # HOST copy of the step's inputs (e2e arm)
     db = batch.to(dev)                           # resident copy (value arm)
     action, target, weight = [t.to(dev) for t in loss_inputs(batch)]
-    scale = 1.0 / world                          # loss = mean over the GLOBAL batch (rainbow.py:312)
+    global_graphs = batch.num_graphs
+    if world > 1:
+        t = torch.tensor([batch.num_graphs], dtype=torch.int64, device=dev)
+        dist.all_reduce(t)
+        global_graphs = int(t.item())
+    scale = batch.num_graphs / global_graphs     # loss = mean over the GLOBAL batch (rainbow.py:312)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
-    loss_host = torch.empty(1, dtype=torch.float32).pin_memory()
-
-    def td_loss(q, ptr):
-        # rainbow.py:301-312 (PER-weighted MSE) as ONE fused launch: loss, td errors and dloss/dq
-        return ops.td_loss(q, ptr, action, target, weight, "mse", scale)[0]
+    # what the learner reads back every step: the loss and the B TD errors that become the PER priorities (rainbow.py:306-309)
+    out_host = torch.empty(1 + batch.num_graphs, dtype=torch.float32).pin_memory()
 
     fused_api = args.api == "train_step" and args.path != "simt"
 
     def fwd_loss_bwd(b):
         if fused_api:
             # rainbow.py:301-316 in one call; sets p.grad exactly like the autograd route (bit-identical, tested)
-            return model.train_step(b.x, b.edge_index, b.batch, b.ptr, action=action, target=target, weight=weight,
-                                    kind="mse", scale=scale)[0]
+            loss, td_err, _ = model.train_step(b.x, b.edge_index, b.batch, b.ptr, action=action, target=target,
+                                               weight=weight, kind="mse", scale=scale)
+            return loss, td_err
         q = model(b.x, b.edge_index, b.batch, b.ptr)
-        loss = td_loss(q, b.ptr)
+        loss, td_err = ops.td_loss(q, b.ptr, action, target, weight, "mse", scale)
         loss.backward()
-        return loss
+        return loss, td_err
 
     def step_resident():
         model.zero_grad(set_to_none=True)
-        loss = fwd_loss_bwd(db)
+        loss, _ = fwd_loss_bwd(db)
         if world > 1:
             model.allreduce_gradients()
         return loss
@@ -273,10 +309,11 @@ def run_fused(args, rank, world, local_rank):
     def step_e2e():
         model.zero_grad(set_to_none=True)
         b = hb.to(dev, non_blocking=True)
-        loss = fwd_loss_bwd(b)
+        loss, td_err = fwd_loss_bwd(b)
         if world > 1:
             model.allreduce_gradients()
-        loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
+        out_host[:1].copy_(loss.detach().reshape(1), non_blocking=True)
+        out_host[1:].copy_(td_err.detach(), non_blocking=True)
         return loss
 
     def barrier():
@@ -343,7 +380,7 @@ def run_fused(args, rank, world, local_rank):
             dist.destroy_process_group()
         return
 
-    graphs = batch.num_graphs * world
+    graphs = global_graphs
     f_fwd, f_train = flops_train(batch)
     pk = peaks()
     # the node-linear contractions run in fp32 (SIMT) or 3xTF32 (tcgen05); the tensor-pipe roofline of
@@ -370,10 +407,14 @@ def run_fused(args, rank, world, local_rank):
         parts = {"avg_launch_ms": fwd_avg_ms, "flops_per_launch": f_fwd, "achieved": tf(f_fwd, fwd_avg_ms),
                  "frac": (tf(f_fwd, fwd_avg_ms) or 0) / tf32_peak}
     achieved = tf(unit_flops, unit_ms)
-    # ncu --set full (same workload): dram read + write per launch, summed over the kernels of the unit
+    # ncu --set full (same workload): dram read + write per launch, summed over the kernels of the unit, and the tensor-pipe
+    # activity per kernel -- READ from the newest committed capture under profiles/ (never measured under the profiler here)
+    ncu = read_ncu_summary() if (args.workload == "play" and args.path != "simt") else None
     traffic = None
-    if args.workload == "play" and args.path != "simt":
-        traffic = (157.8e6 + 302.0e6 + 503.4e6) if trio_n else (302.0e6 + 503.4e6)
+    if ncu:
+        names = ("sage_fwd_tc_kernel", "sage_bwd_tc_kernel", "sage_dw_tc_kernel") if trio_n else ("sage_bwd_tc_kernel", "sage_dw_tc_kernel")
+        if all(k in ncu["kernels"] for k in names):
+            traffic = sum(ncu["kernels"][k]["dram_bytes"] for k in names)
     line = {
         "metric": METRIC, "value": graphs * args.steps / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
@@ -383,12 +424,14 @@ def run_fused(args, rank, world, local_rank):
         "e2e": {"value": graphs * args.steps / (ms_e2e * 1e-3), "unit": UNIT,
                 "h2d_bytes_per_step": int(hb._packed.numel()) if getattr(hb, "_packed", None) is not None else
                 int(sum(t.numel() * t.element_size() for t in (hb.x, hb.edge_index, hb.batch, hb.ptr))),
-                "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps},
+                "d2h_bytes_per_step": int(out_host.numel()) * 4, "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": int(launches),
         "roofline": {"bound": "tensor", "kernel": unit_name,
                      "achieved": achieved, "peak": tf32_peak, "unit": "TFLOP/s",
                      "frac": (achieved / tf32_peak) if achieved else None, "traffic": traffic,
-                     "traffic_source": "ncu dram__bytes_read+write per launch, summed over the unit's kernels, profiles/ncu_full_r1h_tc.csv",
+                     "traffic_source": ("ncu dram__bytes_read+write per launch, summed over the unit's kernels, " + ncu["file"]) if ncu else None,
+                     "tensor_pipe_active_pct": ({k: v["tensor_pct"] for k, v in ncu["kernels"].items() if k.startswith("sage_")}
+                                                if ncu else None),
                      "peak_source": f"0.5 x bf16_tflops ({pk['source']}) = dense TF32",
                      "arithmetic": "3xTF32 (3 tensor-core passes per algorithmic FLOP: ceiling 1/3 of peak)",
                      "flops_per_launch": unit_flops, "avg_launch_ms": unit_ms,

@@ -92,6 +92,42 @@ def collate(graphs: Sequence[HexGraph]) -> HexBatch:
     return HexBatch(x=x, edge_index=edge_index, batch=batch, ptr=ptr, num_graphs=len(graphs))
 
 
+def shard_by_nodes(num_nodes: Sequence[int], world: int):
+    """Data-parallel partition of a replay batch: `world` CONTIGUOUS ranges of graphs, balanced by their
+    node counts (positions have 3..123 nodes, so equal graph counts would not be equal work).  Boundary k is the graph
+    index whose node prefix sum is nearest to k * total / world; every rank gets at least one graph when there are at
+    least `world` of them.  Returns [(start, end)] * world.  Pure host arithmetic on the `ptr` / node-count vector; the
+    same on every rank, no communication."""
+    n = [int(v) for v in num_nodes]
+    G = len(n)
+    if world < 1:
+        raise ValueError("world must be >= 1")
+    pre = [0]
+    for v in n:
+        pre.append(pre[-1] + v)
+    total = pre[-1]
+    cuts = [0]
+    for k in range(1, world):
+        lo = min(cuts[-1] + 1, G) if G >= world else cuts[-1]          # keep ranks non-empty when possible
+        hi = max(lo, G - (world - k)) if G >= world else G
+        target = total * k / world
+        best = lo
+        for g in range(lo, hi + 1):                                   # prefix sums are monotone: first minimum wins
+            if abs(pre[g] - target) < abs(pre[best] - target):
+                best = g
+            elif pre[g] > target:
+                break
+        cuts.append(best)
+    cuts.append(G)
+    return [(cuts[k], cuts[k + 1]) for k in range(world)]
+
+
+def shard_graphs(graphs: Sequence[HexGraph], world: int, rank: int) -> List[HexGraph]:
+    """This rank's contiguous share of `graphs` under `shard_by_nodes`."""
+    a, b = shard_by_nodes([int(g.x.shape[0]) for g in graphs], world)[rank]
+    return list(graphs[a:b])
+
+
 class DeviceCollator:
     """`Batch.from_data_list` over graphs that already live on the GPU (the learner's replay-buffer samples,
     replay_buffer.py:116-117,215-216) as ONE kernel launch (hexgnn_collate) instead of 2 B small cat / add kernels

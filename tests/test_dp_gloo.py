@@ -49,7 +49,7 @@ def _worker(rank, world, port, out):
         mn.allreduce_gradients()
         tot = float(sum(r + 1 for r in range(world)))
         ok_noisy = bool(torch.all(mn._noisy_grad == 10 * tot)) and bool(torch.all(mn.flat_gradient == tot))
-        b = bench.make_batch("play", rank)
+        b = bench.make_batch("play", rank, world)
         out[rank] = (ok_sum, ok_alias and ok_noisy, int(b.num_graphs), int(b.x.shape[0]), float(b.x[:, 0].sum()))
     finally:
         dist.destroy_process_group()
@@ -67,3 +67,23 @@ def test_flat_gradient_allreduce_and_sharding_world2():
         assert ok_sum and ok_alias and ng == 256 and nn > 0
     # shards are different rotations of the fixture (same multiset of graphs, different order)
     assert res[0][3] == res[1][3] and res[0][4] == res[1][4]
+
+
+def test_shard_by_nodes_is_a_balanced_contiguous_cover():
+    """contiguous graph ranges per rank, balanced by node count."""
+    import random
+    sys.path.insert(0, ROOT)
+    from gnn_hex_b200 import data
+    rng = random.Random(3)
+    for world in (1, 2, 3, 4, 8):
+        for G in (0, 1, 5, 8, 256, 2048):
+            ns = [rng.randint(3, 123) for _ in range(G)]
+            r = data.shard_by_nodes(ns, world)
+            assert len(r) == world and r[0][0] == 0 and r[-1][1] == G
+            assert all(r[k][1] == r[k + 1][0] and r[k][0] <= r[k][1] for k in range(world - 1))
+            if G >= world:
+                assert all(b > a for a, b in r)
+                loads = [sum(ns[a:b]) for a, b in r]
+                assert max(loads) - min(loads) <= 2 * 123 + 1, (world, G, loads)
+    # a node-balanced split is not a graph-count split: one heavy graph and many light ones
+    assert data.shard_by_nodes([120] + [4] * 30, 2) == [(0, 1), (1, 31)]
