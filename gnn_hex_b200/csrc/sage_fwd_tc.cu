@@ -41,6 +41,7 @@ struct FwdTcArgs {
   int* tile_flag;   // hexgnn_train_step: released per finished tile (the backward chain starts under the last round)
   int stages;       // ring depth (what fits beside the runtime-sized bias table)
   int max_pair;     // 2: two tiles in flight per CTA; 1: one at a time (HEXGNN_FWD_PAIR=1, for A/B measurements)
+  int pack_grid;    // 1: only ceil(tiles / max_pair) CTAs take tiles (every CTA gets a full group when tiles < 2 x SMs)
 };
 
 constexpr int kFwdMaxStages = 6;
@@ -59,13 +60,13 @@ struct FwdTcSmem {
   static constexpr int off_pool = off_rows + 5 * kTcRows * 4;                    // float [4*Hp]
   static constexpr int off_hid = off_pool + 4 * Hp * 4;                          // float [Hp]
   static constexpr int off_misc = off_hid + Hp * 4;                              // float [16]
-  // per-tile slot (x 2): the tile's CSR, gather table and 1 / deg
+  // per-tile slot (x 2): the tile's CSR, row table and 1 / deg
   static constexpr int slot_inv = 0;                                             // float [128]
   static constexpr int slot_rowptr = slot_inv + kTcRows * 4;                     // int [128 + 4]
   static constexpr int slot_gp = slot_rowptr + (kTcRows + 4) * 4;                // int [64 + 4]
   static constexpr int slot_col = slot_gp + (kMaxTileGraphs + 4) * 4;            // u16 [ECAP]
-  static constexpr int slot_gtab = (slot_col + ECAP * 2 + 15) & ~15;             // gather table (sage_tc.cuh)
-  static constexpr int slot_bytes = (slot_gtab + gather_tab_bytes() + 15) & ~15;
+  static constexpr int slot_gtab = (slot_col + ECAP * 2 + 15) & ~15;             // row table (sage_tc.cuh)
+  static constexpr int slot_bytes = (slot_gtab + row_tab_bytes() + 15) & ~15;
   static constexpr int off_slot = off_misc + 64;
   static constexpr int off_bar = off_slot + 2 * slot_bytes;                      // u64 [2 * kFwdMaxStages + 8], u32 tmem slot
   static constexpr int off_bias = off_bar + (2 * kFwdMaxStages + 8) * 8 + 16;    // float [Lt][Hp] (runtime sized)
@@ -94,9 +95,10 @@ __device__ __forceinline__ TileDims tile_dims(const CsrView& v, int t, int ecap)
   return d;
 }
 // The CTA's next tile in schedule order (sage_tc.cuh tile_position), valid or not; false when the CTA has run out.
-__device__ __forceinline__ bool fetch_tile(const CsrView& v, int ntiles, bool zig, int ecap, int& rnd, TileDims& td) {
-  while (rnd * (int)gridDim.x < ntiles) {
-    const int ti = tile_position(rnd, blockIdx.x, gridDim.x, zig);
+__device__ __forceinline__ bool fetch_tile(const CsrView& v, int ntiles, int G, bool zig, int ecap, int& rnd, TileDims& td) {
+  if ((int)blockIdx.x >= G) return false;
+  while (rnd * G < ntiles) {
+    const int ti = tile_position(rnd, blockIdx.x, G, zig);
     ++rnd;
     if (ti >= ntiles) continue;
     td = tile_dims(v, v.tile_order[ti], ecap);
@@ -106,12 +108,12 @@ __device__ __forceinline__ bool fetch_tile(const CsrView& v, int ntiles, bool zi
 }
 // Up to `max_pair` VALID tiles; tiles that do not fit are reported through `bad` (the epilogue poisons their outputs).
 template <typename BadFn>
-__device__ __forceinline__ int fetch_group(const CsrView& v, int ntiles, bool zig, int ecap, int max_pair, int& rnd,
+__device__ __forceinline__ int fetch_group(const CsrView& v, int ntiles, int G, bool zig, int ecap, int max_pair, int& rnd,
                                            TileDims (&td)[2], BadFn bad) {
   int np = 0;
   while (np < max_pair) {
     TileDims t;
-    if (!fetch_tile(v, ntiles, zig, ecap, rnd, t)) break;
+    if (!fetch_tile(v, ntiles, G, zig, ecap, rnd, t)) break;
     if (!t.ok) { bad(t); continue; }
     td[np++] = t;
   }
@@ -153,6 +155,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const int ntiles = *a.csr.ntiles;
   const bool zig = a.tile_flag == nullptr;
+  // CTAs that take tiles: with fewer than max_pair x gridDim tiles only ceil(tiles / max_pair) CTAs work, each on a full
+  // group -- a tile that runs alone pays its GEMMs un-overlapped, and the SMs left over go to the next kernel at once
+  int G = gridDim.x;
+  if (a.pack_grid) { const int want = (ntiles + a.max_pair - 1) / a.max_pair; G = want < G ? (want < 1 ? 1 : want) : G; }
   const long long t_kernel0 = PH_NOW();
   long long ph0 = 0, ph1 = 0, ph2 = 0, ph3 = 0, ph4 = 0, ph5 = 0, ph6 = 0, ph7 = 0, ph11 = 0, ntl = 0;
 
@@ -179,7 +185,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
       int rnd = 0;
       TileDims td[2];
       for (;;) {
-        const int np = fetch_group(a.csr, ntiles, zig, S::ECAP, a.max_pair, rnd, td, [](const TileDims&) {});
+        const int np = fetch_group(a.csr, ntiles, G, zig, S::ECAP, a.max_pair, rnd, td, [](const TileDims&) {});
         if (np == 0) break;
         for (int s = 1; s < Lt; ++s) {
           const uint8_t* src = (const uint8_t*)a.pv.wimg + (size_t)(s - 1) * NQ * S::stage_bytes;
@@ -203,7 +209,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
       int rnd = 0;
       TileDims td[2];
       for (;;) {
-        const int np = fetch_group(a.csr, ntiles, zig, S::ECAP, a.max_pair, rnd, td, [](const TileDims&) {});
+        const int np = fetch_group(a.csr, ntiles, G, zig, S::ECAP, a.max_pair, rnd, td, [](const TileDims&) {});
         if (np == 0) break;
         for (int s = 1; s < Lt; ++s) {
           for (int k = 0; k < np; ++k, ++job) {
@@ -259,29 +265,43 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
 
     auto slot_ptr = [&](int k) { return smem + S::off_slot + k * S::slot_bytes; };
 
-    // --- a finished row of layer s, lane = channels [4 lane, 4 lane + 4): shared (in place over Zr), stash image, sign
-    //     mask (4 ballot words per row: bit l of word c = h[4 l + c] > 0), ones-channel, embedding copy ---------------
-    auto finish_row = [&](const TileDims& td, int s, int r, float4 h) {
-      if (lane < NV) *(float4*)(bufR + r * P + lane * 4) = h;
+    // --- a finished row of one (tile, layer): lane = channels [4 lane, 4 lane + 4) -> shared (in place over Zr), stash
+    //     image, sign mask (4 ballot words per row: bit l of word c = h[4 l + c] > 0), ones-channel, embedding copy.
+    //     The per-(tile, layer) addresses are formed once (RowOut), the per-row part is a handful of integer ops.
+    struct RowOut { char* img; uint4* mrow; float* erow; int gx; };
+    auto row_out = [&](const TileDims& td, int s) {
+      RowOut o;
+      o.img = nullptr; o.mrow = nullptr; o.erow = nullptr; o.gx = 0;
       if (a.stash) {
-        char* img = (char*)a.stash + ((size_t)s * a.B + td.t) * img_bytes;
-        if (lane < NV) *(float4*)(img + rm32_granule_off(lane >> 1, r) + (lane & 1) * 16) = h;
-        else if (lane == NV) st_global_v8(img + rm32_granule_off(NG, r), 1.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f);
+        const int g = lane < NV ? (lane >> 1) : NG;        // this lane's 8-channel granule (lane NV: the ones channel)
+        o.img = (char*)a.stash + ((size_t)s * a.B + td.t) * img_bytes + (size_t)(g >> 2) * kImgBlockBytes + (lane < NV ? (lane & 1) * 16 : 0);
+        o.gx = g & 3;
+        o.mrow = mask_base + (size_t)s * mask_layer + (size_t)td.t * kTcRows;
+        if (s == a.d.L - 1) o.erow = emb + (int64_t)td.r0 * Hp + (lane < NV ? lane : 0) * 4;
+      }
+      return o;
+    };
+    auto finish_row = [&](const RowOut& o, int r, float4 h) {
+      if (lane < NV) *(float4*)(bufR + r * P + lane * 4) = h;
+      if (o.img) {
+        char* dst = o.img + (r >> 2) * 512 + (r & 3) * 128 + ((o.gx ^ (r & 3)) << 5);      // rm32_granule_off, row part
+        if (lane < NV) *(float4*)dst = h;
+        else if (lane == NV) st_global_v8(dst, 1.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f);
         const bool in = lane < NV;
         const uint32_t b0 = __ballot_sync(0xffffffffu, in && h.x > 0.f), b1 = __ballot_sync(0xffffffffu, in && h.y > 0.f);
         const uint32_t b2 = __ballot_sync(0xffffffffu, in && h.z > 0.f), b3 = __ballot_sync(0xffffffffu, in && h.w > 0.f);
-        if (lane == 0) mask_base[(size_t)s * mask_layer + (size_t)td.t * kTcRows + r] = make_uint4(b0, b1, b2, b3);
-        if (s == a.d.L - 1 && lane < NV) *(float4*)(emb + (int64_t)(td.r0 + r) * Hp + lane * 4) = h;
+        if (lane == 0) o.mrow[r] = make_uint4(b0, b1, b2, b3);
+        if (o.erow && lane < NV) *(float4*)(o.erow + r * Hp) = h;
       }
     };
     // rows [n, ceil32(n)) of the stash image are zeros (the weight-gradient GEMM contracts whole 32-row chunks)
-    auto finish_tail = [&](const TileDims& td, int s) {
-      if (!a.stash) return;
-      char* img = (char*)a.stash + ((size_t)s * a.B + td.t) * img_bytes;
-      const int n32 = (td.n + 31) & ~31;
-      for (int r = td.n + wid; r < n32; r += kTcEpiWarps) {
-        if (lane < NV) *(float4*)(img + rm32_granule_off(lane >> 1, r) + (lane & 1) * 16) = make_float4(0.f, 0.f, 0.f, 0.f);
-        else if (lane == NV) st_global_v8(img + rm32_granule_off(NG, r), 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f);
+    auto finish_tail = [&](const RowOut& o, int n) {
+      if (!o.img) return;
+      const int n32 = (n + 31) & ~31;
+      for (int r = n + wid; r < n32; r += kTcEpiWarps) {
+        char* dst = o.img + (r >> 2) * 512 + (r & 3) * 128 + ((o.gx ^ (r & 3)) << 5);
+        if (lane < NV) *(float4*)dst = make_float4(0.f, 0.f, 0.f, 0.f);
+        else if (lane == NV) st_global_v8(dst, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f);
       }
     };
 
@@ -292,7 +312,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
       int* rowptr_s = (int*)(sl + S::slot_rowptr);
       int* gp_s = (int*)(sl + S::slot_gp);
       unsigned short* col_s = (unsigned short*)(sl + S::slot_col);
-      const GatherTab gtab = gather_tab_view(sl + S::slot_gtab);
+      const RowTab rtab = row_tab_view(sl + S::slot_gtab);
       const int n = td.n, r0 = td.r0;
       int bad = 0;
       for (int i = tid; i <= kTcRows; i += kTcEpiThreads) rowptr_s[i] = (i <= n ? a.csr.rowptr[r0 + i] : a.csr.rowptr[r0 + n]) - td.e0;
@@ -313,7 +333,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
       }
       if (bad) atomicOr(a.csr.status, bad);
       epi_bar();
-      gather_build<NJ>(gtab, rowptr_s, col_s, n, tid);
+      row_tab_build<NJ>(rtab, rowptr_s, col_s, n, tid);
       for (int i = tid; i < kTcRows; i += kTcEpiThreads) {
         const int b = rowptr_s[i], e = rowptr_s[i + 1];
         const int deg = e - b;
@@ -362,14 +382,16 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
         wr0[j] = cv ? wr[2 * c] : 0.f; wr1[j] = cv ? wr[2 * c + 1] : 0.f;
         bb[j] = cv ? bl[c] : 0.f;
       }
-      for (int r = wid; r < td.n; r += kTcEpiWarps) {
+      const RowOut ro = row_out(td, 0);
+      const int n = td.n;
+      for (int r = wid; r < n; r += kTcEpiWarps) {
         const float xm0 = m0_s[r], xm1 = m1_s[r], xx0 = x0_s[r], xx1 = x1_s[r];
         float o[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) o[j] = fmaxf(wl0[j] * xm0 + wl1[j] * xm1 + bb[j] + wr0[j] * xx0 + wr1[j] * xx1, 0.f);
-        finish_row(td, 0, r, make_float4(o[0], o[1], o[2], o[3]));
+        finish_row(ro, r, make_float4(o[0], o[1], o[2], o[3]));
       }
-      finish_tail(td, 0);
+      finish_tail(ro, n);
       epi_bar();
       write_A(td);
     };
@@ -414,24 +436,27 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
       }
     };
 
-    // --- P2: agg_i = sum_{j -> i} Zl_j in CSR order (table of sage_tc.cuh), h'_i = relu(agg_i / deg_i + (Zr_i + b)) ---
+    // --- P2: agg_i = sum_{j -> i} Zl_j (row table of sage_tc.cuh: warp = one row, four independent accumulators over the
+    //     neighbours k = 0, 1, 2, 3 mod 4, combined (s0 + s1) + (s2 + s3)); h'_i = relu(agg_i / deg_i + (Zr_i + b)) ----------
     auto gather_combine = [&](const TileDims& td, int k, int s) {
       uint8_t* sl = slot_ptr(k);
       const float* inv_s = (const float*)(sl + S::slot_inv);
-      const GatherTab g = gather_tab_view(sl + S::slot_gtab);
+      const RowTab g = row_tab_view(sl + S::slot_gtab);
+      const RowOut ro = row_out(td, s);
+      const int n = td.n;
       const int ln = lane < NV ? lane : 0;               // idle lanes shadow lane 0 (their results are discarded)
       const char* sb = (const char*)bufL + ln * 16;
-      const int ng = *g.ngroups;
-      for (int gi = wid; gi < ng; gi += kTcEpiWarps) {
-        const int len = g.glen[gi];
-        const int4* tp = g.tab + g.gstart[gi];
-        const int4 rw = g.grow[gi];
+      const float* zb = bufR + ln * 4;
+      for (int r = wid; r < n; r += kTcEpiWarps) {
+        const int s0 = g.rstart[r], s1 = g.rstart[r + 1];
+        const float iv = inv_s[r];
+        const float4 z = *(const float4*)(zb + r * P);
         float4 acc[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        int kk = 0;
-        for (; kk + 2 <= len; kk += 2) {
-          const int4 o0 = tp[kk], o1 = tp[kk + 1];
+        int kk = s0;
+        for (; kk + 2 <= s1; kk += 2) {
+          const int4 o0 = g.tab[kk], o1 = g.tab[kk + 1];
           const float4 v0 = *(const float4*)(sb + o0.x), v1 = *(const float4*)(sb + o0.y);
           const float4 v2 = *(const float4*)(sb + o0.z), v3 = *(const float4*)(sb + o0.w);
           const float4 u0 = *(const float4*)(sb + o1.x), u1 = *(const float4*)(sb + o1.y);
@@ -439,30 +464,19 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
           fadd2x2(acc[0], v0); fadd2x2(acc[1], v1); fadd2x2(acc[2], v2); fadd2x2(acc[3], v3);
           fadd2x2(acc[0], u0); fadd2x2(acc[1], u1); fadd2x2(acc[2], u2); fadd2x2(acc[3], u3);
         }
-        if (kk < len) {
-          const int4 o0 = tp[kk];
+        if (kk < s1) {
+          const int4 o0 = g.tab[kk];
           const float4 v0 = *(const float4*)(sb + o0.x), v1 = *(const float4*)(sb + o0.y);
           const float4 v2 = *(const float4*)(sb + o0.z), v3 = *(const float4*)(sb + o0.w);
           fadd2x2(acc[0], v0); fadd2x2(acc[1], v1); fadd2x2(acc[2], v2); fadd2x2(acc[3], v3);
         }
-        int rr[4] = {rw.x, rw.y, rw.z, rw.w};
-        if (rw.y == -2) {
-          fadd2x2(acc[0], acc[1]); fadd2x2(acc[0], acc[2]); fadd2x2(acc[0], acc[3]);
-          rr[1] = rr[2] = rr[3] = -1;
-        }
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int r = rr[i];
-          if (r < 0) continue;                            // warp-uniform
-          const float iv = inv_s[r];
-          const float4 z = *(const float4*)(bufR + r * P + ln * 4);
-          float4 h;
-          h.x = fmaxf(fmaf(acc[i].x, iv, z.x), 0.f); h.y = fmaxf(fmaf(acc[i].y, iv, z.y), 0.f);
-          h.z = fmaxf(fmaf(acc[i].z, iv, z.z), 0.f); h.w = fmaxf(fmaf(acc[i].w, iv, z.w), 0.f);
-          finish_row(td, s, r, h);
-        }
+        fadd2x2(acc[0], acc[1]); fadd2x2(acc[2], acc[3]); fadd2x2(acc[0], acc[2]);
+        float4 h;
+        h.x = fmaxf(fmaf(acc[0].x, iv, z.x), 0.f); h.y = fmaxf(fmaf(acc[0].y, iv, z.y), 0.f);
+        h.z = fmaxf(fmaf(acc[0].z, iv, z.z), 0.f); h.w = fmaxf(fmaf(acc[0].w, iv, z.w), 0.f);
+        finish_row(ro, r, h);
       }
-      finish_tail(td, s);
+      finish_tail(ro, n);
     };
 
     // --- dueling head on the final activations (rows of bufR); bufL is scratch by now ------------------------------------
@@ -604,7 +618,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
     int rnd = 0;
     TileDims td[2];
     for (;;) {
-      const int np = fetch_group(a.csr, ntiles, zig, S::ECAP, a.max_pair, rnd, td, poison);
+      const int np = fetch_group(a.csr, ntiles, G, zig, S::ECAP, a.max_pair, rnd, td, poison);
       if (np == 0) break;
       ntl += np;
       long long tq = PH_NOW();
@@ -672,6 +686,15 @@ static int fwd_max_pair() {
   return v;
 }
 
+static int fwd_pack_grid() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("HEXGNN_FWD_PACK_GRID");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v;
+}
+
 template <int NJ>
 static int launch_fwd_tc_t(FwdTcArgs& a, cudaStream_t st) {
   using S = FwdTcSmem<NJ>;
@@ -682,6 +705,7 @@ static int launch_fwd_tc_t(FwdTcArgs& a, cudaStream_t st) {
   if (smem > 227 * 1024) { set_error("forward(tc): %zu bytes of shared memory needed", smem); return HEXGNN_E_UNSUPPORTED; }
   a.stages = stages;
   a.max_pair = fwd_max_pair();
+  a.pack_grid = fwd_pack_grid();
   HEX_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int grid = (int)(a.B < 1 ? 1 : (a.B > bwd_grid_ctas() ? bwd_grid_ctas() : a.B));
   {

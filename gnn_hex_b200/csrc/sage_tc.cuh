@@ -222,6 +222,59 @@ __device__ __forceinline__ void gather_build(const GatherTab& g, const int* __re
   }
   asm volatile("bar.sync 1, %0;" ::"n"(kTcEpiThreads) : "memory");
 }
+// ---- row table (forward kernel): ONE warp walks ONE row.  Step k of a row is an int4 of byte offsets of its neighbours
+// 4k .. 4k+3 (absent ones point at the zero row 128), so a row of degree d takes ceil(d / 4) steps with four independent
+// accumulators, summed (s0 + s1) + (s2 + s3) at the end: fixed order, deterministic.  One row per work unit balances the
+// 16 epilogue warps (6 full rounds for a 94-row tile instead of two ragged rounds of 4-row groups), the terminal rows
+// (degree 20-30) need no special case, and the table is a third of the size (<= (E_cap + 3 * 128) / 4 steps).
+constexpr int kRowTabMaxSteps = (kEdgeCapPerRow * kTcRows + 3 * kTcRows) / 4;
+struct RowTab {
+  int4* tab;      // [kRowTabMaxSteps]
+  int* rstart;    // [128 + 1] first step of every row
+};
+__host__ __device__ constexpr int row_tab_bytes() { return kRowTabMaxSteps * 16 + (kTcRows + 4) * 4; }
+__device__ __forceinline__ RowTab row_tab_view(uint8_t* base) {
+  RowTab g;
+  g.tab = (int4*)base;
+  g.rstart = (int*)(base + kRowTabMaxSteps * 16);
+  return g;
+}
+// All epilogue threads; rowptr_s / col_s complete and visible; ends with the epilogue barrier.
+template <int NJ>
+__device__ __forceinline__ void row_tab_build(const RowTab& g, const int* __restrict__ rowptr_s,
+                                              const unsigned short* __restrict__ col_s, int n, int tid) {
+  constexpr int PB = (16 * NJ + 4) * 4;   // row pitch in bytes
+  const int wid = tid >> 5, lane = tid & 31;
+  if (wid == 0) {
+    int st[4], tot = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int r = 4 * lane + j;
+      const int d = r < n ? rowptr_s[r + 1] - rowptr_s[r] : 0;
+      st[j] = (d + 3) >> 2;
+      tot += st[j];
+    }
+    const int inc = warp_scan_incl(tot, lane);
+    int base = inc - tot;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { g.rstart[4 * lane + j] = base; base += st[j]; }
+    if (lane == 31) g.rstart[kTcRows] = inc;
+  }
+  asm volatile("bar.sync 1, %0;" ::"n"(kTcEpiThreads) : "memory");
+  for (int r = wid; r < n; r += kTcEpiWarps) {
+    const int b = rowptr_s[r], d = rowptr_s[r + 1] - b, s0 = g.rstart[r];
+    for (int k = lane; 4 * k < d; k += 32) {
+      int4 o;
+      o.x = (int)col_s[b + 4 * k] * PB;
+      o.y = (4 * k + 1 < d ? (int)col_s[b + 4 * k + 1] : kTcRows) * PB;
+      o.z = (4 * k + 2 < d ? (int)col_s[b + 4 * k + 2] : kTcRows) * PB;
+      o.w = (4 * k + 3 < d ? (int)col_s[b + 4 * k + 3] : kTcRows) * PB;
+      g.tab[s0 + k] = o;
+    }
+  }
+  asm volatile("bar.sync 1, %0;" ::"n"(kTcEpiThreads) : "memory");
+}
+
 __device__ __forceinline__ void fadd2x2(float4& a, const float4& b) {   // a += b as two packed f32x2 adds
   unsigned long long a0, a1, b0, b1;
   asm("mov.b64 %0, {%1, %2};" : "=l"(a0) : "f"(a.x), "f"(a.y));

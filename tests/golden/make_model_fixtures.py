@@ -31,11 +31,11 @@ import positions  # noqa: E402
 from gnn_hex_b200 import data  # noqa: E402
 
 CASES = {
-    # tag: (hidden, layers, head layers, norm, noisy, positions, count, gradient stride)
-    "S": (35, 10, 2, False, False, "pos_7x7_seed1234.npz", 256, 1),        # BASELINE configs[0] at full size
-    "L": (110, 15, 2, False, False, "pos_11x11_seed1234.npz", 24, 7),      # GNN-L (configs[1] model), 24 positions
-    "S_norm": (35, 10, 2, True, False, "pos_7x7_seed1234.npz", 48, 1),     # --norm True (PyG LayerNorm, whole batch)
-    "S_noisy": (35, 10, 2, False, True, "pos_7x7_seed1234.npz", 48, 1),    # --noisy_dqn True
+    # tag: (hidden, layers, head layers, norm, noisy, positions, count, gradient stride, weight gain)
+    "S": (35, 10, 2, False, False, "pos_7x7_seed1234.npz", 256, 1, 1.5),        # BASELINE configs[0] at full size
+    "L": (110, 15, 2, False, False, "pos_11x11_seed1234.npz", 24, 7, 1.7),      # GNN-L (configs[1] model), 24 positions
+    "S_norm": (35, 10, 2, True, False, "pos_7x7_seed1234.npz", 48, 1, 1.5),     # --norm True (PyG LayerNorm, whole batch)
+    "S_noisy": (35, 10, 2, False, True, "pos_7x7_seed1234.npz", 48, 1, 1.5),    # --noisy_dqn True
 }
 
 
@@ -50,14 +50,14 @@ def batch_of(case, maker):
 
 def run_case(ref, tag):
     case = CASES[tag]
-    out = {"gstride": np.int64(case[7]), "count": np.int64(case[6])}
+    out = {"gstride": np.int64(case[7]), "count": np.int64(case[6]), "gain": np.float64(case[8])}
     for maker in (1, 0):
         b = batch_of(case, maker)
         action, target, weight = helpers.loss_inputs(b)
         res = {}
         for dt in (torch.float32, torch.float64):
             model = ref.get_pre_defined("modern_two_headed", args_of(case))
-            helpers.set_hash_weights(model, seed=0)
+            helpers.set_hash_weights(model, seed=0, gain=case[8])
             model = model.to(dt)
             x = b.x.to(dt)
             q = model(x, b.edge_index, b.batch, b.ptr)

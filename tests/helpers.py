@@ -126,13 +126,16 @@ def hash_uniform(name: str, shape, seed: int = 0) -> torch.Tensor:
 
 
 @torch.no_grad()
-def set_hash_weights(module: torch.nn.Module, seed: int = 0) -> None:
+def set_hash_weights(module: torch.nn.Module, seed: int = 0, gain: float = 1.0) -> None:
     """Fill every parameter / buffer of `module` by NAME (same names in the reference model, the oracle and the product
-    module): matrices U(+-1/sqrt(fan_in)) like the default init, vectors U(+-0.1), LayerNorm weights 1 + U(+-0.2)."""
+    module): matrices U(+-gain/sqrt(fan_in)) (gain 1 = the default init's range), vectors U(+-0.1), LayerNorm weights
+    1 + U(+-0.2).  With gain 1 a 12..17-layer ReLU stack contracts to node-independent embeddings (advantage spread 1e-5 of
+    its mean: Q = v + a - mean(a) is then pure cancellation); the golden cases use gains 1.5 / 1.7, which keep the
+    activations O(1) and the advantages spread over the graph."""
     for name, t in list(module.named_parameters()) + list(module.named_buffers()):
         u = hash_uniform(name, t.shape, seed)
         if t.dim() >= 2:
-            v = u / float(t.shape[-1]) ** 0.5
+            v = gain * u / float(t.shape[-1]) ** 0.5
         elif "norm" in name and name.endswith("weight"):
             v = 1.0 + 0.2 * u
         else:

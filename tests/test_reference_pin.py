@@ -29,10 +29,10 @@ CASES = {
 }
 
 
-def oracle_of(tag, dtype=torch.float32):
+def oracle_of(tag, fx, dtype=torch.float32):
     H, L, Lh, norm, noisy, _ = CASES[tag]
     o = orc.ModernTwoHeadedOracle(H, L, Lh, noisy_dqn=noisy, noisy_sigma0=0.5, norm=norm)
-    helpers.set_hash_weights(o, seed=0)
+    helpers.set_hash_weights(o, seed=0, gain=float(fx["gain"]))
     return o.to(dtype)
 
 
@@ -53,7 +53,7 @@ def test_oracle_equals_reference_module_code(tag, maker):
     fx = helpers.load_model_fixture(tag)
     b = batch_of(tag, fx, maker)
     action, target, weight = (torch.from_numpy(fx[k]) for k in ("action", "target", "weight"))
-    o = oracle_of(tag)
+    o = oracle_of(tag, fx)
     assert sorted(dict(o.named_parameters())) == [str(n) for n in fx["names"]], "parameter names differ from the reference's"
     q = o(b.x, b.edge_index, b.batch, b.ptr)
     emb = o.final_conv_acts.detach()
@@ -87,7 +87,7 @@ def test_fp64_oracle_equals_fp64_reference():
     for tag in ("S", "S_norm"):
         fx = helpers.load_model_fixture(tag)
         b = batch_of(tag, fx, 1)
-        o = oracle_of(tag, torch.float64)
+        o = oracle_of(tag, fx, torch.float64)
         q = o(b.x.double(), b.edge_index, b.batch, b.ptr)
         assert max_rel(q.detach().numpy(), fx["q64_1"]) <= 1e-13
         loss = orc.rainbow_loss(q, b.ptr, torch.from_numpy(fx["action"]), torch.from_numpy(fx["target"]).double(),
