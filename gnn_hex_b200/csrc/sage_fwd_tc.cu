@@ -60,9 +60,8 @@ struct FwdTcSmem {
   static constexpr int off_pool = off_rows + 5 * kTcRows * 4;                    // float [4*Hp]
   static constexpr int off_hid = off_pool + 4 * Hp * 4;                          // float [Hp]
   static constexpr int off_misc = off_hid + Hp * 4;                              // float [16]
-  // per-tile slot (x 2): the tile's CSR, row table and 1 / deg
-  static constexpr int slot_inv = 0;                                             // float [128]
-  static constexpr int slot_rowptr = slot_inv + kTcRows * 4;                     // int [128 + 4]
+  // per-tile slot (x 2): the tile's CSR and row table (whose row headers carry 1 / deg)
+  static constexpr int slot_rowptr = 0;                                          // int [128 + 4]
   static constexpr int slot_gp = slot_rowptr + (kTcRows + 4) * 4;                // int [64 + 4]
   static constexpr int slot_col = slot_gp + (kMaxTileGraphs + 4) * 4;            // u16 [ECAP]
   static constexpr int slot_gtab = (slot_col + ECAP * 2 + 15) & ~15;             // row table (sage_tc.cuh)
@@ -132,7 +131,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
   constexpr int MAXG = (NG + kTcSlices - 1) / kTcSlices;   // granules per (row, slice) thread
   constexpr uint32_t TM_HI = 0, TM_LO = Hp, TM_D = 2 * Hp;     // TMEM columns: R1 = [hi | lo], R2 = [Zl | Zr]
   constexpr uint32_t TM_COLS = (4 * Hp <= 64) ? 64 : (4 * Hp <= 128) ? 128 : (4 * Hp <= 256) ? 256 : 512;
-  static_assert(NV < 32, "lane NV writes the ones-channel granule");
+  static_assert(NV + 2 <= 32, "lanes NV, NV + 1 write the ones-channel granule");
   extern __shared__ __align__(128) uint8_t smem[];
   float* bufL = (float*)(smem + S::off_bufL);
   float* bufR = (float*)(smem + S::off_bufR);
@@ -266,27 +265,31 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
     auto slot_ptr = [&](int k) { return smem + S::off_slot + k * S::slot_bytes; };
 
     // --- a finished row of one (tile, layer): lane = channels [4 lane, 4 lane + 4) -> shared (in place over Zr), stash
-    //     image, sign mask (4 ballot words per row: bit l of word c = h[4 l + c] > 0), ones-channel, embedding copy.
-    //     The per-(tile, layer) addresses are formed once (RowOut), the per-row part is a handful of integer ops.
+    //     image, sign mask (4 ballot words per row: bit l of word c = h[4 l + c] > 0), embedding copy.  Lanes NV and NV + 1
+    //     carry the granule behind the last channel: (1, 0, ...) = the ones channel of the stash image (the bias-gradient
+    //     row of h^T dZ), so ONE 16-byte store per lane writes the whole row.  The per-(tile, layer) addresses are formed
+    //     once (RowOut), the per-row part is a handful of integer ops.
+    const uint32_t sL = smem_u32(bufL), sR = smem_u32(bufR);
+    const int ln = lane < NV ? lane : 0;                   // idle lanes shadow lane 0 in shared-memory reads
     struct RowOut { char* img; uint4* mrow; float* erow; int gx; };
     auto row_out = [&](const TileDims& td, int s) {
       RowOut o;
       o.img = nullptr; o.mrow = nullptr; o.erow = nullptr; o.gx = 0;
       if (a.stash) {
-        const int g = lane < NV ? (lane >> 1) : NG;        // this lane's 8-channel granule (lane NV: the ones channel)
-        o.img = (char*)a.stash + ((size_t)s * a.B + td.t) * img_bytes + (size_t)(g >> 2) * kImgBlockBytes + (lane < NV ? (lane & 1) * 16 : 0);
+        const int g = lane >> 1;                           // this lane's 8-channel granule (NG: the ones channel)
+        o.img = (char*)a.stash + ((size_t)s * a.B + td.t) * img_bytes + (size_t)(g >> 2) * kImgBlockBytes + (lane & 1) * 16;
         o.gx = g & 3;
         o.mrow = mask_base + (size_t)s * mask_layer + (size_t)td.t * kTcRows;
-        if (s == a.d.L - 1) o.erow = emb + (int64_t)td.r0 * Hp + (lane < NV ? lane : 0) * 4;
+        if (s == a.d.L - 1) o.erow = emb + (int64_t)td.r0 * Hp + ln * 4;
       }
       return o;
     };
     auto finish_row = [&](const RowOut& o, int r, float4 h) {
-      if (lane < NV) *(float4*)(bufR + r * P + lane * 4) = h;
+      if (lane < NV) sts128(sR + (uint32_t)(r * (P * 4) + lane * 16), h);
       if (o.img) {
+        if (lane >= NV) h = make_float4(lane == NV ? 1.f : 0.f, 0.f, 0.f, 0.f);
         char* dst = o.img + (r >> 2) * 512 + (r & 3) * 128 + ((o.gx ^ (r & 3)) << 5);      // rm32_granule_off, row part
-        if (lane < NV) *(float4*)dst = h;
-        else if (lane == NV) st_global_v8(dst, 1.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f);
+        if (lane < NV + 2) *(float4*)dst = h;
         const bool in = lane < NV;
         const uint32_t b0 = __ballot_sync(0xffffffffu, in && h.x > 0.f), b1 = __ballot_sync(0xffffffffu, in && h.y > 0.f);
         const uint32_t b2 = __ballot_sync(0xffffffffu, in && h.z > 0.f), b3 = __ballot_sync(0xffffffffu, in && h.w > 0.f);
@@ -300,15 +303,13 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
       const int n32 = (n + 31) & ~31;
       for (int r = n + wid; r < n32; r += kTcEpiWarps) {
         char* dst = o.img + (r >> 2) * 512 + (r & 3) * 128 + ((o.gx ^ (r & 3)) << 5);
-        if (lane < NV) *(float4*)dst = make_float4(0.f, 0.f, 0.f, 0.f);
-        else if (lane == NV) st_global_v8(dst, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f);
+        if (lane < NV + 2) *(float4*)dst = make_float4(0.f, 0.f, 0.f, 0.f);
       }
     };
 
     // --- tile CSR + features -> slot k (+ the shared x / mean staging rows for layer 0) ----------------------------
     auto load_tile = [&](const TileDims& td, int k) {
       uint8_t* sl = slot_ptr(k);
-      float* inv_s = (float*)(sl + S::slot_inv);
       int* rowptr_s = (int*)(sl + S::slot_rowptr);
       int* gp_s = (int*)(sl + S::slot_gp);
       unsigned short* col_s = (unsigned short*)(sl + S::slot_col);
@@ -340,24 +341,23 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
         const float inv = 1.0f / (float)(deg > 0 ? deg : 1);
         float s0 = 0.f, s1 = 0.f;
         for (int p = b; p < e; ++p) { const int j = col_s[p]; s0 += x0_s[j]; s1 += x1_s[j]; }
-        inv_s[i] = inv; m0_s[i] = s0 * inv; m1_s[i] = s1 * inv;
+        m0_s[i] = s0 * inv; m1_s[i] = s1 * inv;
       }
       epi_bar();
     };
 
-    // --- P3: h' rows (bufR) -> tf32 hi / lo -> R1, released to the MMA warp column quarter by column quarter ------
-    auto write_A = [&](const TileDims& td) {
-      const bool live = row < td.n;
+    // --- P3: h' rows (bufR) -> tf32 hi / lo -> R1, released to the MMA warp column quarter by column quarter.  Rows
+    //     >= n of bufR are zero by construction (layer 0 clears them, P1 writes Zr = 0 * W without the bias): no select.
+    auto write_A = [&]() {
 #pragma unroll
       for (int gi = 0; gi < MAXG; ++gi) {
         const int g = slice + gi * kTcSlices;
         if (g < NG) {
           float v[8], hi[8], lo[8];
-          const float4* src = (const float4*)(bufR + row * P + g * 8);
-          const float4 v0 = src[0], v1 = src[1];
+          const float4 v0 = lds128(sR + (uint32_t)(row * (P * 4) + g * 32)), v1 = lds128(sR + (uint32_t)(row * (P * 4) + g * 32 + 16));
           v[0] = v0.x; v[1] = v0.y; v[2] = v0.z; v[3] = v0.w; v[4] = v1.x; v[5] = v1.y; v[6] = v1.z; v[7] = v1.w;
 #pragma unroll
-          for (int u = 0; u < 8; ++u) split_tf32(live ? v[u] : 0.f, hi[u], lo[u]);
+          for (int u = 0; u < 8; ++u) split_tf32(v[u], hi[u], lo[u]);
           tmem_st8(trow + TM_HI + g * 8, hi);
           tmem_st8(trow + TM_LO + g * 8, lo);
         }
@@ -392,13 +392,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
         finish_row(ro, r, make_float4(o[0], o[1], o[2], o[3]));
       }
       finish_tail(ro, n);
+      for (int r = n + wid; r < kTcRows; r += kTcEpiWarps)     // dead rows stay zero through every layer (see write_A)
+        if (lane < NV) sts128(sR + (uint32_t)(r * (P * 4) + lane * 16), make_float4(0.f, 0.f, 0.f, 0.f));
       epi_bar();
-      write_A(td);
+      write_A();
     };
 
-    // --- P1: R2 -> shared (Zl rows -> bufL, Zr + b rows -> bufR); frees R2 ------------------------------------------
-    auto drain = [&](int s) {
-      const float* bias = bias_s + s * Hp;
+    // --- P1: R2 -> shared (Zl rows -> bufL, Zr rows -> bufR; the bias joins in P2); frees R2 ---------------------------------
+    auto drain = [&]() {
       float zl[MAXG][8], zr[MAXG][8];
 #pragma unroll
       for (int gi = 0; gi < MAXG; ++gi) {
@@ -415,9 +416,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
       for (int gi = 0; gi < MAXG; ++gi) {
         const int g = slice + gi * kTcSlices;
         if (g < NG) {
-          float4* dst = (float4*)(bufL + row * P + g * 8);
-          dst[0] = make_float4(zl[gi][0], zl[gi][1], zl[gi][2], zl[gi][3]);
-          dst[1] = make_float4(zl[gi][4], zl[gi][5], zl[gi][6], zl[gi][7]);
+          const uint32_t d = sL + (uint32_t)(row * (P * 4) + g * 32);
+          sts128(d, make_float4(zl[gi][0], zl[gi][1], zl[gi][2], zl[gi][3]));
+          sts128(d + 16, make_float4(zl[gi][4], zl[gi][5], zl[gi][6], zl[gi][7]));
         }
       }
       tmem_wait_ld();
@@ -428,53 +429,54 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
       for (int gi = 0; gi < MAXG; ++gi) {
         const int g = slice + gi * kTcSlices;
         if (g < NG) {
-          const float4 b0 = *(const float4*)(bias + g * 8), b1 = *(const float4*)(bias + g * 8 + 4);
-          float4* dst = (float4*)(bufR + row * P + g * 8);
-          dst[0] = make_float4(zr[gi][0] + b0.x, zr[gi][1] + b0.y, zr[gi][2] + b0.z, zr[gi][3] + b0.w);
-          dst[1] = make_float4(zr[gi][4] + b1.x, zr[gi][5] + b1.y, zr[gi][6] + b1.z, zr[gi][7] + b1.w);
+          const uint32_t d = sR + (uint32_t)(row * (P * 4) + g * 32);
+          sts128(d, make_float4(zr[gi][0], zr[gi][1], zr[gi][2], zr[gi][3]));
+          sts128(d + 16, make_float4(zr[gi][4], zr[gi][5], zr[gi][6], zr[gi][7]));
         }
       }
     };
 
     // --- P2: agg_i = sum_{j -> i} Zl_j (row table of sage_tc.cuh: warp = one row, four independent accumulators over the
-    //     neighbours k = 0, 1, 2, 3 mod 4, combined (s0 + s1) + (s2 + s3)); h'_i = relu(agg_i / deg_i + (Zr_i + b)) ----------
+    //     neighbours k = 0, 1, 2, 3 mod 4, combined (s0 + s1) + (s2 + s3)); h'_i = relu(agg_i / deg_i + (Zr_i + b)).
+    //     Software-pipelined over the warp's rows: the header, first-step offsets and first-step loads of the NEXT row are
+    //     issued before the current row is finished (the loads are volatile asm: program order = issue order). ---------------
     auto gather_combine = [&](const TileDims& td, int k, int s) {
       uint8_t* sl = slot_ptr(k);
-      const float* inv_s = (const float*)(sl + S::slot_inv);
-      const RowTab g = row_tab_view(sl + S::slot_gtab);
+      const uint32_t tabA = smem_u32(sl + S::slot_gtab), hdrA = tabA + kRowTabMaxSteps * 16, firstA = hdrA + kTcRows * 16;
       const RowOut ro = row_out(td, s);
       const int n = td.n;
-      const int ln = lane < NV ? lane : 0;               // idle lanes shadow lane 0 (their results are discarded)
-      const char* sb = (const char*)bufL + ln * 16;
-      const float* zb = bufR + ln * 4;
-      for (int r = wid; r < n; r += kTcEpiWarps) {
-        const int s0 = g.rstart[r], s1 = g.rstart[r + 1];
-        const float iv = inv_s[r];
-        const float4 z = *(const float4*)(zb + r * P);
-        float4 acc[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        int kk = s0;
-        for (; kk + 2 <= s1; kk += 2) {
-          const int4 o0 = g.tab[kk], o1 = g.tab[kk + 1];
-          const float4 v0 = *(const float4*)(sb + o0.x), v1 = *(const float4*)(sb + o0.y);
-          const float4 v2 = *(const float4*)(sb + o0.z), v3 = *(const float4*)(sb + o0.w);
-          const float4 u0 = *(const float4*)(sb + o1.x), u1 = *(const float4*)(sb + o1.y);
-          const float4 u2 = *(const float4*)(sb + o1.z), u3 = *(const float4*)(sb + o1.w);
-          fadd2x2(acc[0], v0); fadd2x2(acc[1], v1); fadd2x2(acc[2], v2); fadd2x2(acc[3], v3);
-          fadd2x2(acc[0], u0); fadd2x2(acc[1], u1); fadd2x2(acc[2], u2); fadd2x2(acc[3], u3);
+      const float4 bs = *(const float4*)(bias_s + s * Hp + ln * 4);
+      const uint32_t sb = sL + ln * 16, zb = sR + ln * 16;
+      int r = wid;
+      if (r < n) {
+        int4 hd = lds128i(hdrA + r * 16);
+        {
+          const int4 f = lds128i(firstA + r * 16);
+          float4 a0 = lds128(sb + f.x), a1 = lds128(sb + f.y), a2 = lds128(sb + f.z), a3 = lds128(sb + f.w);
+          float4 z = lds128(zb + r * (P * 4));
+          for (;;) {
+            const int rn = r + kTcEpiWarps;
+            const int rc = rn < n ? rn : r;                        // last row: harmless re-read of itself
+            const int4 hdn = lds128i(hdrA + rc * 16);
+            const int4 fn = lds128i(firstA + rc * 16);
+            for (int kk = hd.x; kk < hd.y; ++kk) {               // steps beyond the first (degree > 4)
+              const int4 p = lds128i(tabA + kk * 16);
+              const float4 v0 = lds128(sb + p.x), v1 = lds128(sb + p.y), v2 = lds128(sb + p.z), v3 = lds128(sb + p.w);
+              fadd2x2(a0, v0); fadd2x2(a1, v1); fadd2x2(a2, v2); fadd2x2(a3, v3);
+            }
+            const float4 n0 = lds128(sb + fn.x), n1 = lds128(sb + fn.y), n2 = lds128(sb + fn.z), n3 = lds128(sb + fn.w);
+            const float4 zn = lds128(zb + rc * (P * 4));
+            fadd2x2(a0, a1); fadd2x2(a2, a3); fadd2x2(a0, a2);
+            const float iv = __int_as_float(hd.z);
+            z.x += bs.x; z.y += bs.y; z.z += bs.z; z.w += bs.w;
+            float4 h;
+            h.x = fmaxf(fmaf(a0.x, iv, z.x), 0.f); h.y = fmaxf(fmaf(a0.y, iv, z.y), 0.f);
+            h.z = fmaxf(fmaf(a0.z, iv, z.z), 0.f); h.w = fmaxf(fmaf(a0.w, iv, z.w), 0.f);
+            finish_row(ro, r, h);
+            if (rn >= n) break;
+            r = rn; hd = hdn; a0 = n0; a1 = n1; a2 = n2; a3 = n3; z = zn;
+          }
         }
-        if (kk < s1) {
-          const int4 o0 = g.tab[kk];
-          const float4 v0 = *(const float4*)(sb + o0.x), v1 = *(const float4*)(sb + o0.y);
-          const float4 v2 = *(const float4*)(sb + o0.z), v3 = *(const float4*)(sb + o0.w);
-          fadd2x2(acc[0], v0); fadd2x2(acc[1], v1); fadd2x2(acc[2], v2); fadd2x2(acc[3], v3);
-        }
-        fadd2x2(acc[0], acc[1]); fadd2x2(acc[2], acc[3]); fadd2x2(acc[0], acc[2]);
-        float4 h;
-        h.x = fmaxf(fmaf(acc[0].x, iv, z.x), 0.f); h.y = fmaxf(fmaf(acc[0].y, iv, z.y), 0.f);
-        h.z = fmaxf(fmaf(acc[0].z, iv, z.z), 0.f); h.w = fmaxf(fmaf(acc[0].w, iv, z.w), 0.f);
-        finish_row(ro, r, h);
       }
       finish_tail(ro, n);
     };
@@ -638,14 +640,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
           if (np == 2) {                      // next A operand of the OTHER tile: its GEMM runs under this tile's P2
             tq = PH_NOW();
             if (k == 0) {
-              if (s == 1) layer0(td[1]); else write_A(td[1]);       // A of (Y, s)
+              if (s == 1) layer0(td[1]); else write_A();       // A of (Y, s)
             } else if (!last) {
-              write_A(td[0]);                                        // A of (X, s + 1)
+              write_A();                                        // A of (X, s + 1)
             }
             PH_ADD(ph11, tq);
           }
           tq = PH_NOW();
-          drain(s);
+          drain();
           epi_bar();
           PH_ADD(ph1, tq);
           tq = PH_NOW();
@@ -659,7 +661,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
             PH_ADD(ph4, tq);
           } else if (np == 1) {
             tq = PH_NOW();
-            write_A(td[0]);
+            write_A();
             PH_ADD(ph11, tq);
           }
         }

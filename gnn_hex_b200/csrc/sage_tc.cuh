@@ -227,16 +227,21 @@ __device__ __forceinline__ void gather_build(const GatherTab& g, const int* __re
 // accumulators, summed (s0 + s1) + (s2 + s3) at the end: fixed order, deterministic.  One row per work unit balances the
 // 16 epilogue warps (6 full rounds for a 94-row tile instead of two ragged rounds of 4-row groups), the terminal rows
 // (degree 20-30) need no special case, and the table is a third of the size (<= (E_cap + 3 * 128) / 4 steps).
+// Per row TWO 16-byte words that need no dependent address: `first` = the offsets of neighbours 0..3 (step 0, zero-row
+// offsets for a row of degree 0) and `hdr` = {first further step, end step, 1 / max(deg, 1) (float bits), 0}; `tab` holds
+// only the steps k >= 1.  A warp can therefore issue the loads of its NEXT row before it finishes the current one.
 constexpr int kRowTabMaxSteps = (kEdgeCapPerRow * kTcRows + 3 * kTcRows) / 4;
 struct RowTab {
-  int4* tab;      // [kRowTabMaxSteps]
-  int* rstart;    // [128 + 1] first step of every row
+  int4* tab;      // [kRowTabMaxSteps] steps k >= 1 of all rows
+  int4* hdr;      // [128]
+  int4* first;    // [128]
 };
-__host__ __device__ constexpr int row_tab_bytes() { return kRowTabMaxSteps * 16 + (kTcRows + 4) * 4; }
+__host__ __device__ constexpr int row_tab_bytes() { return kRowTabMaxSteps * 16 + 2 * kTcRows * 16; }
 __device__ __forceinline__ RowTab row_tab_view(uint8_t* base) {
   RowTab g;
   g.tab = (int4*)base;
-  g.rstart = (int*)(base + kRowTabMaxSteps * 16);
+  g.hdr = (int4*)(base + kRowTabMaxSteps * 16);
+  g.first = g.hdr + kTcRows;
   return g;
 }
 // All epilogue threads; rowptr_s / col_s complete and visible; ends with the epilogue barrier.
@@ -246,30 +251,31 @@ __device__ __forceinline__ void row_tab_build(const RowTab& g, const int* __rest
   constexpr int PB = (16 * NJ + 4) * 4;   // row pitch in bytes
   const int wid = tid >> 5, lane = tid & 31;
   if (wid == 0) {
-    int st[4], tot = 0;
+    int st[4], dg[4], tot = 0;
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const int r = 4 * lane + j;
-      const int d = r < n ? rowptr_s[r + 1] - rowptr_s[r] : 0;
-      st[j] = (d + 3) >> 2;
+      dg[j] = r < n ? rowptr_s[r + 1] - rowptr_s[r] : 0;
+      st[j] = dg[j] > 4 ? (dg[j] - 1) >> 2 : 0;          // steps beyond the first
       tot += st[j];
     }
-    const int inc = warp_scan_incl(tot, lane);
-    int base = inc - tot;
+    int base = warp_scan_incl(tot, lane) - tot;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) { g.rstart[4 * lane + j] = base; base += st[j]; }
-    if (lane == 31) g.rstart[kTcRows] = inc;
+    for (int j = 0; j < 4; ++j) {
+      g.hdr[4 * lane + j] = make_int4(base, base + st[j], __float_as_int(1.0f / (float)(dg[j] > 0 ? dg[j] : 1)), 0);
+      base += st[j];
+    }
   }
   asm volatile("bar.sync 1, %0;" ::"n"(kTcEpiThreads) : "memory");
-  for (int r = wid; r < n; r += kTcEpiWarps) {
-    const int b = rowptr_s[r], d = rowptr_s[r + 1] - b, s0 = g.rstart[r];
-    for (int k = lane; 4 * k < d; k += 32) {
+  for (int r = wid; r < kTcRows; r += kTcEpiWarps) {
+    const int b = r < n ? rowptr_s[r] : 0, d = r < n ? rowptr_s[r + 1] - b : 0, s0 = g.hdr[r].x;
+    for (int k = lane; 4 * k < d || k == 0; k += 32) {
       int4 o;
-      o.x = (int)col_s[b + 4 * k] * PB;
+      o.x = (4 * k < d ? (int)col_s[b + 4 * k] : kTcRows) * PB;
       o.y = (4 * k + 1 < d ? (int)col_s[b + 4 * k + 1] : kTcRows) * PB;
       o.z = (4 * k + 2 < d ? (int)col_s[b + 4 * k + 2] : kTcRows) * PB;
       o.w = (4 * k + 3 < d ? (int)col_s[b + 4 * k + 3] : kTcRows) * PB;
-      g.tab[s0 + k] = o;
+      if (k == 0) g.first[r] = o; else g.tab[s0 + k - 1] = o;
     }
   }
   asm volatile("bar.sync 1, %0;" ::"n"(kTcEpiThreads) : "memory");

@@ -48,7 +48,8 @@ def test_cuda_path_equals_reference_golden_vectors(tag, maker):
     assert int(m.last_csr.status.item()) == 0
     assert rel(q.detach().cpu().numpy(), fx[f"q_{maker}"]) <= TOL
     assert rel(q.detach().cpu().numpy(), fx[f"q64_{maker}"]) <= TOL
-    assert adv.shape == (b.x.shape[0], 1) and rel(adv.cpu().numpy(), fx[f"adv_{maker}"]) <= TOL
+    ea = rel(adv.cpu().numpy(), fx[f"adv_{maker}"])
+    assert adv.shape == (b.x.shape[0], 1) and ea <= TOL, ("advantages_only", ea, rel(q.detach().cpu().numpy(), fx[f"q64_{maker}"]))
     # value and centred advantage are the two addends of Q (models.py:584): their error is measured on Q's scale (a value
     # head that happens to output ~1e-3 carries the absolute round-off of its pooled sums, not 1e-5 of itself)
     qs = float(np.abs(fx[f"q64_{maker}"]).max())
