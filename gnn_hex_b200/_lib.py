@@ -10,6 +10,7 @@ HEXGNN_ADV_ONLY = 1
 HEXGNN_SEPARATE = 2
 HEXGNN_PATH_SIMT = 0x100
 HEXGNN_PATH_TC = 0x200
+HEXGNN_TF32X1 = 0x400
 
 ST_GRAPH_TOO_LARGE = 1
 ST_EDGE_CROSSES = 2

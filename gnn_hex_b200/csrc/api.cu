@@ -144,6 +144,7 @@ int hexgnn_forward(const HexModelDesc* desc, const float* params, const float* x
   if (!make_dims(desc, &d)) { set_error("forward: bad model descriptor"); return HEXGNN_E_BADARG; }
   if (!params || !x || !csr || !out_nodes || !ws || N < 1 || B < 1 || E < 0) { set_error("forward: bad argument"); return HEXGNN_E_BADARG; }
   if ((flags & HEXGNN_SEPARATE) && !out_value) { set_error("forward: SEPARATE needs out_value"); return HEXGNN_E_BADARG; }
+  if ((flags & HEXGNN_TF32X1) && (stash || !use_tc(d, flags))) { set_error("forward: TF32X1 is an inference mode of the tensor-core path (no stash)"); return HEXGNN_E_BADARG; }
   if (!tile_rows_ok(tile_rows) || d.NJ > 8) { set_error("forward: unsupported tile_rows=%d or hidden=%d", tile_rows, d.H); return HEXGNN_E_UNSUPPORTED; }
   const int64_t need = (pack_floats(d) > tc_pack_floats(d) ? pack_floats(d) : tc_pack_floats(d)) * 4;
   if ((int64_t)ws_bytes < need) { set_error("forward: workspace too small (%zu < %lld)", ws_bytes, (long long)need); return HEXGNN_E_WORKSPACE; }

@@ -247,8 +247,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
     const float b1 = Pm[a.pm.v1_b[head]];
     const size_t act_img = (size_t)tc_act_blocks(Hp) * kImgBlockBytes;
     const size_t dz_img = (size_t)tc_dz_blocks(Hp) * kImgBlockBytes;
-    const uint4* mask_base = (const uint4*)(a.stash + tc_stash_mask_off_floats(a.d, a.N, a.B));
-    const size_t mask_layer = (size_t)a.B * kTcRows;   // uint4 (4 ballot words) per (layer, tile, row), see sage_tc.cuh
+    const uint32_t* mask_base = (const uint32_t*)(a.stash + tc_stash_mask_off_floats(a.d, a.N, a.B));
+    const size_t mask_layer = (size_t)a.B * kTcSlices * kTcRows;
     const int hrec_n = tc_head_rec_floats(a.d), H2p = (H2 + 3) & ~3;
     const int part = tid >> 7, pc = tid & 127;      // row quarter / channel of the column-parallel loops
     uint32_t nr = 0, nd = 0;
@@ -292,7 +292,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
       const int n32 = (n + 31) & ~31;
       const char* act_t = (const char*)a.stash + (size_t)t * act_img;         // + layer * B * act_img
       char* dz_t = (char*)a.dz + (size_t)t * dz_img;                           // + (s-1) * B * dz_img
-      const uint4* mask_t = mask_base + (size_t)t * kTcRows + row;
+      const uint32_t* mask_t = mask_base + ((size_t)t * kTcSlices + slice) * kTcRows + row;
       // ---- g = h_Lt -> dump (row major) -----------------------------------------------------------------
       {
         const char* img = act_t + (size_t)(Lt - 1) * a.B * act_img;
@@ -487,10 +487,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
       for (int s = Lt - 1; s >= 1; --s) {
         const bool first = (s == Lt - 1);
         tq = PH_NOW();
-        const uint4 mw4 = mask_t[(size_t)s * mask_layer];   // signs of h_{s+1}; in flight during the wait below
-        // bit l of word c = sign of channel 4 l + c; this thread's granule g = slice + 4 gi holds channels 8 g + u:
-        // word u % 4, bit 2 g + u / 4 = 2 slice + (8 gi + u / 4)
-        const uint32_t mws[4] = {mw4.x >> (2 * slice), mw4.y >> (2 * slice), mw4.z >> (2 * slice), mw4.w >> (2 * slice)};
+        const uint32_t mw = mask_t[(size_t)s * mask_layer];   // signs of h_{s+1}; in flight during the wait below
         float dh[MAXG][8];
         if (first) {
 #pragma unroll
@@ -531,7 +528,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
               float hi[8], lo[8], sc[8];
 #pragma unroll
               for (int u = 0; u < 8; ++u) {
-                const float r = ((mws[u & 3] >> (gi * 8 + (u >> 2))) & 1u) ? dh[gi][u] : 0.f;
+                const float r = ((mw >> (gi * 8 + u)) & 1u) ? dh[gi][u] : 0.f;
                 dh[gi][u] = r;
                 sc[u] = r * inv;
                 split_tf32(r, hi[u], lo[u]);
@@ -601,8 +598,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
       // ---- layer 0 (2 -> H): dpre_0 = dH_1 (.) (h_1 > 0); rank-2 weight gradients on the CUDA cores -------------------
       tq = PH_NOW();
       {
-        const uint4 mw4 = mask_t[0];
-        const uint32_t mws[4] = {mw4.x >> (2 * slice), mw4.y >> (2 * slice), mw4.z >> (2 * slice), mw4.w >> (2 * slice)};
+        const uint32_t mw = mask_t[0];
         float dh[MAXG][8];
         if (Lt == 1) {
 #pragma unroll
@@ -636,7 +632,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
               de[1] = make_float4(dh[gi][4], dh[gi][5], dh[gi][6], dh[gi][7]);
             }
 #pragma unroll
-            for (int u = 0; u < 8; ++u) dh[gi][u] = ((mws[u & 3] >> (gi * 8 + (u >> 2))) & 1u) ? dh[gi][u] : 0.f;
+            for (int u = 0; u < 8; ++u) dh[gi][u] = ((mw >> (gi * 8 + u)) & 1u) ? dh[gi][u] : 0.f;
             float4* dd = (float4*)(dump + row * P + g * 8);
             dd[0] = make_float4(dh[gi][0], dh[gi][1], dh[gi][2], dh[gi][3]);
             dd[1] = make_float4(dh[gi][4], dh[gi][5], dh[gi][6], dh[gi][7]);

@@ -71,12 +71,12 @@ __device__ __forceinline__ uint32_t rm32_granule_off(int g, int row) {   // 8-ch
   return (uint32_t)(g >> 2) * kImgBlockBytes + (uint32_t)(row >> 2) * 512u + (uint32_t)(row & 3) * 128u +
          ((uint32_t)((g & 3) ^ (row & 3)) << 5);
 }
-// ReLU sign masks of every layer output: four u32 per (layer, tile, row) -- the four warp ballots of the forward's
-// (warp = row, lane = 4 channels) combine pass: bit l of word c is set iff h[row][4 l + c] > 0 -- so the backward chain
-// reads ONE 16-byte word group per thread and layer instead of the activation image.
+// ReLU sign masks of every layer output: one u32 per (layer, tile, column slice, row); bit gi*8+u is set iff
+// h[row][(slice + gi*kTcSlices)*8 + u] > 0 -- the (row, slice) thread mapping of both epilogues, so the backward
+// chain reads ONE coalesced word per thread and layer instead of the activation image.
 inline int64_t tc_mask_words(const Dims& d, int64_t B) { return (int64_t)d.Lt * B * kTcSlices * kTcRows; }
 // forward stash: [Lt][B tiles][act_blocks*16KB] images + row-major embedding copy [N][Hp] (final_conv_acts)
-// + sign masks [Lt][B][128] uint4
+// + sign masks [Lt][B][kTcSlices][128] u32
 __host__ __device__ inline int64_t tc_stash_mask_off_floats(const Dims& d, int64_t N, int64_t B) {
   return (int64_t)d.Lt * B * tc_act_blocks(d.Hp) * (kImgBlockBytes / 4) + N * d.Hp;
 }
@@ -222,65 +222,6 @@ __device__ __forceinline__ void gather_build(const GatherTab& g, const int* __re
   }
   asm volatile("bar.sync 1, %0;" ::"n"(kTcEpiThreads) : "memory");
 }
-// ---- row table (forward kernel): ONE warp walks ONE row.  Step k of a row is an int4 of byte offsets of its neighbours
-// 4k .. 4k+3 (absent ones point at the zero row 128), so a row of degree d takes ceil(d / 4) steps with four independent
-// accumulators, summed (s0 + s1) + (s2 + s3) at the end: fixed order, deterministic.  One row per work unit balances the
-// 16 epilogue warps (6 full rounds for a 94-row tile instead of two ragged rounds of 4-row groups), the terminal rows
-// (degree 20-30) need no special case, and the table is a third of the size (<= (E_cap + 3 * 128) / 4 steps).
-// Per row TWO 16-byte words that need no dependent address: `first` = the offsets of neighbours 0..3 (step 0, zero-row
-// offsets for a row of degree 0) and `hdr` = {first further step, end step, 1 / max(deg, 1) (float bits), 0}; `tab` holds
-// only the steps k >= 1.  A warp can therefore issue the loads of its NEXT row before it finishes the current one.
-constexpr int kRowTabMaxSteps = (kEdgeCapPerRow * kTcRows + 3 * kTcRows) / 4;
-struct RowTab {
-  int4* tab;      // [kRowTabMaxSteps] steps k >= 1 of all rows
-  int4* hdr;      // [128]
-  int4* first;    // [128]
-};
-__host__ __device__ constexpr int row_tab_bytes() { return kRowTabMaxSteps * 16 + 2 * kTcRows * 16; }
-__device__ __forceinline__ RowTab row_tab_view(uint8_t* base) {
-  RowTab g;
-  g.tab = (int4*)base;
-  g.hdr = (int4*)(base + kRowTabMaxSteps * 16);
-  g.first = g.hdr + kTcRows;
-  return g;
-}
-// All epilogue threads; rowptr_s / col_s complete and visible; ends with the epilogue barrier.
-template <int NJ>
-__device__ __forceinline__ void row_tab_build(const RowTab& g, const int* __restrict__ rowptr_s,
-                                              const unsigned short* __restrict__ col_s, int n, int tid) {
-  constexpr int PB = (16 * NJ + 4) * 4;   // row pitch in bytes
-  const int wid = tid >> 5, lane = tid & 31;
-  if (wid == 0) {
-    int st[4], dg[4], tot = 0;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int r = 4 * lane + j;
-      dg[j] = r < n ? rowptr_s[r + 1] - rowptr_s[r] : 0;
-      st[j] = dg[j] > 4 ? (dg[j] - 1) >> 2 : 0;          // steps beyond the first
-      tot += st[j];
-    }
-    int base = warp_scan_incl(tot, lane) - tot;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      g.hdr[4 * lane + j] = make_int4(base, base + st[j], __float_as_int(1.0f / (float)(dg[j] > 0 ? dg[j] : 1)), 0);
-      base += st[j];
-    }
-  }
-  asm volatile("bar.sync 1, %0;" ::"n"(kTcEpiThreads) : "memory");
-  for (int r = wid; r < kTcRows; r += kTcEpiWarps) {
-    const int b = r < n ? rowptr_s[r] : 0, d = r < n ? rowptr_s[r + 1] - b : 0, s0 = g.hdr[r].x;
-    for (int k = lane; 4 * k < d || k == 0; k += 32) {
-      int4 o;
-      o.x = (4 * k < d ? (int)col_s[b + 4 * k] : kTcRows) * PB;
-      o.y = (4 * k + 1 < d ? (int)col_s[b + 4 * k + 1] : kTcRows) * PB;
-      o.z = (4 * k + 2 < d ? (int)col_s[b + 4 * k + 2] : kTcRows) * PB;
-      o.w = (4 * k + 3 < d ? (int)col_s[b + 4 * k + 3] : kTcRows) * PB;
-      if (k == 0) g.first[r] = o; else g.tab[s0 + k - 1] = o;
-    }
-  }
-  asm volatile("bar.sync 1, %0;" ::"n"(kTcEpiThreads) : "memory");
-}
-
 __device__ __forceinline__ void fadd2x2(float4& a, const float4& b) {   // a += b as two packed f32x2 adds
   unsigned long long a0, a1, b0, b1;
   asm("mov.b64 %0, {%1, %2};" : "=l"(a0) : "f"(a.x), "f"(a.y));

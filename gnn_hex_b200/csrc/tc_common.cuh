@@ -134,21 +134,6 @@ __device__ __forceinline__ void tmem_st8(uint32_t taddr, const float (&v)[8]) {
                : "memory");
 }
 
-// ---- shared memory through 32-bit shared-window addresses (one IADD of address arithmetic per access) ----------------------
-__device__ __forceinline__ float4 lds128(uint32_t a) {
-  float4 v;
-  asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
-  return v;
-}
-__device__ __forceinline__ int4 lds128i(uint32_t a) {
-  int4 v;
-  asm volatile("ld.shared.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
-  return v;
-}
-__device__ __forceinline__ void sts128(uint32_t a, const float4& v) {
-  asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w));
-}
-
 // ---- 256-bit global store (sm_100+: STG.256): one full 32-byte sector per thread and instruction -----------------
 __device__ __forceinline__ void st_global_v8(void* p, float v0, float v1, float v2, float v3, float v4, float v5,
                                              float v6, float v7) {

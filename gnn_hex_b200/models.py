@@ -248,7 +248,7 @@ class ModernTwoHeaded(nn.Module):
 
     def __init__(self, hidden_channels: int, num_layers: int, num_head_layers: int = 2, tile_rows: int = 128,
                  strict: bool = False, path: str = "auto", max_graph_nodes: int = 0, noisy_dqn: bool = False,
-                 noisy_sigma0: float = 0.5):
+                 noisy_sigma0: float = 0.5, inference_precision: str = "tf32x3"):
         super().__init__()
         self.hidden_channels = int(hidden_channels)
         self.num_layers = int(num_layers)
@@ -256,6 +256,12 @@ class ModernTwoHeaded(nn.Module):
         self.tile_rows = int(tile_rows)
         self.strict = strict                  # True: sync + raise on device-side status after each forward
         self.path = path                      # "auto" | "simt" | "tc"
+        # SURVEY 7.2(1) precision policy.  "tf32x3" (default): fp32 parity everywhere.  "tf32x1": forwards that keep no
+        # stash (torch.no_grad(): acting, target evaluation) run ONE tensor-core pass per k-step (~1e-3 relative error,
+        # opt-in; rainbow.py:214-239 only takes an arg-max).  Calls that can be differentiated always use 3xTF32.
+        if inference_precision not in ("tf32x3", "tf32x1"):
+            raise ValueError("inference_precision must be 'tf32x3' or 'tf32x1'")
+        self.inference_precision = inference_precision
         self.capture_embed_grads = False      # True: fill final_conv_grads (rl_loop/explain.py:41)
         # > tile_rows: inference calls also run the oversize-graph path (hexgnn_forward_big) for graphs of up to this
         # many nodes (board-size transfer: 13x13 -> 171, evaluate_elo.py:229-251); 0 = such graphs are flagged only
@@ -629,8 +635,11 @@ class ModernTwoHeaded(nn.Module):
         if torch.is_grad_enabled() and anchor.requires_grad:
             out_nodes, out_value = _FusedQ.apply(self, x, csr, flags, anchor)
         else:
+            if self.inference_precision == "tf32x1" and self.path != "simt":
+                flags |= ops.HEXGNN_TF32X1
             out_nodes, out_value, _, _ = ops.fused_forward(self._desc, self._flat, x, csr, flags, want_stash=False,
                                                            ws=self._fwd_ws(csr))
+            flags &= ~ops.HEXGNN_TF32X1
             if self.max_graph_nodes > self.tile_rows:
                 ops.forward_big(self._desc, self._flat, x, csr, flags, self.max_graph_nodes, out_nodes, out_value)
         if self.strict:

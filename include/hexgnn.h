@@ -48,7 +48,11 @@ enum {
   HEXGNN_ADV_ONLY = 1,   /* advantages_only=True: out_nodes = 2*tanh(linear(g)), no value branch (models.py:567-569) */
   HEXGNN_SEPARATE = 2,   /* seperate=True: out_value = tanh(value), out_nodes = adv - mean(adv)  (models.py:580-581) */
   HEXGNN_PATH_SIMT = 0x100, /* force the fp32 CUDA-core kernels (default: tcgen05 3xTF32 kernels when the shape allows) */
-  HEXGNN_PATH_TC = 0x200    /* force the tcgen05 kernels; HEXGNN_E_UNSUPPORTED if the shape does not allow      */
+  HEXGNN_PATH_TC = 0x200,   /* force the tcgen05 kernels; HEXGNN_E_UNSUPPORTED if the shape does not allow      */
+  HEXGNN_TF32X1 = 0x400     /* hexgnn_forward without a stash only (inference, opt-in): ONE tf32 tensor-core pass per
+                               k-step instead of the three of the fp32-parity 3xTF32 scheme -- ~1e-3 relative error, a third
+                               of the tensor-core time.  For self-play acting, where only an arg-max is taken
+                               (rainbow.py:214-239; HexAra infers in fp16, rl_loop/rl_config.py:31).  Never for training. */
 };
 
 /* device-side status bits (csr blob word 0) */
@@ -104,7 +108,8 @@ int64_t hexgnn_param_count(const HexModelDesc* desc);
  *   breaker_head          :  same as maker_head                                           */
 int32_t hexgnn_param_offsets(const HexModelDesc* desc, int64_t* offsets, int32_t max_entries);
 
-/* tile_rows: node capacity of one CTA tile (128 or 192); graphs are packed into tiles whole. */
+/* tile_rows: node capacity of one CTA tile; 128 is the only accepted value (anything else: HEXGNN_E_UNSUPPORTED).
+ * Graphs are packed into tiles whole; a tile also holds at most 1024 directed edges and 64 graphs. */
 int hexgnn_sizes(const HexModelDesc* desc, int64_t N, int64_t E, int64_t B, int32_t tile_rows,
                  HexSizes* out);
 int hexgnn_csr_layout(int64_t N, int64_t E, int64_t B, HexCsrLayout* out);

@@ -826,3 +826,40 @@ def test_csr_five_launch_path_in_subprocess():
     env = dict(os.environ, HEXGNN_CSR_BLOCKS_PER_SM="0", PYTHONPATH=root)
     r = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=300)
     assert "FIVE_LAUNCH_OK" in r.stdout, r.stdout + r.stderr
+
+
+def test_tf32x1_inference_mode_is_opt_in_and_bounded():
+    """SURVEY 7.2(1) precision policy: `inference_precision="tf32x1"` runs ONE tensor-core pass per k-step in forwards that
+    keep no stash (acting / target evaluation, rainbow.py:214-239,259-275): measurably coarser than the 3xTF32 default but
+    within 1e-2, same arg-max as the default on clear-cut positions; differentiable calls ignore it (bit-identical to
+    tf32x3); the C-ABI refuses the flag together with a stash."""
+    import ctypes as C
+    cfg = CONFIGS["L"]
+    o, m = make_pair(cfg["hidden"], cfg["layers"])
+    m = m.to(DEV)
+    b = _batch(cfg, "play", 1, 48)
+    d = b.to(DEV)
+    with torch.no_grad():
+        a_ref = o(b.x, b.edge_index, b.batch, advantages_only=True)
+        a3 = m(d.x, d.edge_index, d.batch, d.ptr, advantages_only=True)
+        m.inference_precision = "tf32x1"
+        a1 = m(d.x, d.edge_index, d.batch, d.ptr, advantages_only=True)
+        q1 = m(d.x, d.edge_index, d.batch, d.ptr)
+    e3, e1 = rel_err(a3, a_ref), rel_err(a1, a_ref)
+    assert e3 <= REL_TOL and REL_TOL < e1 <= 1e-2, (e3, e1)
+    assert rel_err(q1, o(b.x, b.edge_index, b.batch, b.ptr).detach()) <= 1e-2
+    # a call that can be differentiated always runs 3xTF32
+    q_grad = m(d.x, d.edge_index, d.batch, d.ptr)
+    m.inference_precision = "tf32x3"
+    assert torch.equal(q_grad.detach(), m(d.x, d.edge_index, d.batch, d.ptr).detach())
+    with pytest.raises(ValueError):
+        ModernTwoHeaded(12, 3, 2, inference_precision="bf16")
+    csr = m.last_csr
+    sz = _lib.sizes(m._desc, csr.N, csr.E, csr.B, 128)
+    stash = torch.empty(sz.stash_bytes // 4, device=DEV)
+    ws = torch.empty(sz.fwd_ws_bytes // 4, device=DEV)
+    out = torch.empty(csr.N, device=DEV)
+    rc = _lib.lib().hexgnn_forward(C.byref(m._desc), C.c_void_p(m._flat.data_ptr()), C.c_void_p(d.x.data_ptr()), csr.N, csr.E,
+                                   csr.B, C.c_void_p(csr.blob.data_ptr()), 128, ops.HEXGNN_TF32X1, C.c_void_p(out.data_ptr()),
+                                   None, C.c_void_p(stash.data_ptr()), C.c_void_p(ws.data_ptr()), ws.numel() * 4, None)
+    assert rc == -1 and b"TF32X1" in _lib.lib().hexgnn_last_error()

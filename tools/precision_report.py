@@ -1,0 +1,106 @@
+"""Measured precision of the fused path against the fp64 oracle (not a test; writes JSON lines to stdout):
+
+  python tools/precision_report.py > profiles/precision_r2.jsonl
+
+1. inference precision policy: GNN-L, 128 11x11 positions, advantages_only -- 3xTF32 (default) vs the opt-in
+   single-pass TF32 (`inference_precision="tf32x1"`): max error relative to max|adv|, error of the graph-centred advantage,
+   and how often the per-graph arg-max over the non-terminal rows (rainbow.py:222-225) agrees with the fp64 oracle's;
+2. per-tensor gradient errors of the headline batch (GNN-L, 256 positions, learner loss), each relative to that tensor's own
+   largest fp64 gradient entry and to the whole gradient's largest entry, beside the fp32 torch oracle's own errors."""
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import torch  # noqa: E402
+
+import helpers  # noqa: E402
+import positions  # noqa: E402
+from gnn_hex_b200 import ModernTwoHeaded, data  # noqa: E402
+from oracle import hexgnn_oracle as orc  # noqa: E402
+
+
+def argmax_per_graph(adv, ptr):
+    out = []
+    for g in range(len(ptr) - 1):
+        a, b = int(ptr[g]), int(ptr[g + 1])
+        out.append(int(torch.argmax(adv[a + 2:b])) if b - a > 2 else -1)
+    return out
+
+
+def centred(v, batch):
+    cnt = torch.bincount(batch).double()
+    return v - (torch.zeros(len(cnt), dtype=torch.float64).index_add_(0, batch, v) / cnt)[batch]
+
+
+def main():
+    dev = "cuda:0"
+    torch.manual_seed(0)
+    o, m = helpers.make_pair(110, 15, 2, seed=0)
+    o64 = helpers.oracle64(o)
+    m = m.to(dev)
+    # ---- 1. inference precision ------------------------------------------------------------------------------------------
+    b = data.collate(positions.load_positions("pos_11x11_seed1234.npz", maker=1)[:128])
+    d = b.to(dev)
+    with torch.no_grad():
+        ref = o64(b.x.double(), b.edge_index, b.batch, b.ptr, advantages_only=True)[:, 0]
+        am_ref = argmax_per_graph(ref, b.ptr)
+        for mode in ("tf32x3", "tf32x1"):
+            m.inference_precision = mode
+            for _ in range(3):
+                adv = m(d.x, d.edge_index, d.batch, d.ptr, advantages_only=True)
+            torch.cuda.synchronize()
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            for _ in range(20):
+                adv = m(d.x, d.edge_index, d.batch, d.ptr, advantages_only=True)
+            e.record()
+            torch.cuda.synchronize()
+            a = adv[:, 0].cpu().double()
+            am = argmax_per_graph(a, b.ptr)
+            top2 = []
+            for g in range(len(b.ptr) - 1):   # margin between the oracle's best and second-best action, for context
+                v = torch.sort(ref[int(b.ptr[g]) + 2:int(b.ptr[g + 1])], descending=True).values
+                top2.append(float(v[0] - v[1]) if len(v) > 1 else 1.0)
+            print(json.dumps({"report": "inference_precision", "mode": mode, "graphs": 128, "model": "GNN-L",
+                              "max_rel_err_adv": float((a - ref).abs().max() / ref.abs().max()),
+                              "max_rel_err_centred_adv": float((centred(a, b.batch) - centred(ref, b.batch)).abs().max() / ref.abs().max()),
+                              "argmax_agreement": sum(int(x == y) for x, y in zip(am, am_ref)) / len(am_ref),
+                              "median_top2_margin_rel": float(sorted(top2)[len(top2) // 2] / ref.abs().max()),
+                              "ms_per_forward_incl_csr": s.elapsed_time(e) / 20}))
+        m.inference_precision = "tf32x3"
+    # ---- 2. per-tensor gradient errors, headline batch -----------------------------------------------------------------------
+    b = data.collate(positions.load_positions("pos_11x11_seed1234.npz", maker=1))
+    d = b.to(dev)
+    action, target, weight = helpers.loss_inputs(b)
+    t0 = time.time()
+    for mod, dt in ((o, torch.float32), (o64, torch.float64)):
+        mod.zero_grad(set_to_none=True)
+        q = mod(b.x.to(dt), b.edge_index, b.batch, b.ptr)
+        orc.rainbow_loss(q, b.ptr, action, target.to(dt), weight.to(dt)).backward()
+    m.zero_grad(set_to_none=True)
+    m.train_step(d.x, d.edge_index, d.batch, d.ptr, action=action.to(dev), target=target.to(dev), weight=weight.to(dev))
+    torch.cuda.synchronize()
+    r64, r32 = dict(o64.named_parameters()), dict(o.named_parameters())
+    gmax = max(float(p.grad.abs().max()) for p in r64.values() if p.grad is not None)
+    rows, worst_glob, worst_own = [], 0.0, 0.0
+    for name, p in m.named_parameters():
+        g64 = r64[name].grad
+        if g64 is None:
+            continue
+        g = p.grad.detach().cpu().double()
+        own = float(g64.abs().max())
+        err = float((g - g64).abs().max())
+        err32 = float((r32[name].grad.double() - g64).abs().max())
+        rows.append({"tensor": name, "own_max_over_global_max": own / gmax, "err_over_global_max": err / gmax,
+                     "err_over_own_max": err / max(own, 1e-300), "fp32_oracle_err_over_own_max": err32 / max(own, 1e-300)})
+        worst_glob, worst_own = max(worst_glob, err / gmax), max(worst_own, err / max(own, 1e-300))
+    print(json.dumps({"report": "gradient_errors", "model": "GNN-L", "graphs": 256, "whole_gradient_max_rel_err": worst_glob,
+                      "worst_per_tensor_rel_err": worst_own, "oracle_seconds": time.time() - t0, "tensors": rows}))
+
+
+if __name__ == "__main__":
+    main()
