@@ -104,8 +104,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
   constexpr int NQ = Hp / kTcKC;
   constexpr int MAXG = (NG + kTcSlices - 1) / kTcSlices;
   constexpr int NV = Hp / 4, PV = P / 4;
-  constexpr uint32_t TM_HI = 0, TM_LO = Hp, TM_D = 2 * Hp;
-  constexpr uint32_t TM_COLS = (3 * Hp <= 64) ? 64 : (3 * Hp <= 128) ? 128 : (3 * Hp <= 256) ? 256 : 512;
+  // TMEM columns: A hi | A lo | D (the hi * hi products) | Ds (the lo * hi and hi * lo products).  The tensor core's fp32
+  // accumulator TRUNCATES after every MMA, a bias of ~2^-25 of the running sum per accumulation; the small products live in
+  // their own accumulator so that only the 2 x Hp / 8 large ones truncate the large sum (a third of the accumulations), and
+  // the epilogue adds the two in round-to-nearest fp32.
+  constexpr uint32_t TM_HI = 0, TM_LO = Hp, TM_D = 2 * Hp, TM_DS = 3 * Hp;
+  constexpr uint32_t TM_COLS = (4 * Hp <= 64) ? 64 : (4 * Hp <= 128) ? 128 : (4 * Hp <= 256) ? 256 : 512;
   extern __shared__ __align__(128) uint8_t smem[];
   float* dump = (float*)(smem + S::off_dump);
   float* agg = (float*)(smem + S::off_agg);
@@ -203,9 +207,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
                 const uint64_t dhi = make_smem_desc(bhi + kk * 2 * lbo, lbo, sbo);
                 const uint64_t dlo = make_smem_desc(blo + kk * 2 * lbo, lbo, sbo);
                 const uint32_t kcol = q * kTcKC + kk * 8;
-                mma_tf32_ts(tbase + TM_D, tbase + TM_LO + kcol, dhi, idesc, (which | q | kk) != 0);
-                mma_tf32_ts(tbase + TM_D, tbase + TM_HI + kcol, dlo, idesc, true);
-                mma_tf32_ts(tbase + TM_D, tbase + TM_HI + kcol, dhi, idesc, true);
+                mma_tf32_ts(tbase + TM_DS, tbase + TM_LO + kcol, dhi, idesc, (which | q | kk) != 0);
+                mma_tf32_ts(tbase + TM_DS, tbase + TM_HI + kcol, dlo, idesc, true);
+                mma_tf32_ts(tbase + TM_D, tbase + TM_HI + kcol, dhi, idesc, (which | q | kk) != 0);
               }
               mma_commit(&bar_empty[st]);
             }
@@ -512,6 +516,17 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
             if (g < NG) tmem_ld8(trow + TM_D + g * 8, dh[gi]);
           }
           tmem_wait_ld();
+#pragma unroll
+          for (int gi = 0; gi < MAXG; ++gi) {       // + the small-product accumulator (round-to-nearest fp32 add)
+            const int g = slice + gi * kTcSlices;
+            if (g < NG) {
+              float ds[8];
+              tmem_ld8(trow + TM_DS + g * 8, ds);
+              tmem_wait_ld();
+#pragma unroll
+              for (int u = 0; u < 8; ++u) dh[gi][u] += ds[u];
+            }
+          }
         }
         // E1: ReLU mask, dpre -> TMEM (A of dpre*W_r), dump (pre-scaled by 1/deg for the gather), dZ stash
         {
@@ -621,6 +636,17 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
             if (g < NG) tmem_ld8(trow + TM_D + g * 8, dh[gi]);
           }
           tmem_wait_ld();
+#pragma unroll
+          for (int gi = 0; gi < MAXG; ++gi) {
+            const int g = slice + gi * kTcSlices;
+            if (g < NG) {
+              float ds[8];
+              tmem_ld8(trow + TM_DS + g * 8, ds);
+              tmem_wait_ld();
+#pragma unroll
+              for (int u = 0; u < 8; ++u) dh[gi][u] += ds[u];
+            }
+          }
         }
 #pragma unroll
         for (int gi = 0; gi < MAXG; ++gi) {

@@ -26,8 +26,8 @@ for _ in range(20):
 e.record(); torch.cuda.synchronize()
 f, fn = _lib.profile_read(0); bw, bn = _lib.profile_read(1)
 print(f"step ms {s.elapsed_time(e)/20:.4f}  fwd kernel {f/max(fn,1):.4f}  bwd chain kernel {bw/max(bn,1):.4f}")
-NAMES = {0: ["wait_Z", "P1_drain", "P2_gather+combine", "load+l0", "head", "mma:wait_A/R2", "mma:wait_w", "mma:issue", "total", "tiles",
-             "-", "P3_A-write"],
+NAMES = {0: ["wait_Zl", "phase1", "gather", "load+l0", "head", "mma:wait_h", "mma:wait_w", "mma:issue", "total", "tiles",
+             "wait_Zr", "phase3", "p3:ld", "p3:issued"],
          1: ["wait_dH", "E1", "E2_gather", "wait_r+A", "head+load", "layer0", "hl:load", "hl:+build+tanh", "total", "tiles",
              "hd:dq+adv", "hd:colpass", "hd:mlp_fwd", "hd:mlp_bwd", "hd:hrec+dp", "hd:rows"]}
 for which in (0, 1):

@@ -40,6 +40,10 @@ def main():
     dev = "cuda:0"
     torch.manual_seed(0)
     o, m = helpers.make_pair(110, 15, 2, seed=0)
+    # name-hashed weights with gain 1.7 (tests/helpers.set_hash_weights): the default init's range makes a 17-layer ReLU stack
+    # contract to node-independent embeddings (top-2 advantage margin ~1e-5 of max|adv|), where an arg-max says nothing
+    helpers.set_hash_weights(o, seed=0, gain=1.7)
+    m.load_state_dict(o.state_dict())
     o64 = helpers.oracle64(o)
     m = m.to(dev)
     # ---- 1. inference precision ------------------------------------------------------------------------------------------
