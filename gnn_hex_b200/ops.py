@@ -1,6 +1,7 @@
 """Tensor-level wrappers over the C-ABI (include/hexgnn.h).  PyTorch only provides device memory
 and the current stream here; all arithmetic happens in libhexgnn.so."""
 import ctypes as C
+import os
 
 import torch
 
@@ -12,6 +13,7 @@ from ._lib import HEXGNN_ADV_ONLY, HEXGNN_SEPARATE, HEXGNN_PATH_SIMT, HEXGNN_PAT
 # backward: pack, fused, reduce, unpack) -- bench.py's `gpu_launches` is read off this counter.
 LAUNCHES = {"build_csr": 1, "forward": 2, "backward": 5, "td_loss": 1, "train_step": 6, "adam_step": 2, "mask_argmax": 1, "td_target": 1, "forward_big": 0, "allreduce_p2p": 1, "noisy": 1}
 launch_counter = 0
+NVTX = os.environ.get("HEXGNN_NVTX", "0") == "1"
 
 
 def _count(what):
@@ -36,6 +38,15 @@ def _on_tensor_device(fn):
 
     @functools.wraps(fn)
     def wrapped(*args, **kwargs):
+        if NVTX:                                 # HEXGNN_NVTX=1: one range per C-ABI call (tracing)
+            torch.cuda.nvtx.range_push("hexgnn::" + fn.__name__)
+            try:
+                return guarded(*args, **kwargs)
+            finally:
+                torch.cuda.nvtx.range_pop()
+        return guarded(*args, **kwargs)
+
+    def guarded(*args, **kwargs):
         idx = -1
         for a in args:
             t = a.blob if isinstance(a, CsrBlob) else a
