@@ -43,7 +43,12 @@ __global__ void __launch_bounds__(kDwThreads, 1) sage_dw_tc_kernel(const __grid_
   constexpr int a_bytes = ABLK * kDwBlk, b_bytes = NJ * kDwBlk; // one row chunk of each operand (fp32)
   constexpr int half_bytes = a_bytes + b_bytes;             // hi half; the lo half follows
   constexpr int stage_bytes = 2 * half_bytes;
-  constexpr uint32_t TM_COLS = (N2 <= 32) ? 32 : (N2 <= 64) ? 64 : (N2 <= 128) ? 128 : 256;
+  // two accumulators: D (columns [0, N2)) takes the hi * hi products, Ds ([N2, 2 N2)) the lo * hi and hi * lo ones.  The tensor
+  // core truncates its fp32 accumulator after every MMA (~2^-25 of the running sum each), and one item accumulates hundreds of
+  // MMAs (every 8 node rows of its tiles: three); with the small products elsewhere only a third of them truncate the large
+  // sum, and the epilogue adds D + Ds in round-to-nearest fp32.
+  constexpr uint32_t TM_DS = N2;
+  constexpr uint32_t TM_COLS = (2 * N2 <= 32) ? 32 : (2 * N2 <= 64) ? 64 : (2 * N2 <= 128) ? 128 : (2 * N2 <= 256) ? 256 : 512;
   extern __shared__ uint8_t smem_dyn[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_dyn + 1023) & ~(uintptr_t)1023);
   __shared__ uint64_t bar_full[kDwStages], bar_split[kDwStages], bar_empty[kDwStages], bar_done;
@@ -126,9 +131,9 @@ __global__ void __launch_bounds__(kDwThreads, 1) sage_dw_tc_kernel(const __grid_
             const uint64_t dal = make_smem_desc(alo + ks * 1024, kDwBlk, 512) | one;
             const uint64_t dbh = make_smem_desc(bhi + ks * 1024, kDwBlk, 512) | one;
             const uint64_t dbl = make_smem_desc(blo + ks * 1024, kDwBlk, 512) | one;
-            mma_tf32_ss(tbase, dal, dbh, idesc, (it | ks) != 0);
-            mma_tf32_ss(tbase, dah, dbl, idesc, true);
-            mma_tf32_ss(tbase, dah, dbh, idesc, true);
+            mma_tf32_ss(tbase + TM_DS, dal, dbh, idesc, (it | ks) != 0);
+            mma_tf32_ss(tbase + TM_DS, dah, dbl, idesc, true);
+            mma_tf32_ss(tbase, dah, dbh, idesc, (it | ks) != 0);
           }
           mma_commit(&bar_empty[st]);
         }
@@ -173,9 +178,12 @@ __global__ void __launch_bounds__(kDwThreads, 1) sage_dw_tc_kernel(const __grid_
       float* rec = a.big_rec + (int64_t)grp * a.gl.g0;
       const bool have = it > 0;
       for (int c0 = 0; c0 < N2; c0 += 8) {
-        float v[8];
+        float v[8], vs[8];
         tmem_ld8(trow + c0, v);                            // warp-collective: every lane takes part
+        tmem_ld8(trow + TM_DS + c0, vs);
         tmem_wait_ld();
+#pragma unroll
+        for (int u = 0; u < 8; ++u) v[u] += vs[u];
         if (!have) {
 #pragma unroll
           for (int u = 0; u < 8; ++u) v[u] = 0.f;
