@@ -16,11 +16,13 @@ ST_GRAPH_TOO_LARGE = 1
 ST_EDGE_CROSSES = 2
 ST_BATCH_UNSORTED = 4
 ST_FLAG_MIXED = 8
+ST_FP16_RANGE = 16
 STATUS_NAMES = {
     ST_GRAPH_TOO_LARGE: "a graph has more nodes/edges than one tile holds (raise tile_rows)",
     ST_EDGE_CROSSES: "an edge joins two different graphs or is out of range",
     ST_BATCH_UNSORTED: "`batch` is not sorted / out of range",
     ST_FLAG_MIXED: "x[:,2] is not constant over the batch (reference asserts this, GN0/models.py:538)",
+    ST_FP16_RANGE: "an activation left the fp16 range of the forward kernel's mixed product scheme (|h| >= 60000): use path='simt'",
 }
 
 ABI_VERSION = 7

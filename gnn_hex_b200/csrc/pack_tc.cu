@@ -1,6 +1,7 @@
 // Weight images for the tcgen05 kernels (layout documented in sage_tc.cuh): torch layout -> per layer,
 // per 16-wide k chunk, a tf32-hi half and a tf32-lo half in the K-major SWIZZLE_NONE canonical form the
 // tensor core reads, so the kernels fetch each ring stage with ONE contiguous bulk copy.
+#include <cuda_fp16.h>
 #include "sage_tc.cuh"
 #include "td_loss.cuh"
 
@@ -28,13 +29,15 @@ __global__ void pack_tc_kernel(Dims d, ParamMap pm, const float* __restrict__ pa
     float hi, lo;
     tc::split_tf32(val, hi, lo);
     {
-      // forward: stage q8 = B[n][k in 8-chunk q8], n in [0,2Hp) (lin_l rows then lin_r rows), hi half then lo half
-      const int64_t halfF = (int64_t)kTcKF * N2;
+      // forward: stage (which, q8), c = out channel of lin_l (which 0) / lin_r (which 1); layouts in sage_tc.cuh
+      const int which = n < Hp ? 0 : 1;
       const int q8 = k / kTcKF, kq = k % kTcKF;
-      const int64_t off = ((int64_t)(s - 1) * (Hp / kTcKF) + q8) * 2 * halfF + (int64_t)(kq / 4) * (N2 * 4) +
-                          (n / 8) * 32 + (n % 8) * 4 + (kq % 4);
-      pv.wimg[off] = hi;
-      pv.wimg[off + halfF] = lo;
+      char* stage = (char*)pv.wimg + (((int64_t)(s - 1) * 2 + which) * (Hp / kTcKF) + q8) * (int64_t)(Hp * 64);
+      const int64_t rowoff = (int64_t)(c / 8) * 128 + (c % 8) * 16;
+      *(float*)(stage + (int64_t)(kq / 4) * (Hp * 16) + rowoff + (kq % 4) * 4) = hi;                  // part 0: tf32 hi
+      __half* p1 = (__half*)(stage + Hp * 32);
+      p1[(rowoff + kq * 2) / 2] = __float2half_rn(hi);                                               // k' = kq
+      p1[((int64_t)Hp * 16 + rowoff + kq * 2) / 2] = __float2half_rn(lo * 2048.0f);                  // k' = 8 + kq
     }
     if (with_transpose) {
       // backward: dH[i][k] = sum_c dZ_which[i][c] * W_which[c][k]  =>  B[n = k][kk = c], which 0 = lin_r, 1 = lin_l

@@ -34,9 +34,9 @@ struct FwdTcSmem {
   static constexpr int Hp = 16 * NJ;
   static constexpr int P = Hp + 4;                       // row pitch (floats): float4 rows conflict-free
   static constexpr int ECAP = kEdgeCapPerRow * kTcRows;
-  static constexpr int stages = NJ <= 7 ? 5 : 3;         // ring depth
+  static constexpr int stages = NJ <= 7 ? 10 : 6;        // ring depth
   static constexpr int N2 = 32 * NJ;
-  static constexpr int half_bytes = kTcKF * N2 * 4;      // one tf32 half (hi or lo) of a k-chunk stage
+  static constexpr int half_bytes = kTcKF * Hp * 4;      // one part (tf32 hi | fp16 pair operand) of a (lin_l | lin_r, k-chunk) stage
   static constexpr int stage_bytes = 2 * half_bytes;
   static constexpr int off_ring = 0;
   static constexpr int off_dump = off_ring + stages * stage_bytes;               // float [128][P]  Zl rows
@@ -50,8 +50,8 @@ struct FwdTcSmem {
   static constexpr int off_gp = off_rowptr + (kTcRows + 4) * 4;                  // int [64+4]
   static constexpr int off_col = off_gp + (kMaxTileGraphs + 4) * 4;              // u16 [ECAP]
   static constexpr int off_gtab = (off_col + ECAP * 2 + 15) & ~15;               // gather table (sage_tc.cuh)
-  static constexpr int off_bar = off_gtab + gather_tab_bytes();                  // u64 [2*stages + 6], u32 tmem slot
-  static constexpr int off_bias = off_bar + (2 * stages + 6) * 8 + 16;           // float [Lt][Hp] (runtime sized)
+  static constexpr int off_bar = off_gtab + gather_tab_bytes();                  // u64 [2*stages + 8], u32 tmem slot
+  static constexpr int off_bias = off_bar + (2 * stages + 8) * 8 + 16;           // float [Lt][Hp] (runtime sized)
   static size_t bytes(int Lt) { return (size_t)off_bias + (size_t)Lt * Hp * 4; }
 };
 
@@ -85,7 +85,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
   constexpr int NG = 2 * NJ;                 // 8-column granules per row
   constexpr int NQ = Hp / kTcKF;             // k chunks (ring stages) per layer
   constexpr int MAXG = (NG + kTcSlices - 1) / kTcSlices;   // granules per epilogue thread
-  constexpr uint32_t TM_HI = 0, TM_LO = Hp, TM_D = 2 * Hp;     // TMEM columns
+  // TMEM columns: A hi (tf32) | A16 (fp16 pairs [2^11 lo | hi], 8 columns per k-chunk) | D | Ds -- the mixed 3-product scheme
+  // of sage_tc.cuh.  A layer is TWO N = Hp GEMMs on the same A operand: Zl = h W_l^T first, and Zr = h W_r^T while the
+  // epilogue gathers Zl; D takes the large products, Ds the (2^11-scaled) small ones, Z = D + 2^-11 Ds in the epilogue.
+  constexpr uint32_t TM_HI = 0, TM_A16 = Hp, TM_D = 2 * Hp, TM_DS = 3 * Hp;
+  constexpr float kDsScale = 1.0f / 2048.0f;
   constexpr uint32_t TM_COLS = (4 * Hp <= 64) ? 64 : (4 * Hp <= 128) ? 128 : (4 * Hp <= 256) ? 256 : 512;
   extern __shared__ __align__(128) uint8_t smem[];
   float* dump = (float*)(smem + S::off_dump);
@@ -101,8 +105,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
   const GatherTab gtab = gather_tab_view(smem + S::off_gtab);
   uint64_t* bar_full = (uint64_t*)(smem + S::off_bar);
   uint64_t* bar_empty = bar_full + kStages;
-  uint64_t* bar_z = bar_empty + kStages;
-  uint64_t* bar_a = bar_z + 2;               // [4]: column quarter gi of the next A operand is in TMEM
+  uint64_t* bar_z = bar_empty + kStages;     // MMA -> epilogue: Zl complete in D / Ds
+  uint64_t* bar_r = bar_z + 1;               // MMA -> epilogue: Zr complete in D / Ds
+  uint64_t* bar_df = bar_r + 1;              // epilogue -> MMA: Zl has been drained, the Zr GEMM may overwrite D / Ds
+  uint64_t* bar_a = bar_df + 1;              // [4]: column quarter gi of the next A operand is in TMEM
   uint32_t* tmem_slot = (uint32_t*)(bar_a + 4);
   float* bias_s = (float*)(smem + S::off_bias);
 
@@ -115,6 +121,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
   if (tid == 0) {
     for (int i = 0; i < kStages; ++i) { mbar_init(&bar_full[i], 1); mbar_init(&bar_empty[i], 1); }
     mbar_init(bar_z, 1);
+    mbar_init(bar_r, 1);
+    mbar_init(bar_df, kTcEpiWarps);
     for (int i = 0; i < 4; ++i) mbar_init(&bar_a[i], kTcEpiWarps);
     fence_mbar_init();
   }
@@ -137,8 +145,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
       const int t = a.csr.tile_order[ti];
         if (!tile_dims(a.csr, t, S::ECAP).ok) continue;
         for (int s = 1; s < Lt; ++s) {
-          const uint8_t* src = (const uint8_t*)a.pv.wimg + (size_t)(s - 1) * NQ * S::stage_bytes;
-          for (int q = 0; q < NQ; ++q, ++it) {
+          const uint8_t* src = (const uint8_t*)a.pv.wimg + (size_t)(s - 1) * 2 * NQ * S::stage_bytes;
+          for (int q = 0; q < 2 * NQ; ++q, ++it) {   // the lin_l chunks, then the lin_r chunks
             const int st = it % kStages;
             mbar_wait(&bar_empty[st], ((it / kStages) & 1) ^ 1);
             mbar_expect_tx(&bar_full[st], S::stage_bytes);
@@ -151,8 +159,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
   } else if (wid == kTcEpiWarps + 1) {
     // ================= MMA issuer =================
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_tf32(kTcRows, S::N2, false);
-      constexpr uint32_t lbo = S::N2 * 16, sbo = 128;
+      constexpr uint32_t idesc = make_idesc_tf32(kTcRows, Hp, false), idesc16 = make_idesc_f16(kTcRows, Hp);
+      constexpr uint32_t lbo = Hp * 16, sbo = 128;
       const bool x1 = (a.flags & HEXGNN_TF32X1) != 0;
       uint32_t it = 0, na = 0;
       for (int rnd = 0; rnd * (int)gridDim.x < ntiles; ++rnd) {
@@ -162,36 +170,38 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
         if (!tile_dims(a.csr, t, S::ECAP).ok) continue;
         for (int s = 1; s < Lt; ++s) {
           long long tq;
-          for (int q = 0; q < NQ; ++q, ++it) {
-            if ((q % kTcSlices) == 0) {
-              // granules [q, q + kTcSlices) of h (k-steps q .. q+3) are in TMEM; for q = 0 also: D has been drained.
-              // The epilogue releases h quarter by quarter, so these MMAs run under the rest of its phase 3.
+          for (int which = 0; which < 2; ++which) {        // Zl = h W_l^T, then Zr = h W_r^T (same A operand)
+            for (int q = 0; q < NQ; ++q, ++it) {
+              if (which == 0 && (q % kTcSlices) == 0) {
+                // granules [q, q + kTcSlices) of h (k-chunks q .. q+3) are in TMEM; the epilogue releases h quarter by
+                // quarter (and has read Zr of the previous layer before the first quarter), so these MMAs run under the
+                // rest of its phase 3
+                tq = PH_NOW();
+                mbar_wait(&bar_a[q / kTcSlices], na & 1);
+                PH_ADD(ph5, tq);
+                tc_fence_after();
+              }
+              if (which == 1 && q == 0) {                    // Zl has been drained from D / Ds
+                tq = PH_NOW();
+                mbar_wait(bar_df, na & 1);
+                PH_ADD(ph5, tq);
+                tc_fence_after();
+              }
+              const int st = it % kStages;
               tq = PH_NOW();
-              mbar_wait(&bar_a[q / kTcSlices], na & 1);
-              PH_ADD(ph5, tq);
+              mbar_wait(&bar_full[st], (it / kStages) & 1);
+              PH_ADD(ph6, tq);
+              tq = PH_NOW();
               tc_fence_after();
+              const uint32_t b0 = smem_u32(smem + S::off_ring + st * S::stage_bytes);
+              // (HEXGNN_TF32X1, opt-in inference: the large product alone)
+              if (!x1) mma_f16_ts(tbase + TM_DS, tbase + TM_A16 + q * 8, make_smem_desc(b0 + S::half_bytes, lbo, sbo), idesc16, q != 0);
+              mma_tf32_ts(tbase + TM_D, tbase + TM_HI + q * kTcKF, make_smem_desc(b0, lbo, sbo), idesc, q != 0);
+              mma_commit(&bar_empty[st]);   // stage free once these MMAs have read it
+              PH_ADD(ph7, tq);
             }
-            const int st = it % kStages;
-            tq = PH_NOW();
-            mbar_wait(&bar_full[st], (it / kStages) & 1);
-            PH_ADD(ph6, tq);
-            tq = PH_NOW();
-            tc_fence_after();
-            const uint32_t bhi = smem_u32(smem + S::off_ring + st * S::stage_bytes);
-            const uint64_t dhi = make_smem_desc(bhi, lbo, sbo);
-            const uint64_t dlo = make_smem_desc(bhi + S::half_bytes, lbo, sbo);
-            const uint32_t kcol = q * kTcKF;
-            if (x1) {   // HEXGNN_TF32X1 (opt-in inference): the hi * hi pass alone
-              mma_tf32_ts(tbase + TM_D, tbase + TM_HI + kcol, dhi, idesc, q != 0);
-            } else {
-              mma_tf32_ts(tbase + TM_D, tbase + TM_LO + kcol, dhi, idesc, q != 0);
-              mma_tf32_ts(tbase + TM_D, tbase + TM_HI + kcol, dlo, idesc, true);
-              mma_tf32_ts(tbase + TM_D, tbase + TM_HI + kcol, dhi, idesc, true);
-            }
-            mma_commit(&bar_empty[st]);   // stage free once these MMAs have read it
-            PH_ADD(ph7, tq);
+            mma_commit(which == 0 ? bar_z : bar_r);
           }
-          mma_commit(bar_z);              // Z complete
           ++na;
         }
       }
@@ -208,6 +218,25 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
     const float flag = a.x[2];
     const int head = (flag == 1.0f) ? 0 : 1;
     const float* Pm = a.params;
+    const bool x1e = (a.flags & HEXGNN_TF32X1) != 0;   // single-pass inference: Ds is not written
+    int range_bad = 0;
+    // one 8-channel granule (= one k-chunk) of the next A operand: tf32 hi columns + the fp16 pair columns [2^11 lo | hi]
+    auto store_A = [&](int g, const float (&v)[8]) {
+      float hi[8], lo[8];
+      uint32_t pk[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        split_tf32(v[u], hi[u], lo[u]);
+        if (v[u] >= 60000.f) range_bad = 1;              // (activations are ReLU outputs: >= 0)
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        pk[j] = pack_f16x2(lo[2 * j] * 2048.0f, lo[2 * j + 1] * 2048.0f);    // k' = 2j, 2j + 1
+        pk[4 + j] = pack_f16x2(hi[2 * j], hi[2 * j + 1]);                    // k' = 8 + 2j, 8 + 2j + 1
+      }
+      tmem_st8(trow + TM_HI + g * 8, hi);
+      tmem_st8u(trow + TM_A16 + g * 8, pk);
+    };
     uint32_t nd = 0;
     for (int rnd = 0; rnd * (int)gridDim.x < ntiles; ++rnd) {
       const int ti = tile_position(rnd, blockIdx.x, gridDim.x, a.tile_flag == nullptr);
@@ -278,7 +307,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
         const float xm0 = m0_s[row], xm1 = m1_s[row], xx0 = x0_s[row], xx1 = x1_s[row];
         uint32_t mw = 0;
         for (int g = slice, gi = 0; g < NG; g += kTcSlices, ++gi) {
-          float v[8], hi[8], lo[8];
+          float v[8];
 #pragma unroll
           for (int u = 0; u < 8; ++u) {
             const int c = g * 8 + u;
@@ -287,10 +316,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
               r = fmaxf(wl[2 * c] * xm0 + wl[2 * c + 1] * xm1 + bl[c] + wr[2 * c] * xx0 + wr[2 * c + 1] * xx1, 0.f);
             v[u] = r;
             if (r > 0.f) mw |= 1u << (gi * 8 + u);
-            split_tf32(r, hi[u], lo[u]);
           }
-          tmem_st8(trow + TM_HI + g * 8, hi);
-          tmem_st8(trow + TM_LO + g * 8, lo);
+          store_A(g, v);
           if (st_img && row < n32) {
             st_global_v8(st_img + rm32_granule_off(g, row), v[0], v[1], v[2], v[3], v[4], v[5], v[6], v[7]);
           }
@@ -330,6 +357,24 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
             if (g < NG) tmem_ld8(trow + TM_D + g * 8, v[gi]);
           }
           tmem_wait_ld();
+          if (!x1e) {
+#pragma unroll
+            for (int gi = 0; gi < MAXG; gi += 2) {       // + 2^-11 x the small-product accumulator, two granules per round trip
+              float d0[8], d1[8];
+              const int g0_ = slice + gi * kTcSlices, g1_ = slice + (gi + 1) * kTcSlices;
+              if (g0_ < NG) tmem_ld8(trow + TM_DS + g0_ * 8, d0);
+              if (gi + 1 < MAXG && g1_ < NG) tmem_ld8(trow + TM_DS + g1_ * 8, d1);
+              tmem_wait_ld();
+#pragma unroll
+              for (int u = 0; u < 8; ++u) {
+                if (g0_ < NG) v[gi][u] = fmaf(d0[u], kDsScale, v[gi][u]);
+                if (gi + 1 < MAXG && g1_ < NG) v[gi + 1][u] = fmaf(d1[u], kDsScale, v[gi + 1][u]);
+              }
+            }
+          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_df);          // Zl is in registers: the Zr GEMM may start (it runs under phase 2)
 #pragma unroll
           for (int gi = 0; gi < MAXG; ++gi) {
             const int g = slice + gi * kTcSlices;
@@ -354,19 +399,37 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
         char* st = (a.stash && row < n32) ? st_img + (size_t)s * a.B * img_bytes : nullptr;
         {
           float zr[MAXG][8];
+          mbar_wait(bar_r, (nd - 1) & 1);             // Zr complete (its GEMM ran under the gather)
+          tc_fence_after();
+          PH_ADD(ph10, tq);
 #pragma unroll
           for (int gi = 0; gi < MAXG; ++gi) {
             const int g = slice + gi * kTcSlices;
-            if (g < NG) tmem_ld8(trow + TM_D + Hp + g * 8, zr[gi]);
+            if (g < NG) tmem_ld8(trow + TM_D + g * 8, zr[gi]);
           }
           tmem_wait_ld();
+          if (!x1e) {
+#pragma unroll
+            for (int gi = 0; gi < MAXG; gi += 2) {
+              float d0[8], d1[8];
+              const int g0_ = slice + gi * kTcSlices, g1_ = slice + (gi + 1) * kTcSlices;
+              if (g0_ < NG) tmem_ld8(trow + TM_DS + g0_ * 8, d0);
+              if (gi + 1 < MAXG && g1_ < NG) tmem_ld8(trow + TM_DS + g1_ * 8, d1);
+              tmem_wait_ld();
+#pragma unroll
+              for (int u = 0; u < 8; ++u) {
+                if (g0_ < NG) zr[gi][u] = fmaf(d0[u], kDsScale, zr[gi][u]);
+                if (gi + 1 < MAXG && g1_ < NG) zr[gi + 1][u] = fmaf(d1[u], kDsScale, zr[gi + 1][u]);
+              }
+            }
+          }
           PH_ADD(ph12, tq);
           uint32_t mw = 0;
 #pragma unroll
           for (int gi = 0; gi < MAXG; ++gi) {
             const int g = slice + gi * kTcSlices;
             if (g < NG) {
-              float acc[8], hi[8], lo[8];
+              float acc[8];
               if (live) {
                 const float4* src = (const float4*)(agg + row * P + g * 8);
                 const float4 v0 = src[0], v1 = src[1];
@@ -378,7 +441,6 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
                 const float r = live ? fmaxf(fmaf(acc[u], inv, zr[gi][u] + bias[g * 8 + u]), 0.f) : 0.f;
                 acc[u] = r;
                 if (r > 0.f) mw |= 1u << (gi * 8 + u);
-                split_tf32(r, hi[u], lo[u]);
               }
               if (st) {
                 st_global_v8(st + rm32_granule_off(g, row), acc[0], acc[1], acc[2], acc[3], acc[4], acc[5], acc[6], acc[7]);
@@ -389,8 +451,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
                 dst[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
               }
               if (!last) {
-                tmem_st8(trow + TM_HI + g * 8, hi);
-                tmem_st8(trow + TM_LO + g * 8, lo);
+                store_A(g, acc);
               } else {
                 tmem_st8(trow + TM_D + g * 8, acc);   // park the exact fp32 activations in the drained Zl columns
               }
@@ -411,6 +472,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
         tmem_wait_st();
         PH_ADD(ph11, tq);
       }
+      if (range_bad) { atomicOr(a.csr.status, HEXGNN_ST_FP16_RANGE); range_bad = 0; }
       tq = PH_NOW();
       // ---- final activations -> shared (row major) for the head ----------------------------------------------------
       epi_bar();   // every gather of the last layer has finished reading the dump

@@ -33,12 +33,22 @@ constexpr int kTcEpiThreads = kTcEpiWarps * 32;
 constexpr int kTcThreads = kTcEpiThreads + 64;  // + producer warp + MMA warp
 
 // Weight images for the forward, one per SAGE layer s = 1..Lt-1 of the taken head:
-//   img[s-1][q8][half][...]  q8 = 8-wide k chunk (Hp/8 of them) = one ring stage = one contiguous bulk copy = the
-//   operand of one 3xTF32 MMA triple; half 0 = tf32 hi, 1 = tf32 lo
-//   inside a half: K-major SWIZZLE_NONE canonical B operand, B[n][k], n in [0,2Hp), k in [8 q8, 8 q8 + 8):
-//   byte = ((k%8)/4) * (2Hp*16) + (n/8)*128 + (n%8)*16 + (k%4)*4
-// One N = 2Hp instruction per k-step: splitting N (Zl / Zr) was measured on B200 and is a loss -- an N = 112 tf32 MMA
-// costs ~100 cycles against ~124 for N = 224.
+//   img[s-1][which][q8][part][...]  which 0 = lin_l, 1 = lin_r; q8 = 8-wide k chunk (Hp/8 of them); one (which, q8) = one ring
+//   stage = one contiguous bulk copy = the operands of one (fp16 MMA, tf32 MMA) pair, see "mixed 3-product scheme" below.
+//   part 0 (Hp*32 bytes): tf32 hi of W, K-major SWIZZLE_NONE canonical B operand, B[c][k], c in [0,Hp) the out channel,
+//          k in [8 q8, 8 q8 + 8):  byte = ((k%8)/4) * (Hp*16) + (c/8)*128 + (c%8)*16 + (k%4)*4
+//   part 1 (Hp*32 bytes): fp16 operand of the two SMALL products, K = 16: k' in [0,8) = hi(W[c][8 q8 + k']),
+//          k' in [8,16) = 2^11 lo(W[c][8 q8 + k' - 8]):  byte = (k'/8) * (Hp*16) + (c/8)*128 + (c%8)*16 + (k'%8)*2
+// A layer is two N = Hp GEMMs on the same A operand (Zl first; Zr runs under the CSR gather of Zl), see sage_fwd_tc.cu.
+//
+// Mixed 3-product scheme of the forward.  a*b ~= hi_a*hi_b + (lo_a*hi_b + hi_a*lo_b) as before (every factor an exact
+// 11-bit-mantissa value), but the two small products of a k-chunk are ONE kind::f16 MMA with K = 16:
+//     A16 = [2^11 lo_a (8 values) | hi_a (8 values)],  B16 = [hi_b ; 2^11 lo_b]   ->  Ds += 2^11 (lo_a*hi_b + hi_a*lo_b)
+// (tf32 and fp16 both carry 11 significant bits, so hi_a, hi_b, 2^11 lo_a, 2^11 lo_b convert EXACTLY while they stay inside
+// the fp16 range: |activation|, |weight| < 65504; the 2^11 keeps the lo parts away from fp16's subnormals), accumulated in
+// its own TMEM accumulator Ds, and the large product stays a kind::tf32 MMA into D.  Z = D + 2^-11 Ds in the epilogue (fp32,
+// round to nearest).  Two MMAs per k-chunk instead of three, and only the Hp/8 large products truncate the large sum (the
+// tensor core truncates its fp32 accumulator after every MMA).  Activations beyond the fp16 range set HEXGNN_ST_FP16_RANGE.
 constexpr int kTcKF = 8;              // k values per forward ring stage (one MMA k-step)
 struct TcPackView {
   float* wimg;    // forward images   (Lt-1) * Hp * 2Hp * 2 floats

@@ -60,7 +60,9 @@ enum {
   HEXGNN_ST_GRAPH_TOO_LARGE = 1, /* a graph has more nodes/edges than one tile holds   */
   HEXGNN_ST_EDGE_CROSSES = 2,    /* an edge joins two different graphs (or is out of range) */
   HEXGNN_ST_BATCH_UNSORTED = 4,  /* `batch` is not non-decreasing                     */
-  HEXGNN_ST_FLAG_MIXED = 8       /* x[:,2] is not constant (the reference asserts this, models.py:538) */
+  HEXGNN_ST_FLAG_MIXED = 8,      /* x[:,2] is not constant (the reference asserts this, models.py:538) */
+  HEXGNN_ST_FP16_RANGE = 16      /* an activation reached |h| >= 60000: outside the exact range of the forward kernel's
+                                    mixed fp16 / tf32 product scheme (csrc/sage_tc.cuh); use the fp32 path (PATH_SIMT)   */
 };
 
 /* Hyper-parameters of modern_two_headed (GN0/models.py:928-947): in_channels is 2. */
