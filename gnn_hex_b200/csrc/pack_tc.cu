@@ -29,15 +29,14 @@ __global__ void pack_tc_kernel(Dims d, ParamMap pm, const float* __restrict__ pa
     float hi, lo;
     tc::split_tf32(val, hi, lo);
     {
-      // forward: stage (which, q8), c = out channel of lin_l (which 0) / lin_r (which 1); layouts in sage_tc.cuh
+      // forward: stage (which, p), c = out channel of lin_l (which 0) / lin_r (which 1); fp16 hi | 2^11 lo (sage_tc.cuh)
       const int which = n < Hp ? 0 : 1;
-      const int q8 = k / kTcKF, kq = k % kTcKF;
-      char* stage = (char*)pv.wimg + (((int64_t)(s - 1) * 2 + which) * (Hp / kTcKF) + q8) * (int64_t)(Hp * 64);
-      const int64_t rowoff = (int64_t)(c / 8) * 128 + (c % 8) * 16;
-      *(float*)(stage + (int64_t)(kq / 4) * (Hp * 16) + rowoff + (kq % 4) * 4) = hi;                  // part 0: tf32 hi
-      __half* p1 = (__half*)(stage + Hp * 32);
-      p1[(rowoff + kq * 2) / 2] = __float2half_rn(hi);                                               // k' = kq
-      p1[((int64_t)Hp * 16 + rowoff + kq * 2) / 2] = __float2half_rn(lo * 2048.0f);                  // k' = 8 + kq
+      const int pq = k / kTcKF, kk = k % kTcKF;
+      char* stage = (char*)pv.wimg + (((int64_t)(s - 1) * 2 + which) * (Hp / kTcKF) + pq) * (int64_t)(Hp * 64);
+      const int64_t off = (int64_t)(kk / 8) * (Hp * 16) + (int64_t)(c / 8) * 128 + (c % 8) * 16 + (kk % 8) * 2;
+      const __half h16 = __float2half_rn(val);
+      *(__half*)(stage + off) = h16;
+      *(__half*)(stage + Hp * 32 + off) = __float2half_rn((val - __half2float(h16)) * 2048.0f);
     }
     if (with_transpose) {
       // backward: dH[i][k] = sum_c dZ_which[i][c] * W_which[c][k]  =>  B[n = k][kk = c], which 0 = lin_r, 1 = lin_l

@@ -36,7 +36,7 @@ struct FwdTcSmem {
   static constexpr int ECAP = kEdgeCapPerRow * kTcRows;
   static constexpr int stages = NJ <= 7 ? 10 : 6;        // ring depth
   static constexpr int N2 = 32 * NJ;
-  static constexpr int half_bytes = kTcKF * Hp * 4;      // one part (tf32 hi | fp16 pair operand) of a (lin_l | lin_r, k-chunk) stage
+  static constexpr int half_bytes = kTcKF * Hp * 2;      // one part (fp16 hi | fp16 2^11 lo) of a (lin_l | lin_r, 16-k chunk) stage
   static constexpr int stage_bytes = 2 * half_bytes;
   static constexpr int off_ring = 0;
   static constexpr int off_dump = off_ring + stages * stage_bytes;               // float [128][P]  Zl rows
@@ -85,12 +85,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
   constexpr int NG = 2 * NJ;                 // 8-column granules per row
   constexpr int NQ = Hp / kTcKF;             // k chunks (ring stages) per layer
   constexpr int MAXG = (NG + kTcSlices - 1) / kTcSlices;   // granules per epilogue thread
-  // TMEM columns: A hi (tf32) | A16 (fp16 pairs [2^11 lo | hi], 8 columns per k-chunk) | D | Ds -- the mixed 3-product scheme
-  // of sage_tc.cuh.  A layer is TWO N = Hp GEMMs on the same A operand: Zl = h W_l^T first, and Zr = h W_r^T while the
+  // TMEM columns: A (fp16 pairs; per 16-k chunk 8 columns of 2^11 lo, then 8 columns of hi) | D | Ds -- the all-fp16 3-product
+  // scheme of sage_tc.cuh.  A layer is TWO N = Hp GEMMs on the same A operand: Zl = h W_l^T first, and Zr = h W_r^T while the
   // epilogue gathers Zl; D takes the large products, Ds the (2^11-scaled) small ones, Z = D + 2^-11 Ds in the epilogue.
-  constexpr uint32_t TM_HI = 0, TM_A16 = Hp, TM_D = 2 * Hp, TM_DS = 3 * Hp;
+  constexpr uint32_t TM_A = 0, TM_D = Hp, TM_DS = 2 * Hp;
   constexpr float kDsScale = 1.0f / 2048.0f;
-  constexpr uint32_t TM_COLS = (4 * Hp <= 64) ? 64 : (4 * Hp <= 128) ? 128 : (4 * Hp <= 256) ? 256 : 512;
+  constexpr uint32_t TM_COLS = (3 * Hp <= 64) ? 64 : (3 * Hp <= 128) ? 128 : (3 * Hp <= 256) ? 256 : 512;
   extern __shared__ __align__(128) uint8_t smem[];
   float* dump = (float*)(smem + S::off_dump);
   float* agg = (float*)(smem + S::off_agg);
@@ -159,7 +159,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
   } else if (wid == kTcEpiWarps + 1) {
     // ================= MMA issuer =================
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_tf32(kTcRows, Hp, false), idesc16 = make_idesc_f16(kTcRows, Hp);
+      constexpr uint32_t idesc16 = make_idesc_f16(kTcRows, Hp);
       constexpr uint32_t lbo = Hp * 16, sbo = 128;
       const bool x1 = (a.flags & HEXGNN_TF32X1) != 0;
       uint32_t it = 0, na = 0;
@@ -171,13 +171,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
         for (int s = 1; s < Lt; ++s) {
           long long tq;
           for (int which = 0; which < 2; ++which) {        // Zl = h W_l^T, then Zr = h W_r^T (same A operand)
-            for (int q = 0; q < NQ; ++q, ++it) {
-              if (which == 0 && (q % kTcSlices) == 0) {
-                // granules [q, q + kTcSlices) of h (k-chunks q .. q+3) are in TMEM; the epilogue releases h quarter by
-                // quarter (and has read Zr of the previous layer before the first quarter), so these MMAs run under the
-                // rest of its phase 3
+            for (int q = 0; q < NQ; ++q, ++it) {           // 16-k chunks = granules 2q, 2q + 1 of h
+              if (which == 0 && (q % 2) == 0) {
+                // granules [2q, 2q + 4) of h are in TMEM; the epilogue releases h quarter by quarter (and has read Zr of the
+                // previous layer before the first quarter), so these MMAs run under the rest of its phase 3
                 tq = PH_NOW();
-                mbar_wait(&bar_a[q / kTcSlices], na & 1);
+                mbar_wait(&bar_a[q / 2], na & 1);
                 PH_ADD(ph5, tq);
                 tc_fence_after();
               }
@@ -194,9 +193,13 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
               tq = PH_NOW();
               tc_fence_after();
               const uint32_t b0 = smem_u32(smem + S::off_ring + st * S::stage_bytes);
-              // (HEXGNN_TF32X1, opt-in inference: the large product alone)
-              if (!x1) mma_f16_ts(tbase + TM_DS, tbase + TM_A16 + q * 8, make_smem_desc(b0 + S::half_bytes, lbo, sbo), idesc16, q != 0);
-              mma_tf32_ts(tbase + TM_D, tbase + TM_HI + q * kTcKF, make_smem_desc(b0, lbo, sbo), idesc, q != 0);
+              const uint64_t bhi = make_smem_desc(b0, lbo, sbo), blo = make_smem_desc(b0 + S::half_bytes, lbo, sbo);
+              const uint32_t alo = tbase + TM_A + q * 16, ahi = alo + 8;
+              if (!x1) {   // (HEXGNN_TF32X1, opt-in inference: the large product alone)
+                mma_f16_ts(tbase + TM_DS, alo, bhi, idesc16, q != 0);
+                mma_f16_ts(tbase + TM_DS, ahi, blo, idesc16, true);
+              }
+              mma_f16_ts(tbase + TM_D, ahi, bhi, idesc16, q != 0);
               mma_commit(&bar_empty[st]);   // stage free once these MMAs have read it
               PH_ADD(ph7, tq);
             }
@@ -220,22 +223,18 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
     const float* Pm = a.params;
     const bool x1e = (a.flags & HEXGNN_TF32X1) != 0;   // single-pass inference: Ds is not written
     int range_bad = 0;
-    // one 8-channel granule (= one k-chunk) of the next A operand: tf32 hi columns + the fp16 pair columns [2^11 lo | hi]
+    // one 8-channel granule of the next A operand: fp16 hi and 2^11-scaled lo halves, 4 packed columns each, into the
+    // granule's half of its 16-k chunk ([lo(2q) lo(2q+1) | hi(2q) hi(2q+1)])
     auto store_A = [&](int g, const float (&v)[8]) {
-      float hi[8], lo[8];
-      uint32_t pk[8];
-#pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        split_tf32(v[u], hi[u], lo[u]);
-        if (v[u] >= 60000.f) range_bad = 1;              // (activations are ReLU outputs: >= 0)
-      }
+      uint32_t hi4[4], lo4[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        pk[j] = pack_f16x2(lo[2 * j] * 2048.0f, lo[2 * j + 1] * 2048.0f);    // k' = 2j, 2j + 1
-        pk[4 + j] = pack_f16x2(hi[2 * j], hi[2 * j + 1]);                    // k' = 8 + 2j, 8 + 2j + 1
+        split_f16x2(v[2 * j], v[2 * j + 1], hi4[j], lo4[j]);
+        if (v[2 * j] >= 60000.f || v[2 * j + 1] >= 60000.f) range_bad = 1;     // (activations are ReLU outputs: >= 0)
       }
-      tmem_st8(trow + TM_HI + g * 8, hi);
-      tmem_st8u(trow + TM_A16 + g * 8, pk);
+      const uint32_t c = trow + TM_A + (g >> 1) * 16 + (g & 1) * 4;
+      tmem_st4u(c, lo4);
+      tmem_st4u(c + 8, hi4);
     };
     uint32_t nd = 0;
     for (int rnd = 0; rnd * (int)gridDim.x < ntiles; ++rnd) {

@@ -33,23 +33,25 @@ constexpr int kTcEpiThreads = kTcEpiWarps * 32;
 constexpr int kTcThreads = kTcEpiThreads + 64;  // + producer warp + MMA warp
 
 // Weight images for the forward, one per SAGE layer s = 1..Lt-1 of the taken head:
-//   img[s-1][which][q8][part][...]  which 0 = lin_l, 1 = lin_r; q8 = 8-wide k chunk (Hp/8 of them); one (which, q8) = one ring
-//   stage = one contiguous bulk copy = the operands of one (fp16 MMA, tf32 MMA) pair, see "mixed 3-product scheme" below.
-//   part 0 (Hp*32 bytes): tf32 hi of W, K-major SWIZZLE_NONE canonical B operand, B[c][k], c in [0,Hp) the out channel,
-//          k in [8 q8, 8 q8 + 8):  byte = ((k%8)/4) * (Hp*16) + (c/8)*128 + (c%8)*16 + (k%4)*4
-//   part 1 (Hp*32 bytes): fp16 operand of the two SMALL products, K = 16: k' in [0,8) = hi(W[c][8 q8 + k']),
-//          k' in [8,16) = 2^11 lo(W[c][8 q8 + k' - 8]):  byte = (k'/8) * (Hp*16) + (c/8)*128 + (c%8)*16 + (k'%8)*2
+//   img[s-1][which][p][part][...]  which 0 = lin_l, 1 = lin_r; p = 16-wide k chunk (Hp/16 of them); one (which, p) = one ring
+//   stage = one contiguous bulk copy = the B operands of one MMA triple of the all-fp16 3-product scheme below
+//   part 0 (Hp*32 bytes) = hi halves, part 1 (Hp*32 bytes) = 2^11-scaled lo halves of W[c][16 p + kk], both fp16, each a
+//   K-major SWIZZLE_NONE canonical B operand B[c][kk], c in [0,Hp) the out channel, kk in [0,16):
+//          byte = (kk/8) * (Hp*16) + (c/8)*128 + (c%8)*16 + (kk%8)*2
 // A layer is two N = Hp GEMMs on the same A operand (Zl first; Zr runs under the CSR gather of Zl), see sage_fwd_tc.cu.
 //
-// Mixed 3-product scheme of the forward.  a*b ~= hi_a*hi_b + (lo_a*hi_b + hi_a*lo_b) as before (every factor an exact
-// 11-bit-mantissa value), but the two small products of a k-chunk are ONE kind::f16 MMA with K = 16:
-//     A16 = [2^11 lo_a (8 values) | hi_a (8 values)],  B16 = [hi_b ; 2^11 lo_b]   ->  Ds += 2^11 (lo_a*hi_b + hi_a*lo_b)
-// (tf32 and fp16 both carry 11 significant bits, so hi_a, hi_b, 2^11 lo_a, 2^11 lo_b convert EXACTLY while they stay inside
-// the fp16 range: |activation|, |weight| < 65504; the 2^11 keeps the lo parts away from fp16's subnormals), accumulated in
-// its own TMEM accumulator Ds, and the large product stays a kind::tf32 MMA into D.  Z = D + 2^-11 Ds in the epilogue (fp32,
-// round to nearest).  Two MMAs per k-chunk instead of three, and only the Hp/8 large products truncate the large sum (the
-// tensor core truncates its fp32 accumulator after every MMA).  Activations beyond the fp16 range set HEXGNN_ST_FP16_RANGE.
-constexpr int kTcKF = 8;              // k values per forward ring stage (one MMA k-step)
+// All-fp16 3-product scheme of the forward.  a*b ~= hi_a*hi_b + (lo_a*hi_b + hi_a*lo_b) with 11-bit-mantissa factors, as in
+// 3xTF32 -- but fp16 carries the same 11 significant bits as tf32 at half the bytes and twice the k per MMA (K = 16):
+//     hi = fp16(x),  lo = fp16(2^11 (x - hi))        (x = hi + 2^-11 lo to 2^-22 |x|; the 2^11 keeps lo out of the subnormals)
+//     D  += hi_a * hi_b                               one kind::f16 MMA per 16 k-values (every product exact in fp32)
+//     Ds += lo_a * hi_b;  Ds += hi_a * lo_b           two more, into their OWN accumulator
+//     Z = D + 2^-11 Ds                                 in the epilogue, fp32 round-to-nearest
+// Against 3xTF32: half the weight bytes through the ring (the L2 -> shared stream bounds the GEMM phases), half the
+// shared-memory operand reads, and only the Hp/16 large products truncate the large sum (the tensor core truncates its fp32
+// accumulator after every MMA).  Exact while |activation|, |weight| < 65504 (fp16 range; below 6e-5 the error is ~1e-11
+// absolute instead of relative); activations beyond it set HEXGNN_ST_FP16_RANGE.  The backward keeps 3xTF32: its operands
+// (loss gradients, ~1e-6) sit outside fp16's range.
+constexpr int kTcKF = 16;             // k values per forward ring stage (one fp16 MMA k-step)
 struct TcPackView {
   float* wimg;    // forward images   (Lt-1) * Hp * 2Hp * 2 floats
   float* wimgT;   // backward images  (same size), layout above tc_imgB_floats

@@ -202,6 +202,19 @@ __device__ __forceinline__ uint32_t pack_f16x2(float a, float b) {
   asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(b), "f"(a));
   return d;
 }
+__device__ __forceinline__ void tmem_st4u(uint32_t taddr, const uint32_t (&v)[4]) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1,%2,%3,%4};"
+               ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]) : "memory");
+}
+// fp16 split of the all-fp16 3-product scheme (sage_tc.cuh): hi = fp16(a), lo = fp16(2^11 (a - hi)); returned packed in pairs
+// (element 0 in the low half).  a = hi + 2^-11 lo to ~2^-22 |a| (and to ~1e-11 absolute below fp16's normal range).
+__device__ __forceinline__ void split_f16x2(float a0, float a1, uint32_t& hi2, uint32_t& lo2) {
+  asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(hi2) : "f"(a1), "f"(a0));
+  float h0, h1;
+  asm("{\n\t.reg .b16 l, h;\n\tmov.b32 {l, h}, %2;\n\tcvt.f32.f16 %0, l;\n\tcvt.f32.f16 %1, h;\n\t}" : "=f"(h0), "=f"(h1) : "r"(hi2));
+  const float r0 = (a0 - h0) * 2048.0f, r1 = (a1 - h1) * 2048.0f;
+  asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(lo2) : "f"(r1), "f"(r0));
+}
 __device__ __forceinline__ void tmem_st8u(uint32_t taddr, const uint32_t (&v)[8]) {
   asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
                ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])

@@ -17,14 +17,12 @@ CASES = {
     "S_noisy": (35, 10, 2, True, "pos_7x7_seed1234.npz"),
 }
 TOL = 1e-5   # BASELINE.json north_star: 1e-5 relative (fp32) on Q-values and gradients
-# Whole-gradient bound on these golden cases.  Their weights (gain 1.5 / 1.7) keep a 12..17-layer ReLU stack well away from
-# the contracting regime of the default init, so every rounding difference is carried through all layers: the reference's own
-# fp32 run is 0.7 .. 1.7e-6 from its fp64 run, the 3xTF32 tensor-core path 1e-6 .. 2.9e-5 (tools/pin_report.py, recorded in
-# profiles/precision_r2.md).  What is left above 1e-5 is the forward kernel's accumulator: tcgen05 truncates its fp32
-# accumulator after each of the 3 x Hp / 8 MMAs of a layer; the backward chain keeps the small products in a second
-# accumulator (a third of the truncations), the forward has no tensor memory left for one.  The default-init
-# cases of test_gpu_parity.py hold 1e-5 on the whole gradient; `path="simt"` (fp32 FFMA) holds it everywhere.
-GRAD_TOL = 3e-5
+# Whole-gradient bound on these golden cases: the same 1e-5.  (Their weights -- gain 1.5 / 1.7 -- keep a 12..17-layer ReLU
+# stack away from the contracting regime of the default init, so every rounding difference is carried through all layers.
+# Achieved, tools/pin_report.py -> profiles/precision_r2.md: 0.7 .. 5.2e-6 against the reference's fp64 run, whose own fp32 run
+# is 0.7 .. 1.7e-6 off.  Before the tensor-core accumulators were split -- large products in one, the 2^-11-sized ones in
+# another, DESIGN.md 4 -- the worst case was 2.9e-5.)
+GRAD_TOL = TOL
 
 
 def rel(a, b):
