@@ -41,12 +41,14 @@ __global__ void pack_tc_kernel(Dims d, ParamMap pm, const float* __restrict__ pa
     if (with_transpose) {
       // backward: dH[i][k] = sum_c dZ_which[i][c] * W_which[c][k]  =>  B[n = k][kk = c], which 0 = lin_r, 1 = lin_l
       const int which = n < Hp ? 1 : 0;
-      const int64_t halfB = (int64_t)kTcKC * Hp;                  // floats per half of a (which, q) stage
+      // stage (which, q) = [fp16 hi | fp16 2^11 lo] of B[n = k][kk = c in 16-chunk q], K-major SWIZZLE_NONE:
+      //   byte = (kk/8) * (Hp*16) + (k/8)*128 + (k%8)*16 + (kk%8)*2          (all-fp16 3-product scheme, sage_tc.cuh)
       const int q = c / kTcKC, cq = c % kTcKC;
-      const int64_t off = (((int64_t)(s - 1) * 2 + which) * NQ + q) * 2 * halfB + (int64_t)(cq / 4) * (Hp * 4) +
-                          (k / 8) * 32 + (k % 8) * 4 + (cq % 4);
-      pv.wimgT[off] = hi;
-      pv.wimgT[off + halfB] = lo;
+      char* stage = (char*)pv.wimgT + ((((int64_t)(s - 1) * 2 + which) * NQ + q) * (int64_t)(Hp * 64));
+      const int64_t off = (int64_t)(cq / 8) * (Hp * 16) + (int64_t)(k / 8) * 128 + (k % 8) * 16 + (cq % 8) * 2;
+      const __half h16 = __float2half_rn(val);
+      *(__half*)(stage + off) = h16;
+      *(__half*)(stage + Hp * 32 + off) = __float2half_rn((val - __half2float(h16)) * 2048.0f);
     }
   }
   const int nb = d.Lt * Hp;

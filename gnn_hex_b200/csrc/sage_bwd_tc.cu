@@ -21,7 +21,7 @@
 namespace hexgnn {
 using namespace tc;
 
-constexpr int kBwdStages = 5;
+constexpr int kBwdStages = 8;
 
 struct BwdTcArgs {
   Dims d;
@@ -51,7 +51,7 @@ struct BwdTcSmem {
   static constexpr int Hp = 16 * NJ;
   static constexpr int P = Hp + 4;
   static constexpr int ECAP = kEdgeCapPerRow * kTcRows;
-  static constexpr int half_bytes = kTcKC * Hp * 4;
+  static constexpr int half_bytes = kTcKC * Hp * 2;      // fp16 hi | fp16 2^11 lo part of a (which, 16-c chunk) stage
   static constexpr int stage_bytes = 2 * half_bytes;
   static constexpr int off_ring = 0;
   static constexpr int off_dump = off_ring + kBwdStages * stage_bytes;           // float [128][P]
@@ -63,8 +63,8 @@ struct BwdTcSmem {
   static constexpr int off_part = off_agg;                                       // float [4][6][Hp] row-part partials
                                                                                  // (head / layer 0 only: aliases agg)
   static constexpr int off_acc = off_arg + 2 * Hp * 4;                           // float [8*Hp + 16] CTA accumulators
-  static constexpr int off_misc = off_acc + (8 * Hp + 16) * 4;                   // float [16]
-  static constexpr int off_rowptr = off_misc + 64;                               // int [128+4]
+  static constexpr int off_misc = off_acc + (8 * Hp + 16) * 4;                   // float [64]: [0..3] scalars, [4..36) per-warp max |dpre| of the last two layers
+  static constexpr int off_rowptr = off_misc + 256;                              // int [128+4]
   static constexpr int off_gp = off_rowptr + (kTcRows + 4) * 4;                  // int [64+4]
   static constexpr int off_col = off_gp + (kMaxTileGraphs + 4) * 4;              // u16 [ECAP]
   static constexpr int off_gtab = (off_col + ECAP * 2 + 15) & ~15;               // gather table (sage_tc.cuh)
@@ -104,12 +104,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
   constexpr int NQ = Hp / kTcKC;
   constexpr int MAXG = (NG + kTcSlices - 1) / kTcSlices;
   constexpr int NV = Hp / 4, PV = P / 4;
-  // TMEM columns: A hi | A lo | D (the hi * hi products) | Ds (the lo * hi and hi * lo products).  The tensor core's fp32
-  // accumulator TRUNCATES after every MMA, a bias of ~2^-25 of the running sum per accumulation; the small products live in
-  // their own accumulator so that only the 2 x Hp / 8 large ones truncate the large sum (a third of the accumulations), and
-  // the epilogue adds the two in round-to-nearest fp32.
-  constexpr uint32_t TM_HI = 0, TM_LO = Hp, TM_D = 2 * Hp, TM_DS = 3 * Hp;
-  constexpr uint32_t TM_COLS = (4 * Hp <= 64) ? 64 : (4 * Hp <= 128) ? 128 : (4 * Hp <= 256) ? 256 : 512;
+  // TMEM columns: A (fp16 pairs; per 16-c chunk 8 columns of 2^11 lo, then 8 columns of hi) | D | Ds: the all-fp16 3-product
+  // scheme of sage_tc.cuh -- D takes the large products, Ds the 2^11-scaled small ones (the tensor core TRUNCATES its fp32
+  // accumulator after every MMA; only the 2 x Hp / 16 large products truncate the large sum), dH = D + 2^-11 Ds.
+  // Loss gradients are ~1e-6 .. 1e-3, far below fp16's normal range, so the A operand of a (tile, layer) is scaled by a power of
+  // two 2^S chosen from the tile's max |dpre| (to ~2^9: dZl, a sum over neighbours, has 2^6 head-room to fp16's 65504) and dH is
+  // scaled back by 2^-S when it is read: exact, local to the two GEMMs, every other quantity stays as it was.
+  constexpr uint32_t TM_A = 0, TM_D = Hp, TM_DS = 2 * Hp;
+  constexpr uint32_t TM_COLS = (3 * Hp <= 64) ? 64 : (3 * Hp <= 128) ? 128 : (3 * Hp <= 256) ? 256 : 512;
   extern __shared__ __align__(128) uint8_t smem[];
   float* dump = (float*)(smem + S::off_dump);
   float* agg = (float*)(smem + S::off_agg);
@@ -180,7 +182,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
   } else if (wid == kTcEpiWarps + 1) {
     // ================= MMA issuer =================
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_tf32(kTcRows, Hp, false);
+      constexpr uint32_t idesc16 = make_idesc_f16(kTcRows, Hp);
       constexpr uint32_t lbo = Hp * 16, sbo = 128;
       uint32_t it = 0, na = 0;
       for (int rnd = 0; rnd * (int)gridDim.x < ntiles; ++rnd) {
@@ -200,17 +202,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
               const int st = it % kBwdStages;
               mbar_wait(&bar_full[st], (it / kBwdStages) & 1);
               tc_fence_after();
-              const uint32_t bhi = smem_u32(smem + S::off_ring + st * S::stage_bytes);
-              const uint32_t blo = bhi + S::half_bytes;
-#pragma unroll
-              for (int kk = 0; kk < kTcKC / 8; ++kk) {
-                const uint64_t dhi = make_smem_desc(bhi + kk * 2 * lbo, lbo, sbo);
-                const uint64_t dlo = make_smem_desc(blo + kk * 2 * lbo, lbo, sbo);
-                const uint32_t kcol = q * kTcKC + kk * 8;
-                mma_tf32_ts(tbase + TM_DS, tbase + TM_LO + kcol, dhi, idesc, (which | q | kk) != 0);
-                mma_tf32_ts(tbase + TM_DS, tbase + TM_HI + kcol, dlo, idesc, true);
-                mma_tf32_ts(tbase + TM_D, tbase + TM_HI + kcol, dhi, idesc, (which | q | kk) != 0);
-              }
+              const uint32_t b0 = smem_u32(smem + S::off_ring + st * S::stage_bytes);
+              const uint64_t bhi = make_smem_desc(b0, lbo, sbo), blo = make_smem_desc(b0 + S::half_bytes, lbo, sbo);
+              const uint32_t alo = tbase + TM_A + q * 16, ahi = alo + 8;
+              mma_f16_ts(tbase + TM_DS, alo, bhi, idesc16, (which | q) != 0);
+              mma_f16_ts(tbase + TM_DS, ahi, blo, idesc16, true);
+              mma_f16_ts(tbase + TM_D, ahi, bhi, idesc16, (which | q) != 0);
               mma_commit(&bar_empty[st]);
             }
             mma_commit(which == 0 ? bar_r : bar_d);
@@ -256,6 +253,45 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
     const int hrec_n = tc_head_rec_floats(a.d), H2p = (H2 + 3) & ~3;
     const int part = tid >> 7, pc = tid & 127;      // row quarter / channel of the column-parallel loops
     uint32_t nr = 0, nd = 0;
+    int range_bad = 0;
+    float unscale = 1.f;                    // 2^-S of the scale the A operands of the GEMMs behind the current D / Ds carried
+    // one 8-channel granule of the A operand, scaled by sc = 2^S: fp16 hi and 2^11-scaled lo halves, 4 packed columns each, into
+    // the granule's half of its 16-c chunk ([lo(2q) lo(2q+1) | hi(2q) hi(2q+1)])
+    auto store_A = [&](int g, const float (&v)[8], float sc) {
+      uint32_t hi4[4], lo4[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float v0 = v[2 * j] * sc, v1 = v[2 * j + 1] * sc;
+        split_f16x2(v0, v1, hi4[j], lo4[j]);
+        if (fabsf(v0) >= 60000.f || fabsf(v1) >= 60000.f) range_bad = 1;
+      }
+      const uint32_t c = trow + TM_A + (g >> 1) * 16 + (g & 1) * 4;
+      tmem_st4u(c, lo4);
+      tmem_st4u(c + 8, hi4);
+    };
+    // dH of this thread's granules = (D + 2^-11 Ds) * unscale
+    auto load_dH = [&](float (&dh)[MAXG][8]) {
+#pragma unroll
+      for (int gi = 0; gi < MAXG; ++gi) {
+        const int g = slice + gi * kTcSlices;
+        if (g < NG) tmem_ld8(trow + TM_D + g * 8, dh[gi]);
+      }
+      tmem_wait_ld();
+      const float us = unscale, uss = unscale * (1.0f / 2048.0f);
+#pragma unroll
+      for (int gi = 0; gi < MAXG; gi += 2) {       // + the small-product accumulator, two granules per round trip
+        float d0[8], d1[8];
+        const int g0_ = slice + gi * kTcSlices, g1_ = slice + (gi + 1) * kTcSlices;
+        if (g0_ < NG) tmem_ld8(trow + TM_DS + g0_ * 8, d0);
+        if (gi + 1 < MAXG && g1_ < NG) tmem_ld8(trow + TM_DS + g1_ * 8, d1);
+        tmem_wait_ld();
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          if (g0_ < NG) dh[gi][u] = fmaf(d0[u], uss, dh[gi][u] * us);
+          if (gi + 1 < MAXG && g1_ < NG) dh[gi + 1][u] = fmaf(d1[u], uss, dh[gi + 1][u] * us);
+        }
+      }
+    };
     for (int rnd = 0; rnd * (int)gridDim.x < ntiles; ++rnd) {
       const int ti = tile_position(rnd, blockIdx.x, gridDim.x, a.td.fwd_flag == nullptr);
       if (ti >= ntiles) continue;
@@ -510,27 +546,17 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
           tc_fence_after();
           PH_ADD(ph0, tq);
           tq = PH_NOW();
-#pragma unroll
-          for (int gi = 0; gi < MAXG; ++gi) {
-            const int g = slice + gi * kTcSlices;
-            if (g < NG) tmem_ld8(trow + TM_D + g * 8, dh[gi]);
-          }
-          tmem_wait_ld();
-#pragma unroll
-          for (int gi = 0; gi < MAXG; ++gi) {       // + the small-product accumulator (round-to-nearest fp32 add)
-            const int g = slice + gi * kTcSlices;
-            if (g < NG) {
-              float ds[8];
-              tmem_ld8(trow + TM_DS + g * 8, ds);
-              tmem_wait_ld();
-#pragma unroll
-              for (int u = 0; u < 8; ++u) dh[gi][u] += ds[u];
-            }
-          }
+          load_dH(dh);
         }
-        // E1: ReLU mask, dpre -> TMEM (A of dpre*W_r), dump (pre-scaled by 1/deg for the gather), dZ stash
+        // E1: ReLU mask, dpre -> TMEM (A of dpre*W_r), dump (pre-scaled by 1/deg for the gather), dZ stash.  The power-of-two
+        // scale 2^S of this layer's two GEMMs puts the tile's max |dpre| near 2^6: measured exactly for the first layer (one
+        // extra barrier per tile), afterwards taken from the PREVIOUS layer's max (published by every warp, read a layer
+        // later: no barrier) -- fp16 leaves 2^10 of head-room above 2^6, i.e. the gradient of a tile may grow 2^4 from one
+        // layer to the next AND dZl (a sum over neighbours) may be 2^6 larger than dpre before anything is flagged.
+        float ascale;
         {
           char* zimg = dz_t + (size_t)(s - 1) * a.B * dz_img;
+          float mx = 0.f;
 #pragma unroll
           for (int gi = 0; gi < MAXG; ++gi) {
             const int g = slice + gi * kTcSlices;
@@ -540,19 +566,35 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
                 de[0] = make_float4(dh[gi][0], dh[gi][1], dh[gi][2], dh[gi][3]);
                 de[1] = make_float4(dh[gi][4], dh[gi][5], dh[gi][6], dh[gi][7]);
               }
-              float hi[8], lo[8], sc[8];
 #pragma unroll
               for (int u = 0; u < 8; ++u) {
                 const float r = ((mw >> (gi * 8 + u)) & 1u) ? dh[gi][u] : 0.f;
                 dh[gi][u] = r;
-                sc[u] = r * inv;
-                split_tf32(r, hi[u], lo[u]);
+                mx = fmaxf(mx, fabsf(r));
               }
-              tmem_st8(trow + TM_HI + g * 8, hi);
-              tmem_st8(trow + TM_LO + g * 8, lo);
+            }
+          }
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+          float* mxbuf = misc + 4 + 16 * (s & 1);       // this layer's per-warp maxima; the other half holds the previous layer's
+          if (lane == 0) mxbuf[wid] = mx;
+          if (first) epi_bar_b();                       // first layer of the tile: its own maximum
+          mx = (first ? mxbuf : misc + 4 + 16 * ((s + 1) & 1))[lane & 15];
+#pragma unroll
+          for (int o = 8; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+          // 2^S with max * 2^S in [2^6, 2^7); a tile without gradient (or a non-finite one) keeps S = 0
+          int e = (int)((__float_as_uint(mx) >> 23) & 0xffu);
+          if (e < 10 || e == 255) e = 127 + 6;
+          ascale = __uint_as_float((uint32_t)(127 + 6 + 127 - e) << 23);
+          unscale = __uint_as_float((uint32_t)(e - 6) << 23);
+#pragma unroll
+          for (int gi = 0; gi < MAXG; ++gi) {
+            const int g = slice + gi * kTcSlices;
+            if (g < NG) {
+              store_A(g, dh[gi], ascale);
               float4* dd = (float4*)(dump + row * P + g * 8);
-              dd[0] = make_float4(sc[0], sc[1], sc[2], sc[3]);
-              dd[1] = make_float4(sc[4], sc[5], sc[6], sc[7]);
+              dd[0] = make_float4(dh[gi][0] * inv, dh[gi][1] * inv, dh[gi][2] * inv, dh[gi][3] * inv);
+              dd[1] = make_float4(dh[gi][4] * inv, dh[gi][5] * inv, dh[gi][6] * inv, dh[gi][7] * inv);
               if (row < n32) {
                 st_global_v8(zimg + rm32_granule_off(NG + g, row), dh[gi][0], dh[gi][1], dh[gi][2], dh[gi][3], dh[gi][4],
                              dh[gi][5], dh[gi][6], dh[gi][7]);
@@ -595,13 +637,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
 #pragma unroll
           for (int gi = 0; gi < MAXG; ++gi) {
             const int g = slice + gi * kTcSlices;
-            if (g < NG) {
-              float hi[8], lo[8];
-#pragma unroll
-              for (int u = 0; u < 8; ++u) split_tf32(acc[gi][u], hi[u], lo[u]);
-              tmem_st8(trow + TM_HI + g * 8, hi);
-              tmem_st8(trow + TM_LO + g * 8, lo);
-            }
+            if (g < NG) store_A(g, acc[gi], ascale);
             tmem_wait_st();
             tc_fence_before();
             __syncwarp();
@@ -630,23 +666,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
           mbar_wait(bar_d, nd & 1);
           ++nd;
           tc_fence_after();
-#pragma unroll
-          for (int gi = 0; gi < MAXG; ++gi) {
-            const int g = slice + gi * kTcSlices;
-            if (g < NG) tmem_ld8(trow + TM_D + g * 8, dh[gi]);
-          }
-          tmem_wait_ld();
-#pragma unroll
-          for (int gi = 0; gi < MAXG; ++gi) {
-            const int g = slice + gi * kTcSlices;
-            if (g < NG) {
-              float ds[8];
-              tmem_ld8(trow + TM_DS + g * 8, ds);
-              tmem_wait_ld();
-#pragma unroll
-              for (int u = 0; u < 8; ++u) dh[gi][u] += ds[u];
-            }
-          }
+          load_dH(dh);
         }
 #pragma unroll
         for (int gi = 0; gi < MAXG; ++gi) {
@@ -720,6 +740,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
         }
       }
       PH_ADD(ph5, tq);
+      if (range_bad) { atomicOr(a.csr.status, HEXGNN_ST_FP16_RANGE); range_bad = 0; }
       // ---- hand the tile to the dW GEMM: all dZ stores of all epilogue threads, then one release ----------------------
       fence_proxy_async_global();          // the consumer reads with bulk copies (async proxy)
       epi_bar_b();
