@@ -740,7 +740,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_bwd_tc_kernel(const __grid
         }
       }
       PH_ADD(ph5, tq);
-      if (range_bad) { atomicOr(a.csr.status, HEXGNN_ST_FP16_RANGE); range_bad = 0; }
+      // an operand outside fp16's range (a gradient that grew > 2^10 between two layers): flag the batch and poison the
+      // tile's record, like a tile that does not fit -- the fused optimizer skips a step whose gradient is not finite
+      if (range_bad) { atomicOr(a.csr.status, HEXGNN_ST_FP16_RANGE); accs[A_GB0] = __int_as_float(0x7fc00000); range_bad = 0; }
       // ---- hand the tile to the dW GEMM: all dZ stores of all epilogue threads, then one release ----------------------
       fence_proxy_async_global();          // the consumer reads with bulk copies (async proxy)
       epi_bar_b();

@@ -258,6 +258,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
       // ---- tile CSR + features -> shared ------------------------------------------------------------
       {
         int bad = 0;
+        if (tid == 0) ((int*)misc)[8] = 0;      // "an activation left the fp16 range" flag of this tile
         for (int i = tid; i <= kTcRows; i += kTcEpiThreads) rowptr_s[i] = (i <= n ? a.csr.rowptr[r0 + i] : a.csr.rowptr[r0 + n]) - td.e0;
         for (int g = tid; g <= g1 - g0; g += kTcEpiThreads) gp_s[g] = a.csr.gptr[g0 + g] - r0;
         for (int e = tid; e < td.ne; e += kTcEpiThreads) {
@@ -471,10 +472,13 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
         tmem_wait_st();
         PH_ADD(ph11, tq);
       }
-      if (range_bad) { atomicOr(a.csr.status, HEXGNN_ST_FP16_RANGE); range_bad = 0; }
+      // an activation outside fp16's range: the products of this tile were not exact -- flag it and poison its outputs (NaN,
+      // like a tile that does not fit), so that neither an arg-max nor an optimizer step is taken from them
+      if (range_bad) { atomicOr(a.csr.status, HEXGNN_ST_FP16_RANGE); atomicOr((int*)misc + 8, 1); range_bad = 0; }
       tq = PH_NOW();
       // ---- final activations -> shared (row major) for the head ----------------------------------------------------
       epi_bar();   // every gather of the last layer has finished reading the dump
+      const bool poisoned = ((volatile int*)misc)[8] != 0;
       for (int g = slice; g < NG; g += kTcSlices) {
         float v[8];
         tmem_ld8(trow + TM_D + g * 8, v);
@@ -515,7 +519,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
         epi_bar();
       }
       if (a.flags & HEXGNN_ADV_ONLY) {
-        for (int i = tid; i < n; i += kTcEpiThreads) a.out_nodes[r0 + i] = adv_s[i];
+        for (int i = tid; i < n; i += kTcEpiThreads) a.out_nodes[r0 + i] = poisoned ? __int_as_float(0x7fc00000) : adv_s[i];
         PH_ADD(ph4, tq);
         continue;
       }
@@ -592,11 +596,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) sage_fwd_tc_kernel(const __grid
         epi_bar();
         const float val = misc[0], amean = misc[1];
         if (a.flags & HEXGNN_SEPARATE) {
-          for (int i = rs + tid; i < re; i += kTcEpiThreads) a.out_nodes[r0 + i] = adv_s[i] - amean;
+          for (int i = rs + tid; i < re; i += kTcEpiThreads) a.out_nodes[r0 + i] = poisoned ? __int_as_float(0x7fc00000) : adv_s[i] - amean;
         } else {
-          for (int i = rs + tid; i < re; i += kTcEpiThreads) a.out_nodes[r0 + i] = val + (adv_s[i] - amean);
+          for (int i = rs + tid; i < re; i += kTcEpiThreads) a.out_nodes[r0 + i] = poisoned ? __int_as_float(0x7fc00000) : val + (adv_s[i] - amean);
         }
-        if (tid == 0 && a.out_value) a.out_value[g0 + g] = val;
+        if (tid == 0 && a.out_value) a.out_value[g0 + g] = poisoned ? __int_as_float(0x7fc00000) : val;
         epi_bar();
       }
       PH_ADD(ph4, tq);

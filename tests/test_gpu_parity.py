@@ -863,3 +863,55 @@ def test_tf32x1_inference_mode_is_opt_in_and_bounded():
                                    csr.B, C.c_void_p(csr.blob.data_ptr()), 128, ops.HEXGNN_TF32X1, C.c_void_p(out.data_ptr()),
                                    None, C.c_void_p(stash.data_ptr()), C.c_void_p(ws.data_ptr()), ws.numel() * 4, None)
     assert rc == -1 and b"TF32X1" in _lib.lib().hexgnn_last_error()
+
+
+def test_fp16_range_guard_poisons_and_flags():
+    """The forward's tensor-core products are exact fp16 x fp16 (all-fp16 3-product scheme, csrc/sage_tc.cuh) while the
+    activations stay below 65504.  Beyond that the tile is flagged (status bit 16) and its outputs are NaN -- never a
+    silently wrong Q."""
+    cfg = CONFIGS["S"]
+    o, m = make_pair(cfg["hidden"], cfg["layers"])
+    with torch.no_grad():
+        m.gnn.convs[0].lin_r.weight.mul_(3e5)          # layer-0 output ~1e5 .. 1e6 for the degree feature
+    m = m.to(DEV)
+    b = _batch(cfg, "play", 1, 8)
+    d = b.to(DEV)
+    with torch.no_grad():
+        q = m(d.x, d.edge_index, d.batch, d.ptr)
+    assert int(m.last_csr.status.item()) & _lib.ST_FP16_RANGE
+    assert torch.isnan(q).all()
+    m.strict = True
+    with pytest.raises(_lib.HexGnnError, match="fp16 range"):
+        with torch.no_grad():
+            m(d.x, d.edge_index, d.batch, d.ptr)
+
+
+def test_fused_adam_skips_a_non_finite_step():
+    """one NaN gradient (an oversize graph's poisoned record) must not reach the parameters: the fused optimizer
+    leaves parameters, moments and step counters untouched and reports the non-finite norm."""
+    from gnn_hex_b200 import FusedAdam
+    cfg = CONFIGS["S"]
+    o, m = make_pair(cfg["hidden"], cfg["layers"])
+    m = m.to(DEV)
+    b = _batch(cfg, "play", 1, 16)
+    d = b.to(DEV)
+    action, target, weight = [t.to(DEV) for t in loss_inputs(b)]
+    opt = FusedAdam(m, lr=1e-3, max_grad_norm=10.0)
+    m.train_step(d.x, d.edge_index, d.batch, d.ptr, action=action, target=target, weight=weight)
+    opt.step(d.x)                                      # a regular step: counters (1, 1, 0, taken = 1)
+    p0, m0, v0, s0 = m.flat_parameters.clone(), opt.exp_avg.clone(), opt.exp_avg_sq.clone(), opt.state.clone()
+    m.zero_grad(set_to_none=True)
+    m.train_step(d.x, d.edge_index, d.batch, d.ptr, action=action, target=target, weight=weight)
+    g_before = m.flat_gradient.clone()
+    m.flat_gradient[123] = float("nan")
+    norm = opt.step(d.x)
+    torch.cuda.synchronize()
+    assert not torch.isfinite(norm)
+    assert torch.equal(m.flat_parameters, p0) and torch.equal(opt.exp_avg, m0) and torch.equal(opt.exp_avg_sq, v0)
+    assert torch.equal(opt.state, s0)
+    g_after = m.flat_gradient.clone()
+    g_after[123] = g_before[123]
+    assert torch.equal(g_after, g_before)              # not even the in-place clip touched the gradient
+    m.flat_gradient[123] = g_before[123]
+    assert torch.isfinite(opt.step(d.x))               # the next finite step goes through
+    assert int(opt.state[0]) == int(s0[0]) + 1 and not torch.equal(m.flat_parameters, p0)
