@@ -25,7 +25,7 @@ STATUS_NAMES = {
     ST_FP16_RANGE: "an activation left the fp16 range of the forward kernel's mixed product scheme (|h| >= 60000): use path='simt'",
 }
 
-ABI_VERSION = 7
+ABI_VERSION = 8
 
 
 class HexModelDesc(C.Structure):
@@ -38,6 +38,11 @@ class HexSizes(C.Structure):
                 ("bwd_ws_bytes", C.c_int64), ("hidden_padded", C.c_int64)]
 
 
+class HexLwSizes(C.Structure):
+    _fields_ = [("fwd_ws_bytes", C.c_int64), ("bwd_ws_bytes", C.c_int64), ("stash_bytes", C.c_int64),
+                ("norm_floats", C.c_int64), ("embed_offset_floats", C.c_int64), ("hidden_padded", C.c_int64)]
+
+
 class HexCsrLayout(C.Structure):
     _fields_ = [("status", C.c_int64), ("ntiles", C.c_int64), ("gptr", C.c_int64), ("rowptr", C.c_int64),
                 ("col", C.c_int64), ("tile_g0", C.c_int64), ("scratch", C.c_int64), ("total_words", C.c_int64)]
@@ -47,7 +52,8 @@ EXPORTS = ["hexgnn_abi_version", "hexgnn_last_error", "hexgnn_param_count", "hex
            "hexgnn_sizes", "hexgnn_csr_layout", "hexgnn_build_csr", "hexgnn_forward", "hexgnn_backward",
            "hexgnn_profile_enable", "hexgnn_profile_read", "hexgnn_selftest_mma", "hexgnn_debug_phases", "hexgnn_stash_embed", "hexgnn_td_loss", "hexgnn_train_step", "hexgnn_adam_step", "hexgnn_adam_ws_bytes", "hexgnn_collate", "hexgnn_collate_ws_bytes",
            "hexgnn_mask_argmax", "hexgnn_td_target", "hexgnn_forward_big", "hexgnn_allreduce_p2p",
-           "hexgnn_noisy_compose", "hexgnn_noisy_grads", "hexgnn_backward_dx"]
+           "hexgnn_noisy_compose", "hexgnn_noisy_grads", "hexgnn_backward_dx",
+           "hexgnn_lw_sizes", "hexgnn_forward_lw", "hexgnn_backward_lw"]
 
 _lib = None
 
@@ -117,6 +123,12 @@ def lib():
     l.hexgnn_mask_argmax.argtypes = [p, p, i64, i64, i32, C.c_float, p, p, p]
     l.hexgnn_td_target.restype = C.c_int
     l.hexgnn_td_target.argtypes = [p, p, p, p, C.c_float, i64, i64, p, p]
+    l.hexgnn_lw_sizes.restype = C.c_int
+    l.hexgnn_lw_sizes.argtypes = [D, i64, i64, i64, i32, C.POINTER(HexLwSizes)]
+    l.hexgnn_forward_lw.restype = C.c_int
+    l.hexgnn_forward_lw.argtypes = [D, p, p, p, i64, i64, i64, p, i32, p, p, p, p, sz, p]
+    l.hexgnn_backward_lw.restype = C.c_int
+    l.hexgnn_backward_lw.argtypes = [D, p, p, p, i64, i64, i64, p, i32, p, p, p, p, p, p, p, sz, p]
     l.hexgnn_debug_phases.restype = C.c_int
     l.hexgnn_debug_phases.argtypes = [i32, C.POINTER(i64), i32]
     l.hexgnn_profile_enable.restype = C.c_int
@@ -143,6 +155,12 @@ def make_desc(hidden, num_layers, num_head_layers):
 def sizes(desc, N, E, B, tile_rows):
     s = HexSizes()
     check(lib().hexgnn_sizes(C.byref(desc), N, E, B, tile_rows, C.byref(s)), "hexgnn_sizes")
+    return s
+
+
+def lw_sizes(desc, N, E, B, norm):
+    s = HexLwSizes()
+    check(lib().hexgnn_lw_sizes(C.byref(desc), N, E, B, 1 if norm else 0, C.byref(s)), "hexgnn_lw_sizes")
     return s
 
 

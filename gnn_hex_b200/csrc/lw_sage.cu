@@ -1,0 +1,447 @@
+// Layer-at-a-time tensor-core SAGE layer (see lw.cuh): out = epi([x_i | aggr_i(x)] * [W_self ; W_agg]) for all node rows,
+// 128 rows per CTA.  Math: GN0/torch_script_models.py:52-73 (SAGEConv, mean aggregation, root weight without bias),
+// layer loop GN0/models.py:261-294.
+//
+// CTA = 16 worker warps + 1 control warp.
+//   control lane 0   bulk-copies the layer's whole weight image into shared memory (2Kp/16 stages, one mbarrier each; issued
+//                    BEFORE griddepcontrol.wait: the images do not depend on the previous layer), later issues the MMAs
+//   workers, phase G warp per row: self row + CSR gather of the neighbour rows from global memory (L2), fp32, fixed order
+//                    -> shared staging tile [128][2Kp + 4]
+//   workers, phase A thread = (row, column slice): staging -> fp16 hi / 2^11 lo split -> tcgen05.st into the A operand in TMEM
+//   control          D += hi*hi, Ds += lo*hi + hi*lo per 16-k stage (kind::f16, M = 128, N = Np), commit
+//   workers, phase E thread = (row, slice): tcgen05.ld D, Ds -> D + 2^-11 Ds -> unscale, bias, mask / ReLU -> global rows,
+//                    optional statistics (LayerNorm) and |max| (operand scale of the next backward layer)
+#include "lw.cuh"
+
+namespace hexgnn {
+using namespace tc;
+
+namespace {
+
+__device__ __forceinline__ void work_bar() { asm volatile("bar.sync 1, %0;" ::"n"(kLwWorkThreads) : "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+struct LwSmem {
+  int off_w, off_stage, off_bar, off_red, total;
+  int SP;      // staging row pitch (floats)
+  int nst;     // weight stages
+};
+__host__ __device__ inline LwSmem lw_smem(int Kp, int Np) {
+  LwSmem s;
+  s.nst = 2 * Kp / 16;
+  s.SP = 2 * Kp + 4;
+  s.off_w = 0;
+  s.off_stage = s.nst * Np * 64;
+  s.off_bar = s.off_stage + kLwRows * s.SP * 4;
+  s.off_red = s.off_bar + 16 * 8 + 16;                 // <= 14 stage barriers + bar_a + bar_mma, tmem slot
+  s.total = s.off_red + kLwWorkWarps * 2 * 8;
+  return s;
+}
+
+__global__ void __launch_bounds__(kLwThreads, 1) lw_sage_kernel(const __grid_constant__ LwSageArgs a) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const int Kp = a.Kp, Np = a.Np;
+  const LwSmem L = lw_smem(Kp, Np);
+  float* stage = (float*)(smem + L.off_stage);
+  uint64_t* bar_w = (uint64_t*)(smem + L.off_bar);
+  uint64_t* bar_a = bar_w + 14;
+  uint64_t* bar_mma = bar_w + 15;
+  uint32_t* tmem_slot = (uint32_t*)(bar_w + 16);
+  double* red = (double*)(smem + L.off_red);
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int SP = L.SP, nst = L.nst;
+  const uint32_t TM_A = 0, TM_D = 2 * Kp, TM_DS = 2 * Kp + Np;
+  const uint32_t need = 2 * Kp + 2 * Np;
+  const uint32_t TM_COLS = need <= 32 ? 32 : need <= 64 ? 64 : need <= 128 ? 128 : need <= 256 ? 256 : 512;
+  const int64_t row0 = (int64_t)blockIdx.x * kLwRows;
+
+  if (tid == 0) {
+    for (int i = 0; i < nst; ++i) mbar_init(&bar_w[i], 1);
+    mbar_init(bar_a, kLwWorkWarps);
+    mbar_init(bar_mma, 1);
+    fence_mbar_init();
+  }
+  if (wid == kLwWorkWarps) tmem_alloc(tmem_slot, TM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tbase = *tmem_slot;
+  const int stage_bytes = Np * 64, half_bytes = Np * 32;
+
+  if (wid == kLwWorkWarps) {
+    // ================= control warp =================
+    if (lane == 0) {
+      for (int q = 0; q < nst; ++q) {
+        mbar_expect_tx(&bar_w[q], (uint32_t)stage_bytes);
+        bulk_g2s(smem + L.off_w + q * stage_bytes, a.wimg + (size_t)q * stage_bytes, (uint32_t)stage_bytes, &bar_w[q]);
+      }
+      pdl_wait();                 // (the weight images were packed at least two launches ago: see launch order in lw_model.cu)
+      pdl_launch_dependents();
+      const uint32_t idesc = make_idesc_f16(kLwRows, Np);
+      const uint32_t lbo = (uint32_t)Np * 16u, sbo = 128u;
+      mbar_wait(bar_a, 0);
+      tc_fence_after();
+      for (int q = 0; q < nst; ++q) {
+        mbar_wait(&bar_w[q], 0);
+        tc_fence_after();
+        const uint32_t b0 = smem_u32(smem + L.off_w + q * stage_bytes);
+        const uint64_t bhi = make_smem_desc(b0, lbo, sbo), blo = make_smem_desc(b0 + half_bytes, lbo, sbo);
+        const uint32_t alo = tbase + TM_A + q * 16, ahi = alo + 8;
+        mma_f16_ts(tbase + TM_DS, alo, bhi, idesc, q != 0);
+        mma_f16_ts(tbase + TM_DS, ahi, blo, idesc, true);
+        mma_f16_ts(tbase + TM_D, ahi, bhi, idesc, q != 0);
+      }
+      mma_commit(bar_mma);
+    }
+  } else {
+    // ================= workers =================
+    pdl_wait();
+    // operand scale 2^(6 - floor(log2 max|x|)) for gradient inputs (exact; keeps both fp16 halves inside fp16's range)
+    float ascale = 1.0f, unscale = 1.0f;
+    if (a.in_absmax) {
+      int e = (int)((*a.in_absmax >> 23) & 0xffu);
+      if (e != 0) {
+        e = e < 10 ? 10 : (e > 250 ? 250 : e);
+        ascale = __uint_as_float((uint32_t)(260 - e) << 23);
+        unscale = __uint_as_float((uint32_t)(e - 6) << 23);
+      }
+    }
+    // ---- phase G: [self | aggregated] rows -> staging ----------------------------------------------------
+    const int NV = Kp / 4;
+    for (int r = wid; r < kLwRows; r += kLwWorkWarps) {
+      const int64_t gr = row0 + r;
+      float4 self = make_float4(0.f, 0.f, 0.f, 0.f), acc = self;
+      if (gr < a.N && lane < NV) {
+        const float* xb = a.x + 4 * lane;
+        self = *(const float4*)(xb + gr * a.ldx);
+        const int b = a.rowptr[gr], e = a.rowptr[gr + 1];
+        int p = b;
+        if (!a.adjoint) {
+          for (; p + 4 <= e; p += 4) {
+            const int j0 = a.col[p], j1 = a.col[p + 1], j2 = a.col[p + 2], j3 = a.col[p + 3];
+            const float4 v0 = *(const float4*)(xb + (int64_t)j0 * a.ldx), v1 = *(const float4*)(xb + (int64_t)j1 * a.ldx);
+            const float4 v2 = *(const float4*)(xb + (int64_t)j2 * a.ldx), v3 = *(const float4*)(xb + (int64_t)j3 * a.ldx);
+            acc.x = ((acc.x + v0.x) + v1.x) + v2.x + v3.x; acc.y = ((acc.y + v0.y) + v1.y) + v2.y + v3.y;
+            acc.z = ((acc.z + v0.z) + v1.z) + v2.z + v3.z; acc.w = ((acc.w + v0.w) + v1.w) + v2.w + v3.w;
+          }
+          for (; p < e; ++p) {
+            const float4 v = *(const float4*)(xb + (int64_t)a.col[p] * a.ldx);
+            acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+          }
+          const float dg = a.degf[gr];
+          acc.x /= dg; acc.y /= dg; acc.z /= dg; acc.w /= dg;
+        } else {
+          for (; p < e; ++p) {
+            const int j = a.col[p];
+            const float dj = a.degf[j];
+            const float4 v = *(const float4*)(xb + (int64_t)j * a.ldx);
+            acc.x += v.x / dj; acc.y += v.y / dj; acc.z += v.z / dj; acc.w += v.w / dj;
+          }
+        }
+        if (a.agg_out) *(float4*)(a.agg_out + gr * a.lda + 4 * lane) = acc;
+      }
+      if (lane < NV) {
+        float* sr = stage + r * SP + 4 * lane;
+        *(float4*)sr = make_float4(self.x * ascale, self.y * ascale, self.z * ascale, self.w * ascale);
+        *(float4*)(sr + Kp) = make_float4(acc.x * ascale, acc.y * ascale, acc.z * ascale, acc.w * ascale);
+      }
+    }
+    work_bar();
+    // ---- phase A: staging -> fp16 split -> tensor memory ---------------------------------------------------
+    const int q4 = wid & 3, slice = wid >> 2;
+    const int row = q4 * 32 + lane;
+    const uint32_t trow = tbase + ((uint32_t)(q4 * 32) << 16);
+    int range_bad = 0;
+    for (int g = slice; g < 2 * Kp / 8; g += 4) {
+      const float4 u0 = *(const float4*)(stage + row * SP + 8 * g), u1 = *(const float4*)(stage + row * SP + 8 * g + 4);
+      const float v[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
+      uint32_t hi4[4], lo4[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        split_f16x2(v[2 * j], v[2 * j + 1], hi4[j], lo4[j]);
+        if (fabsf(v[2 * j]) >= 60000.f || fabsf(v[2 * j + 1]) >= 60000.f) range_bad = 1;
+      }
+      const uint32_t c = trow + TM_A + (g >> 1) * 16 + (g & 1) * 4;
+      tmem_st4u(c, lo4);
+      tmem_st4u(c + 8, hi4);
+    }
+    tmem_wait_st();
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(bar_a);
+    if (range_bad && a.status) atomicOr(a.status, HEXGNN_ST_FP16_RANGE);
+    // ---- phase E -------------------------------------------------------------------------------------
+    mbar_wait(bar_mma, 0);
+    tc_fence_after();
+    const int64_t gr = row0 + row;
+    const bool live = gr < a.N;
+    float s1 = 0.f, s2 = 0.f, mx = 0.f;
+    const float poison = (range_bad && a.status) ? __int_as_float(0x7fc00000) : 0.f;
+    for (int g = slice; g < Np / 8; g += 4) {
+      float v[8], vs[8];
+      tmem_ld8(trow + TM_D + 8 * g, v);
+      tmem_ld8(trow + TM_DS + 8 * g, vs);
+      tmem_wait_ld();
+      if (!live) continue;
+      const int c0 = 8 * g;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        float z = (v[u] + vs[u] * (1.0f / 2048.0f)) * unscale;
+        if (a.bias) z += a.bias[c0 + u];
+        if (a.relu) z = fmaxf(z, 0.f);
+        v[u] = z + poison;
+      }
+      if (a.mask_src) {
+        const float4 m0 = *(const float4*)(a.mask_src + gr * a.ldm + c0), m1 = *(const float4*)(a.mask_src + gr * a.ldm + c0 + 4);
+        const float m[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+#pragma unroll
+        for (int u = 0; u < 8; ++u) v[u] = m[u] > 0.f ? v[u] : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        if (c0 + u >= a.Nout) v[u] = 0.f;
+        s1 += v[u]; s2 += v[u] * v[u];
+        mx = fmaxf(mx, fabsf(v[u]));
+      }
+      float* o = a.out + gr * a.ldo + c0;
+      *(float4*)o = make_float4(v[0], v[1], v[2], v[3]);
+      *(float4*)(o + 4) = make_float4(v[4], v[5], v[6], v[7]);
+    }
+    if (a.out_absmax) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+      if (lane == 0 && mx > 0.f) atomicMax(a.out_absmax, __float_as_uint(mx));
+    }
+    if (a.stats) {
+      const double d1 = warp_sum_d((double)s1), d2 = warp_sum_d((double)s2);
+      if (lane == 0) { red[2 * wid] = d1; red[2 * wid + 1] = d2; }
+      work_bar();
+      if (tid == 0) {
+        double t1 = 0.0, t2 = 0.0;
+        for (int w = 0; w < kLwWorkWarps; ++w) { t1 += red[2 * w]; t2 += red[2 * w + 1]; }
+        a.stats[2 * (int64_t)blockIdx.x] = t1;
+        a.stats[2 * (int64_t)blockIdx.x + 1] = t2;
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (wid == kLwWorkWarps) tmem_dealloc(tbase, TM_COLS);
+}
+
+// ---- weight images --------------------------------------------------------------------------------------------
+__global__ void lw_pack_kernel(const __grid_constant__ LwPackArgs a) {
+  const LwPackEntry& e = a.e[blockIdx.y];
+  const int v = (a.x && a.x[2] != 1.0f) ? 1 : 0;
+  const int Kp = e.Kp, Np = e.Np;
+  const int npairs = 2 * Kp * Np / 2;
+  const float* ws = a.params + e.w_self[v];
+  const float* wa = a.params + e.w_agg[v];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < npairs; i += gridDim.x * blockDim.x) {
+    // pair index -> (stage q, kk pair, c): consecutive threads = consecutive c (coalesced 16-byte granules do not matter here)
+    const int c = i % Np, kp = (i / Np) % 8, q = i / (Np * 8);
+    float val[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int kg = 16 * q + 2 * kp + u;
+      const bool self = kg < Kp;
+      const int k = self ? kg : kg - Kp;
+      float w = 0.f;
+      if (c < e.Nn && k < e.K) {
+        const float* src = self ? ws : wa;
+        w = e.transposed ? src[(int64_t)k * e.ld + c] : src[(int64_t)c * e.ld + k];
+      }
+      val[u] = w;
+    }
+    uint32_t hi2, lo2;
+    split_f16x2(val[0], val[1], hi2, lo2);
+    const int kk = 2 * kp;
+    const int64_t byte = (int64_t)q * Np * 64 + (kk / 8) * (Np * 16) + (c / 8) * 128 + (c % 8) * 16 + (kk % 8) * 2;
+    *(uint32_t*)(a.img + e.img_off + byte) = hi2;
+    *(uint32_t*)(a.img + e.img_off + byte + Np * 32) = lo2;
+  }
+  if (blockIdx.x == 0 && e.bias[v] >= 0) {
+    for (int c = threadIdx.x; c < Np; c += blockDim.x) a.bias_out[e.bias_off + c] = c < e.Nn ? a.params[e.bias[v] + c] : 0.f;
+  }
+}
+
+__global__ void lw_prepare_kernel(const int* __restrict__ rowptr, int64_t N, float* __restrict__ degf, unsigned* zero,
+                                  int zero_words) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < N) {
+    const int d = rowptr[i + 1] - rowptr[i];
+    degf[i] = (float)(d > 0 ? d : 1);
+  }
+  if (i < zero_words) zero[i] = 0u;
+}
+
+// ---- first layer ------------------------------------------------------------------------------------------------
+constexpr int kL0Threads = 256, kL0Rows = 64;
+__global__ void __launch_bounds__(kL0Threads) lw_layer0_kernel(const __grid_constant__ LwLayer0Args a) {
+  __shared__ double red[kL0Threads / 32][2];
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int64_t row0 = (int64_t)blockIdx.x * kL0Rows;
+  float s1 = 0.f, s2 = 0.f;
+  for (int r = wid; r < kL0Rows; r += kL0Threads / 32) {
+    const int64_t gr = row0 + r;
+    if (gr >= a.N) break;
+    float self[4] = {0.f, 0.f, 0.f, 0.f}, mean[4] = {0.f, 0.f, 0.f, 0.f};
+    const int b = a.rowptr[gr], e = a.rowptr[gr + 1];
+    for (int k = 0; k < a.Cin; ++k) self[k] = a.x[gr * a.ldx + a.xoff + k];
+    for (int p = b; p < e; ++p) {
+      const int64_t j = a.col[p];
+      for (int k = 0; k < a.Cin; ++k) mean[k] += a.x[j * a.ldx + a.xoff + k];
+    }
+    const float dg = a.degf[gr];
+    for (int k = 0; k < a.Cin; ++k) mean[k] /= dg;
+    for (int c = lane; c < a.Hp; c += 32) {
+      float v = 0.f;
+      if (c < a.H) {
+        v = a.bl[c];
+        for (int k = 0; k < a.Cin; ++k) v = fmaf(a.wl[c * a.Cin + k], mean[k], v);
+        for (int k = 0; k < a.Cin; ++k) v = fmaf(a.wr[c * a.Cin + k], self[k], v);
+        if (a.relu) v = fmaxf(v, 0.f);
+        s1 += v; s2 += v * v;
+      }
+      a.out[gr * a.ldo + c] = v;
+    }
+  }
+  if (a.stats) {
+    const double d1 = warp_sum_d((double)s1), d2 = warp_sum_d((double)s2);
+    if (lane == 0) { red[wid][0] = d1; red[wid][1] = d2; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double t1 = 0.0, t2 = 0.0;
+      for (int w = 0; w < kL0Threads / 32; ++w) { t1 += red[w][0]; t2 += red[w][1]; }
+      a.stats[2 * (int64_t)blockIdx.x] = t1;
+      a.stats[2 * (int64_t)blockIdx.x + 1] = t2;
+    }
+  }
+}
+
+// ---- graph-mode LayerNorm (+ ReLU), element-wise ----------------------------------------------------------------------
+constexpr int kNormThreads = 256, kNormRows = 64;
+__global__ void __launch_bounds__(kNormThreads) lw_norm_kernel(const __grid_constant__ LwNormArgs a) {
+  __shared__ double red[kNormThreads / 32][2];
+  __shared__ float mu_s, sd_s;
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (wid == 0) {   // statistics from the producer's partial sums, fixed order
+    double t1 = 0.0, t2 = 0.0;
+    for (int i = lane; i < a.nparts; i += 32) { t1 += a.stats_in[2 * i]; t2 += a.stats_in[2 * i + 1]; }
+    t1 = warp_sum_d(t1); t2 = warp_sum_d(t2);
+    if (lane == 0) {
+      const double M = (double)a.N * (double)a.H;
+      const double mu = t1 / M;
+      double var = t2 / M - mu * mu;
+      var = var > 0.0 ? var : 0.0;
+      mu_s = (float)mu;
+      sd_s = (float)sqrt(var) + a.eps;
+    }
+  }
+  __syncthreads();
+  const float mu = mu_s, sd = sd_s;
+  const int v = (a.x && a.x[2] != 1.0f) ? 1 : 0;
+  const float* gamma = a.gamma[v];
+  const float* beta = a.beta[v];
+  const int64_t row0 = (int64_t)blockIdx.x * kNormRows;
+  float s1 = 0.f, s2 = 0.f;
+  for (int r = wid; r < kNormRows; r += kNormThreads / 32) {
+    const int64_t gr = row0 + r;
+    if (gr >= a.N) break;
+    for (int c = lane; c < a.Hp; c += 32) {
+      float y = 0.f;
+      if (c < a.H) {
+        y = ((a.in[gr * a.ldi + c] - mu) / sd) * gamma[c] + beta[c];
+        if (a.relu) y = fmaxf(y, 0.f);
+        s1 += y; s2 += y * y;
+      }
+      a.out[gr * a.ldo + c] = y;
+    }
+  }
+  if (a.stats_out) {
+    const double d1 = warp_sum_d((double)s1), d2 = warp_sum_d((double)s2);
+    if (lane == 0) { red[wid][0] = d1; red[wid][1] = d2; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double t1 = 0.0, t2 = 0.0;
+      for (int w = 0; w < kNormThreads / 32; ++w) { t1 += red[w][0]; t2 += red[w][1]; }
+      a.stats_out[2 * (int64_t)blockIdx.x] = t1;
+      a.stats_out[2 * (int64_t)blockIdx.x + 1] = t2;
+    }
+  }
+}
+
+template <typename K, typename A>
+int launch_pdl(K kern, dim3 grid, dim3 block, size_t smem, cudaStream_t st, const A& args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  HEX_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, args));
+  return HEXGNN_OK;
+}
+
+}  // namespace
+
+int launch_lw_sage(const LwSageArgs& a, cudaStream_t st) {
+  if (a.Kp < 16 || a.Kp > kLwMaxK || a.Kp % 16 || a.Np < 16 || a.Np > kLwMaxK || a.Np % 16 || a.ldx % 4 || a.ldo % 4 ||
+      (a.mask_src && a.ldm % 4) || (a.agg_out && a.lda % 4)) {
+    set_error("lw_sage: unsupported shape Kp=%d Np=%d ldx=%d ldo=%d", a.Kp, a.Np, a.ldx, a.ldo);
+    return HEXGNN_E_UNSUPPORTED;
+  }
+  if (a.N <= 0) return HEXGNN_OK;
+  const LwSmem L = lw_smem(a.Kp, a.Np);
+  static int max_set = 0;   // idempotent attribute
+  if (L.total > max_set) {
+    HEX_CUDA_CHECK(cudaFuncSetAttribute(lw_sage_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
+    max_set = 232448;
+  }
+  return launch_pdl(lw_sage_kernel, dim3((unsigned)lw_blocks(a.N)), dim3(kLwThreads), (size_t)L.total, st, a);
+}
+
+int launch_lw_pack(const LwPackArgs& a, cudaStream_t st) {
+  if (a.n <= 0) return HEXGNN_OK;
+  if (a.n > kLwMaxPack) { set_error("lw_pack: too many entries"); return HEXGNN_E_BADARG; }
+  lw_pack_kernel<<<dim3(16, (unsigned)a.n), 256, 0, st>>>(a);
+  HEX_CUDA_CHECK(cudaGetLastError());
+  return HEXGNN_OK;
+}
+
+int launch_lw_prepare(const int* rowptr, int64_t N, float* degf, unsigned* zero, int zero_words, cudaStream_t st) {
+  const int64_t n = N > zero_words ? N : zero_words;
+  if (n <= 0) return HEXGNN_OK;
+  lw_prepare_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(rowptr, N, degf, zero, zero_words);
+  HEX_CUDA_CHECK(cudaGetLastError());
+  return HEXGNN_OK;
+}
+
+int lw_layer0_blocks(int64_t N) { return (int)((N + kL0Rows - 1) / kL0Rows); }
+int launch_lw_layer0(const LwLayer0Args& a, cudaStream_t st) {
+  if (a.Cin < 1 || a.Cin > 4) { set_error("lw_layer0: C_in=%d", a.Cin); return HEXGNN_E_UNSUPPORTED; }
+  if (a.N <= 0) return HEXGNN_OK;
+  return launch_pdl(lw_layer0_kernel, dim3((unsigned)lw_layer0_blocks(a.N)), dim3(kL0Threads), 0, st, a);
+}
+
+int lw_norm_blocks(int64_t N) { return (int)((N + kNormRows - 1) / kNormRows); }
+int launch_lw_norm(const LwNormArgs& a, cudaStream_t st) {
+  if (a.N <= 0) return HEXGNN_OK;
+  return launch_pdl(lw_norm_kernel, dim3((unsigned)lw_norm_blocks(a.N)), dim3(kNormThreads), 0, st, a);
+}
+
+}  // namespace hexgnn

@@ -11,7 +11,7 @@ from ._lib import HEXGNN_ADV_ONLY, HEXGNN_SEPARATE, HEXGNN_PATH_SIMT, HEXGNN_PAT
 
 # kernels launched by each C-ABI call (csr: init, hist, scan, fill, sort; forward: pack, fused;
 # backward: pack, fused, reduce, unpack) -- bench.py's `gpu_launches` is read off this counter.
-LAUNCHES = {"build_csr": 1, "forward": 2, "backward": 5, "td_loss": 1, "train_step": 6, "adam_step": 2, "mask_argmax": 1, "td_target": 1, "forward_big": 0, "allreduce_p2p": 1, "noisy": 1}
+LAUNCHES = {"build_csr": 1, "forward": 2, "backward": 5, "td_loss": 1, "train_step": 6, "adam_step": 2, "mask_argmax": 1, "td_target": 1, "forward_big": 0, "allreduce_p2p": 1, "noisy": 1, "forward_lw": 0, "backward_lw": 0}
 launch_counter = 0
 NVTX = os.environ.get("HEXGNN_NVTX", "0") == "1"
 
@@ -206,6 +206,61 @@ def fused_backward(desc, flat_params, x, csr, flags, d_nodes, d_value, stash, wa
     _lib.check(rc, "hexgnn_backward")
     _count("backward")
     return grad_out, d_embeds
+
+
+@_on_tensor_device
+def lw_forward(desc, flat_params, norm_params, x, csr, flags=0, want_stash=False, ws=None):
+    """hexgnn_forward_lw (layer-at-a-time tensor-core path: any graph size, optional graph-mode LayerNorm).
+    Returns (out_nodes [N], out_value [B], stash or None, HexLwSizes)."""
+    _require_cuda(x, "x")
+    _require_cuda(flat_params, "parameters")
+    if x.dtype != torch.float32 or x.dim() != 2 or x.shape[1] != 3:
+        raise _lib.HexGnnError("x must be float32 [N,3]")
+    x = x.contiguous()
+    N, E, B = csr.N, csr.E, csr.B
+    if x.shape[0] != N:
+        raise _lib.HexGnnError("x rows != csr nodes")
+    sz = _lib.lw_sizes(desc, N, E, B, norm_params is not None)
+    if norm_params is not None and (not norm_params.is_cuda or norm_params.numel() != sz.norm_floats):
+        raise _lib.HexGnnError("lw_forward: norm_params must be a CUDA tensor of hexgnn_lw_sizes().norm_floats")
+    dev = x.device
+    if ws is None or ws.numel() * 4 < sz.fwd_ws_bytes:
+        ws = torch.empty((sz.fwd_ws_bytes + 3) // 4, dtype=torch.float32, device=dev)
+    out_nodes = torch.empty(N, dtype=torch.float32, device=dev)
+    out_value = torch.empty(B, dtype=torch.float32, device=dev)
+    stash = torch.empty(sz.stash_bytes // 4, dtype=torch.float32, device=dev) if want_stash else None
+    rc = _lib.lib().hexgnn_forward_lw(C.byref(desc), _ptr(flat_params), _ptr(norm_params), _ptr(x), N, E, B, _ptr(csr.blob),
+                                      flags, _ptr(out_nodes), _ptr(out_value), _ptr(stash), _ptr(ws), ws.numel() * 4,
+                                      _stream(dev))
+    _lib.check(rc, "hexgnn_forward_lw")
+    _count("forward_lw")
+    return out_nodes, out_value, stash, sz
+
+
+@_on_tensor_device
+def lw_backward(desc, flat_params, norm_params, x, csr, flags, d_nodes, d_value, stash, want_d_embeds=False, ws=None,
+                grad_out=None, grad_norm=None):
+    """hexgnn_backward_lw.  Returns (flat gradient [P], norm gradient or None, d_embeds [N,Hp] or None)."""
+    N, E, B = csr.N, csr.E, csr.B
+    sz = _lib.lw_sizes(desc, N, E, B, norm_params is not None)
+    dev = x.device
+    x = x.contiguous()
+    if ws is None or ws.numel() * 4 < sz.bwd_ws_bytes:
+        ws = torch.empty((sz.bwd_ws_bytes + 3) // 4, dtype=torch.float32, device=dev)
+    if grad_out is None:
+        grad_out = torch.empty(flat_params.numel(), dtype=torch.float32, device=dev)
+    if norm_params is not None and grad_norm is None:
+        grad_norm = torch.empty_like(norm_params)
+    d_nodes = d_nodes.contiguous().float()
+    if d_value is not None:
+        d_value = d_value.contiguous().float()
+    d_embeds = torch.empty((N, int(sz.hidden_padded)), dtype=torch.float32, device=dev) if want_d_embeds else None
+    rc = _lib.lib().hexgnn_backward_lw(C.byref(desc), _ptr(flat_params), _ptr(norm_params), _ptr(x), N, E, B, _ptr(csr.blob),
+                                       flags, _ptr(d_nodes), _ptr(d_value), _ptr(stash), _ptr(grad_out), _ptr(grad_norm),
+                                       _ptr(d_embeds), _ptr(ws), ws.numel() * 4, _stream(dev))
+    _lib.check(rc, "hexgnn_backward_lw")
+    _count("backward_lw")
+    return grad_out, grad_norm, d_embeds
 
 
 LOSS_KINDS = {"mse": 0, "smooth_l1": 1, "huber": 1}

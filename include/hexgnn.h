@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define HEXGNN_ABI_VERSION 7
+#define HEXGNN_ABI_VERSION 8
 
 enum {
   HEXGNN_OK = 0,
@@ -166,6 +166,34 @@ int hexgnn_backward_dx(const HexModelDesc* desc, const float* params, const floa
 int hexgnn_forward_big(const HexModelDesc* desc, const float* params, const float* x, int64_t N, int64_t E, int64_t B,
                        const void* csr, int32_t tile_rows, int32_t flags, int32_t max_rows, float* out_nodes,
                        float* out_value, void* ws, size_t ws_bytes, void* stream);
+
+/* ---- Layer-at-a-time tensor-core path ("lw") ----------------------------------------------------------------------
+ * The same network evaluated one SAGE layer per launch over ALL node rows (tcgen05, fp32-parity fp16 split), activations in
+ * global memory.  It covers what the fused one-tile-per-CTA kernels cannot hold on chip:
+ *   - graphs of any size (12x12 .. 19x19 boards of the transfer evaluation, evaluate_elo.py:228-251, plotting.py:61-80),
+ *     forward AND training;
+ *   - `--norm=True`: PyG LayerNorm in graph mode without a batch vector (statistics over all nodes and channels of the
+ *     batch) after every SAGE layer and once more between body and heads (GN0/models.py:283-287,158-162,481-482,550-551).
+ * norm_params == NULL: norm=False.  Otherwise (L + 1 + 2 Lh) blocks of gamma[H] | beta[H]: body layers 0..L-1
+ * (`gnn.norms.i`), `after_embed_norm`, maker head layers (`maker_head.gnn.norms.j`), breaker head layers.
+ * Everything else (params, x, csr, flags, outputs) as in hexgnn_forward / hexgnn_backward; HEXGNN_ST_GRAPH_TOO_LARGE is
+ * cleared (no tile limit here).  stash: stash_bytes of hexgnn_lw_sizes (NULL = inference); the body embedding
+ * (`final_conv_acts`, after after_embed_norm when norm is on) is the row-major [N, hidden_padded] block at
+ * embed_offset_floats.  grad_norm: same layout as norm_params, OVERWRITTEN.  Deterministic. */
+typedef struct HexLwSizes {
+  int64_t fwd_ws_bytes, bwd_ws_bytes, stash_bytes;
+  int64_t norm_floats;          /* length of norm_params / grad_norm */
+  int64_t embed_offset_floats;  /* final_conv_acts inside the stash  */
+  int64_t hidden_padded;
+} HexLwSizes;
+int hexgnn_lw_sizes(const HexModelDesc* desc, int64_t N, int64_t E, int64_t B, int32_t norm, HexLwSizes* out);
+int hexgnn_forward_lw(const HexModelDesc* desc, const float* params, const float* norm_params, const float* x, int64_t N,
+                      int64_t E, int64_t B, const void* csr, int32_t flags, float* out_nodes, float* out_value, float* stash,
+                      void* ws, size_t ws_bytes, void* stream);
+int hexgnn_backward_lw(const HexModelDesc* desc, const float* params, const float* norm_params, const float* x, int64_t N,
+                       int64_t E, int64_t B, const void* csr, int32_t flags, const float* d_nodes, const float* d_value,
+                       const float* stash, float* grad_params, float* grad_norm, float* d_embeds, void* ws, size_t ws_bytes,
+                       void* stream);
 
 /* One learner step in one call (replaces rainbow.py:301-316: Q = model(states); td_est = Q[action + ptr[:-1]];
  * loss = mean(w * l(td_tgt, td_est)); loss.backward()): forward with stash, TD loss, backward and the deterministic
