@@ -48,6 +48,7 @@ struct LwSageArgs {
   unsigned* out_absmax;             // atomicMax of the bits of max |out|, or nullptr
   double* stats;                    // [gridDim.x][2]: sum, sum of squares of `out` over live rows and real channels; or nullptr
   float* agg_out; int lda;          // the aggregated half of the operand rows ([N][lda], columns [0, Kp)), or nullptr
+  float* raw_out; int ldr;          // a copy of `out` BEFORE the mask (the embedding-gradient tap), or nullptr
   int* status;                      // HEXGNN_ST_* bits
 };
 int launch_lw_sage(const LwSageArgs& a, cudaStream_t st);

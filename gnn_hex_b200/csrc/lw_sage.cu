@@ -197,6 +197,11 @@ __global__ void __launch_bounds__(kLwThreads, 1) lw_sage_kernel(const __grid_con
         if (a.relu) z = fmaxf(z, 0.f);
         v[u] = z + poison;
       }
+      if (a.raw_out) {
+        float* o = a.raw_out + gr * a.ldr + c0;
+        *(float4*)o = make_float4(v[0], v[1], v[2], v[3]);
+        *(float4*)(o + 4) = make_float4(v[4], v[5], v[6], v[7]);
+      }
       if (a.mask_src) {
         const float4 m0 = *(const float4*)(a.mask_src + gr * a.ldm + c0), m1 = *(const float4*)(a.mask_src + gr * a.ldm + c0 + 4);
         const float m[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
