@@ -23,23 +23,39 @@ class _Conv(nn.Module):
         self.lin_r = nn.Linear(cin, cout, bias=False)
 
 
+class _NormParams(nn.Module):
+    """Affine parameters named like PyG `LayerNorm(hidden)` (`weight` ones, `bias` zeros), the `norm` the reference passes
+    to GraphSAGE with `--norm=True` (GN0/models.py:935,945).  Evaluated inside libhexgnn.so (graph-mode statistics over
+    the whole batch, because models.py:285 calls it without `batch`)."""
+
+    def __init__(self, channels):
+        super().__init__()
+        self.weight = nn.Parameter(torch.ones(channels))
+        self.bias = nn.Parameter(torch.zeros(channels))
+
+
 class _SageParams(nn.Module):
-    """Holder named like `cachify_gnn(GraphSAGE)` (GN0/models.py:144-160): `.convs`, plus the
-    attributes callers read (`hidden_channels` train.py:301, `has_cache` rainbow.py:344)."""
+    """Holder named like `cachify_gnn(GraphSAGE)` (GN0/models.py:144-160): `.convs` (+ `.norms` with norm=True, one per
+    layer incl. the last: models.py:158-162), plus the attributes callers read (`hidden_channels` train.py:301,
+    `has_cache` rainbow.py:344)."""
     supports_cache = True
 
-    def __init__(self, in_channels, hidden, num_layers):
+    def __init__(self, in_channels, hidden, num_layers, norm=False):
         super().__init__()
         self.in_channels = in_channels
         self.hidden_channels = hidden
         self.num_layers = num_layers
         self.has_cache = False
         self.convs = nn.ModuleList([_Conv(in_channels if i == 0 else hidden, hidden) for i in range(num_layers)])
+        self.norms = nn.ModuleList([_NormParams(hidden) for _ in range(num_layers)]) if norm else None
 
     @torch.no_grad()
     def grow_depth(self, additional_layers):
         """GN0/models.py:166-185: append layers that start as the identity (lin_l = 0, lin_r = I; the input is a ReLU
         output, so relu(I x) = x and the network's function is unchanged)."""
+        if self.norms is not None:
+            raise NotImplementedError("grow_depth with norm=True (the reference's identity layer is not the identity "
+                                      "through a LayerNorm either)")
         dev = self.convs[0].lin_l.weight.device
         H = self.hidden_channels
         for _ in range(int(additional_layers)):
@@ -57,6 +73,8 @@ class _SageParams(nn.Module):
         nothing of the new input columns (zeros), the new rows keep their random init."""
         if self.num_layers < 2:
             raise NotImplementedError("grow_width of a one-layer stack")
+        if self.norms is not None:
+            raise NotImplementedError("grow_width with norm=True (models.py:187-238 rebuilds the convs only)")
         dev = self.convs[0].lin_l.weight.device
         old, H = self.convs, self.hidden_channels
         old_in = self.in_channels
@@ -162,9 +180,9 @@ class _HeadParams(nn.Module):
     """Holder named like `HeadNetwork` (GN0/models.py:318-334): gnn, linear, value_head."""
     supports_cache = True
 
-    def __init__(self, hidden, num_layers, noisy_dqn=False, noise_sigma=0.0):
+    def __init__(self, hidden, num_layers, noisy_dqn=False, noise_sigma=0.0, norm=False):
         super().__init__()
-        self.gnn = _SageParams(hidden, hidden, num_layers)
+        self.gnn = _SageParams(hidden, hidden, num_layers, norm=norm)
         self.linear = FactorizedNoisyLinear(hidden, 1, noise_sigma) if noisy_dqn else nn.Linear(hidden, 1)
         self.value_head = _MLPParams(hidden // 2, 4 * hidden, 1)
         self.hidden_channels = hidden
@@ -235,8 +253,38 @@ class _FusedQ(torch.autograd.Function):
         return None, d_x, None, None, None
 
 
+class _LwQ(torch.autograd.Function):
+    """Autograd node around hexgnn_forward_lw / hexgnn_backward_lw (layer-at-a-time tensor-core path: graphs of any size,
+    norm=True).  Same contract as `_FusedQ`; the LayerNorm affine gradients go to a second small flat buffer."""
+
+    @staticmethod
+    def forward(ctx, model, x, csr, flags, anchor):
+        out_nodes, out_value, stash, sz = ops.lw_forward(model._desc, model._flat, model._norm_flat, x, csr, flags,
+                                                         want_stash=True, ws=model._lw_ws(csr, "fwd"))
+        ctx.model, ctx.csr, ctx.flags, ctx.stash = model, csr, flags, stash
+        ctx.save_for_backward(x)
+        ctx.flat_version = model._flat_version
+        off, pitch = int(sz.embed_offset_floats), int(sz.hidden_padded)
+        model.final_conv_acts = stash[off:off + csr.N * pitch].view(csr.N, pitch)[:, :model.hidden_channels]
+        return out_nodes, out_value
+
+    @staticmethod
+    def backward(ctx, d_nodes, d_value):
+        model = ctx.model
+        (x,) = ctx.saved_tensors
+        if ctx.flat_version != model._flat_version:
+            raise _lib.HexGnnError("parameters were re-flattened between forward and backward")
+        if ctx.needs_input_grad[1]:
+            raise _lib.HexGnnError("dL/dx is available on the fused path only (norm=False, graphs within one tile)")
+        if d_nodes is None:
+            d_nodes = torch.zeros(ctx.csr.N, dtype=torch.float32, device=x.device)
+        use_dv = bool(ctx.flags & ops.HEXGNN_SEPARATE) and d_value is not None
+        model._lw_backward(x, ctx.csr, ctx.flags, d_nodes, d_value if use_dv else None, ctx.stash)
+        return None, None, None, None, None
+
+
 class ModernTwoHeaded(nn.Module):
-    """Drop-in for `get_pre_defined("modern_two_headed", args)` with norm=False, noisy_dqn=False.
+    """Drop-in for `get_pre_defined("modern_two_headed", args)` (norm, noisy_dqn included).
 
     forward(x, edge_index, graph_indices=None, ptr=None, set_cache=False, advantages_only=False,
             seperate=False)            -- GN0/models.py:537
@@ -248,14 +296,21 @@ class ModernTwoHeaded(nn.Module):
 
     def __init__(self, hidden_channels: int, num_layers: int, num_head_layers: int = 2, tile_rows: int = 128,
                  strict: bool = False, path: str = "auto", max_graph_nodes: int = 0, noisy_dqn: bool = False,
-                 noisy_sigma0: float = 0.5, inference_precision: str = "tf32x3"):
+                 noisy_sigma0: float = 0.5, inference_precision: str = "tf32x3", norm: bool = False):
         super().__init__()
         self.hidden_channels = int(hidden_channels)
         self.num_layers = int(num_layers)
         self.num_head_layers = int(num_head_layers)
         self.tile_rows = int(tile_rows)
         self.strict = strict                  # True: sync + raise on device-side status after each forward
-        self.path = path                      # "auto" | "simt" | "tc"
+        self.path = path                      # "auto" | "simt" | "tc" | "lw" (layer-at-a-time tensor-core path)
+        if path not in ("auto", "simt", "tc", "lw"):
+            raise ValueError("path must be 'auto', 'simt', 'tc' or 'lw'")
+        # args.norm (models.py:935,945): PyG LayerNorm after every conv + after_embed_norm (models.py:480-483), statistics
+        # over the whole batch -> always the layer-at-a-time path
+        self.norm = bool(norm)
+        if self.norm and path in ("simt", "tc"):
+            raise ValueError("norm=True runs on the layer-at-a-time path only (path='auto' or 'lw')")
         # SURVEY 7.2(1) precision policy.  "tf32x3" (default): fp32 parity everywhere.  "tf32x1": forwards that keep no
         # stash (torch.no_grad(): acting, target evaluation) run ONE tensor-core pass per k-step (~1e-3 relative error,
         # opt-in; rainbow.py:214-239 only takes an arg-max).  Calls that can be differentiated always use 3xTF32.
@@ -263,14 +318,16 @@ class ModernTwoHeaded(nn.Module):
             raise ValueError("inference_precision must be 'tf32x3' or 'tf32x1'")
         self.inference_precision = inference_precision
         self.capture_embed_grads = False      # True: fill final_conv_grads (rl_loop/explain.py:41)
-        # > tile_rows: inference calls also run the oversize-graph path (hexgnn_forward_big) for graphs of up to this
-        # many nodes (board-size transfer: 13x13 -> 171, evaluate_elo.py:229-251); 0 = such graphs are flagged only
+        # > tile_rows: the batch may hold graphs that do not fit one tile of the fused kernels (board-size transfer up to
+        # 19x19 = 363 nodes, evaluate_elo.py:229-251, plotting.py:61-80): every call, training included, then runs the
+        # layer-at-a-time path, which has no graph-size limit (the number itself is not a limit any more); 0 = such graphs
+        # are flagged (NaN outputs + status bit)
         self.max_graph_nodes = int(max_graph_nodes)
-        self.gnn = _SageParams(2, hidden_channels, num_layers)
+        self.gnn = _SageParams(2, hidden_channels, num_layers, norm=self.norm)
         self.noisy_dqn = bool(noisy_dqn)      # args.noisy_dqn / args.noisy_sigma0 (models.py:944-945)
-        self.maker_head = _HeadParams(hidden_channels, num_head_layers, self.noisy_dqn, noisy_sigma0)
-        self.breaker_head = _HeadParams(hidden_channels, num_head_layers, self.noisy_dqn, noisy_sigma0)
-        self.after_embed_norm = None
+        self.maker_head = _HeadParams(hidden_channels, num_head_layers, self.noisy_dqn, noisy_sigma0, norm=self.norm)
+        self.breaker_head = _HeadParams(hidden_channels, num_head_layers, self.noisy_dqn, noisy_sigma0, norm=self.norm)
+        self.after_embed_norm = _NormParams(hidden_channels) if self.norm else None
         self.final_conv_acts = None
         self.final_conv_grads = None
         self._desc = _lib.make_desc(hidden_channels, num_layers, num_head_layers)
@@ -283,8 +340,24 @@ class ModernTwoHeaded(nn.Module):
         self._p2p = None
         self._noisy = self._noisy_grad = None
         self._noisy_params = []
+        self._norm_flat = self._norm_grad = None
+        self._norm_params = []
+        self._norm_views = []
         self._shape_sig = self._shape_signature()
         self.last_csr = None
+
+    def _uses_lw(self):
+        return self.norm or self.path == "lw" or (self.path == "auto" and self.max_graph_nodes > self.tile_rows)
+
+    def _ordered_norm_params(self):
+        """hexgnn_lw_sizes().norm_floats block: per LayerNorm weight[H] then bias[H]; body layers, after_embed_norm, maker
+        head layers, breaker head layers."""
+        mods = list(self.gnn.norms) + [self.after_embed_norm] + list(self.maker_head.gnn.norms) + \
+            list(self.breaker_head.gnn.norms)
+        ps = []
+        for m in mods:
+            ps += [m.weight, m.bias]
+        return ps
 
     # ---- parameter order == include/hexgnn.h flat layout ---------------------------------------------
     def _ordered_params(self):
@@ -324,6 +397,17 @@ class ModernTwoHeaded(nn.Module):
         self._flat_grad = None
         self._grad_views = {}
         self._params_cache = ps
+        self._norm_flat = self._norm_grad = None
+        self._norm_params, self._norm_views = [], []
+        if self.norm:
+            nps = self._ordered_norm_params()
+            H = self.hidden_channels
+            nf = torch.empty(len(nps) * H, dtype=torch.float32, device=dev)
+            with torch.no_grad():
+                for i, q in enumerate(nps):
+                    nf[i * H:(i + 1) * H].copy_(q.detach().to(torch.float32))
+                    q.data = nf[i * H:(i + 1) * H]
+            self._norm_flat, self._norm_params = nf, nps
         self._noisy = self._noisy_grad = None
         self._noisy_params = []
         if self.noisy_dqn:
@@ -378,6 +462,12 @@ class ModernTwoHeaded(nn.Module):
             lin = self.maker_head.linear
             if lin.weight_mu.data_ptr() != self._noisy.data_ptr():
                 return False
+        if self.norm:
+            nps = self._ordered_norm_params()
+            if self._norm_flat is None or len(nps) != len(self._norm_params) or nps[0] is not self._norm_params[0] or \
+                    nps[0].data_ptr() != self._norm_flat.data_ptr() or \
+                    nps[-1].data_ptr() != self._norm_flat.data_ptr() + 4 * (len(nps) - 1) * self.hidden_channels:
+                return False
         return True
 
     def __deepcopy__(self, memo):
@@ -388,12 +478,15 @@ class ModernTwoHeaded(nn.Module):
         new = cls.__new__(cls)
         memo[id(self)] = new
         skip = {"_flat", "_slices", "_ws", "_flat_grad", "_grad_views", "_p2p", "_noisy", "_noisy_grad", "_noisy_params",
-                "_noisy_views", "_params_cache", "last_csr", "final_conv_acts", "final_conv_grads"}
+                "_noisy_views", "_params_cache", "last_csr", "final_conv_acts", "final_conv_grads", "_norm_flat",
+                "_norm_grad", "_norm_params", "_norm_views"}
         for k, v in self.__dict__.items():
             if k not in skip:
                 new.__dict__[k] = copy.deepcopy(v, memo)
         new._flat = new._slices = new._flat_grad = new._p2p = new._noisy = new._noisy_grad = None
         new._ws, new._grad_views, new._noisy_params, new._params_cache = {}, {}, [], None
+        new._norm_flat = new._norm_grad = None
+        new._norm_params, new._norm_views = [], []
         new.last_csr = new.final_conv_acts = new.final_conv_grads = None
         for p in new.parameters():
             p.grad = None
@@ -477,10 +570,14 @@ class ModernTwoHeaded(nn.Module):
                 p.grad = None
             for p, *_ in self._noisy_params:
                 p.grad = None
+            for p in self._norm_params:
+                p.grad = None
         elif self._grads_in_place():
             self._flat_grad.zero_()
             if self._noisy_grad is not None:
                 self._noisy_grad.zero_()
+            if self._norm_grad is not None:
+                self._norm_grad.zero_()
         else:
             super().zero_grad(set_to_none=False)
 
@@ -583,6 +680,8 @@ class ModernTwoHeaded(nn.Module):
         import torch.distributed as dist
         if self.noisy_dqn and self._noisy_grad is not None:
             dist.all_reduce(self._noisy_grad, op=dist.ReduceOp.SUM, group=group)
+        if self.norm and self._norm_grad is not None:   # LayerNorm affine gradients: a second small flat buffer
+            dist.all_reduce(self._norm_grad, op=dist.ReduceOp.SUM, group=group)
 
     @property
     def flat_parameters(self):
@@ -604,6 +703,51 @@ class ModernTwoHeaded(nn.Module):
             w = torch.empty(need, dtype=torch.float32, device=csr.blob.device)
             self._ws["bwd"] = w
         return w
+
+    def _lw_ws(self, csr, which):
+        sz = _lib.lw_sizes(self._desc, csr.N, csr.E, csr.B, self.norm)
+        need = ((sz.fwd_ws_bytes if which == "fwd" else sz.bwd_ws_bytes) + 3) // 4
+        w = self._ws.get("lw_" + which)
+        if w is None or w.numel() < need or w.device != csr.blob.device:
+            w = torch.empty(need, dtype=torch.float32, device=csr.blob.device)
+            self._ws["lw_" + which] = w
+        return w
+
+    def _lw_backward(self, x, csr, flags, d_nodes, d_value, stash):
+        """hexgnn_backward_lw into the flat gradient (+ the LayerNorm gradient block), with the same accumulate-or-assign
+        semantics as the fused route."""
+        accumulate = self._grads_in_place()
+        out = self._grad_scratch() if accumulate else self._flat_grad_buffer()
+        gn = None
+        if self.norm:
+            if self._norm_grad is None or self._norm_grad.device != self._norm_flat.device:
+                self._norm_grad = torch.zeros_like(self._norm_flat)
+                H = self.hidden_channels
+                self._norm_views = [self._norm_grad[i * H:(i + 1) * H] for i in range(len(self._norm_params))]
+            gn = self._ws.get("gnorm")
+            if gn is None or gn.device != self._norm_flat.device or gn.numel() != self._norm_flat.numel():
+                gn = self._ws["gnorm"] = torch.empty_like(self._norm_flat)
+        grad, gnorm, d_emb = ops.lw_backward(self._desc, self._flat, self._norm_flat, x, csr, flags, d_nodes, d_value, stash,
+                                             want_d_embeds=self.capture_embed_grads, ws=self._lw_ws(csr, "bwd"),
+                                             grad_out=out, grad_norm=gn)
+        if accumulate:
+            self._flat_grad.add_(grad)
+        else:
+            self._point_grads()
+        if self.norm:
+            acc = all(p.grad is not None and p.grad.data_ptr() == v.data_ptr()
+                      for p, v in zip(self._norm_params, self._norm_views))
+            if acc:
+                self._norm_grad.add_(gnorm)
+            else:
+                self._norm_grad.copy_(gnorm)
+            for p, v in zip(self._norm_params, self._norm_views):
+                if p.requires_grad:
+                    p.grad = v
+        self._noisy_backward(grad)
+        if d_emb is not None:
+            self.final_conv_grads = d_emb[:, :self.hidden_channels]
+        return grad
 
     # ---- reference API ---------------------------------------------------------------------------------
     def build_csr(self, edge_index, graph_indices=None, ptr=None, num_nodes=None, num_graphs=None):
@@ -632,7 +776,14 @@ class ModernTwoHeaded(nn.Module):
         self.final_conv_acts = None
         self.last_csr = csr
         anchor = self._params_cache[0]
-        if torch.is_grad_enabled() and anchor.requires_grad:
+        if self._uses_lw():
+            flags &= ops.HEXGNN_ADV_ONLY | ops.HEXGNN_SEPARATE
+            if torch.is_grad_enabled() and anchor.requires_grad:
+                out_nodes, out_value = _LwQ.apply(self, x, csr, flags, anchor)
+            else:
+                out_nodes, out_value, _, _ = ops.lw_forward(self._desc, self._flat, self._norm_flat, x, csr, flags,
+                                                            want_stash=False, ws=self._lw_ws(csr, "fwd"))
+        elif torch.is_grad_enabled() and anchor.requires_grad:
             out_nodes, out_value = _FusedQ.apply(self, x, csr, flags, anchor)
         else:
             if self.inference_precision == "tf32x1" and self.path != "simt":
@@ -640,7 +791,7 @@ class ModernTwoHeaded(nn.Module):
             out_nodes, out_value, _, _ = ops.fused_forward(self._desc, self._flat, x, csr, flags, want_stash=False,
                                                            ws=self._fwd_ws(csr))
             flags &= ~ops.HEXGNN_TF32X1
-            if self.max_graph_nodes > self.tile_rows:
+            if self.max_graph_nodes > self.tile_rows:   # path == "tc" / "simt" forced: CUDA-core kernels for the oversize graphs
                 ops.forward_big(self._desc, self._flat, x, csr, flags, self.max_graph_nodes, out_nodes, out_value)
         if self.strict:
             csr.raise_on_error()
@@ -668,6 +819,18 @@ class ModernTwoHeaded(nn.Module):
             csr = self.build_csr(edge_index, graph_indices, ptr, num_nodes=int(x.shape[0]), num_graphs=num_graphs)
         self.last_csr = csr
         self.final_conv_acts = None
+        if self._uses_lw():
+            # same three results through the layer-at-a-time path: forward (stash), hexgnn_td_loss, hexgnn_backward_lw
+            q, _, stash, _ = ops.lw_forward(self._desc, self._flat, self._norm_flat, x, csr, 0, want_stash=True,
+                                            ws=self._lw_ws(csr, "fwd"))
+            with torch.enable_grad():
+                qd = q.detach().requires_grad_(True)
+                loss, td_err = ops.td_loss(qd, ptr, action, target, weight, kind, scale)
+                (d_q,) = torch.autograd.grad(loss, qd)
+            self._lw_backward(x, csr, 0, d_q, None, stash)
+            if self.strict:
+                csr.raise_on_error()
+            return loss.detach(), td_err, q
         accumulate = self._grads_in_place()
         out = self._grad_scratch() if accumulate else self._flat_grad_buffer()
         loss, td_err, q, grad = ops.fused_train_step(self._desc, self._flat, x, csr, ptr, action, target, weight, kind, scale,
@@ -744,6 +907,9 @@ class FusedAdam:
         if m.noisy_dqn:
             raise NotImplementedError("FusedAdam steps the flat parameter buffer; with noisy_dqn=True the advantage layer's "
                                       "mu / sigma live outside it: use torch.optim.Adam(model.parameters())")
+        if m.norm:
+            raise NotImplementedError("FusedAdam steps the flat parameter buffer; with norm=True the LayerNorm weights live "
+                                      "outside it: use torch.optim.Adam(model.parameters())")
         if self._version != m._flat_version or self.exp_avg is None or self.exp_avg.device != m._flat.device:
             old = (self.exp_avg, self.exp_avg_sq, self.state)
             self.exp_avg = torch.zeros_like(m._flat)
@@ -781,9 +947,8 @@ def get_pre_defined(name, args=None):
     """`GN0/models.py:892` for the one name this package implements."""
     if name != "modern_two_headed":
         raise NotImplementedError(f"gnn_hex_b200 implements only 'modern_two_headed', not {name!r}")
-    if getattr(args, "norm", False):
-        raise NotImplementedError("norm=True (PyG LayerNorm over the whole batch) is not on the fused path (SURVEY.md §8 f4)")
     return ModernTwoHeaded(args.hidden_channels, args.num_layers,
                            args.num_head_layers if hasattr(args, "num_head_layers") else 2,
                            noisy_dqn=bool(getattr(args, "noisy_dqn", False)),
-                           noisy_sigma0=float(getattr(args, "noisy_sigma0", 0.5)))
+                           noisy_sigma0=float(getattr(args, "noisy_sigma0", 0.5)),
+                           norm=bool(getattr(args, "norm", False)))

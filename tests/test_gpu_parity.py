@@ -275,9 +275,12 @@ def test_mask_argmax_and_td_target_match_torch():
 @pytest.mark.parametrize("mode", ["q", "adv", "sep"])
 def test_oversize_graphs_board_size_transfer(mode):
     """BASELINE configs[3]: a mixed 5x5..13x13 batch; the 12x12 / 13x13 positions (up to 171 nodes) do not fit one
-    128-row tile and go through hexgnn_forward_big.  Every graph must match the oracle; the status word ends clean."""
+    128-row tile and -- with the fused path forced (path="tc"; the default route for such batches is the layer-at-a-time
+    tensor-core path, tests/test_gpu_lw.py) -- go through hexgnn_forward_big.  Every graph must match the oracle; the status
+    word ends clean."""
     o, m = make_pair(110, 15)
     m = m.to(DEV)
+    m.path = "tc"
     m.max_graph_nodes = 256
     m.strict = True
     gs = positions.load_positions("pos_mix_5_13_seed1234.npz", maker=1)

@@ -202,6 +202,30 @@ def test_noisy_model_names_and_product_holder():
     assert not lin.weight_epsilon.any() and not lin.bias_epsilon.any()
 
 
+def test_norm_model_names_and_product_holder():
+    """`norm=True` adds PyG LayerNorm parameters (models.py:935,945: one per layer incl. the last, :158-162; plus
+    after_embed_norm, :480-483); names and order interchange with the oracle (and so with the reference: test_reference_pin)."""
+    from gnn_hex_b200 import ModernTwoHeaded, get_pre_defined
+    from types import SimpleNamespace
+    o = orc.ModernTwoHeadedOracle(12, 3, 2, norm=True)
+    m = get_pre_defined("modern_two_headed", SimpleNamespace(hidden_channels=12, num_layers=3, num_head_layers=2, norm=True,
+                                                             noisy_dqn=False))
+    assert isinstance(m, ModernTwoHeaded) and m.norm and m._uses_lw()
+    assert sorted(o.state_dict().keys()) == sorted(m.state_dict().keys())
+    for k in ("gnn.norms.2.weight", "after_embed_norm.bias", "breaker_head.gnn.norms.1.weight"):
+        assert k in m.state_dict()
+    m.load_state_dict(o.state_dict())
+    # the order of the C-ABI's norm block: body layers, after_embed_norm, maker head, breaker head; weight then bias
+    ps = m._ordered_norm_params()
+    assert len(ps) == 2 * (3 + 1 + 2 + 2) and ps[0] is m.gnn.norms[0].weight and ps[7] is m.after_embed_norm.bias
+    assert ps[8] is m.maker_head.gnn.norms[0].weight and ps[-1] is m.breaker_head.gnn.norms[1].bias
+    with pytest.raises(NotImplementedError):
+        m.grow_depth(1)
+    with pytest.raises(ValueError):
+        ModernTwoHeaded(12, 3, 2, norm=True, path="simt")
+    assert not ModernTwoHeaded(12, 3, 2)._uses_lw() and ModernTwoHeaded(12, 3, 2, max_graph_nodes=363)._uses_lw()
+
+
 def test_grow_depth_keeps_the_function_and_grow_width_layout():
     """grow_depth appends identity layers (models.py:166-185): same Q-values; grow_width (models.py:187-238,336-358,52-73):
     old weights in the top-left block, zeros right of them, product holder == oracle bit for bit under the same seed."""
