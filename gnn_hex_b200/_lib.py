@@ -25,7 +25,7 @@ STATUS_NAMES = {
     ST_FP16_RANGE: "an activation left the fp16 range of the forward kernel's mixed product scheme (|h| >= 60000): use path='simt'",
 }
 
-ABI_VERSION = 8
+ABI_VERSION = 9
 
 
 class HexModelDesc(C.Structure):
@@ -53,7 +53,7 @@ EXPORTS = ["hexgnn_abi_version", "hexgnn_last_error", "hexgnn_param_count", "hex
            "hexgnn_profile_enable", "hexgnn_profile_read", "hexgnn_selftest_mma", "hexgnn_debug_phases", "hexgnn_stash_embed", "hexgnn_td_loss", "hexgnn_train_step", "hexgnn_adam_step", "hexgnn_adam_ws_bytes", "hexgnn_collate", "hexgnn_collate_ws_bytes",
            "hexgnn_mask_argmax", "hexgnn_td_target", "hexgnn_forward_big", "hexgnn_allreduce_p2p",
            "hexgnn_noisy_compose", "hexgnn_noisy_grads", "hexgnn_backward_dx",
-           "hexgnn_lw_sizes", "hexgnn_forward_lw", "hexgnn_backward_lw"]
+           "hexgnn_lw_sizes", "hexgnn_forward_lw", "hexgnn_backward_lw", "hexgnn_forward_static"]
 
 _lib = None
 
@@ -129,6 +129,8 @@ def lib():
     l.hexgnn_forward_lw.argtypes = [D, p, p, p, i64, i64, i64, p, i32, p, p, p, p, sz, p]
     l.hexgnn_backward_lw.restype = C.c_int
     l.hexgnn_backward_lw.argtypes = [D, p, p, p, i64, i64, i64, p, i32, p, p, p, p, p, p, p, sz, p]
+    l.hexgnn_forward_static.restype = C.c_int
+    l.hexgnn_forward_static.argtypes = [D, p, p, i64, i64, i64, p, i32, i32, p, p, p]
     l.hexgnn_debug_phases.restype = C.c_int
     l.hexgnn_debug_phases.argtypes = [i32, C.POINTER(i64), i32]
     l.hexgnn_profile_enable.restype = C.c_int

@@ -174,6 +174,29 @@ def fused_forward(desc, flat_params, x, csr, flags=0, want_stash=False, ws=None)
     return out_nodes, out_value, stash, int(sz.hidden_padded)
 
 
+STATIC_WS_BYTES = 2 * 1024 * 1024   # HEXGNN_STATIC_WS_BYTES
+
+
+@_on_tensor_device
+def fused_forward_static(desc, flat_params, x, csr, out_nodes, out_value, flags=0):
+    """hexgnn_forward_static: inference forward whose scratch is a static device array inside libhexgnn.so -- the call
+    allocates nothing (the caller passes the outputs: out_nodes [N] f32, out_value [B] f32).  Models beyond
+    HEXGNN_STATIC_WS_BYTES are refused; calls that overlap on the GPU race on the shared scratch."""
+    _require_cuda(x, "x")
+    _require_cuda(flat_params, "parameters")
+    N, E, B = csr.N, csr.E, csr.B
+    if x.dtype != torch.float32 or not x.is_contiguous() or tuple(x.shape) != (N, 3):
+        raise _lib.HexGnnError("x must be a contiguous float32 [N,3] tensor")
+    for t, n, name in ((out_nodes, N, "out_nodes"), (out_value, B, "out_value")):
+        if t is None or not t.is_cuda or t.dtype != torch.float32 or not t.is_contiguous() or t.numel() != n:
+            raise _lib.HexGnnError(f"fused_forward_static: {name} must be a contiguous float32 CUDA tensor of {n} elements")
+    rc = _lib.lib().hexgnn_forward_static(C.byref(desc), _ptr(flat_params), _ptr(x), N, E, B, _ptr(csr.blob), csr.tile_rows,
+                                          flags, _ptr(out_nodes), _ptr(out_value), _stream(x.device))
+    _lib.check(rc, "hexgnn_forward_static")
+    _count("forward")
+    return out_nodes, out_value
+
+
 @_on_tensor_device
 def fused_backward(desc, flat_params, x, csr, flags, d_nodes, d_value, stash, want_d_embeds=False, ws=None,
                    grad_out=None, d_x=None):

@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define HEXGNN_ABI_VERSION 8
+#define HEXGNN_ABI_VERSION 9
 
 enum {
   HEXGNN_OK = 0,
@@ -135,6 +135,24 @@ int hexgnn_build_csr(const int64_t* edge_index, int64_t E, const int64_t* batch,
 int hexgnn_forward(const HexModelDesc* desc, const float* params, const float* x, int64_t N, int64_t E,
                    int64_t B, const void* csr, int32_t tile_rows, int32_t flags, float* out_nodes,
                    float* out_value, float* stash, void* ws, size_t ws_bytes, void* stream);
+
+/* hexgnn_forward for inference WITHOUT a caller workspace and without any allocation.  No counterpart in the reference:
+ * added for callers that cannot call cudaMalloc (code under CUDA-graph capture,
+ * tight serving loops, harnesses that forbid allocation).  The only scratch hexgnn_forward needs -- the tensor-core weight
+ * images and padded bias rows, rebuilt from `params` on every call -- lives in a file-scope static __device__ array of
+ * HEXGNN_STATIC_WS_BYTES inside libhexgnn.so (held by every GPU that loads the library until the process exits).  Same
+ * arguments, kernels and results as hexgnn_forward with stash == NULL (tensor-core path; HEXGNN_PATH_SIMT is refused); the
+ * caller still passes inputs and outputs.  A model whose images need more than HEXGNN_STATIC_WS_BYTES (GNN-L, hidden 110 /
+ * 15 + 2 layers, needs 1.62 MB) is refused with HEXGNN_E_UNSUPPORTED and a message that names both sizes.  Calls no
+ * cudaMalloc / cudaFree / allocating library routine (keep hexgnn_profile_enable off: its event brackets are created on
+ * demand); the first call on each device looks the array's address up (cudaGetSymbolAddress, that device current) -- make it
+ * once outside a capture.  ALL calls on a device share the array: it keeps the last call's images, every byte a call reads
+ * is rewritten by that call's own pack kernel (nothing relies on zeros), and two calls that overlap on the GPU (different
+ * streams without a dependency) race on it -- serialise them. */
+#define HEXGNN_STATIC_WS_BYTES (2 * 1024 * 1024)
+int hexgnn_forward_static(const HexModelDesc* desc, const float* params, const float* x, int64_t N, int64_t E, int64_t B,
+                          const void* csr, int32_t tile_rows, int32_t flags, float* out_nodes, float* out_value,
+                          void* stream);
 
 /* Fused backward (replaces loss.backward() through the model, rainbow.py:316).
  *   d_nodes      [N] gradient w.r.t. out_nodes
