@@ -10,3 +10,4 @@ from .ops import (CsrBlob, adam_step, build_csr, fused_backward, fused_forward, 
 from . import data  # noqa: F401
 from . import custom_ops  # noqa: F401  (registers torch.ops.hexgnn.*)
 from .learner import RainbowLearner  # noqa: F401
+from .hexara import SAGETorchScript, get_current_model  # noqa: F401

@@ -25,7 +25,7 @@ STATUS_NAMES = {
     ST_FP16_RANGE: "an activation left the fp16 range of the forward kernel's mixed product scheme (|h| >= 60000): use path='simt'",
 }
 
-ABI_VERSION = 9
+ABI_VERSION = 10
 
 
 class HexModelDesc(C.Structure):
@@ -43,6 +43,15 @@ class HexLwSizes(C.Structure):
                 ("norm_floats", C.c_int64), ("embed_offset_floats", C.c_int64), ("hidden_padded", C.c_int64)]
 
 
+class HexAraDesc(C.Structure):
+    _fields_ = [("hidden", C.c_int32), ("hidden_layers", C.c_int32), ("policy_layers", C.c_int32),
+                ("value_layers", C.c_int32), ("in_channels", C.c_int32), ("swap_allowed", C.c_int32)]
+
+
+class HexAraSizes(C.Structure):
+    _fields_ = [("ws_bytes", C.c_int64), ("max_policy_entries", C.c_int64), ("hidden_padded", C.c_int64)]
+
+
 class HexCsrLayout(C.Structure):
     _fields_ = [("status", C.c_int64), ("ntiles", C.c_int64), ("gptr", C.c_int64), ("rowptr", C.c_int64),
                 ("col", C.c_int64), ("tile_g0", C.c_int64), ("scratch", C.c_int64), ("total_words", C.c_int64)]
@@ -53,7 +62,8 @@ EXPORTS = ["hexgnn_abi_version", "hexgnn_last_error", "hexgnn_param_count", "hex
            "hexgnn_profile_enable", "hexgnn_profile_read", "hexgnn_selftest_mma", "hexgnn_debug_phases", "hexgnn_stash_embed", "hexgnn_td_loss", "hexgnn_train_step", "hexgnn_adam_step", "hexgnn_adam_ws_bytes", "hexgnn_collate", "hexgnn_collate_ws_bytes",
            "hexgnn_mask_argmax", "hexgnn_td_target", "hexgnn_forward_big", "hexgnn_allreduce_p2p",
            "hexgnn_noisy_compose", "hexgnn_noisy_grads", "hexgnn_backward_dx",
-           "hexgnn_lw_sizes", "hexgnn_forward_lw", "hexgnn_backward_lw", "hexgnn_forward_static"]
+           "hexgnn_lw_sizes", "hexgnn_forward_lw", "hexgnn_backward_lw", "hexgnn_forward_static",
+           "hexgnn_hexara_param_count", "hexgnn_hexara_param_offsets", "hexgnn_hexara_sizes", "hexgnn_hexara_forward"]
 
 _lib = None
 
@@ -129,6 +139,15 @@ def lib():
     l.hexgnn_forward_lw.argtypes = [D, p, p, p, i64, i64, i64, p, i32, p, p, p, p, sz, p]
     l.hexgnn_backward_lw.restype = C.c_int
     l.hexgnn_backward_lw.argtypes = [D, p, p, p, i64, i64, i64, p, i32, p, p, p, p, p, p, p, sz, p]
+    A = C.POINTER(HexAraDesc)
+    l.hexgnn_hexara_param_count.restype = C.c_int64
+    l.hexgnn_hexara_param_count.argtypes = [A]
+    l.hexgnn_hexara_param_offsets.restype = C.c_int32
+    l.hexgnn_hexara_param_offsets.argtypes = [A, C.POINTER(i64), i32]
+    l.hexgnn_hexara_sizes.restype = C.c_int
+    l.hexgnn_hexara_sizes.argtypes = [A, i64, i64, i64, C.POINTER(HexAraSizes)]
+    l.hexgnn_hexara_forward.restype = C.c_int
+    l.hexgnn_hexara_forward.argtypes = [A, p, p, i64, i64, i64, p, p, p, p, p, p, p, sz, p]
     l.hexgnn_forward_static.restype = C.c_int
     l.hexgnn_forward_static.argtypes = [D, p, p, i64, i64, i64, p, i32, i32, p, p, p]
     l.hexgnn_debug_phases.restype = C.c_int

@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define HEXGNN_ABI_VERSION 9
+#define HEXGNN_ABI_VERSION 10
 
 enum {
   HEXGNN_OK = 0,
@@ -212,6 +212,43 @@ int hexgnn_backward_lw(const HexModelDesc* desc, const float* params, const floa
                        int64_t E, int64_t B, const void* csr, int32_t flags, const float* d_nodes, const float* d_value,
                        const float* stash, float* grad_params, float* grad_norm, float* d_embeds, void* ws, size_t ws_bytes,
                        void* stream);
+
+/* ---- HexAra policy / value network ---------------------------------------------------------------------
+ * SAGE_torch_script (GN0/torch_script_models.py:286-379; factory get_current_model :495-500, defaults hidden 60, 15 body
+ * layers, 2 policy / 2 value layers), the TorchScript module the C++ engine evaluates through NN_api::predict
+ * (cpp_hex/CrazyAra/nn_api.cpp:14-19) on collate_batch output (cpp_hex/hex_graph_game/util.cpp:22-41): inference forward on
+ * the layer-at-a-time tensor-core kernels (graphs of any size).
+ *   x [N,3] f32 in the C++ feature convention (shannon_node_switching_game.cpp:690-726): IS_TERMINAL, two swap flags -- all
+ *   three are network inputs; rows 0, 1 of every graph are its terminal nodes.  csr: hexgnn_build_csr of the collated batch.
+ *   params: flat fp32 in state_dict order -- gnn.convs.i.(lin_l.weight, lin_l.bias, lin_r.weight); my_modules.value_head.convs.j.*;
+ *   my_modules.policy_head.convs.j.* (the last conv has ONE output channel); my_modules.value_linear.layers.{0,1}.(weight, bias);
+ *   my_modules.swap_linear.layers.{0,1}.(weight, bias)   (hexgnn_hexara_param_offsets gives the float offsets).
+ * Outputs = the module's 4-tuple (torch_script_models.py:379):
+ *   pi [max_policy_entries] f32   per graph: log-softmax over its non-terminal nodes, in node order, followed -- when
+ *                                 swap_allowed and x[last node of the graph, 2] != 0 -- by the swap entry (:337-366); the
+ *                                 number of entries written is out_batch_ptr[B]  (= N - 2B without swap)
+ *   value [B] f32                 tanh(value_linear([sum|max|min|mean] pooling of the value stack))
+ *   out_graph_indices [max_policy_entries] i64, out_batch_ptr [B+1] i64
+ *   embeds [N, hidden_padded] f32 or NULL: the body output (`final_conv_acts`, :314)                                   */
+typedef struct HexAraDesc {
+  int32_t hidden;         /* hidden_channels (60)                        */
+  int32_t hidden_layers;  /* body convs (15)                             */
+  int32_t policy_layers;  /* policy stack convs (2)                      */
+  int32_t value_layers;   /* value stack convs (2)                       */
+  int32_t in_channels;    /* must be 3                                   */
+  int32_t swap_allowed;   /* SAGE_torch_script(swap_allowed=...)         */
+} HexAraDesc;
+typedef struct HexAraSizes {
+  int64_t ws_bytes;            /* workspace of hexgnn_hexara_forward                     */
+  int64_t max_policy_entries;  /* N - 2B (+ B with swap_allowed): size pi / out_graph_indices */
+  int64_t hidden_padded;
+} HexAraSizes;
+int64_t hexgnn_hexara_param_count(const HexAraDesc* desc);
+int32_t hexgnn_hexara_param_offsets(const HexAraDesc* desc, int64_t* offsets, int32_t max_entries);
+int hexgnn_hexara_sizes(const HexAraDesc* desc, int64_t N, int64_t E, int64_t B, HexAraSizes* out);
+int hexgnn_hexara_forward(const HexAraDesc* desc, const float* params, const float* x, int64_t N, int64_t E, int64_t B,
+                          const void* csr, float* pi, float* value, int64_t* out_graph_indices, int64_t* out_batch_ptr,
+                          float* embeds, void* ws, size_t ws_bytes, void* stream);
 
 /* One learner step in one call (replaces rainbow.py:301-316: Q = model(states); td_est = Q[action + ptr[:-1]];
  * loss = mean(w * l(td_tgt, td_est)); loss.backward()): forward with stash, TD loss, backward and the deterministic

@@ -498,3 +498,94 @@ def flops_forward(n_nodes: int, num_graphs: int, hidden: int, num_layers: int, n
     if not advantages_only:
         f += num_graphs * 2 * (4 * H * (H // 2) + (H // 2))
     return f
+
+
+# ---- HexAra network: GN0/torch_script_models.py:286-379 -----------------------------------------------
+class _AraStack(torch.nn.Module):
+    """``ModifiedBaseNet(in, hidden, num_layers, out_channels=None|1, conv_class=ModifiedSAGEConv, norm=None)``
+    (GN0/torch_script_models.py:96-189): convs in -> hidden, (num_layers - 2) x hidden -> hidden, hidden -> out (a one-layer
+    stack is the single conv in -> out); ReLU after every conv EXCEPT the last (:178-183)."""
+
+    def __init__(self, in_channels: int, hidden: int, num_layers: int, out_channels: Optional[int] = None):
+        super().__init__()
+        self.num_layers = num_layers
+        self.convs = torch.nn.ModuleList()
+        cin = in_channels
+        for i in range(num_layers):
+            cout = (out_channels if out_channels is not None else hidden) if i == num_layers - 1 else hidden
+            self.convs.append(_SageStack._new_conv(cin, cout))
+            cin = hidden
+
+    def forward(self, x, edge_index):
+        for i, c in enumerate(self.convs):
+            x = sage_conv(x, edge_index, c.lin_l.weight, c.lin_l.bias, c.lin_r.weight)
+            if i != self.num_layers - 1:
+                x = F.relu(x)
+        return x
+
+
+class _AraMLP(torch.nn.Module):
+    """``MLP(hidden//2, 1, 4*hidden, 1)`` of torch_script_models.py:263-284: Linear -> ReLU -> Linear, no output activation."""
+
+    def __init__(self, hidden: int, num_input: int, num_output: int):
+        super().__init__()
+        self.layers = torch.nn.ModuleList([torch.nn.Linear(num_input, hidden), torch.nn.Linear(hidden, num_output)])
+
+    def forward(self, x):
+        return self.layers[1](F.relu(self.layers[0](x)))
+
+
+def scatter_log_softmax(src: torch.Tensor, index: torch.Tensor, dim_size: int, eps: float = 1e-12) -> torch.Tensor:
+    """torch_scatter 2.1.0 ``composite.scatter_log_softmax``: x - max_g(x) - log(sum_g exp(x - max_g) + eps)."""
+    mx = scatter(src, index, dim_size, "max")
+    rec = src - mx.index_select(0, index)
+    norm = _scatter_sum(rec.exp(), index, dim_size)
+    return rec - (norm + eps).log().index_select(0, index)
+
+
+class HexAraOracle(torch.nn.Module):
+    """``SAGE_torch_script(hidden_channels, hidden_layers, policy_layers, value_layers, in_channels=3, swap_allowed)``
+    (GN0/torch_script_models.py:286-379, factory ``get_current_model`` :495-500; called from C++ at
+    cpp_hex/CrazyAra/nn_api.cpp:14-19).  x follows the C++ convention (shannon_node_switching_game.cpp:690-726): column 0 =
+    IS_TERMINAL, columns 1 / 2 = swap flags; all three are network inputs.  Returns (log-policy over the non-terminal nodes
+    of every graph [+ one swap entry per graph whose last node has x[:,2] != 0], value [B], output graph ids, output ptr)."""
+
+    def __init__(self, hidden_channels: int, hidden_layers: int, policy_layers: int, value_layers: int, in_channels: int = 3,
+                 swap_allowed: bool = False):
+        super().__init__()
+        self.swap_allowed = swap_allowed
+        self.gnn = _AraStack(in_channels, hidden_channels, hidden_layers)
+        self.my_modules = torch.nn.ModuleDict()
+        self.my_modules["value_head"] = _AraStack(hidden_channels, hidden_channels, value_layers)
+        self.my_modules["policy_head"] = _AraStack(hidden_channels, hidden_channels, policy_layers, out_channels=1)
+        self.my_modules["value_linear"] = _AraMLP(hidden_channels // 2, hidden_channels * 4, 1)
+        self.my_modules["swap_linear"] = _AraMLP(hidden_channels // 2, hidden_channels * 4, 1)
+
+    def forward(self, x, edge_index, graph_indices, batch_ptr):
+        B = batch_ptr.numel() - 1
+        n = batch_ptr[1:] - batch_ptr[:-1]
+        assert bool((n > 2).all())                                                          # :311
+        embeds = self.gnn(x, edge_index)                                                    # :312 (norm=None)
+        pi = self.my_modules["policy_head"](embeds, edge_index).reshape(-1)                 # :318, :330
+        ve = self.my_modules["value_head"](embeds, edge_index)                              # :319
+        parts = torch.cat([scatter(ve, graph_indices, B, r) for r in ("sum", "max", "min", "mean")], dim=1)   # :320-324
+        value = torch.tanh(self.my_modules["value_linear"](parts)).reshape(-1)              # :326-327
+        # terminal-row removal (+ swap rule), :337-373, restated per graph: graph g keeps its non-terminal nodes in order and,
+        # when swapping is allowed in it (x[last node of g, 2] != 0), one more entry -- the swap logit -- right after them
+        # (the reference writes it into the slot of the NEXT graph's first terminal node and re-labels it, :353-357, or
+        # appends it for the last graph, :364-366: the same position)
+        swap = torch.zeros(B, dtype=torch.bool)
+        if self.swap_allowed:
+            swap = x[batch_ptr[1:] - 1, 2] != 0                                             # :340, :349
+            logit = self.my_modules["swap_linear"](parts).reshape(-1)                       # :338-339
+        pieces, gids = [], []
+        for g in range(B):
+            pieces.append(pi[int(batch_ptr[g]) + 2:int(batch_ptr[g + 1])])
+            cnt = int(n[g]) - 2
+            if bool(swap[g]):
+                pieces.append(logit[g:g + 1])
+                cnt += 1
+            gids.append(torch.full((cnt,), g, dtype=torch.long))
+        out_gi = torch.cat(gids)
+        out_ptr = batch_ptr - 2 * torch.arange(B + 1) + torch.cat([torch.zeros(1, dtype=torch.long), swap.long().cumsum(0)])  # :351, :371
+        return scatter_log_softmax(torch.cat(pieces), out_gi, B), value, out_gi, out_ptr    # :378-379

@@ -111,6 +111,18 @@ def import_reference_models():
     return ref_models
 
 
+def import_reference_torch_script_models():
+    """`GN0.torch_script_models` of the reference (HexAra networks), imported where it lies on the PyG stand-in; None when
+    /root/reference is not mounted."""
+    if not os.path.isdir(os.path.join(REFERENCE_ROOT, "GN0")):
+        return None
+    for p in (REFERENCE_ROOT, PYG_STUB):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import GN0.torch_script_models as ref
+    return ref
+
+
 def hash_uniform(name: str, shape, seed: int = 0) -> torch.Tensor:
     """U(-1, 1) values that depend only on (name, seed, element index): splitmix64 in integer arithmetic, so the golden
     weights are reproducible on any box / library version without being stored."""
