@@ -68,7 +68,7 @@ struct AraWs { int64_t degf, zero, bias, img, act, pi, total; int64_t act_stride
 AraWs ara_ws(const AraDims& d, const AraMap& m, int64_t N) {
   AraWs w;
   int64_t o = 0;
-  w.degf = o; o += align_up(N * 4, 256);
+  w.degf = o; o += align_up(2 * N * 4, 256);   // max(deg, 1) | its reciprocal
   w.zero = o; o += 256;
   w.bias = o; o += align_up((int64_t)d.nconv * d.Hp * 4, 256);
   w.img = o;
@@ -292,7 +292,7 @@ int hexgnn_hexara_forward(const HexAraDesc* desc, const float* params, const flo
   auto sage = [&](int c, const float* in, float* out, int ldo, bool relu) {
     LwSageArgs a = {};
     a.x = in; a.ldx = Hp; a.N = N; a.Kp = Hp; a.Np = pm.cout[c] == 1 ? 16 : Hp; a.Nout = pm.cout[c];
-    a.rowptr = cv.rowptr; a.col = cv.col; a.degf = degf; a.adjoint = 0;
+    a.rowptr = cv.rowptr; a.col = cv.col; a.degf = degf; a.rdeg = degf + N; a.adjoint = 0;
     a.wimg = img + img_off[c];
     a.bias = bias + (int64_t)c * Hp;
     a.out = out; a.ldo = ldo; a.relu = relu ? 1 : 0;

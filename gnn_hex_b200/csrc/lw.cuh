@@ -28,7 +28,6 @@ constexpr int kLwMaxK = 112;                 // padded channel counts supported 
 constexpr int kLwMaxPack = 40;               // weight-image entries per pack launch
 
 inline int lw_pad16(int c) { return (c + 15) / 16 * 16; }
-inline int64_t lw_blocks(int64_t N) { return (N + kLwRows - 1) / kLwRows; }
 // bytes of the weight image of one layer direction: 2 Kp / 16 stages of Np * 64 bytes
 inline int64_t lw_img_bytes(int Kp, int Np) { return (int64_t)(2 * Kp / 16) * Np * 64; }
 
@@ -38,6 +37,7 @@ struct LwSageArgs {
   int Kp, Np, Nout;                 // padded in / out channels (multiples of 16, <= 112), real out channels
   const int* rowptr; const int* col;
   const float* degf;                // [N] max(deg, 1) as float
+  const float* rdeg;                // [N] 1 / max(deg, 1)
   int adjoint;                      // 0: aggr_i = (sum_j x_j) / deg_i   1: aggr_j = sum_i x_i / deg_i
   const uint8_t* wimg;              // lw_img_bytes(Kp, Np)
   const float* bias;                // [Np] or nullptr
@@ -50,8 +50,11 @@ struct LwSageArgs {
   float* agg_out; int lda;          // the aggregated half of the operand rows ([N][lda], columns [0, Kp)), or nullptr
   float* raw_out; int ldr;          // a copy of `out` BEFORE the mask (the embedding-gradient tap), or nullptr
   int* status;                      // HEXGNN_ST_* bits
+  int rows;                         // set by the launcher: live rows per block (lw_sage_rows)
 };
 int launch_lw_sage(const LwSageArgs& a, cudaStream_t st);
+int lw_sage_rows(int64_t N);        // rows per block of lw_sage_kernel for N node rows
+int lw_sage_blocks(int64_t N);      // its grid size == number of statistics partial sums it writes
 
 // Weight image of one layer direction.  value(c, k) of the [Np x 2Kp] operand, c = output column of the GEMM, k = contraction
 // index: k < Kp -> W_self, else W_agg (k - Kp); transposed == 0: W[c * ld + k] (forward: lin.weight[out][in]);
@@ -74,7 +77,7 @@ struct LwPackArgs {
 };
 int launch_lw_pack(const LwPackArgs& a, cudaStream_t st);
 
-// degf[i] = max(deg_i, 1); also zeroes `zero_words` 32-bit words at `zero` (absmax slots, status scratch)
+// degf[i] = max(deg_i, 1), degf[N + i] = 1 / degf[i]; also zeroes `zero_words` 32-bit words at `zero` (absmax slots, status scratch)
 int launch_lw_prepare(const int* rowptr, int64_t N, float* degf, unsigned* zero, int zero_words, cudaStream_t st);
 
 // First layer (C_in <= 4 input channels read from x[:, xoff : xoff + C_in], row pitch ldx) on the CUDA cores:

@@ -416,20 +416,33 @@ __global__ void __launch_bounds__(kDwThreads2, 1) lw_dw_kernel(const __grid_cons
       mbar_wait(&bar_empty[stg], ((it / kDwStages2) & 1) ^ 1);
       uint8_t* base = smem + stg * stage_bytes;
       const int64_t r0 = c * kDwChunk;
-      for (int i = tid; i < kDwChunk * per_row; i += kDwLoadThreads) {
+      // all global loads of the chunk are issued before the first is used (one L2 / HBM latency per chunk, not one per element)
+      constexpr int kIter = 6;                              // 16 rows x (Hp + 2Hp) / 4 float4 <= 1344 <= 6 x 256 threads
+      float4 v[kIter];
+#pragma unroll
+      for (int u = 0; u < kIter; ++u) {
+        const int i = tid + u * kDwLoadThreads;
+        v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (i < kDwChunk * per_row) {
+          const int r = i / per_row, q = i - r * per_row;
+          const int64_t gr = r0 + r;
+          if (gr < a.N) v[u] = q < xv ? *(const float4*)(X + gr * Hp + 4 * q) : *(const float4*)(Y + gr * N2 + 4 * (q - xv));
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kIter; ++u) {
+        const int i = tid + u * kDwLoadThreads;
+        if (i >= kDwChunk * per_row) break;
         const int r = i / per_row, q = i - r * per_row;
-        const int64_t gr = r0 + r;
         const bool isx = q < xv;
         const int ch = 4 * (isx ? q : q - xv);
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (gr < a.N) v = isx ? *(const float4*)(X + gr * Hp + ch) : *(const float4*)(Y + gr * N2 + ch);
         const uint32_t off = (uint32_t)(ch >> 5) * kDwBlkB + (uint32_t)(r >> 2) * 512u + (uint32_t)(r & 3) * 128u +
                              ((uint32_t)(((ch & 31) >> 3) ^ (r & 3)) << 5) + (uint32_t)(ch & 7) * 4u;
         uint8_t* dst = base + (isx ? 0 : a_bytes) + off;
         float4 l;
-        l.x = tf32_rn(v.x - tf32_trunc(v.x)); l.y = tf32_rn(v.y - tf32_trunc(v.y));
-        l.z = tf32_rn(v.z - tf32_trunc(v.z)); l.w = tf32_rn(v.w - tf32_trunc(v.w));
-        *(float4*)dst = v;
+        l.x = tf32_rn(v[u].x - tf32_trunc(v[u].x)); l.y = tf32_rn(v[u].y - tf32_trunc(v[u].y));
+        l.z = tf32_rn(v[u].z - tf32_trunc(v[u].z)); l.w = tf32_rn(v[u].w - tf32_trunc(v[u].w));
+        *(float4*)dst = v[u];
         *(float4*)(dst + half_bytes) = l;
       }
       // the rest of the X block that holds channel Hp: ones for live rows, zeros elsewhere (lo image: zeros)
@@ -480,7 +493,7 @@ __global__ void __launch_bounds__(kDwThreads2, 1) lw_dw_kernel(const __grid_cons
 
 // ---- first layer's weight gradients (C_in <= 4) on the CUDA cores -----------------------------------------------------------
 //   d lin_l.W[c][k] = sum_i dpre_i[c] mean_i[k],  d lin_l.b[c] = sum_i dpre_i[c],  d lin_r.W[c][k] = sum_i dpre_i[c] x_i[k]
-constexpr int kD0Threads = 128, kD0Rows = 256;
+constexpr int kD0Threads = 128, kD0Rows = 64;
 struct LwDw0Args {
   const float* x; int ldx, xoff, Cin;
   int64_t N;
@@ -566,7 +579,10 @@ __global__ void lw_reduce_small_kernel(const __grid_constant__ LwReduceArgs a) {
   for (int i = gtid; i < H2 * 4 * H; i += gsz) {
     const int k = i / (4 * H), q = i - k * 4 * H;
     float t = 0.f;
-    for (int g = 0; g < a.B; ++g) t = fmaf(a.hrec[(int64_t)g * R.total + R.dt + k], a.hrec[(int64_t)g * R.total + R.pooled + q], t);
+    const float* pd = a.hrec + R.dt + k;
+    const float* pp = a.hrec + R.pooled + q;
+#pragma unroll 8
+    for (int g = 0; g < a.B; ++g) t = fmaf(pd[(int64_t)g * R.total], pp[(int64_t)g * R.total], t);   // fixed order (graph order)
     v0w[i] = t;
   }
   for (int i = gtid; i < H + 1 + H2 + H2 + 1; i += gsz) {
@@ -624,7 +640,7 @@ LwBwdWs lw_bwd_ws(const Dims& d, int64_t N, int64_t B, bool norm) {
   w.G = bwd_grid_ctas() / (d.Lt - 1 > 0 ? d.Lt - 1 : 1);
   if (w.G < 1) w.G = 1;
   w.nbn = (int)((N + kNbRows - 1) / kNbRows);
-  w.degf = o; o += align_up(N * 4, 256);
+  w.degf = o; o += align_up(2 * N * 4, 256);   // max(deg, 1) | its reciprocal
   w.zero = o; o += 256;
   w.imgT = o; o += align_up((int64_t)(d.Lt - 1) * lw_img_bytes(d.Hp, d.Hp), 256);
   w.y = o; o += align_up((int64_t)d.Lt * N * 2 * d.Hp * 4, 256);
@@ -722,7 +738,7 @@ int launch_backward_lw(const Dims& d, const ParamMap& pm, const float* params, c
     if (rc) return rc;
     if (norm) {
       const int s = Lt - 1;
-      rc = norm_bwd(prebuf(s), hbuf(s), s < L ? s : s + 1, s, s == 0 ? lw_layer0_blocks(N) : (int)lw_blocks(N),
+      rc = norm_bwd(prebuf(s), hbuf(s), s < L ? s : s + 1, s, s == 0 ? lw_layer0_blocks(N) : lw_sage_blocks(N),
                     s < L ? s : s + 1, Ys(s), N2, absmax + s);
       if (rc) return rc;
     }
@@ -731,7 +747,7 @@ int launch_backward_lw(const Dims& d, const ParamMap& pm, const float* params, c
   for (int s = Lt - 1; s >= 1; --s) {
     LwSageArgs a = {};
     a.x = Ys(s); a.ldx = N2; a.N = N; a.Kp = Hp; a.Np = Hp; a.Nout = H;
-    a.rowptr = cv.rowptr; a.col = cv.col; a.degf = degf; a.adjoint = 1;
+    a.rowptr = cv.rowptr; a.col = cv.col; a.degf = degf; a.rdeg = degf + N; a.adjoint = 1;
     a.wimg = imgT + (int64_t)(s - 1) * lw_img_bytes(Hp, Hp);
     a.in_absmax = absmax + s;
     a.agg_out = Ys(s) + Hp; a.lda = N2;
@@ -754,7 +770,7 @@ int launch_backward_lw(const Dims& d, const ParamMap& pm, const float* params, c
         if (rc) return rc;
       }
       const int t = s - 1;   // through relu(LN_t(pre_t))
-      rc = norm_bwd(prebuf(t), hbuf(t), t < L ? t : t + 1, t, t == 0 ? lw_layer0_blocks(N) : (int)lw_blocks(N),
+      rc = norm_bwd(prebuf(t), hbuf(t), t < L ? t : t + 1, t, t == 0 ? lw_layer0_blocks(N) : lw_sage_blocks(N),
                     t < L ? t : t + 1, Ys(t), N2, absmax + t);
       if (rc) return rc;
     }
@@ -787,7 +803,7 @@ int launch_backward_lw(const Dims& d, const ParamMap& pm, const float* params, c
     rc = launch_pdl2(lw_reduce_sage_kernel, dim3(32, (unsigned)(Lt - 1)), dim3(256), 0, st, ra);
     if (rc) return rc;
   }
-  rc = launch_pdl2(lw_reduce_small_kernel, dim3(64), dim3(256), 0, st, ra);
+  rc = launch_pdl2(lw_reduce_small_kernel, dim3(2 * (unsigned)bwd_grid_ctas()), dim3(128), 0, st, ra);
   return rc;
 }
 

@@ -102,7 +102,7 @@ __global__ void lw_clear_status_kernel(int* status, int bits) { atomicAnd(status
 LwModelWs lw_model_ws(const Dims& d, int64_t N, bool backward) {
   LwModelWs w;
   int64_t o = 0;
-  w.degf = o; o += align_up(N * 4, 256);
+  w.degf = o; o += align_up(2 * N * 4, 256);   // max(deg, 1) | its reciprocal
   w.zero = o; o += 256;
   w.bias = o; o += align_up((int64_t)d.Lt * d.Hp * 4, 256);
   w.img = o; o += align_up((int64_t)(d.Lt - 1) * lw_img_bytes(d.Hp, d.Hp), 256);
@@ -201,7 +201,7 @@ int launch_forward_lw(const Dims& d, const ParamMap& pm, const float* params, co
     LwSageArgs a = {};
     a.x = (norm && s == L) ? emb2 : hbuf(s - 1); a.ldx = Hp; a.N = N;
     a.Kp = Hp; a.Np = Hp; a.Nout = H;
-    a.rowptr = cv.rowptr; a.col = cv.col; a.degf = degf; a.adjoint = 0;
+    a.rowptr = cv.rowptr; a.col = cv.col; a.degf = degf; a.rdeg = degf + N; a.adjoint = 0;
     a.wimg = img + (int64_t)(s - 1) * lw_img_bytes(Hp, Hp);
     a.bias = bias + (int64_t)s * Hp;
     a.out = norm ? prebuf(s) : hbuf(s); a.ldo = Hp;
@@ -212,7 +212,7 @@ int launch_forward_lw(const Dims& d, const ParamMap& pm, const float* params, co
     if (rc) return rc;
     if (norm) {
       const int idx = s < L ? s : s + 1;
-      rc = run_norm(prebuf(s), hbuf(s), idx, s, (int)lw_blocks(N), 1, s == L - 1 ? Lt : -1);
+      rc = run_norm(prebuf(s), hbuf(s), idx, s, lw_sage_blocks(N), 1, s == L - 1 ? Lt : -1);
       if (rc) return rc;
       if (s == L - 1) { rc = run_norm(hbuf(s), emb2, L, Lt, lw_norm_blocks(N), 0, -1); if (rc) return rc; }
     }

@@ -59,7 +59,7 @@ __global__ void __launch_bounds__(kLwThreads, 1) lw_sage_kernel(const __grid_con
   const uint32_t TM_A = 0, TM_D = 2 * Kp, TM_DS = 2 * Kp + Np;
   const uint32_t need = 2 * Kp + 2 * Np;
   const uint32_t TM_COLS = need <= 32 ? 32 : need <= 64 ? 64 : need <= 128 ? 128 : need <= 256 ? 256 : 512;
-  const int64_t row0 = (int64_t)blockIdx.x * kLwRows;
+  const int64_t row0 = (int64_t)blockIdx.x * a.rows;
 
   if (tid == 0) {
     for (int i = 0; i < nst; ++i) mbar_init(&bar_w[i], 1);
@@ -112,45 +112,55 @@ __global__ void __launch_bounds__(kLwThreads, 1) lw_sage_kernel(const __grid_con
         unscale = __uint_as_float((uint32_t)(e - 6) << 23);
       }
     }
-    // ---- phase G: [self | aggregated] rows -> staging ----------------------------------------------------
+    // ---- phase G1: this block's own rows -> staging (coalesced; they are the self half of the operand AND the source of
+    //      every in-block neighbour below: graphs are contiguous row ranges, so almost all neighbours live in the block) ----
     const int NV = Kp / 4;
+    const int R = a.rows;                                       // live rows of this block (<= 128, balanced over the SMs)
+    const int64_t rlo = row0, rhi = (row0 + R < a.N) ? row0 + R : a.N;
     for (int r = wid; r < kLwRows; r += kLwWorkWarps) {
       const int64_t gr = row0 + r;
-      float4 self = make_float4(0.f, 0.f, 0.f, 0.f), acc = self;
-      if (gr < a.N && lane < NV) {
+      if (lane < NV) {
+        float4 self = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (gr < rhi) self = *(const float4*)(a.x + gr * a.ldx + 4 * lane);
+        *(float4*)(stage + r * SP + 4 * lane) = self;
+      }
+    }
+    work_bar();
+    // ---- phase G2: aggregated half.  Neighbour rows come from the staged tile (shared memory) when they belong to this
+    //      block, from global memory (L2) otherwise; fixed summation order (CSR order) either way ---------------------
+    for (int r = wid; r < kLwRows; r += kLwWorkWarps) {
+      const int64_t gr = row0 + r;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (gr < rhi && lane < NV) {
         const float* xb = a.x + 4 * lane;
-        self = *(const float4*)(xb + gr * a.ldx);
+        const float* sb = stage + 4 * lane;
         const int b = a.rowptr[gr], e = a.rowptr[gr + 1];
-        int p = b;
         if (!a.adjoint) {
-          for (; p + 4 <= e; p += 4) {
-            const int j0 = a.col[p], j1 = a.col[p + 1], j2 = a.col[p + 2], j3 = a.col[p + 3];
-            const float4 v0 = *(const float4*)(xb + (int64_t)j0 * a.ldx), v1 = *(const float4*)(xb + (int64_t)j1 * a.ldx);
-            const float4 v2 = *(const float4*)(xb + (int64_t)j2 * a.ldx), v3 = *(const float4*)(xb + (int64_t)j3 * a.ldx);
-            acc.x = ((acc.x + v0.x) + v1.x) + v2.x + v3.x; acc.y = ((acc.y + v0.y) + v1.y) + v2.y + v3.y;
-            acc.z = ((acc.z + v0.z) + v1.z) + v2.z + v3.z; acc.w = ((acc.w + v0.w) + v1.w) + v2.w + v3.w;
-          }
-          for (; p < e; ++p) {
-            const float4 v = *(const float4*)(xb + (int64_t)a.col[p] * a.ldx);
+#pragma unroll 4
+          for (int p = b; p < e; ++p) {
+            const int64_t j = a.col[p];
+            float4 v;
+            if (j >= rlo && j < rhi) v = *(const float4*)(sb + (int)(j - rlo) * SP);
+            else v = *(const float4*)(xb + j * a.ldx);
             acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
           }
-          const float dg = a.degf[gr];
-          acc.x /= dg; acc.y /= dg; acc.z /= dg; acc.w /= dg;
+          // x * fl(1 / deg): within one ulp of the reference's division (a division per element costs ~45 instructions here)
+          const float rd = a.rdeg[gr];
+          acc.x *= rd; acc.y *= rd; acc.z *= rd; acc.w *= rd;
         } else {
-          for (; p < e; ++p) {
-            const int j = a.col[p];
-            const float dj = a.degf[j];
-            const float4 v = *(const float4*)(xb + (int64_t)j * a.ldx);
-            acc.x += v.x / dj; acc.y += v.y / dj; acc.z += v.z / dj; acc.w += v.w / dj;
+#pragma unroll 4
+          for (int p = b; p < e; ++p) {
+            const int64_t j = a.col[p];
+            const float rj = a.rdeg[j];
+            float4 v;
+            if (j >= rlo && j < rhi) v = *(const float4*)(sb + (int)(j - rlo) * SP);
+            else v = *(const float4*)(xb + j * a.ldx);
+            acc.x = fmaf(v.x, rj, acc.x); acc.y = fmaf(v.y, rj, acc.y); acc.z = fmaf(v.z, rj, acc.z); acc.w = fmaf(v.w, rj, acc.w);
           }
         }
         if (a.agg_out) *(float4*)(a.agg_out + gr * a.lda + 4 * lane) = acc;
       }
-      if (lane < NV) {
-        float* sr = stage + r * SP + 4 * lane;
-        *(float4*)sr = make_float4(self.x * ascale, self.y * ascale, self.z * ascale, self.w * ascale);
-        *(float4*)(sr + Kp) = make_float4(acc.x * ascale, acc.y * ascale, acc.z * ascale, acc.w * ascale);
-      }
+      if (lane < NV) *(float4*)(stage + r * SP + Kp + 4 * lane) = acc;
     }
     work_bar();
     // ---- phase A: staging -> fp16 split -> tensor memory ---------------------------------------------------
@@ -158,9 +168,13 @@ __global__ void __launch_bounds__(kLwThreads, 1) lw_sage_kernel(const __grid_con
     const int row = q4 * 32 + lane;
     const uint32_t trow = tbase + ((uint32_t)(q4 * 32) << 16);
     int range_bad = 0;
-    for (int g = slice; g < 2 * Kp / 8; g += 4) {
+    // a TMEM lane quarter without live rows (balanced blocks hold fewer than 128 rows) is left as it is: accumulator rows
+    // are independent, and nothing of a dead row is read back
+    const bool quarter_live = q4 * 32 < (int)(rhi - rlo);
+    for (int g = slice; quarter_live && g < 2 * Kp / 8; g += 4) {
       const float4 u0 = *(const float4*)(stage + row * SP + 8 * g), u1 = *(const float4*)(stage + row * SP + 8 * g + 4);
-      const float v[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
+      const float v[8] = {u0.x * ascale, u0.y * ascale, u0.z * ascale, u0.w * ascale,
+                          u1.x * ascale, u1.y * ascale, u1.z * ascale, u1.w * ascale};
       uint32_t hi4[4], lo4[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
@@ -180,10 +194,10 @@ __global__ void __launch_bounds__(kLwThreads, 1) lw_sage_kernel(const __grid_con
     mbar_wait(bar_mma, 0);
     tc_fence_after();
     const int64_t gr = row0 + row;
-    const bool live = gr < a.N;
+    const bool live = row < a.rows && gr < a.N;
     float s1 = 0.f, s2 = 0.f, mx = 0.f;
     const float poison = (range_bad && a.status) ? __int_as_float(0x7fc00000) : 0.f;
-    for (int g = slice; g < Np / 8; g += 4) {
+    for (int g = slice; quarter_live && g < Np / 8; g += 4) {
       float v[8], vs[8];
       tmem_ld8(trow + TM_D + 8 * g, v);
       tmem_ld8(trow + TM_DS + 8 * g, vs);
@@ -282,6 +296,7 @@ __global__ void lw_prepare_kernel(const int* __restrict__ rowptr, int64_t N, flo
   if (i < N) {
     const int d = rowptr[i + 1] - rowptr[i];
     degf[i] = (float)(d > 0 ? d : 1);
+    degf[N + i] = 1.0f / (float)(d > 0 ? d : 1);
   }
   if (i < zero_words) zero[i] = 0u;
 }
@@ -294,25 +309,34 @@ __global__ void __launch_bounds__(kL0Threads) lw_layer0_kernel(const __grid_cons
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int64_t row0 = (int64_t)blockIdx.x * kL0Rows;
+  // phase 1, one thread per row: self features and the neighbour mean (independent latency chains, not 8 rows per warp in turn)
+  __shared__ float feat[kL0Rows][8];
+  if (threadIdx.x < kL0Rows) {
+    const int64_t gr = row0 + threadIdx.x;
+    float self[4] = {0.f, 0.f, 0.f, 0.f}, mean[4] = {0.f, 0.f, 0.f, 0.f};
+    if (gr < a.N) {
+      const int b = a.rowptr[gr], e = a.rowptr[gr + 1];
+      for (int k = 0; k < a.Cin; ++k) self[k] = a.x[gr * a.ldx + a.xoff + k];
+      for (int p = b; p < e; ++p) {
+        const int64_t j = a.col[p];
+        for (int k = 0; k < a.Cin; ++k) mean[k] += a.x[j * a.ldx + a.xoff + k];
+      }
+      const float dg = a.degf[gr];
+      for (int k = 0; k < a.Cin; ++k) mean[k] /= dg;
+    }
+    for (int k = 0; k < 4; ++k) { feat[threadIdx.x][k] = mean[k]; feat[threadIdx.x][4 + k] = self[k]; }
+  }
+  __syncthreads();
   float s1 = 0.f, s2 = 0.f;
   for (int r = wid; r < kL0Rows; r += kL0Threads / 32) {
     const int64_t gr = row0 + r;
     if (gr >= a.N) break;
-    float self[4] = {0.f, 0.f, 0.f, 0.f}, mean[4] = {0.f, 0.f, 0.f, 0.f};
-    const int b = a.rowptr[gr], e = a.rowptr[gr + 1];
-    for (int k = 0; k < a.Cin; ++k) self[k] = a.x[gr * a.ldx + a.xoff + k];
-    for (int p = b; p < e; ++p) {
-      const int64_t j = a.col[p];
-      for (int k = 0; k < a.Cin; ++k) mean[k] += a.x[j * a.ldx + a.xoff + k];
-    }
-    const float dg = a.degf[gr];
-    for (int k = 0; k < a.Cin; ++k) mean[k] /= dg;
     for (int c = lane; c < a.Hp; c += 32) {
       float v = 0.f;
       if (c < a.H) {
         v = a.bl[c];
-        for (int k = 0; k < a.Cin; ++k) v = fmaf(a.wl[c * a.Cin + k], mean[k], v);
-        for (int k = 0; k < a.Cin; ++k) v = fmaf(a.wr[c * a.Cin + k], self[k], v);
+        for (int k = 0; k < a.Cin; ++k) v = fmaf(a.wl[c * a.Cin + k], feat[r][k], v);
+        for (int k = 0; k < a.Cin; ++k) v = fmaf(a.wr[c * a.Cin + k], feat[r][4 + k], v);
         if (a.relu) v = fmaxf(v, 0.f);
         s1 += v; s2 += v * v;
       }
@@ -404,7 +428,24 @@ int launch_pdl(K kern, dim3 grid, dim3 block, size_t smem, cudaStream_t st, cons
 
 }  // namespace
 
-int launch_lw_sage(const LwSageArgs& a, cudaStream_t st) {
+// Rows per block: 128, or -- when that needs more blocks than SMs -- the even split of the rows over k full waves of the SMs
+// (>= 64 rows: lw_stat_parts(N) slots always suffice for the per-block statistics).
+int lw_sage_rows(int64_t N) {
+  const int sms = bwd_grid_ctas();
+  const int64_t blocks = (N + kLwRows - 1) / kLwRows;
+  if (blocks <= sms) return kLwRows;
+  const int64_t k = (blocks + sms - 1) / sms;
+  int64_t r = (N + sms * k - 1) / (sms * k);
+  return (int)(r < 64 ? 64 : (r > kLwRows ? kLwRows : r));
+}
+int lw_sage_blocks(int64_t N) {
+  const int r = lw_sage_rows(N);
+  return (int)((N + r - 1) / r);
+}
+
+int launch_lw_sage(const LwSageArgs& a_in, cudaStream_t st) {
+  LwSageArgs a = a_in;
+  a.rows = lw_sage_rows(a.N);
   if (a.Kp < 16 || a.Kp > kLwMaxK || a.Kp % 16 || a.Np < 16 || a.Np > kLwMaxK || a.Np % 16 || a.ldx % 4 || a.ldo % 4 ||
       (a.mask_src && a.ldm % 4) || (a.agg_out && a.lda % 4)) {
     set_error("lw_sage: unsupported shape Kp=%d Np=%d ldx=%d ldo=%d", a.Kp, a.Np, a.ldx, a.ldo);
@@ -417,7 +458,7 @@ int launch_lw_sage(const LwSageArgs& a, cudaStream_t st) {
     HEX_CUDA_CHECK(cudaFuncSetAttribute(lw_sage_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
     max_set = 232448;
   }
-  return launch_pdl(lw_sage_kernel, dim3((unsigned)lw_blocks(a.N)), dim3(kLwThreads), (size_t)L.total, st, a);
+  return launch_pdl(lw_sage_kernel, dim3((unsigned)lw_sage_blocks(a.N)), dim3(kLwThreads), (size_t)L.total, st, a);
 }
 
 int launch_lw_pack(const LwPackArgs& a, cudaStream_t st) {
