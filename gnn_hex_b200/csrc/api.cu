@@ -4,6 +4,7 @@
 #include <vector>
 #include "common.cuh"
 #include "sage_tc.cuh"
+#include "lw.cuh"
 
 namespace hexgnn {
 
@@ -393,6 +394,7 @@ int hexgnn_debug_phases(int32_t which, int64_t* host_out, int32_t n) {
   if (!host_out || n < 1) { set_error("debug_phases: bad argument"); return HEXGNN_E_BADARG; }
   if (which == 0) return debug_read_fwd_phases((long long*)host_out, n);
   if (which == 1) return debug_read_bwd_phases((long long*)host_out, n);
+  if (which == 2) return debug_read_lw_phases((long long*)host_out, n);
   set_error("debug_phases: unknown kernel %d", which);
   return HEXGNN_E_BADARG;
 }

@@ -133,6 +133,7 @@ __global__ void __launch_bounds__(kAhThreads) hexara_head_kernel(const __grid_co
   // pooling over ALL rows of the graph, terminals included (:320-324)
   for (int c = tid; c < H; c += kAhThreads) {
     float sum = 0.f, mx = -INFINITY, mn = INFINITY;
+#pragma unroll 4
     for (int i = 0; i < n; ++i) {
       const float v = a.vemb[(int64_t)(r0 + i) * Hp + c];
       sum += v; mx = fmaxf(mx, v); mn = fminf(mn, v);

@@ -53,6 +53,7 @@ struct LwSageArgs {
   int rows;                         // set by the launcher: live rows per block (lw_sage_rows)
 };
 int launch_lw_sage(const LwSageArgs& a, cudaStream_t st);
+int debug_read_lw_phases(long long* host, int n);   // HEXGNN_PHASES builds: summed per-phase cycles of lw_sage_kernel
 int lw_sage_rows(int64_t N);        // rows per block of lw_sage_kernel for N node rows
 int lw_sage_blocks(int64_t N);      // its grid size == number of statistics partial sums it writes
 

@@ -108,6 +108,7 @@ __global__ void __launch_bounds__(kHbThreads) lw_head_bwd_kernel(const __grid_co
     for (int c = tid; c < H; c += kHbThreads) {
       float sum = 0.f, mx = -INFINITY, mn = INFINITY;
       int imx = 0, imn = 0;
+#pragma unroll 4
       for (int i = 0; i < n; ++i) {
         const float v = a.hin[(int64_t)(r0 + i) * Hp + c];
         sum += v;
@@ -158,7 +159,10 @@ __global__ void __launch_bounds__(kHbThreads) lw_head_bwd_kernel(const __grid_co
   // (e) the record
   for (int c = tid; c < Hp; c += kHbThreads) {
     float s = 0.f;
-    if (c < H) for (int i = 0; i < n; ++i) s = fmaf(a.du[r0 + i], a.hin[(int64_t)(r0 + i) * Hp + c], s);
+    if (c < H) {
+#pragma unroll 4
+      for (int i = 0; i < n; ++i) s = fmaf(a.du[r0 + i], a.hin[(int64_t)(r0 + i) * Hp + c], s);
+    }
     rec[R.glin + c] = s;
   }
   if (wid == 0) {
@@ -410,52 +414,70 @@ __global__ void __launch_bounds__(kDwThreads2, 1) lw_dw_kernel(const __grid_cons
     // image byte of (channel ch, row r) inside a chunk: (ch/32)*2048 + (r/4)*512 + (r%4)*128 + ((((ch%32)/8) ^ (r%4))*32) + (ch%8)*4
     const int xv = Hp / 4, yv = N2 / 4;                     // float4 per row of X / Y
     const int per_row = xv + yv;
-    uint32_t it = 0;
-    for (int64_t c = grp; c < nchunks; c += a.G, ++it) {
-      const int stg = it % kDwStages2;
-      mbar_wait(&bar_empty[stg], ((it / kDwStages2) & 1) ^ 1);
-      uint8_t* base = smem + stg * stage_bytes;
-      const int64_t r0 = c * kDwChunk;
-      // all global loads of the chunk are issued before the first is used (one L2 / HBM latency per chunk, not one per element)
-      constexpr int kIter = 6;                              // 16 rows x (Hp + 2Hp) / 4 float4 <= 1344 <= 6 x 256 threads
-      float4 v[kIter];
+    // A thread moves the same (row, float4) elements of every chunk: the index arithmetic (divisions by a run-time row
+    // length, the swizzled image offset) is done once, outside the chunk loop.
+    constexpr int kIter = 6;                                // 16 rows x (Hp + 2Hp) / 4 float4 <= 1344 <= 6 x 256 threads
+    int64_t goff[kIter];                                    // float offset from the chunk's first row of X / Y; < 0: no element
+    uint32_t soff[kIter];                                   // byte offset inside the stage (hi image; lo = + half_bytes)
+    int rrow[kIter];
+    uint32_t isx_mask = 0;
 #pragma unroll
-      for (int u = 0; u < kIter; ++u) {
-        const int i = tid + u * kDwLoadThreads;
-        v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (i < kDwChunk * per_row) {
-          const int r = i / per_row, q = i - r * per_row;
-          const int64_t gr = r0 + r;
-          if (gr < a.N) v[u] = q < xv ? *(const float4*)(X + gr * Hp + 4 * q) : *(const float4*)(Y + gr * N2 + 4 * (q - xv));
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < kIter; ++u) {
-        const int i = tid + u * kDwLoadThreads;
-        if (i >= kDwChunk * per_row) break;
+    for (int u = 0; u < kIter; ++u) {
+      const int i = tid + u * kDwLoadThreads;
+      goff[u] = -1; soff[u] = 0; rrow[u] = 0;
+      if (i < kDwChunk * per_row) {
         const int r = i / per_row, q = i - r * per_row;
         const bool isx = q < xv;
         const int ch = 4 * (isx ? q : q - xv);
-        const uint32_t off = (uint32_t)(ch >> 5) * kDwBlkB + (uint32_t)(r >> 2) * 512u + (uint32_t)(r & 3) * 128u +
-                             ((uint32_t)(((ch & 31) >> 3) ^ (r & 3)) << 5) + (uint32_t)(ch & 7) * 4u;
-        uint8_t* dst = base + (isx ? 0 : a_bytes) + off;
+        goff[u] = isx ? (int64_t)r * Hp + ch : (int64_t)r * N2 + ch;
+        soff[u] = (isx ? 0u : (uint32_t)a_bytes) + (uint32_t)(ch >> 5) * kDwBlkB + (uint32_t)(r >> 2) * 512u +
+                  (uint32_t)(r & 3) * 128u + ((uint32_t)(((ch & 31) >> 3) ^ (r & 3)) << 5) + (uint32_t)(ch & 7) * 4u;
+        rrow[u] = r;
+        if (isx) isx_mask |= 1u << u;
+      }
+    }
+    // the rest of the X block that holds channel Hp (ones for live rows, zeros elsewhere; lo image: zeros): 16 x rem <= 512
+    const int rem = CB * 32 - Hp;
+    uint32_t ooff[2]; int orow[2]; bool oone[2], ohave[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int i = tid + u * kDwLoadThreads;
+      ohave[u] = i < kDwChunk * rem;
+      const int r = ohave[u] ? i / rem : 0, ch = Hp + (ohave[u] ? i - r * rem : 0);
+      ooff[u] = (uint32_t)(ch >> 5) * kDwBlkB + (uint32_t)(r >> 2) * 512u + (uint32_t)(r & 3) * 128u +
+                ((uint32_t)(((ch & 31) >> 3) ^ (r & 3)) << 5) + (uint32_t)(ch & 7) * 4u;
+      orow[u] = r; oone[u] = ch == Hp;
+    }
+    uint32_t it = 0;
+    for (int64_t c = grp; c < nchunks; c += a.G, ++it) {
+      const int stg = it % kDwStages2;
+      const int64_t r0 = c * kDwChunk;
+      const float* Xc = X + r0 * Hp;
+      const float* Yc = Y + r0 * N2;
+      // all global loads of the chunk are issued before the ring slot is even free (one L2 / HBM latency per chunk)
+      float4 v[kIter];
+#pragma unroll
+      for (int u = 0; u < kIter; ++u) {
+        v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (goff[u] >= 0 && r0 + rrow[u] < a.N) v[u] = *(const float4*)(((isx_mask >> u) & 1u ? Xc : Yc) + goff[u]);
+      }
+      mbar_wait(&bar_empty[stg], ((it / kDwStages2) & 1) ^ 1);
+      uint8_t* base = smem + stg * stage_bytes;
+#pragma unroll
+      for (int u = 0; u < kIter; ++u) {
+        if (goff[u] < 0) continue;
+        uint8_t* dst = base + soff[u];
         float4 l;
         l.x = tf32_rn(v[u].x - tf32_trunc(v[u].x)); l.y = tf32_rn(v[u].y - tf32_trunc(v[u].y));
         l.z = tf32_rn(v[u].z - tf32_trunc(v[u].z)); l.w = tf32_rn(v[u].w - tf32_trunc(v[u].w));
         *(float4*)dst = v[u];
         *(float4*)(dst + half_bytes) = l;
       }
-      // the rest of the X block that holds channel Hp: ones for live rows, zeros elsewhere (lo image: zeros)
-      {
-        const int rem = CB * 32 - Hp;                       // channels [Hp, CB*32)
-        for (int i = tid; i < kDwChunk * rem; i += kDwLoadThreads) {
-          const int r = i / rem, ch = Hp + (i - r * rem);
-          const int64_t gr = r0 + r;
-          const uint32_t off = (uint32_t)(ch >> 5) * kDwBlkB + (uint32_t)(r >> 2) * 512u + (uint32_t)(r & 3) * 128u +
-                               ((uint32_t)(((ch & 31) >> 3) ^ (r & 3)) << 5) + (uint32_t)(ch & 7) * 4u;
-          *(float*)(base + off) = (ch == Hp && gr < a.N) ? 1.0f : 0.f;
-          *(float*)(base + half_bytes + off) = 0.f;
-        }
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        if (!ohave[u]) continue;
+        *(float*)(base + ooff[u]) = (oone[u] && r0 + orow[u] < a.N) ? 1.0f : 0.f;
+        *(float*)(base + half_bytes + ooff[u]) = 0.f;
       }
       fence_proxy_async();
       mbar_arrive(&bar_full[stg]);
@@ -568,23 +590,53 @@ __global__ void lw_reduce_sage_kernel(const __grid_constant__ LwReduceArgs a) {
     else if (!which) bl[c] = t;
   }
 }
+// value MLP first weight: d W0[k][q] = sum_g dt_g[k] * pooled_g[q], graphs in order (a [H2 x B] x [B x 4H] product, staged
+// through shared memory in 128-graph chunks; one block per 32 columns q)
+constexpr int kV0Threads = 256, kV0Q = 32, kV0G = 128, kV0K = 64;
+__global__ void __launch_bounds__(kV0Threads) lw_reduce_v0w_kernel(const __grid_constant__ LwReduceArgs a) {
+  __shared__ float sd[kV0G][kV0K];
+  __shared__ float sp[kV0G][kV0Q];
+  pdl_wait();
+  pdl_launch_dependents();
+  const int H = a.d.H, H2 = a.d.H2;
+  const int head = (a.x[2] == 1.0f) ? 0 : 1;
+  const HeadRec R = head_rec(a.d);
+  const int tid = threadIdx.x, ql = tid & 31, kb = tid >> 5;      // outputs of this thread: k = kb + 8u, column q0 + ql
+  const int q0 = blockIdx.x * kV0Q;
+  float acc[kV0K / 8];
+#pragma unroll
+  for (int u = 0; u < kV0K / 8; ++u) acc[u] = 0.f;
+  for (int g0 = 0; g0 < a.B; g0 += kV0G) {
+    __syncthreads();
+    for (int i = tid; i < kV0G * kV0K; i += kV0Threads) {
+      const int g = i / kV0K, k = i - g * kV0K;
+      sd[g][k] = (g0 + g < a.B && k < H2) ? a.hrec[(int64_t)(g0 + g) * R.total + R.dt + k] : 0.f;
+    }
+    for (int i = tid; i < kV0G * kV0Q; i += kV0Threads) {
+      const int g = i / kV0Q, q = q0 + (i - g * kV0Q);
+      sp[g][i - g * kV0Q] = (g0 + g < a.B && q < 4 * H) ? a.hrec[(int64_t)(g0 + g) * R.total + R.pooled + q] : 0.f;
+    }
+    __syncthreads();
+    for (int g = 0; g < kV0G; ++g) {
+      const float pq = sp[g][ql];
+#pragma unroll
+      for (int u = 0; u < kV0K / 8; ++u) acc[u] = fmaf(sd[g][kb + 8 * u], pq, acc[u]);
+    }
+  }
+  float* v0w = a.grad + a.pm.v0_w[head];
+  if (q0 + ql < 4 * H) {
+#pragma unroll
+    for (int u = 0; u < kV0K / 8; ++u)
+      if (kb + 8 * u < H2) v0w[(int64_t)(kb + 8 * u) * 4 * H + q0 + ql] = acc[u];
+  }
+}
+
 __global__ void lw_reduce_small_kernel(const __grid_constant__ LwReduceArgs a) {
   pdl_wait();
   const int H = a.d.H, Hp = a.d.Hp, H2 = a.d.H2;
   const int head = (a.x[2] == 1.0f) ? 0 : 1;
   const HeadRec R = head_rec(a.d);
   const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gsz = gridDim.x * blockDim.x;
-  // value MLP first weight: sum_g dt_g (x) pooled_g
-  float* v0w = a.grad + a.pm.v0_w[head];
-  for (int i = gtid; i < H2 * 4 * H; i += gsz) {
-    const int k = i / (4 * H), q = i - k * 4 * H;
-    float t = 0.f;
-    const float* pd = a.hrec + R.dt + k;
-    const float* pp = a.hrec + R.pooled + q;
-#pragma unroll 8
-    for (int g = 0; g < a.B; ++g) t = fmaf(pd[(int64_t)g * R.total], pp[(int64_t)g * R.total], t);   // fixed order (graph order)
-    v0w[i] = t;
-  }
   for (int i = gtid; i < H + 1 + H2 + H2 + 1; i += gsz) {
     int off; float* dst;
     if (i < H) { off = R.glin + i; dst = a.grad + a.pm.lin_w[head] + i; }
@@ -593,6 +645,7 @@ __global__ void lw_reduce_small_kernel(const __grid_constant__ LwReduceArgs a) {
     else if (i < H + 1 + 2 * H2) { off = R.gv1 + (i - H - 1 - H2); dst = a.grad + a.pm.v1_w[head] + (i - H - 1 - H2); }
     else { off = R.gv1b; dst = a.grad + a.pm.v1_b[head]; }
     float t = 0.f;
+#pragma unroll 8
     for (int g = 0; g < a.B; ++g) t += a.hrec[(int64_t)g * R.total + off];
     *dst = t;
   }
@@ -600,6 +653,7 @@ __global__ void lw_reduce_small_kernel(const __grid_constant__ LwReduceArgs a) {
   for (int i = gtid; i < 5 * H; i += gsz) {
     const int row = i / H, c = i - row * H;
     float t = 0.f;
+#pragma unroll 8
     for (int b = 0; b < a.nblk0; ++b) t += a.part0[((int64_t)b * 5 + row) * Hp + c];
     if (row < 2) a.grad[sage_wl(a.pm, 0, 0) + (int64_t)c * 2 + row] = t;
     else if (row == 2) a.grad[sage_bl(a.pm, 0, 0, H) + c] = t;
@@ -611,6 +665,7 @@ __global__ void lw_reduce_small_kernel(const __grid_constant__ LwReduceArgs a) {
     for (int i = gtid; i < a.n_norm * 2 * H; i += gsz) {
       const int j = i / (2 * H), rem = i - j * 2 * H, which = rem / H, c = rem - which * H;
       float t = 0.f;
+#pragma unroll 8
       for (int b = 0; b < a.nbn; ++b) t += a.gb_part[(((int64_t)j * a.nbn + b) * 2 + which) * Hp + c];
       const int idx = j <= L ? j : j + head * Lh;            // slots: body 0..L-1, after_embed L, head layers L+1..L+Lh
       a.gnorm[((int64_t)idx * 2 + which) * H + c] = t;
@@ -803,7 +858,10 @@ int launch_backward_lw(const Dims& d, const ParamMap& pm, const float* params, c
     rc = launch_pdl2(lw_reduce_sage_kernel, dim3(32, (unsigned)(Lt - 1)), dim3(256), 0, st, ra);
     if (rc) return rc;
   }
-  rc = launch_pdl2(lw_reduce_small_kernel, dim3(2 * (unsigned)bwd_grid_ctas()), dim3(128), 0, st, ra);
+  if (d.H2 > kV0K) { set_error("backward_lw: hidden=%d not supported by the value-MLP reduction", H); return HEXGNN_E_UNSUPPORTED; }
+  rc = launch_pdl2(lw_reduce_v0w_kernel, dim3((unsigned)((4 * H + kV0Q - 1) / kV0Q)), dim3(kV0Threads), 0, st, ra);
+  if (rc) return rc;
+  rc = launch_pdl2(lw_reduce_small_kernel, dim3(64), dim3(128), 0, st, ra);
   return rc;
 }
 

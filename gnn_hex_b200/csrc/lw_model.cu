@@ -56,6 +56,7 @@ __global__ void __launch_bounds__(kHeadThreads) lw_head_kernel(const __grid_cons
   if (a.flags & HEXGNN_ADV_ONLY) return;
   for (int c = tid; c < H; c += kHeadThreads) {
     float sum = 0.f, mx = -INFINITY, mn = INFINITY;
+#pragma unroll 4
     for (int i = 0; i < n; ++i) {
       const float v = a.hin[(int64_t)(r0 + i) * Hp + c];
       sum += v; mx = fmaxf(mx, v); mn = fminf(mn, v);

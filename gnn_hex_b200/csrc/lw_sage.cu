@@ -28,7 +28,7 @@ __device__ __forceinline__ double warp_sum_d(double v) {
 }
 
 struct LwSmem {
-  int off_w, off_stage, off_bar, off_red, total;
+  int off_w, off_stage, off_bar, off_red, off_bias, off_rp, off_col, ncol, total;
   int SP;      // staging row pitch (floats)
   int nst;     // weight stages
 };
@@ -40,9 +40,21 @@ __host__ __device__ inline LwSmem lw_smem(int Kp, int Np) {
   s.off_stage = s.nst * Np * 64;
   s.off_bar = s.off_stage + kLwRows * s.SP * 4;
   s.off_red = s.off_bar + 16 * 8 + 16;                 // <= 14 stage barriers + bar_a + bar_mma, tmem slot
-  s.total = s.off_red + kLwWorkWarps * 2 * 8;
+  s.off_bias = s.off_red + kLwWorkWarps * 2 * 8;        // bias row (Np floats)
+  s.off_rp = s.off_bias + kLwMaxK * 4;                  // CSR row pointers of the block's rows (<= 129)
+  s.off_col = s.off_rp + 132 * 4;                       // ... and their column indices (as many as fit, <= 3072)
+  const int room = (232448 - s.off_col) / 4;
+  s.ncol = room < 3072 ? (room < 0 ? 0 : room) : 3072;
+  s.total = s.off_col + s.ncol * 4;
   return s;
 }
+
+#ifdef HEXGNN_PHASES
+__device__ unsigned long long g_lw_phase[8];   // summed over CTAs: [0] setup, [1] G1, [2] G2, [3] A, [4] wait MMA, [5] E, [6] CTAs
+#define LW_STAMP(k) do { if (tid == 0) { const long long t_ = clock64(); atomicAdd(&g_lw_phase[k], (unsigned long long)(t_ - t_prev)); t_prev = t_; } } while (0)
+#else
+#define LW_STAMP(k) do { } while (0)
+#endif
 
 __global__ void __launch_bounds__(kLwThreads, 1) lw_sage_kernel(const __grid_constant__ LwSageArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
@@ -50,20 +62,28 @@ __global__ void __launch_bounds__(kLwThreads, 1) lw_sage_kernel(const __grid_con
   const LwSmem L = lw_smem(Kp, Np);
   float* stage = (float*)(smem + L.off_stage);
   uint64_t* bar_w = (uint64_t*)(smem + L.off_bar);
-  uint64_t* bar_a = bar_w + 14;
+  uint64_t* bar_a = bar_w + 14;        // self half of the A operand is in tensor memory
   uint64_t* bar_mma = bar_w + 15;
-  uint32_t* tmem_slot = (uint32_t*)(bar_w + 16);
+  uint64_t* bar_a1 = bar_w + 16;       // aggregated half
+  uint32_t* tmem_slot = (uint32_t*)(bar_w + 17);
   double* red = (double*)(smem + L.off_red);
+  float* s_bias = (float*)(smem + L.off_bias);
+  int* s_rp = (int*)(smem + L.off_rp);
+  int* s_col = (int*)(smem + L.off_col);
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const int SP = L.SP, nst = L.nst;
   const uint32_t TM_A = 0, TM_D = 2 * Kp, TM_DS = 2 * Kp + Np;
   const uint32_t need = 2 * Kp + 2 * Np;
   const uint32_t TM_COLS = need <= 32 ? 32 : need <= 64 ? 64 : need <= 128 ? 128 : need <= 256 ? 256 : 512;
   const int64_t row0 = (int64_t)blockIdx.x * a.rows;
+#ifdef HEXGNN_PHASES
+  long long t_prev = clock64();
+#endif
 
   if (tid == 0) {
     for (int i = 0; i < nst; ++i) mbar_init(&bar_w[i], 1);
     mbar_init(bar_a, kLwWorkWarps);
+    mbar_init(bar_a1, kLwWorkWarps);
     mbar_init(bar_mma, 1);
     fence_mbar_init();
   }
@@ -85,9 +105,10 @@ __global__ void __launch_bounds__(kLwThreads, 1) lw_sage_kernel(const __grid_con
       pdl_launch_dependents();
       const uint32_t idesc = make_idesc_f16(kLwRows, Np);
       const uint32_t lbo = (uint32_t)Np * 16u, sbo = 128u;
-      mbar_wait(bar_a, 0);
+      mbar_wait(bar_a, 0);        // the k-steps of the self half run under the workers' gather
       tc_fence_after();
       for (int q = 0; q < nst; ++q) {
+        if (q == nst / 2) { mbar_wait(bar_a1, 0); tc_fence_after(); }
         mbar_wait(&bar_w[q], 0);
         tc_fence_after();
         const uint32_t b0 = smem_u32(smem + L.off_w + q * stage_bytes);
@@ -102,6 +123,7 @@ __global__ void __launch_bounds__(kLwThreads, 1) lw_sage_kernel(const __grid_con
   } else {
     // ================= workers =================
     pdl_wait();
+    LW_STAMP(0);
     // operand scale 2^(6 - floor(log2 max|x|)) for gradient inputs (exact; keeps both fp16 halves inside fp16's range)
     float ascale = 1.0f, unscale = 1.0f;
     if (a.in_absmax) {
@@ -117,13 +139,75 @@ __global__ void __launch_bounds__(kLwThreads, 1) lw_sage_kernel(const __grid_con
     const int NV = Kp / 4;
     const int R = a.rows;                                       // live rows of this block (<= 128, balanced over the SMs)
     const int64_t rlo = row0, rhi = (row0 + R < a.N) ? row0 + R : a.N;
-    for (int r = wid; r < kLwRows; r += kLwWorkWarps) {
-      const int64_t gr = row0 + r;
-      if (lane < NV) {
-        float4 self = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (gr < rhi) self = *(const float4*)(a.x + gr * a.ldx + 4 * lane);
-        *(float4*)(stage + r * SP + 4 * lane) = self;
+    const int nrows = (int)(rhi - rlo);
+    // the block's slice of the CSR goes to shared memory too (coalesced, one L2 latency for the whole block instead of two
+    // dependent ones per row)
+    if (tid <= nrows) s_rp[tid] = a.rowptr[rlo + tid];
+    if (tid < Np) s_bias[tid] = a.bias ? a.bias[tid] : 0.f;
+    {
+      // all eight rows of the warp are requested before the first is stored (one L2 latency, not eight in turn)
+      constexpr int kRW = kLwRows / kLwWorkWarps;
+      float4 selfv[kRW];
+      float rdv[kRW];
+#pragma unroll
+      for (int k = 0; k < kRW; ++k) {
+        const int64_t gr = row0 + wid + k * kLwWorkWarps;
+        selfv[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        rdv[k] = 0.f;
+        if (gr < rhi && lane < NV) selfv[k] = *(const float4*)(a.x + gr * a.ldx + 4 * lane);
+        if (gr < rhi && lane == 31) rdv[k] = a.rdeg[gr];
       }
+#pragma unroll
+      for (int k = 0; k < kRW; ++k) {
+        const int r = wid + k * kLwWorkWarps;
+        if (lane < NV) *(float4*)(stage + r * SP + 4 * lane) = selfv[k];
+        if (lane == 31) stage[r * SP + 2 * Kp] = rdv[k];                      // pad slot: 1 / deg of the row
+      }
+    }
+    work_bar();
+    LW_STAMP(1);
+    // the column indices are requested now and parked in registers: their latency hides behind the split of the self half
+    const int e0 = s_rp[0];
+    const int ne = s_rp[nrows] - e0, nc = ne < L.ncol ? ne : L.ncol;
+    int colreg[6];
+#pragma unroll
+    for (int u = 0; u < 6; ++u) {
+      const int i = tid + u * kLwWorkThreads;
+      colreg[u] = i < nc ? a.col[e0 + i] : 0;
+    }
+    // ---- phase A (self half): staging -> fp16 split -> tensor memory; its MMAs start while the gather below runs ----------
+    const int q4 = wid & 3, slice = wid >> 2;
+    const int row = q4 * 32 + lane;
+    const uint32_t trow = tbase + ((uint32_t)(q4 * 32) << 16);
+    int range_bad = 0;
+    // a TMEM lane quarter without live rows (balanced blocks hold fewer than 128 rows) is left as it is: accumulator rows
+    // are independent, and nothing of a dead row is read back
+    const bool quarter_live = q4 * 32 < nrows;
+    auto split_groups = [&](int g_begin, int g_end) {
+      for (int g = g_begin + slice; quarter_live && g < g_end; g += 4) {
+        const float4 u0 = *(const float4*)(stage + row * SP + 8 * g), u1 = *(const float4*)(stage + row * SP + 8 * g + 4);
+        const float v[8] = {u0.x * ascale, u0.y * ascale, u0.z * ascale, u0.w * ascale,
+                            u1.x * ascale, u1.y * ascale, u1.z * ascale, u1.w * ascale};
+        uint32_t hi4[4], lo4[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          split_f16x2(v[2 * j], v[2 * j + 1], hi4[j], lo4[j]);
+          if (fabsf(v[2 * j]) >= 60000.f || fabsf(v[2 * j + 1]) >= 60000.f) range_bad = 1;
+        }
+        const uint32_t c = trow + TM_A + (g >> 1) * 16 + (g & 1) * 4;
+        tmem_st4u(c, lo4);
+        tmem_st4u(c + 8, hi4);
+      }
+      tmem_wait_st();
+      tc_fence_before();
+      __syncwarp();
+    };
+    split_groups(0, Kp / 8);
+    if (lane == 0) mbar_arrive(bar_a);
+#pragma unroll
+    for (int u = 0; u < 6; ++u) {
+      const int i = tid + u * kLwWorkThreads;
+      if (i < nc) s_col[i] = colreg[u];
     }
     work_bar();
     // ---- phase G2: aggregated half.  Neighbour rows come from the staged tile (shared memory) when they belong to this
@@ -134,27 +218,31 @@ __global__ void __launch_bounds__(kLwThreads, 1) lw_sage_kernel(const __grid_con
       if (gr < rhi && lane < NV) {
         const float* xb = a.x + 4 * lane;
         const float* sb = stage + 4 * lane;
-        const int b = a.rowptr[gr], e = a.rowptr[gr + 1];
+        const int b = s_rp[r] - e0, e = s_rp[r + 1] - e0;
+        // neighbours in CSR order; a neighbour inside the block comes from shared memory, one outside (a graph that
+        // straddles two blocks) from global memory -- both as predicated loads, so the four visits of an unrolled step are
+        // in flight together whatever their mix
         if (!a.adjoint) {
 #pragma unroll 4
           for (int p = b; p < e; ++p) {
-            const int64_t j = a.col[p];
-            float4 v;
-            if (j >= rlo && j < rhi) v = *(const float4*)(sb + (int)(j - rlo) * SP);
-            else v = *(const float4*)(xb + j * a.ldx);
+            const int64_t j = p < L.ncol ? s_col[p] : a.col[e0 + p];
+            const bool in = j >= rlo && j < rhi;
+            float4 v = *(const float4*)(sb + (in ? (int)(j - rlo) : 0) * SP);
+            if (!in) v = *(const float4*)(xb + j * a.ldx);
             acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
           }
           // x * fl(1 / deg): within one ulp of the reference's division (a division per element costs ~45 instructions here)
-          const float rd = a.rdeg[gr];
+          const float rd = stage[r * SP + 2 * Kp];
           acc.x *= rd; acc.y *= rd; acc.z *= rd; acc.w *= rd;
         } else {
 #pragma unroll 4
           for (int p = b; p < e; ++p) {
-            const int64_t j = a.col[p];
-            const float rj = a.rdeg[j];
-            float4 v;
-            if (j >= rlo && j < rhi) v = *(const float4*)(sb + (int)(j - rlo) * SP);
-            else v = *(const float4*)(xb + j * a.ldx);
+            const int64_t j = p < L.ncol ? s_col[p] : a.col[e0 + p];
+            const bool in = j >= rlo && j < rhi;
+            const int jr = in ? (int)(j - rlo) : 0;
+            float4 v = *(const float4*)(sb + jr * SP);
+            float rj = stage[jr * SP + 2 * Kp];
+            if (!in) { v = *(const float4*)(xb + j * a.ldx); rj = a.rdeg[j]; }
             acc.x = fmaf(v.x, rj, acc.x); acc.y = fmaf(v.y, rj, acc.y); acc.z = fmaf(v.z, rj, acc.z); acc.w = fmaf(v.w, rj, acc.w);
           }
         }
@@ -163,36 +251,16 @@ __global__ void __launch_bounds__(kLwThreads, 1) lw_sage_kernel(const __grid_con
       if (lane < NV) *(float4*)(stage + r * SP + Kp + 4 * lane) = acc;
     }
     work_bar();
-    // ---- phase A: staging -> fp16 split -> tensor memory ---------------------------------------------------
-    const int q4 = wid & 3, slice = wid >> 2;
-    const int row = q4 * 32 + lane;
-    const uint32_t trow = tbase + ((uint32_t)(q4 * 32) << 16);
-    int range_bad = 0;
-    // a TMEM lane quarter without live rows (balanced blocks hold fewer than 128 rows) is left as it is: accumulator rows
-    // are independent, and nothing of a dead row is read back
-    const bool quarter_live = q4 * 32 < (int)(rhi - rlo);
-    for (int g = slice; quarter_live && g < 2 * Kp / 8; g += 4) {
-      const float4 u0 = *(const float4*)(stage + row * SP + 8 * g), u1 = *(const float4*)(stage + row * SP + 8 * g + 4);
-      const float v[8] = {u0.x * ascale, u0.y * ascale, u0.z * ascale, u0.w * ascale,
-                          u1.x * ascale, u1.y * ascale, u1.z * ascale, u1.w * ascale};
-      uint32_t hi4[4], lo4[4];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        split_f16x2(v[2 * j], v[2 * j + 1], hi4[j], lo4[j]);
-        if (fabsf(v[2 * j]) >= 60000.f || fabsf(v[2 * j + 1]) >= 60000.f) range_bad = 1;
-      }
-      const uint32_t c = trow + TM_A + (g >> 1) * 16 + (g & 1) * 4;
-      tmem_st4u(c, lo4);
-      tmem_st4u(c + 8, hi4);
-    }
-    tmem_wait_st();
-    tc_fence_before();
-    __syncwarp();
-    if (lane == 0) mbar_arrive(bar_a);
+    LW_STAMP(2);
+    // ---- phase A (aggregated half) ----------------------------------------------------------------------------
+    split_groups(Kp / 8, 2 * Kp / 8);
+    if (lane == 0) mbar_arrive(bar_a1);
     if (range_bad && a.status) atomicOr(a.status, HEXGNN_ST_FP16_RANGE);
     // ---- phase E -------------------------------------------------------------------------------------
+    LW_STAMP(3);
     mbar_wait(bar_mma, 0);
     tc_fence_after();
+    LW_STAMP(4);
     const int64_t gr = row0 + row;
     const bool live = row < a.rows && gr < a.N;
     float s1 = 0.f, s2 = 0.f, mx = 0.f;
@@ -207,7 +275,7 @@ __global__ void __launch_bounds__(kLwThreads, 1) lw_sage_kernel(const __grid_con
 #pragma unroll
       for (int u = 0; u < 8; ++u) {
         float z = (v[u] + vs[u] * (1.0f / 2048.0f)) * unscale;
-        if (a.bias) z += a.bias[c0 + u];
+        z += s_bias[c0 + u];
         if (a.relu) z = fmaxf(z, 0.f);
         v[u] = z + poison;
       }
@@ -249,6 +317,9 @@ __global__ void __launch_bounds__(kLwThreads, 1) lw_sage_kernel(const __grid_con
       }
     }
   }
+#ifdef HEXGNN_PHASES
+  if (wid < kLwWorkWarps) { LW_STAMP(5); if (tid == 0) atomicAdd(&g_lw_phase[6], 1ull); }
+#endif
   tc_fence_before();
   __syncthreads();
   if (wid == kLwWorkWarps) tmem_dealloc(tbase, TM_COLS);
@@ -475,6 +546,20 @@ int launch_lw_prepare(const int* rowptr, int64_t N, float* degf, unsigned* zero,
   lw_prepare_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(rowptr, N, degf, zero, zero_words);
   HEX_CUDA_CHECK(cudaGetLastError());
   return HEXGNN_OK;
+}
+
+int debug_read_lw_phases(long long* host, int n) {
+#ifdef HEXGNN_PHASES
+  if (n > 8) n = 8;
+  HEX_CUDA_CHECK(cudaMemcpyFromSymbol(host, g_lw_phase, sizeof(long long) * n));
+  unsigned long long z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  HEX_CUDA_CHECK(cudaMemcpyToSymbol(g_lw_phase, z, sizeof(z)));
+  return HEXGNN_OK;
+#else
+  (void)host; (void)n;
+  set_error("debug_phases: the library was built without HEXGNN_PHASES");
+  return HEXGNN_E_UNSUPPORTED;
+#endif
 }
 
 int lw_layer0_blocks(int64_t N) { return (int)((N + kL0Rows - 1) / kL0Rows); }

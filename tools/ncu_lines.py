@@ -17,7 +17,7 @@ for r in rows:
         cur_fn = r[1].split('(')[0].split('::')[-1][:24]; continue
     if r[0] == 'Line No':
         hdr = r
-        ie = hdr.index('Instructions Executed'); iw = hdr.index('L1 Wavefronts Shared'); ism = hdr.index('# Samples')
+        ie = hdr.index('Instructions Executed'); iw = hdr.index('L1 Wavefronts Shared') if 'L1 Wavefronts Shared' in hdr else ie; ism = hdr.index('# Samples')
         continue
     if hdr is None or r[0] == '':
         continue
