@@ -44,9 +44,11 @@ def parse():
     ap.add_argument("--workload", default="play", choices=["play", "empty"],
                     help="play: 256 seeded random-playout positions (mean 77 nodes); empty: 256 empty boards (123 nodes)")
     ap.add_argument("--path", default="auto", choices=["auto", "simt", "tc"])
-    ap.add_argument("--allreduce", default="nccl", choices=["p2p", "nccl"],
-                    help="N > 1: NCCL (default: measured faster for the 1.95 MB gradient), or the library's own one-shot "
-                         "all-reduce kernel over NVLink peer memory")
+    ap.add_argument("--allreduce", default="auto", choices=["auto", "p2p", "pull", "mc", "nccl"],
+                    help="N > 1: auto = the own multimem kernel from 4 ranks on where a multicast address exists (measured: "
+                         "0.643 vs 0.652 ms/step at N = 8, a tie at N = 4, NCCL ahead at N = 2), else NCCL.  NCCL, or the library's own all-reduce over NVLink peer memory -- mc: two-shot in place "
+                         "through the NVSwitch (multimem.ld_reduce / multimem.st), pull: one-shot rank-ordered pull, "
+                         "p2p: mc where a multicast address exists, else pull")
     ap.add_argument("--api", default="train_step", choices=["train_step", "autograd"],
                     help="train_step: model.train_step (hexgnn_train_step: forward + TD loss + backward in one call, the "
                          "three tensor-core kernels overlapped); autograd: model(...) -> ops.td_loss -> loss.backward()")
@@ -270,8 +272,19 @@ def run_fused(args, rank, world, local_rank):
     model = ModernTwoHeaded(HIDDEN, LAYERS, HEAD_LAYERS, path=args.path).to(dev)
     collective = "none"
     if world > 1:
-        collective = "p2p (hexgnn_allreduce_p2p over NVLink peer memory)" if (
-            args.allreduce == "p2p" and model.enable_p2p_allreduce()) else "nccl all_reduce"
+        collective = "nccl all_reduce"
+        if args.allreduce == "auto":
+            args.allreduce = "mc_or_nccl" if world >= 4 else "nccl"
+        if args.allreduce == "mc_or_nccl":
+            try:
+                ok = model.enable_p2p_allreduce(mode="mc")
+            except Exception:  # noqa: BLE001 -- no multicast address on this box: NCCL (every rank takes the same branch)
+                ok = False
+            if ok:
+                collective = "hexgnn_allreduce_mc (own kernel: two-shot in place through the NVSwitch, multimem.ld_reduce / .st)"
+        elif args.allreduce != "nccl" and model.enable_p2p_allreduce(mode={"p2p": "auto"}.get(args.allreduce, args.allreduce)):
+            collective = ("hexgnn_allreduce_mc (own kernel: two-shot in place through the NVSwitch, multimem.ld_reduce / .st)"
+                          if model._p2p["mc"] else "hexgnn_allreduce_p2p (own kernel: one-shot pull over NVLink peer memory)")
     batch = make_batch(args.workload, rank, world)
     hb = batch.pin_memory()                      # HOST copy of the step's inputs (e2e arm)
     db = batch.to(dev)                           # resident copy (value arm)

@@ -62,7 +62,7 @@ EXPORTS = ["hexgnn_abi_version", "hexgnn_last_error", "hexgnn_param_count", "hex
            "hexgnn_profile_enable", "hexgnn_profile_read", "hexgnn_selftest_mma", "hexgnn_debug_phases", "hexgnn_stash_embed", "hexgnn_td_loss", "hexgnn_train_step", "hexgnn_adam_step", "hexgnn_adam_ws_bytes", "hexgnn_collate", "hexgnn_collate_ws_bytes",
            "hexgnn_mask_argmax", "hexgnn_td_target", "hexgnn_forward_big", "hexgnn_allreduce_p2p",
            "hexgnn_noisy_compose", "hexgnn_noisy_grads", "hexgnn_backward_dx",
-           "hexgnn_lw_sizes", "hexgnn_forward_lw", "hexgnn_backward_lw", "hexgnn_forward_static",
+           "hexgnn_lw_sizes", "hexgnn_forward_lw", "hexgnn_backward_lw", "hexgnn_forward_static", "hexgnn_allreduce_mc",
            "hexgnn_hexara_param_count", "hexgnn_hexara_param_offsets", "hexgnn_hexara_sizes", "hexgnn_hexara_forward"]
 
 _lib = None
@@ -129,6 +129,8 @@ def lib():
     l.hexgnn_forward_big.argtypes = [D, p, p, i64, i64, i64, p, i32, i32, i32, p, p, p, sz, p]
     l.hexgnn_allreduce_p2p.restype = C.c_int
     l.hexgnn_allreduce_p2p.argtypes = [p, i32, i64, p, p]
+    l.hexgnn_allreduce_mc.restype = C.c_int
+    l.hexgnn_allreduce_mc.argtypes = [p, p, i32, i32, i64, i32, p, p]
     l.hexgnn_mask_argmax.restype = C.c_int
     l.hexgnn_mask_argmax.argtypes = [p, p, i64, i64, i32, C.c_float, p, p, p]
     l.hexgnn_td_target.restype = C.c_int

@@ -358,6 +358,19 @@ int hexgnn_forward_big(const HexModelDesc* desc, const float* params, const floa
                             (cudaStream_t)stream);
 }
 
+int hexgnn_allreduce_mc(float* mc_buf, int32_t* const* peer_flags, int32_t rank, int32_t world, int64_t n, int32_t epoch,
+                        int32_t* counter, void* stream) {
+  if (!mc_buf || !peer_flags || !counter || world < 1 || world > 64 || rank < 0 || rank >= world || n < 1 || epoch < 1) {
+    set_error("allreduce_mc: bad argument");
+    return HEXGNN_E_BADARG;
+  }
+  if (((uintptr_t)mc_buf & 15) != 0 || n % (4 * (int64_t)world) != 0) {
+    set_error("allreduce_mc: the buffer must be 16-byte aligned and n a multiple of 4 * world (pad it)");
+    return HEXGNN_E_BADARG;
+  }
+  return launch_allreduce_mc(mc_buf, (int* const*)peer_flags, rank, world, n, epoch, (int*)counter, (cudaStream_t)stream);
+}
+
 int hexgnn_allreduce_p2p(const float* const* peer_bufs, int32_t world, int64_t n, float* out, void* stream) {
   if (!peer_bufs || !out || world < 1 || world > 64 || n < 1) { set_error("allreduce_p2p: bad argument"); return HEXGNN_E_BADARG; }
   if (((uintptr_t)out & 15) != 0) { set_error("allreduce_p2p: out must be 16-byte aligned"); return HEXGNN_E_BADARG; }

@@ -240,6 +240,8 @@ int launch_forward_big(const Dims& d, const ParamMap& pm, const float* params, c
                        int64_t B, const void* csr, int tile_rows, int flags, int max_rows, float* out_nodes,
                        float* out_value, float* ws, cudaStream_t st);
 int launch_allreduce_p2p(const float* const* peers_dev, int world, int64_t n, float* out, cudaStream_t st);
+int launch_allreduce_mc(float* mc_buf, int* const* peer_flags_dev, int rank, int world, int64_t n, int epoch, int* counter,
+                        cudaStream_t st);
 int launch_mask_argmax(float* q, const int64_t* ptr, int64_t N, int64_t B, int mask_terminals, float mask_value,
                        float* out_max, int64_t* out_arg, cudaStream_t st);
 int launch_td_target(const float* q_target, const int64_t* best, const float* reward, const float* done, float gamma_n,

@@ -111,6 +111,84 @@ __global__ void __launch_bounds__(256) allreduce_p2p_kernel(const float* const* 
   }
 }
 
+// ---- the same all-reduce through the NVSwitch (two-shot, in place) --------------------------------------------------------
+// The flat gradients sit in a symmetric allocation that is also bound to a MULTICAST address (NVLS).  Rank r owns slice r of
+// the buffer: one `multimem.ld_reduce` per 16 bytes makes the switch fetch that granule from all W GPUs and return the fp32
+// sum, one `multimem.st` writes the sum back into all W buffers.  Per GPU 2 x n / W floats cross its links (the one-shot
+// kernel above pulls W x n).  The block that finishes last then tells every peer "my slice is in your buffer" (release store
+// into the peer's flag word) and waits for the same word from every peer, so kernel completion on a rank means its buffer
+// holds the complete sum.  Each slice is reduced by one rank and broadcast: all ranks end with identical bits.
+__device__ __forceinline__ float4 multimem_ld_reduce_add(const float4* p) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st(float4* p, const float4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+               :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+__device__ __forceinline__ void mc_wait_flags(const int* flags, int world, int want) {
+  if ((int)threadIdx.x < world) {
+    const int* f = flags + threadIdx.x;
+    int v;
+    long long spins = 0;
+    do {
+      asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+      if (++spins > (1ll << 31)) __trap();             // a peer never arrived: fail loudly instead of hanging the box
+    } while (v < want);
+  }
+  __syncthreads();
+}
+
+// Flag protocol (one int32 word per (owner rank, writer rank), values only grow): call number e writes 2e - 1 = "my gradient
+// of this step is in my buffer" before the reduction and 2e = "my slice of the sums is in your buffer" after it.
+__global__ void __launch_bounds__(256) allreduce_mc_kernel(float4* __restrict__ mc, int* const* __restrict__ peer_flags, int rank,
+                                                           int world, int64_t n4, int epoch, int* __restrict__ counter) {
+  __shared__ int last_s;
+  // ---- barrier in: every rank's backward has written its buffer (the writes precede this kernel in stream order) ----
+  if (blockIdx.x == 0 && (int)threadIdx.x < world) {
+    __threadfence_system();
+    asm volatile("st.release.sys.global.s32 [%0], %1;" :: "l"(peer_flags[threadIdx.x] + rank), "r"(2 * epoch - 1) : "memory");
+  }
+  mc_wait_flags(peer_flags[rank], world, 2 * epoch - 1);
+  // ---- this rank's slice: the switch sums the W copies, the sum goes back into all W buffers ----------------------------
+  const int64_t per = n4 / world;                      // n4 is a multiple of world (the host pads the buffer)
+  const int64_t lo = per * rank, hi = lo + per;
+  const int64_t nth = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += 4 * nth) {
+    float4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) if (i + u * nth < hi) v[u] = multimem_ld_reduce_add(mc + i + u * nth);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) if (i + u * nth < hi) multimem_st(mc + i + u * nth, v[u]);
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) last_s = atomicAdd(counter, 1) == (int)gridDim.x - 1;
+  __syncthreads();
+  if (!last_s) return;
+  // ---- barrier out (last block only): kernel completion == every peer's slice has landed in this rank's buffer ----------
+  __threadfence_system();
+  if ((int)threadIdx.x < world)
+    asm volatile("st.release.sys.global.s32 [%0], %1;" :: "l"(peer_flags[threadIdx.x] + rank), "r"(2 * epoch) : "memory");
+  mc_wait_flags(peer_flags[rank], world, 2 * epoch);
+  if (threadIdx.x == 0) *counter = 0;                  // ready for the next call on this stream
+}
+
+int launch_allreduce_mc(float* mc_buf, int* const* peer_flags_dev, int rank, int world, int64_t n, int epoch, int* counter,
+                        cudaStream_t st) {
+  const int64_t n4 = n / 4;
+  const int64_t per = n4 / world;
+  int blocks = (int)((per + 255) / 256);
+  if (blocks < 1) blocks = 1;
+  if (blocks > bwd_grid_ctas()) blocks = bwd_grid_ctas();   // all blocks spin on the barrier in: they must be co-resident
+  allreduce_mc_kernel<<<blocks, 256, 0, st>>>((float4*)mc_buf, peer_flags_dev, rank, world, n4, epoch, counter);
+  HEX_CUDA_CHECK(cudaGetLastError());
+  return HEXGNN_OK;
+}
+
 int launch_allreduce_p2p(const float* const* peers_dev, int world, int64_t n, float* out, cudaStream_t st) {
   const int64_t n4 = n / 4;
   int blocks = (int)((n4 + 255) / 256);

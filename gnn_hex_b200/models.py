@@ -508,7 +508,7 @@ class ModernTwoHeaded(nn.Module):
         if self._p2p is not None:
             # peer-mapped, double-buffered: the backward writes where the peers will read; buffer k is reused two steps
             # later, after the next step's barrier has proven that every rank finished reading it
-            self._flat_grad = self._p2p["bufs"][self._p2p["k"]]
+            self._flat_grad = self._p2p["views"][self._p2p["k"]]
         return self._flat_grad
 
     def _grad_scratch(self):
@@ -621,30 +621,45 @@ class ModernTwoHeaded(nn.Module):
         """The flat fp32 gradient all `p.grad` alias (None before the first backward)."""
         return self._flat_grad
 
-    def enable_p2p_allreduce(self, group=None):
-        """Put the flat gradient into NVLink peer-mapped (symmetric) memory so `allreduce_gradients` can run the
-        library's own one-shot all-reduce kernel (`hexgnn_allreduce_p2p`: every rank reads all peers over NVLink /
-        NVSwitch and sums in rank order) instead of NCCL.  Collective: every rank of `group` must call it, after
-        `.to(device)` and before the first backward.  Returns False (and keeps NCCL) where symmetric memory is
-        unavailable."""
+    def enable_p2p_allreduce(self, group=None, mode="auto"):
+        """Put the flat gradient into NVLink peer-mapped (symmetric) memory so `allreduce_gradients` runs the library's own
+        all-reduce instead of NCCL.  mode "mc" (or "auto" where the allocation has a multicast address): two-shot IN PLACE
+        through the NVSwitch (`hexgnn_allreduce_mc`: multimem.ld_reduce of this rank's slice, multimem.st of the sums into
+        every rank's buffer); mode "pull": the one-shot kernel (`hexgnn_allreduce_p2p`: every rank reads all peers and sums
+        in rank order).  Collective: every rank of `group` must call it, after `.to(device)` and before the first
+        backward.  Returns False (and keeps NCCL) where symmetric memory is unavailable."""
         import torch.distributed as dist
         self._ensure_flat()
         if not (dist.is_initialized() and dist.get_world_size(group) > 1 and self._flat.is_cuda):
             return False
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        n = self._flat.numel()
+        npad = (n + 4 * world - 1) // (4 * world) * (4 * world)
         try:
             import torch.distributed._symmetric_memory as symm
             g = group if group is not None else dist.group.WORLD
             bufs, hdls = [], []
             for _ in range(2):
-                buf = symm.empty(self._flat.numel(), dtype=torch.float32, device=self._flat.device)
+                buf = symm.empty(npad, dtype=torch.float32, device=self._flat.device)
                 hdls.append(symm.rendezvous(buf, g))
                 buf.zero_()
                 bufs.append(buf)
+            flags = symm.empty(max(world, 4), dtype=torch.int32, device=self._flat.device)
+            fhdl = symm.rendezvous(flags, g)
+            flags.zero_()
         except Exception as e:  # noqa: BLE001 -- any failure here means "no peer memory": stay on NCCL, say so
             import warnings
             warnings.warn(f"gnn_hex_b200: symmetric memory unavailable ({e!r}); gradients stay on NCCL all-reduce")
             return False
-        self._p2p = {"bufs": bufs, "hdls": hdls, "red": torch.zeros_like(self._flat), "k": 0}
+        has_mc = all(int(getattr(h, "multicast_ptr", 0) or 0) != 0 for h in hdls)
+        if mode == "mc" and not has_mc:
+            raise _lib.HexGnnError("enable_p2p_allreduce(mode='mc'): the symmetric allocation has no multicast address here")
+        use_mc = has_mc and mode in ("auto", "mc")
+        self._p2p = {"bufs": bufs, "views": [b[:n] for b in bufs], "hdls": hdls, "red": None if use_mc else torch.zeros_like(self._flat),
+                     "k": 0, "mc": use_mc, "flags": flags, "fhdl": fhdl, "epoch": 0, "rank": rank, "npad": npad,
+                     "counter": torch.zeros(1, dtype=torch.int32, device=self._flat.device)}
+        torch.cuda.synchronize(self._flat.device)
+        hdls[0].barrier(channel=0)      # every rank's buffers and flag words are zeroed before anybody signals
         self._flat_grad = None          # next backward adopts a peer-mapped buffer
         for p in self._params_cache:
             p.grad = None
@@ -652,10 +667,11 @@ class ModernTwoHeaded(nn.Module):
 
     def allreduce_gradients(self, group=None):
         """Data-parallel learner step (BASELINE config 5): ONE all-reduce (sum) of the flat gradient; the caller
-        scales its loss by 1/world_size.  After `enable_p2p_allreduce()`: one cross-rank barrier, then
-        `hexgnn_allreduce_p2p` (own kernel over NVLink peer memory, rank-ordered sum) into a private buffer the
-        `p.grad` views are re-pointed to; the two peer-mapped buffers alternate so no second barrier is needed.
-        Gradients accumulated over several backwards (p.grad kept alive) fall back to NCCL.  No reference counterpart."""
+        scales its loss by 1/world_size.  After `enable_p2p_allreduce()`: one cross-rank barrier, then the library's own
+        kernel over NVLink peer memory -- in place through the switch (`hexgnn_allreduce_mc`) or, in "pull" mode,
+        `hexgnn_allreduce_p2p` into a private buffer the `p.grad` views are re-pointed to; the two peer-mapped buffers
+        alternate so no second barrier is needed.  Gradients accumulated over several backwards (p.grad kept alive) fall
+        back to NCCL.  No reference counterpart."""
         import torch.distributed as dist
         if self._flat_grad is None or not dist.is_initialized() or dist.get_world_size(group) <= 1:
             return
@@ -663,10 +679,15 @@ class ModernTwoHeaded(nn.Module):
         if p2p is not None and self._flat_grad.data_ptr() == p2p["bufs"][p2p["k"]].data_ptr():
             k = p2p["k"]
             hdl = p2p["hdls"][k]
-            hdl.barrier(channel=0)      # every rank's backward has written its gradient into its buffer k
-            ops.allreduce_p2p(hdl.buffer_ptrs_dev, hdl.world_size, self._flat_grad.numel(), p2p["red"])
-            self._flat_grad = p2p["red"]          # p.grad now alias the reduced (private) buffer
-            self._point_grads()
+            if p2p["mc"]:
+                p2p["epoch"] += 1       # the kernel carries both barriers (flag words in peer-mapped memory)
+                ops.allreduce_mc(hdl.multicast_ptr, p2p["fhdl"].buffer_ptrs_dev, p2p["rank"], hdl.world_size, p2p["npad"],
+                                 p2p["epoch"], p2p["counter"])          # p.grad already alias buffer k: reduced in place
+            else:
+                hdl.barrier(channel=0)  # every rank's backward has written its gradient into its buffer k
+                ops.allreduce_p2p(hdl.buffer_ptrs_dev, hdl.world_size, self._flat_grad.numel(), p2p["red"])
+                self._flat_grad = p2p["red"]          # p.grad now alias the reduced (private) buffer
+                self._point_grads()
             p2p["k"] = k ^ 1
             self._allreduce_noisy(group)
             return

@@ -479,6 +479,17 @@ def allreduce_p2p(peer_ptrs_dev, world, n, out):
     return out
 
 
+def allreduce_mc(mc_ptr, peer_flags_dev, rank, world, n, epoch, counter):
+    """hexgnn_allreduce_mc: two-shot in-place all-reduce of the symmetric buffers behind the multicast address `mc_ptr`
+    (multimem.ld_reduce / multimem.st through the NVSwitch), cross-rank barriers included."""
+    _require_cuda(counter, "counter")
+    with torch.cuda.device(counter.device):
+        rc = _lib.lib().hexgnn_allreduce_mc(C.c_void_p(int(mc_ptr)), C.c_void_p(int(peer_flags_dev)), int(rank), int(world),
+                                            int(n), int(epoch), _ptr(counter), _stream(counter.device))
+    _lib.check(rc, "hexgnn_allreduce_mc")
+    _count("allreduce_p2p")
+
+
 @torch.no_grad()
 @_on_tensor_device
 def adam_step(desc, flat_params, flat_grad, exp_avg, exp_avg_sq, state, x, lr, betas=(0.9, 0.999), eps=1e-8,

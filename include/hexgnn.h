@@ -332,6 +332,18 @@ int hexgnn_td_target(const float* q_target, const int64_t* best, const float* re
  * rank.  The caller brackets the call with cross-rank barriers: all ranks have written before it, none overwrites its
  * buffer until all have returned from it (torch.distributed._symmetric_memory.barrier in the Python host side). */
 int hexgnn_allreduce_p2p(const float* const* peer_bufs, int32_t world, int64_t n, float* out, void* stream);
+/* The same all-reduce through the NVSwitch, two-shot and IN PLACE (no reference counterpart).  mc_buf = the
+ * MULTICAST (NVLS) address of a symmetric allocation that holds every rank's n floats (16-byte aligned, n a multiple of
+ * 4 * world: pad with zeros).  Rank r reduces slice r with multimem.ld_reduce (the switch adds the W copies in fp32) and
+ * writes the sums into all W buffers with multimem.st; 2n / W floats cross each GPU's links instead of the W * n of the
+ * one-shot pull.  peer_flags: DEVICE array of `world` pointers, entry r = rank r's int32 flag array [world] in peer-mapped
+ * memory (zeroed once); epoch: 1, 2, 3, ... (one more per call, the same on every rank); counter: one device int32, zeroed
+ * once.  Both barriers are inside the kernel (flag words, values only grow): it starts reducing when every rank has reached the
+ * call -- the gradient writes precede it in stream order -- and returns only when every peer's slice has landed in this
+ * rank's buffer.  Every rank must make the same sequence of calls.  Every rank ends with identical bits (each slice is summed
+ * once, by one rank). */
+int hexgnn_allreduce_mc(float* mc_buf, int32_t* const* peer_flags, int32_t rank, int32_t world, int64_t n, int32_t epoch,
+                        int32_t* counter, void* stream);
 
 /* Where forward (with `flags`) leaves the body embedding h_L (`final_conv_acts`, models.py:553) inside the stash:
  * float offset of a row-major [N, row_pitch] block.  (The two kernel paths keep different stash formats.) */

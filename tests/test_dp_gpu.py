@@ -3,7 +3,7 @@
 The sum over ranks of the shard gradients -- every rank runs `train_step` on its node-balanced contiguous shard
 (data.shard_graphs) with the loss scaled by B_local / B_global, then `allreduce_gradients()` -- must equal the 1-GPU gradient
 of the union batch to fp32 summation-order round-off, for NCCL and for the library's own all-reduce over NVLink peer memory
-(`hexgnn_allreduce_p2p`), and every rank must end up with the same bits.  Skipped with fewer than two devices."""
+(`hexgnn_allreduce_p2p` one-shot pull, `hexgnn_allreduce_mc` two-shot through the NVSwitch), and every rank must end up with the same bits.  Skipped with fewer than two devices."""
 import os
 import socket
 import sys
@@ -41,8 +41,15 @@ def _worker(rank, world, port, mode, out):
         action, target, weight = helpers.loss_inputs(union)
         torch.manual_seed(0)
         m = ModernTwoHeaded(110, 15, 2).to(dev)          # same seed on every rank: identical replicas
-        if mode == "p2p":
-            assert m.enable_p2p_allreduce(), "symmetric memory unavailable"
+        if mode in ("pull", "mc"):
+            try:
+                assert m.enable_p2p_allreduce(mode=mode), "symmetric memory unavailable"
+            except Exception as e:  # noqa: BLE001
+                if mode == "mc" and "multicast" in str(e):
+                    out[rank] = ("skip", str(e), 0)
+                    return
+                raise
+            assert m._p2p["mc"] == (mode == "mc")
         a, b = data.shard_by_nodes([int(g.x.shape[0]) for g in gs], world)[rank]
         shard = data.collate(gs[a:b]).to(dev)
         m.zero_grad(set_to_none=True)
@@ -51,6 +58,13 @@ def _worker(rank, world, port, mode, out):
         m.allreduce_gradients()
         torch.cuda.synchronize()
         g_dp = m.flat_gradient.clone()
+        # a second step through the other peer-mapped buffer (they alternate) gives the same reduced gradient again
+        m.zero_grad(set_to_none=True)
+        m.train_step(shard.x, shard.edge_index, shard.batch, shard.ptr, action=action[a:b].to(dev), target=target[a:b].to(dev),
+                     weight=weight[a:b].to(dev), scale=(b - a) / len(gs))
+        m.allreduce_gradients()
+        torch.cuda.synchronize()
+        assert torch.equal(m.flat_gradient, g_dp)
         gathered = [torch.empty_like(g_dp) for _ in range(world)]
         dist.all_gather(gathered, g_dp)
         same_bits = all(torch.equal(gathered[0], t) for t in gathered)
@@ -68,7 +82,7 @@ def _worker(rank, world, port, mode, out):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("mode", ["nccl", "p2p"])
+@pytest.mark.parametrize("mode", ["nccl", "pull", "mc"])
 def test_two_rank_gradient_equals_union_gradient(mode):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two CUDA devices")
@@ -78,6 +92,8 @@ def test_two_rank_gradient_equals_union_gradient(mode):
         mp.spawn(_worker, args=(world, _free_port(), mode, out), nprocs=world, join=True)
         res = dict(out)
     assert set(res) == {0, 1}
+    if res[0][0] == "skip":
+        pytest.skip("no multicast (NVLS) address for symmetric memory on this box: " + res[0][1])
     assert res[0][0] and res[1][0], "ranks hold different reduced gradients"
     assert res[0][2] + res[1][2] == 96 and res[0][2] != 48      # node-balanced, not a graph-count split
     assert res[0][1] is not None and res[0][1] <= 1e-6, res[0][1]

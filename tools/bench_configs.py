@@ -1,7 +1,10 @@
 """Secondary configurations of BASELINE.json (not the headline: bench.py measures configs[1]).  One JSON line each:
   gnn_s     configs[0]  GNN-S (hidden 35, 10+2 layers) fwd+bwd, 256 7x7 positions
   selfplay  configs[2]  GNN-L forward only, 128 11x11 positions, advantages_only + terminal mask + per-graph argmax
-  ragged    configs[3]  GNN-L forward, 256 graphs of mixed 5x5..13x13 boards (ragged CSR)
+  ragged    configs[3]  GNN-L forward, 256 graphs of mixed 5x5..13x13 boards (ragged CSR; layer-at-a-time tensor-core path),
+                        the same batch through train_step, and the mix with 14x14..19x19 boards added
+  norm      SURVEY 8 f4: GNN-L with norm=True (PyG LayerNorm, whole-batch statistics) fwd+bwd, 256 11x11 positions
+  hexara    SURVEY 8 f3: HexAra SAGE_torch_script (hidden 60, 15+2+2 convs) inference, 128 / 256 11x11 positions
   learner   SURVEY 8 f1+f2: the whole Rainbow learner step on GNN-L, 256 + 256 positions (RainbowLearner.train:
             2 CSR builds, 3 forwards, mask/argmax, TD target, train_step, clip + Adam)
 CUDA events, inputs resident, 256 MiB L2 flush between iterations.   python tools/bench_configs.py [iters]"""
@@ -60,14 +63,52 @@ out.append({"config": "selfplay: GNN-L forward (advantages_only) + mask + argmax
             "ms": ms, "graphs_per_s": 128 / ms * 1e3})
 # configs[3]
 b = data.collate(positions.load_positions("pos_mix_5_13_seed1234.npz", maker=1)[:256]); d = b.to(dev)
-m.max_graph_nodes = 256   # 12x12 / 13x13 positions (146 / 171 nodes) take the oversize-graph path
+m.max_graph_nodes = 363   # batches with graphs beyond one 128-row tile run the layer-at-a-time tensor-core path
 def fwd():
     with torch.no_grad():
         return m(d.x, d.edge_index, d.batch, d.ptr)
 ms = timed(fwd)
 status = int(m.last_csr.status.item()) if getattr(m, "last_csr", None) is not None else 0
-out.append({"config": "ragged: GNN-L forward, 256 graphs of 5x5..13x13 boards (oversize graphs via hexgnn_forward_big)", "nodes": int(b.x.shape[0]), "graphs": b.num_graphs,
+out.append({"config": "ragged: GNN-L forward, 256 graphs of 5x5..13x13 boards (hexgnn_forward_lw)", "nodes": int(b.x.shape[0]), "graphs": b.num_graphs,
             "ms": ms, "graphs_per_s": b.num_graphs / ms * 1e3, "device_status": status})
+a, t, w = loss_inputs(b)
+def step_ragged():
+    m.zero_grad(set_to_none=True)
+    m.train_step(d.x, d.edge_index, d.batch, d.ptr, action=a, target=t, weight=w)
+ms = timed(step_ragged)
+out.append({"config": "ragged: GNN-L fwd+bwd (train_step via hexgnn_forward_lw / hexgnn_backward_lw), same batch", "nodes": int(b.x.shape[0]),
+            "graphs": b.num_graphs, "ms": ms, "graphs_per_s": b.num_graphs / ms * 1e3})
+b = data.collate(positions.load_positions("pos_mix_5_13_seed1234.npz", maker=1)[:244] +
+                 positions.load_positions("pos_transfer_14_19_seed1234.npz", maker=1)); d = b.to(dev)
+ms = timed(fwd)
+out.append({"config": "ragged + 14x14..19x19 boards (up to 363 nodes): GNN-L forward, 256 graphs", "nodes": int(b.x.shape[0]),
+            "graphs": b.num_graphs, "ms": ms, "graphs_per_s": b.num_graphs / ms * 1e3})
+# f4: norm=True
+mn = ModernTwoHeaded(110, 15, 2, norm=True).to(dev)
+b = data.collate(positions.load_positions("pos_11x11_seed1234.npz", maker=1)[:256]); d = b.to(dev)
+a, t, w = loss_inputs(b)
+def step_norm():
+    mn.zero_grad(set_to_none=True)
+    mn.train_step(d.x, d.edge_index, d.batch, d.ptr, action=a, target=t, weight=w)
+ms = timed(step_norm)
+out.append({"config": "norm=True: GNN-L fwd+bwd (LayerNorm over the whole batch), 256 11x11 positions", "nodes": int(b.x.shape[0]),
+            "ms": ms, "graphs_per_s": 256 / ms * 1e3})
+def fwd_norm():
+    with torch.no_grad():
+        return mn(d.x, d.edge_index, d.batch, d.ptr)
+ms = timed(fwd_norm)
+out.append({"config": "norm=True: GNN-L forward, 256 11x11 positions", "nodes": int(b.x.shape[0]), "ms": ms, "graphs_per_s": 256 / ms * 1e3})
+# f3: HexAra
+from gnn_hex_b200 import get_current_model
+ara = get_current_model("SAGE", swap_allowed=True).to(dev)
+for count in (128, 256):
+    b = data.collate(positions.load_positions_cpp("pos_11x11_seed1234.npz")[:count]); d = b.to(dev)
+    def predict():
+        with torch.no_grad():
+            return ara(d.x, d.edge_index, d.batch, d.ptr)
+    ms = timed(predict)
+    out.append({"config": f"hexara: SAGE_torch_script (hidden 60, 15+2+2 convs, swap) inference incl. CSR build, {count} 11x11 positions",
+                "nodes": int(b.x.shape[0]), "ms": ms, "graphs_per_s": count / ms * 1e3})
 # learner step (f1 + f2)
 from gnn_hex_b200 import RainbowLearner
 pol, tgt = ModernTwoHeaded(110, 15, 2).to(dev), ModernTwoHeaded(110, 15, 2).to(dev)
