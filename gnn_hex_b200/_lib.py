@@ -25,7 +25,7 @@ STATUS_NAMES = {
     ST_FP16_RANGE: "an activation left the fp16 range of the forward kernel's mixed product scheme (|h| >= 60000): use path='simt'",
 }
 
-ABI_VERSION = 10
+ABI_VERSION = 11
 
 
 class HexModelDesc(C.Structure):
@@ -49,7 +49,8 @@ class HexAraDesc(C.Structure):
 
 
 class HexAraSizes(C.Structure):
-    _fields_ = [("ws_bytes", C.c_int64), ("max_policy_entries", C.c_int64), ("hidden_padded", C.c_int64)]
+    _fields_ = [("ws_bytes", C.c_int64), ("max_policy_entries", C.c_int64), ("hidden_padded", C.c_int64),
+                ("stash_bytes", C.c_int64), ("bwd_ws_bytes", C.c_int64)]
 
 
 class HexCsrLayout(C.Structure):
@@ -63,7 +64,7 @@ EXPORTS = ["hexgnn_abi_version", "hexgnn_last_error", "hexgnn_param_count", "hex
            "hexgnn_mask_argmax", "hexgnn_td_target", "hexgnn_forward_big", "hexgnn_allreduce_p2p",
            "hexgnn_noisy_compose", "hexgnn_noisy_grads", "hexgnn_backward_dx",
            "hexgnn_lw_sizes", "hexgnn_forward_lw", "hexgnn_backward_lw", "hexgnn_forward_static", "hexgnn_allreduce_mc",
-           "hexgnn_hexara_param_count", "hexgnn_hexara_param_offsets", "hexgnn_hexara_sizes", "hexgnn_hexara_forward"]
+           "hexgnn_hexara_param_count", "hexgnn_hexara_param_offsets", "hexgnn_hexara_sizes", "hexgnn_hexara_forward", "hexgnn_hexara_backward"]
 
 _lib = None
 
@@ -149,7 +150,9 @@ def lib():
     l.hexgnn_hexara_sizes.restype = C.c_int
     l.hexgnn_hexara_sizes.argtypes = [A, i64, i64, i64, C.POINTER(HexAraSizes)]
     l.hexgnn_hexara_forward.restype = C.c_int
-    l.hexgnn_hexara_forward.argtypes = [A, p, p, i64, i64, i64, p, p, p, p, p, p, p, sz, p]
+    l.hexgnn_hexara_forward.argtypes = [A, p, p, i64, i64, i64, p, p, p, p, p, p, p, p, sz, p]
+    l.hexgnn_hexara_backward.restype = C.c_int
+    l.hexgnn_hexara_backward.argtypes = [A, p, p, i64, i64, i64, p, p, p, p, p, p, p, p, sz, p]
     l.hexgnn_forward_static.restype = C.c_int
     l.hexgnn_forward_static.argtypes = [D, p, p, i64, i64, i64, p, i32, i32, p, p, p]
     l.hexgnn_debug_phases.restype = C.c_int

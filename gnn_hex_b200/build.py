@@ -7,7 +7,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 # HEXGNN_LIB: build / load another file instead (e.g. a -DHEXGNN_PHASES profiling build beside the product build)
 LIB = os.environ.get("HEXGNN_LIB") or os.path.join(HERE, "libhexgnn.so")
-SOURCES = ["api.cu", "csr_build.cu", "pack.cu", "sage_fwd_simt.cu", "sage_bwd_simt.cu", "tc_selftest.cu", "pack_tc.cu", "sage_fwd_tc.cu", "sage_bwd_tc.cu", "sage_dw_tc.cu", "td_loss.cu", "sage_big.cu", "optim.cu", "collate.cu", "noisy.cu", "lw_sage.cu", "lw_model.cu", "lw_bwd.cu", "api_lw.cu", "api_static.cu", "hexara.cu"]
+SOURCES = ["api.cu", "csr_build.cu", "pack.cu", "sage_fwd_simt.cu", "sage_bwd_simt.cu", "tc_selftest.cu", "pack_tc.cu", "sage_fwd_tc.cu", "sage_bwd_tc.cu", "sage_dw_tc.cu", "td_loss.cu", "sage_big.cu", "optim.cu", "collate.cu", "noisy.cu", "lw_sage.cu", "lw_model.cu", "lw_bwd.cu", "api_lw.cu", "api_static.cu", "hexara.cu", "hexara_bwd.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "--compiler-options", "-fPIC", "-Xptxas", "-v"]
 

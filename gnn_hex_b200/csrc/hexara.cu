@@ -8,61 +8,12 @@
 //   value  = tanh(MLP_v([sum|max|min|mean]_g value_stack(embeds)))
 //   pi     = log_softmax_g( policy_stack(embeds)[non-terminal rows of g]  [+ MLP_s(pooled_g) if swapping is allowed in g] )
 // Launches: weight pack, degrees, layer 0 (CUDA cores), one lw_sage_kernel per further conv (the policy stack's last conv has
-// one output channel: the same kernel with N = 16), one per-graph head kernel.  Inference only.
-#include "lw.cuh"
+// one output channel: the same kernel with N = 16), one per-graph head kernel.  Backward: hexara_bwd.cu.
+#include "hexara.cuh"
 
 namespace hexgnn {
 
 namespace {
-
-constexpr int kAraMaxConvs = 96;
-
-struct AraDims {
-  int H, Hp, H2, Cin, swap;
-  int nl[3];          // layers of the stacks: 0 body, 1 value, 2 policy
-  int nconv;
-};
-struct AraMap {
-  int64_t wl[kAraMaxConvs], bl[kAraMaxConvs], wr[kAraMaxConvs];   // conv index = stack-major: body, value, policy
-  int cin[kAraMaxConvs], cout[kAraMaxConvs];
-  int64_t mlp[2][4];  // [value_linear | swap_linear][layers.0.weight, layers.0.bias, layers.1.weight, layers.1.bias]
-  int64_t total;
-};
-
-bool make_ara_dims(const HexAraDesc* s, AraDims* d) {
-  if (!s || s->hidden < 2 || s->hidden_layers < 1 || s->policy_layers < 1 || s->value_layers < 1 || s->in_channels != 3)
-    return false;
-  d->H = s->hidden;
-  d->Hp = lw_pad16(s->hidden);
-  d->H2 = s->hidden / 2;
-  d->Cin = s->in_channels;
-  d->swap = s->swap_allowed ? 1 : 0;
-  d->nl[0] = s->hidden_layers; d->nl[1] = s->value_layers; d->nl[2] = s->policy_layers;
-  d->nconv = d->nl[0] + d->nl[1] + d->nl[2];
-  return d->nconv <= kAraMaxConvs && d->H2 >= 1;
-}
-
-inline int conv_index(const AraDims& d, int stack, int i) { return (stack > 0 ? d.nl[0] : 0) + (stack > 1 ? d.nl[1] : 0) + i; }
-
-void make_ara_map(const AraDims& d, AraMap* m) {
-  int64_t o = 0;
-  for (int k = 0; k < 3; ++k)
-    for (int i = 0; i < d.nl[k]; ++i) {
-      const int c = conv_index(d, k, i);
-      m->cin[c] = (k == 0 && i == 0) ? d.Cin : d.H;
-      m->cout[c] = (k == 2 && i == d.nl[2] - 1) ? 1 : d.H;
-      m->wl[c] = o; o += (int64_t)m->cout[c] * m->cin[c];
-      m->bl[c] = o; o += m->cout[c];
-      m->wr[c] = o; o += (int64_t)m->cout[c] * m->cin[c];
-    }
-  for (int j = 0; j < 2; ++j) {
-    m->mlp[j][0] = o; o += (int64_t)d.H2 * 4 * d.H;
-    m->mlp[j][1] = o; o += d.H2;
-    m->mlp[j][2] = o; o += d.H2;
-    m->mlp[j][3] = o; o += 1;
-  }
-  m->total = o;
-}
 
 struct AraWs { int64_t degf, zero, bias, img, act, pi, total; int64_t act_stride; };
 AraWs ara_ws(const AraDims& d, const AraMap& m, int64_t N) {
@@ -237,6 +188,8 @@ int hexgnn_hexara_sizes(const HexAraDesc* desc, int64_t N, int64_t E, int64_t B,
   AraMap m;
   make_ara_map(d, &m);
   out->ws_bytes = ara_ws(d, m, N).total;
+  out->stash_bytes = ara_stash_floats(d, N) * 4;
+  out->bwd_ws_bytes = (d.Hp <= kLwMaxK && d.nconv - 2 <= kMaxSage) ? ara_bwd_ws_bytes(d, m, N, B) : 0;
   out->max_policy_entries = (N - 2 * B > 0 ? N - 2 * B : 0) + (d.swap ? B : 0);
   out->hidden_padded = d.Hp;
   return HEXGNN_OK;
@@ -244,7 +197,7 @@ int hexgnn_hexara_sizes(const HexAraDesc* desc, int64_t N, int64_t E, int64_t B,
 
 int hexgnn_hexara_forward(const HexAraDesc* desc, const float* params, const float* x, int64_t N, int64_t E, int64_t B,
                           const void* csr, float* pi, float* value, int64_t* out_graph_indices, int64_t* out_batch_ptr,
-                          float* embeds, void* ws, size_t ws_bytes, void* stream) {
+                          float* embeds, float* stash, void* ws, size_t ws_bytes, void* stream) {
   AraDims d;
   if (!make_ara_dims(desc, &d)) { set_error("hexara_forward: bad model descriptor"); return HEXGNN_E_BADARG; }
   if (!params || !x || !csr || !pi || !value || !out_graph_indices || !out_batch_ptr || !ws || N < 1 || B < 1 || E < 0 ||
@@ -263,9 +216,12 @@ int hexgnn_hexara_forward(const HexAraDesc* desc, const float* params, const flo
   uint8_t* img = wb + W.img;
   float* act[5];
   for (int i = 0; i < 5; ++i) act[i] = (float*)(wb + W.act + i * W.act_stride);
-  float* emb = embeds ? embeds : act[0];
-  float* pi_raw = (float*)(wb + W.pi);
   const int H = d.H, Hp = d.Hp;
+  // with a stash (training) every conv writes its output into its own slot; without, the buffers ping-pong
+  auto slot = [&](int c) { return stash + (int64_t)c * N * Hp; };
+  const int c_emb = conv_index(d, 0, d.nl[0] - 1), c_pi = conv_index(d, 2, d.nl[2] - 1);
+  float* emb = stash ? slot(c_emb) : (embeds ? embeds : act[0]);
+  float* pi_raw = stash ? slot(c_pi) : (float*)(wb + W.pi);
 
   // ---- weight images of every conv but the first ------------------------------------------------------------------
   int64_t img_off[kAraMaxConvs];
@@ -308,15 +264,15 @@ int hexgnn_hexara_forward(const HexAraDesc* desc, const float* params, const flo
     a0.rowptr = cv.rowptr; a0.col = cv.col; a0.degf = degf;
     a0.wl = params + pm.wl[0]; a0.bl = params + pm.bl[0]; a0.wr = params + pm.wr[0];
     a0.H = H; a0.Hp = Hp;
-    a0.out = L == 1 ? emb : act[1]; a0.ldo = Hp;
+    a0.out = L == 1 ? emb : (stash ? slot(0) : act[1]); a0.ldo = Hp;
     a0.relu = L > 1 ? 1 : 0;
     a0.stats = nullptr;
     rc = launch_lw_layer0(a0, st);
     if (rc) return rc;
   }
-  const float* cur = act[1];
+  const float* cur = stash ? slot(0) : act[1];
   for (int s = 1; s < L; ++s) {
-    float* out = s == L - 1 ? emb : act[1 + (s & 1)];
+    float* out = s == L - 1 ? emb : (stash ? slot(s) : act[1 + (s & 1)]);
     rc = sage(conv_index(d, 0, s), cur, out, Hp, s < L - 1);
     if (rc) return rc;
     cur = out;
@@ -324,7 +280,7 @@ int hexgnn_hexara_forward(const HexAraDesc* desc, const float* params, const flo
   // ---- value stack (act[1], act[2]) and policy stack (act[3], act[4]) ------------------------------------------------------
   const float* vout = emb;
   for (int j = 0; j < d.nl[1]; ++j) {
-    float* out = act[1 + (j & 1)];
+    float* out = stash ? slot(conv_index(d, 1, j)) : act[1 + (j & 1)];
     rc = sage(conv_index(d, 1, j), vout, out, Hp, j < d.nl[1] - 1);
     if (rc) return rc;
     vout = out;
@@ -332,7 +288,7 @@ int hexgnn_hexara_forward(const HexAraDesc* desc, const float* params, const flo
   const float* pin = emb;
   for (int j = 0; j < d.nl[2]; ++j) {
     const bool last = j == d.nl[2] - 1;
-    float* out = last ? pi_raw : act[3 + (j & 1)];
+    float* out = last ? pi_raw : (stash ? slot(conv_index(d, 2, j)) : act[3 + (j & 1)]);
     rc = sage(conv_index(d, 2, j), pin, out, last ? 16 : Hp, !last);
     if (rc) return rc;
     pin = out;
@@ -343,7 +299,25 @@ int hexgnn_hexara_forward(const HexAraDesc* desc, const float* params, const flo
   ha.pi = pi; ha.value = value; ha.out_gi = out_graph_indices; ha.out_ptr = out_batch_ptr;
   hexara_head_kernel<<<(unsigned)B, kAhThreads, (size_t)(4 * H + 2 * d.H2 + 16) * sizeof(float), st>>>(ha);
   HEX_CUDA_CHECK(cudaGetLastError());
+  if (stash && embeds) HEX_CUDA_CHECK(cudaMemcpyAsync(embeds, emb, (size_t)N * Hp * 4, cudaMemcpyDeviceToDevice, st));
   return HEXGNN_OK;
+}
+
+int hexgnn_hexara_backward(const HexAraDesc* desc, const float* params, const float* x, int64_t N, int64_t E, int64_t B,
+                           const void* csr, const float* pi, const int64_t* out_batch_ptr, const float* d_pi,
+                           const float* d_value, const float* stash, float* grad_params, void* ws, size_t ws_bytes,
+                           void* stream) {
+  AraDims d;
+  if (!make_ara_dims(desc, &d)) { set_error("hexara_backward: bad model descriptor"); return HEXGNN_E_BADARG; }
+  if (!params || !x || !csr || !pi || !out_batch_ptr || !stash || !grad_params || !ws || N < 1 || B < 1 || E < 0 ||
+      B > 0x7fffffff || (!d_pi && !d_value)) { set_error("hexara_backward: bad argument"); return HEXGNN_E_BADARG; }
+  if (d.Hp > kLwMaxK || d.nconv - 2 > kMaxSage) { set_error("hexara_backward: unsupported shape (hidden %d, %d convs)", d.H, d.nconv); return HEXGNN_E_UNSUPPORTED; }
+  AraMap pm;
+  make_ara_map(d, &pm);
+  const int64_t need = ara_bwd_ws_bytes(d, pm, N, B);
+  if ((int64_t)ws_bytes < need) { set_error("hexara_backward: workspace too small (%zu < %lld)", ws_bytes, (long long)need); return HEXGNN_E_WORKSPACE; }
+  return launch_hexara_backward(d, pm, params, x, N, E, B, csr, pi, out_batch_ptr, d_pi, d_value, stash, grad_params, ws,
+                                (cudaStream_t)stream);
 }
 
 }  // extern "C"

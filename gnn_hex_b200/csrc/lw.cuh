@@ -49,6 +49,7 @@ struct LwSageArgs {
   double* stats;                    // [gridDim.x][2]: sum, sum of squares of `out` over live rows and real channels; or nullptr
   float* agg_out; int lda;          // the aggregated half of the operand rows ([N][lda], columns [0, Kp)), or nullptr
   float* raw_out; int ldr;          // a copy of `out` BEFORE the mask (the embedding-gradient tap), or nullptr
+  int accum;                        // 1: out += result (after mask / ReLU; each element has one writer: deterministic)
   int* status;                      // HEXGNN_ST_* bits
   int rows;                         // set by the launcher: live rows per block (lw_sage_rows)
 };

@@ -346,6 +346,9 @@ constexpr int kDwChunk = 16;
 constexpr int kDwBlkB = kDwChunk * 128;     // bytes of one 32-channel block of a chunk
 
 struct LwDwArgs {
+  const float* xtab[kMaxSage];   // use_tab: operand pointers per work-item layer (X = the conv's input rows [N][Hp],
+  const float* ytab[kMaxSage];   //          Y = its [dpre | dZl] rows [N][2Hp]); item index = blockIdx.x / G
+  int use_tab;
   const float* hs;          // stash base: h[s] = hs + s * N * Hp   (input of layer s = h[s - 1] ...)
   const float* emb2;        // with norm: the input of layer L (after_embed_norm output); else nullptr
   const float* y;           // [Lt][N][2Hp]: Y_s = y + s * N * 2Hp
@@ -381,8 +384,8 @@ __global__ void __launch_bounds__(kDwThreads2, 1) lw_dw_kernel(const __grid_cons
   pdl_wait();
   pdl_launch_dependents();
 
-  const float* X = (a.emb2 && s == a.L) ? a.emb2 : a.hs + (int64_t)(s - 1) * a.N * Hp;
-  const float* Y = a.y + (int64_t)s * a.N * N2;
+  const float* X = a.use_tab ? a.xtab[item / a.G] : (a.emb2 && s == a.L) ? a.emb2 : a.hs + (int64_t)(s - 1) * a.N * Hp;
+  const float* Y = a.use_tab ? a.ytab[item / a.G] : a.y + (int64_t)s * a.N * N2;
 
   if (wid == kDwLoadWarps) {
     if (lane == 0) {
@@ -714,6 +717,31 @@ LwBwdWs lw_bwd_ws(const Dims& d, int64_t N, int64_t B, bool norm) {
 
 int64_t lw_bwd_ws_bytes(const Dims& d, int64_t N, int64_t B, bool norm) { return lw_bwd_ws(d, N, B, norm).total; }
 
+// ---- the weight-gradient kernels for other callers (hexara_bwd.cu) ------------------------------------------------------
+int lw_dw_groups(int nitems) {
+  int g = bwd_grid_ctas() / (nitems > 0 ? nitems : 1);
+  return g < 1 ? 1 : g;
+}
+int64_t lw_dw_rec_floats(int Hp, int nitems) { return (int64_t)nitems * lw_dw_groups(nitems) * (Hp + 1) * 2 * Hp; }
+int launch_lw_dw_tab(const float* const* xs, const float* const* ys, int nitems, int64_t N, int Hp, float* rec, cudaStream_t st) {
+  if (nitems < 1) return HEXGNN_OK;
+  if (nitems > kMaxSage) { set_error("lw_dw: %d layers (max %d)", nitems, kMaxSage); return HEXGNN_E_UNSUPPORTED; }
+  LwDwArgs da = {};
+  for (int i = 0; i < nitems; ++i) { da.xtab[i] = xs[i]; da.ytab[i] = ys[i]; }
+  da.use_tab = 1; da.N = N; da.Hp = Hp; da.L = 0; da.Lt = nitems + 1; da.G = lw_dw_groups(nitems); da.rec = rec;
+  const size_t smem = (size_t)kDwStages2 * 2 * (4 * kDwBlkB + (2 * Hp / 32) * kDwBlkB) + 1024;
+  HEX_CUDA_CHECK(cudaFuncSetAttribute(lw_dw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  return launch_pdl2(lw_dw_kernel, dim3((unsigned)(nitems * da.G)), dim3(kDwThreads2), smem, st, da);
+}
+int lw_dw0_blocks(int64_t N) { return (int)((N + kD0Rows - 1) / kD0Rows); }
+int launch_lw_dw0(const float* x, int ldx, int Cin, int64_t N, const int* rowptr, const int* col, const float* degf,
+                  const float* dpre, int ldd, int Hp, float* part, cudaStream_t st) {
+  LwDw0Args a0;
+  a0.x = x; a0.ldx = ldx; a0.xoff = 0; a0.Cin = Cin; a0.N = N; a0.rowptr = rowptr; a0.col = col; a0.degf = degf;
+  a0.dpre = dpre; a0.ldd = ldd; a0.Hp = Hp; a0.part = part;
+  return launch_pdl2(lw_dw0_kernel, dim3((unsigned)lw_dw0_blocks(N)), dim3(kD0Threads), 0, st, a0);
+}
+
 int launch_backward_lw(const Dims& d, const ParamMap& pm, const float* params, const float* normp, const float* x, int64_t N,
                        int64_t E, int64_t B, const void* csr, int flags, const float* d_nodes, const float* d_value,
                        const float* stash, float* grad_params, float* grad_norm, float* d_embeds, void* ws, cudaStream_t st) {
@@ -832,7 +860,7 @@ int launch_backward_lw(const Dims& d, const ParamMap& pm, const float* params, c
   }
   // ---- weight gradients ---------------------------------------------------------------------------------------------------
   if (Lt > 1) {
-    LwDwArgs da;
+    LwDwArgs da = {};
     da.hs = stash; da.emb2 = emb2; da.y = Y; da.N = N; da.Hp = Hp; da.L = L; da.Lt = Lt; da.G = W.G; da.rec = rec;
     const size_t smem = (size_t)kDwStages2 * 2 * (4 * kDwBlkB + (N2 / 32) * kDwBlkB) + 1024;
     static size_t max_set = 0;

@@ -32,4 +32,15 @@ int launch_backward_lw(const Dims& d, const ParamMap& pm, const float* params, c
                        int64_t E, int64_t B, const void* csr, int flags, const float* d_nodes, const float* d_value,
                        const float* stash, float* grad_params, float* grad_norm, float* d_embeds, void* ws, cudaStream_t st);
 
+// weight-gradient GEMM over a table of (input rows X [N][Hp], [dpre | dZl] rows Y [N][2Hp]) pairs, one per H -> H conv:
+// records rec [nitems][lw_dw_groups][(Hp + 1)][2Hp] (row k < Hp: d W^T rows, row Hp: the bias row; columns [0, Hp) belong to
+// lin_r / the bias, [Hp, 2Hp) to lin_l); first-layer partials part [lw_dw0_blocks][2 Cin + 1][Hp] (rows: lin_l.W[:, k], bias,
+// lin_r.W[:, k])
+int lw_dw_groups(int nitems);
+int64_t lw_dw_rec_floats(int Hp, int nitems);
+int launch_lw_dw_tab(const float* const* xs, const float* const* ys, int nitems, int64_t N, int Hp, float* rec, cudaStream_t st);
+int lw_dw0_blocks(int64_t N);
+int launch_lw_dw0(const float* x, int ldx, int Cin, int64_t N, const int* rowptr, const int* col, const float* degf,
+                  const float* dpre, int ldd, int Hp, float* part, cudaStream_t st);
+
 }  // namespace hexgnn

@@ -290,6 +290,10 @@ __global__ void __launch_bounds__(kLwThreads, 1) lw_sage_kernel(const __grid_con
 #pragma unroll
         for (int u = 0; u < 8; ++u) v[u] = m[u] > 0.f ? v[u] : 0.f;
       }
+      if (a.accum) {
+        const float4 o0 = *(const float4*)(a.out + gr * a.ldo + c0), o1 = *(const float4*)(a.out + gr * a.ldo + c0 + 4);
+        v[0] += o0.x; v[1] += o0.y; v[2] += o0.z; v[3] += o0.w; v[4] += o1.x; v[5] += o1.y; v[6] += o1.z; v[7] += o1.w;
+      }
 #pragma unroll
       for (int u = 0; u < 8; ++u) {
         if (c0 + u >= a.Nout) v[u] = 0.f;

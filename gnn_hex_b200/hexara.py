@@ -3,7 +3,8 @@
 evaluates through `NN_api::predict` (cpp_hex/CrazyAra/nn_api.cpp:14-19).  Same constructor arguments, parameter NAMES
 (`gnn.convs.i.lin_l/lin_r`, `my_modules.{value_head,policy_head}.convs.j...`, `my_modules.{value_linear,swap_linear}.layers.k`)
 and the same 4-tuple from forward, so reference checkpoints load with `load_state_dict`.  All arithmetic runs in libhexgnn.so
-(`hexgnn_hexara_forward`: layer-at-a-time tcgen05 kernels); inference only -- a call that would need gradients raises."""
+(`hexgnn_hexara_forward` / `hexgnn_hexara_backward`: layer-at-a-time tcgen05 kernels): inference, and training through
+autograd (`loss.backward()` fills every `p.grad`, rl_loop/trainer_agent_pytorch.py:245-275)."""
 import ctypes as C
 
 import torch
@@ -26,6 +27,44 @@ class _AraStackParams(nn.Module):
         for i in range(num_layers):
             self.convs.append(_Conv(cin, self.out_channels if i == num_layers - 1 else hidden))
             cin = hidden
+
+
+class _AraFn(torch.autograd.Function):
+    """Autograd node around hexgnn_hexara_forward (with stash) / hexgnn_hexara_backward.  `anchor` (one parameter) makes the
+    outputs require grad; the backward kernel writes the whole flat gradient and every `p.grad` becomes (or receives) its slice."""
+
+    @staticmethod
+    def forward(ctx, model, x, csr, anchor):
+        pi, value, gi, bp, emb, model._ws, stash = ops.hexara_forward(model._desc, model._flat, x, csr,
+                                                                      want_embeds=model.capture_embeds, ws=model._ws,
+                                                                      want_stash=True)
+        ctx.model, ctx.csr, ctx.stash, ctx.flat = model, csr, stash, model._flat
+        ctx.save_for_backward(x, pi, bp)
+        ctx.mark_non_differentiable(gi, bp)
+        ctx.set_materialize_grads(False)
+        model._emb = emb
+        return pi, value, gi, bp
+
+    @staticmethod
+    def backward(ctx, d_pi, d_value, _gi, _bp):
+        model = ctx.model
+        x, pi, bp = ctx.saved_tensors
+        if ctx.flat is not model._flat:
+            raise _lib.HexGnnError("parameters were re-flattened between forward and backward")
+        if d_pi is None and d_value is None:
+            return None, None, None, None
+        grad, model._bws = ops.hexara_backward(model._desc, model._flat, x, ctx.csr, pi, bp, d_pi, d_value, ctx.stash,
+                                               ws=model._bws)
+        for p, (o, n, shp) in zip(model._params_cache, model._slices):
+            if not p.requires_grad:
+                continue
+            g = grad[o:o + n].view(shp)
+            if p.grad is None:
+                p.grad = g
+            else:
+                p.grad = p.grad + g
+        model.flat_gradient = grad
+        return None, None, None, None
 
 
 class SAGETorchScript(nn.Module):
@@ -55,7 +94,10 @@ class SAGETorchScript(nn.Module):
         self._desc = _lib.HexAraDesc(int(hidden_channels), int(hidden_layers), int(policy_layers), int(value_layers),
                                      int(in_channels), 1 if swap_allowed else 0)
         self._flat = None
-        self._ws = None
+        self._ws = self._bws = None
+        self._slices = self._params_cache = None
+        self._emb = None
+        self.flat_gradient = None         # the flat gradient of the last backward (every p.grad is a slice of one)
         self.capture_embeds = False       # True: fill final_conv_acts (torch_script_models.py:314)
         self.last_csr = None
 
@@ -92,6 +134,8 @@ class SAGETorchScript(nn.Module):
         if int(offs[-1]) + ps[-1].numel() != total:
             raise _lib.HexGnnError("hexara: flat parameter size mismatch")
         self._flat = flat
+        self._params_cache = ps
+        self._slices = [(int(o), p.numel(), tuple(p.shape)) for p, o in zip(ps, offs)]
 
     def _apply(self, fn, *args, **kwargs):
         out = super()._apply(fn, *args, **kwargs)
@@ -105,13 +149,16 @@ class SAGETorchScript(nn.Module):
 
     def forward(self, x, edge_index, graph_indices, batch_ptr):
         self._ensure_flat()
-        if torch.is_grad_enabled() and any(p.requires_grad for p in self._ordered_params()):
-            raise _lib.HexGnnError("SAGETorchScript runs inference only (hexgnn_hexara_forward): call it under torch.no_grad() "
-                                   "or freeze the parameters")
         csr = ops.build_csr(edge_index, graph_indices, batch_ptr, num_nodes=int(x.shape[0]))
         self.last_csr = csr
-        pi, value, gi, bp, emb, self._ws = ops.hexara_forward(self._desc, self._flat, x, csr, want_embeds=self.capture_embeds,
-                                                             ws=self._ws)
+        anchor = self._params_cache[0]
+        if torch.is_grad_enabled() and any(p.requires_grad for p in self._params_cache):
+            # training (rl_loop/trainer_agent_pytorch.py:245-275): the activations are stashed for hexgnn_hexara_backward
+            pi, value, gi, bp = _AraFn.apply(self, x, csr, anchor)
+            emb = self._emb
+        else:
+            pi, value, gi, bp, emb, self._ws, _ = ops.hexara_forward(self._desc, self._flat, x, csr,
+                                                                    want_embeds=self.capture_embeds, ws=self._ws)
         self.final_conv_acts = emb[:, :self.hidden_channels] if emb is not None else None
         count = int(x.shape[0]) - 2 * csr.B
         if self.swap_allowed:

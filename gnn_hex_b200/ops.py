@@ -11,7 +11,7 @@ from ._lib import HEXGNN_ADV_ONLY, HEXGNN_SEPARATE, HEXGNN_PATH_SIMT, HEXGNN_PAT
 
 # kernels launched by each C-ABI call (csr: init, hist, scan, fill, sort; forward: pack, fused;
 # backward: pack, fused, reduce, unpack) -- bench.py's `gpu_launches` is read off this counter.
-LAUNCHES = {"build_csr": 1, "forward": 2, "backward": 5, "td_loss": 1, "train_step": 6, "adam_step": 2, "mask_argmax": 1, "td_target": 1, "forward_big": 0, "allreduce_p2p": 1, "noisy": 1, "forward_lw": 0, "backward_lw": 0, "hexara_forward": 0}
+LAUNCHES = {"build_csr": 1, "forward": 2, "backward": 5, "td_loss": 1, "train_step": 6, "adam_step": 2, "mask_argmax": 1, "td_target": 1, "forward_big": 0, "allreduce_p2p": 1, "noisy": 1, "forward_lw": 0, "backward_lw": 0, "hexara_forward": 0, "hexara_backward": 0}
 launch_counter = 0
 NVTX = os.environ.get("HEXGNN_NVTX", "0") == "1"
 
@@ -288,10 +288,10 @@ def lw_backward(desc, flat_params, norm_params, x, csr, flags, d_nodes, d_value,
 
 @torch.no_grad()
 @_on_tensor_device
-def hexara_forward(desc, flat_params, x, csr, want_embeds=False, ws=None):
+def hexara_forward(desc, flat_params, x, csr, want_embeds=False, ws=None, want_stash=False):
     """hexgnn_hexara_forward (HexAra `SAGE_torch_script`, GN0/torch_script_models.py:286-379).  Returns
-    (pi [max entries], value [B], out_graph_indices [max entries] i64, out_batch_ptr [B+1] i64, embeds [N,Hp] or None, ws);
-    out_batch_ptr[B] entries of pi / out_graph_indices are valid."""
+    (pi [max entries], value [B], out_graph_indices [max entries] i64, out_batch_ptr [B+1] i64, embeds [N,Hp] or None, ws,
+    stash or None); out_batch_ptr[B] entries of pi / out_graph_indices are valid."""
     _require_cuda(x, "x")
     _require_cuda(flat_params, "parameters")
     if x.dtype != torch.float32 or x.dim() != 2 or x.shape[1] != 3:
@@ -311,11 +311,36 @@ def hexara_forward(desc, flat_params, x, csr, want_embeds=False, ws=None):
     gi = torch.empty(cap, dtype=torch.int64, device=dev)
     bp = torch.empty(B + 1, dtype=torch.int64, device=dev)
     emb = torch.empty((N, int(sz.hidden_padded)), dtype=torch.float32, device=dev) if want_embeds else None
+    stash = torch.empty(int(sz.stash_bytes) // 4, dtype=torch.float32, device=dev) if want_stash else None
     rc = _lib.lib().hexgnn_hexara_forward(C.byref(desc), _ptr(flat_params), _ptr(x), N, E, B, _ptr(csr.blob), _ptr(pi),
-                                          _ptr(value), _ptr(gi), _ptr(bp), _ptr(emb), _ptr(ws), ws.numel() * 4, _stream(dev))
+                                          _ptr(value), _ptr(gi), _ptr(bp), _ptr(emb), _ptr(stash), _ptr(ws), ws.numel() * 4,
+                                          _stream(dev))
     _lib.check(rc, "hexgnn_hexara_forward")
     _count("hexara_forward")
-    return pi, value, gi, bp, emb, ws
+    return pi, value, gi, bp, emb, ws, stash
+
+
+@torch.no_grad()
+@_on_tensor_device
+def hexara_backward(desc, flat_params, x, csr, pi, out_batch_ptr, d_pi, d_value, stash, grad_out=None, ws=None):
+    """hexgnn_hexara_backward.  Returns (flat gradient [P], ws)."""
+    N, E, B = csr.N, csr.E, csr.B
+    sz = _lib.HexAraSizes()
+    _lib.check(_lib.lib().hexgnn_hexara_sizes(C.byref(desc), N, E, B, C.byref(sz)), "hexgnn_hexara_sizes")
+    dev = x.device
+    x = x.contiguous()
+    if ws is None or ws.numel() * 4 < sz.bwd_ws_bytes or ws.device != dev:
+        ws = torch.empty((sz.bwd_ws_bytes + 3) // 4, dtype=torch.float32, device=dev)
+    if grad_out is None:
+        grad_out = torch.empty(flat_params.numel(), dtype=torch.float32, device=dev)
+    d_pi = d_pi.contiguous().float() if d_pi is not None else None
+    d_value = d_value.contiguous().float() if d_value is not None else None
+    rc = _lib.lib().hexgnn_hexara_backward(C.byref(desc), _ptr(flat_params), _ptr(x), N, E, B, _ptr(csr.blob), _ptr(pi),
+                                           _ptr(out_batch_ptr), _ptr(d_pi), _ptr(d_value), _ptr(stash), _ptr(grad_out),
+                                           _ptr(ws), ws.numel() * 4, _stream(dev))
+    _lib.check(rc, "hexgnn_hexara_backward")
+    _count("hexara_backward")
+    return grad_out, ws
 
 
 LOSS_KINDS = {"mse": 0, "smooth_l1": 1, "huber": 1}

@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define HEXGNN_ABI_VERSION 10
+#define HEXGNN_ABI_VERSION 11
 
 enum {
   HEXGNN_OK = 0,
@@ -229,7 +229,8 @@ int hexgnn_backward_lw(const HexModelDesc* desc, const float* params, const floa
  *                                 number of entries written is out_batch_ptr[B]  (= N - 2B without swap)
  *   value [B] f32                 tanh(value_linear([sum|max|min|mean] pooling of the value stack))
  *   out_graph_indices [max_policy_entries] i64, out_batch_ptr [B+1] i64
- *   embeds [N, hidden_padded] f32 or NULL: the body output (`final_conv_acts`, :314)                                   */
+ *   embeds [N, hidden_padded] f32 or NULL: the body output (`final_conv_acts`, :314)
+ *   stash: NULL for inference; stash_bytes to keep every conv's output for hexgnn_hexara_backward                    */
 typedef struct HexAraDesc {
   int32_t hidden;         /* hidden_channels (60)                        */
   int32_t hidden_layers;  /* body convs (15)                             */
@@ -242,13 +243,24 @@ typedef struct HexAraSizes {
   int64_t ws_bytes;            /* workspace of hexgnn_hexara_forward                     */
   int64_t max_policy_entries;  /* N - 2B (+ B with swap_allowed): size pi / out_graph_indices */
   int64_t hidden_padded;
+  int64_t stash_bytes;         /* training: activation stash written by forward, read by backward */
+  int64_t bwd_ws_bytes;        /* workspace of hexgnn_hexara_backward                    */
 } HexAraSizes;
 int64_t hexgnn_hexara_param_count(const HexAraDesc* desc);
 int32_t hexgnn_hexara_param_offsets(const HexAraDesc* desc, int64_t* offsets, int32_t max_entries);
 int hexgnn_hexara_sizes(const HexAraDesc* desc, int64_t N, int64_t E, int64_t B, HexAraSizes* out);
 int hexgnn_hexara_forward(const HexAraDesc* desc, const float* params, const float* x, int64_t N, int64_t E, int64_t B,
                           const void* csr, float* pi, float* value, int64_t* out_graph_indices, int64_t* out_batch_ptr,
-                          float* embeds, void* ws, size_t ws_bytes, void* stream);
+                          float* embeds, float* stash, void* ws, size_t ws_bytes, void* stream);
+/* Backward of the same network (replaces `combined_loss.backward()` of rl_loop/trainer_agent_pytorch.py:245-275: value MSE
+ * + policy cross-entropy on the module's outputs).  stash = the buffer hexgnn_hexara_forward filled (stash != NULL there;
+ * stash_bytes), pi / out_batch_ptr = that call's outputs, d_pi [out_batch_ptr[B]] and d_value [B] = the loss gradients w.r.t.
+ * pi and value (either may be NULL = zero).  grad_params: flat fp32 in the parameter layout, OVERWRITTEN (parameters the loss
+ * does not reach -- swap_linear without a swap entry -- get zeros).  Deterministic.  ws = bwd_ws_bytes. */
+int hexgnn_hexara_backward(const HexAraDesc* desc, const float* params, const float* x, int64_t N, int64_t E, int64_t B,
+                           const void* csr, const float* pi, const int64_t* out_batch_ptr, const float* d_pi,
+                           const float* d_value, const float* stash, float* grad_params, void* ws, size_t ws_bytes,
+                           void* stream);
 
 /* One learner step in one call (replaces rainbow.py:301-316: Q = model(states); td_est = Q[action + ptr[:-1]];
  * loss = mean(w * l(td_tgt, td_est)); loss.backward()): forward with stash, TD loss, backward and the deterministic

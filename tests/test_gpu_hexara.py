@@ -81,9 +81,59 @@ def test_default_model_full_batch_and_large_boards(swap):
 def test_hexara_argument_checks():
     m = get_current_model("SAGE", hidden_channels=28, hidden_layers=3).to(DEV)
     b = data.collate(positions.load_positions_cpp("pos_7x7_seed1234.npz")[:4]).to(DEV)
-    with pytest.raises(_lib.HexGnnError):          # grad mode: inference only
-        m(b.x, b.edge_index, b.batch, b.ptr)
     with pytest.raises(NotImplementedError):
         get_current_model("SAGE", norm=torch.nn.LayerNorm)
     with torch.no_grad(), pytest.raises(_lib.HexGnnError):
         m(b.x[:, :2].contiguous(), b.edge_index, b.batch, b.ptr)
+
+
+@pytest.mark.parametrize("shape,swap", [((28, 5, 2, 2), True), ((60, 15, 2, 2), False), ((44, 3, 1, 3), True), ((32, 1, 2, 1), True)])
+def test_training_gradients(shape, swap):
+    """`combined_loss.backward()` of the HexAra trainer (rl_loop/trainer_agent_pytorch.py:245-275: value MSE * batch size +
+    policy cross-entropy) through hexgnn_hexara_backward: every parameter gradient against the fp64 oracle; a second backward
+    accumulates; the result is bit-reproducible."""
+    H, L, Lp, Lv = shape
+    o = orc.HexAraOracle(H, L, Lp, Lv, swap_allowed=swap)
+    helpers.set_hash_weights(o, seed=5, gain=1.5)
+    o64 = orc.HexAraOracle(H, L, Lp, Lv, swap_allowed=swap).double()
+    o64.load_state_dict({k: v.double() for k, v in o.state_dict().items()})
+    m = get_current_model("SAGE", hidden_channels=H, hidden_layers=L, policy_layers=Lp, value_layers=Lv, swap_allowed=swap)
+    m.load_state_dict(o.state_dict())
+    m = m.to(DEV)
+    b = data.collate(positions.load_positions_cpp("pos_7x7_seed1234.npz")[:48])
+    d = b.to(DEV)
+    g = torch.Generator().manual_seed(3)
+    y = torch.rand(b.num_graphs, generator=g) * 2 - 1
+
+    def loss_of(model, bb, dt, dev):
+        pi, value, gi, bp = model(bb.x.to(dt), bb.edge_index, bb.batch, bb.ptr)
+        # a seeded target distribution per graph over the policy entries
+        gt = torch.Generator().manual_seed(4)
+        t = torch.rand(pi.shape[0], generator=gt).double()
+        gic = gi.cpu()
+        tsum = torch.zeros(bb.num_graphs, dtype=torch.float64).index_add_(0, gic, t)       # on the CPU: CUDA index_add_ is
+        t = (t / tsum[gic]).to(dt).to(dev)                                                  # an atomic, order-dependent sum
+        policy_loss = -(t * pi).sum() / bb.num_graphs
+        value_loss = torch.nn.functional.mse_loss(value.reshape(-1), y.to(dev).to(dt)) * bb.num_graphs
+        return 0.01 * value_loss + 0.99 * policy_loss
+
+    loss_of(o, b, torch.float32, "cpu").backward()
+    l64 = loss_of(o64, b, torch.float64, "cpu")
+    l64.backward()
+    loss = loss_of(m, d, torch.float32, DEV)
+    loss.backward()
+    assert rel_err(loss, l64) <= REL_TOL
+    glob, worst, name = helpers.grad_errs(m, o, o64)
+    assert glob <= REL_TOL or worst <= 1.0, (glob, worst, name)
+    if not swap:    # without a swap entry the swap MLP is not on the path: the reference leaves its .grad at None, here zeros
+        assert not m.my_modules["swap_linear"].layers[0].weight.grad.any()
+    g1 = m.flat_gradient.clone()
+    loss_of(m, d, torch.float32, DEV).backward()
+    assert torch.equal(m.flat_gradient, g1)                        # the same bits again ...
+    assert torch.equal(m.gnn.convs[0].lin_l.weight.grad, 2 * g1[:m.gnn.convs[0].lin_l.weight.numel()].view_as(m.gnn.convs[0].lin_l.weight))  # ... accumulated
+    opt = torch.optim.Adam(m.parameters(), lr=1e-3)
+    w0 = m.my_modules["policy_head"].convs[-1].lin_l.weight.detach().clone()
+    opt.step()
+    assert not torch.equal(m.my_modules["policy_head"].convs[-1].lin_l.weight.detach(), w0)
+    with torch.no_grad():
+        m(d.x, d.edge_index, d.batch, d.ptr)                       # the kernels see the stepped weights (views of the flat buffer)

@@ -77,5 +77,5 @@ def test_product_holder_names_and_parameter_table(lib_built):
     assert l.hexgnn_hexara_param_count(C.byref(bad)) == -1
     with pytest.raises(NotImplementedError):
         get_current_model("PNA")
-    with pytest.raises(_lib.HexGnnError):      # inference only: refuses a call that would need gradients
+    with pytest.raises(_lib.HexGnnError):      # no CPU fallback: CPU tensors are refused
         m(torch.zeros(4, 3), torch.zeros(2, 0, dtype=torch.long), torch.zeros(4, dtype=torch.long), torch.tensor([0, 4]))

@@ -109,6 +109,15 @@ for count in (128, 256):
     ms = timed(predict)
     out.append({"config": f"hexara: SAGE_torch_script (hidden 60, 15+2+2 convs, swap) inference incl. CSR build, {count} 11x11 positions",
                 "nodes": int(b.x.shape[0]), "ms": ms, "graphs_per_s": count / ms * 1e3})
+yv = torch.rand(256, device=dev) * 2 - 1
+def ara_train():
+    ara.zero_grad(set_to_none=True)
+    pi, value, gi, bp = ara(d.x, d.edge_index, d.batch, d.ptr)
+    loss = 0.01 * torch.nn.functional.mse_loss(value, yv) * 256 - 0.99 * pi.sum() / 256     # trainer_agent_pytorch.py:255-261 shape
+    loss.backward()
+ms = timed(ara_train)
+out.append({"config": "hexara: SAGE_torch_script fwd + loss + bwd (autograd -> hexgnn_hexara_backward) incl. CSR build, 256 11x11 positions",
+            "nodes": int(b.x.shape[0]), "ms": ms, "graphs_per_s": 256 / ms * 1e3})
 # learner step (f1 + f2)
 from gnn_hex_b200 import RainbowLearner
 pol, tgt = ModernTwoHeaded(110, 15, 2).to(dev), ModernTwoHeaded(110, 15, 2).to(dev)

@@ -5,7 +5,7 @@
 
 Each rank takes global_batch / N positions (state and next_state: the committed 11x11 fixture, repeated and rotated per
 rank), runs RainbowLearner.train = TD target (one CSR, two next-state forwards, mask + arg-max), train_step (forward +
-PER-weighted loss + backward, loss scaled by 1/N), ONE NCCL all-reduce of the flat 1.95 MB gradient, clip + Adam.
+PER-weighted loss + backward, loss scaled by 1/N), ONE all-reduce of the flat 1.95 MB gradient (own multimem kernel; HEXGNN_ALLREDUCE=nccl for NCCL), clip + Adam.
 Strong scaling: the global batch is fixed.  CUDA events per step, L2 flushed between steps, max over ranks; rank 0 prints
 one JSON line."""
 import json, os, sys
@@ -45,6 +45,15 @@ done = (torch.rand(per, generator=g) < 0.1).float().to(dev)
 
 torch.manual_seed(0)
 pol, tgt = ModernTwoHeaded(110, 15, 2).to(dev), ModernTwoHeaded(110, 15, 2).to(dev)
+collective = "none"
+if world > 1:
+    collective = "nccl"
+    if os.environ.get("HEXGNN_ALLREDUCE", "mc") == "mc":
+        try:
+            if pol.enable_p2p_allreduce(mode="mc"):
+                collective = "hexgnn_allreduce_mc"
+        except Exception:  # noqa: BLE001 -- no multicast address: NCCL
+            pass
 lrn = RainbowLearner(pol, tgt, lr=1e-4, adam_eps=1.5e-4, max_grad_norm=10.0, gamma=0.97, n_step=2, world_size=world)
 lrn.sync_Q_target()
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
@@ -79,7 +88,7 @@ else:
 status = int(pol.last_csr.status.item())
 if rank == 0:
     print(json.dumps({"config": f"dp learner: RainbowLearner.train, GNN-L, global batch {global_batch} (state + next_state 11x11 "
-                                f"positions) over {world} B200, NCCL all-reduce of the flat gradient, clip + Adam",
+                                f"positions) over {world} B200, {collective} all-reduce of the flat gradient, clip + Adam",
                       "n_gpus": world, "graphs_per_gpu": per, "nodes_per_gpu": int(hs.x.shape[0] + hn.x.shape[0]), "ms_per_step": float(ms),
                       "graphs_per_s": global_batch / float(ms) * 1e3, "scaling": "strong", "replicas_identical": in_step,
                       "loss": float(out["loss"]), "device_status": status}), flush=True)
