@@ -137,3 +137,28 @@ def test_training_gradients(shape, swap):
     assert not torch.equal(m.my_modules["policy_head"].convs[-1].lin_l.weight.detach(), w0)
     with torch.no_grad():
         m(d.x, d.edge_index, d.batch, d.ptr)                       # the kernels see the stepped weights (views of the flat buffer)
+
+
+def test_hexara_single_graph_and_isolated_nodes():
+    """One graph per call (the C++ engine's batch of one, nn_api.cpp:14-19), isolated nodes, a graph of three nodes (the
+    smallest the reference accepts, torch_script_models.py:311): outputs against the fp64 oracle."""
+    o = orc.HexAraOracle(28, 3, 2, 2, swap_allowed=True)
+    helpers.set_hash_weights(o, seed=6, gain=1.5)
+    o64 = orc.HexAraOracle(28, 3, 2, 2, swap_allowed=True).double()
+    o64.load_state_dict({k: v.double() for k, v in o.state_dict().items()})
+    m = get_current_model("SAGE", hidden_channels=28, hidden_layers=3, swap_allowed=True)
+    m.load_state_dict(o.state_dict())
+    m = m.to(DEV)
+    full = positions.load_positions_cpp("pos_7x7_seed1234.npz")
+    e = torch.tensor([[0, 2], [2, 0]], dtype=torch.long)
+    x3 = torch.tensor([[1., 0, 1], [1, 0, 1], [0, 0, 1]])
+    tiny = data.HexGraph(x=x3, edge_index=e)                      # node 1 isolated, swap flag set
+    for gs in ([full[0]], [tiny], [tiny, full[3], tiny]):
+        b = data.collate(gs)
+        d = b.to(DEV)
+        with torch.no_grad():
+            pi, value, gi, bp = m(d.x, d.edge_index, d.batch, d.ptr)
+            r = o64(b.x.double(), b.edge_index, b.batch, b.ptr)
+        assert torch.equal(gi.cpu(), r[2]) and torch.equal(bp.cpu(), r[3])
+        assert float((pi.cpu().double() - r[0]).abs().max()) <= REL_TOL * max(1.0, float(r[0].abs().max()))
+        assert float((value.cpu().double() - r[1]).abs().max()) <= REL_TOL

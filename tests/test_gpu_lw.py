@@ -234,3 +234,45 @@ def test_lw_argument_checks():
         q.sum().backward()
     with pytest.raises(ValueError):
         ModernTwoHeaded(35, 10, norm=True, path="tc")
+
+
+def _tiny_graph(n, edges, maker=1):
+    """A hand-made graph (undirected edge list -> both directions); rows 0, 1 are the terminals."""
+    e = torch.tensor(edges, dtype=torch.long).t().reshape(2, -1)
+    ei = torch.cat([e, e.flip(0)], dim=1)
+    x = torch.zeros(n, 3)
+    x[:, 0] = torch.bincount(ei[1], minlength=n).float() if ei.numel() else 0
+    x[:2, 1] = 1
+    x[:, 2] = maker
+    return data.HexGraph(x=x, edge_index=ei)
+
+
+@pytest.mark.parametrize("norm", [False, True])
+def test_lw_edge_cases_isolated_nodes_single_graph_tiny_batches(norm):
+    """Empty neighbourhoods (mean of nothing = 0, PyG / torch_scatter semantics), a single 3-node graph, a batch far smaller
+    than one 128-row block, node counts that are not multiples of anything: forward and gradients against the fp64 oracle."""
+    o, o64, m = make_pair(35, 4, norm=norm, path="lw")
+    graphs = [_tiny_graph(3, [(0, 2)]),                                   # node 1 isolated
+              _tiny_graph(7, [(0, 2), (2, 3), (3, 1), (4, 5)]),           # node 6 isolated, two components
+              _tiny_graph(5, []),                                          # no edges at all
+              positions.load_positions("pos_7x7_seed1234.npz", maker=1)[0]]
+    for gs in (graphs[:1], graphs):
+        b = data.collate(gs)
+        d = b.to(DEV)
+        n = b.ptr[1:] - b.ptr[:-1]
+        action = (n - 1).clamp(min=0)
+        target = torch.linspace(-0.5, 0.5, b.num_graphs)
+        weight = torch.ones(b.num_graphs)
+        for mod in (o, o64):
+            mod.zero_grad()
+        td_loss_of(o, b, action, target, weight, torch.float32).backward()
+        l64 = td_loss_of(o64, b, action, target, weight, torch.float64)
+        l64.backward()
+        m.zero_grad()
+        loss, td_err, q = m.train_step(d.x, d.edge_index, d.batch, d.ptr, action=action.to(DEV), target=target.to(DEV),
+                                       weight=weight.to(DEV))
+        with torch.no_grad():
+            q64 = o64(b.x.double(), b.edge_index, b.batch, b.ptr)
+        assert int(m.last_csr.status.item()) == 0
+        assert not torch.isnan(q).any() and rel_err(q, q64) <= REL_TOL and rel_err(loss, l64) <= REL_TOL
+        check_grads(m, o, o64)
