@@ -325,8 +325,11 @@ def run_fused(args, rank, world, local_rank):
         loss, td_err = fwd_loss_bwd(b)
         if world > 1:
             model.allreduce_gradients()
-        out_host[:1].copy_(loss.detach().reshape(1), non_blocking=True)
-        out_host[1:].copy_(td_err.detach(), non_blocking=True)
+        if fused_api:
+            out_host.copy_(ops.loss_and_td_err(loss), non_blocking=True)     # loss + TD errors: one buffer, one D2H copy
+        else:
+            out_host[:1].copy_(loss.detach().reshape(1), non_blocking=True)
+            out_host[1:].copy_(td_err.detach(), non_blocking=True)
         return loss
 
     def barrier():

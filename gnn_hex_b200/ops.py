@@ -374,8 +374,10 @@ def fused_train_step(desc, flat_params, x, csr, ptr, action, target, weight=None
     if grad_out is None:
         grad_out = torch.empty(flat_params.numel(), dtype=torch.float32, device=dev)
     q = torch.empty(N, dtype=torch.float32, device=dev)
-    loss = torch.empty(1, dtype=torch.float32, device=dev)
-    td_err = torch.empty(B, dtype=torch.float32, device=dev)
+    # loss and the B TD errors share one buffer: what the learner reads back every step (loss + PER priorities,
+    # rainbow.py:306-309) is ONE device-to-host copy of `loss_and_td_err(loss)`
+    out = torch.empty(1 + B, dtype=torch.float32, device=dev)
+    loss, td_err = out[:1], out[1:]
     stash = torch.empty(sz.stash_bytes // 4, dtype=torch.float32, device=dev)
     rc = _lib.lib().hexgnn_train_step(C.byref(desc), _ptr(flat_params), _ptr(x), N, E, B, _ptr(csr.blob), csr.tile_rows, 0,
                                       _ptr(ptr), _ptr(action), _ptr(target), _ptr(weight), LOSS_KINDS[kind], float(scale),
@@ -384,6 +386,13 @@ def fused_train_step(desc, flat_params, x, csr, ptr, action, target, weight=None
     _lib.check(rc, "hexgnn_train_step")
     _count("train_step")
     return loss.reshape(()), td_err, q, grad_out
+
+
+def loss_and_td_err(loss):
+    """The contiguous [1 + B] device tensor behind the (loss, td_err) pair `fused_train_step` / `model.train_step` return
+    (loss first): one device-to-host copy fetches both."""
+    base = loss._base if loss._base is not None else loss
+    return base
 
 
 class _TDLoss(torch.autograd.Function):
