@@ -125,7 +125,9 @@ __device__ __forceinline__ void csr_scan_dev(CsrView v, int N) {
 __global__ void __launch_bounds__(256) csr_scan_kernel(CsrView v, int N) { csr_scan_dev(v, N); }
 
 // ---- 4. unstable fill with edge ids + greedy tile packing (last block) ----------------------------
-__device__ __forceinline__ void csr_tiles_dev(CsrView v, int B, int tile_rows, int tile_edges) {
+__device__ __forceinline__ void csr_tiles_dev(CsrView v, int B, int tile_rows_packed, int tile_edges) {
+  // low 16 bits: capacity of a tile (MMA M = 128); high 16 bits: rows up to which further graphs are PACKED into an open tile
+  const int tile_rows = tile_rows_packed & 0xffff, pack_rows = (tile_rows_packed >> 16) ? (tile_rows_packed >> 16) : tile_rows;
   {
     // Greedy packing of whole graphs into tiles of <= tile_rows nodes, <= tile_edges edges, <= kMaxTileGraphs graphs:
     // tile starts s_0 = 0, s_{k+1} = next[s_k], where next[i] = first graph that no longer fits a tile opened at graph i
@@ -152,7 +154,7 @@ __device__ __forceinline__ void csr_tiles_dev(CsrView v, int B, int tile_rows, i
       for (int i = threadIdx.x; i < gn; i += blockDim.x) {
         int rows = n_s[i], edges = ne_s[i], cnt = 1, j = i + 1;
         if (rows > tile_rows || edges > tile_edges) status |= HEXGNN_ST_GRAPH_TOO_LARGE;
-        while (j < gl && cnt < kMaxTileGraphs && rows + n_s[j] <= tile_rows && edges + ne_s[j] <= tile_edges) {
+        while (j < gl && cnt < kMaxTileGraphs && rows + n_s[j] <= pack_rows && edges + ne_s[j] <= tile_edges) {
           rows += n_s[j]; edges += ne_s[j]; ++cnt; ++j;
         }
         next_s[i] = gb + j;
@@ -282,6 +284,27 @@ int launch_build_csr(const int64_t* edge_index, int64_t E, const int64_t* batch,
   const int threads = 256;
   auto blocks = [&](int64_t n) { int64_t b = (n + threads - 1) / threads; return (int)(b < 1 ? 1 : (b > 1184 ? 1184 : b)); };
   const int64_t init_n = (N + 1 > B + 1) ? N + 1 : B + 1;
+  // Rows up to which further graphs are packed into an open tile (<= tile_rows).  A batch with fewer than one full round of
+  // 128-row tiles is packed LESS tightly, so that its tiles spread over all SMs (a tile's cost grows with its rows, and an
+  // SM without a tile does nothing): about 1.25 N / #SMs rows, in steps of 16, at least 64.  Measured on GNN-S, 256 7x7
+  // positions (8,139 rows): 0.229 ms (128: 66 tiles) -> 0.202 ms (80).  Batches of a full round or more keep 128 (fewer,
+  // fuller tiles are cheaper there: 0.614 ms at 128, 0.649 at 96, 0.677 at 64 on the headline batch).  HEXGNN_PACK_ROWS pins it.
+  static int pack_env = -1;
+  if (pack_env < 0) {
+    pack_env = 0;
+    if (const char* e = getenv("HEXGNN_PACK_ROWS")) { const int c = atoi(e); if (c >= 1 && c <= tile_rows) pack_env = c; }
+  }
+  int pack_rows = pack_env;
+  if (pack_rows == 0) {
+    const int64_t sms = bwd_grid_ctas();
+    pack_rows = tile_rows;
+    if (N < (int64_t)tile_rows * sms) {
+      int64_t p = (5 * N + 4 * sms - 1) / (4 * sms);
+      p = (p + 15) / 16 * 16;
+      pack_rows = (int)(p < 64 ? 64 : (p > tile_rows ? tile_rows : p));
+    }
+  }
+  int trp = tile_rows | (pack_rows << 16);
   {
     // one cooperative launch when the whole grid can be resident (always, short of ~300 k nodes per call)
     static int coop_max = -1;     // resident 256-thread blocks of the fused kernel on this device, 0 = unsupported
@@ -307,7 +330,7 @@ int launch_build_csr(const int64_t* edge_index, int64_t E, const int64_t* batch,
     if (grid < 2) grid = 2;
     if (coop_max >= 2 && nscan < grid && grid <= coop_max) {
       int Ni = (int)N, Ei = (int)E, Bi = (int)B, te = tile_rows * kEdgeCapPerRow, ns = nscan;
-      void* args[] = {&v, (void*)&edge_index, (void*)&batch, (void*)&ptr, &Ni, &Ei, &Bi, &tile_rows, &te, &ns};
+      void* args[] = {&v, (void*)&edge_index, (void*)&batch, (void*)&ptr, &Ni, &Ei, &Bi, &trp, &te, &ns};
       if (cudaLaunchCooperativeKernel((const void*)csr_build_fused_kernel, dim3(grid), dim3(threads), args, 0, st) == cudaSuccess)
         return HEXGNN_OK;
       (void)cudaGetLastError();   // refused (e.g. a context that cannot guarantee co-residency): use the five-launch path
@@ -317,7 +340,7 @@ int launch_build_csr(const int64_t* edge_index, int64_t E, const int64_t* batch,
   csr_init_kernel<<<blocks(init_n), threads, 0, st>>>(v, batch, ptr, (int)N, (int)B);
   if (E > 0) csr_hist_kernel<<<blocks(E), threads, 0, st>>>(v, edge_index, (int)E, (int)N);
   csr_scan_kernel<<<(int)csr_scan_blocks(N), 256, 0, st>>>(v, (int)N);
-  csr_fill_kernel<<<blocks(E) + 1, threads, 0, st>>>(v, edge_index, (int)E, (int)N, (int)B, tile_rows,
+  csr_fill_kernel<<<blocks(E) + 1, threads, 0, st>>>(v, edge_index, (int)E, (int)N, (int)B, trp,
                                                     tile_rows * kEdgeCapPerRow);
   if (E > 0) csr_rank_kernel<<<blocks(E), threads, 0, st>>>(v, edge_index, (int)E, (int)N);
   HEX_CUDA_CHECK(cudaGetLastError());
