@@ -129,14 +129,24 @@ __device__ __forceinline__ void multimem_st(float4* p, const float4& v) {
                :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 
+__device__ __forceinline__ unsigned long long mc_now_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 __device__ __forceinline__ void mc_wait_flags(const int* flags, int world, int want) {
   if ((int)threadIdx.x < world) {
     const int* f = flags + threadIdx.x;
     int v;
-    long long spins = 0;
+    unsigned spins = 0;
+    unsigned long long t0 = 0;
     do {
       asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
-      if (++spins > (1ll << 31)) __trap();             // a peer never arrived: fail loudly instead of hanging the box
+      if ((++spins & 0xfffu) == 0) {                   // a peer that has not arrived after 60 s never will: fail loudly
+        const unsigned long long now = mc_now_ns();    // instead of hanging the box
+        if (t0 == 0) t0 = now;
+        else if (now - t0 > 60ull * 1000000000ull) __trap();
+      }
     } while (v < want);
   }
   __syncthreads();
