@@ -27,9 +27,10 @@ class RainbowLearner:
         self.loss_fn = "mse" if loss_fn == "mse" else "smooth_l1"   # rainbow.py:84-85
         self.world_size = int(world_size)
         self.max_grad_norm = float(max_grad_norm)
-        if getattr(q_policy, "noisy_dqn", False):
-            # noisy nets: the advantage layer's mu / sigma live outside the flat parameter block FusedAdam walks, so the
-            # optimizer is the reference's own pair (rainbow.py:79,320-326) over the named parameters
+        if getattr(q_policy, "noisy_dqn", False) or getattr(q_policy, "norm", False):
+            # noisy nets / norm=True: the advantage layer's mu / sigma and the LayerNorm weights live outside the flat
+            # parameter block FusedAdam walks, so the optimizer is the reference's own pair (rainbow.py:79,320-326) over
+            # the named parameters
             self.opt = torch.optim.Adam(q_policy.parameters(), lr=lr, eps=adam_eps)
             self._fused_opt = False
         else:

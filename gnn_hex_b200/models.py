@@ -878,6 +878,10 @@ class ModernTwoHeaded(nn.Module):
             raise _lib.HexGnnError("copy_parameters_from: noisy_dqn differs")
         if self.noisy_dqn:
             self._noisy.copy_(other._noisy, non_blocking=True)   # mu, sigma and the epsilon buffers (state_dict has all three)
+        if self.norm != other.norm:
+            raise _lib.HexGnnError("copy_parameters_from: norm differs")
+        if self.norm:
+            self._norm_flat.copy_(other._norm_flat, non_blocking=True)   # the LayerNorm weights live in their own flat block
 
     def simple_forward(self, data):
         if getattr(data, "batch", None) is not None:

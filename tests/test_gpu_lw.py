@@ -276,3 +276,31 @@ def test_lw_edge_cases_isolated_nodes_single_graph_tiny_batches(norm):
         assert int(m.last_csr.status.item()) == 0
         assert not torch.isnan(q).any() and rel_err(q, q64) <= REL_TOL and rel_err(loss, l64) <= REL_TOL
         check_grads(m, o, o64)
+
+
+def test_learner_step_with_norm_model():
+    """RainbowLearner over a norm=True pair (rainbow.py:259-338): the target sync carries the LayerNorm weights, a step runs on
+    the layer-at-a-time path with torch.optim.Adam over the named parameters and changes conv AND norm weights."""
+    from gnn_hex_b200 import RainbowLearner
+    o, _, pol = make_pair(35, 4, norm=True)
+    tgt = ModernTwoHeaded(35, 4, 2, norm=True).to(DEV)
+    lrn = RainbowLearner(pol, tgt, lr=1e-3, adam_eps=1.5e-4, max_grad_norm=10.0, gamma=0.97, n_step=2)
+    lrn.sync_Q_target()
+    assert torch.equal(tgt.gnn.norms[2].weight, pol.gnn.norms[2].weight) and torch.equal(tgt.after_embed_norm.bias, pol.after_embed_norm.bias)
+    gs = positions.load_positions("pos_7x7_seed1234.npz", maker=1)
+    hs, hn = data.collate(gs[:32]), data.collate(gs[32:64])
+    ds, dn = hs.to(DEV), hn.to(DEV)
+    action, _, weight = loss_inputs(hs)
+    reward = torch.zeros(32, device=DEV)
+    done = torch.zeros(32, device=DEV)
+    with torch.no_grad():
+        q_before = pol(ds.x, ds.edge_index, ds.batch, ds.ptr).clone()
+        t_before = tgt(ds.x, ds.edge_index, ds.batch, ds.ptr).clone()
+    assert torch.equal(q_before, t_before)                       # identical replicas after the sync
+    n0 = pol.gnn.norms[1].weight.detach().clone()
+    out = lrn.train(ds, dn, action.to(DEV), reward, done, weight.to(DEV))
+    assert torch.isfinite(out["loss"]) and torch.isfinite(out["grad_norm"])
+    assert not torch.equal(pol.gnn.norms[1].weight.detach(), n0)
+    with torch.no_grad():
+        assert not torch.equal(pol(ds.x, ds.edge_index, ds.batch, ds.ptr), q_before)
+        assert torch.equal(tgt(ds.x, ds.edge_index, ds.batch, ds.ptr), t_before)
