@@ -248,8 +248,27 @@ __global__ void __launch_bounds__(kNbThreads) lw_norm_bwd1_kernel(const __grid_c
   const int64_t row0 = (int64_t)blockIdx.x * kNbRows;
   double S1 = 0.0, S2 = 0.0;
   float dg[4] = {0.f, 0.f, 0.f, 0.f}, db[4] = {0.f, 0.f, 0.f, 0.f};   // channels lane, lane+32, lane+64, lane+96
-  for (int r = wid; r < kNbRows; r += kNbThreads / 32) {
-    const int64_t gr = row0 + r;
+  // the loads of all eight rows of the warp are issued first (one memory latency per block instead of one per row)
+  constexpr int kRW = kNbRows / (kNbThreads / 32);
+  float vd[kRW][4], vx[kRW][4], vm[kRW][4];
+#pragma unroll
+  for (int k = 0; k < kRW; ++k) {
+    const int64_t gr = row0 + wid + k * (kNbThreads / 32);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int c = lane + 32 * j;
+      const bool ok = gr < a.N && c < a.H;
+      vd[k][j] = ok ? a.d[gr * a.ldd + c] : 0.f;
+      vx[k][j] = ok ? a.xin[gr * a.ldx + c] : 0.f;
+      vm[k][j] = (ok && a.mask_src) ? a.mask_src[gr * a.ldm + c] : 1.f;
+    }
+  }
+  float gmv[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) gmv[j] = (lane + 32 * j) < a.H ? gamma[lane + 32 * j] : 0.f;
+#pragma unroll
+  for (int k = 0; k < kRW; ++k) {
+    const int64_t gr = row0 + wid + k * (kNbThreads / 32);
     if (gr >= a.N) break;
     float p1 = 0.f, p2 = 0.f;
 #pragma unroll
@@ -258,11 +277,11 @@ __global__ void __launch_bounds__(kNbThreads) lw_norm_bwd1_kernel(const __grid_c
       if (c >= a.Hp) break;
       float dxh = 0.f;
       if (c < a.H) {
-        float dz = a.d[gr * a.ldd + c];
-        if (a.mask_src && !(a.mask_src[gr * a.ldm + c] > 0.f)) dz = 0.f;
-        const float xh = (a.xin[gr * a.ldx + c] - mu) / s;
+        float dz = vd[k][j];
+        if (!(vm[k][j] > 0.f)) dz = 0.f;
+        const float xh = (vx[k][j] - mu) / s;
         dg[j] += dz * xh; db[j] += dz;
-        dxh = dz * gamma[c];
+        dxh = dz * gmv[j];
         p1 += dxh; p2 += dxh * xh;
       }
       a.d[gr * a.ldd + c] = dxh;
@@ -312,14 +331,31 @@ __global__ void __launch_bounds__(kNbThreads) lw_norm_bwd2_kernel(const __grid_c
   const float mu = st[0], s = st[1], m1 = st[2], m2 = st[3];
   const int64_t row0 = (int64_t)blockIdx.x * kNbRows;
   float mx = 0.f;
-  for (int r = wid; r < kNbRows; r += kNbThreads / 32) {
-    const int64_t gr = row0 + r;
+  constexpr int kRW = kNbRows / (kNbThreads / 32);
+  float vd[kRW][4], vx[kRW][4];
+#pragma unroll
+  for (int k = 0; k < kRW; ++k) {
+    const int64_t gr = row0 + wid + k * (kNbThreads / 32);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int c = lane + 32 * j;
+      const bool ok = gr < a.N && c < a.H;
+      vd[k][j] = ok ? a.d[gr * a.ldd + c] : 0.f;
+      vx[k][j] = ok ? a.xin[gr * a.ldx + c] : 0.f;
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < kRW; ++k) {
+    const int64_t gr = row0 + wid + k * (kNbThreads / 32);
     if (gr >= a.N) break;
-    for (int c = lane; c < a.Hp; c += 32) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int c = lane + 32 * j;
+      if (c >= a.Hp) break;
       float dx = 0.f;
       if (c < a.H) {
-        const float xh = (a.xin[gr * a.ldx + c] - mu) / s;
-        dx = (a.d[gr * a.ldd + c] - m1) / s - xh * m2;
+        const float xh = (vx[k][j] - mu) / s;
+        dx = (vd[k][j] - m1) / s - xh * m2;
       }
       a.out[gr * a.ldo + c] = dx;
       mx = fmaxf(mx, fabsf(dx));

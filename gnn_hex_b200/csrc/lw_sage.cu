@@ -459,13 +459,36 @@ __global__ void __launch_bounds__(kNormThreads) lw_norm_kernel(const __grid_cons
   const float* beta = a.beta[v];
   const int64_t row0 = (int64_t)blockIdx.x * kNormRows;
   float s1 = 0.f, s2 = 0.f;
-  for (int r = wid; r < kNormRows; r += kNormThreads / 32) {
-    const int64_t gr = row0 + r;
+  // all loads of the warp's eight rows are issued before the first value is used (one memory latency per block, not eight)
+  constexpr int kRW = kNormRows / (kNormThreads / 32), kCL = kLwMaxK / 32 + 1;
+  float vin[kRW][kCL];
+#pragma unroll
+  for (int k = 0; k < kRW; ++k) {
+    const int64_t gr = row0 + wid + k * (kNormThreads / 32);
+#pragma unroll
+    for (int j = 0; j < kCL; ++j) {
+      const int c = lane + 32 * j;
+      vin[k][j] = (gr < a.N && c < a.H) ? a.in[gr * a.ldi + c] : 0.f;
+    }
+  }
+  float gm[kCL], bt[kCL];
+#pragma unroll
+  for (int j = 0; j < kCL; ++j) {
+    const int c = lane + 32 * j;
+    gm[j] = c < a.H ? gamma[c] : 0.f;
+    bt[j] = c < a.H ? beta[c] : 0.f;
+  }
+#pragma unroll
+  for (int k = 0; k < kRW; ++k) {
+    const int64_t gr = row0 + wid + k * (kNormThreads / 32);
     if (gr >= a.N) break;
-    for (int c = lane; c < a.Hp; c += 32) {
+#pragma unroll
+    for (int j = 0; j < kCL; ++j) {
+      const int c = lane + 32 * j;
+      if (c >= a.Hp) break;
       float y = 0.f;
       if (c < a.H) {
-        y = ((a.in[gr * a.ldi + c] - mu) / sd) * gamma[c] + beta[c];
+        y = ((vin[k][j] - mu) / sd) * gm[j] + bt[j];
         if (a.relu) y = fmaxf(y, 0.f);
         s1 += y; s2 += y * y;
       }
