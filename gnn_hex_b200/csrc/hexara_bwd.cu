@@ -284,39 +284,43 @@ __global__ void __launch_bounds__(kV0Threads) ara_reduce_w0_kernel(const __grid_
       if (kb + 8 * u < H2) w0[(int64_t)(kb + 8 * u) * 4 * H + q0 + ql] = acc[u];
   }
 }
+// one warp per output: lane l adds elements l, l + 32, ... in order, then a butterfly over the lanes (fixed order)
+__device__ __forceinline__ float warp_strided_sum(const float* p, int64_t stride, int n, int lane) {
+  float t = 0.f;
+#pragma unroll 4
+  for (int i = lane; i < n; i += 32) t += p[(int64_t)i * stride];
+  return wsum(t);
+}
 __global__ void ara_reduce_small_kernel(const __grid_constant__ AraReduceArgs a) {
   pdl_wait();
   const int H = a.d.H, Hp = a.d.Hp, H2 = a.d.H2, Cin = a.d.Cin;
   const AraRec R = ara_rec(a.d);
-  const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gsz = gridDim.x * blockDim.x;
+  const int lane = threadIdx.x & 31;
+  const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = (gridDim.x * blockDim.x) >> 5;
   // MLP biases and output layers: sums of record entries over the graphs
-  for (int i = gtid; i < 2 * (2 * H2 + 1); i += gsz) {
+  for (int i = gw; i < 2 * (2 * H2 + 1); i += nw) {
     const int j = i / (2 * H2 + 1), r = i - j * (2 * H2 + 1);
     int off; float* dst;
     if (r < H2) { off = (j == 0 ? R.dtv : R.dts) + r; dst = a.grad + a.pm.mlp[j][1] + r; }
     else if (r < 2 * H2) { off = (j == 0 ? R.gv1 : R.gs1) + (r - H2); dst = a.grad + a.pm.mlp[j][2] + (r - H2); }
     else { off = R.misc + j; dst = a.grad + a.pm.mlp[j][3]; }
-    float s = 0.f;
-#pragma unroll 8
-    for (int g = 0; g < a.B; ++g) s += a.hrec[(int64_t)g * R.total + off];
-    *dst = s;
+    const float s = warp_strided_sum(a.hrec + off, R.total, a.B, lane);
+    if (lane == 0) *dst = s;
   }
   // first conv (Cin -> H)
-  for (int i = gtid; i < (2 * Cin + 1) * H; i += gsz) {
+  for (int i = gw; i < (2 * Cin + 1) * H; i += nw) {
     const int row = i / H, c = i - row * H;
-    float s = 0.f;
-#pragma unroll 8
-    for (int b = 0; b < a.nblk0; ++b) s += a.part0[((int64_t)b * (2 * Cin + 1) + row) * Hp + c];
+    const float s = warp_strided_sum(a.part0 + (int64_t)row * Hp + c, (int64_t)(2 * Cin + 1) * Hp, a.nblk0, lane);
+    if (lane != 0) continue;
     if (row < Cin) a.grad[a.pm.wl[0] + (int64_t)c * Cin + row] = s;
     else if (row == Cin) a.grad[a.pm.bl[0] + c] = s;
     else a.grad[a.pm.wr[0] + (int64_t)c * Cin + (row - Cin - 1)] = s;
   }
   // 1-channel policy conv
-  for (int i = gtid; i < 2 * H + 1; i += gsz) {
+  for (int i = gw; i < 2 * H + 1; i += nw) {
     const int row = i / H, k = i - row * H;     // row 0: lin_r.W[0][k], 1: lin_l.W[0][k], 2 (k == 0): bias
-    float s = 0.f;
-#pragma unroll 8
-    for (int b = 0; b < a.nblkp; ++b) s += a.partp[((int64_t)b * 3 + row) * Hp + k];
+    const float s = warp_strided_sum(a.partp + (int64_t)row * Hp + k, (int64_t)3 * Hp, a.nblkp, lane);
+    if (lane != 0) continue;
     if (row == 0) a.grad[a.pm.wr[a.c_pi] + k] = s;
     else if (row == 1) a.grad[a.pm.wl[a.c_pi] + k] = s;
     else a.grad[a.pm.bl[a.c_pi]] = s;
@@ -475,7 +479,7 @@ int launch_hexara_backward(const AraDims& d, const AraMap& pm, const float* para
   if (d.H2 > kV0K) { set_error("hexara_backward: hidden=%d not supported by the MLP reduction", H); return HEXGNN_E_UNSUPPORTED; }
   rc = launch_pdl3(ara_reduce_w0_kernel, dim3((unsigned)((4 * H + kV0Q - 1) / kV0Q), 2), dim3(kV0Threads), 0, st, ra);
   if (rc) return rc;
-  return launch_pdl3(ara_reduce_small_kernel, dim3(64), dim3(128), 0, st, ra);
+  return launch_pdl3(ara_reduce_small_kernel, dim3((unsigned)bwd_grid_ctas()), dim3(256), 0, st, ra);
 }
 
 }  // namespace hexgnn

@@ -670,30 +670,36 @@ __global__ void __launch_bounds__(kV0Threads) lw_reduce_v0w_kernel(const __grid_
   }
 }
 
+// sum of n elements p[0], p[stride], ... by one warp: lane l adds elements l, l + 32, ... in order, then a butterfly over
+// the lanes -- a fixed order (deterministic), and the loads of a lane are independent (no serial latency chain)
+__device__ __forceinline__ float warp_strided_sum(const float* p, int64_t stride, int n, int lane) {
+  float t = 0.f;
+#pragma unroll 4
+  for (int i = lane; i < n; i += 32) t += p[(int64_t)i * stride];
+  return wsum(t);
+}
 __global__ void lw_reduce_small_kernel(const __grid_constant__ LwReduceArgs a) {
   pdl_wait();
   const int H = a.d.H, Hp = a.d.Hp, H2 = a.d.H2;
   const int head = (a.x[2] == 1.0f) ? 0 : 1;
   const HeadRec R = head_rec(a.d);
-  const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gsz = gridDim.x * blockDim.x;
-  for (int i = gtid; i < H + 1 + H2 + H2 + 1; i += gsz) {
+  const int lane = threadIdx.x & 31;
+  const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = (gridDim.x * blockDim.x) >> 5;   // one warp per output
+  for (int i = gw; i < H + 1 + H2 + H2 + 1; i += nw) {
     int off; float* dst;
     if (i < H) { off = R.glin + i; dst = a.grad + a.pm.lin_w[head] + i; }
     else if (i == H) { off = R.glinb; dst = a.grad + a.pm.lin_b[head]; }
     else if (i < H + 1 + H2) { off = R.dt + (i - H - 1); dst = a.grad + a.pm.v0_b[head] + (i - H - 1); }
     else if (i < H + 1 + 2 * H2) { off = R.gv1 + (i - H - 1 - H2); dst = a.grad + a.pm.v1_w[head] + (i - H - 1 - H2); }
     else { off = R.gv1b; dst = a.grad + a.pm.v1_b[head]; }
-    float t = 0.f;
-#pragma unroll 8
-    for (int g = 0; g < a.B; ++g) t += a.hrec[(int64_t)g * R.total + off];
-    *dst = t;
+    const float t = warp_strided_sum(a.hrec + off, R.total, a.B, lane);
+    if (lane == 0) *dst = t;
   }
   // layer 0: partials [nblk0][2 Cin + 1][Hp], Cin = 2: rows 0,1 = lin_l.W[:, k], 2 = bias, 3,4 = lin_r.W[:, k]
-  for (int i = gtid; i < 5 * H; i += gsz) {
+  for (int i = gw; i < 5 * H; i += nw) {
     const int row = i / H, c = i - row * H;
-    float t = 0.f;
-#pragma unroll 8
-    for (int b = 0; b < a.nblk0; ++b) t += a.part0[((int64_t)b * 5 + row) * Hp + c];
+    const float t = warp_strided_sum(a.part0 + (int64_t)row * Hp + c, (int64_t)5 * Hp, a.nblk0, lane);
+    if (lane != 0) continue;
     if (row < 2) a.grad[sage_wl(a.pm, 0, 0) + (int64_t)c * 2 + row] = t;
     else if (row == 2) a.grad[sage_bl(a.pm, 0, 0, H) + c] = t;
     else a.grad[sage_wr(a.pm, 0, 0, H) + (int64_t)c * 2 + (row - 3)] = t;
@@ -701,13 +707,11 @@ __global__ void lw_reduce_small_kernel(const __grid_constant__ LwReduceArgs a) {
   // LayerNorm affine gradients: slot j of gb_part -> norm index (the taken head's variant for head norms)
   if (a.gnorm) {
     const int L = a.d.L, Lh = a.d.Lh;
-    for (int i = gtid; i < a.n_norm * 2 * H; i += gsz) {
+    for (int i = gw; i < a.n_norm * 2 * H; i += nw) {
       const int j = i / (2 * H), rem = i - j * 2 * H, which = rem / H, c = rem - which * H;
-      float t = 0.f;
-#pragma unroll 8
-      for (int b = 0; b < a.nbn; ++b) t += a.gb_part[(((int64_t)j * a.nbn + b) * 2 + which) * Hp + c];
+      const float t = warp_strided_sum(a.gb_part + ((int64_t)j * a.nbn * 2 + which) * Hp + c, (int64_t)2 * Hp, a.nbn, lane);
       const int idx = j <= L ? j : j + head * Lh;            // slots: body 0..L-1, after_embed L, head layers L+1..L+Lh
-      a.gnorm[((int64_t)idx * 2 + which) * H + c] = t;
+      if (lane == 0) a.gnorm[((int64_t)idx * 2 + which) * H + c] = t;
     }
   }
 }
@@ -925,7 +929,7 @@ int launch_backward_lw(const Dims& d, const ParamMap& pm, const float* params, c
   if (d.H2 > kV0K) { set_error("backward_lw: hidden=%d not supported by the value-MLP reduction", H); return HEXGNN_E_UNSUPPORTED; }
   rc = launch_pdl2(lw_reduce_v0w_kernel, dim3((unsigned)((4 * H + kV0Q - 1) / kV0Q)), dim3(kV0Threads), 0, st, ra);
   if (rc) return rc;
-  rc = launch_pdl2(lw_reduce_small_kernel, dim3(64), dim3(128), 0, st, ra);
+  rc = launch_pdl2(lw_reduce_small_kernel, dim3((unsigned)bwd_grid_ctas()), dim3(256), 0, st, ra);
   return rc;
 }
 
