@@ -304,3 +304,30 @@ def test_learner_step_with_norm_model():
     with torch.no_grad():
         assert not torch.equal(pol(ds.x, ds.edge_index, ds.batch, ds.ptr), q_before)
         assert torch.equal(tgt(ds.x, ds.edge_index, ds.batch, ds.ptr), t_before)
+
+
+def test_ragged_transfer_batch_full_size():
+    """BASELINE configs[3] at full size: 256 graphs of 5x5 .. 13x13 boards (3 .. 171 nodes, 14,646 rows) through the default
+    route for such batches (max_graph_nodes > 128 -> layer-at-a-time path): Q against the fp64 oracle; a permutation of the
+    GRAPH order permutes Q (graphs are independent; blocks are cut differently, so equality is to round-off)."""
+    o, o64, m = make_pair(110, 15, gain=1.7, max_graph_nodes=256)
+    gs = positions.load_positions("pos_mix_5_13_seed1234.npz", maker=1)
+    assert len(gs) == 256
+    b = data.collate(gs)
+    d = b.to(DEV)
+    with torch.no_grad():
+        q = m(d.x, d.edge_index, d.batch, d.ptr)
+        q64 = o64(b.x.double(), b.edge_index, b.batch, b.ptr)
+    assert int(m.last_csr.status.item()) == 0 and int((b.ptr[1:] - b.ptr[:-1]).max()) > 128
+    assert rel_err(q, q64) <= REL_TOL
+    perm = torch.randperm(256, generator=torch.Generator().manual_seed(9)).tolist()
+    b2 = data.collate([gs[i] for i in perm])
+    d2 = b2.to(DEV)
+    with torch.no_grad():
+        q2 = m(d2.x, d2.edge_index, d2.batch, d2.ptr).cpu()
+    qc = q.cpu()
+    for k in (0, 17, 101, 255):
+        g = perm[k]
+        a = qc[int(b.ptr[g]):int(b.ptr[g + 1])]
+        c = q2[int(b2.ptr[k]):int(b2.ptr[k + 1])]
+        assert float((a - c).abs().max()) <= REL_TOL * float(qc.abs().max())
