@@ -91,3 +91,24 @@ def _backward(ctx, d_nodes, d_value, d_stash):
 
 
 fused_forward.register_autograd(_backward, setup_context=_setup_context)
+
+
+# ---- HexAra network: the op a TorchScript / C++ front end binds instead of the traced SAGE_torch_script ----
+@torch.library.custom_op("hexgnn::hexara_forward", mutates_args=(), device_types="cuda")
+def hexara_forward(params: Tensor, x: Tensor, edge_index: Tensor, graph_indices: Tensor, batch_ptr: Tensor, hidden: int,
+                   hidden_layers: int, policy_layers: int, value_layers: int,
+                   swap_allowed: bool = False) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    """`SAGE_torch_script.forward(x, edge_index, graph_indices, batch_ptr)` (GN0/torch_script_models.py:309-379) on the flat
+    parameter buffer (`SAGETorchScript.flat_parameters`): (pi, value, output_graph_indices, output_batch_ptr).  pi and
+    output_graph_indices have the CAPACITY length N - 2B (+ B with swap_allowed); output_batch_ptr[-1] entries are valid."""
+    desc = _lib.HexAraDesc(int(hidden), int(hidden_layers), int(policy_layers), int(value_layers), 3, 1 if swap_allowed else 0)
+    csr = ops.build_csr(edge_index, graph_indices, batch_ptr, num_nodes=int(x.shape[0]), num_graphs=int(batch_ptr.shape[0]) - 1)
+    pi, value, gi, bp, _, _, _ = ops.hexara_forward(desc, params.contiguous(), x, csr)
+    return pi, value, gi, bp
+
+
+@hexara_forward.register_fake
+def _(params, x, edge_index, graph_indices, batch_ptr, hidden, hidden_layers, policy_layers, value_layers, swap_allowed=False):
+    N, B = int(x.shape[0]), int(batch_ptr.shape[0]) - 1
+    cap = max(N - 2 * B, 0) + (B if swap_allowed else 0)
+    return (x.new_empty(cap), x.new_empty(B), batch_ptr.new_empty(cap), batch_ptr.new_empty(B + 1))

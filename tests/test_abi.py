@@ -78,6 +78,12 @@ def test_custom_ops_registered_with_fake_kernels(lib_built):
         assert st0.numel() == 0
         g = torch.ops.hexgnn.fused_backward(params, x, csr, st, qn, None, 500, 4, 35, 10, 2, 128, 0)
         assert g.shape == (P,)
+        # HexAra network: capacity shapes of the 4-tuple (N - 2B entries, + B with swap)
+        gi = torch.empty(100, dtype=torch.int64, device="cuda")
+        pa = torch.empty(1000, device="cuda")
+        pi, v, ogi, obp = torch.ops.hexgnn.hexara_forward(pa, x, ei, gi, ptr, 60, 15, 2, 2, True)
+        assert pi.shape == (100 - 8 + 4,) and v.shape == (4,) and ogi.dtype == torch.int64 and obp.shape == (5,)
+        assert torch.ops.hexgnn.hexara_forward(pa, x, ei, gi, ptr, 60, 15, 2, 2, False)[0].shape == (92,)
 
 
 def test_deepcopy_and_pickle_reflatten(lib_built):

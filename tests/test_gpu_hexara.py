@@ -162,3 +162,14 @@ def test_hexara_single_graph_and_isolated_nodes():
         assert torch.equal(gi.cpu(), r[2]) and torch.equal(bp.cpu(), r[3])
         assert float((pi.cpu().double() - r[0]).abs().max()) <= REL_TOL * max(1.0, float(r[0].abs().max()))
         assert float((value.cpu().double() - r[1]).abs().max()) <= REL_TOL
+
+
+def test_hexara_custom_op_matches_the_module():
+    """torch.ops.hexgnn.hexara_forward (the functional face a TorchScript / C++ front end binds) == the module, bit for bit."""
+    m = get_current_model("SAGE", hidden_channels=28, hidden_layers=4, swap_allowed=True).to(DEV)
+    b = data.collate(positions.load_positions_cpp("pos_7x7_seed1234.npz")[:12]).to(DEV)
+    with torch.no_grad():
+        pi, value, gi, bp = m(b.x, b.edge_index, b.batch, b.ptr)
+        pi2, value2, gi2, bp2 = torch.ops.hexgnn.hexara_forward(m.flat_parameters, b.x, b.edge_index, b.batch, b.ptr, 28, 4, 2, 2, True)
+    n = int(bp[-1])
+    assert torch.equal(bp, bp2) and torch.equal(value, value2) and torch.equal(pi, pi2[:n]) and torch.equal(gi, gi2[:n])
